@@ -1,0 +1,237 @@
+"""Synthetic inputs for the EAM + TTM hot path.
+
+Everything here is host-side set-up, not the hot path:
+
+* analytic Johnson-style nearest-neighbour EAM functions tabulated in IMD potential
+  format 2 (reader: reference imd_potential.c:394-466) -- ``write_pot_table2`` /
+  ``read_pot_table2``; the in-memory form mirrors ``pot_table_t`` (types.h:537-549),
+  including the shift-to-zero of radial tables (imd_potential.c:441-452) and the two
+  extrapolated rows of ``init_threepoint`` (imd_potential.c:1260-1276);
+* fcc lattices in the order and placement of the reference generator ``init_cubic``
+  (imd_generate.c:291-586) is NOT reproduced bit for bit -- parity inputs come from the
+  reference's own dumps (tests/golden); these lattices feed bench.py and property tests;
+* IMD parameter files for the reference binary (keywords: imd_param.c:314-3722).
+"""
+from __future__ import annotations
+
+import dataclasses
+import io
+import os
+from typing import Dict, Optional, Sequence, Tuple
+
+import numpy as np
+
+
+# ----------------------------------------------------------------------------- tables
+
+@dataclasses.dataclass
+class PotTable:
+    """Mirror of the reference's ``pot_table_t`` (types.h:537-549), ncols columns."""
+    begin: np.ndarray      # [ncols]
+    end: np.ndarray        # [ncols]
+    step: np.ndarray       # [ncols]
+    invstep: np.ndarray    # [ncols]
+    len: np.ndarray        # [ncols] int32
+    maxsteps: int
+    table: np.ndarray      # [(maxsteps+2), ncols] float64, C order
+
+    @property
+    def ncols(self) -> int:
+        return int(self.begin.shape[0])
+
+
+def _table_from_columns(begin, end, step, cols, radial: bool) -> PotTable:
+    """Assemble a PotTable from per-column value arrays exactly as read_pot_table2 +
+    init_threepoint do (imd_potential.c:394-466, 1260-1276)."""
+    ncols = len(cols)
+    begin = np.asarray(begin, dtype=np.float64)
+    end = np.asarray(end, dtype=np.float64)
+    step = np.asarray(step, dtype=np.float64)
+    invstep = 1.0 / step
+    numstep = 1 + (end - begin) / step
+    ln = (numstep + 0.49).astype(np.int32)
+    maxsteps = int(ln.max())
+    tab = np.zeros((maxsteps + 2, ncols), dtype=np.float64)
+    for i, c in enumerate(cols):
+        c = np.asarray(c, dtype=np.float64)
+        assert c.shape[0] == ln[i], (c.shape, ln[i])
+        tab[: ln[i], i] = c
+    if radial:
+        for i in range(ncols):
+            delta = tab[ln[i] - 1, i]
+            if delta != 0.0:
+                tab[: ln[i], i] -= delta
+    for i in range(ncols):
+        n = int(ln[i])
+        y = tab[:, i]
+        y[n] = 3 * y[n - 1] - 3 * y[n - 2] + y[n - 3]
+        y[n + 1] = 6 * y[n - 1] - 8 * y[n - 2] + 3 * y[n - 3]
+    return PotTable(begin, end, step, invstep, ln, maxsteps, np.ascontiguousarray(tab))
+
+
+def write_pot_table2(path: str, begin, end, step, cols) -> None:
+    """IMD potential format 2: header '#F 2 ncols' / '#E', one info line per column
+    (begin end step), then the values column after column (imd_potential.c:385-393)."""
+    with open(path, "w") as f:
+        f.write("#F 2 %d\n#E\n" % len(cols))
+        for b, e, s in zip(begin, end, step):
+            f.write("%.16e %.16e %.16e\n" % (b, e, s))
+        for c in cols:
+            f.write("\n")
+            for v in c:
+                f.write("%.16e\n" % v)
+
+
+def read_pot_table2(path: str, ncols: int, radial: bool) -> PotTable:
+    """Reader for format 2 with the semantics of read_pot_table2 (imd_potential.c:394)."""
+    with open(path) as f:
+        lines = [ln for ln in f if not ln.startswith("#")]
+    toks = " ".join(lines).split()
+    vals = np.array(toks, dtype=np.float64)
+    info = vals[: 3 * ncols].reshape(ncols, 3)
+    begin, end, step = info[:, 0], info[:, 1], info[:, 2]
+    numstep = 1 + (end - begin) / step
+    ln = (numstep + 0.49).astype(np.int64)
+    cols, p = [], 3 * ncols
+    for i in range(ncols):
+        cols.append(vals[p: p + ln[i]])
+        p += ln[i]
+    return _table_from_columns(begin, end, step, cols, radial)
+
+
+@dataclasses.dataclass
+class EamSpec:
+    """Analytic Johnson-style EAM: f(r)=f_e exp(-beta(r/r_e-1)) s(r),
+    phi(r)=phi_e exp(-gamma(r/r_e-1)) s(r), s = quintic smoothstep to 0 on [0.9 r_c, r_c],
+    F(rho) = -E_c (1-(alpha/beta) ln x) x^(alpha/beta) - 6 phi_e x^(gamma/beta), x=rho/rho_e."""
+    name: str
+    a: float          # lattice constant (Angstrom)
+    r_c: float
+    E_c: float
+    phi_e: float
+    alpha: float
+    beta: float
+    gamma: float
+    mass: float       # IMD mass unit: amu * 1.0364e-4 is applied by the caller if wanted
+    f_e: float = 1.0
+    rho_e: float = 12.0
+    rows: int = 2000
+    r2_begin: float = 1.0
+
+    @property
+    def r_e(self) -> float:
+        return self.a / np.sqrt(2.0)
+
+
+CU = EamSpec("cu", a=3.615, r_c=4.95, E_c=3.54, phi_e=0.59, alpha=5.09, beta=5.85,
+             gamma=8.0, mass=63.546)
+AL = EamSpec("al", a=4.05, r_c=6.3, E_c=3.36, phi_e=0.30, alpha=4.60, beta=5.40,
+             gamma=7.6, mass=26.9815)
+
+
+def _smooth(r, r_c):
+    t = np.clip((r - 0.9 * r_c) / (0.1 * r_c), 0.0, 1.0)
+    return 1.0 - (10 * t**3 - 15 * t**4 + 6 * t**5)
+
+
+def eam_columns(spec: EamSpec):
+    """Return ((begin,end,step,col) for pair, rho) on an r^2 grid and embed on a rho grid."""
+    r2 = np.linspace(spec.r2_begin, spec.r_c**2, spec.rows)
+    step = (spec.r_c**2 - spec.r2_begin) / (spec.rows - 1)
+    r = np.sqrt(r2)
+    s = _smooth(r, spec.r_c)
+    f = spec.f_e * np.exp(-spec.beta * (r / spec.r_e - 1.0)) * s
+    phi = spec.phi_e * np.exp(-spec.gamma * (r / spec.r_e - 1.0)) * s
+    rho_end = 3.0 * spec.rho_e
+    rho = np.linspace(0.0, rho_end, spec.rows)
+    rstep = rho_end / (spec.rows - 1)
+    x = np.maximum(rho / spec.rho_e, 1e-300)
+    ab, gb = spec.alpha / spec.beta, spec.gamma / spec.beta
+    F = -spec.E_c * (1.0 - ab * np.log(x)) * x**ab - 6.0 * spec.phi_e * x**gb
+    F[0] = 0.0
+    return ((spec.r2_begin, spec.r_c**2, step, phi),
+            (spec.r2_begin, spec.r_c**2, step, f),
+            (0.0, rho_end, rstep, F))
+
+
+def make_eam_tables(spec: EamSpec, outdir: Optional[str] = None) -> Dict[str, PotTable]:
+    """Tables for ntypes=1.  When ``outdir`` is given the three IMD format-2 files
+    ``<name>.pair/.rho/.emb`` are written and the tables are re-read from the files, so
+    that the in-memory values are exactly what the reference parses from the same text."""
+    pair, rho, emb = eam_columns(spec)
+    if outdir is not None:
+        os.makedirs(outdir, exist_ok=True)
+        out = {}
+        for key, (b, e, s, c), radial in (("pair", pair, True), ("rho", rho, True), ("emb", emb, False)):
+            path = os.path.join(outdir, "%s.%s" % (spec.name, key))
+            write_pot_table2(path, [b], [e], [s], [c])
+            out[key] = read_pot_table2(path, 1, radial)
+        return out
+    return {
+        "pair": _table_from_columns([pair[0]], [pair[1]], [pair[2]], [pair[3]], True),
+        "rho": _table_from_columns([rho[0]], [rho[1]], [rho[2]], [rho[3]], True),
+        "emb": _table_from_columns([emb[0]], [emb[1]], [emb[2]], [emb[3]], False),
+    }
+
+
+# ----------------------------------------------------------------------------- lattices
+
+def fcc_lattice(ncell: Sequence[int], a: float, dtype=np.float64) -> Tuple[np.ndarray, np.ndarray]:
+    """fcc positions (4 per cubic cell, basis offset a/4 as a generic interior point) and
+    the orthorhombic box matrix (rows box_x, box_y, box_z)."""
+    nx, ny, nz = ncell
+    basis = np.array([[0, 0, 0], [0.5, 0.5, 0], [0.5, 0, 0.5], [0, 0.5, 0.5]], dtype=np.float64) + 0.25
+    ix, iy, iz = np.meshgrid(np.arange(nx), np.arange(ny), np.arange(nz), indexing="ij")
+    cells = np.stack([ix, iy, iz], axis=-1).reshape(-1, 1, 3).astype(np.float64)
+    pos = ((cells + basis[None, :, :]) * a).reshape(-1, 3).astype(dtype)
+    box = np.diag([nx * a, ny * a, nz * a]).astype(np.float64)
+    return pos, box
+
+
+def maxwell_momenta(n: int, mass: float, temp_ev: float, seed: int = 4711) -> np.ndarray:
+    """Gaussian momenta with <p^2/2m> = 3/2 kT per atom and zero total momentum
+    (role of imd_maxwell.c; different RNG stream than drand48)."""
+    rng = np.random.default_rng(seed)
+    p = rng.normal(0.0, np.sqrt(mass * temp_ev), size=(n, 3))
+    p -= p.mean(axis=0, keepdims=True)
+    return p
+
+
+def film_lattice(ncell: Sequence[int], a: float, vac_front: float, vac_rear: float):
+    """fcc film: ncell cubic cells of material, vacuum of the given widths (Angstrom)
+    before and behind it along x (the laser axis); box non-periodic in x."""
+    pos, box = fcc_lattice(ncell, a)
+    pos[:, 0] += vac_front
+    box[0, 0] += vac_front + vac_rear
+    return pos, box
+
+
+# ----------------------------------------------------------------------------- IMD input
+
+def write_param_file(path: str, spec: EamSpec, box_param: Sequence[int], maxsteps: int,
+                     outfiles: str, potdir: str = ".", pbc=(1, 1, 1), starttemp: float = 0.0258,
+                     timestep: float = 0.1, nbl_margin: float = 0.5, seed: int = 4711,
+                     eng_int: int = 1, extra: str = "") -> None:
+    """IMD parameter file for the serial reference binary (keywords of imd_param.c)."""
+    txt = io.StringIO()
+    txt.write("coordname    _fcc\n")
+    txt.write("outfiles     %s\n" % outfiles)
+    txt.write("ensemble     nve\n")
+    txt.write("maxsteps     %d\n" % maxsteps)
+    txt.write("timestep     %.17g\n" % timestep)
+    txt.write("ntypes       1\ntotal_types  1\n")
+    txt.write("masses       %.17g\n" % spec.mass)
+    txt.write("types        0\n")
+    txt.write("box_param    %d %d %d\n" % tuple(box_param))
+    txt.write("box_unit     %.17g\n" % spec.a)
+    txt.write("pbc_dirs     %d %d %d\n" % tuple(pbc))
+    txt.write("starttemp    %.17g\n" % starttemp)
+    txt.write("eng_int      %d\ncheckpt_int  0\n" % eng_int)
+    txt.write("seed         %d\n" % seed)
+    txt.write("core_potential_file   %s\n" % os.path.join(potdir, spec.name + ".pair"))
+    txt.write("embedding_energy_file %s\n" % os.path.join(potdir, spec.name + ".emb"))
+    txt.write("atomic_e-density_file %s\n" % os.path.join(potdir, spec.name + ".rho"))
+    txt.write("nbl_margin   %.17g\nnbl_size     1.3\ncpu_dim      1 1 1\n" % nbl_margin)
+    txt.write(extra)
+    with open(path, "w") as f:
+        f.write(txt.getvalue())
