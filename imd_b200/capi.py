@@ -1,0 +1,221 @@
+"""ctypes binding of the C ABI in include/imdcu.h (imd_b200/libimdcu.so).
+
+This is the same boundary a C host (the IMD stubs of INTEGRATION.md) binds; nothing
+here computes anything.  There is no CPU fallback: if the library is missing, or there
+is no CUDA device, the calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libimdcu.so")
+
+NPHASE = 8
+PHASE_NAMES = ["bin_sort", "nbl_build", "ghost_refresh", "eam_pass1", "embed", "eam_pass2",
+               "integrate", "ttm"]
+
+c_dp = C.POINTER(C.c_double)
+c_ip = C.POINTER(C.c_int32)
+c_lp = C.POINTER(C.c_int64)
+
+_lib = None
+
+
+class ImdcuError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("imdcu error %d: %s" % (code, msg))
+        self.code = code
+
+
+def load():
+    """dlopen libimdcu.so and declare every symbol of include/imdcu.h."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImdcuError(-100, "%s not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                               "(there is no CPU fallback)" % LIB_PATH)
+    L = C.CDLL(LIB_PATH)
+    vp = C.c_void_p
+    sig = {
+        "imdcu_abi_version": (C.c_int, []),
+        "imdcu_create": (C.c_int, [C.POINTER(vp), C.c_int]),
+        "imdcu_destroy": (C.c_int, [vp]),
+        "imdcu_last_error": (C.c_char_p, [vp]),
+        "imdcu_set_box": (C.c_int, [vp, c_dp, c_ip, C.c_double, C.c_double, c_ip]),
+        "imdcu_set_table": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, c_dp, c_dp, c_dp, c_dp, c_ip, c_dp]),
+        "imdcu_set_params": (C.c_int, [vp, C.c_int, C.c_double, C.c_int, c_dp]),
+        "imdcu_set_pdecay": (C.c_int, [vp, C.c_int, C.c_double, C.c_double, C.c_double]),
+        "imdcu_upload_atoms": (C.c_int, [vp, C.c_int64, c_ip, c_ip, c_ip, c_dp, c_dp, c_dp]),
+        "imdcu_num_atoms": (C.c_int64, [vp]),
+        "imdcu_download_atoms": (C.c_int, [vp, c_ip, c_ip, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_ip, c_ip]),
+        "imdcu_calc_forces": (C.c_int, [vp, C.c_int, c_dp]),
+        "imdcu_move_atoms_nve": (C.c_int, [vp, c_dp, c_ip]),
+        "imdcu_run_nve": (C.c_int, [vp, C.c_int, C.c_int, c_dp]),
+        "imdcu_get_cell_grid": (C.c_int, [vp, c_ip, c_dp]),
+        "imdcu_get_nblist_pairs": (C.c_int, [vp, c_lp, c_ip]),
+        "imdcu_nbl_count": (C.c_int, [vp]),
+        "imdcu_invalidate_nblist": (C.c_int, [vp]),
+        "imdcu_launch_count": (C.c_int64, [vp]),
+        "imdcu_set_profiling": (C.c_int, [vp, C.c_int]),
+        "imdcu_get_phase_times": (C.c_int, [vp, c_dp, c_lp]),
+        "imdcu_stream": (vp, [vp]),
+        "imdcu_synchronize": (C.c_int, [vp]),
+        "imdcu_eval_table": (C.c_int, [vp, C.c_int, C.c_int, C.c_int64, c_dp, c_dp, c_dp]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(L, name)
+        fn.restype = res
+        fn.argtypes = args
+    L._declared = sorted(sig)
+    _lib = L
+    return L
+
+
+def _dp(a):
+    return None if a is None else a.ctypes.data_as(c_dp)
+
+
+def _ip(a):
+    return None if a is None else a.ctypes.data_as(c_ip)
+
+
+class Context:
+    """One imdcu_ctx (one GPU).  Thin: argument marshalling and error translation only."""
+
+    def __init__(self, device: int = 0):
+        self.L = load()
+        h = C.c_void_p()
+        rc = self.L.imdcu_create(C.byref(h), device)
+        if rc != 0:
+            raise ImdcuError(rc, (self.L.imdcu_last_error(None) or b"").decode())
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.imdcu_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise ImdcuError(rc, (self.L.imdcu_last_error(self.h) or b"").decode())
+
+    # ---- set-up
+    def set_table(self, which: int, pt):
+        begin = np.ascontiguousarray(pt.begin, np.float64); end = np.ascontiguousarray(pt.end, np.float64)
+        step = np.ascontiguousarray(pt.step, np.float64); inv = np.ascontiguousarray(pt.invstep, np.float64)
+        ln = np.ascontiguousarray(pt.len, np.int32); tab = np.ascontiguousarray(pt.table, np.float64)
+        self._ck(self.L.imdcu_set_table(self.h, which, pt.ncols, pt.maxsteps, _dp(begin), _dp(end), _dp(step),
+                                        _dp(inv), _ip(ln), _dp(tab)))
+
+    def set_box(self, box, pbc, nbl_margin, nbl_size=1.3, divisor=None):
+        box = np.ascontiguousarray(box, np.float64).reshape(9)
+        pbc = np.ascontiguousarray(pbc, np.int32)
+        div = None if divisor is None else np.ascontiguousarray(divisor, np.int32)
+        self._ck(self.L.imdcu_set_box(self.h, _dp(box), _ip(pbc), float(nbl_margin), float(nbl_size), _ip(div)))
+
+    def set_params(self, ntypes, timestep, restrictions=None):
+        rs = np.ones((1, 3)) if restrictions is None else np.ascontiguousarray(restrictions, np.float64).reshape(-1, 3)
+        self._ck(self.L.imdcu_set_params(self.h, int(ntypes), float(timestep), rs.shape[0], _dp(rs)))
+
+    def set_pdecay(self, enabled, xipdecay=0.0, ramp_start=0.0, ramp_end=1.0):
+        self._ck(self.L.imdcu_set_pdecay(self.h, int(enabled), xipdecay, ramp_start, ramp_end))
+
+    # ---- atoms
+    def upload_atoms(self, pos, mom, mass, types=None, ids=None, vtypes=None):
+        pos = np.ascontiguousarray(pos, np.float64); mom = np.ascontiguousarray(mom, np.float64)
+        n = pos.shape[0]
+        mass = np.ascontiguousarray(np.broadcast_to(np.asarray(mass, np.float64), (n,)))
+        ty = None if types is None else np.ascontiguousarray(types, np.int32)
+        vt = None if vtypes is None else np.ascontiguousarray(vtypes, np.int32)
+        idd = None if ids is None else np.ascontiguousarray(ids, np.int32)
+        self._ck(self.L.imdcu_upload_atoms(self.h, n, _ip(idd), _ip(ty), _ip(vt), _dp(mass), _dp(pos), _dp(mom)))
+
+    @property
+    def n(self):
+        return int(self.L.imdcu_num_atoms(self.h))
+
+    def download(self, fields=("id", "pos", "mom", "force", "epot", "rho", "dF", "numneighs", "cell")):
+        n = self.n
+        buf = {
+            "id": np.empty(n, np.int32), "type": np.empty(n, np.int32), "mass": np.empty(n),
+            "pos": np.empty((n, 3)), "mom": np.empty((n, 3)), "force": np.empty((n, 3)),
+            "epot": np.empty(n), "rho": np.empty(n), "dF": np.empty(n),
+            "numneighs": np.empty(n, np.int32), "cell": np.empty((n, 3), np.int32),
+        }
+        g = lambda k: buf[k] if k in fields else None  # noqa: E731
+        self._ck(self.L.imdcu_download_atoms(self.h, _ip(g("id")), _ip(g("type")), _dp(g("mass")), _dp(g("pos")),
+                                             _dp(g("mom")), _dp(g("force")), _dp(g("epot")), _dp(g("rho")),
+                                             _dp(g("dF")), _ip(g("numneighs")), _ip(g("cell"))))
+        return {k: buf[k] for k in fields}
+
+    # ---- hot path
+    def calc_forces(self, steps=0):
+        out = np.zeros(8)
+        self._ck(self.L.imdcu_calc_forces(self.h, steps, _dp(out)))
+        return out
+
+    def move_atoms_nve(self):
+        out = np.zeros(8); valid = C.c_int32(0)
+        self._ck(self.L.imdcu_move_atoms_nve(self.h, _dp(out), C.byref(valid)))
+        return out, bool(valid.value)
+
+    def run_nve(self, first_step, nsteps, want_energies=True):
+        e = np.zeros((nsteps, 2)) if want_energies else None
+        self._ck(self.L.imdcu_run_nve(self.h, first_step, nsteps, _dp(e)))
+        return e
+
+    # ---- inspection
+    def cell_grid(self):
+        g = np.zeros(3, np.int32); cs = C.c_double()
+        self._ck(self.L.imdcu_get_cell_grid(self.h, _ip(g), C.byref(cs)))
+        return g, cs.value
+
+    def nblist_pairs(self):
+        npairs = C.c_int64(0)
+        self._ck(self.L.imdcu_get_nblist_pairs(self.h, C.byref(npairs), None))
+        pairs = np.empty((npairs.value, 2), np.int32)
+        self._ck(self.L.imdcu_get_nblist_pairs(self.h, C.byref(npairs), _ip(pairs)))
+        return pairs
+
+    @property
+    def nbl_count(self):
+        return int(self.L.imdcu_nbl_count(self.h))
+
+    def invalidate_nblist(self):
+        self._ck(self.L.imdcu_invalidate_nblist(self.h))
+
+    @property
+    def launch_count(self):
+        return int(self.L.imdcu_launch_count(self.h))
+
+    def set_profiling(self, on=True):
+        self._ck(self.L.imdcu_set_profiling(self.h, int(on)))
+
+    def phase_times(self):
+        ms = np.zeros(NPHASE); ln = np.zeros(NPHASE, np.int64)
+        self._ck(self.L.imdcu_get_phase_times(self.h, _dp(ms), ln.ctypes.data_as(c_lp)))
+        return dict(zip(PHASE_NAMES, ms)), dict(zip(PHASE_NAMES, ln.tolist()))
+
+    @property
+    def stream(self):
+        return int(self.L.imdcu_stream(self.h) or 0)
+
+    def synchronize(self):
+        self._ck(self.L.imdcu_synchronize(self.h))
+
+    def eval_table(self, which, arg, col=0):
+        arg = np.ascontiguousarray(arg, np.float64)
+        val = np.empty_like(arg); grad = np.empty_like(arg)
+        self._ck(self.L.imdcu_eval_table(self.h, which, col, arg.shape[0], _dp(arg), _dp(val), _dp(grad)))
+        return val, grad

@@ -1,0 +1,122 @@
+// imd_b200/csrc/api.cu -- the hot-path entry points of the C ABI (include/imdcu.h)
+#include "device.cuh"
+
+static int check_ready(imdcu_ctx *c)
+{
+  if (!c) return IMDCU_EINVAL;
+  if (!c->box_set) return c->fail(IMDCU_EINVAL, "imdcu_set_box has not been called");
+  if (!c->params_set) return c->fail(IMDCU_EINVAL, "imdcu_set_params has not been called");
+  for (int t = 0; t < 3; t++)
+    if (!c->tab[t].set) return c->fail(IMDCU_EINVAL, "potential tables not set");
+  if (c->tab[IMDCU_TAB_PAIR].ncols != c->ntypes * c->ntypes || c->tab[IMDCU_TAB_RHO].ncols != c->ntypes * c->ntypes ||
+      c->tab[IMDCU_TAB_EMBED].ncols != c->ntypes)
+    return c->fail(IMDCU_EINVAL, "table column counts do not match ntypes");
+  cudaSetDevice(c->device);
+  return IMDCU_OK;
+}
+
+// calc_forces (imd_forces_nbl.c:295-1054)
+extern "C" int imdcu_calc_forces(imdcu_ctx *c, int steps, double out8[8])
+{
+  (void) steps;
+  RET_IF(check_ready(c));
+  if (!c->have_valid_nbl) {
+    RET_IF(imdcu_rebuild_cells(c));              // fix_cells (:304)
+    RET_IF(imdcu_refresh_ghosts(c, true));       // send_cells(copy_cell) (:311)
+    RET_IF(imdcu_build_nblist(c));               // make_nblist (:315)
+  } else {
+    RET_IF(imdcu_refresh_ghosts(c, false));
+  }
+  return imdcu_eam_forces(c, out8);
+}
+
+// move_atoms_nve + check_nblist (imd_main_3d.c:564, :812)
+extern "C" int imdcu_move_atoms_nve(imdcu_ctx *c, double out8[8], int *have_valid_nbl)
+{
+  RET_IF(check_ready(c));
+  return imdcu_integrate_nve(c, out8, have_valid_nbl);
+}
+
+// main-loop segment (imd_main_3d.c:151-916 restricted to the hot calls)
+extern "C" int imdcu_run_nve(imdcu_ctx *c, int first_step, int nsteps, double *energies)
+{
+  RET_IF(check_ready(c));
+  double f8[8], m8[8];
+  int valid = 0;
+  for (int s = 0; s < nsteps; s++) {
+    RET_IF(imdcu_calc_forces(c, first_step + s, energies ? f8 : nullptr));
+    RET_IF(imdcu_integrate_nve(c, m8, &valid));
+    if (energies) { energies[2 * s] = f8[0]; energies[2 * s + 1] = m8[0]; }
+  }
+  return IMDCU_OK;
+}
+
+extern "C" int imdcu_nbl_count(const imdcu_ctx *c) { return c ? c->nbl_count : -1; }
+
+extern "C" int imdcu_invalidate_nblist(imdcu_ctx *c)
+{
+  if (!c) return IMDCU_EINVAL;
+  c->have_valid_nbl = false;
+  return IMDCU_OK;
+}
+
+extern "C" int64_t imdcu_launch_count(const imdcu_ctx *c) { return c ? c->launches : -1; }
+
+extern "C" int imdcu_set_profiling(imdcu_ctx *c, int enabled)
+{
+  if (!c) return IMDCU_EINVAL;
+  c->profiling = enabled != 0;
+  for (int k = 0; k < IMDCU_NPHASE; k++) { c->phase_ms[k] = 0; c->phase_launches[k] = 0; }
+  return IMDCU_OK;
+}
+
+extern "C" int imdcu_get_phase_times(imdcu_ctx *c, double ms[IMDCU_NPHASE], int64_t launches[IMDCU_NPHASE])
+{
+  if (!c) return IMDCU_EINVAL;
+  for (int k = 0; k < IMDCU_NPHASE; k++) {
+    if (ms) ms[k] = c->phase_ms[k];
+    if (launches) launches[k] = c->phase_launches[k];
+  }
+  return IMDCU_OK;
+}
+
+extern "C" void *imdcu_stream(const imdcu_ctx *c) { return c ? (void *) c->stream : nullptr; }
+
+extern "C" int imdcu_synchronize(imdcu_ctx *c)
+{
+  if (!c) return IMDCU_EINVAL;
+  cudaSetDevice(c->device);
+  CU_CHECK(c, cudaStreamSynchronize(c->stream));
+  return IMDCU_OK;
+}
+
+// ----------------------------------------------------------------------------- table probe
+__global__ void k_eval_table(TabView v, int col, int64_t n, const double *__restrict__ arg,
+                             double *__restrict__ val, double *__restrict__ grad)
+{
+  int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  TabCol t = tab_col(v, v.coef, col);
+  double p, g; int is_short = 0;
+  pair_int2(t, arg[i], p, g, is_short);
+  val[i] = p; grad[i] = g;
+}
+
+extern "C" int imdcu_eval_table(imdcu_ctx *c, int which, int col, int64_t n, const double *arg,
+                                double *val, double *grad)
+{
+  if (!c || which < 0 || which > 2 || !c->tab[which].set || col < 0 || col >= c->tab[which].ncols || n < 0)
+    return c ? c->fail(IMDCU_EINVAL, "imdcu_eval_table: bad argument") : IMDCU_EINVAL;
+  cudaSetDevice(c->device);
+  if (n == 0) return IMDCU_OK;
+  double *d = nullptr;
+  CU_CHECK(c, cudaMalloc(&d, 3 * n * sizeof(double)));
+  CU_CHECK(c, cudaMemcpyAsync(d, arg, n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  k_eval_table<<<div_up(n, 256), 256, 0, c->stream>>>(imdcu_tab_view(c->tab[which]), col, n, d, d + n, d + 2 * n);
+  c->count_launch();
+  CU_CHECK(c, cudaMemcpyAsync(val, d + n, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CU_CHECK(c, cudaMemcpyAsync(grad, d + 2 * n, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CU_CHECK(c, cudaStreamSynchronize(c->stream));
+  cudaFree(d);
+  return IMDCU_OK;
+}

@@ -1,0 +1,221 @@
+// imd_b200/csrc/common.cuh -- shared declarations of libimdcu.so (sm_100a only).
+//
+// Device-resident state of one rank: atoms in cell-sorted SoA/packed arrays, an extended
+// cell grid (one ghost layer, like the reference's cell_dim = local + 2,
+// imd_geom_3d.c:262-274) whose ghost cells hold shifted image atoms, a FULL neighbour
+// list in a tile-padded ("sliced ELL", 32 atoms per slice) layout, and the potential
+// tables re-packed as per-interval coefficient rows.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/imdcu.h"
+
+#define IMDCU_TILE 32            // atoms per neighbour-list slice (= warp size)
+
+// ----------------------------------------------------------------------------- errors
+#define CU_CHECK(ctx, expr)                                                              \
+  do {                                                                                   \
+    cudaError_t _e = (expr);                                                             \
+    if (_e != cudaSuccess) {                                                             \
+      (ctx)->set_error(std::string(#expr) + ": " + cudaGetErrorString(_e) + " at " +     \
+                       __FILE__ + ":" + std::to_string(__LINE__));                       \
+      return IMDCU_ECUDA;                                                                \
+    }                                                                                    \
+  } while (0)
+
+#define RET_IF(expr)                                                                     \
+  do { int _r = (expr); if (_r != IMDCU_OK) return _r; } while (0)
+
+// ----------------------------------------------------------------------------- buffers
+template <typename T>
+struct DevBuf {
+  T     *p   = nullptr;
+  size_t cap = 0;
+  cudaError_t ensure(size_t n, double slack = 1.0) {
+    if (n <= cap) return cudaSuccess;
+    size_t want = (size_t) (n * slack) + 64;
+    T *q = nullptr;
+    cudaError_t e = cudaMalloc(&q, want * sizeof(T));
+    if (e != cudaSuccess) return e;
+    if (p) cudaFree(p);
+    p = q; cap = want;
+    return cudaSuccess;
+  }
+  cudaError_t ensure_exact(size_t n) {          // capacity >= n, no slack added
+    if (n <= cap) return cudaSuccess;
+    T *q = nullptr;
+    cudaError_t e = cudaMalloc(&q, n * sizeof(T));
+    if (e != cudaSuccess) return e;
+    if (p) cudaFree(p);
+    p = q; cap = n;
+    return cudaSuccess;
+  }
+  // grow but keep the first `keep` elements
+  cudaError_t ensure_keep(size_t n, size_t keep, cudaStream_t st, double slack = 1.0) {
+    if (n <= cap) return cudaSuccess;
+    size_t want = (size_t) (n * slack) + 64;
+    T *q = nullptr;
+    cudaError_t e = cudaMalloc(&q, want * sizeof(T));
+    if (e != cudaSuccess) return e;
+    if (p && keep) {
+      e = cudaMemcpyAsync(q, p, keep * sizeof(T), cudaMemcpyDeviceToDevice, st);
+      if (e != cudaSuccess) return e;
+      cudaStreamSynchronize(st);
+    }
+    if (p) cudaFree(p);
+    p = q; cap = want;
+    return cudaSuccess;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+// ----------------------------------------------------------------------------- tables
+// One tabulated function set on the device.  Row k of column c holds the three numbers
+// the reference's 3-point macros derive from table rows k..k+2 (potaccess.h:344-349):
+//   {p0, dv = p1-p0, d2v = p2-2*p1+p0}
+// computed once on the host with the same operations, so a lookup is one 24-byte read.
+struct DevTable {
+  int     ncols = 0, nrows = 0;       // nrows = maxsteps
+  double *coef = nullptr;             // [ncols][nrows][3]
+  double *begin = nullptr, *end = nullptr, *invstep = nullptr;   // [ncols] (device)
+  std::vector<double> h_begin, h_end, h_step, h_invstep, h_table;
+  std::vector<int>    h_len;
+  int     maxsteps = 0;
+  bool    set = false;
+  size_t  coef_bytes() const { return (size_t) ncols * nrows * 3 * sizeof(double); }
+};
+
+struct TabView {                      // passed by value to kernels
+  const double *coef;                 // global coefficient rows
+  const double *begin, *end, *invstep;
+  int ncols, nrows;
+};
+
+// ----------------------------------------------------------------------------- geometry
+struct Geom {                         // passed by value to kernels
+  double box[9];                      // rows box_x, box_y, box_z
+  double tbox[9];
+  int    pbc[3];
+  int    gdim[3];                     // global_cell_dim
+  int    ldim[3];                     // cells owned by this rank (x-slab decomposition)
+  int    edim[3];                     // ldim + 2
+  int    xoff;                        // first owned global x cell layer
+  double cellsz;                      // (r_cut + margin)^2
+};
+
+// ghost-cell plan entry (host built at set_box; stage order z, y, x like send_cells,
+// imd_comm_force_3d.c:270-396)
+struct GhostCell {
+  int cell;        // extended index of the ghost cell
+  int src;         // extended index of the source cell (real or earlier-stage ghost)
+  int code;        // shift of this stage: trits (sx+1) + 3*(sy+1) + 9*(sz+1)
+};
+
+struct Reduce8 { double v[8]; };
+
+// ----------------------------------------------------------------------------- context
+struct imdcu_ctx {
+  int          device = 0;
+  cudaStream_t stream = nullptr;
+  std::string  err;
+  int          num_sms = 148;
+  size_t       smem_optin = 0;
+
+  // parameters
+  int    ntypes = 1, nvtypes = 1;
+  double timestep = 0.0, nbl_margin = 0.0, nbl_size = 1.3;
+  std::vector<double> restrictions;          // host copy
+  DevBuf<double> d_restrictions;
+  int    pdecay = 0; double xipdecay = 0, ramp_start = 0, ramp_end = 1;
+  bool   box_set = false, params_set = false;
+
+  Geom   geom;
+  DevTable tab[3];
+
+  // atoms: [0,n) real, [n, n+ng) ghosts
+  int64_t n = 0, ng = 0;
+  DevBuf<double4> pos4, pos4_alt;            // x,y,z,dF
+  DevBuf<double4> mom4, mom4_alt;            // px,py,pz,mass
+  DevBuf<double4> frc4;                      // fx,fy,fz,epot
+  DevBuf<double>  rho, refx, refy, refz;
+  DevBuf<int>     type, type_alt;            // [n+ng]
+  DevBuf<int>     vtype, vtype_alt, id, id_alt, numneighs;
+  DevBuf<int>     key, key_alt, perm, perm_alt;
+  DevBuf<unsigned char> cub_tmp;
+
+  // cells (extended grid)
+  int  ncell_ext = 0;
+  DevBuf<int> cell_begin, cell_count;        // [ncell_ext]
+  std::vector<GhostCell> gplan;              // host
+  int  gstage_cells[4] = {0, 0, 0, 0};       // plan index ranges per stage z,y,x
+  DevBuf<GhostCell> d_gplan;
+  DevBuf<int> gcell_off;                     // [nplan+1] exclusive scan of ghost cell counts
+  int64_t gstage_atoms[4] = {0, 0, 0, 0};    // ghost atom ranges per stage (relative to n)
+  DevBuf<int> ghost_src;                     // [ng] immediate source index
+  DevBuf<int> ghost_code;                    // [ng] stage shift code
+  DevBuf<int> ghost_root;                    // [ng] owning real atom (local)
+  DevBuf<int> ghost_tcode;                   // [ng] total shift code
+  DevBuf<double> ghost_raw;                  // [3*ng] root's unshifted position at build
+
+  // neighbour list
+  bool have_valid_nbl = false;
+  int  nbl_count = 0;
+  int  nbl_cap = 0;                          // slots per atom
+  DevBuf<int> nbl_idx;                       // [ntiles*cap*32]
+  DevBuf<int> nbl_num;                       // [n]
+  int  last_max_neigh = 0;
+
+  // reductions / flags (device + pinned host mirror)
+  DevBuf<double> partials;                   // per-block partial sums
+  double *d_results = nullptr;               // [32] doubles
+  double *h_results = nullptr;               // pinned
+  unsigned int *d_ticket = nullptr;          // last-block tickets
+  int *d_flags = nullptr;                    // [8] ints: overflow, maxneigh, is_short ...
+  int *h_flags = nullptr;                    // pinned
+
+  // bookkeeping
+  int64_t launches = 0;
+  bool    profiling = false;
+  double  phase_ms[IMDCU_NPHASE] = {0};
+  int64_t phase_launches[IMDCU_NPHASE] = {0};
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  int     cur_phase = -1;
+
+  void set_error(const std::string &m) { err = m; }
+  int  fail(int code, const std::string &m) { err = m; return code; }
+  void count_launch(int k = 1) { launches += k; if (cur_phase >= 0) phase_launches[cur_phase] += k; }
+};
+
+struct PhaseTimer {                 // CUDA-event bracket on the context's stream
+  imdcu_ctx *c; int phase;
+  PhaseTimer(imdcu_ctx *ctx, int ph) : c(ctx), phase(ph) {
+    c->cur_phase = ph;
+    if (c->profiling) cudaEventRecord(c->ev0, c->stream);
+  }
+  ~PhaseTimer() {
+    if (c->profiling) {
+      cudaEventRecord(c->ev1, c->stream);
+      cudaEventSynchronize(c->ev1);
+      float ms = 0; cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+      c->phase_ms[phase] += ms;
+    }
+    c->cur_phase = -1;
+  }
+};
+
+// ----------------------------------------------------------------------------- internal API
+int imdcu_rebuild_cells(imdcu_ctx *ctx);                 // cells.cu: wrap, bin, sort, ghosts
+int imdcu_refresh_ghosts(imdcu_ctx *ctx, bool at_build); // cells.cu
+int imdcu_build_nblist(imdcu_ctx *ctx);                  // nblist.cu
+int imdcu_eam_forces(imdcu_ctx *ctx, double out8[8]);    // eam.cu
+int imdcu_integrate_nve(imdcu_ctx *ctx, double out8[8], int *valid);   // integrate.cu
+TabView imdcu_tab_view(const DevTable &t);
+
+static inline int div_up(int64_t a, int64_t b) { return (int) ((a + b - 1) / b); }

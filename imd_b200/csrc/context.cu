@@ -1,0 +1,264 @@
+// imd_b200/csrc/context.cu -- life cycle, set-up and host<->device staging of libimdcu.so
+#include "common.cuh"
+
+#include <cmath>
+
+static thread_local std::string g_create_error;
+
+extern "C" int imdcu_abi_version(void) { return IMDCU_ABI_VERSION; }
+
+extern "C" const char *imdcu_last_error(const imdcu_ctx *ctx)
+{
+  return ctx ? ctx->err.c_str() : g_create_error.c_str();
+}
+
+extern "C" int imdcu_create(imdcu_ctx **out, int device)
+{
+  if (!out) return IMDCU_EINVAL;
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    g_create_error = std::string("no CUDA device: ") + cudaGetErrorString(e) +
+                     " (libimdcu has no CPU fallback)";
+    return IMDCU_ENODEVICE;
+  }
+  if (device < 0 || device >= ndev) {
+    g_create_error = "device ordinal out of range";
+    return IMDCU_EINVAL;
+  }
+  imdcu_ctx *c = new imdcu_ctx();
+  c->device = device;
+#define CREATE_CHECK(expr)                                                              \
+  do { cudaError_t _e = (expr); if (_e != cudaSuccess) {                                \
+         g_create_error = std::string(#expr) + ": " + cudaGetErrorString(_e);           \
+         delete c; return IMDCU_ECUDA; } } while (0)
+  CREATE_CHECK(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CREATE_CHECK(cudaGetDeviceProperties(&prop, device));
+  c->num_sms = prop.multiProcessorCount;
+  c->smem_optin = prop.sharedMemPerBlockOptin;
+  CREATE_CHECK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  CREATE_CHECK(cudaEventCreate(&c->ev0));
+  CREATE_CHECK(cudaEventCreate(&c->ev1));
+  CREATE_CHECK(cudaMalloc(&c->d_results, 32 * sizeof(double)));
+  CREATE_CHECK(cudaMemset(c->d_results, 0, 32 * sizeof(double)));
+  CREATE_CHECK(cudaMallocHost(&c->h_results, 32 * sizeof(double)));
+  CREATE_CHECK(cudaMalloc(&c->d_ticket, 8 * sizeof(unsigned int)));
+  CREATE_CHECK(cudaMemset(c->d_ticket, 0, 8 * sizeof(unsigned int)));
+  CREATE_CHECK(cudaMalloc(&c->d_flags, 8 * sizeof(int)));
+  CREATE_CHECK(cudaMemset(c->d_flags, 0, 8 * sizeof(int)));
+  CREATE_CHECK(cudaMallocHost(&c->h_flags, 8 * sizeof(int)));
+#undef CREATE_CHECK
+  c->restrictions.assign(3, 1.0);
+  *out = c;
+  return IMDCU_OK;
+}
+
+extern "C" int imdcu_destroy(imdcu_ctx *c)
+{
+  if (!c) return IMDCU_EINVAL;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  c->pos4.release(); c->pos4_alt.release(); c->mom4.release(); c->mom4_alt.release();
+  c->frc4.release(); c->rho.release(); c->refx.release(); c->refy.release(); c->refz.release();
+  c->type.release(); c->type_alt.release(); c->vtype.release(); c->vtype_alt.release();
+  c->id.release(); c->id_alt.release(); c->numneighs.release();
+  c->key.release(); c->key_alt.release(); c->perm.release(); c->perm_alt.release();
+  c->cub_tmp.release(); c->cell_begin.release(); c->cell_count.release();
+  c->d_gplan.release(); c->gcell_off.release(); c->ghost_src.release(); c->ghost_code.release();
+  c->ghost_root.release(); c->ghost_tcode.release(); c->ghost_raw.release();
+  c->nbl_idx.release(); c->nbl_num.release(); c->partials.release(); c->d_restrictions.release();
+  for (int t = 0; t < 3; t++) {
+    if (c->tab[t].coef) cudaFree(c->tab[t].coef);
+    if (c->tab[t].begin) cudaFree(c->tab[t].begin);
+  }
+  cudaFree(c->d_results); cudaFreeHost(c->h_results);
+  cudaFree(c->d_ticket); cudaFree(c->d_flags); cudaFreeHost(c->h_flags);
+  cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1);
+  cudaStreamDestroy(c->stream);
+  delete c;
+  return IMDCU_OK;
+}
+
+// ----------------------------------------------------------------------------- tables
+
+TabView imdcu_tab_view(const DevTable &t)
+{
+  TabView v;
+  v.coef = t.coef; v.begin = t.begin; v.end = t.end; v.invstep = t.invstep;
+  v.ncols = t.ncols; v.nrows = t.nrows;
+  return v;
+}
+
+extern "C" int imdcu_set_table(imdcu_ctx *c, int which, int ncols, int maxsteps,
+                               const double *begin, const double *end, const double *step,
+                               const double *invstep, const int *len, const double *table)
+{
+  if (!c || which < 0 || which > 2 || ncols < 1 || maxsteps < 3 || !begin || !end || !step ||
+      !invstep || !len || !table)
+    return c ? c->fail(IMDCU_EINVAL, "imdcu_set_table: bad argument") : IMDCU_EINVAL;
+  cudaSetDevice(c->device);
+  DevTable &t = c->tab[which];
+  if (t.coef) { cudaFree(t.coef); t.coef = nullptr; }
+  if (t.begin) { cudaFree(t.begin); t.begin = nullptr; }
+  t.ncols = ncols; t.nrows = maxsteps; t.maxsteps = maxsteps;
+  t.h_begin.assign(begin, begin + ncols); t.h_end.assign(end, end + ncols);
+  t.h_step.assign(step, step + ncols); t.h_invstep.assign(invstep, invstep + ncols);
+  t.h_len.assign(len, len + ncols);
+  t.h_table.assign(table, table + (size_t) (maxsteps + 2) * ncols);
+  // coefficient rows: same operations as the macro body (potaccess.h:344-349)
+  std::vector<double> coef((size_t) ncols * maxsteps * 3);
+  for (int col = 0; col < ncols; col++)
+    for (int k = 0; k < maxsteps; k++) {
+      volatile double p0 = table[(size_t) k * ncols + col];
+      volatile double p1 = table[(size_t) (k + 1) * ncols + col];
+      volatile double p2 = table[(size_t) (k + 2) * ncols + col];
+      volatile double dv = p1 - p0;
+      volatile double two_p1 = 2 * p1;
+      volatile double t1 = p2 - two_p1;
+      volatile double d2v = t1 + p0;
+      double *o = &coef[((size_t) col * maxsteps + k) * 3];
+      o[0] = p0; o[1] = dv; o[2] = d2v;
+    }
+  CU_CHECK(c, cudaMalloc(&t.coef, coef.size() * sizeof(double)));
+  CU_CHECK(c, cudaMemcpy(t.coef, coef.data(), coef.size() * sizeof(double), cudaMemcpyHostToDevice));
+  std::vector<double> info(3 * (size_t) ncols);
+  for (int i = 0; i < ncols; i++) { info[i] = begin[i]; info[ncols + i] = end[i]; info[2 * ncols + i] = invstep[i]; }
+  CU_CHECK(c, cudaMalloc(&t.begin, info.size() * sizeof(double)));
+  CU_CHECK(c, cudaMemcpy(t.begin, info.data(), info.size() * sizeof(double), cudaMemcpyHostToDevice));
+  t.end = t.begin + ncols; t.invstep = t.begin + 2 * ncols;
+  t.set = true;
+  return IMDCU_OK;
+}
+
+// ----------------------------------------------------------------------------- params
+
+extern "C" int imdcu_set_params(imdcu_ctx *c, int ntypes, double timestep, int nvtypes,
+                                const double *restrictions)
+{
+  if (!c || ntypes < 1 || nvtypes < 1)
+    return c ? c->fail(IMDCU_EINVAL, "imdcu_set_params: bad argument") : IMDCU_EINVAL;
+  cudaSetDevice(c->device);
+  c->ntypes = ntypes; c->timestep = timestep; c->nvtypes = nvtypes;
+  c->restrictions.assign(3 * (size_t) nvtypes, 1.0);
+  if (restrictions) c->restrictions.assign(restrictions, restrictions + 3 * (size_t) nvtypes);
+  CU_CHECK(c, c->d_restrictions.ensure(c->restrictions.size()));
+  CU_CHECK(c, cudaMemcpy(c->d_restrictions.p, c->restrictions.data(),
+                         c->restrictions.size() * sizeof(double), cudaMemcpyHostToDevice));
+  c->params_set = true;
+  return IMDCU_OK;
+}
+
+extern "C" int imdcu_set_pdecay(imdcu_ctx *c, int enabled, double xipdecay, double ramp_start,
+                                double ramp_end)
+{
+  if (!c) return IMDCU_EINVAL;
+  c->pdecay = enabled; c->xipdecay = xipdecay; c->ramp_start = ramp_start; c->ramp_end = ramp_end;
+  return IMDCU_OK;
+}
+
+// ----------------------------------------------------------------------------- box / cells
+
+static void cross3(const double *u, const double *v, double *w)
+{
+  w[0] = u[1] * v[2] - u[2] * v[1];
+  w[1] = u[2] * v[0] - u[0] * v[2];
+  w[2] = u[0] * v[1] - u[1] * v[0];
+}
+static double dot3(const double *a, const double *b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
+
+static inline int eidx(const Geom &g, int i, int j, int k) { return (i * g.edim[1] + j) * g.edim[2] + k; }
+
+// stage order z, y, x as send_cells (imd_comm_force_3d.c:270-396); unlike the reference's
+// AR scheme both x sides are filled because the device list is a full list.
+static void build_ghost_plan(imdcu_ctx *c)
+{
+  Geom &g = c->geom;
+  const int ex = g.edim[0], ey = g.edim[1], ez = g.edim[2];
+  auto code = [](int sx, int sy, int sz) { return (sx + 1) + 3 * (sy + 1) + 9 * (sz + 1); };
+  c->gplan.clear();
+  c->gstage_cells[0] = 0;
+  if (g.pbc[2])
+    for (int i = 1; i < ex - 1; i++)
+      for (int j = 1; j < ey - 1; j++) {
+        c->gplan.push_back({eidx(g, i, j, ez - 1), eidx(g, i, j, 1), code(0, 0, +1)});
+        c->gplan.push_back({eidx(g, i, j, 0), eidx(g, i, j, ez - 2), code(0, 0, -1)});
+      }
+  c->gstage_cells[1] = (int) c->gplan.size();
+  if (g.pbc[1])
+    for (int i = 1; i < ex - 1; i++)
+      for (int k = 0; k < ez; k++) {
+        c->gplan.push_back({eidx(g, i, ey - 1, k), eidx(g, i, 1, k), code(0, +1, 0)});
+        c->gplan.push_back({eidx(g, i, 0, k), eidx(g, i, ey - 2, k), code(0, -1, 0)});
+      }
+  c->gstage_cells[2] = (int) c->gplan.size();
+  if (g.pbc[0])
+    for (int j = 0; j < ey; j++)
+      for (int k = 0; k < ez; k++) {
+        c->gplan.push_back({eidx(g, ex - 1, j, k), eidx(g, 1, j, k), code(+1, 0, 0)});
+        c->gplan.push_back({eidx(g, 0, j, k), eidx(g, ex - 2, j, k), code(-1, 0, 0)});
+      }
+  c->gstage_cells[3] = (int) c->gplan.size();
+}
+
+extern "C" int imdcu_set_box(imdcu_ctx *c, const double box[9], const int pbc[3],
+                             double nbl_margin, double nbl_size, const int divisor[3])
+{
+  if (!c || !box || !pbc) return c ? c->fail(IMDCU_EINVAL, "imdcu_set_box: bad argument") : IMDCU_EINVAL;
+  if (!c->tab[IMDCU_TAB_PAIR].set || !c->tab[IMDCU_TAB_RHO].set)
+    return c->fail(IMDCU_EINVAL, "imdcu_set_box: set the pair and rho tables first (cellsz comes from them)");
+  cudaSetDevice(c->device);
+  Geom &g = c->geom;
+  memcpy(g.box, box, sizeof g.box);
+  for (int d = 0; d < 3; d++) g.pbc[d] = pbc[d];
+  // make_box (imd_geom_3d.c:61-84)
+  cross3(box + 3, box + 6, g.tbox + 0);
+  cross3(box + 6, box + 0, g.tbox + 3);
+  cross3(box + 0, box + 3, g.tbox + 6);
+  volatile double volume = dot3(box, g.tbox);
+  if (volume == 0) return c->fail(IMDCU_EINVAL, "Box Edges are parallel.");
+  for (int k = 0; k < 9; k++) g.tbox[k] /= volume;
+  double height[3];
+  for (int d = 0; d < 3; d++) height[d] = 1.0 / dot3(g.tbox + 3 * d, g.tbox + 3 * d);
+  // cellsz: max r2 end of the radial tables (imd_potential.c:406) + margin (imd_geom_3d.c:129-131)
+  double cellsz = 0.0;
+  for (int t = 0; t < 2; t++)
+    for (int i = 0; i < c->tab[t].ncols; i++) cellsz = std::max(cellsz, c->tab[t].h_end[i]);
+  volatile double rc = sqrt((double) cellsz) + nbl_margin;
+  g.cellsz = rc * rc;
+  c->nbl_margin = nbl_margin;
+  c->nbl_size = nbl_size > 1.0 ? nbl_size : 1.3;
+  for (int d = 0; d < 3; d++) {
+    int cd = divisor ? divisor[d] : 1;
+    if (cd < 1) cd = 1;
+    volatile double scale = sqrt(1.0 * g.cellsz / height[d]);
+    g.gdim[d] = (int) (1.0 / scale);
+    if (0 != g.gdim[d] % cd) g.gdim[d] = ((int) (g.gdim[d] / cd)) * cd;
+    if (g.gdim[d] < cd || g.gdim[d] < 1)
+      return c->fail(IMDCU_EINVAL, "global_cell_dim too small for the cutoff (imd_geom_3d.c:186-199)");
+    g.ldim[d] = g.gdim[d];
+    g.edim[d] = g.ldim[d] + 2;
+  }
+  g.xoff = 0;
+  c->ncell_ext = g.edim[0] * g.edim[1] * g.edim[2];
+  build_ghost_plan(c);
+  CU_CHECK(c, c->cell_begin.ensure(c->ncell_ext + 1));
+  CU_CHECK(c, c->cell_count.ensure(c->ncell_ext + 1));
+  CU_CHECK(c, c->d_gplan.ensure(c->gplan.size() + 1));
+  CU_CHECK(c, c->gcell_off.ensure(c->gplan.size() + 2));
+  if (!c->gplan.empty())
+    CU_CHECK(c, cudaMemcpy(c->d_gplan.p, c->gplan.data(), c->gplan.size() * sizeof(GhostCell),
+                           cudaMemcpyHostToDevice));
+  c->box_set = true;
+  c->have_valid_nbl = false;
+  return IMDCU_OK;
+}
+
+extern "C" int imdcu_get_cell_grid(const imdcu_ctx *c, int gdim[3], double *cellsz)
+{
+  if (!c || !c->box_set) return IMDCU_EINVAL;
+  for (int d = 0; d < 3; d++) gdim[d] = c->geom.gdim[d];
+  if (cellsz) *cellsz = c->geom.cellsz;
+  return IMDCU_OK;
+}

@@ -1,0 +1,72 @@
+// imd_b200/csrc/integrate.cu -- leap-frog NVE step fused with the neighbour-list validity
+// check: move_atoms_nve (imd_integrate.c:35-561, the plain-NVE branch incl. the PDECAY rear
+// absorber :233-239) + check_nblist (imd_forces_nbl.c:1062-1092) in one pass over the atoms.
+// HBM-bound streaming kernel: 32 (mom) + 32 (force) + 32 (pos) + 24 (ref) + 4 (vtype) bytes
+// read, 64 bytes written per atom.
+#include "device.cuh"
+
+struct MoveArgs {
+  int n;
+  double4 *pos4; double4 *mom4; const double4 *frc4;
+  const double *refx, *refy, *refz;
+  const int *vtype; const double *restrictions;
+  double timestep;
+  int pdecay; double xipdecay, ramp_start, pd_a;
+  double *partials; unsigned int *ticket; double *results;
+};
+
+__global__ void __launch_bounds__(256)
+k_move_nve(MoveArgs a)
+{
+  double ekin[1] = {0.0}, dmax[1] = {0.0};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += gridDim.x * blockDim.x) {
+    double4 p = a.mom4[i];
+    const double4 f4 = a.frc4[i];
+    double4 x = a.pos4[i];
+    const double *rs = a.restrictions + 3 * a.vtype[i];
+    const double m = p.w;
+    const double k1 = p.x * p.x + p.y * p.y + p.z * p.z;
+    double fx = f4.x * rs[0], fy = f4.y * rs[1], fz = f4.z * rs[2];
+    if (a.pdecay && x.x > a.ramp_start)
+      fx -= (p.x / m) * a.xipdecay * a.pd_a * (x.x - a.ramp_start) * (x.x - a.ramp_start);
+    p.x += a.timestep * fx; p.y += a.timestep * fy; p.z += a.timestep * fz;
+    const double k2 = p.x * p.x + p.y * p.y + p.z * p.z;
+    ekin[0] += (k1 + k2) / (4 * m);
+    const double tmp = a.timestep / m;
+    x.x += tmp * p.x; x.y += tmp * p.y; x.z += tmp * p.z;
+    a.mom4[i] = p;
+    a.pos4[i] = x;
+    const double dx = x.x - a.refx[i], dy = x.y - a.refy[i], dz = x.z - a.refz[i];
+    dmax[0] = fmax(dmax[0], r2_exact(dx, dy, dz));
+  }
+  grid_reduce<1, 0>(ekin, a.partials, a.ticket, a.results);
+  grid_reduce<1, 1>(dmax, a.partials + gridDim.x, a.ticket + 1, a.results + 1);
+}
+
+int imdcu_integrate_nve(imdcu_ctx *c, double out8[8], int *valid)
+{
+  PhaseTimer pt(c, 6);
+  MoveArgs a;
+  a.n = (int) c->n;
+  a.pos4 = c->pos4.p; a.mom4 = c->mom4.p; a.frc4 = c->frc4.p;
+  a.refx = c->refx.p; a.refy = c->refy.p; a.refz = c->refz.p;
+  a.vtype = c->vtype.p; a.restrictions = c->d_restrictions.p;
+  a.timestep = c->timestep;
+  a.pdecay = c->pdecay; a.xipdecay = c->xipdecay; a.ramp_start = c->ramp_start;
+  { double t = 1.0 / (c->ramp_end - c->ramp_start); a.pd_a = t * t; }
+  const int grid = std::max(1, std::min(div_up(a.n, 256), c->num_sms * 8));
+  CU_CHECK(c, c->partials.ensure((size_t) grid * 4 + 64));
+  a.partials = c->partials.p; a.ticket = c->d_ticket + 2; a.results = c->d_results + 4;
+  k_move_nve<<<grid, 256, 0, c->stream>>>(a);
+  c->count_launch();
+  CU_CHECK(c, cudaGetLastError());
+  CU_CHECK(c, cudaMemcpyAsync(c->h_results + 4, c->d_results + 4, 2 * sizeof(double),
+                              cudaMemcpyDeviceToHost, c->stream));
+  CU_CHECK(c, cudaStreamSynchronize(c->stream));
+  if (out8) { for (int k = 0; k < 8; k++) out8[k] = 0.0; out8[0] = c->h_results[4]; }
+  // check_nblist: invalidate when max displacement^2 > (0.5*nbl_margin)^2
+  const double lim = (0.5 * c->nbl_margin) * (0.5 * c->nbl_margin);
+  if (c->h_results[5] > lim) c->have_valid_nbl = false;
+  if (valid) *valid = c->have_valid_nbl ? 1 : 0;
+  return IMDCU_OK;
+}

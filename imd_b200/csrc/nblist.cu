@@ -1,0 +1,140 @@
+// imd_b200/csrc/nblist.cu -- Verlet neighbour list build (replaces make_nblist and
+// estimate_nblist_size, imd_forces_nbl.c:75-287).
+//
+// Differences in FORM, not in content: the reference builds a CSR half list over the
+// 14-cell half stencil (imd_geom_3d.c:917-922); here every atom gets its FULL list over
+// the 27-cell stencil (no scatter, no atomics in the force passes), stored in slices of
+// 32 atoms:  idx[(tile*cap + k)*32 + lane]  so that a warp reads slot k of its 32 atoms
+// as one 128-byte line.  The unordered pair SET equals the reference's bit for bit:
+// the predicate r2 < cellsz is evaluated with the reference's rounding AND in the
+// reference's orientation -- for a pair that the reference sees as (owner i, image of j)
+// the distance is ((x_j + shift) - x_i) also when the pair is met from j's side.
+#include "device.cuh"
+
+template <bool COUNT_ONLY>
+__global__ void __launch_bounds__(128)
+k_nbl_build(Geom g, int n, const double4 *__restrict__ pos4, const int *__restrict__ key,
+            const int *__restrict__ cell_begin, const int *__restrict__ cell_count,
+            const int *__restrict__ gtcode, const double *__restrict__ graw,
+            int cap, int *__restrict__ idx, int *__restrict__ num, int *__restrict__ flags)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  int cnt = 0;
+  if (i < n) {
+    const double4 pi = pos4[i];
+    const int c = key[i];
+    const int ey = g.edim[1], ez = g.edim[2];
+    int *slot = idx + ((size_t) (i >> 5) * cap) * 32 + lane;
+    for (int l = -1; l <= 1; l++)
+      for (int m = -1; m <= 1; m++)
+        for (int q = -1; q <= 1; q++) {
+          const int c2 = c + (l * ey + m) * ez + q;
+          const int b = cell_begin[c2], e = b + cell_count[c2];
+          const bool lexneg = (l < 0) || (l == 0 && m < 0) || (l == 0 && m == 0 && q < 0);
+          for (int j = b; j < e; j++) {
+            if (j == i) continue;
+            double dx, dy, dz;
+            if (j >= n && lexneg) {
+              // the reference meets this pair from the other atom: image of i minus raw j
+              double x = pi.x, y = pi.y, z = pi.z;
+              apply_shift(g, gtcode[j - n], -1.0, x, y, z);
+              const double *r = graw + 3 * (size_t) (j - n);
+              dx = x - r[0]; dy = y - r[1]; dz = z - r[2];
+            } else {
+              const double2 xy = *reinterpret_cast<const double2 *>(&pos4[j]);
+              const double zz = pos4[j].z;
+              dx = xy.x - pi.x; dy = xy.y - pi.y; dz = zz - pi.z;
+            }
+            const double r2 = r2_exact(dx, dy, dz);
+            if (r2 < g.cellsz) {
+              if (!COUNT_ONLY && cnt < cap) slot[(size_t) cnt * 32] = j;
+              cnt++;
+            }
+          }
+        }
+    num[i] = cnt;
+  }
+  int mx = cnt;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if (lane == 0 && mx > 0) atomicMax(&flags[1], mx);
+}
+
+int imdcu_build_nblist(imdcu_ctx *c)
+{
+  PhaseTimer pt(c, 1);
+  const int n = (int) c->n;
+  cudaStream_t st = c->stream;
+  if (n == 0) { c->have_valid_nbl = true; c->nbl_count++; return IMDCU_OK; }
+  const int nb = div_up(n, 128);
+  const size_t ntiles = (size_t) div_up(n, 32);
+  auto run = [&](bool count_only) -> int {
+    CU_CHECK(c, cudaMemsetAsync(c->d_flags, 0, 8 * sizeof(int), st));
+    if (count_only)
+      k_nbl_build<true><<<nb, 128, 0, st>>>(c->geom, n, c->pos4.p, c->key.p, c->cell_begin.p, c->cell_count.p,
+                                             c->ghost_tcode.p, c->ghost_raw.p, 0, nullptr, c->nbl_num.p, c->d_flags);
+    else
+      k_nbl_build<false><<<nb, 128, 0, st>>>(c->geom, n, c->pos4.p, c->key.p, c->cell_begin.p, c->cell_count.p,
+                                              c->ghost_tcode.p, c->ghost_raw.p, c->nbl_cap, c->nbl_idx.p,
+                                              c->nbl_num.p, c->d_flags);
+    c->count_launch();
+    CU_CHECK(c, cudaMemcpyAsync(c->h_flags, c->d_flags, 8 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU_CHECK(c, cudaStreamSynchronize(st));
+    return IMDCU_OK;
+  };
+  auto grow = [&](int maxn) -> int {
+    // same policy as the reference: nbl_size * measured need (imd_forces_nbl.c:181-190)
+    int cap = (int) (c->nbl_size * maxn) + 1;
+    cap = (cap + 3) & ~3;
+    c->nbl_cap = cap;
+    CU_CHECK(c, c->nbl_idx.ensure(ntiles * (size_t) cap * 32));
+    return IMDCU_OK;
+  };
+  if (c->nbl_cap == 0) {                     // first build: estimate_nblist_size
+    RET_IF(run(true));
+    RET_IF(grow(c->h_flags[1]));
+  }
+  CU_CHECK(c, c->nbl_idx.ensure(ntiles * (size_t) c->nbl_cap * 32));
+  RET_IF(run(false));
+  if (c->h_flags[1] > c->nbl_cap) {          // "neighbor table full": grow and redo once
+    RET_IF(grow(c->h_flags[1]));
+    RET_IF(run(false));
+    if (c->h_flags[1] > c->nbl_cap) return c->fail(IMDCU_EOVERFLOW, "neighbor table full - increase nbl_size");
+  }
+  c->last_max_neigh = c->h_flags[1];
+  c->have_valid_nbl = true;
+  c->nbl_count++;
+  return IMDCU_OK;
+}
+
+// every unordered pair once, as atom ids (parity tests; not a hot path)
+extern "C" int imdcu_get_nblist_pairs(imdcu_ctx *c, int64_t *npairs, int32_t *pairs)
+{
+  if (!c || !npairs) return IMDCU_EINVAL;
+  if (!c->have_valid_nbl) return c->fail(IMDCU_EINVAL, "no valid neighbour list");
+  cudaSetDevice(c->device);
+  const int64_t n = c->n, ng = c->ng;
+  const int cap = c->nbl_cap;
+  CU_CHECK(c, cudaStreamSynchronize(c->stream));
+  std::vector<int> num((size_t) n), id((size_t) n), root((size_t) ng + 1);
+  std::vector<int> idx((size_t) div_up(n, 32) * cap * 32);
+  CU_CHECK(c, cudaMemcpy(num.data(), c->nbl_num.p, n * sizeof(int), cudaMemcpyDeviceToHost));
+  CU_CHECK(c, cudaMemcpy(id.data(), c->id.p, n * sizeof(int), cudaMemcpyDeviceToHost));
+  if (ng) CU_CHECK(c, cudaMemcpy(root.data(), c->ghost_root.p, ng * sizeof(int), cudaMemcpyDeviceToHost));
+  CU_CHECK(c, cudaMemcpy(idx.data(), c->nbl_idx.p, idx.size() * sizeof(int), cudaMemcpyDeviceToHost));
+  int64_t np = 0;
+  for (int64_t i = 0; i < n; i++) {
+    const size_t base = ((size_t) (i >> 5) * cap) * 32 + (i & 31);
+    for (int k = 0; k < num[i]; k++) {
+      int j = idx[base + (size_t) k * 32];
+      int r = j < n ? j : root[j - n];
+      if (id[i] < id[r] || (id[i] == id[r] && j >= n && i < j)) {
+        if (pairs) { pairs[2 * np] = id[i]; pairs[2 * np + 1] = id[r]; }
+        np++;
+      }
+    }
+  }
+  *npairs = np;
+  return IMDCU_OK;
+}

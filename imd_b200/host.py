@@ -1,0 +1,91 @@
+"""Host-side mirror of the reference's call sites for the hot path.
+
+The reference drives the path through global-state functions:
+``calc_forces(steps)`` (imd_forces_nbl.c:295), ``move_atoms()`` -> ``move_atoms_nve``
+(imd_integrate.c:35), ``check_nblist()`` (imd_forces_nbl.c:1062), with results in the
+globals ``tot_pot_energy, virial, tot_kin_energy, have_valid_nbl, nbl_count``.  ``Imd``
+keeps that vocabulary over one C-ABI context so the parity tests read like a main loop
+(imd_main_3d.c:151-916).  All arithmetic happens in libimdcu.so on the GPU.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from . import capi
+
+TAB_PAIR, TAB_RHO, TAB_EMBED = 0, 1, 2
+
+
+class Imd:
+    def __init__(self, device: int = 0):
+        self.ctx = capi.Context(device)
+        self.tot_pot_energy = 0.0
+        self.virial = 0.0
+        self.tot_kin_energy = 0.0
+        self.have_valid_nbl = 0
+        self.steps = 0
+
+    # setup_potentials (imd_potential.c:43): pair_pot, rho_h_tab, embed_pot
+    def setup_potentials(self, tables):
+        self.ctx.set_table(TAB_PAIR, tables["pair"])
+        self.ctx.set_table(TAB_RHO, tables["rho"])
+        self.ctx.set_table(TAB_EMBED, tables["emb"])
+
+    # make_box + init_cells (imd_geom_3d.c:52, 118)
+    def make_box(self, box, pbc_dirs, nbl_margin, nbl_size=1.3, cell_divisor=None):
+        self.ctx.set_box(box, pbc_dirs, nbl_margin, nbl_size, cell_divisor)
+        self.global_cell_dim, self.cellsz = self.ctx.cell_grid()
+
+    def set_params(self, ntypes=1, timestep=0.1, restrictions=None):
+        self.ctx.set_params(ntypes, timestep, restrictions)
+
+    # read_atoms / generate_atoms hand-over (imd.c:131-142)
+    def set_atoms(self, pos, mom, mass, types=None, ids=None, vtypes=None):
+        self.ctx.upload_atoms(pos, mom, mass, types, ids, vtypes)
+        self.have_valid_nbl = 0
+
+    @property
+    def natoms(self):
+        return self.ctx.n
+
+    @property
+    def nbl_count(self):
+        return self.ctx.nbl_count
+
+    def calc_forces(self, steps=None):
+        out = self.ctx.calc_forces(self.steps if steps is None else steps)
+        self.tot_pot_energy, self.virial = float(out[0]), float(out[1])
+        self.have_valid_nbl = 1
+        return out
+
+    def move_atoms(self):
+        """move_atoms_nve followed by check_nblist, as the main loop does (:564, :812)."""
+        out, valid = self.ctx.move_atoms_nve()
+        self.tot_kin_energy = float(out[0])
+        self.have_valid_nbl = int(valid)
+        return out
+
+    def main_loop(self, nsteps):
+        """calc_forces -> move_atoms -> check_nblist for nsteps; returns [nsteps,2] energies."""
+        e = self.ctx.run_nve(self.steps, nsteps, True)
+        self.steps += nsteps
+        if nsteps:
+            self.tot_pot_energy, self.tot_kin_energy = float(e[-1, 0]), float(e[-1, 1])
+        return e
+
+    def atoms(self, fields=("id", "pos", "mom", "force", "epot", "rho", "dF", "numneighs", "cell"),
+              sort_by_id=True):
+        f = tuple(fields)
+        if sort_by_id and "id" not in f:
+            f = ("id",) + f
+        d = self.ctx.download(f)
+        if sort_by_id:
+            order = np.argsort(d["id"], kind="stable")
+            d = {k: v[order] for k, v in d.items()}
+        return d
+
+    def nblist_pairs(self):
+        return self.ctx.nblist_pairs()
+
+    def close(self):
+        self.ctx.close()

@@ -1,0 +1,154 @@
+"""Parity tests proper: the CUDA path, called through the C ABI, against
+(1) the golden dumps of the UNMODIFIED reference (tests/golden) and
+(2) the oracle on seeded inputs.
+Integer results (cell ids, neighbour index sets, numneighs) bit exact; FP64 results within
+1e-10 relative (north_star), tolerance written below."""
+import numpy as np
+import pytest
+
+from imd_b200 import host, synth
+from tests.util import GOLDEN_CASES, Golden, canon_pairs
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-10
+
+
+def rel_err(a, b):
+    return np.max(np.abs(a - b)) / (np.max(np.abs(b)) + 1e-300)
+
+
+def make_imd(box, pbc, tables, margin, timestep=0.1):
+    imd = host.Imd(0)
+    imd.setup_potentials(tables)
+    imd.make_box(box, pbc, margin)
+    imd.set_params(1, timestep)
+    return imd
+
+
+def test_table_access_matches_oracle():
+    from oracle.binding import Table
+    tables = synth.make_eam_tables(synth.CU)
+    imd = make_imd(np.diag([30.0, 30, 30]), (1, 1, 1), tables, 0.5)
+    rng = np.random.default_rng(0)
+    for which, key in ((0, "pair"), (1, "rho"), (2, "emb")):
+        pt = tables[key]
+        # inside, below begin (is_short clamp), above end (clamped to end), exact knots
+        arg = np.concatenate([rng.uniform(pt.begin[0] - 0.5, pt.end[0] + 1.0, 20000),
+                              pt.begin[0] + pt.step[0] * np.arange(0, pt.len[0], 37),
+                              [pt.begin[0], pt.end[0]]])
+        val, grad = imd.ctx.eval_table(which, arg)
+        oval, ograd = Table(pt).pair_int(arg)
+        # same operations; only FMA contraction may differ -> 1e-13 relative to the table scale
+        assert np.max(np.abs(val - oval)) <= 1e-13 * np.max(np.abs(oval))
+        assert np.max(np.abs(grad - ograd)) <= 1e-12 * np.max(np.abs(ograd))
+    imd.close()
+
+
+@pytest.mark.parametrize("case", GOLDEN_CASES)
+def test_golden_cells_nblist_forces(case):
+    g = Golden(case)
+    for s in g.steps:
+        if "s%d_nblpairs" % s not in g.z:
+            continue
+        imd = make_imd(g.box, g.pbc, g.tables, g.margin, g.timestep)
+        sc = g.step(s, "scalars")
+        assert [int(x) for x in imd.global_cell_dim] == [int(x) for x in sc[4:7]]
+        assert imd.cellsz == sc[7]
+        imd.set_atoms(g.step(s, "pre_pos"), g.step(s, "pre_mom"), g.step(s, "pre_mass"),
+                      g.step(s, "pre_type"), g.step(s, "pre_id"))
+        imd.calc_forces(s)
+        got = imd.atoms()
+        assert np.array_equal(got["id"], g.ids_sorted(s))
+        # bit exact: wrapped positions, cell ids, neighbour index set
+        assert np.array_equal(got["pos"], g.by_id(s, "post_pos"))
+        assert np.array_equal(got["cell"], g.by_id(s, "cell"))
+        mine, ref = canon_pairs(imd.nblist_pairs()), canon_pairs(g.step(s, "nblpairs"))
+        assert mine.shape == ref.shape and np.array_equal(mine, ref)
+        # FP64 within 1e-10 relative
+        for key in ("force", "epot", "rho", "dF"):
+            assert rel_err(got[key], g.by_id(s, key)) < RTOL, (case, s, key)
+        assert abs(imd.tot_pot_energy - sc[0]) < RTOL * abs(sc[0])
+        assert abs(imd.virial - sc[1]) < 1e-9 * max(1.0, abs(sc[1]))
+        imd.close()
+
+
+def test_golden_trajectory():
+    """NVE from the reference's step-0 state: calc_forces -> move_atoms -> check_nblist on the
+    device reproduces the reference's dumped states and its rebuild schedule."""
+    g = Golden("cu_6x6x6_pbc")
+    imd = make_imd(g.box, g.pbc, g.tables, g.margin, g.timestep)
+    imd.set_atoms(g.step(0, "pre_pos"), g.step(0, "pre_mom"), g.step(0, "pre_mass"),
+                  g.step(0, "pre_type"), g.step(0, "pre_id"))
+    eng = g.z["eng"]
+    for step in range(0, max(g.steps) + 1):
+        count0 = imd.nbl_count
+        imd.calc_forces(step)
+        if step in g.steps:
+            got = imd.atoms()
+            assert rel_err(got["force"], g.by_id(step, "force")) < 1e-8, step
+            assert (imd.nbl_count != count0) == ("s%d_nblpairs" % step in g.z), step
+            assert abs(imd.tot_pot_energy - g.step(step, "scalars")[0]) < 1e-9 * abs(g.step(step, "scalars")[0])
+        imd.move_atoms()
+    assert eng.shape[0] >= 2
+    imd.close()
+
+
+@pytest.mark.parametrize("ncell,pbc,spec", [((9, 7, 8), (1, 1, 1), synth.CU),
+                                            ((12, 6, 6), (0, 1, 1), synth.AL),
+                                            ((6, 6, 6), (0, 0, 0), synth.CU)])
+def test_oracle_parity_seeded(ncell, pbc, spec):
+    from oracle.binding import EamOracle
+    tables = synth.make_eam_tables(spec)
+    pos, box = synth.fcc_lattice(ncell, spec.a)
+    rng = np.random.default_rng(7)
+    pos = pos + rng.normal(0, 0.08, pos.shape)
+    mom = synth.maxwell_momenta(pos.shape[0], spec.mass, 0.05, seed=3)
+    margin = 0.4
+    imd = make_imd(box, pbc, tables, margin)
+    imd.set_atoms(pos, mom, spec.mass)
+    orc = EamOracle(box, pbc, tables, margin)
+    p = pos.copy()
+    cells = orc.fix_cells(p)
+    pairs = orc.make_nblist()
+    ref = orc.calc_forces(p, np.zeros(pos.shape[0], np.int32))
+    imd.calc_forces(0)
+    got = imd.atoms()
+    assert np.array_equal(got["pos"], p)
+    assert np.array_equal(got["cell"], cells)
+    assert np.array_equal(canon_pairs(imd.nblist_pairs()), canon_pairs(pairs))
+    assert np.array_equal(got["numneighs"], ref["numneighs"])
+    for key in ("force", "epot", "rho", "dF"):
+        assert rel_err(got[key], ref[key]) < RTOL, key
+    assert abs(imd.tot_pot_energy - ref["tot_pot_energy"]) < RTOL * abs(ref["tot_pot_energy"])
+    # integrator + displacement check against the oracle's
+    f = ref["force"]
+    mass = np.full(pos.shape[0], spec.mass)
+    p2, m2 = p.copy(), mom.copy()
+    ekin = orc.move_atoms_nve(p2, m2, f, mass, 0.1)
+    imd.move_atoms()
+    got2 = imd.atoms(("id", "pos", "mom"))
+    assert rel_err(got2["pos"], p2) < 1e-14 and rel_err(got2["mom"], m2) < 1e-13
+    assert abs(imd.tot_kin_energy - ekin) < 1e-12 * ekin
+    imd.close()
+    orc.close()
+
+
+def test_energy_conservation_and_momentum():
+    """Size-independent properties on a larger box: Newton's third law (sum F = 0),
+    NVE energy drift small, total momentum conserved."""
+    spec = synth.CU
+    tables = synth.make_eam_tables(spec)
+    pos, box = synth.fcc_lattice((20, 20, 20), spec.a)
+    mom = synth.maxwell_momenta(pos.shape[0], spec.mass, 0.0258, seed=5)
+    imd = make_imd(box, (1, 1, 1), tables, 0.5)
+    imd.set_atoms(pos, mom, spec.mass)
+    e = imd.main_loop(60)
+    got = imd.atoms(("id", "force", "mom"))
+    fsum = np.abs(got["force"].sum(axis=0)).max()
+    assert fsum < 1e-9 * np.abs(got["force"]).sum()
+    assert np.abs(got["mom"].sum(axis=0)).max() < 1e-8
+    etot = e[1:, 0] + e[1:, 1]        # leap-frog: first step has no half-step history
+    drift = np.abs(etot - etot[0]).max() / pos.shape[0]
+    assert drift < 2e-5, drift
+    assert imd.nbl_count >= 1
+    imd.close()
