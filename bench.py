@@ -1,0 +1,350 @@
+#!/usr/bin/env python
+"""bench.py -- EAM(+TTM) atom-steps/s of the B200-native hot path (BASELINE.json metric).
+
+    python bench.py --gpus 1 --steps K --warmup W            # our arm
+    python bench.py --impl reference --gpus N --steps K ...   # the reference's CPU code
+
+A "step" is one MD step of the main-loop segment calc_forces -> move_atoms -> check_nblist
+(imd_main_3d.c:406,564,812) over the whole synthetic system, neighbour-list rebuilds
+included whenever check_nblist asks for them.  Workload at N=1: BASELINE.json configs[1],
+"Al fcc EAM2 2M-atom slab NVE on 1 B200" (80^3 cubic cells = 2 048 000 atoms, 300 K).
+
+value : whole-job atom-steps/s with atoms resident in HBM (device-timed, CUDA events).
+e2e   : the same step driven through the C ABI with HOST buffers: every step uploads
+        positions+momenta from pinned host memory (imdcu_update_atoms) and downloads
+        positions, momenta, forces, per-atom energies and the energy sums.
+roofline : dominant kernel (k_eam_pass1), algorithmic bytes (64 + 4*N_h per atom,
+        SURVEY.md 8d) / its mean launch time measured live with CUDA events.
+cpu_baseline : the UNMODIFIED reference binary (oracle/_ref, author's flags) on the host
+        cores, a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import re
+import shutil
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "EAM atom-steps/s"
+UNIT = "atom-steps/s"
+N_H_AL = 39                 # half-list neighbours per atom, Al r_c 6.3 + margin 0.4
+REF_FAST = os.path.join(ROOT, "oracle", "_ref", "imd_ref_eam_nve_nbl_fast")
+REF_IEEE = os.path.join(ROOT, "oracle", "_ref", "imd_ref_eam_nve_nbl")
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ----------------------------------------------------------------------------- clocks
+
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None,
+                "sm_max_mhz": float(max(mx)) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------- reference arm
+
+def run_reference_sample(box_cells, steps, nproc, use_fast=True):
+    """P concurrent runs of the UNMODIFIED serial reference binary (the reference's only
+    parallel mode is MPI, which this image does not have): each process runs the same Al
+    NVE sample; throughput = sum over processes of atoms*steps / its main-loop time."""
+    from imd_b200 import synth
+    binary = REF_FAST if (use_fast and os.path.exists(REF_FAST)) else REF_IEEE
+    if not os.path.exists(binary):
+        return None
+    spec = synth.AL
+    work = tempfile.mkdtemp(prefix="imdbench_")
+    try:
+        synth.make_eam_tables(spec, work)
+        procs = []
+        for p in range(nproc):
+            d = os.path.join(work, "p%d" % p)
+            os.makedirs(os.path.join(d, "out"))
+            synth.write_param_file(os.path.join(d, "run.param"), spec, box_cells, steps, "out/run",
+                                   potdir="..", pbc=(1, 1, 1), starttemp=0.0258, nbl_margin=0.4,
+                                   eng_int=0, seed=4711 + p)
+            procs.append(subprocess.Popen([binary, "-p", "run.param"], cwd=d, stdout=subprocess.PIPE,
+                                          stderr=subprocess.STDOUT, text=True))
+        t0 = time.perf_counter()
+        outs = [p.communicate()[0] for p in procs]
+        wall = time.perf_counter() - t0
+        natoms = 4 * box_cells[0] * box_cells[1] * box_cells[2]
+        rate, tmain = 0.0, []
+        for o, p in zip(outs, procs):
+            m = re.search(r"([0-9.eE+-]+) seconds excluding setup time", o)
+            if p.returncode != 0 or not m:
+                raise RuntimeError("reference run failed:\n" + o[-2000:])
+            tm = float(m.group(1))
+            tmain.append(tm)
+            rate += natoms * (steps + 1) / tm          # imd.c:388-392 counts steps_max+1 steps
+        return {"value": rate, "natoms": natoms, "steps": steps + 1, "nproc": nproc,
+                "main_loop_s": float(np.max(tmain)), "wall_s": wall,
+                "binary": os.path.basename(binary)}
+    finally:
+        shutil.rmtree(work, ignore_errors=True)
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def reference_arm(args, rank, world):
+    if rank != 0:
+        return 0
+    cells = (24, 24, 24)
+    nproc = max(1, host_cores())
+    steps = max(2, min(args.steps + args.warmup, 60))
+    r = run_reference_sample(cells, steps, nproc)
+    base = {"metric": METRIC, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(args)}
+    if r is None:
+        base["unavailable"] = "oracle/_ref binaries not built (make -C oracle ref needs /root/reference)"
+        print(json.dumps(base))
+        return 0
+    sample = ("%d concurrent serial runs of the unmodified reference (%s; no MPI in this image), each Al fcc "
+              "%dx%dx%d cells = %d atoms, %d NVE steps, 300 K; rate = sum atoms*steps/main-loop time"
+              % (r["nproc"], r["binary"], cells[0], cells[1], cells[2], r["natoms"], r["steps"]))
+    base.update({"value": r["value"], "ms_per_step": 1e3 * r["main_loop_s"] / r["steps"],
+                 "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["nproc"], "kind": "reference",
+                                  "sample": sample},
+                 "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                 "gpu_launches": 0})
+    print(json.dumps(base))
+    return 0
+
+
+def workload_config(args):
+    c = args.cells
+    return {"workload": "Al fcc EAM2 NVE slab, %dx%dx%d cubic cells = %d atoms per GPU, 300 K, "
+                        "timestep 0.1 (1.018 fs), nbl_margin 0.4 (BASELINE.json configs[1])"
+                        % (c[0], c[1], c[2], 4 * c[0] * c[1] * c[2]),
+            "atoms_per_gpu": 4 * c[0] * c[1] * c[2],
+            "l2_policy": "inputs larger than L2 (neighbour list alone ~0.8 GB per 2M atoms)",
+            "parallelism": "1 GPU" if args.gpus == 1 else "x-slab domain decomposition, %d GPUs" % args.gpus}
+
+
+# ----------------------------------------------------------------------------- our arm
+
+def build_system(cells, seed):
+    from imd_b200 import synth
+    spec = synth.AL
+    pos, box = synth.fcc_lattice(cells, spec.a)
+    mom = synth.maxwell_momenta(pos.shape[0], spec.mass, 0.0258, seed=seed)
+    return spec, pos, box, mom
+
+
+def our_arm(args, rank, local_rank, world):
+    import torch
+    import torch.distributed as dist
+    from imd_b200 import host, synth
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product path has no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    spec, pos, box, mom = build_system(args.cells, 1234 + rank)
+    natoms = pos.shape[0]
+    tables = synth.make_eam_tables(spec)
+    imd = host.Imd(local_rank)
+    imd.setup_potentials(tables)
+    imd.make_box(box, (1, 1, 1), 0.4)
+    imd.set_params(1, 0.1)
+    imd.set_atoms(pos, mom, spec.mass)
+    ctx = imd.ctx
+    stream = torch.cuda.ExternalStream(ctx.stream, device=local_rank)
+
+    def barrier():
+        ctx.synchronize()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    # ---- device-resident throughput
+    ctx.run_nve(0, args.warmup, False)
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    l0 = ctx.launch_count
+    nbl0 = ctx.nbl_count
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    ctx.run_nve(args.warmup, args.steps, False)
+    ev1.record(stream)
+    barrier()
+    clocks = sampler.stop()
+    ms = ev0.elapsed_time(ev1)
+    launches = ctx.launch_count - l0
+    rebuilds = ctx.nbl_count - nbl0
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    value = natoms * world * args.steps / (ms * 1e-3)
+
+    # ---- end to end through the C ABI with host buffers (pinned)
+    ke = max(1, min(args.steps, args.e2e_steps))
+    hp = torch.empty((natoms, 3), dtype=torch.float64).pin_memory()
+    hm = torch.empty((natoms, 3), dtype=torch.float64).pin_memory()
+    hf = torch.empty((natoms, 3), dtype=torch.float64).pin_memory()
+    he = torch.empty((natoms,), dtype=torch.float64).pin_memory()
+    np_p, np_m, np_f, np_e = hp.numpy(), hm.numpy(), hf.numpy(), he.numpy()
+    ctx.download_into(np_p, np_m, np_f, np_e)
+
+    def e2e_step(s):
+        ctx.update_atoms(np_p, np_m)             # H2D: this step's inputs
+        out = ctx.calc_forces(s)                 # D2H: energy sums
+        out2, _ = ctx.move_atoms_nve()
+        ctx.download_into(np_p, np_m, np_f, np_e)  # D2H: the step's results
+        return out[0] + out2[0]
+
+    for s in range(2):
+        e2e_step(s)
+    barrier()
+    t0 = time.perf_counter()
+    for s in range(ke):
+        e2e_step(s)
+    barrier()
+    dt = time.perf_counter() - t0
+    t = torch.tensor([dt], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = natoms * world * ke / float(t.item())
+    h2d = natoms * 48
+    d2h = natoms * 80 + 2 * 64
+
+    # ---- per-kernel times (CUDA events inside the library, separate short segment)
+    roofline = None
+    phases = None
+    if rank == 0:
+        ctx.set_profiling(True)
+        ctx.run_nve(0, args.profile_steps, False)
+        ms_ph, ln_ph = ctx.phase_times()
+        ctx.set_profiling(False)
+        phases = {k: {"ms_total": ms_ph[k], "launches": ln_ph[k]} for k in ms_ph if ln_ph[k]}
+        p1_ms = ms_ph["eam_pass1"] / max(1, ln_ph["eam_pass1"])
+        alg_bytes = (64 + 4 * N_H_AL) * natoms
+        peak, peak_src = measured_peak_gbs()
+        achieved = alg_bytes / (p1_ms * 1e-3) / 1e9
+        roofline = {"kernel": "k_eam_pass1", "bound": "hbm", "achieved": achieved, "peak": peak,
+                    "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                    "alg_bytes_per_launch": alg_bytes, "ms_per_launch": p1_ms,
+                    "note": "FP64-pipe-bound kernel (about 45 DP instr per pair); HBM fraction is low by nature"}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            nproc = max(1, host_cores())
+            r = run_reference_sample((20, 20, 20), 12, nproc)
+            if r:
+                cpu = {"value": r["value"], "unit": UNIT, "cores": r["nproc"], "kind": "reference",
+                       "sample": "%d concurrent serial runs of the unmodified reference (%s), each Al fcc 20^3 cells "
+                                 "= %d atoms, %d NVE steps (%.1f s wall)" % (r["nproc"], r["binary"], r["natoms"],
+                                                                           r["steps"], r["wall_s"])}
+        except Exception as ex:                    # the baseline must not take the bench down
+            cpu = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "failed: %s" % ex}
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": workload_config(args), "clocks": clocks,
+                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                        "steps": ke},
+                "gpu_launches": int(launches), "nbl_rebuilds": int(rebuilds),
+                "roofline": roofline, "cpu_baseline": cpu, "phases": phases}
+        print(json.dumps(line))
+    imd.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=40)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--cells", type=int, nargs=3, default=[80, 80, 80], help="cubic fcc cells per GPU")
+    ap.add_argument("--e2e-steps", type=int, default=10)
+    ap.add_argument("--profile-steps", type=int, default=5)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        return reference_arm(args, rank, world)
+    return our_arm(args, rank, local_rank, world)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -52,6 +52,7 @@ def load():
         "imdcu_set_pdecay": (C.c_int, [vp, C.c_int, C.c_double, C.c_double, C.c_double]),
         "imdcu_upload_atoms": (C.c_int, [vp, C.c_int64, c_ip, c_ip, c_ip, c_dp, c_dp, c_dp]),
         "imdcu_num_atoms": (C.c_int64, [vp]),
+        "imdcu_update_atoms": (C.c_int, [vp, c_dp, c_dp]),
         "imdcu_download_atoms": (C.c_int, [vp, c_ip, c_ip, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_ip, c_ip]),
         "imdcu_calc_forces": (C.c_int, [vp, C.c_int, c_dp]),
         "imdcu_move_atoms_nve": (C.c_int, [vp, c_dp, c_ip]),
@@ -140,6 +141,15 @@ class Context:
         vt = None if vtypes is None else np.ascontiguousarray(vtypes, np.int32)
         idd = None if ids is None else np.ascontiguousarray(ids, np.int32)
         self._ck(self.L.imdcu_upload_atoms(self.h, n, _ip(idd), _ip(ty), _ip(vt), _dp(mass), _dp(pos), _dp(mom)))
+
+    def update_atoms(self, pos, mom):
+        """pos/mom [n,3] float64 C-contiguous in device order (pinned memory for full speed)."""
+        self._ck(self.L.imdcu_update_atoms(self.h, _dp(pos), _dp(mom)))
+
+    def download_into(self, pos=None, mom=None, force=None, epot=None):
+        """Raw download into caller buffers (e.g. pinned), device order."""
+        self._ck(self.L.imdcu_download_atoms(self.h, None, None, None, _dp(pos), _dp(mom), _dp(force), _dp(epot),
+                                             None, None, None, None))
 
     @property
     def n(self):

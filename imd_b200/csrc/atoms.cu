@@ -1,4 +1,7 @@
-// imd_b200/csrc/atoms.cu -- host <-> device staging of per-atom state
+// imd_b200/csrc/atoms.cu -- host <-> device staging of per-atom state.
+// Host arrays cross the ABI in the reference's AoS form (ORT/IMPULS/KRAFT: 3 doubles per
+// atom, makros.h:143-145); they are copied raw (cudaMemcpyAsync, full speed when the caller's
+// memory is pinned) into a device staging buffer and (un)packed by a kernel.
 #include "common.cuh"
 
 static int ensure_atom_capacity(imdcu_ctx *c, int64_t n)
@@ -14,9 +17,47 @@ static int ensure_atom_capacity(imdcu_ctx *c, int64_t n)
   CU_CHECK(c, c->key.ensure(n, slack));       CU_CHECK(c, c->key_alt.ensure(n, slack));
   CU_CHECK(c, c->perm.ensure(n, slack));      CU_CHECK(c, c->perm_alt.ensure(n, slack));
   // arrays that also hold ghosts start with room for 50 % ghosts and grow on demand
-  CU_CHECK(c, c->pos4.ensure(n + n / 2 + 1024));  CU_CHECK(c, c->pos4_alt.ensure(n + 1024, slack));
-  CU_CHECK(c, c->type.ensure(n + n / 2 + 1024));  CU_CHECK(c, c->type_alt.ensure(n + 1024, slack));
+  CU_CHECK(c, c->pos4.ensure(n + n / 2 + 1024));  CU_CHECK(c, c->pos4_alt.ensure_exact(c->pos4.cap));
+  CU_CHECK(c, c->type.ensure(n + n / 2 + 1024));  CU_CHECK(c, c->type_alt.ensure_exact(c->type.cap));
+  CU_CHECK(c, c->stage.ensure(10 * (size_t) n + 64));
   return IMDCU_OK;
+}
+
+// staging layout (doubles): [0,3n) pos, [3n,6n) mom, [6n,7n) mass   (in)
+//                           [0,3n) pos, [3n,6n) mom, [6n,9n) force, [9n,10n) epot (out)
+__global__ void __launch_bounds__(256)
+k_unpack_in(int n, const double *__restrict__ st, int have_mass, double4 *__restrict__ pos4,
+            double4 *__restrict__ mom4)
+{
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double *p = st + 3 * (size_t) i, *m = st + 3 * (size_t) n + 3 * (size_t) i;
+  double4 x = pos4[i], q = mom4[i];
+  x.x = p[0]; x.y = p[1]; x.z = p[2];
+  q.x = m[0]; q.y = m[1]; q.z = m[2];
+  if (have_mass) { q.w = st[6 * (size_t) n + i]; x.w = 0.0; }
+  pos4[i] = x; mom4[i] = q;
+}
+
+__global__ void __launch_bounds__(256)
+k_pack_out(int n, const double4 *__restrict__ pos4, const double4 *__restrict__ mom4,
+           const double4 *__restrict__ frc4, double *__restrict__ st)
+{
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double4 x = pos4[i], q = mom4[i], f = frc4[i];
+  double *p = st + 3 * (size_t) i;
+  p[0] = x.x; p[1] = x.y; p[2] = x.z;
+  p += 3 * (size_t) n; p[0] = q.x; p[1] = q.y; p[2] = q.z;
+  p += 3 * (size_t) n; p[0] = f.x; p[1] = f.y; p[2] = f.z;
+  st[9 * (size_t) n + i] = f.w;
+}
+
+__global__ void __launch_bounds__(256)
+k_pack_w(int n, const double4 *__restrict__ a, double *__restrict__ out)
+{
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = a[i].w;
 }
 
 extern "C" int imdcu_upload_atoms(imdcu_ctx *c, int64_t n, const int32_t *id, const int32_t *type,
@@ -28,23 +69,23 @@ extern "C" int imdcu_upload_atoms(imdcu_ctx *c, int64_t n, const int32_t *id, co
   if (n >= (int64_t) 1 << 30) return c->fail(IMDCU_EINVAL, "imdcu_upload_atoms: more than 2^30 atoms per rank");
   cudaSetDevice(c->device);
   RET_IF(ensure_atom_capacity(c, n));
-  std::vector<double4> hp((size_t) n), hm((size_t) n);
   std::vector<int> ht((size_t) n), hv((size_t) n), hi((size_t) n);
   for (int64_t i = 0; i < n; i++) {
-    hp[i] = make_double4(pos[3 * i], pos[3 * i + 1], pos[3 * i + 2], 0.0);
-    hm[i] = make_double4(mom[3 * i], mom[3 * i + 1], mom[3 * i + 2], mass[i]);
     ht[i] = type ? type[i] : 0;
-    hv[i] = vtype ? vtype[i] : ht[i];
+    hv[i] = vtype ? vtype[i] : (c->nvtypes > ht[i] ? ht[i] : 0);
     hi[i] = id ? id[i] : (int) i;
     if (ht[i] < 0 || ht[i] >= c->ntypes) return c->fail(IMDCU_EINVAL, "atom type out of range");
     if (hv[i] < 0 || hv[i] >= c->nvtypes) return c->fail(IMDCU_EINVAL, "atom vtype out of range");
   }
   cudaStream_t s = c->stream;
-  CU_CHECK(c, cudaMemcpyAsync(c->pos4.p, hp.data(), n * sizeof(double4), cudaMemcpyHostToDevice, s));
-  CU_CHECK(c, cudaMemcpyAsync(c->mom4.p, hm.data(), n * sizeof(double4), cudaMemcpyHostToDevice, s));
+  double *st = c->stage.p;
+  CU_CHECK(c, cudaMemcpyAsync(st, pos, 3 * n * sizeof(double), cudaMemcpyHostToDevice, s));
+  CU_CHECK(c, cudaMemcpyAsync(st + 3 * n, mom, 3 * n * sizeof(double), cudaMemcpyHostToDevice, s));
+  CU_CHECK(c, cudaMemcpyAsync(st + 6 * n, mass, n * sizeof(double), cudaMemcpyHostToDevice, s));
   CU_CHECK(c, cudaMemcpyAsync(c->type.p, ht.data(), n * sizeof(int), cudaMemcpyHostToDevice, s));
   CU_CHECK(c, cudaMemcpyAsync(c->vtype.p, hv.data(), n * sizeof(int), cudaMemcpyHostToDevice, s));
   CU_CHECK(c, cudaMemcpyAsync(c->id.p, hi.data(), n * sizeof(int), cudaMemcpyHostToDevice, s));
+  if (n) { k_unpack_in<<<div_up(n, 256), 256, 0, s>>>((int) n, st, 1, c->pos4.p, c->mom4.p); c->count_launch(); }
   CU_CHECK(c, cudaMemsetAsync(c->frc4.p, 0, n * sizeof(double4), s));
   CU_CHECK(c, cudaMemsetAsync(c->rho.p, 0, n * sizeof(double), s));
   CU_CHECK(c, cudaMemsetAsync(c->numneighs.p, 0, n * sizeof(int), s));
@@ -52,6 +93,24 @@ extern "C" int imdcu_upload_atoms(imdcu_ctx *c, int64_t n, const int32_t *id, co
   CU_CHECK(c, cudaStreamSynchronize(s));
   c->n = n; c->ng = 0;
   c->have_valid_nbl = false;
+  return IMDCU_OK;
+}
+
+// positions and momenta of the SAME atoms in the device's current order (the order of the
+// last imdcu_download_atoms): the neighbour list stays valid, check_nblist decides later.
+extern "C" int imdcu_update_atoms(imdcu_ctx *c, const double *pos, const double *mom)
+{
+  if (!c || !pos || !mom) return c ? c->fail(IMDCU_EINVAL, "imdcu_update_atoms: bad argument") : IMDCU_EINVAL;
+  cudaSetDevice(c->device);
+  const int64_t n = c->n;
+  if (n == 0) return IMDCU_OK;
+  cudaStream_t s = c->stream;
+  double *st = c->stage.p;
+  CU_CHECK(c, cudaMemcpyAsync(st, pos, 3 * n * sizeof(double), cudaMemcpyHostToDevice, s));
+  CU_CHECK(c, cudaMemcpyAsync(st + 3 * n, mom, 3 * n * sizeof(double), cudaMemcpyHostToDevice, s));
+  k_unpack_in<<<div_up(n, 256), 256, 0, s>>>((int) n, st, 0, c->pos4.p, c->mom4.p);
+  c->count_launch();
+  CU_CHECK(c, cudaGetLastError());
   return IMDCU_OK;
 }
 
@@ -65,33 +124,33 @@ extern "C" int imdcu_download_atoms(imdcu_ctx *c, int32_t *id, int32_t *type, do
   cudaSetDevice(c->device);
   const int64_t n = c->n;
   cudaStream_t s = c->stream;
+  if (n == 0) return IMDCU_OK;
+  double *st = c->stage.p;
+  const int nb = div_up(n, 256);
+  if (pos || mom || force || epot) {
+    k_pack_out<<<nb, 256, 0, s>>>((int) n, c->pos4.p, c->mom4.p, c->frc4.p, st);
+    c->count_launch();
+    if (pos) CU_CHECK(c, cudaMemcpyAsync(pos, st, 3 * n * sizeof(double), cudaMemcpyDeviceToHost, s));
+    if (mom) CU_CHECK(c, cudaMemcpyAsync(mom, st + 3 * n, 3 * n * sizeof(double), cudaMemcpyDeviceToHost, s));
+    if (force) CU_CHECK(c, cudaMemcpyAsync(force, st + 6 * n, 3 * n * sizeof(double), cudaMemcpyDeviceToHost, s));
+    if (epot) CU_CHECK(c, cudaMemcpyAsync(epot, st + 9 * n, n * sizeof(double), cudaMemcpyDeviceToHost, s));
+    CU_CHECK(c, cudaStreamSynchronize(s));
+  }
+  if (dF) {
+    k_pack_w<<<nb, 256, 0, s>>>((int) n, c->pos4.p, st); c->count_launch();
+    CU_CHECK(c, cudaMemcpyAsync(dF, st, n * sizeof(double), cudaMemcpyDeviceToHost, s));
+    CU_CHECK(c, cudaStreamSynchronize(s));
+  }
+  if (mass) {
+    k_pack_w<<<nb, 256, 0, s>>>((int) n, c->mom4.p, st); c->count_launch();
+    CU_CHECK(c, cudaMemcpyAsync(mass, st, n * sizeof(double), cudaMemcpyDeviceToHost, s));
+    CU_CHECK(c, cudaStreamSynchronize(s));
+  }
+  if (rho) CU_CHECK(c, cudaMemcpyAsync(rho, c->rho.p, n * sizeof(double), cudaMemcpyDeviceToHost, s));
+  if (id) CU_CHECK(c, cudaMemcpyAsync(id, c->id.p, n * sizeof(int), cudaMemcpyDeviceToHost, s));
+  if (type) CU_CHECK(c, cudaMemcpyAsync(type, c->type.p, n * sizeof(int), cudaMemcpyDeviceToHost, s));
+  if (numneighs) CU_CHECK(c, cudaMemcpyAsync(numneighs, c->numneighs.p, n * sizeof(int), cudaMemcpyDeviceToHost, s));
   CU_CHECK(c, cudaStreamSynchronize(s));
-  std::vector<double4> h((size_t) n);
-  if (pos || dF) {
-    CU_CHECK(c, cudaMemcpy(h.data(), c->pos4.p, n * sizeof(double4), cudaMemcpyDeviceToHost));
-    for (int64_t i = 0; i < n; i++) {
-      if (pos) { pos[3 * i] = h[i].x; pos[3 * i + 1] = h[i].y; pos[3 * i + 2] = h[i].z; }
-      if (dF) dF[i] = h[i].w;
-    }
-  }
-  if (mom || mass) {
-    CU_CHECK(c, cudaMemcpy(h.data(), c->mom4.p, n * sizeof(double4), cudaMemcpyDeviceToHost));
-    for (int64_t i = 0; i < n; i++) {
-      if (mom) { mom[3 * i] = h[i].x; mom[3 * i + 1] = h[i].y; mom[3 * i + 2] = h[i].z; }
-      if (mass) mass[i] = h[i].w;
-    }
-  }
-  if (force || epot) {
-    CU_CHECK(c, cudaMemcpy(h.data(), c->frc4.p, n * sizeof(double4), cudaMemcpyDeviceToHost));
-    for (int64_t i = 0; i < n; i++) {
-      if (force) { force[3 * i] = h[i].x; force[3 * i + 1] = h[i].y; force[3 * i + 2] = h[i].z; }
-      if (epot) epot[i] = h[i].w;
-    }
-  }
-  if (rho) CU_CHECK(c, cudaMemcpy(rho, c->rho.p, n * sizeof(double), cudaMemcpyDeviceToHost));
-  if (id) CU_CHECK(c, cudaMemcpy(id, c->id.p, n * sizeof(int), cudaMemcpyDeviceToHost));
-  if (type) CU_CHECK(c, cudaMemcpy(type, c->type.p, n * sizeof(int), cudaMemcpyDeviceToHost));
-  if (numneighs) CU_CHECK(c, cudaMemcpy(numneighs, c->numneighs.p, n * sizeof(int), cudaMemcpyDeviceToHost));
   if (cell3) {
     // key = extended cell index at the last rebuild -> global cell coordinates
     std::vector<int> k((size_t) n);

@@ -149,6 +149,7 @@ struct imdcu_ctx {
   DevBuf<int>     vtype, vtype_alt, id, id_alt, numneighs;
   DevBuf<int>     key, key_alt, perm, perm_alt;
   DevBuf<unsigned char> cub_tmp;
+  DevBuf<double>  stage;                     // host<->device staging (atoms.cu)
 
   // cells (extended grid)
   int  ncell_ext = 0;

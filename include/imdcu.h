@@ -77,6 +77,10 @@ int  imdcu_upload_atoms(imdcu_ctx *ctx, int64_t n, const int32_t *id, const int3
                         const int32_t *vtype, const double *mass,
                         const double *pos, const double *mom);
 int64_t imdcu_num_atoms(const imdcu_ctx *ctx);
+/* New positions and momenta for the SAME atoms in the device's current order (the order
+ * imdcu_download_atoms returns).  For hosts that keep the integrator or apply external
+ * modifications; the neighbour list stays valid until check_nblist says otherwise. */
+int  imdcu_update_atoms(imdcu_ctx *ctx, const double *pos, const double *mom);
 /* Download in the device's current (cell-sorted) order; any pointer may be NULL.
  * This is the "sync to host" the IMD writers need (imd_io_3d.c:721-979). */
 int  imdcu_download_atoms(imdcu_ctx *ctx, int32_t *id, int32_t *type, double *mass,
