@@ -54,36 +54,32 @@ def measured_peak_gbs():
 # ----------------------------------------------------------------------------- clocks
 
 class ClockSampler:
+    """Polls nvidia-smi (one-shot queries from a thread) while the GPU is under load."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, gpu_index):
-        self.idx = gpu_index
-        self.proc = None
-        self.lines = []
+    def __init__(self, gpu_index, period=0.2):
+        self.idx, self.period = gpu_index, period
+        self.lines, self.stop_flag, self.t = [], threading.Event(), None
+
+    def _poll(self):
+        while not self.stop_flag.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5)
+                self.lines.extend(out.stdout.strip().splitlines())
+            except Exception:
+                return
+            self.stop_flag.wait(self.period)
 
     def start(self):
-        try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "200"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.t = threading.Thread(target=self._read, daemon=True)
-            self.t.start()
-        except Exception:
-            self.proc = None
-
-    def _read(self):
-        for ln in self.proc.stdout:
-            self.lines.append(ln.strip())
+        self.t = threading.Thread(target=self._poll, daemon=True)
+        self.t.start()
 
     def stop(self):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except Exception:
-            self.proc.kill()
+        self.stop_flag.set()
+        if self.t:
+            self.t.join(timeout=6)
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for ln in self.lines:
@@ -97,8 +93,9 @@ class ClockSampler:
             for nm, v in zip(names, f[2:6]):
                 if v.lower().startswith("active"):
                     reasons.add(nm)
-        return {"sm_mhz": float(np.median(sm)) if sm else None,
-                "sm_max_mhz": float(max(mx)) if mx else None, "reasons": sorted(reasons),
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"], "samples": 0}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
                 "samples": len(sm)}
 
 
@@ -227,10 +224,10 @@ def our_arm(args, rank, local_rank, world):
             dist.barrier()
 
     # ---- device-resident throughput
-    ctx.run_nve(0, args.warmup, False)
     sampler = ClockSampler(local_rank)
+    sampler.start()                              # clocks under load: warm-up + timed region
+    ctx.run_nve(0, args.warmup, False)
     barrier()
-    sampler.start()
     l0 = ctx.launch_count
     nbl0 = ctx.nbl_count
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -301,10 +298,10 @@ def our_arm(args, rank, local_rank, world):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
             nproc = max(1, host_cores())
-            r = run_reference_sample((20, 20, 20), 12, nproc)
+            r = run_reference_sample((28, 28, 28), 30, nproc)
             if r:
                 cpu = {"value": r["value"], "unit": UNIT, "cores": r["nproc"], "kind": "reference",
-                       "sample": "%d concurrent serial runs of the unmodified reference (%s), each Al fcc 20^3 cells "
+                       "sample": "%d concurrent serial runs of the unmodified reference (%s), each Al fcc 28^3 cells "
                                  "= %d atoms, %d NVE steps (%.1f s wall)" % (r["nproc"], r["binary"], r["natoms"],
                                                                            r["steps"], r["wall_s"])}
         except Exception as ex:                    # the baseline must not take the bench down

@@ -9,6 +9,7 @@ static int ensure_atom_capacity(imdcu_ctx *c, int64_t n)
   const double slack = 1.1;
   CU_CHECK(c, c->mom4.ensure(n, slack));      CU_CHECK(c, c->mom4_alt.ensure(n, slack));
   CU_CHECK(c, c->frc4.ensure(n, slack));      CU_CHECK(c, c->rho.ensure(n, slack));
+  CU_CHECK(c, c->dF.ensure(n, slack));
   CU_CHECK(c, c->refx.ensure(n, slack));      CU_CHECK(c, c->refy.ensure(n, slack));
   CU_CHECK(c, c->refz.ensure(n, slack));
   CU_CHECK(c, c->vtype.ensure(n, slack));     CU_CHECK(c, c->vtype_alt.ensure(n, slack));

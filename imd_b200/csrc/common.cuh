@@ -144,7 +144,7 @@ struct imdcu_ctx {
   DevBuf<double4> pos4, pos4_alt;            // x,y,z,dF
   DevBuf<double4> mom4, mom4_alt;            // px,py,pz,mass
   DevBuf<double4> frc4;                      // fx,fy,fz,epot
-  DevBuf<double>  rho, refx, refy, refz;
+  DevBuf<double>  rho, dF, refx, refy, refz;
   DevBuf<int>     type, type_alt;            // [n+ng]
   DevBuf<int>     vtype, vtype_alt, id, id_alt, numneighs;
   DevBuf<int>     key, key_alt, perm, perm_alt;

@@ -61,7 +61,7 @@ extern "C" int imdcu_destroy(imdcu_ctx *c)
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
   c->pos4.release(); c->pos4_alt.release(); c->mom4.release(); c->mom4_alt.release();
-  c->frc4.release(); c->rho.release(); c->refx.release(); c->refy.release(); c->refz.release();
+  c->frc4.release(); c->rho.release(); c->dF.release(); c->refx.release(); c->refy.release(); c->refz.release();
   c->type.release(); c->type_alt.release(); c->vtype.release(); c->vtype_alt.release();
   c->id.release(); c->id_alt.release(); c->numneighs.release();
   c->key.release(); c->key_alt.release(); c->perm.release(); c->perm_alt.release();

@@ -23,6 +23,15 @@ __device__ __forceinline__ void apply_shift(const Geom &g, int code, double sign
   x = __dadd_rn(x, __dmul_rn(fx, g.box[0])); y = __dadd_rn(y, __dmul_rn(fx, g.box[1])); z = __dadd_rn(z, __dmul_rn(fx, g.box[2]));
 }
 
+// one 256-bit load of a packed atom record {x,y,z,w} (sm_100: LDG.E.256).  A gathered
+// neighbour is exactly one 32-byte sector, so this is one request and one sector.
+__device__ __forceinline__ double4 ld256(const double4 *p)
+{
+  double4 v;
+  asm volatile("ld.global.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(v.x), "=d"(v.y), "=d"(v.z), "=d"(v.w) : "l"(p));
+  return v;
+}
+
 // ----------------------------------------------------------------------------- tables
 // 3-point (quadratic in the argument) table access, potaccess.h:323-354.  `c` points to
 // the coefficient rows {p0, dv, d2v} of one column (shared or global memory).

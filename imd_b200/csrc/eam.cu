@@ -27,6 +27,7 @@ struct EamArgs {
   const int *nbl_idx, *nbl_num;
   double4 *frc4;                 // [n] fx,fy,fz,epot
   double *rho;                   // [n]
+  double *dF;                    // [n] F'(rho) out of pass 1
   int *numneighs;                // [n]
   TabView pair, rhot, emb;
   double *partials; unsigned int *ticket; double *results; int *flags;
@@ -89,9 +90,8 @@ k_eam_pass1(EamArgs a)
 #pragma unroll 2
       for (int k = sub; k < num; k += LPA) {
         const int j = slot[(size_t) k * 32];
-        const double2 xy = *reinterpret_cast<const double2 *>(&a.pos4[j]);
-        const double zz = a.pos4[j].z;
-        const double dx = xy.x - pi.x, dy = xy.y - pi.y, dz = zz - pi.z;
+        const double4 pj = ld256(&a.pos4[j]);
+        const double dx = pj.x - pi.x, dy = pj.y - pi.y, dz = pj.z - pi.z;
         const double r2 = r2_exact(dx, dy, dz);
         TabCol tp = tp0, tr = tr0;
         int jt = 0;
@@ -125,7 +125,7 @@ k_eam_pass1(EamArgs a)
       ee += pot;
       a.frc4[i] = make_double4(fx, fy, fz, ee);
       a.rho[i] = rh;
-      a.pos4[i].w = dF;            // nobody reads .w during this kernel
+      a.dF[i] = dF;                // merged into pos4.w by k_set_dF before the image refresh
       if (a.count_ttm) a.numneighs[i] = nn;
       acc[0] += ee; acc[1] += vir;
     }
@@ -173,7 +173,7 @@ k_eam_pass2(EamArgs a)
 #pragma unroll 2
       for (int k = sub; k < num; k += LPA) {
         const int j = slot[(size_t) k * 32];
-        const double4 pj = a.pos4[j];
+        const double4 pj = ld256(&a.pos4[j]);
         const double dx = pj.x - pi.x, dy = pj.y - pi.y, dz = pj.z - pi.z;
         const double r2 = r2_exact(dx, dy, dz);
         if (!MULTI) {
@@ -213,6 +213,13 @@ k_eam_pass2(EamArgs a)
   grid_reduce<1, 0>(acc, a.partials, a.ticket + 1, a.results + 2);
 }
 
+__global__ void __launch_bounds__(256)
+k_set_dF(int n, const double *__restrict__ dF, double4 *__restrict__ pos4)
+{
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) pos4[i].w = dF[i];
+}
+
 // ----------------------------------------------------------------------------- dispatch
 
 template <typename K>
@@ -241,6 +248,11 @@ static int run_passes(imdcu_ctx *c, EamArgs &a, size_t smem1, size_t smem2)
   {
     PhaseTimer pt(c, 3);
     k_eam_pass1<LPA, SMEM, MULTI><<<g1, EAM_BLOCK, smem1, c->stream>>>(a);
+    c->count_launch();
+  }
+  {
+    PhaseTimer pt(c, 4);
+    k_set_dF<<<div_up(a.n, 256), 256, 0, c->stream>>>(a.n, a.dF, a.pos4);
     c->count_launch();
   }
   RET_IF(imdcu_refresh_ghosts(c, false));          // F' (and positions again) to the images
@@ -274,7 +286,7 @@ int imdcu_eam_forces(imdcu_ctx *c, double out8[8])
   a.n = (int) c->n; a.ntypes = c->ntypes; a.cap = c->nbl_cap;
   a.pos4 = c->pos4.p; a.type = c->type.p;
   a.nbl_idx = c->nbl_idx.p; a.nbl_num = c->nbl_num.p;
-  a.frc4 = c->frc4.p; a.rho = c->rho.p; a.numneighs = c->numneighs.p;
+  a.frc4 = c->frc4.p; a.rho = c->rho.p; a.dF = c->dF.p; a.numneighs = c->numneighs.p;
   a.pair = imdcu_tab_view(c->tab[IMDCU_TAB_PAIR]);
   a.rhot = imdcu_tab_view(c->tab[IMDCU_TAB_RHO]);
   a.emb = imdcu_tab_view(c->tab[IMDCU_TAB_EMBED]);
@@ -283,8 +295,13 @@ int imdcu_eam_forces(imdcu_ctx *c, double out8[8])
   if (a.n > 0) {
     // lanes per atom: keep at least ~2 resident waves of threads on the machine
     const int64_t want = (int64_t) c->num_sms * 2048;
-    int rc;
-    if (a.n >= want) rc = run_lpa<1>(c, a);
+    int rc, force_lpa = 0;
+    if (const char *e = getenv("IMDCU_LPA")) force_lpa = atoi(e);      // tuning knob
+    if (force_lpa == 1) rc = run_lpa<1>(c, a);
+    else if (force_lpa == 2) rc = run_lpa<2>(c, a);
+    else if (force_lpa == 4) rc = run_lpa<4>(c, a);
+    else if (force_lpa == 8) rc = run_lpa<8>(c, a);
+    else if (a.n >= want) rc = run_lpa<1>(c, a);
     else if (a.n * 2 >= want) rc = run_lpa<2>(c, a);
     else if (a.n * 4 >= want) rc = run_lpa<4>(c, a);
     else rc = run_lpa<8>(c, a);

@@ -42,9 +42,8 @@ k_nbl_build(Geom g, int n, const double4 *__restrict__ pos4, const int *__restri
               const double *r = graw + 3 * (size_t) (j - n);
               dx = x - r[0]; dy = y - r[1]; dz = z - r[2];
             } else {
-              const double2 xy = *reinterpret_cast<const double2 *>(&pos4[j]);
-              const double zz = pos4[j].z;
-              dx = xy.x - pi.x; dy = xy.y - pi.y; dz = zz - pi.z;
+              const double4 pj = ld256(&pos4[j]);
+              dx = pj.x - pi.x; dy = pj.y - pi.y; dz = pj.z - pi.z;
             }
             const double r2 = r2_exact(dx, dy, dz);
             if (r2 < g.cellsz) {
