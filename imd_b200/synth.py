@@ -211,12 +211,13 @@ def film_lattice(ncell: Sequence[int], a: float, vac_front: float, vac_rear: flo
 def write_param_file(path: str, spec: EamSpec, box_param: Sequence[int], maxsteps: int,
                      outfiles: str, potdir: str = ".", pbc=(1, 1, 1), starttemp: float = 0.0258,
                      timestep: float = 0.1, nbl_margin: float = 0.5, seed: int = 4711,
-                     eng_int: int = 1, extra: str = "") -> None:
+                     eng_int: int = 1, extra: str = "", ensemble: str = "nve",
+                     cpu_dim=(1, 1, 1)) -> None:
     """IMD parameter file for the serial reference binary (keywords of imd_param.c)."""
     txt = io.StringIO()
     txt.write("coordname    _fcc\n")
     txt.write("outfiles     %s\n" % outfiles)
-    txt.write("ensemble     nve\n")
+    txt.write("ensemble     %s\n" % ensemble)
     txt.write("maxsteps     %d\n" % maxsteps)
     txt.write("timestep     %.17g\n" % timestep)
     txt.write("ntypes       1\ntotal_types  1\n")
@@ -231,7 +232,104 @@ def write_param_file(path: str, spec: EamSpec, box_param: Sequence[int], maxstep
     txt.write("core_potential_file   %s\n" % os.path.join(potdir, spec.name + ".pair"))
     txt.write("embedding_energy_file %s\n" % os.path.join(potdir, spec.name + ".emb"))
     txt.write("atomic_e-density_file %s\n" % os.path.join(potdir, spec.name + ".rho"))
-    txt.write("nbl_margin   %.17g\nnbl_size     1.3\ncpu_dim      1 1 1\n" % nbl_margin)
+    txt.write("nbl_margin   %.17g\nnbl_size     1.3\n" % nbl_margin)
+    txt.write("cpu_dim      %d %d %d\n" % tuple(cpu_dim))
     txt.write(extra)
     with open(path, "w") as f:
         f.write(txt.getvalue())
+
+
+# ----------------------------------------------------------------------------- TTM inputs
+
+AMU = 1.66053907e-27
+KB = 1.380649e-23
+HBAR = 1.054571817e-34
+EMASS = 9.1093837015e-31
+
+
+@dataclasses.dataclass
+class EosTable:
+    """One EOS interpolation table as nn_read_table parses it (imd_interpol.c:1170-1271):
+    ``is`` x ``js`` scattered points (x, y, z) with x the outer index.  Ours are rectilinear:
+    x[i] (density, kg/m^3), y[j], z[i, j].  ``diag`` (uint8 [is-1, js-1]) says which diagonal
+    of each grid rectangle the reference's Delaunay triangulation (libnn, via Triangle) uses:
+    0 = (i,j)-(i+1,j+1), 1 = (i+1,j)-(i,j+1); it is an INPUT of the device path because a
+    triangulation of co-circular points is not unique ("EOS tables")."""
+    x: np.ndarray
+    y: np.ndarray
+    z: np.ndarray
+    diag: Optional[np.ndarray] = None
+
+    def write(self, path: str) -> None:
+        with open(path, "w") as f:
+            f.write("%d %d\n" % (self.x.shape[0], self.y.shape[0]))
+            f.write("%.17g %.17g %.17g %.17g\n" % (self.x[0], self.x[-1], self.y[0], self.y[-1]))
+            for i in range(self.x.shape[0]):
+                for j in range(self.y.shape[0]):
+                    f.write("%.17g %.17g %.17g\n" % (self.x[i], self.y[j], self.z[i, j]))
+
+    @staticmethod
+    def read(path: str) -> "EosTable":
+        with open(path) as f:
+            toks = f.read().split()
+        ni, nj = int(toks[0]), int(toks[1])
+        v = np.array(toks[6:6 + 3 * ni * nj], dtype=np.float64).reshape(ni, nj, 3)
+        return EosTable(np.ascontiguousarray(v[:, 0, 0]), np.ascontiguousarray(v[0, :, 1]),
+                        np.ascontiguousarray(v[:, :, 2]))
+
+
+def make_eos_tables(nrho: int = 48, nt: int = 96, z_free: float = 3.0, a_weight: float = 26.9815,
+                    rho_range=(30.0, 4000.0), t_range=(30.0, 2.9e6)) -> Dict[str, EosTable]:
+    """Synthetic free-electron-like Al EOS (the reference's EOS_*.txt are missing blobs):
+    cve(rho,T) = c0 T / sqrt(T^2 + a(rho)^2)  [J/(K kg)],  ee = int_0^T cve = c0 (sqrt(T^2+a^2) - a)
+    [J/kg], a = (3/pi^2) T_F(rho), c0 = 3/2 k_B n_e/rho -- Sommerfeld at low T, classical at high T,
+    and ee consistent with cve as imd_ttm.c:1577-1579 requires.  Axes: density uniform; the cve table
+    is over T (geometric), the ee table over sqrt(T) (uniform), the phase table over T_i."""
+    rho = np.linspace(rho_range[0], rho_range[1], nrho)
+    ne = z_free * rho / (a_weight * AMU)
+    t_f = HBAR**2 * (3 * np.pi**2 * ne) ** (2.0 / 3.0) / (2 * EMASS) / KB
+    a = (3.0 / np.pi**2) * t_f
+    c0 = 1.5 * KB * z_free / (a_weight * AMU)
+    t_geo = np.geomspace(t_range[0], t_range[1], nt)
+    cve = c0 * t_geo[None, :] / np.sqrt(t_geo[None, :] ** 2 + a[:, None] ** 2)
+    ts = np.linspace(np.sqrt(t_range[0]), np.sqrt(t_range[1]), nt)
+    ee = c0 * (np.sqrt(ts[None, :] ** 4 + a[:, None] ** 2) - a[:, None])
+    ti = np.linspace(t_range[0], 2.0e4, 8)
+    phase = np.ones((nrho, ti.shape[0]))
+    return {"cve": EosTable(rho, t_geo, cve), "ee": EosTable(rho, ts, ee), "phase": EosTable(rho, ti, phase)}
+
+
+def write_eos_files(tabs: Dict[str, EosTable], outdir: str) -> None:
+    """The file names init_ttm opens relative to the run directory's parent (imd_ttm.c:1130-1132)."""
+    tabs["cve"].write(os.path.join(outdir, "EOS_cve_from_r_te.txt"))
+    tabs["ee"].write(os.path.join(outdir, "EOS_ee_from_r_tesqrt.txt"))
+    tabs["phase"].write(os.path.join(outdir, "EOS_phase_from_r_ti.txt"))
+
+
+@dataclasses.dataclass
+class TtmParams:
+    """Run-time TTM parameters (keywords of imd_param.c:1979-2092) + the analytic source."""
+    ttmdimx: int = 32
+    fd_n_timesteps: int = 20
+    fd_min_atoms: int = 10
+    vlatdim: int = 8
+    vlatbuffer: int = 2
+    vlatdens: float = 2.665655433e+03       # globals.h:1226
+    atomic_weight: float = 26.9815
+    atomic_charge: float = 13.0
+    I0: float = 5.0e15                      # W/m^2
+    lam: float = 800e-9                     # m
+    laser_t_0: float = 30e-15               # s
+    laser_sigma_t: float = 20e-15           # s
+    tmm_laser_threshold: float = 1e-5       # globals.h:479
+    src_mu: float = 1.0 / 80.0              # 1/Angstrom, analytic Beer-Lambert source
+    src_abs: float = 0.1
+    Temin: float = 1e-3                     # globals.h:1196
+
+    def param_text(self) -> str:
+        return ("fd_ext 1 1 1\nfd_n_timesteps %d\nttm_int 100000000\nfd_min_atoms %d\nttmdimx %d\n"
+                "vlatdim %d\nvlatbuffer %d\natomic_weight %.17g\natomic_charge %.17g\nI0 %.17g\n"
+                "lambda %.17g\nlaser_t_0 %.17g\nlaser_sigma_t %.17g\ntmm_threshold 10.0\n"
+                % (self.fd_n_timesteps, self.fd_min_atoms, self.ttmdimx, self.vlatdim, self.vlatbuffer,
+                   self.atomic_weight, self.atomic_charge, self.I0, self.lam, self.laser_t_0,
+                   self.laser_sigma_t))

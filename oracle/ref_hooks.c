@@ -38,7 +38,11 @@ static FILE *dump_open(const char *dir, int steps, const char *name)
 {
   char fn[1024];
   FILE *f;
+#ifdef MPI
+  snprintf(fn, sizeof fn, "%s/s%d.%s.r%d.bin", dir, steps, name, myid);   /* one file per rank */
+#else
   snprintf(fn, sizeof fn, "%s/s%d.%s.bin", dir, steps, name);
+#endif
   f = fopen(fn, "wb");
   if (f == NULL) { perror(fn); exit(3); }
   return f;
