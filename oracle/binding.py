@@ -26,7 +26,7 @@ class OrcTable(C.Structure):
 
 def build(force: bool = False) -> str:
     so = os.path.join(_HERE, "liboracle.so")
-    srcs = [os.path.join(_HERE, f) for f in ("eam_oracle.c", "ttm_oracle.c", "oracle.h")]
+    srcs = [os.path.join(_HERE, f) for f in ("eam_oracle.c", "ttm_oracle.c", "oracle.h", "ttm_oracle.h")]
     stale = (not os.path.exists(so)) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs)
     if force or stale:
         subprocess.check_call(["make", "-C", _HERE, "oracle"], stdout=subprocess.DEVNULL)
@@ -164,3 +164,153 @@ class EamOracle:
 
     def max_displacement2(self, pos, ref):
         return self.L.orc_max_displacement2(pos.shape[0], _dp(pos), _dp(ref))
+
+
+# ----------------------------------------------------------------------------- TTM
+
+class OrcEos(C.Structure):
+    _fields_ = [("nx", C.c_int), ("ny", C.c_int), ("x", c_dp), ("y", c_dp), ("z", c_dp),
+                ("diag", C.POINTER(C.c_ubyte))]
+
+
+class OrcTtmParams(C.Structure):
+    _fields_ = [("G", C.c_int), ("P", C.c_int), ("fd_n_timesteps", C.c_int), ("fd_min_atoms", C.c_int),
+                ("vlatdim", C.c_int), ("vlatbuffer", C.c_int),
+                ("vlatdens", C.c_double), ("atomic_weight", C.c_double), ("atomic_charge", C.c_double),
+                ("Temin", C.c_double), ("timestep", C.c_double),
+                ("box_x", C.c_double), ("box_y", C.c_double), ("box_z", C.c_double),
+                ("r2_cut_pair", C.c_double),
+                ("I0", C.c_double), ("lam", C.c_double), ("laser_t_0", C.c_double),
+                ("laser_sigma_t", C.c_double), ("tmm_laser_threshold", C.c_double),
+                ("src_mu", C.c_double), ("src_abs", C.c_double)]
+
+
+TTM_FIELDS = ["natoms", "natoms_old", "temp", "md_temp", "xi", "dens", "fd_k", "fd_g", "Z", "ne", "Ce", "U",
+              "source"]
+_TTM_DECL = False
+
+
+def _ttm_lib():
+    global _TTM_DECL
+    L = lib()
+    if not _TTM_DECL:
+        L.orc_ttm_create.restype = C.c_void_p
+        L.orc_ttm_create.argtypes = [C.POINTER(OrcTtmParams), C.POINTER(OrcEos), C.POINTER(OrcEos)]
+        L.orc_ttm_destroy.argtypes = [C.c_void_p]
+        L.orc_ttm_step.argtypes = [C.c_void_p, C.c_int, C.c_long, c_dp, c_dp, c_dp, c_ip, c_ip, c_ip]
+        L.orc_ttm_error.restype = C.c_char_p
+        L.orc_ttm_error.argtypes = [C.c_void_p]
+        L.orc_ttm_get_cells.argtypes = [C.c_void_p, c_dp]
+        L.orc_ttm_get_arrays.argtypes = [C.c_void_p, c_dp, c_dp, c_dp, c_dp, c_dp]
+        L.orc_ttm_get_scalars.argtypes = [C.c_void_p, c_dp]
+        L.orc_ttm_get_vlattice.argtypes = [C.c_void_p, c_dp]
+        L.orc_move_atoms_ttm.restype = C.c_double
+        L.orc_move_atoms_ttm.argtypes = [C.c_void_p, C.c_long, c_dp, c_dp, c_dp, c_dp, c_ip, c_ip, c_dp,
+                                         C.c_int, C.c_double, C.c_double, C.c_double]
+        L.orc_eos_interp.restype = C.c_double
+        L.orc_eos_interp.argtypes = [C.POINTER(OrcEos), C.c_double, C.c_double]
+        L.orc_eos_te_from_r_ee.restype = C.c_double
+        L.orc_eos_te_from_r_ee.argtypes = [C.POINTER(OrcEos), C.c_double, C.c_double]
+        L.orc_ttm_mean_charge.restype = C.c_double
+        L.orc_ttm_mean_charge.argtypes = [C.c_double] * 4
+        for f in (L.orc_ttm_kappa, L.orc_ttm_gamma):
+            f.restype = C.c_double
+            f.argtypes = [C.c_double] * 5 + [C.c_int]
+        _TTM_DECL = True
+    return L
+
+
+class Eos:
+    """Keeps the numpy buffers of an EOS table (imd_b200.synth.EosTable) alive next to the C struct."""
+
+    def __init__(self, tab):
+        self.x = np.ascontiguousarray(tab.x, np.float64)
+        self.y = np.ascontiguousarray(tab.y, np.float64)
+        self.z = np.ascontiguousarray(tab.z, np.float64)
+        d = tab.diag if tab.diag is not None else np.zeros((self.x.size - 1, self.y.size - 1), np.uint8)
+        self.diag = np.ascontiguousarray(d, np.uint8)
+        self.c = OrcEos(self.x.size, self.y.size, _dp(self.x), _dp(self.y), _dp(self.z),
+                        self.diag.ctypes.data_as(C.POINTER(C.c_ubyte)))
+
+    def interp(self, x, y):
+        L = _ttm_lib()
+        return np.array([L.orc_eos_interp(C.byref(self.c), float(a), float(b)) for a, b in zip(x, y)])
+
+    def te_from_r_ee(self, r, e):
+        L = _ttm_lib()
+        return np.array([L.orc_eos_te_from_r_ee(C.byref(self.c), float(a), float(b)) for a, b in zip(r, e)])
+
+
+class TtmOracle:
+    """calc_ttm + move_atoms_ttm of the reference (1-D TTM), emulating P MPI ranks."""
+
+    def __init__(self, tp, eos, box, r2_cut_pair, timestep, nranks):
+        self.L = _ttm_lib()
+        self.cve, self.ee = Eos(eos["cve"]), Eos(eos["ee"])
+        box = np.asarray(box, np.float64).reshape(3, 3)
+        self.par = OrcTtmParams(tp.ttmdimx, nranks, tp.fd_n_timesteps, tp.fd_min_atoms, tp.vlatdim, tp.vlatbuffer,
+                                tp.vlatdens, tp.atomic_weight, tp.atomic_charge, tp.Temin, timestep,
+                                box[0, 0], box[1, 1], box[2, 2], r2_cut_pair, tp.I0, tp.lam, tp.laser_t_0,
+                                tp.laser_sigma_t, tp.tmm_laser_threshold, tp.src_mu, tp.src_abs)
+        self.G = tp.ttmdimx
+        self.vlatdim = tp.vlatdim
+        self.t = self.L.orc_ttm_create(C.byref(self.par), C.byref(self.cve.c), C.byref(self.ee.c))
+        if not self.t:
+            raise RuntimeError("orc_ttm_create failed (ttmdimx % nranks != 0?)")
+
+    def close(self):
+        if getattr(self, "t", None):
+            self.L.orc_ttm_destroy(self.t)
+            self.t = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def step(self, steps, pos, mom, mass, types, numneighs, fdi):
+        """fdi: int32 [n] in/out (slab index of the previous call)."""
+        n = pos.shape[0]
+        pos = np.ascontiguousarray(pos, np.float64); mom = np.ascontiguousarray(mom, np.float64)
+        mass = np.ascontiguousarray(np.broadcast_to(np.asarray(mass, np.float64), (n,)))
+        types = np.ascontiguousarray(types, np.int32); nn = np.ascontiguousarray(numneighs, np.int32)
+        assert fdi.dtype == np.int32 and fdi.flags.c_contiguous
+        rc = self.L.orc_ttm_step(self.t, int(steps), n, _dp(pos), _dp(mom), _dp(mass), _ip(types), _ip(nn), _ip(fdi))
+        if rc != 0:
+            raise RuntimeError("orc_ttm_step: " + self.L.orc_ttm_error(self.t).decode())
+
+    def cells(self):
+        f = np.zeros((self.G, len(TTM_FIELDS)))
+        self.L.orc_ttm_get_cells(self.t, _dp(f))
+        return {k: f[:, i].copy() for i, k in enumerate(TTM_FIELDS)}
+
+    def arrays(self):
+        xi = np.zeros(self.G); vcom = np.zeros((3, self.G)); na = np.zeros(self.G)
+        fl = np.zeros(self.G); fr = np.zeros(self.G)
+        self.L.orc_ttm_get_arrays(self.t, _dp(xi), _dp(vcom), _dp(na), _dp(fl), _dp(fr))
+        return dict(xiarr=xi, vcom=vcom, natomsglobal=na, fluxl=fl, fluxr=fr)
+
+    def scalars(self):
+        s = np.zeros(16)
+        self.L.orc_ttm_get_scalars(self.t, _dp(s))
+        keys = ["diff_substeps", "max_dt_ttm", "last_active_cell_global", "cur_vlattice_proc", "Eabs",
+                "tot_elec_energy", "fd_hx", "fd_vol", "neighvol", "laser_active", "tmm_time"]
+        return dict(zip(keys, s))
+
+    def vlattice(self):
+        v = np.zeros((max(self.vlatdim, 1), 6))
+        self.L.orc_ttm_get_vlattice(self.t, _dp(v))
+        return v[: self.vlatdim]
+
+    def move_atoms(self, pos, mom, force, mass, types, vtypes=None, restrictions=None, pdecay=None):
+        n = pos.shape[0]
+        assert pos.flags.c_contiguous and mom.flags.c_contiguous
+        force = np.ascontiguousarray(force, np.float64)
+        mass = np.ascontiguousarray(np.broadcast_to(np.asarray(mass, np.float64), (n,)))
+        types = np.ascontiguousarray(types, np.int32)
+        vt = types if vtypes is None else np.ascontiguousarray(vtypes, np.int32)
+        rs = np.ones((int(vt.max()) + 1, 3)) if restrictions is None else np.ascontiguousarray(restrictions, np.float64)
+        pd = pdecay or (0, 0.0, 0.0, 1.0)
+        return self.L.orc_move_atoms_ttm(self.t, n, _dp(pos), _dp(mom), _dp(force), _dp(mass), _ip(types), _ip(vt),
+                                         _dp(rs), int(pd[0]), float(pd[1]), float(pd[2]), float(pd[3]))
