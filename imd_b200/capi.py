@@ -25,6 +25,22 @@ c_lp = C.POINTER(C.c_int64)
 _lib = None
 
 
+class TtmParamsC(C.Structure):
+    """imdcu_ttm_params (include/imdcu.h)."""
+    _fields_ = [("ttmdimx", C.c_int), ("nranks_ref", C.c_int), ("fd_n_timesteps", C.c_int),
+                ("fd_min_atoms", C.c_int), ("vlatdim", C.c_int), ("vlatbuffer", C.c_int),
+                ("vlatdens", C.c_double), ("atomic_weight", C.c_double), ("atomic_charge", C.c_double),
+                ("Temin", C.c_double), ("I0", C.c_double), ("lam", C.c_double), ("laser_t_0", C.c_double),
+                ("laser_sigma_t", C.c_double), ("tmm_laser_threshold", C.c_double), ("src_mu", C.c_double),
+                ("src_abs", C.c_double)]
+
+
+TTM_FIELDS = ["natoms", "natoms_old", "temp", "md_temp", "xi", "dens", "fd_k", "fd_g", "Z", "ne", "Ce", "U",
+              "source"]
+TTM_SCALARS = ["diff_substeps", "max_dt_ttm", "last_active_cell_global", "cur_vlattice_proc", "Eabs",
+               "tot_elec_energy", "fd_hx", "fd_vol", "neighvol", "laser_active", "tmm_time", "err"]
+
+
 class ImdcuError(RuntimeError):
     def __init__(self, code, msg):
         super().__init__("imdcu error %d: %s" % (code, msg))
@@ -57,6 +73,12 @@ def load():
         "imdcu_calc_forces": (C.c_int, [vp, C.c_int, c_dp]),
         "imdcu_move_atoms_nve": (C.c_int, [vp, c_dp, c_ip]),
         "imdcu_run_nve": (C.c_int, [vp, C.c_int, C.c_int, c_dp]),
+        "imdcu_ttm_set_eos": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, c_dp, c_dp, c_dp, C.POINTER(C.c_ubyte)]),
+        "imdcu_ttm_init": (C.c_int, [vp, C.POINTER(TtmParamsC)]),
+        "imdcu_calc_ttm": (C.c_int, [vp, C.c_int, c_dp]),
+        "imdcu_move_atoms_ttm": (C.c_int, [vp, c_dp, c_ip]),
+        "imdcu_run_ttm": (C.c_int, [vp, C.c_int, C.c_int, c_dp]),
+        "imdcu_download_ttm": (C.c_int, [vp, c_dp, c_dp, c_dp, c_dp]),
         "imdcu_get_cell_grid": (C.c_int, [vp, c_ip, c_dp]),
         "imdcu_get_nblist_pairs": (C.c_int, [vp, c_lp, c_ip]),
         "imdcu_nbl_count": (C.c_int, [vp]),
@@ -184,6 +206,46 @@ class Context:
         e = np.zeros((nsteps, 2)) if want_energies else None
         self._ck(self.L.imdcu_run_nve(self.h, first_step, nsteps, _dp(e)))
         return e
+
+    # ---- two-temperature model
+    def ttm_set_eos(self, which, tab):
+        """tab: imd_b200.synth.EosTable (x, y, z[nx,ny], diag[nx-1,ny-1] or None)."""
+        x = np.ascontiguousarray(tab.x, np.float64); y = np.ascontiguousarray(tab.y, np.float64)
+        z = np.ascontiguousarray(tab.z, np.float64)
+        d = None if tab.diag is None else np.ascontiguousarray(tab.diag, np.uint8)
+        dp = None if d is None else d.ctypes.data_as(C.POINTER(C.c_ubyte))
+        self._ck(self.L.imdcu_ttm_set_eos(self.h, which, x.size, y.size, _dp(x), _dp(y), _dp(z), dp))
+
+    def ttm_init(self, tp, nranks_ref=1):
+        """tp: imd_b200.synth.TtmParams."""
+        self._ttm_G, self._ttm_vlatdim = tp.ttmdimx, tp.vlatdim
+        par = TtmParamsC(tp.ttmdimx, nranks_ref, tp.fd_n_timesteps, tp.fd_min_atoms, tp.vlatdim, tp.vlatbuffer,
+                         tp.vlatdens, tp.atomic_weight, tp.atomic_charge, tp.Temin, tp.I0, tp.lam, tp.laser_t_0,
+                         tp.laser_sigma_t, tp.tmm_laser_threshold, tp.src_mu, tp.src_abs)
+        self._ck(self.L.imdcu_ttm_init(self.h, C.byref(par)))
+
+    def calc_ttm(self, steps, want_scalars=True):
+        out = np.zeros(16) if want_scalars else None
+        self._ck(self.L.imdcu_calc_ttm(self.h, int(steps), _dp(out)))
+        return None if out is None else dict(zip(TTM_SCALARS, out))
+
+    def move_atoms_ttm(self):
+        out = np.zeros(8); valid = C.c_int32(0)
+        self._ck(self.L.imdcu_move_atoms_ttm(self.h, _dp(out), C.byref(valid)))
+        return out, bool(valid.value)
+
+    def run_ttm(self, first_step, nsteps, want_energies=True):
+        e = np.zeros((nsteps, 2)) if want_energies else None
+        self._ck(self.L.imdcu_run_ttm(self.h, first_step, nsteps, _dp(e)))
+        return e
+
+    def download_ttm(self):
+        G, nv = self._ttm_G, self._ttm_vlatdim
+        cells = np.zeros((G, len(TTM_FIELDS))); xi = np.zeros(G); vcom = np.zeros((3, G))
+        vlat = np.zeros((max(nv, 1), 6))
+        self._ck(self.L.imdcu_download_ttm(self.h, _dp(cells), _dp(xi), _dp(vcom), _dp(vlat)))
+        d = {k: cells[:, i].copy() for i, k in enumerate(TTM_FIELDS)}
+        return dict(fields=d, xiarr=xi, vcom=vcom, vlat=vlat[:nv])
 
     # ---- inspection
     def cell_grid(self):

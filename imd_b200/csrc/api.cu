@@ -51,6 +51,35 @@ extern "C" int imdcu_run_nve(imdcu_ctx *c, int first_step, int nsteps, double *e
   return IMDCU_OK;
 }
 
+// calc_ttm (imd_main_3d.c:534 -> imd_ttm.c:75)
+extern "C" int imdcu_calc_ttm(imdcu_ctx *c, int steps, double out16[16])
+{
+  RET_IF(check_ready(c));
+  return imdcu_ttm_step(c, steps, out16);
+}
+
+// move_atoms_ttm + check_nblist (imd_main_3d.c:564, :812)
+extern "C" int imdcu_move_atoms_ttm(imdcu_ctx *c, double out8[8], int *have_valid_nbl)
+{
+  RET_IF(check_ready(c));
+  return imdcu_integrate_ttm(c, out8, have_valid_nbl);
+}
+
+// main-loop segment with the TTM (imd_main_3d.c:406,534,564,812)
+extern "C" int imdcu_run_ttm(imdcu_ctx *c, int first_step, int nsteps, double *energies)
+{
+  RET_IF(check_ready(c));
+  double f8[8], m8[8], t16[16];
+  int valid = 0;
+  for (int s = 0; s < nsteps; s++) {
+    RET_IF(imdcu_calc_forces(c, first_step + s, energies ? f8 : nullptr));
+    RET_IF(imdcu_ttm_step(c, first_step + s, (s == nsteps - 1) ? t16 : nullptr));   // errors surface at the end
+    RET_IF(imdcu_integrate_ttm(c, m8, &valid));
+    if (energies) { energies[2 * s] = f8[0]; energies[2 * s + 1] = m8[0]; }
+  }
+  return IMDCU_OK;
+}
+
 extern "C" int imdcu_nbl_count(const imdcu_ctx *c) { return c ? c->nbl_count : -1; }
 
 extern "C" int imdcu_invalidate_nblist(imdcu_ctx *c)

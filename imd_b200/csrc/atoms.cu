@@ -91,6 +91,10 @@ extern "C" int imdcu_upload_atoms(imdcu_ctx *c, int64_t n, const int32_t *id, co
   CU_CHECK(c, cudaMemsetAsync(c->rho.p, 0, n * sizeof(double), s));
   CU_CHECK(c, cudaMemsetAsync(c->numneighs.p, 0, n * sizeof(int), s));
   CU_CHECK(c, cudaMemsetAsync(c->key.p, 0, n * sizeof(int), s));
+  if (c->ttm.inited) {                          // fresh atoms: no stored FD slab yet
+    CU_CHECK(c, c->ttm.fdi.ensure(c->key.cap)); CU_CHECK(c, c->ttm.fdi_alt.ensure(c->key.cap));
+    CU_CHECK(c, cudaMemsetAsync(c->ttm.fdi.p, 0, c->key.cap * sizeof(int), s));
+  }
   CU_CHECK(c, cudaStreamSynchronize(s));
   c->n = n; c->ng = 0;
   c->have_valid_nbl = false;

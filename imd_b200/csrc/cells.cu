@@ -55,11 +55,13 @@ k_gather(int n, const int *__restrict__ perm,
          const int *__restrict__ type_in, const int *__restrict__ vtype_in, const int *__restrict__ id_in,
          double4 *__restrict__ pos_out, double4 *__restrict__ mom_out,
          int *__restrict__ type_out, int *__restrict__ vtype_out, int *__restrict__ id_out,
-         double *__restrict__ refx, double *__restrict__ refy, double *__restrict__ refz)
+         double *__restrict__ refx, double *__restrict__ refy, double *__restrict__ refz,
+         const int *__restrict__ fdi_in, int *__restrict__ fdi_out)
 {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   int s = perm[i];
+  if (fdi_in) fdi_out[i] = fdi_in[s];              // p->fdi travels with the atom (imd_ttm.c:313)
   double4 p = pos_in[s];
   pos_out[i] = p;
   mom_out[i] = mom_in[s];
@@ -213,8 +215,10 @@ int imdcu_rebuild_cells(imdcu_ctx *c)
   CU_CHECK(c, c->type_alt.ensure_exact(c->type.cap));
   k_gather<<<nb, 256, 0, st>>>(n, c->perm_alt.p, c->pos4.p, c->mom4.p, c->type.p, c->vtype.p, c->id.p,
                                c->pos4_alt.p, c->mom4_alt.p, c->type_alt.p, c->vtype_alt.p, c->id_alt.p,
-                               c->refx.p, c->refy.p, c->refz.p);
+                               c->refx.p, c->refy.p, c->refz.p,
+                               c->ttm.inited && c->ttm.fdi.cap >= (size_t) n ? c->ttm.fdi.p : nullptr, c->ttm.fdi_alt.p);
   c->count_launch();
+  if (c->ttm.inited && c->ttm.fdi.cap >= (size_t) n) swap_buf(c->ttm.fdi, c->ttm.fdi_alt);
   swap_buf(c->pos4, c->pos4_alt); swap_buf(c->mom4, c->mom4_alt); swap_buf(c->type, c->type_alt);
   swap_buf(c->vtype, c->vtype_alt); swap_buf(c->id, c->id_alt); swap_buf(c->key, c->key_alt);
 

@@ -120,6 +120,45 @@ struct GhostCell {
 
 struct Reduce8 { double v[8]; };
 
+// ----------------------------------------------------------------------------- TTM (1-D)
+// One FD cell, the fields of ttm_Element (types.h:441-492) the TTM1D path touches.
+struct TCell {
+  int    natoms, natoms_old;
+  double temp, xi, md_temp, source, dens, fd_k, fd_g, Z, Ce, ne, U;
+};
+
+// rectilinear EOS table + diagonal flags of the reference's Delaunay triangulation
+struct EosView {
+  int nx, ny;
+  const double *x, *y, *z;
+  const unsigned char *diag;
+};
+
+struct TtmState {
+  bool   inited = false;
+  imdcu_ttm_params p;
+  int    G = 0, P = 1, L = 0, LD = 0;
+  double fd_hx = 0, fd_vol = 0, neighvol = 0, omega_laser = 0, sigma_t_sq = 0;
+  // EOS tables (device)
+  DevBuf<double> eos_buf[2];
+  DevBuf<unsigned char> eos_diag[2];
+  int    eos_nx[2] = {0, 0}, eos_ny[2] = {0, 0};
+  bool   eos_set[2] = {false, false};
+  // lattices: lat[0], lat[1] = [P*LD] TCell each; vlat[0], vlat[1] = [vlatdim]
+  DevBuf<TCell> lat, vlat;
+  // slab sums: ints {natoms, totneighs, fluxl, fluxr}[G], doubles {px,py,pz,mdtemp}[G]
+  DevBuf<int>    isum;
+  DevBuf<double> dsum;
+  DevBuf<double> xiarr;             // [G] xiarr_global
+  DevBuf<double> xiloc;             // [P*LD] xiarr_local
+  DevBuf<double> vcom;              // [3*G]
+  DevBuf<double> src_e;             // [P*LD] exp(-mu*depth) per cell
+  DevBuf<int>    fdi, fdi_alt;      // per atom: slab of the previous step (p->fdi)
+  // device scalars: see ttm.cu (TtmScal)
+  void  *d_scal = nullptr;
+  void  *h_scal = nullptr;          // pinned mirror
+};
+
 // ----------------------------------------------------------------------------- context
 struct imdcu_ctx {
   int          device = 0;
@@ -181,6 +220,8 @@ struct imdcu_ctx {
   int *d_flags = nullptr;                    // [8] ints: overflow, maxneigh, is_short ...
   int *h_flags = nullptr;                    // pinned
 
+  TtmState ttm;
+
   // bookkeeping
   int64_t launches = 0;
   bool    profiling = false;
@@ -217,6 +258,9 @@ int imdcu_refresh_ghosts(imdcu_ctx *ctx, bool at_build); // cells.cu
 int imdcu_build_nblist(imdcu_ctx *ctx);                  // nblist.cu
 int imdcu_eam_forces(imdcu_ctx *ctx, double out8[8]);    // eam.cu
 int imdcu_integrate_nve(imdcu_ctx *ctx, double out8[8], int *valid);   // integrate.cu
+int imdcu_integrate_ttm(imdcu_ctx *ctx, double out8[8], int *valid);   // integrate.cu
+int imdcu_ttm_step(imdcu_ctx *ctx, int steps, double out16[16]);       // ttm.cu
+void imdcu_ttm_release(imdcu_ctx *ctx);                                // ttm.cu
 TabView imdcu_tab_view(const DevTable &t);
 
 static inline int div_up(int64_t a, int64_t b) { return (int) ((a + b - 1) / b); }

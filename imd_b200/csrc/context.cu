@@ -69,6 +69,7 @@ extern "C" int imdcu_destroy(imdcu_ctx *c)
   c->d_gplan.release(); c->gcell_off.release(); c->ghost_src.release(); c->ghost_code.release();
   c->ghost_root.release(); c->ghost_tcode.release(); c->ghost_raw.release();
   c->nbl_idx.release(); c->nbl_num.release(); c->partials.release(); c->d_restrictions.release();
+  imdcu_ttm_release(c);
   for (int t = 0; t < 3; t++) {
     if (c->tab[t].coef) cudaFree(c->tab[t].coef);
     if (c->tab[t].begin) cudaFree(c->tab[t].begin);

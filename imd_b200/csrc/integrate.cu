@@ -43,7 +43,59 @@ k_move_nve(MoveArgs a)
   grid_reduce<1, 1>(dmax, a.partials + gridDim.x, a.ticket + 1, a.results + 1);
 }
 
-int imdcu_integrate_nve(imdcu_ctx *c, double out8[8], int *valid)
+// move_atoms_ttm (imd_integrate.c:581-811, TTM1D [+PDECAY]): as above plus the electron-phonon
+// coupling force xi * m * (p/m - v_com) with xi, v_com of the atom's FD slab (:649-667, 738-747).
+// xiarr/vcom are G-sized and cache resident; +12 B/atom (type, slab arithmetic on x).
+__global__ void __launch_bounds__(256)
+k_move_ttm(MoveArgs a, const int *__restrict__ type, int G, double fd_hx,
+           const double *__restrict__ xiarr, const double *__restrict__ vcom)
+{
+  double ekin[1] = {0.0}, dmax[1] = {0.0};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += gridDim.x * blockDim.x) {
+    double4 p = a.mom4[i];
+    const double4 f4 = a.frc4[i];
+    double4 x = a.pos4[i];
+    const double *rs = a.restrictions + 3 * a.vtype[i];
+    const double m = p.w;
+    int ig = 0;
+    double xi = 0.0;
+    if (type[i] == 0) {
+      ig = (int) (x.x / fd_hx);
+      ig = ig < G - 1 ? ig : G - 1;
+      ig = ig > 0 ? ig : 0;
+      xi = xiarr[ig];
+    }
+    const double k1 = p.x * p.x + p.y * p.y + p.z * p.z;
+    double fx = f4.x * rs[0], fy = f4.y * rs[1], fz = f4.z * rs[2];
+    if (a.pdecay && x.x > a.ramp_start)
+      fx -= (p.x / m) * a.xipdecay * a.pd_a * (x.x - a.ramp_start) * (x.x - a.ramp_start);
+    const double vx = vcom[ig], vy = vcom[G + ig], vz = vcom[2 * G + ig];
+    p.x += a.timestep * (fx + xi * m * (p.x / m - vx));
+    p.y += a.timestep * (fy + xi * m * (p.y / m - vy));
+    p.z += a.timestep * (fz + xi * m * (p.z / m - vz));
+    const double k2 = p.x * p.x + p.y * p.y + p.z * p.z;
+    ekin[0] += (k1 + k2) / (4 * m);
+    const double tmp = a.timestep / m;
+    x.x += tmp * p.x; x.y += tmp * p.y; x.z += tmp * p.z;
+    a.mom4[i] = p;
+    a.pos4[i] = x;
+    const double dx = x.x - a.refx[i], dy = x.y - a.refy[i], dz = x.z - a.refz[i];
+    dmax[0] = fmax(dmax[0], r2_exact(dx, dy, dz));
+  }
+  grid_reduce<1, 0>(ekin, a.partials, a.ticket, a.results);
+  grid_reduce<1, 1>(dmax, a.partials + gridDim.x, a.ticket + 1, a.results + 1);
+}
+
+static int integrate(imdcu_ctx *c, double out8[8], int *valid, bool ttm);
+
+int imdcu_integrate_nve(imdcu_ctx *c, double out8[8], int *valid) { return integrate(c, out8, valid, false); }
+int imdcu_integrate_ttm(imdcu_ctx *c, double out8[8], int *valid)
+{
+  if (!c->ttm.inited) return c->fail(IMDCU_EINVAL, "imdcu_ttm_init has not been called");
+  return integrate(c, out8, valid, true);
+}
+
+static int integrate(imdcu_ctx *c, double out8[8], int *valid, bool ttm)
 {
   PhaseTimer pt(c, 6);
   MoveArgs a;
@@ -57,7 +109,8 @@ int imdcu_integrate_nve(imdcu_ctx *c, double out8[8], int *valid)
   const int grid = std::max(1, std::min(div_up(a.n, 256), c->num_sms * 8));
   CU_CHECK(c, c->partials.ensure((size_t) grid * 4 + 64));
   a.partials = c->partials.p; a.ticket = c->d_ticket + 2; a.results = c->d_results + 4;
-  k_move_nve<<<grid, 256, 0, c->stream>>>(a);
+  if (ttm) k_move_ttm<<<grid, 256, 0, c->stream>>>(a, c->type.p, c->ttm.G, c->ttm.fd_hx, c->ttm.xiarr.p, c->ttm.vcom.p);
+  else k_move_nve<<<grid, 256, 0, c->stream>>>(a);
   c->count_launch();
   CU_CHECK(c, cudaGetLastError());
   CU_CHECK(c, cudaMemcpyAsync(c->h_results + 4, c->d_results + 4, 2 * sizeof(double),

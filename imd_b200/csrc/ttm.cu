@@ -1,0 +1,865 @@
+// imd_b200/csrc/ttm.cu -- the 1-D two-temperature model on the device: calc_ttm
+// (imd_ttm.c:75-156) and everything it calls.
+//
+//   k_ttm_atoms1 : update_fd's first atom loop (imd_ttm.c:269-318): atoms -> FD slabs
+//                  (count, sum numneighs, sum p, left/right fluxes vs the stored slab index)
+//   k_ttm_atoms2 : update_fd's second atom loop (:368-394): sum m (p/m - v_com)^2
+//   k_ttm_grid   : the G-sized rest of calc_ttm in ONE launch: reconstruct l1/l2 (:401-541),
+//                  do_ADV incl. the Brent inverse of the EOS (:1208-1301, fminbnd3.c),
+//                  do_cell_activation (:1311-1425), do_FILLMESH (:629-852), CFL_maxdt
+//                  (:2444-2480) and the whole sub-step loop {source, do_DIFF (:1473-1678),
+//                  do_FILLMESH, ttm_fill_ghost_layers (:3264-3356)} -- diff_substeps is decided
+//                  on the device, so the >= fd_n_timesteps sub-steps need no host round trip.
+//
+// The FD lattice is tiny (G = ttmdimx cells, L2/L1 resident); its cost is latency (~15 pow per
+// cell and sub-step), so one CTA works on it while the atom kernels are HBM-streaming kernels.
+// The reference's result depends on its MPI decomposition; the lattice keeps the reference's
+// layout for P = nranks_ref emulated ranks: P x (L+2) cells with ghost cells, two lattices
+// swapped by index (l1/l2).  Compiled with -fmad=false: the Brent iteration must see the
+// same IEEE operations as the host code.
+#include "device.cuh"
+
+#include <cmath>
+
+#define RHOMIN 2
+namespace {
+__constant__ const double C_ECONST = 8.841941282883075e-12;
+__constant__ const double C_HBAR = 1.054571800139113e-34;
+__constant__ const double C_EMASS = 9.109383560000000e-31;
+__constant__ const double C_BOLTZMAN = 1.380648520000000e-23;
+__constant__ const double C_ECHARGE = 1.602176620000000e-19;
+__constant__ const double C_AMU = 1.660539040200000e-27;
+__constant__ const double C_J2eV = 6.2415090744607626077762409809304458998869658961709711e18;
+__constant__ const double C_eV2J = 1.602176634E-19;
+}
+
+#define DMAX(a, b) ((a) > (b) ? (a) : (b))
+#define DMIN(a, b) ((a) < (b) ? (a) : (b))
+#define DABS(a) ((a) > 0 ? (a) : -(a))
+
+// ----------------------------------------------------------------------------- EOS tables
+__device__ __forceinline__ int eos_find(const double *a, int n, double v)
+{
+  if (!(v >= a[0]) || !(v <= a[n - 1])) return -1;
+  int lo = 0, hi = n - 1;
+  while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (a[mid] <= v) lo = mid; else hi = mid; }
+  return lo;
+}
+
+// linear interpolation on the reference's triangulation (lpi_interpolate_point)
+__device__ double eos_interp(const EosView &e, double x, double y)
+{
+  const int i = eos_find(e.x, e.nx, x), j = eos_find(e.y, e.ny, y);
+  if (i < 0 || j < 0) return nan("");
+  const int ny = e.ny;
+  const double x0 = e.x[i], x1 = e.x[i + 1], y0 = e.y[j], y1 = e.y[j + 1];
+  const double z00 = e.z[i * ny + j], z01 = e.z[i * ny + j + 1];
+  const double z10 = e.z[(i + 1) * ny + j], z11 = e.z[(i + 1) * ny + j + 1];
+  const double u = (x - x0) / (x1 - x0), v = (y - y0) / (y1 - y0);
+  const int d = e.diag[i * (ny - 1) + j];
+  if (d == 0) {
+    if (v <= u) return z00 + u * (z10 - z00) + v * (z11 - z10);
+    return z00 + u * (z11 - z01) + v * (z01 - z00);
+  }
+  if (u + v <= 1.0) return z00 + u * (z10 - z00) + v * (z01 - z00);
+  return z11 + (1.0 - u) * (z01 - z11) + (1.0 - v) * (z10 - z11);
+}
+
+__device__ __forceinline__ double eos_ee_from_r_te(const EosView &ee, double r, double t)
+{
+  return eos_interp(ee, r, sqrt(t));                                   // imd_ttm.c:2483-2529
+}
+__device__ __forceinline__ double eos_cve_from_r_te(const EosView &cve, double r, double t)
+{
+  double z = eos_interp(cve, r, t);                                    // imd_ttm.c:2531-2592
+  z *= r; z *= 11604.5; z *= 1e-30; z *= C_J2eV;
+  return z;
+}
+
+__device__ __forceinline__ double eeminfun(const EosView &ee, double x, double r, double e)
+{
+  double a = eos_ee_from_r_te(ee, r, x) - e;
+  return DABS(a);
+}
+
+// fminbnd (fminbnd3.c:6-106) incl. the effect of the unparenthesised SIGNUM macro (makros.h:338)
+__device__ double fminbnd_ref(const EosView &ee, double a, double b, double rho, double eng)
+{
+  const double tolx = 1e-5;
+  const double c = 0.5 * (3 - sqrt(5.0));
+  double v = a + c * (b - a), w = v, x = v, e = 0;
+  double fv = eeminfun(ee, x, rho, eng), fw = fv, fval = fv, fu = 0.0;
+  const int imax = 500;
+  double xm, tol, r, q, p, d = 0.0, u;
+  const double sqrteps = 2.220446049250313e-16;
+  int dogs;
+  for (int i = 0; i < imax + 1; i++) {
+    xm = 0.5 * (a + b);
+    tol = 2.0 * sqrteps * DABS(x) + tolx / 3.0;
+    if (DABS(x - xm) <= (2 * tol - 0.5 * (b - a)) || i == imax) return x;
+    if (DABS(e) > tol) {
+      dogs = 0;
+      r = (x - w) * (fval - fv);
+      q = (x - v) * (fval - fw);
+      p = (x - v) * q - (x - w) * r;
+      q = 2 * (q - r);
+      p *= (q > 0) ? 1 : ((q < 0) ? -1 : 0);
+      q = DABS(q);
+      r = e;
+      e = d;
+      if (DABS(p) < DABS(0.5 * q * r) && p > q * (a - x) && p < q * (b - x)) {
+        d = p / q;
+        u = x + d;
+        if (DMIN(u - a, b - u) < 2 * tol) d = tol * ((xm - x > 0) ? 1 : (((xm - x < 0) ? -1 : 0) + (xm == x)));
+      } else dogs = 1;
+    } else dogs = 1;
+    if (dogs == 1) {
+      e = (x >= xm ? a - x : b - x);
+      d = c * e;
+    }
+    u = x + DMAX(DABS(d), tol) * ((d > 0) ? 1 : (((d < 0) ? -1 : 0) + (d == 0)));
+    fu = eeminfun(ee, u, rho, eng);
+    if (fu < fval) {
+      if (u < x) b = x; else a = x;
+      v = w; fv = fw; w = x; fw = fval; x = u; fval = fu;
+    } else {
+      if (u < x) a = u; else b = u;
+      if (fu <= fw || w == x) { v = w; fv = fw; w = u; fw = fu; }
+      else if (fu <= fv || v == x || v == w) { v = u; fv = fu; }
+    }
+  }
+  return -1;
+}
+
+// EOS_te_from_r_ee (imd_ttm.c:2699-2724)
+__device__ double eos_te_from_r_ee(const EosView &ee, double r, double e)
+{
+  if (r < ee.x[0] || r > ee.x[ee.nx - 1]) { r = DMIN(r, ee.x[ee.nx - 1]); r = DMAX(r, ee.x[0]); }
+  const double a = ee.y[0] * ee.y[0], b = ee.y[ee.ny - 1] * ee.y[ee.ny - 1];     // pow(y, 2.0) is exact y*y
+  return fminbnd_ref(ee, a, b, r, e);
+}
+
+// ----------------------------------------------------------------------------- wide-range models (imd_ttm.c:2191-2399)
+__device__ __forceinline__ double fermi_E(double ne)
+{
+  return C_HBAR * C_HBAR * pow(3.0 * M_PI * M_PI * ne, 2.0 / 3.0) / 2.0 / C_EMASS;
+}
+__device__ __forceinline__ double fermi_T(double ne) { return 2.0 * fermi_E(ne) / (3.0 * C_BOLTZMAN); }
+__device__ __forceinline__ double omega_pl(double ne) { return sqrt(ne * C_ECHARGE * C_ECHARGE / C_EMASS / C_ECONST); }
+__device__ __forceinline__ double r0_(double ni) { return pow(3.0 / (4 * M_PI * ni), 1.0 / 3.0); }
+__device__ __forceinline__ double bMin(double Z, double Te)
+{
+  return DMAX(Z * C_ECHARGE * C_ECHARGE / (C_BOLTZMAN * Te), C_HBAR / sqrt(2 * C_EMASS * C_BOLTZMAN * Te));
+}
+__device__ double bMax(double omega_las, double Z, double ni, double Te, int la)
+{
+  const double ft = fermi_T(ni * Z);
+  const double teff = sqrt(Te * Te + ft * ft);
+  if (la) return DMAX(r0_(ni), sqrt(C_BOLTZMAN * teff / (C_EMASS)) / DMAX(omega_las, omega_pl(ni * Z)));
+  return DMAX(r0_(ni), sqrt(C_BOLTZMAN * teff / (C_EMASS)) / omega_pl(ni * Z));
+}
+__device__ double coulomb_log(double omega_las, double Z, double ni, double Te, int la)
+{
+  return DMAX(2.0, log(bMax(omega_las, Z, ni, Te, la) / bMin(Z, Te)));
+}
+__device__ double mean_charge(double temp, double rho, double z0, double am)
+{
+  temp *= 1e-3; rho *= 1e-3;
+  const double YA1 = 0.003323, YA2 = 0.971832, YA3 = 0.926148e-5, YA4 = 3.10165, YB0 = -1.7630, YB1 = 1.43175,
+               YB2 = 0.315463, YC1 = 0.036666667, YC2 = 0.983333333, YAL = 0.143139e2, YBE = 0.6624e0;
+  const double t0 = temp / pow(z0, 4. / 3.);
+  const double r0 = rho / (z0 * am);
+  const double ytf = t0 / (1.0 + t0);
+  const double ya = YA1 * pow(t0, YA2) + YA3 * pow(t0, YA4);
+  const double yb = -exp(YB0 + YB1 * ytf + YB2 * ytf * ytf);
+  const double yc = YC1 * ytf + YC2;
+  const double yq1 = ya * pow(r0, yb);
+  const double yq = pow(pow(r0, yc) + pow(yq1, yc), 1.0 / yc);
+  const double yx = YAL * pow(yq, YBE);
+  return z0 * yx / (1.0 + yx + sqrt(1.0 + 2.0 * yx));
+}
+__device__ __forceinline__ double numet(double A1, double A2, double Te, double Ti, double TF)
+{
+  return 1.309202957843054e+11 * (A1 * Ti + A2 * Te * Te / TF);
+}
+__device__ __forceinline__ double numax(double A3, double vf, double Te, double ni)
+{
+  return A3 / r0_(ni) * sqrt(vf * vf + C_BOLTZMAN * Te / C_EMASS);
+}
+__device__ double nupl(double omega_las, double Z, double ni, double ne, double Te, int la)
+{
+  const double coulomb = coulomb_log(omega_las, Z, ni, Te, la);
+  return 1.863839656495274e-40 * Z * ne * coulomb / pow(C_BOLTZMAN * Te, 1.5);
+}
+__device__ double get_gamma(double Te, double Ti, double Ne, double Z, double omega_laser, int la)
+{
+  Te *= 11604.5; Ti *= 11604.5;
+  const double A1g = 50, A2g = 20, A3g = 0.25, m_atom = 26.9815;
+  const double Ni = Ne / Z;
+  const double EF = fermi_E(Ne);
+  const double TF = 4.828648689433765e+22 * EF;
+  const double VF = 1.481734876966785e+15 * sqrt(EF);
+  const double nu_eff = DMIN(numet(A1g, A2g, Te, Ti, TF), DMIN(numax(A3g, VF, Te, Ni), nupl(omega_laser, Z, Ni, Ne, Te, la)));
+  return 2.783313120645740e-74 / (m_atom * C_AMU) * Ne * nu_eff;
+}
+__device__ double get_kappa(double Te, double Ti, double Ne, double Z, double omega_laser, int la)
+{
+  Te *= 11604.5; Ti *= 11604.5;
+  const double A1t = 2.95, A2t = 0.5, A3t = 0.16, A4t = 1.2;
+  const double Ni = Ne / Z;
+  const double EF = fermi_E(Ne);
+  const double TF = 4.828648689433765e+22 * EF;
+  const double VF = 1.481734876966785e+15 * sqrt(EF);
+  const double nu_eff = DMIN(numet(A1t, A2t, Te, Ti, TF), numax(A3t, VF, Te, Ni));
+  const double coulomb = coulomb_log(omega_laser, Z, Ni, Te, la);
+  const double kappa_met = 6.884236239621913e-16 * Ne * Te / nu_eff;
+  const double kappa_pl = 4.428788911416808e+43 * pow(C_BOLTZMAN * Te, 2.5) / Z / coulomb;
+  const double kappa_wr = kappa_pl + (kappa_met - kappa_pl) * exp(-A4t * Te / TF);
+  return kappa_wr * 0.073768115942029;
+}
+
+// ----------------------------------------------------------------------------- device state
+struct TtmScal {                     // persists between MD steps (device), mirrored to the host on demand
+  int    cur, vcur;                  // which lattice is l1 / which virtual lattice is vlattice1
+  int    last_active_cell_global, cur_vlattice_proc;
+  int    diff_substeps, laser_active, err, pad;
+  double max_dt_ttm, tmm_time, Eabs, tot_elec_energy;
+};
+
+struct TtmArgs {
+  int G, P, L, LD, steps, ncell_tot;
+  imdcu_ttm_params p;
+  double timestep, fd_hx, fd_vol, neighvol, omega_laser, sigma_t_sq;
+  EosView cve, ee;
+  TCell *lat, *vlat;                 // [2][P*LD], [2][vlatdim]
+  int *isum; double *dsum;           // slab sums, see k_ttm_atoms1
+  double *xiarr, *xiloc, *vcom, *src_e;
+  TtmScal *scal;
+};
+
+// ----------------------------------------------------------------------------- atom kernels
+// slab index of an atom (imd_ttm.c:277-279)
+__device__ __forceinline__ int slab_of(double x, double fd_hx, int G)
+{
+  int ig = (int) (x / fd_hx);
+  ig = ig < G - 1 ? ig : G - 1;
+  ig = ig > 0 ? ig : 0;
+  return ig;
+}
+
+#define TTM_WIN 64                   // slabs privatised in shared memory per CTA
+
+// update_fd, first atom loop.  Atoms are cell-sorted (x slowest), so a CTA's atoms fall into
+// a few neighbouring slabs: sums go to a shared-memory window first, one flush per CTA.
+// isum = {natoms, totneighs, fluxl, fluxr}[G], dsum = {px, py, pz, mdtemp}[G]
+__global__ void __launch_bounds__(256)
+k_ttm_atoms1(int n, int G, double fd_hx, int steps, const double4 *__restrict__ pos4,
+             const double4 *__restrict__ mom4, const int *__restrict__ type, const int *__restrict__ numneighs,
+             int *__restrict__ fdi, int *__restrict__ isum, double *__restrict__ dsum)
+{
+  __shared__ int s_i[4][TTM_WIN];
+  __shared__ double s_d[3][TTM_WIN];
+  __shared__ int s_base;
+  for (int k = threadIdx.x; k < TTM_WIN; k += blockDim.x) {
+    s_i[0][k] = s_i[1][k] = s_i[2][k] = s_i[3][k] = 0;
+    s_d[0][k] = s_d[1][k] = s_d[2][k] = 0.0;
+  }
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  int ig = -1;
+  double4 p = make_double4(0, 0, 0, 0);
+  if (i < n && type[i] == 0) { ig = slab_of(pos4[i].x, fd_hx, G); p = mom4[i]; }
+  if (threadIdx.x == 0) s_base = 1 << 30;
+  __syncthreads();
+  if (ig >= 0) atomicMin(&s_base, ig);
+  __syncthreads();
+  const int base = s_base;
+  if (ig >= 0) {
+    const int nn = numneighs[i];
+    int fl = 0, fr = 0;
+    if (steps > 0) { const int old = fdi[i]; if (old > ig) fr = 1; else if (old < ig) fl = 1; }
+    fdi[i] = ig;
+    const int w = ig - base;
+    if (w < TTM_WIN) {
+      atomicAdd(&s_i[0][w], 1); atomicAdd(&s_i[1][w], nn);
+      if (fl) atomicAdd(&s_i[2][w], 1);
+      if (fr) atomicAdd(&s_i[3][w], 1);
+      atomicAdd(&s_d[0][w], p.x); atomicAdd(&s_d[1][w], p.y); atomicAdd(&s_d[2][w], p.z);
+    } else {
+      atomicAdd(&isum[ig], 1); atomicAdd(&isum[G + ig], nn);
+      if (fl) atomicAdd(&isum[2 * G + ig], 1);
+      if (fr) atomicAdd(&isum[3 * G + ig], 1);
+      atomicAdd(&dsum[ig], p.x); atomicAdd(&dsum[G + ig], p.y); atomicAdd(&dsum[2 * G + ig], p.z);
+    }
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < TTM_WIN; k += blockDim.x) {
+    const int g = base + k;
+    if (g < G && s_i[0][k] > 0) {
+      atomicAdd(&isum[g], s_i[0][k]); atomicAdd(&isum[G + g], s_i[1][k]);
+      if (s_i[2][k]) atomicAdd(&isum[2 * G + g], s_i[2][k]);
+      if (s_i[3][k]) atomicAdd(&isum[3 * G + g], s_i[3][k]);
+      atomicAdd(&dsum[g], s_d[0][k]); atomicAdd(&dsum[G + g], s_d[1][k]); atomicAdd(&dsum[2 * G + g], s_d[2][k]);
+    }
+  }
+}
+
+// update_fd, second atom loop: md_temp sums with v_com = sum p / (natoms * atomic_weight)
+__global__ void __launch_bounds__(256)
+k_ttm_atoms2(int n, int G, double fd_hx, double atomic_weight, const double4 *__restrict__ mom4,
+             const int *__restrict__ type, const int *__restrict__ fdi, const int *__restrict__ isum,
+             double *__restrict__ dsum)
+{
+  __shared__ double s_d[TTM_WIN];
+  __shared__ int s_base;
+  for (int k = threadIdx.x; k < TTM_WIN; k += blockDim.x) s_d[k] = 0.0;
+  if (threadIdx.x == 0) s_base = 1 << 30;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  int ig = -1;
+  if (i < n && type[i] == 0) ig = fdi[i];            // set by k_ttm_atoms1 from the same positions
+  __syncthreads();
+  if (ig >= 0) atomicMin(&s_base, ig);
+  __syncthreads();
+  const int base = s_base;
+  if (ig >= 0) {
+    const double4 p = mom4[i];
+    const double m = p.w;
+    const double totmass = (double) isum[ig] * atomic_weight;      // > 0: this atom is in the slab
+    const double vx = dsum[ig] / totmass, vy = dsum[G + ig] / totmass, vz = dsum[2 * G + ig] / totmass;
+    double d, t = 0.0;
+    d = p.x / m - vx; t += m * (d * d);
+    d = p.y / m - vy; t += m * (d * d);
+    d = p.z / m - vz; t += m * (d * d);
+    const int w = ig - base;
+    if (w < TTM_WIN) atomicAdd(&s_d[w], t); else atomicAdd(&dsum[3 * G + ig], t);
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < TTM_WIN; k += blockDim.x)
+    if (base + k < G && s_d[k] != 0.0) atomicAdd(&dsum[3 * G + base + k], s_d[k]);
+}
+
+// ----------------------------------------------------------------------------- grid kernel
+#define TTM_NT 1024
+
+__device__ __forceinline__ bool active_gt(const TCell &c, int mn) { return c.natoms >= mn && c.dens > RHOMIN; }
+__device__ __forceinline__ bool active_ge(const TCell &c, int mn) { return c.natoms >= mn && c.dens >= RHOMIN; }
+
+// block-wide reductions (deterministic tree); every thread of the CTA must call
+__device__ double block_reduce(double v, int op /*0 sum, 1 min*/, double *s_red)
+{
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const double t = __shfl_xor_sync(0xffffffffu, v, o);
+    v = op == 0 ? v + t : fmin(v, t);
+  }
+  __syncthreads();
+  if (lane == 0) s_red[warp] = v;
+  __syncthreads();
+  double r = op == 0 ? 0.0 : 1e300;
+  for (int k = 0; k < nw; k++) r = op == 0 ? r + s_red[k] : fmin(r, s_red[k]);
+  return r;
+}
+__device__ int block_reduce_int(int v, int op /*1 min, 2 max*/, int *s_red)
+{
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const int t = __shfl_xor_sync(0xffffffffu, v, o);
+    v = op == 1 ? min(v, t) : max(v, t);
+  }
+  __syncthreads();
+  if (lane == 0) s_red[warp] = v;
+  __syncthreads();
+  int r = s_red[0];
+  for (int k = 1; k < nw; k++) r = op == 1 ? min(r, s_red[k]) : max(r, s_red[k]);
+  return r;
+}
+
+// wide-range properties of one cell (the body of do_FILLMESH's active branch / the vlattice loop)
+__device__ void fill_props(const TtmArgs &a, TCell &c, int la)
+{
+  c.Z = mean_charge(c.temp * 11604.5, c.dens, a.p.atomic_charge, a.p.atomic_weight);
+  c.ne = c.Z * c.dens / (a.p.atomic_weight * C_AMU);
+  c.Ce = eos_cve_from_r_te(a.cve, c.dens, c.temp * 11604.5);
+  c.fd_k = get_kappa(c.temp, c.md_temp, c.ne, c.Z, a.omega_laser, la);
+  c.fd_g = get_gamma(c.temp, c.md_temp, c.ne, c.Z, a.omega_laser, la);
+}
+
+// do_FILLMESH (imd_ttm.c:629-852) for the calling thread's cells + the virtual lattice
+__device__ void fillmesh(const TtmArgs &a, TCell *l1, TCell *l2, TCell *v1, TCell *v2, int last_active,
+                         int rv, int la, int *err)
+{
+  const int ncell = a.P * a.L, mn = a.p.fd_min_atoms;
+  for (int c = threadIdx.x; c < ncell + a.p.vlatdim; c += blockDim.x) {
+    if (c < ncell) {
+      if (c > last_active) continue;
+      const int idx = (c / a.L) * a.LD + (c % a.L) + 1;
+      TCell &x = l1[idx], &y = l2[idx];
+      if (active_gt(x, mn)) {
+        fill_props(a, x, la);
+        y.ne = x.ne; y.Ce = x.Ce; y.fd_k = x.fd_k; y.fd_g = x.fd_g;
+        if (x.Ce < 0 || isnan(x.Ce)) atomicMax(err, 1);
+        if (isnan(x.fd_k) || x.fd_k < 0) atomicMax(err, 2);
+        if (isnan(x.fd_g) || x.fd_g < 0) atomicMax(err, 3);
+        if (a.steps < 1) {                                                 // :765-807
+          x.U = eos_ee_from_r_te(a.ee, x.dens, x.temp * 11604.5) * 26.9815 * C_AMU * C_J2eV;
+          y.U = x.U;
+          const double echeck = eos_ee_from_r_te(a.ee, x.dens, x.temp * 11604.5) * 26.9815 * C_AMU * C_J2eV;
+          const double tcheck = eos_te_from_r_ee(a.ee, x.dens, echeck / 26.9815 / C_AMU * C_eV2J) / 11604.5;
+          const double tinit = x.temp;
+          if (DABS(tcheck - tinit) > tinit * 0.01) atomicMax(err, 4);
+        }
+      } else { x.fd_k = 0.0; x.fd_g = 0.0; x.Z = 0.0; x.ne = 0.0; x.Ce = 0.0; x.temp = 0.0; }
+    } else if (rv >= 0 && rv < a.P) {                                      // :825-845
+      const int i = c - ncell;
+      fill_props(a, v1[i], la);
+      v2[i].Z = v1[i].Z; v2[i].ne = v1[i].ne; v2[i].fd_k = v1[i].fd_k; v2[i].fd_g = v1[i].fd_g;
+    }
+  }
+}
+
+// ttm_fill_ghost_layers (imd_ttm.c:3264-3356): one thread per emulated rank
+__device__ void fill_ghosts(const TtmArgs &a, TCell *l1)
+{
+  const int L = a.L, LD = a.LD, P = a.P;
+  for (int r = threadIdx.x; r < P; r += blockDim.x) {
+    if (r < P - 1) { l1[r * LD + L + 1].temp = l1[(r + 1) * LD + 1].temp; l1[r * LD + L + 1].fd_k = l1[(r + 1) * LD + 1].fd_k; }
+    if (r > 0) { l1[r * LD].temp = l1[(r - 1) * LD + L].temp; l1[r * LD].fd_k = l1[(r - 1) * LD + L].fd_k; }
+    if (r == 0) l1[r * LD].natoms = 0;
+    if (r == P - 1) l1[r * LD + L + 1].natoms = 0;
+  }
+}
+
+__global__ void __launch_bounds__(TTM_NT)
+k_ttm_grid(TtmArgs a)
+{
+  __shared__ double s_red[32];
+  __shared__ int s_ired[32];
+  __shared__ int s_last_active, s_rv, s_substeps;
+  __shared__ double s_maxdt;
+  const int G = a.G, P = a.P, L = a.L, LD = a.LD, ncell = P * L, mn = a.p.fd_min_atoms;
+  const int nl = P * LD;
+  TtmScal *sc = a.scal;
+  int cur = sc->cur, vcur = sc->vcur;
+  TCell *l1 = a.lat + cur * nl, *l2 = a.lat + (1 - cur) * nl;
+  TCell *v1 = a.vlat + vcur * a.p.vlatdim, *v2 = a.vlat + (1 - vcur) * a.p.vlatdim;
+  const int *natomsg = a.isum, *totneigh = a.isum + G, *fluxl = a.isum + 2 * G, *fluxr = a.isum + 3 * G;
+  int *err = &sc->err;
+
+  // ---------------------------------------------------------------- update_fd, grid part (:241-264, 341-363, 401-541)
+  for (int r = threadIdx.x; r < P; r += blockDim.x) l1[r * LD].temp = l1[r * LD + L + 1].temp = 0;
+  int last_local = -5000;
+  for (int c = threadIdx.x; c < ncell; c += blockDim.x) {
+    const int r = c / L, i = c % L + 1, g = c, idx = r * LD + i;
+    TCell &x = l1[idx], &y = l2[idx];
+    const double totmass = (double) natomsg[g] * a.p.atomic_weight;
+    if (totmass > 0) { a.vcom[g] = a.dsum[g] / totmass; a.vcom[G + g] = a.dsum[G + g] / totmass; a.vcom[2 * G + g] = a.dsum[2 * G + g] / totmass; }
+    else a.vcom[g] = a.vcom[G + g] = a.vcom[2 * G + g] = 0.0;
+    a.xiarr[g] = 0.0;
+    x.source = y.source = 0.0;
+    x.natoms_old = y.natoms_old = x.natoms;
+    x.xi = y.xi = 0.0;
+    a.xiloc[idx] = 0.0;
+    x.natoms = natomsg[g]; y.natoms = x.natoms;
+    if (x.natoms > 0) {
+      x.dens = ((double) totneigh[g]) / ((double) x.natoms) * a.p.atomic_weight / a.neighvol * 1660.53907;
+      if (x.dens == 0) x.dens = (double) x.natoms * a.p.atomic_weight / a.fd_vol * 1660.53907;
+      x.md_temp = a.dsum[3 * G + g];
+      x.md_temp /= (3.0 * (double) x.natoms);
+      if (active_gt(x, mn)) last_local = max(last_local, g - a.p.vlatbuffer);
+    } else { x.dens = 0.0; x.md_temp = 0.0; x.natoms = y.natoms = 0; }
+    y.md_temp = x.md_temp; y.dens = x.dens;
+    if (i == 1) {
+      TCell &ga = l1[r * LD], &gb = l2[r * LD];
+      ga.natoms = g - 1 >= 0 ? natomsg[g - 1] : 0;
+      if (ga.natoms > 0) ga.dens = ((double) totneigh[g - 1]) / ((double) ga.natoms) * a.p.atomic_weight / a.neighvol * 1660.53907;
+      gb.natoms = ga.natoms; gb.dens = ga.dens;
+    } else if (i == L) {
+      TCell &ga = l1[r * LD + L + 1], &gb = l2[r * LD + L + 1];
+      ga.natoms = g + 1 < G ? natomsg[g + 1] : 0;
+      if (ga.natoms > 0) ga.dens = ((double) totneigh[g + 1]) / ((double) ga.natoms) * a.p.atomic_weight / a.neighvol * 1660.53907;
+      gb.natoms = ga.natoms; gb.dens = ga.dens;
+    }
+    if (a.steps < 1) {
+      x.natoms_old = y.natoms_old = x.natoms;
+      if (active_gt(x, mn)) x.temp = y.temp = x.md_temp;
+    }
+  }
+  last_local = block_reduce_int(last_local, 2, s_ired);
+  if (threadIdx.x == 0) {
+    if (a.steps == 0) sc->last_active_cell_global = last_local;
+    s_last_active = sc->last_active_cell_global;
+    s_rv = (int) (((double) s_last_active * P) / ((double) G));
+    sc->cur_vlattice_proc = s_rv;
+  }
+  __syncthreads();
+  const int last_active = s_last_active, rv = s_rv;
+  for (int c = threadIdx.x; c < ncell; c += blockDim.x)
+    if (c > last_active) { const int idx = (c / L) * LD + c % L + 1; l1[idx].natoms = l2[idx].natoms = -1; }
+  __syncthreads();
+
+  // ---------------------------------------------------------------- do_ADV (:1208-1301)
+  if (a.steps >= 1) {
+    for (int r = threadIdx.x; r < P; r += blockDim.x) {                   // do_COMMFLUX
+      if (r > 0) l1[r * LD].U = l1[(r - 1) * LD + L].U;
+      if (r < P - 1) l1[r * LD + L + 1].U = l1[(r + 1) * LD + 1].U;
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < ncell; c += blockDim.x) {
+      const int g = c, idx = (c / L) * LD + c % L + 1;
+      const TCell &x = l1[idx]; TCell &y = l2[idx];
+      const double Nold = (double) x.natoms_old, Nnew = (double) x.natoms;
+      if (Nnew > 0) {
+        const double fr_g = (double) fluxr[g], fl_g = (double) fluxl[g];
+        const double fl_g1 = g + 1 < G ? (double) fluxl[g + 1] : 0.0;
+        const double fr_gm = g - 1 >= 0 ? (double) fluxr[g - 1] : 0.0;
+        y.U = x.U * Nold / Nnew + 1.0 * (+fr_g * l1[idx + 1].U - fl_g1 * x.U + fl_g * l1[idx - 1].U - fr_gm * x.U) / Nnew;
+        if (active_gt(x, mn)) y.temp = eos_te_from_r_ee(a.ee, x.dens, y.U / (26.9815 * C_AMU * C_J2eV)) / 11604.5;
+      } else if (Nnew < 1) { y.U = 0.0; y.temp = 0.0; }
+    }
+    __syncthreads();
+    cur = 1 - cur;
+    { TCell *t = l1; l1 = l2; l2 = t; }
+  }
+
+  // ---------------------------------------------------------------- do_cell_activation (:1311-1425), in cell order
+  if (threadIdx.x == 0) {
+    for (int c = 0; c < ncell; c++) {
+      const int idx = (c / L) * LD + c % L + 1;
+      TCell &x = l1[idx], &y = l2[idx];
+      if (x.natoms_old >= mn && x.natoms < mn && x.dens > RHOMIN) x.xi = 0.0;
+      else if (x.natoms_old < mn && x.natoms >= mn && x.dens > RHOMIN) {
+        if (c > last_active) continue;
+        if (isnan(x.temp) || x.temp <= a.p.Temin) {
+          int nn = 0; double e_nb = 0.0;
+          const TCell &xp = l1[idx + 1], &xm = l1[idx - 1];
+          if (active_ge(xp, mn)) { e_nb += xp.temp * xp.temp; nn++; }
+          if (active_ge(xm, mn)) { e_nb += xm.temp * xm.temp; nn++; }
+          if (nn != 0) {
+            x.temp = sqrt(e_nb / ((double) nn)); y.temp = x.temp;
+            if (x.temp < a.p.Temin) y.temp = x.temp = x.md_temp;
+          } else { x.temp = x.md_temp; y.temp = x.temp; }
+          x.U = y.U = eos_ee_from_r_te(a.ee, x.dens, x.temp * 11604.5) * 26.9815 * C_AMU * C_J2eV;
+        }
+      }
+    }
+  }
+  __syncthreads();
+
+  // ---------------------------------------------------------------- do_FILLMESH, ghosts, CFL_maxdt (:103-108)
+  int la = sc->laser_active;
+  fillmesh(a, l1, l2, v1, v2, last_active, rv, la, err);
+  __syncthreads();
+  fill_ghosts(a, l1);
+  __syncthreads();
+  {
+    double maxdttmp = 1e9;
+    const double dxsq = a.fd_hx * a.fd_hx;
+    for (int c = threadIdx.x; c < ncell; c += blockDim.x) {
+      const int idx = (c / L) * LD + c % L + 1;
+      const TCell &x = l1[idx];
+      if (active_gt(x, mn)) {
+        const TCell &xp = l1[idx + 1];
+        const double khalf = x.fd_k + (active_ge(xp, mn) ? xp.fd_k : x.fd_k);
+        maxdttmp = fmin(maxdttmp, x.Ce * dxsq / khalf);
+      }
+    }
+    maxdttmp = block_reduce(maxdttmp, 1, s_red);
+    if (threadIdx.x == 0) {
+      double m = a.steps > 0 ? maxdttmp : a.timestep / ((double) a.p.fd_n_timesteps);
+      m *= 0.9;
+      s_maxdt = m;
+      const int q = (int) (a.timestep / m);
+      s_substeps = a.p.fd_n_timesteps > q ? a.p.fd_n_timesteps : q;
+    }
+    __syncthreads();
+  }
+  const int diff_substeps = s_substeps;
+  const double tau = a.timestep / ((double) diff_substeps);
+
+  // first active cell: depth origin of the source; natoms/dens do not change during the sub-steps
+  int first = 1 << 30;
+  for (int c = threadIdx.x; c < ncell; c += blockDim.x)
+    if (active_ge(l1[(c / L) * LD + c % L + 1], mn)) first = min(first, c);
+  first = block_reduce_int(first, 1, s_ired);
+  for (int c = threadIdx.x; c < ncell; c += blockDim.x) {
+    const int idx = (c / L) * LD + c % L + 1;
+    a.src_e[idx] = active_ge(l1[idx], mn) ? exp(-a.p.src_mu * ((double) (c - first) * a.fd_hx)) : -1.0;
+  }
+
+  // ---------------------------------------------------------------- sub-step loop (:111-121)
+  double tmm_time = sc->tmm_time, eabs = 0.0;
+  const double xi_fac = 26.9815 * C_AMU / 3.0 * 1e30 / ((double) diff_substeps);
+  const double invxsq = 1.0 / (a.fd_hx * a.fd_hx);
+  const double Imp = 3.769911184307751e+02;
+  double Ci = 8.589449886e+02;
+  Ci *= a.p.vlatdens; Ci *= 11604.5; Ci *= 1e-30; Ci *= C_J2eV;
+  for (int s = 0; s < diff_substeps; s++) {
+    // analytic source (replaces do_tmm): I_t and the laser_active switch of imd_tmm.c:197-208
+    const double dtl = tmm_time - a.p.laser_t_0;
+    const double I_t = a.p.I0 * exp(-(dtl * dtl) / a.sigma_t_sq);
+    la = !(sqrt(2.0 * I_t * Imp) < a.p.tmm_laser_threshold * sqrt(2 * a.p.I0 * Imp));
+    tmm_time += tau * 10.18 * 1.0e-15;
+    for (int c = threadIdx.x; c < ncell + a.p.vlatdim; c += blockDim.x) {
+      if (c < ncell) {
+        const int r = c / L, idx = r * LD + c % L + 1;
+        TCell &x = l1[idx], &y = l2[idx];
+        double src = 0.0;
+        if (la && a.src_e[idx] >= 0.0) { src = I_t * a.p.src_abs * a.p.src_mu * a.src_e[idx]; src *= 1e10; src *= 6.3538562638e-26; }
+        x.source = y.source = src;
+        if (c > last_active) continue;                                   // do_DIFF (:1506-1598)
+        if (la) eabs += src * a.fd_vol * tau;
+        if (x.natoms < mn || x.dens < RHOMIN) continue;
+        const TCell &cm = l1[idx - 1], &cp = l1[idx + 1];
+        const TCell &xmin = (cm.natoms < mn || cm.dens < RHOMIN) ? x : cm;
+        const TCell &xmax = (cp.natoms < mn || cp.dens < RHOMIN) ? x : cp;
+        double xmaxTe = xmax.temp, xminTe = xmin.temp, xmaxk = xmax.fd_k, xmink = xmin.fd_k;
+        if (rv == r) { xmaxTe = v1[0].temp; xmaxk = v1[0].fd_k; }           // :1548-1552
+        const double Ce = x.Ce;
+        y.temp = tau / Ce * ((((x.fd_k + xmaxk) / 2 * (xmaxTe - x.temp) * invxsq)
+                              - ((x.fd_k + xmink) / 2 * (x.temp - xminTe) * invxsq))
+                             - x.fd_g * (x.temp - x.md_temp) + src) + x.temp;
+        y.U = x.U + (y.temp - x.temp) * Ce * a.fd_vol / ((double) x.natoms);
+        const double dxi = (y.temp - x.md_temp) * xi_fac * x.fd_g / x.md_temp / x.dens;
+        x.xi += dxi;
+        y.xi = x.xi;
+        a.xiloc[idx] += dxi;
+        if (isnan(y.temp) || isinf(y.temp)) atomicMax(err, 5);
+      } else if (rv >= 0 && rv < P) {                                      // virtual lattice (:1602-1657)
+        const int i = c - ncell, nv = a.p.vlatdim;
+        const int ilocal = last_active + 1 - rv * L;
+        double xminTe, xmink, xmaxTe, xmaxk;
+        if (i == 0) { xminTe = l1[rv * LD + ilocal].temp; xmink = l1[rv * LD + ilocal].fd_k; }
+        else { xminTe = v1[i - 1].temp; xmink = v1[i - 1].fd_k; }
+        if (i < nv - 1) { xmaxk = v1[i + 1].fd_k; xmaxTe = v1[i + 1].temp; }
+        else { xmaxk = v1[i].fd_k; xmaxTe = v1[i].temp; }
+        const double Ce = v1[i].Ce;
+        v2[i].temp = tau / Ce * (((v1[i].fd_k + xmaxk) / 2 * (xmaxTe - v1[i].temp) * invxsq)
+                                 - ((v1[i].fd_k + xmink) / 2 * (v1[i].temp - xminTe) * invxsq)
+                                 - v1[i].fd_g * (v1[i].temp - v1[i].md_temp)) + v1[i].temp;
+        const double dT = tau / Ci * v1[i].fd_g * (v1[i].temp - v1[i].md_temp);
+        v2[i].md_temp = v1[i].md_temp + dT;
+      }
+    }
+    __syncthreads();
+    cur = 1 - cur; vcur = 1 - vcur;
+    { TCell *t = l1; l1 = l2; l2 = t; t = v1; v1 = v2; v2 = t; }
+    fillmesh(a, l1, l2, v1, v2, last_active, rv, la, err);
+    __syncthreads();
+    fill_ghosts(a, l1);
+    __syncthreads();
+  }
+
+  // ---------------------------------------------------------------- xi gather, U from the EOS (:124-148)
+  double eel = 0.0;
+  for (int c = threadIdx.x; c < ncell; c += blockDim.x) {
+    const int idx = (c / L) * LD + c % L + 1;
+    TCell &x = l1[idx], &y = l2[idx];
+    a.xiarr[c] = a.xiloc[idx];
+    if (active_ge(x, mn)) {
+      x.U = eos_ee_from_r_te(a.ee, x.dens, x.temp * 11604.5) * 26.9815 * C_AMU * C_J2eV;
+      y.U = x.U;
+      eel += x.U * ((double) x.natoms);
+    }
+  }
+  eel = block_reduce(eel, 0, s_red);
+  eabs = block_reduce(eabs, 0, s_red);
+  if (threadIdx.x == 0) {
+    sc->cur = cur; sc->vcur = vcur;
+    sc->diff_substeps = diff_substeps; sc->laser_active = la;
+    sc->max_dt_ttm = s_maxdt; sc->tmm_time = tmm_time;
+    sc->Eabs += eabs; sc->tot_elec_energy = eel;
+  }
+}
+
+// ----------------------------------------------------------------------------- host side
+
+static EosView eos_view(const TtmState &t, int w)
+{
+  EosView v;
+  v.nx = t.eos_nx[w]; v.ny = t.eos_ny[w];
+  v.x = t.eos_buf[w].p; v.y = v.x + v.nx; v.z = v.y + v.ny;
+  v.diag = t.eos_diag[w].p;
+  return v;
+}
+
+extern "C" int imdcu_ttm_set_eos(imdcu_ctx *c, int which, int nx, int ny, const double *x, const double *y,
+                                 const double *z, const unsigned char *diag)
+{
+  if (!c || which < 0 || which > 1 || nx < 2 || ny < 2 || !x || !y || !z)
+    return c ? c->fail(IMDCU_EINVAL, "imdcu_ttm_set_eos: bad argument") : IMDCU_EINVAL;
+  for (int i = 1; i < nx; i++) if (!(x[i] > x[i - 1])) return c->fail(IMDCU_EINVAL, "imdcu_ttm_set_eos: x axis is not increasing (the table must be rectilinear)");
+  for (int j = 1; j < ny; j++) if (!(y[j] > y[j - 1])) return c->fail(IMDCU_EINVAL, "imdcu_ttm_set_eos: y axis is not increasing (the table must be rectilinear)");
+  cudaSetDevice(c->device);
+  TtmState &t = c->ttm;
+  const size_t nd = (size_t) nx + ny + (size_t) nx * ny, ng = (size_t) (nx - 1) * (ny - 1);
+  CU_CHECK(c, t.eos_buf[which].ensure(nd));
+  CU_CHECK(c, t.eos_diag[which].ensure(ng));
+  CU_CHECK(c, cudaMemcpy(t.eos_buf[which].p, x, nx * sizeof(double), cudaMemcpyHostToDevice));
+  CU_CHECK(c, cudaMemcpy(t.eos_buf[which].p + nx, y, ny * sizeof(double), cudaMemcpyHostToDevice));
+  CU_CHECK(c, cudaMemcpy(t.eos_buf[which].p + nx + ny, z, (size_t) nx * ny * sizeof(double), cudaMemcpyHostToDevice));
+  if (diag) {
+    for (size_t k = 0; k < ng; k++) if (diag[k] > 1) return c->fail(IMDCU_EINVAL, "imdcu_ttm_set_eos: diag entries must be 0 or 1");
+    CU_CHECK(c, cudaMemcpy(t.eos_diag[which].p, diag, ng, cudaMemcpyHostToDevice));
+  } else CU_CHECK(c, cudaMemset(t.eos_diag[which].p, 0, ng));
+  t.eos_nx[which] = nx; t.eos_ny[which] = ny; t.eos_set[which] = true;
+  return IMDCU_OK;
+}
+
+// init_ttm (imd_ttm.c:955-1201) + tmm_init as far as the analytic source needs it
+extern "C" int imdcu_ttm_init(imdcu_ctx *c, const imdcu_ttm_params *p)
+{
+  if (!c || !p) return c ? c->fail(IMDCU_EINVAL, "imdcu_ttm_init: bad argument") : IMDCU_EINVAL;
+  if (!c->box_set || !c->params_set || !c->tab[IMDCU_TAB_PAIR].set)
+    return c->fail(IMDCU_EINVAL, "imdcu_ttm_init: set box, params and tables first");
+  TtmState &t = c->ttm;
+  if (!t.eos_set[0] || !t.eos_set[1]) return c->fail(IMDCU_EINVAL, "imdcu_ttm_init: EOS tables not set");
+  if (p->ttmdimx < 1 || p->nranks_ref < 1 || p->ttmdimx % p->nranks_ref != 0)
+    return c->fail(IMDCU_EINVAL, "global_fd_dim.x mod num_cpus != 0.");            // imd_ttm.c:964-967
+  if (p->fd_n_timesteps < 1 || p->vlatdim < 0 || p->vlatdim > 4096)
+    return c->fail(IMDCU_EINVAL, "imdcu_ttm_init: bad fd_n_timesteps / vlatdim");
+  const Geom &g = c->geom;
+  if (g.box[1] != 0 || g.box[2] != 0 || g.box[3] != 0 || g.box[5] != 0 || g.box[6] != 0 || g.box[7] != 0)
+    return c->fail(IMDCU_EINVAL, "imdcu_ttm_init: the 1-D TTM needs an orthorhombic box");
+  cudaSetDevice(c->device);
+  t.p = *p;
+  t.G = p->ttmdimx; t.P = p->nranks_ref; t.L = t.G / t.P; t.LD = t.L + 2;
+  t.fd_hx = g.box[0] / t.G;
+  t.fd_vol = t.fd_hx * g.box[4] * g.box[8];
+  t.neighvol = pow(sqrt(c->tab[IMDCU_TAB_PAIR].h_end[0]), 3.0) * 4.0 / 3.0 * M_PI;
+  t.sigma_t_sq = p->laser_sigma_t * p->laser_sigma_t;
+  t.omega_laser = 2.0 * M_PI * 3.0e8 / p->lambda;
+  const int nl = t.P * t.LD, nv = p->vlatdim > 0 ? p->vlatdim : 1;
+  CU_CHECK(c, t.lat.ensure(2 * (size_t) nl));
+  CU_CHECK(c, t.vlat.ensure(2 * (size_t) nv));
+  CU_CHECK(c, t.isum.ensure(4 * (size_t) t.G)); CU_CHECK(c, t.dsum.ensure(4 * (size_t) t.G));
+  CU_CHECK(c, t.xiarr.ensure(t.G)); CU_CHECK(c, t.xiloc.ensure(nl)); CU_CHECK(c, t.vcom.ensure(3 * (size_t) t.G));
+  CU_CHECK(c, t.src_e.ensure(nl));
+  CU_CHECK(c, cudaMemset(t.lat.p, 0, 2 * (size_t) nl * sizeof(TCell)));
+  CU_CHECK(c, cudaMemset(t.xiarr.p, 0, t.G * sizeof(double)));
+  CU_CHECK(c, cudaMemset(t.xiloc.p, 0, nl * sizeof(double)));
+  CU_CHECK(c, cudaMemset(t.vcom.p, 0, 3 * (size_t) t.G * sizeof(double)));
+  std::vector<TCell> hv(2 * (size_t) nv);
+  memset(hv.data(), 0, hv.size() * sizeof(TCell));
+  for (int k = 0; k < 2 * nv; k++) { hv[k].dens = p->vlatdens; hv[k].temp = 0.0264; hv[k].md_temp = 0.0264; }   // :1036-1041
+  CU_CHECK(c, cudaMemcpy(t.vlat.p, hv.data(), hv.size() * sizeof(TCell), cudaMemcpyHostToDevice));
+  if (!t.d_scal) {
+    CU_CHECK(c, cudaMalloc(&t.d_scal, sizeof(TtmScal)));
+    CU_CHECK(c, cudaMallocHost(&t.h_scal, sizeof(TtmScal)));
+  }
+  TtmScal s0;
+  memset(&s0, 0, sizeof s0);
+  s0.diff_substeps = 100;                                                         // globals.h:1187
+  s0.max_dt_ttm = c->timestep / ((double) p->fd_n_timesteps);
+  CU_CHECK(c, cudaMemcpy(t.d_scal, &s0, sizeof s0, cudaMemcpyHostToDevice));
+  if (c->n > 0) {
+    CU_CHECK(c, t.fdi.ensure(c->key.cap)); CU_CHECK(c, t.fdi_alt.ensure(c->key.cap));
+    CU_CHECK(c, cudaMemset(t.fdi.p, 0, c->key.cap * sizeof(int)));
+  }
+  t.inited = true;
+  return IMDCU_OK;
+}
+
+void imdcu_ttm_release(imdcu_ctx *c)
+{
+  TtmState &t = c->ttm;
+  for (int w = 0; w < 2; w++) { t.eos_buf[w].release(); t.eos_diag[w].release(); }
+  t.lat.release(); t.vlat.release(); t.isum.release(); t.dsum.release(); t.xiarr.release(); t.xiloc.release();
+  t.vcom.release(); t.src_e.release(); t.fdi.release(); t.fdi_alt.release();
+  if (t.d_scal) cudaFree(t.d_scal);
+  if (t.h_scal) cudaFreeHost(t.h_scal);
+  t.d_scal = t.h_scal = nullptr;
+}
+
+static int ttm_read_scalars(imdcu_ctx *c, double out16[16])
+{
+  TtmState &t = c->ttm;
+  CU_CHECK(c, cudaMemcpyAsync(t.h_scal, t.d_scal, sizeof(TtmScal), cudaMemcpyDeviceToHost, c->stream));
+  CU_CHECK(c, cudaStreamSynchronize(c->stream));
+  const TtmScal *s = (const TtmScal *) t.h_scal;
+  for (int k = 0; k < 16; k++) out16[k] = 0.0;
+  out16[0] = s->diff_substeps; out16[1] = s->max_dt_ttm; out16[2] = s->last_active_cell_global;
+  out16[3] = s->cur_vlattice_proc; out16[4] = s->Eabs; out16[5] = s->tot_elec_energy;
+  out16[6] = t.fd_hx; out16[7] = t.fd_vol; out16[8] = t.neighvol; out16[9] = s->laser_active;
+  out16[10] = s->tmm_time; out16[11] = s->err;
+  if (s->err) {
+    static const char *msg[] = {"", "ERROR during CfromT in FILLMESH", "fd_k is NaN", "fd_g is NaN",
+                                "EOS Plausibility check failed, TfromU != Tinit", "Te got NaN or Inf in diffloop"};
+    return c->fail(IMDCU_EINVAL, std::string("calc_ttm: ") + msg[s->err < 6 ? s->err : 0]);
+  }
+  return IMDCU_OK;
+}
+
+// calc_ttm (imd_ttm.c:75-156)
+int imdcu_ttm_step(imdcu_ctx *c, int steps, double out16[16])
+{
+  TtmState &t = c->ttm;
+  if (!t.inited) return c->fail(IMDCU_EINVAL, "imdcu_ttm_init has not been called");
+  PhaseTimer pt(c, 7);
+  cudaStream_t st = c->stream;
+  const int n = (int) c->n, G = t.G;
+  if (t.fdi.cap < (size_t) n) {
+    CU_CHECK(c, t.fdi.ensure(c->key.cap)); CU_CHECK(c, t.fdi_alt.ensure(c->key.cap));
+    CU_CHECK(c, cudaMemsetAsync(t.fdi.p, 0, c->key.cap * sizeof(int), st));
+  }
+  CU_CHECK(c, cudaMemsetAsync(t.isum.p, 0, 4 * (size_t) G * sizeof(int), st));
+  CU_CHECK(c, cudaMemsetAsync(t.dsum.p, 0, 4 * (size_t) G * sizeof(double), st));
+  if (n > 0) {
+    const int nb = div_up(n, 256);
+    k_ttm_atoms1<<<nb, 256, 0, st>>>(n, G, t.fd_hx, steps, c->pos4.p, c->mom4.p, c->type.p, c->numneighs.p,
+                                     t.fdi.p, t.isum.p, t.dsum.p);
+    k_ttm_atoms2<<<nb, 256, 0, st>>>(n, G, t.fd_hx, t.p.atomic_weight, c->mom4.p, c->type.p, t.fdi.p, t.isum.p,
+                                     t.dsum.p);
+    c->count_launch(2);
+  }
+  TtmArgs a;
+  a.G = G; a.P = t.P; a.L = t.L; a.LD = t.LD; a.steps = steps; a.ncell_tot = t.P * t.L + t.p.vlatdim;
+  a.p = t.p;
+  a.timestep = c->timestep; a.fd_hx = t.fd_hx; a.fd_vol = t.fd_vol; a.neighvol = t.neighvol;
+  a.omega_laser = t.omega_laser; a.sigma_t_sq = t.sigma_t_sq;
+  a.cve = eos_view(t, 0); a.ee = eos_view(t, 1);
+  a.lat = t.lat.p; a.vlat = t.vlat.p; a.isum = t.isum.p; a.dsum = t.dsum.p;
+  a.xiarr = t.xiarr.p; a.xiloc = t.xiloc.p; a.vcom = t.vcom.p; a.src_e = t.src_e.p;
+  a.scal = (TtmScal *) t.d_scal;
+  int nt = ((a.ncell_tot + 31) / 32) * 32;
+  if (nt > TTM_NT) nt = TTM_NT;
+  if (nt < 32) nt = 32;
+  k_ttm_grid<<<1, nt, 0, st>>>(a);
+  c->count_launch();
+  CU_CHECK(c, cudaGetLastError());
+  if (out16) return ttm_read_scalars(c, out16);
+  return IMDCU_OK;
+}
+
+extern "C" int imdcu_download_ttm(imdcu_ctx *c, double *cells, double *xiarr, double *vcom, double *vlat)
+{
+  if (!c || !c->ttm.inited) return c ? c->fail(IMDCU_EINVAL, "TTM not initialised") : IMDCU_EINVAL;
+  cudaSetDevice(c->device);
+  TtmState &t = c->ttm;
+  CU_CHECK(c, cudaStreamSynchronize(c->stream));
+  TtmScal s;
+  CU_CHECK(c, cudaMemcpy(&s, t.d_scal, sizeof s, cudaMemcpyDeviceToHost));
+  const int nl = t.P * t.LD, nv = t.p.vlatdim;
+  if (cells) {
+    std::vector<TCell> h((size_t) nl);
+    CU_CHECK(c, cudaMemcpy(h.data(), t.lat.p + (size_t) s.cur * nl, nl * sizeof(TCell), cudaMemcpyDeviceToHost));
+    for (int r = 0; r < t.P; r++)
+      for (int i = 1; i <= t.L; i++) {
+        const TCell &x = h[(size_t) r * t.LD + i];
+        double *o = cells + (size_t) ((i - 1) + r * t.L) * 13;
+        o[0] = x.natoms; o[1] = x.natoms_old; o[2] = x.temp; o[3] = x.md_temp; o[4] = x.xi; o[5] = x.dens;
+        o[6] = x.fd_k; o[7] = x.fd_g; o[8] = x.Z; o[9] = x.ne; o[10] = x.Ce; o[11] = x.U; o[12] = x.source;
+      }
+  }
+  if (xiarr) CU_CHECK(c, cudaMemcpy(xiarr, t.xiarr.p, t.G * sizeof(double), cudaMemcpyDeviceToHost));
+  if (vcom) CU_CHECK(c, cudaMemcpy(vcom, t.vcom.p, 3 * (size_t) t.G * sizeof(double), cudaMemcpyDeviceToHost));
+  if (vlat && nv > 0) {
+    std::vector<TCell> h((size_t) nv);
+    CU_CHECK(c, cudaMemcpy(h.data(), t.vlat.p + (size_t) s.vcur * nv, nv * sizeof(TCell), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < nv; i++) {
+      double *o = vlat + 6 * (size_t) i;
+      o[0] = h[i].temp; o[1] = h[i].md_temp; o[2] = h[i].fd_k; o[3] = h[i].fd_g; o[4] = h[i].Ce; o[5] = h[i].Z;
+    }
+  }
+  return IMDCU_OK;
+}

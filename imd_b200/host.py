@@ -14,6 +14,7 @@ import numpy as np
 from . import capi
 
 TAB_PAIR, TAB_RHO, TAB_EMBED = 0, 1, 2
+capi_EOS_CVE, capi_EOS_EE = 0, 1
 
 
 class Imd:
@@ -72,6 +73,33 @@ class Imd:
         if nsteps:
             self.tot_pot_energy, self.tot_kin_energy = float(e[-1, 0]), float(e[-1, 1])
         return e
+
+    # init_ttm + tmm_init (imd.c:237,245): EOS tables + TTM parameters
+    def init_ttm(self, tp, eos, nranks_ref=1):
+        self.ctx.ttm_set_eos(capi_EOS_CVE, eos["cve"])
+        self.ctx.ttm_set_eos(capi_EOS_EE, eos["ee"])
+        self.ctx.ttm_init(tp, nranks_ref)
+
+    # calc_ttm (imd_main_3d.c:534)
+    def calc_ttm(self, steps=None):
+        return self.ctx.calc_ttm(self.steps if steps is None else steps)
+
+    def move_atoms_ttm(self):
+        out, valid = self.ctx.move_atoms_ttm()
+        self.tot_kin_energy = float(out[0])
+        self.have_valid_nbl = int(valid)
+        return out
+
+    def main_loop_ttm(self, nsteps):
+        """calc_forces -> calc_ttm -> move_atoms_ttm -> check_nblist for nsteps."""
+        e = self.ctx.run_ttm(self.steps, nsteps, True)
+        self.steps += nsteps
+        if nsteps:
+            self.tot_pot_energy, self.tot_kin_energy = float(e[-1, 0]), float(e[-1, 1])
+        return e
+
+    def ttm_lattice(self):
+        return self.ctx.download_ttm()
 
     def atoms(self, fields=("id", "pos", "mom", "force", "epot", "rho", "dF", "numneighs", "cell"),
               sort_by_id=True):

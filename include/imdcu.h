@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define IMDCU_ABI_VERSION 1
+#define IMDCU_ABI_VERSION 2
 
 #define IMDCU_OK            0
 #define IMDCU_EINVAL       -1   /* bad argument / call order                       */
@@ -101,6 +101,48 @@ int  imdcu_move_atoms_nve(imdcu_ctx *ctx, double out8[8], int *have_valid_nbl);
  * (imd_main_3d.c:406,564,812) for nsteps steps without returning to the host code;
  * energies[2*s] = tot_pot_energy, energies[2*s+1] = tot_kin_energy (may be NULL). */
 int  imdcu_run_nve(imdcu_ctx *ctx, int first_step, int nsteps, double *energies);
+
+/* ------------------------------------------------------------------ two-temperature model (1-D) */
+/* Run-time parameters of the 1-D TTM: the keywords of imd_param.c:1979-2092 and the globals
+ * init_ttm / tmm_init derive from them (imd_ttm.c:955-1201, imd_tmm.c:98-190).
+ * nranks_ref: the reference's result depends on its MPI decomposition (per-rank ghost cells,
+ * the virtual-lattice owner rank, imd_ttm.c:1548-1552); the device reproduces a run with
+ * num_cpus = nranks_ref (>= 1, must divide ttmdimx).  The laser source is the analytic
+ * Beer-Lambert term documented in DESIGN.md (the reference's transfer-matrix solver do_tmm
+ * needs data files that are not in its tree): src_mu [1/Angstrom], src_abs = absorbed fraction. */
+typedef struct {
+  int    ttmdimx, nranks_ref;
+  int    fd_n_timesteps, fd_min_atoms, vlatdim, vlatbuffer;
+  double vlatdens, atomic_weight, atomic_charge, Temin;
+  double I0, lambda, laser_t_0, laser_sigma_t, tmm_laser_threshold, src_mu, src_abs;
+} imdcu_ttm_params;
+
+#define IMDCU_EOS_CVE 0   /* EOS_cve_from_r_te.txt    : (rho [kg/m^3], Te [K])       -> J/(K kg) */
+#define IMDCU_EOS_EE  1   /* EOS_ee_from_r_tesqrt.txt : (rho [kg/m^3], sqrt(Te [K])) -> J/kg     */
+/* One EOS interpolation table (nn_read_table, imd_interpol.c:1170-1271).  The point set must be
+ * rectilinear: x[nx], y[ny], z[nx*ny] with x the outer index.  diag[(nx-1)*(ny-1)] tells which
+ * diagonal the reference's Delaunay triangulation (libnn delaunay_build) put into each grid
+ * rectangle: 0 = (i,j)-(i+1,j+1), 1 = (i+1,j)-(i,j+1); NULL = all 0.  Replaces
+ * lpi_interpolate_point at imd_ttm.c:2517,2568. */
+int  imdcu_ttm_set_eos(imdcu_ctx *ctx, int which, int nx, int ny, const double *x, const double *y,
+                       const double *z, const unsigned char *diag);
+/* init_ttm + tmm_init (imd.c:237,245).  Needs box, tables, params and both EOS tables. */
+int  imdcu_ttm_init(imdcu_ctx *ctx, const imdcu_ttm_params *p);
+/* calc_ttm (imd_ttm.c:75-156) for MD step `steps`, after imdcu_calc_forces of the same step
+ * (it consumes numneighs).  out16 (may be NULL: no host synchronisation) = {diff_substeps,
+ * max_dt_ttm, last_active_cell_global, cur_vlattice_proc, Eabs, tot_elec_energy, fd_h.x, fd_vol,
+ * neighvol, laser_active, tmm_time, error flag, 0...}. */
+int  imdcu_calc_ttm(imdcu_ctx *ctx, int steps, double out16[16]);
+/* move_atoms_ttm (imd_integrate.c:581-811, TTM1D [+PDECAY]) fused with check_nblist */
+int  imdcu_move_atoms_ttm(imdcu_ctx *ctx, double out8[8], int *have_valid_nbl);
+/* main-loop segment calc_forces -> calc_ttm -> move_atoms_ttm -> check_nblist
+ * (imd_main_3d.c:406,534,564,812); energies[2*s], [2*s+1] = tot_pot_energy, tot_kin_energy */
+int  imdcu_run_ttm(imdcu_ctx *ctx, int first_step, int nsteps, double *energies);
+/* FD lattice l1 after the last calc_ttm, assembled over the emulated ranks: cells[G*13] =
+ * {natoms, natoms_old, temp, md_temp, xi, dens, fd_k, fd_g, Z, ne, Ce, U, source} per cell;
+ * xiarr[G]; vcom[3*G]; vlat[vlatdim*6] = {temp, md_temp, fd_k, fd_g, Ce, Z}.  Any may be NULL.
+ * This is what ttm_writeout (imd_ttm.c:1683) needs on the host. */
+int  imdcu_download_ttm(imdcu_ctx *ctx, double *cells, double *xiarr, double *vcom, double *vlat);
 
 /* ------------------------------------------------------------------ inspection (parity) */
 /* geometry chosen by imdcu_set_box: global_cell_dim and cellsz */

@@ -1,0 +1,150 @@
+"""GPU parity of the 1-D TTM path (calc_ttm, move_atoms_ttm) through the C ABI, against
+(a) dumps of the unmodified reference (tests/golden/ttm_*.npz) and (b) the CPU oracle on
+seeded inputs.  Tolerances: tests/ttm_util.py."""
+import numpy as np
+import pytest
+
+from imd_b200 import host, synth
+from tests.ttm_util import (REL_STEP0, TE_ABS_K, TTM_CASES, TTM_FIELDS, TtmGolden, compare_cells)
+
+pytestmark = pytest.mark.gpu
+
+
+def make_imd(g, atoms=None, nranks=None):
+    a = g.atoms(0) if atoms is None else atoms
+    imd = host.Imd(0)
+    imd.setup_potentials(g.tables)
+    imd.make_box(g.box, (0, 1, 1), g.margin)
+    imd.set_params(1, g.timestep)
+    if g.pdecay:
+        imd.ctx.set_pdecay(*g.pdecay)
+    imd.set_atoms(a["pos"], a["mom"], a["mass"], a["type"], a["id"])
+    imd.init_ttm(g.tp, g.eos, g.nranks if nranks is None else nranks)
+    return imd
+
+
+@pytest.mark.parametrize("name", TTM_CASES)
+def test_calc_ttm_step0_matches_reference(name):
+    """Step 0 has no root finding on the path: every field to 1e-10 (we see ~1e-15)."""
+    g = TtmGolden(name)
+    imd = make_imd(g)
+    imd.calc_forces(0)
+    got = imd.atoms(fields=("id", "numneighs", "force"))
+    a = g.atoms(0)
+    assert np.array_equal(got["numneighs"], a["numneighs"])
+    sc = imd.calc_ttm(0)
+    ref = g.ttm(0)
+    hdr = ref["hdr"][0]
+    assert int(sc["diff_substeps"]) == int(hdr[4])
+    assert int(sc["last_active_cell_global"]) == int(hdr[6])
+    assert int(sc["cur_vlattice_proc"]) == int(hdr[7])
+    np.testing.assert_allclose(sc["max_dt_ttm"], hdr[5], rtol=1e-14)
+    np.testing.assert_allclose(sc["Eabs"], float(ref["Eabs"]), rtol=1e-11)
+    np.testing.assert_allclose(sc["tot_elec_energy"], float(ref["tot_elec_energy"]), rtol=1e-11)
+    lat = imd.ttm_lattice()
+    compare_cells(lat["fields"], ref["fields"], 0, int(hdr[6]), name)
+    pscale = np.sqrt(g.spec.mass * 0.0258) / g.spec.mass
+    np.testing.assert_allclose(lat["vcom"], ref["vcom"], rtol=0, atol=1e-11 * pscale)
+    np.testing.assert_allclose(lat["xiarr"], ref["xiarr"], rtol=REL_STEP0, atol=1e-18)
+    np.testing.assert_allclose(lat["vlat"][:, :5], ref["vlat"][:, :5], rtol=REL_STEP0)
+    imd.close()
+
+
+@pytest.mark.parametrize("name", TTM_CASES)
+def test_full_loop_matches_reference(name):
+    """calc_forces -> calc_ttm -> move_atoms_ttm on the device for the whole reference run,
+    compared at every dumped step: atoms, numneighs (bit exact) and the FD lattice."""
+    g = TtmGolden(name)
+    imd = make_imd(g)
+    box = np.diag(g.box)
+    s = 0
+    for target in g.steps:
+        # run up to (not including) `target`, then do its force + ttm part step by step
+        if target > s:
+            imd.main_loop_ttm(target - s)
+            s = target
+        imd.calc_forces(s)
+        sc = imd.calc_ttm(s)
+        got = imd.atoms(fields=("id", "pos", "mom", "force", "numneighs"))
+        a, ref = g.atoms(s), g.ttm(s)
+        d = got["pos"] - a["pos"]
+        d[:, 1:] -= np.round(d[:, 1:] / box[1:]) * box[1:]
+        assert np.abs(d).max() < 1e-9
+        assert np.array_equal(got["numneighs"], a["numneighs"])
+        fs = np.abs(a["force"]).max()
+        assert np.abs(got["force"] - a["force"]).max() < 1e-9 * fs
+        hdr = ref["hdr"][0]
+        assert int(sc["diff_substeps"]) == int(hdr[4])
+        np.testing.assert_allclose(sc["Eabs"], float(ref["Eabs"]), rtol=1e-9)
+        compare_cells(imd.ttm_lattice()["fields"], ref["fields"], s, int(hdr[6]), name)
+        imd.move_atoms_ttm()
+        s += 1
+        imd.steps = s
+    imd.close()
+
+
+def test_against_oracle_seeded_film():
+    """A film the reference never saw (different size, seed, slab count, emulated rank count):
+    device vs CPU oracle, step by step for a few steps."""
+    from oracle.binding import EamOracle, TtmOracle
+    spec = synth.AL
+    tables = synth.make_eam_tables(spec)
+    g0 = TtmGolden(TTM_CASES[0])                       # only for the EOS diagonal flags
+    eos = g0.eos
+    pos, box = synth.film_lattice((40, 5, 5), spec.a, 18.0, 22.0)
+    rng = np.random.default_rng(5)
+    pos = pos + rng.normal(0, 0.03, pos.shape)
+    n = pos.shape[0]
+    mom = synth.maxwell_momenta(n, spec.mass, 0.04, seed=11)
+    mass = np.full(n, spec.mass); types = np.zeros(n, np.int32); ids = np.arange(n, dtype=np.int32)
+    tp = synth.TtmParams(ttmdimx=12, fd_n_timesteps=25, fd_min_atoms=15, vlatdim=6, vlatbuffer=1, I0=3.0e16)
+    P = 3
+    imd = host.Imd(0)
+    imd.setup_potentials(tables)
+    imd.make_box(box, (0, 1, 1), 0.4)
+    imd.set_params(1, 0.1)
+    imd.set_atoms(pos, mom, mass, types, ids)
+    imd.init_ttm(tp, eos, P)
+    eam = EamOracle(box, (0, 1, 1), tables, 0.4)
+    ttm = TtmOracle(tp, eos, box, float(tables["pair"].end[0]), 0.1, P)
+    opos, omom = pos.copy(), mom.copy()
+    fdi = np.zeros(n, np.int32)
+    for s in range(4):
+        eam.fix_cells(opos); eam.make_nblist()
+        f = eam.calc_forces(opos, types)
+        ttm.step(s, opos, omom, mass, types, f["numneighs"], fdi)
+        imd.calc_forces(s)
+        sc = imd.calc_ttm(s)
+        osc = ttm.scalars()
+        assert int(sc["diff_substeps"]) == int(osc["diff_substeps"])
+        assert int(sc["last_active_cell_global"]) == int(osc["last_active_cell_global"])
+        lat, oc = imd.ttm_lattice(), ttm.cells()
+        compare_cells(lat["fields"], oc, s, int(osc["last_active_cell_global"]), "seeded")
+        np.testing.assert_allclose(sc["Eabs"], osc["Eabs"], rtol=1e-9)
+        ttm.move_atoms(opos, omom, f["force"], mass, types)
+        imd.move_atoms_ttm()
+        got = imd.atoms(fields=("id", "pos", "mom"))
+        d = got["pos"] - opos
+        bx = np.diag(box)
+        d[:, 1:] -= np.round(d[:, 1:] / bx[1:]) * bx[1:]
+        assert np.abs(d).max() < 1e-10
+        np.testing.assert_allclose(got["mom"], omom, rtol=0, atol=1e-10 * np.sqrt(spec.mass * 0.04))
+    assert TE_ABS_K > 0 and len(TTM_FIELDS) == 13
+    imd.close(); eam.close(); ttm.close()
+
+
+def test_ttm_error_paths():
+    g = TtmGolden(TTM_CASES[0])
+    imd = host.Imd(0)
+    imd.setup_potentials(g.tables)
+    imd.make_box(g.box, (0, 1, 1), g.margin)
+    imd.set_params(1, g.timestep)
+    from imd_b200 import capi
+    with pytest.raises(capi.ImdcuError):                 # EOS tables not set
+        imd.ctx.ttm_init(g.tp, 2)
+    imd.ctx.ttm_set_eos(0, g.eos["cve"]); imd.ctx.ttm_set_eos(1, g.eos["ee"])
+    with pytest.raises(capi.ImdcuError):                 # global_fd_dim.x mod num_cpus != 0
+        imd.ctx.ttm_init(g.tp, 5)
+    with pytest.raises(capi.ImdcuError):                 # calc_ttm before init
+        imd.ctx.calc_ttm(0)
+    imd.close()
