@@ -73,6 +73,9 @@ def load():
         "imdcu_calc_forces": (C.c_int, [vp, C.c_int, c_dp]),
         "imdcu_move_atoms_nve": (C.c_int, [vp, c_dp, c_ip]),
         "imdcu_run_nve": (C.c_int, [vp, C.c_int, C.c_int, c_dp]),
+        "imdcu_comm_unique_id": (C.c_int, [C.c_char_p]),
+        "imdcu_comm_init": (C.c_int, [vp, C.c_char_p, C.c_int, C.c_int]),
+        "imdcu_comm_rank": (C.c_int, [vp, c_ip, c_ip, c_ip, c_ip]),
         "imdcu_ttm_set_eos": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, c_dp, c_dp, c_dp, C.POINTER(C.c_ubyte)]),
         "imdcu_ttm_init": (C.c_int, [vp, C.POINTER(TtmParamsC)]),
         "imdcu_calc_ttm": (C.c_int, [vp, C.c_int, c_dp]),
@@ -132,6 +135,23 @@ class Context:
     def _ck(self, rc):
         if rc != 0:
             raise ImdcuError(rc, (self.L.imdcu_last_error(self.h) or b"").decode())
+
+    # ---- multi-GPU
+    @staticmethod
+    def comm_unique_id() -> bytes:
+        buf = C.create_string_buffer(128)
+        rc = load().imdcu_comm_unique_id(buf)
+        if rc != 0:
+            raise ImdcuError(rc, "ncclGetUniqueId failed")
+        return buf.raw
+
+    def comm_init(self, uid: bytes, rank: int, nranks: int):
+        self._ck(self.L.imdcu_comm_init(self.h, uid, int(rank), int(nranks)))
+
+    def comm_rank(self):
+        v = [C.c_int32(0) for _ in range(4)]
+        self._ck(self.L.imdcu_comm_rank(self.h, *[C.byref(x) for x in v]))
+        return dict(rank=v[0].value, nranks=v[1].value, xoff=v[2].value, ldimx=v[3].value)
 
     # ---- set-up
     def set_table(self, which: int, pt):

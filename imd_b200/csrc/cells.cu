@@ -12,7 +12,8 @@
 
 // PBC wrap (x, then y, then z, each on the updated position) + cell key.
 __global__ void __launch_bounds__(256)
-k_wrap_key(Geom g, int n, double4 *__restrict__ pos4, int *__restrict__ key, int *__restrict__ perm)
+k_wrap_key(Geom g, int n, int nranks, int ncell_ext, double4 *__restrict__ pos4, int *__restrict__ key,
+           int *__restrict__ perm)
 {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
@@ -41,12 +42,17 @@ k_wrap_key(Geom g, int n, double4 *__restrict__ pos4, int *__restrict__ key, int
   }
   p.x = x; p.y = y; p.z = z;
   pos4[i] = p;
-  // local extended index; atoms outside this rank's x-slab are clamped into the edge layer
-  // (they are migrated by the multi-GPU layer before this kernel runs)
+  // local extended index.  Decomposed runs: an atom whose cell layer belongs to the west/east
+  // neighbour gets the sentinel key ncell_ext / ncell_ext+1 (sorted to the end, sent away by
+  // multi.cu); across a periodic x boundary the layer distance is taken modulo gdim.x.
   int li = cc[0] - g.xoff;
-  if (li < 0) li = 0; else if (li >= g.ldim[0]) li = g.ldim[0] - 1;
-  key[i] = ((li + 1) * g.edim[1] + (cc[1] + 1)) * g.edim[2] + (cc[2] + 1);
   perm[i] = i;
+  if (nranks > 1) {
+    if (g.pbc[0]) { if (li > g.gdim[0] / 2) li -= g.gdim[0]; else if (li < -(g.gdim[0] / 2)) li += g.gdim[0]; }
+    if (li < 0) { key[i] = ncell_ext; return; }
+    if (li >= g.ldim[0]) { key[i] = ncell_ext + 1; return; }
+  } else { if (li < 0) li = 0; else if (li >= g.ldim[0]) li = g.ldim[0] - 1; }
+  key[i] = ((li + 1) * g.edim[1] + (cc[1] + 1)) * g.edim[2] + (cc[2] + 1);
 }
 
 __global__ void __launch_bounds__(256)
@@ -97,6 +103,7 @@ k_ghost_counts(int q0, int q1, const GhostCell *__restrict__ plan, int *__restri
 {
   int q = q0 + blockIdx.x * blockDim.x + threadIdx.x;
   if (q >= q1) return;
+  if (plan[q].src < 0) { gcount[q] = cell_count[plan[q].cell]; return; }   // remote plane: set by multi.cu
   int c = cell_count[plan[q].src];
   cell_count[plan[q].cell] = c;
   gcount[q] = c;
@@ -116,12 +123,14 @@ k_ghost_begin(int nplan, int n, const GhostCell *__restrict__ plan, const int *_
 __global__ void __launch_bounds__(256)
 k_ghost_fill(int q0, int q1, int n, const GhostCell *__restrict__ plan, const int *__restrict__ goff,
              const int *__restrict__ cell_begin, int *__restrict__ gsrc, int *__restrict__ gcode,
-             int *__restrict__ groot, int *__restrict__ gtcode, int *__restrict__ type)
+             int *__restrict__ groot, int *__restrict__ gtcode, int *__restrict__ type,
+             const int *__restrict__ id, int *__restrict__ ggid)
 {
   int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   int q = q0 + warp;
   if (q >= q1) return;
   GhostCell gc = plan[q];
+  if (gc.src < 0) return;                           // remote plane: filled by multi.cu
   int cnt = goff[q + 1] - goff[q];
   int sb = cell_begin[gc.src], tb = goff[q];
   for (int o = lane; o < cnt; o += 32) {
@@ -129,11 +138,12 @@ k_ghost_fill(int q0, int q1, int n, const GhostCell *__restrict__ plan, const in
     gsrc[t] = s;
     gcode[t] = gc.code;
     int sx = gc.code % 3 - 1, sy = (gc.code / 3) % 3 - 1, sz = gc.code / 9 - 1;
-    if (s < n) { groot[t] = s; gtcode[t] = gc.code; }
+    if (s < n) { groot[t] = s; gtcode[t] = gc.code; ggid[t] = id[s]; }
     else {
       int pc = gtcode[s - n];
       groot[t] = groot[s - n];
       gtcode[t] = (pc % 3 - 1 + sx + 1) + 3 * ((pc / 3) % 3 - 1 + sy + 1) + 9 * (pc / 9 - 1 + sz + 1);
+      ggid[t] = ggid[s - n];
     }
     type[n + t] = type[s];
   }
@@ -172,7 +182,12 @@ int imdcu_refresh_ghosts(imdcu_ctx *c, bool at_build)
 {
   PhaseTimer pt(c, 2);
   const int n = (int) c->n;
+  const bool multi = c->comm.nranks > 1;
   for (int s = 0; s < 3; s++) {
+    if (s == 2 && multi) {                         // x stage: the planes come from the neighbour ranks
+      if (!at_build) RET_IF(imdcu_multi_ghost_refresh(c));
+      continue;                                    // (at a rebuild imdcu_multi_ghost_build filled them)
+    }
     int t0 = (int) c->gstage_atoms[s], t1 = (int) c->gstage_atoms[s + 1];
     if (t1 <= t0) continue;
     if (at_build)
@@ -184,49 +199,64 @@ int imdcu_refresh_ghosts(imdcu_ctx *c, bool at_build)
     c->count_launch();
   }
   CU_CHECK(c, cudaGetLastError());
+  if (at_build && multi) RET_IF(imdcu_multi_ghost_build(c));
   return IMDCU_OK;
 }
 
 int imdcu_rebuild_cells(imdcu_ctx *c)
 {
   PhaseTimer pt(c, 0);
-  const int n = (int) c->n;
+  int n = (int) c->n;
   cudaStream_t st = c->stream;
-  if (n == 0) { c->ng = 0; return IMDCU_OK; }
-  const int nb = div_up(n, 256);
+  const bool multi = c->comm.nranks > 1;
+  if (n == 0 && !multi) { c->ng = 0; return IMDCU_OK; }
 
-  k_wrap_key<<<nb, 256, 0, st>>>(c->geom, n, c->pos4.p, c->key.p, c->perm.p);
-  c->count_launch();
+  if (n > 0) {
+    k_wrap_key<<<div_up(n, 256), 256, 0, st>>>(c->geom, n, c->comm.nranks, c->ncell_ext, c->pos4.p, c->key.p, c->perm.p);
+    c->count_launch();
+  }
+  int n_sort = n;                                   // elements to sort (stayers + movers + arrivals)
+  if (multi) RET_IF(imdcu_multi_migrate(c, &n_sort));
+  const int n_new = (int) c->n;                     // owned atoms after migration (set by multi_migrate)
 
-  // radix sort (key, perm) over just the bits a cell index needs
-  int bits = 1; while ((1 << bits) < c->ncell_ext) bits++;
+  // radix sort (key, perm) over just the bits a cell index (+ 2 sentinels) needs
+  int bits = 1; while ((1 << bits) < c->ncell_ext + 2) bits++;
   size_t tmp_bytes = 0;
   cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, c->key.p, c->key_alt.p, c->perm.p, c->perm_alt.p,
-                                  n, 0, bits, st);
+                                  n_sort, 0, bits, st);
   size_t scan_bytes = 0;
   const int nplan = (int) c->gplan.size();
   cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, c->gcell_off.p, c->gcell_off.p, nplan + 1, st);
   CU_CHECK(c, c->cub_tmp.ensure(std::max(tmp_bytes, scan_bytes) + 256));
-  CU_CHECK(c, cub::DeviceRadixSort::SortPairs(c->cub_tmp.p, tmp_bytes, c->key.p, c->key_alt.p, c->perm.p,
-                                              c->perm_alt.p, n, 0, bits, st));
-  c->count_launch(4);   // cub: histogram + onesweep passes (approximate count)
+  if (n_sort > 0) {
+    CU_CHECK(c, cub::DeviceRadixSort::SortPairs(c->cub_tmp.p, tmp_bytes, c->key.p, c->key_alt.p, c->perm.p,
+                                                c->perm_alt.p, n_sort, 0, bits, st));
+    c->count_launch(4);   // cub: histogram + onesweep passes (approximate count)
+  }
+  n = n_new;
+  const int nb = div_up(std::max(n, 1), 256);
 
   CU_CHECK(c, c->pos4_alt.ensure_exact(c->pos4.cap));   // same capacity on both sides of the swap
   CU_CHECK(c, c->type_alt.ensure_exact(c->type.cap));
-  k_gather<<<nb, 256, 0, st>>>(n, c->perm_alt.p, c->pos4.p, c->mom4.p, c->type.p, c->vtype.p, c->id.p,
-                               c->pos4_alt.p, c->mom4_alt.p, c->type_alt.p, c->vtype_alt.p, c->id_alt.p,
-                               c->refx.p, c->refy.p, c->refz.p,
-                               c->ttm.inited && c->ttm.fdi.cap >= (size_t) n ? c->ttm.fdi.p : nullptr, c->ttm.fdi_alt.p);
-  c->count_launch();
-  if (c->ttm.inited && c->ttm.fdi.cap >= (size_t) n) swap_buf(c->ttm.fdi, c->ttm.fdi_alt);
+  const bool have_fdi = c->ttm.inited && c->ttm.fdi.cap >= (size_t) n_sort;
+  if (n > 0) {
+    k_gather<<<nb, 256, 0, st>>>(n, c->perm_alt.p, c->pos4.p, c->mom4.p, c->type.p, c->vtype.p, c->id.p,
+                                 c->pos4_alt.p, c->mom4_alt.p, c->type_alt.p, c->vtype_alt.p, c->id_alt.p,
+                                 c->refx.p, c->refy.p, c->refz.p, have_fdi ? c->ttm.fdi.p : nullptr, c->ttm.fdi_alt.p);
+    c->count_launch();
+  }
+  if (have_fdi) swap_buf(c->ttm.fdi, c->ttm.fdi_alt);
   swap_buf(c->pos4, c->pos4_alt); swap_buf(c->mom4, c->mom4_alt); swap_buf(c->type, c->type_alt);
   swap_buf(c->vtype, c->vtype_alt); swap_buf(c->id, c->id_alt); swap_buf(c->key, c->key_alt);
 
   CU_CHECK(c, cudaMemsetAsync(c->cell_begin.p, 0, (c->ncell_ext + 1) * sizeof(int), st));
   CU_CHECK(c, cudaMemsetAsync(c->cell_count.p, 0, (c->ncell_ext + 1) * sizeof(int), st));
-  k_cell_bounds<<<nb, 256, 0, st>>>(n, c->key.p, c->cell_begin.p, c->cell_count.p);
+  if (n > 0) {
+    k_cell_bounds<<<nb, 256, 0, st>>>(n, c->key.p, c->cell_begin.p, c->cell_count.p);
+    c->count_launch();
+  }
   k_cell_fix_count<<<div_up(c->ncell_ext, 256), 256, 0, st>>>(c->ncell_ext, c->cell_begin.p, c->cell_count.p);
-  c->count_launch(2);
+  c->count_launch();
 
   // ghost cells: counts stage by stage, offsets by one exclusive scan over the plan
   c->ng = 0;
@@ -236,6 +266,7 @@ int imdcu_rebuild_cells(imdcu_ctx *c)
     for (int s = 0; s < 3; s++) {
       int q0 = c->gstage_cells[s], q1 = c->gstage_cells[s + 1];
       if (q1 > q0) {
+        if (s == 2 && multi) RET_IF(imdcu_multi_ghost_counts(c));      // needs the y/z ghost counts of the planes
         k_ghost_counts<<<div_up(q1 - q0, 256), 256, 0, st>>>(q0, q1, c->d_gplan.p, c->cell_count.p, c->gcell_off.p);
         c->count_launch();
       }
@@ -255,15 +286,16 @@ int imdcu_rebuild_cells(imdcu_ctx *c)
     CU_CHECK(c, c->type.ensure_keep(nt, n, st, 1.1));
     CU_CHECK(c, c->ghost_src.ensure(c->ng, 1.1));  CU_CHECK(c, c->ghost_code.ensure(c->ng, 1.1));
     CU_CHECK(c, c->ghost_root.ensure(c->ng, 1.1)); CU_CHECK(c, c->ghost_tcode.ensure(c->ng, 1.1));
+    CU_CHECK(c, c->ghost_gid.ensure(c->ng, 1.1));
     CU_CHECK(c, c->ghost_raw.ensure(3 * c->ng, 1.1));
     k_ghost_begin<<<div_up(nplan, 256), 256, 0, st>>>(nplan, n, c->d_gplan.p, c->gcell_off.p, c->cell_begin.p);
     c->count_launch();
     for (int s = 0; s < 3; s++) {
       int q0 = c->gstage_cells[s], q1 = c->gstage_cells[s + 1];
-      if (q1 > q0) {
+      if (q1 > q0 && !(s == 2 && multi)) {
         k_ghost_fill<<<div_up((int64_t) (q1 - q0) * 32, 256), 256, 0, st>>>(
             q0, q1, n, c->d_gplan.p, c->gcell_off.p, c->cell_begin.p, c->ghost_src.p, c->ghost_code.p,
-            c->ghost_root.p, c->ghost_tcode.p, c->type.p);
+            c->ghost_root.p, c->ghost_tcode.p, c->type.p, c->id.p, c->ghost_gid.p);
         c->count_launch();
       }
     }

@@ -222,6 +222,26 @@ struct imdcu_ctx {
 
   TtmState ttm;
 
+  // multi-GPU (x-slab decomposition, multi.cu); nranks == 1: everything below is unused
+  struct Comm {
+    void *nccl = nullptr;                    // ncclComm_t
+    int   rank = 0, nranks = 1;
+    int   west = -1, east = -1;              // x-neighbour ranks, -1: open end
+    int   wrap_w = 0, wrap_e = 0;            // message to west/east crosses the periodic x boundary
+    int   nplane = 0;                        // cells per yz plane of the extended grid (ey*ez)
+    int   q_east = 0, q_west = 0;            // first plan entry of the ghost planes x = ex-1 / x = 0
+    int   plane_cnt[2] = {0, 0};             // atoms in my west / east plane (packed layout: west first)
+    int   nsend[2] = {0, 0}, nrecv[2] = {0, 0};   // [0] west plane / from east, [1] east plane / from west
+    int64_t recv_off[2] = {0, 0};            // ghost atom offset (relative to n) of the two received planes
+    DevBuf<int>     send_idx;                // [nsend[0] + nsend[1]] local indices, plane-cell order
+    DevBuf<double4> send_buf;                // packed records
+    DevBuf<int>     cnt_send, cnt_recv;      // [2*nplane] per-cell occupancies
+    DevBuf<double>  build_send, build_recv;  // build-time metadata records
+    DevBuf<double>  mig_send, mig_recv;      // migration records
+    int  *d_migcnt = nullptr, *h_migcnt = nullptr;   // [4]
+  } comm;
+  DevBuf<int> ghost_gid;                     // [ng] atom id of every image atom (pair export)
+
   // bookkeeping
   int64_t launches = 0;
   bool    profiling = false;
@@ -260,6 +280,17 @@ int imdcu_eam_forces(imdcu_ctx *ctx, double out8[8]);    // eam.cu
 int imdcu_integrate_nve(imdcu_ctx *ctx, double out8[8], int *valid);   // integrate.cu
 int imdcu_integrate_ttm(imdcu_ctx *ctx, double out8[8], int *valid);   // integrate.cu
 int imdcu_ttm_step(imdcu_ctx *ctx, int steps, double out16[16]);       // ttm.cu
+// multi.cu
+int  imdcu_multi_migrate(imdcu_ctx *ctx, int *n_total);      // after k_wrap_key: movers out, arrivals appended
+int  imdcu_multi_ghost_counts(imdcu_ctx *ctx);               // x-stage ghost cell occupancies from the neighbours
+int  imdcu_multi_ghost_build(imdcu_ctx *ctx);                // x-stage ghost atoms + metadata at a rebuild
+int  imdcu_multi_ghost_refresh(imdcu_ctx *ctx);              // x-stage positions / F' every step
+int  imdcu_multi_allreduce(imdcu_ctx *ctx, void *buf, int count, int kind);   // kind 0 sum f64, 1 max f64, 2 sum i32
+void imdcu_multi_release(imdcu_ctx *ctx);
+__device__ __host__ inline int imdcu_combine_code(int pc, int code)
+{
+  return (pc % 3 - 1 + code % 3 - 1 + 1) + 3 * ((pc / 3) % 3 - 1 + (code / 3) % 3 - 1 + 1) + 9 * (pc / 9 - 1 + code / 9 - 1 + 1);
+}
 void imdcu_ttm_release(imdcu_ctx *ctx);                                // ttm.cu
 TabView imdcu_tab_view(const DevTable &t);
 

@@ -70,6 +70,8 @@ extern "C" int imdcu_destroy(imdcu_ctx *c)
   c->ghost_root.release(); c->ghost_tcode.release(); c->ghost_raw.release();
   c->nbl_idx.release(); c->nbl_num.release(); c->partials.release(); c->d_restrictions.release();
   imdcu_ttm_release(c);
+  imdcu_multi_release(c);
+  c->ghost_gid.release();
   for (int t = 0; t < 3; t++) {
     if (c->tab[t].coef) cudaFree(c->tab[t].coef);
     if (c->tab[t].begin) cudaFree(c->tab[t].begin);
@@ -194,7 +196,25 @@ static void build_ghost_plan(imdcu_ctx *c)
         c->gplan.push_back({eidx(g, i, 0, k), eidx(g, i, ey - 2, k), code(0, -1, 0)});
       }
   c->gstage_cells[2] = (int) c->gplan.size();
-  if (g.pbc[0])
+  if (c->comm.nranks > 1) {
+    // decomposed along x: the two ghost planes are filled from the neighbour ranks (multi.cu);
+    // src = -1 marks a remote plane; each plane is one contiguous block of plan entries
+    imdcu_ctx::Comm &m = c->comm;
+    m.nplane = ey * ez;
+    const int N = m.nranks, r = m.rank;
+    m.east = r + 1 < N ? r + 1 : (g.pbc[0] ? 0 : -1);
+    m.west = r - 1 >= 0 ? r - 1 : (g.pbc[0] ? N - 1 : -1);
+    m.wrap_e = (r == N - 1 && g.pbc[0]) ? 1 : 0;
+    m.wrap_w = (r == 0 && g.pbc[0]) ? 1 : 0;
+    m.q_east = (int) c->gplan.size();
+    if (m.east >= 0)
+      for (int j = 0; j < ey; j++)
+        for (int k = 0; k < ez; k++) c->gplan.push_back({eidx(g, ex - 1, j, k), -1, code(m.wrap_e ? +1 : 0, 0, 0)});
+    m.q_west = (int) c->gplan.size();
+    if (m.west >= 0)
+      for (int j = 0; j < ey; j++)
+        for (int k = 0; k < ez; k++) c->gplan.push_back({eidx(g, 0, j, k), -1, code(m.wrap_w ? -1 : 0, 0, 0)});
+  } else if (g.pbc[0])
     for (int j = 0; j < ey; j++)
       for (int k = 0; k < ez; k++) {
         c->gplan.push_back({eidx(g, ex - 1, j, k), eidx(g, 1, j, k), code(+1, 0, 0)});
@@ -233,6 +253,7 @@ extern "C" int imdcu_set_box(imdcu_ctx *c, const double box[9], const int pbc[3]
   for (int d = 0; d < 3; d++) {
     int cd = divisor ? divisor[d] : 1;
     if (cd < 1) cd = 1;
+    if (d == 0) cd *= c->comm.nranks;            // cpu_dim.x of the reference (imd_geom_3d.c:168-176)
     volatile double scale = sqrt(1.0 * g.cellsz / height[d]);
     g.gdim[d] = (int) (1.0 / scale);
     if (0 != g.gdim[d] % cd) g.gdim[d] = ((int) (g.gdim[d] / cd)) * cd;
@@ -242,6 +263,12 @@ extern "C" int imdcu_set_box(imdcu_ctx *c, const double box[9], const int pbc[3]
     g.edim[d] = g.ldim[d] + 2;
   }
   g.xoff = 0;
+  if (c->comm.nranks > 1) {                      // x slabs of equal cell-layer count, rank r owns [r*l, (r+1)*l)
+    g.ldim[0] = g.gdim[0] / c->comm.nranks;
+    g.edim[0] = g.ldim[0] + 2;
+    g.xoff = c->comm.rank * g.ldim[0];
+    if (g.pbc[0] && c->comm.nranks == 2 && g.ldim[0] < 1) return c->fail(IMDCU_EINVAL, "x slab too thin");
+  }
   c->ncell_ext = g.edim[0] * g.edim[1] * g.edim[2];
   build_ghost_plan(c);
   CU_CHECK(c, c->cell_begin.ensure(c->ncell_ext + 1));

@@ -308,7 +308,9 @@ int imdcu_eam_forces(imdcu_ctx *c, double out8[8])
     RET_IF(rc);
   } else {
     CU_CHECK(c, cudaMemsetAsync(c->d_results, 0, 4 * sizeof(double), c->stream));
+    if (c->comm.nranks > 1) RET_IF(imdcu_refresh_ghosts(c, false));   // the neighbours still expect the F' exchange
   }
+  RET_IF(imdcu_multi_allreduce(c, c->d_results, 3, 0));               // MPI_Allreduce of imd_forces_nbl.c:997-1016
   if (out8) {
     CU_CHECK(c, cudaMemcpyAsync(c->h_results, c->d_results, 4 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     CU_CHECK(c, cudaStreamSynchronize(c->stream));

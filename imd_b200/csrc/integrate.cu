@@ -113,6 +113,8 @@ static int integrate(imdcu_ctx *c, double out8[8], int *valid, bool ttm)
   else k_move_nve<<<grid, 256, 0, c->stream>>>(a);
   c->count_launch();
   CU_CHECK(c, cudaGetLastError());
+  RET_IF(imdcu_multi_allreduce(c, c->d_results + 4, 1, 0));           // tot_kin_energy (imd_integrate.c:790-808)
+  RET_IF(imdcu_multi_allreduce(c, c->d_results + 5, 1, 1));           // check_nblist's MAX (imd_forces_nbl.c:1085)
   CU_CHECK(c, cudaMemcpyAsync(c->h_results + 4, c->d_results + 4, 2 * sizeof(double),
                               cudaMemcpyDeviceToHost, c->stream));
   CU_CHECK(c, cudaStreamSynchronize(c->stream));

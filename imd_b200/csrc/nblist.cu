@@ -116,20 +116,20 @@ extern "C" int imdcu_get_nblist_pairs(imdcu_ctx *c, int64_t *npairs, int32_t *pa
   const int64_t n = c->n, ng = c->ng;
   const int cap = c->nbl_cap;
   CU_CHECK(c, cudaStreamSynchronize(c->stream));
-  std::vector<int> num((size_t) n), id((size_t) n), root((size_t) ng + 1);
+  std::vector<int> num((size_t) n), id((size_t) n), gid((size_t) ng + 1);
   std::vector<int> idx((size_t) div_up(n, 32) * cap * 32);
   CU_CHECK(c, cudaMemcpy(num.data(), c->nbl_num.p, n * sizeof(int), cudaMemcpyDeviceToHost));
   CU_CHECK(c, cudaMemcpy(id.data(), c->id.p, n * sizeof(int), cudaMemcpyDeviceToHost));
-  if (ng) CU_CHECK(c, cudaMemcpy(root.data(), c->ghost_root.p, ng * sizeof(int), cudaMemcpyDeviceToHost));
+  if (ng) CU_CHECK(c, cudaMemcpy(gid.data(), c->ghost_gid.p, ng * sizeof(int), cudaMemcpyDeviceToHost));
   CU_CHECK(c, cudaMemcpy(idx.data(), c->nbl_idx.p, idx.size() * sizeof(int), cudaMemcpyDeviceToHost));
   int64_t np = 0;
   for (int64_t i = 0; i < n; i++) {
     const size_t base = ((size_t) (i >> 5) * cap) * 32 + (i & 31);
     for (int k = 0; k < num[i]; k++) {
       int j = idx[base + (size_t) k * 32];
-      int r = j < n ? j : root[j - n];
-      if (id[i] < id[r] || (id[i] == id[r] && j >= n && i < j)) {
-        if (pairs) { pairs[2 * np] = id[i]; pairs[2 * np + 1] = id[r]; }
+      const int idj = j < n ? id[j] : gid[j - n];
+      if (id[i] < idj || (id[i] == idj && j >= n && i < j)) {
+        if (pairs) { pairs[2 * np] = id[i]; pairs[2 * np + 1] = idj; }
         np++;
       }
     }

@@ -804,14 +804,22 @@ int imdcu_ttm_step(imdcu_ctx *c, int steps, double out16[16])
   }
   CU_CHECK(c, cudaMemsetAsync(t.isum.p, 0, 4 * (size_t) G * sizeof(int), st));
   CU_CHECK(c, cudaMemsetAsync(t.dsum.p, 0, 4 * (size_t) G * sizeof(double), st));
+  const int nb = div_up(std::max(n, 1), 256);
   if (n > 0) {
-    const int nb = div_up(n, 256);
     k_ttm_atoms1<<<nb, 256, 0, st>>>(n, G, t.fd_hx, steps, c->pos4.p, c->mom4.p, c->type.p, c->numneighs.p,
                                      t.fdi.p, t.isum.p, t.dsum.p);
+    c->count_launch();
+  }
+  // the 7 MPI_Allreduce of imd_ttm.c:325-334 as two calls on the packed buffers; afterwards every
+  // GPU holds the global slab sums and advances the identical (replicated) FD lattice
+  RET_IF(imdcu_multi_allreduce(c, t.isum.p, 4 * G, 2));
+  RET_IF(imdcu_multi_allreduce(c, t.dsum.p, 3 * G, 0));
+  if (n > 0) {
     k_ttm_atoms2<<<nb, 256, 0, st>>>(n, G, t.fd_hx, t.p.atomic_weight, c->mom4.p, c->type.p, t.fdi.p, t.isum.p,
                                      t.dsum.p);
-    c->count_launch(2);
+    c->count_launch();
   }
+  RET_IF(imdcu_multi_allreduce(c, t.dsum.p + 3 * (size_t) G, G, 0));   // imd_ttm.c:395
   TtmArgs a;
   a.G = G; a.P = t.P; a.L = t.L; a.LD = t.LD; a.steps = steps; a.ncell_tot = t.P * t.L + t.p.vlatdim;
   a.p = t.p;

@@ -17,9 +17,30 @@ TAB_PAIR, TAB_RHO, TAB_EMBED = 0, 1, 2
 capi_EOS_CVE, capi_EOS_EE = 0, 1
 
 
+def slab_rank_of_atoms(pos, box, pbc_x, gdim_x, nranks):
+    """Owner rank of every atom for the x-slab decomposition cpu_dim = nranks 1 1: global cell
+    layer by cell_coord (imd_geom_3d.c:1077-1097), rank r owns layers [r*l, (r+1)*l), l = gdim_x/nranks
+    (imd_geom_mpi_3d.c:119-128).  Host-side helper: which atoms a rank uploads."""
+    tbox_x = np.linalg.inv(np.asarray(box, np.float64).reshape(3, 3))[:, 0]
+    s = np.asarray(pos, np.float64) @ tbox_x
+    if pbc_x:
+        s = s - np.floor(s)
+    g = int(gdim_x)
+    if g % nranks != 0:
+        raise ValueError("global_cell_dim.x %d is not a multiple of the number of ranks %d" % (g, nranks))
+    cx = np.clip((g * s).astype(np.int64), 0, g - 1)
+    return (cx // (g // nranks)).astype(np.int32)
+
+
 class Imd:
-    def __init__(self, device: int = 0):
+    def __init__(self, device: int = 0, comm=None):
+        """comm = (ncclUniqueId bytes, rank, nranks): x-slab decomposition over nranks GPUs, the
+        reference's cpu_dim = nranks 1 1 (one process per GPU, like one MPI rank per core)."""
         self.ctx = capi.Context(device)
+        self.rank, self.nranks = 0, 1
+        if comm is not None:
+            uid, self.rank, self.nranks = comm
+            self.ctx.comm_init(uid, self.rank, self.nranks)
         self.tot_pot_energy = 0.0
         self.virial = 0.0
         self.tot_kin_energy = 0.0
@@ -36,6 +57,16 @@ class Imd:
     def make_box(self, box, pbc_dirs, nbl_margin, nbl_size=1.3, cell_divisor=None):
         self.ctx.set_box(box, pbc_dirs, nbl_margin, nbl_size, cell_divisor)
         self.global_cell_dim, self.cellsz = self.ctx.cell_grid()
+        self.box = np.asarray(box, np.float64).reshape(3, 3)
+        self.pbc_dirs = tuple(int(p) for p in pbc_dirs)
+        self.slab = self.ctx.comm_rank()
+
+    def owned_mask(self, pos):
+        """Which atoms lie in this rank's x slab (cell_coord, imd_geom_3d.c:1077-1097; an atom the
+        host puts one slab off migrates at the first rebuild)."""
+        if self.nranks == 1:
+            return np.ones(pos.shape[0], bool)
+        return slab_rank_of_atoms(pos, self.box, self.pbc_dirs[0], self.global_cell_dim[0], self.nranks) == self.rank
 
     def set_params(self, ntypes=1, timestep=0.1, restrictions=None):
         self.ctx.set_params(ntypes, timestep, restrictions)

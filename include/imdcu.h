@@ -49,6 +49,19 @@ int  imdcu_create(imdcu_ctx **ctx, int device);
 int  imdcu_destroy(imdcu_ctx *ctx);
 const char *imdcu_last_error(const imdcu_ctx *ctx);   /* ctx may be NULL: create errors */
 
+/* ------------------------------------------------------------------ multi-GPU (one context per rank) */
+/* Domain decomposition in x slabs, cpu_dim = nranks 1 1 (setup_mpi_topology, imd_geom_mpi_3d.c;
+ * the halo exchange of imd_comm_force_3d.c and the MPI_Allreduce calls of the path become NCCL
+ * send/recv/allreduce).  id: an ncclUniqueId as 128 opaque bytes, created on one rank with
+ * imdcu_comm_unique_id and distributed by the host (MPI_Bcast in IMD, torch.distributed in
+ * bench.py).  Must be called before imdcu_set_box; nranks == 1 is a no-op.  Every rank then
+ * uploads the atoms of its own slab (imdcu_comm_rank gives the owned global x cell layers
+ * [xoff, xoff+ldimx)); atoms that cross a slab boundary migrate at neighbour-list rebuilds
+ * (send_atoms of fix_cells, imd_fix_cells_3d.c:43-306). */
+int  imdcu_comm_unique_id(char id[128]);
+int  imdcu_comm_init(imdcu_ctx *ctx, const char id[128], int rank, int nranks);
+int  imdcu_comm_rank(const imdcu_ctx *ctx, int *rank, int *nranks, int *xoff, int *ldimx);
+
 /* ------------------------------------------------------------------ set-up */
 /* Box and cell grid.  Replaces make_box (imd_geom_3d.c:52-108) and init_cells
  * (imd_geom_3d.c:118-330): box = rows box_x, box_y, box_z; tbox and heights are
