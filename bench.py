@@ -15,8 +15,11 @@ e2e   : the same step driven through the C ABI with HOST buffers: every step upl
         positions, momenta, forces, per-atom energies and the energy sums.
 roofline : dominant kernel (k_eam_pass1), algorithmic bytes (64 + 4*N_h per atom,
         SURVEY.md 8d) / its mean launch time measured live with CUDA events.
-cpu_baseline : the UNMODIFIED reference binary (oracle/_ref, author's flags) on the host
-        cores, a bounded sample of the same workload.
+cpu_baseline : the UNMODIFIED reference (oracle/_ref, author's flags), its own MPI build run
+        over oracle/shmpi with one rank per host core (cpu_dim P 1 1), a bounded sample of the
+        same workload; falls back to P concurrent serial runs if the MPI run fails.
+N > 1  : weak scaling -- every GPU owns an x slab of --cells cubic cells (cpu_dim = N 1 1), halo
+        planes over NCCL; --ttm adds calc_ttm + move_atoms_ttm (BASELINE.json configs[2]).
 """
 from __future__ import annotations
 
@@ -36,11 +39,12 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-METRIC = "EAM atom-steps/s"
+METRIC = "EAM+TTM atom-steps/s"
 UNIT = "atom-steps/s"
 N_H_AL = 39                 # half-list neighbours per atom, Al r_c 6.3 + margin 0.4
 REF_FAST = os.path.join(ROOT, "oracle", "_ref", "imd_ref_eam_nve_nbl_fast")
 REF_IEEE = os.path.join(ROOT, "oracle", "_ref", "imd_ref_eam_nve_nbl")
+REF_MPI = os.path.join(ROOT, "oracle", "_ref", "imd_ref_mpi_eam_nve_nbl_fast")
 
 
 def measured_peak_gbs():
@@ -141,6 +145,68 @@ def run_reference_sample(box_cells, steps, nproc, use_fast=True):
         shutil.rmtree(work, ignore_errors=True)
 
 
+def run_reference_mpi(cells_per_rank, steps, nproc):
+    """The reference's own MPI build (cpu_dim nproc 1 1, x slabs like the GPU decomposition) over
+    oracle/shmpi; throughput from the reference's own main-loop timer (imd.c:387-392, MPI_Wtime)."""
+    from imd_b200 import synth
+    if not os.path.exists(REF_MPI):
+        return None
+    spec = synth.AL
+    work = tempfile.mkdtemp(prefix="imdbench_mpi_")
+    try:
+        synth.make_eam_tables(spec, work)
+        os.makedirs(os.path.join(work, "out"))
+        cx, cy, cz = cells_per_rank
+        synth.write_param_file(os.path.join(work, "run.param"), spec, (cx * nproc, cy, cz), steps, "out/run",
+                               potdir=".", pbc=(1, 1, 1), starttemp=0.0258, nbl_margin=0.4, eng_int=0,
+                               cpu_dim=(nproc, 1, 1))
+        env = dict(os.environ, SHMPI_NP=str(nproc), SHMPI_RING_MB="4")
+        t0 = time.perf_counter()
+        res = subprocess.run([REF_MPI, "-p", "run.param"], cwd=work, env=env, stdout=subprocess.PIPE,
+                             stderr=subprocess.STDOUT, text=True, timeout=900)
+        wall = time.perf_counter() - t0
+        m = re.search(r"([0-9.eE+-]+) seconds excluding setup time", res.stdout)
+        n = re.search(r"Did (\d+) steps with (\d+) atoms", res.stdout)
+        if res.returncode != 0 or not m or not n:
+            raise RuntimeError("reference MPI run failed:\n" + res.stdout[-1500:])
+        tm, nsteps, natoms = float(m.group(1)), int(n.group(1)), int(n.group(2))
+        return {"value": natoms * nsteps / tm, "natoms": natoms, "steps": nsteps, "nproc": nproc,
+                "main_loop_s": tm, "wall_s": wall, "binary": os.path.basename(REF_MPI), "mode": "mpi"}
+    finally:
+        shutil.rmtree(work, ignore_errors=True)
+
+
+def reference_sample(cells, world, steps):
+    """The reference on the bench workload itself: global lattice (cells.x * world) x cells.y x cells.z,
+    MPI build on as many ranks as divide the x extent (>= 5 lattice cells = 20 A per rank, <= cores,
+    <= 40); concurrent serial runs of a 24^3 sample as the fallback."""
+    cores = max(1, host_cores())
+    gx = cells[0] * world
+    nproc = max([p for p in range(1, min(cores, 40) + 1) if gx % p == 0 and gx // p >= 5] or [1])
+    try:
+        r = run_reference_mpi((gx // nproc, cells[1], cells[2]), steps, nproc) if nproc >= 2 else None
+        if r:
+            r["sample"] = ("the reference's MPI build (%s, author's flags) over oracle/shmpi, %d ranks (cpu_dim %d 1 1) on %d "
+                           "host cores, Al fcc %dx%dx%d cells = %d atoms, %d NVE steps, 300 K (main loop %.1f s, wall %.1f s)"
+                           % (r["binary"], nproc, nproc, cores, gx, cells[1], cells[2], r["natoms"], r["steps"],
+                              r["main_loop_s"], r["wall_s"]))
+            return r
+    except Exception as ex:                               # fall through to the serial form
+        sys.stderr.write("bench: MPI reference failed (%s); using concurrent serial runs\n" % ex)
+    r = run_reference_sample((24, 24, 24), steps, cores)
+    if r:
+        r["mode"] = "serial x%d" % cores
+        r["sample"] = ("%d concurrent serial runs of the unmodified reference (%s), each Al fcc 24^3 cells = %d atoms, "
+                       "%d NVE steps (%.1f s wall)" % (r["nproc"], r["binary"], r["natoms"], r["steps"], r["wall_s"]))
+    return r
+
+
+def reference_steps(cells, world, want):
+    """Bound the CPU sample: about 3e8 atom-steps (10-30 s on 16 cores), never fewer than 5 steps."""
+    natoms = 4 * cells[0] * cells[1] * cells[2] * world
+    return int(max(5, min(want, 3.0e8 / natoms)))
+
+
 def host_cores():
     try:
         return len(os.sched_getaffinity(0))
@@ -151,10 +217,8 @@ def host_cores():
 def reference_arm(args, rank, world):
     if rank != 0:
         return 0
-    cells = (24, 24, 24)
-    nproc = max(1, host_cores())
-    steps = max(2, min(args.steps + args.warmup, 60))
-    r = run_reference_sample(cells, steps, nproc)
+    steps = reference_steps(args.cells, max(1, args.gpus), args.steps + args.warmup)
+    r = reference_sample(args.cells, max(1, args.gpus), steps)
     base = {"metric": METRIC, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -163,9 +227,7 @@ def reference_arm(args, rank, world):
         base["unavailable"] = "oracle/_ref binaries not built (make -C oracle ref needs /root/reference)"
         print(json.dumps(base))
         return 0
-    sample = ("%d concurrent serial runs of the unmodified reference (%s; no MPI in this image), each Al fcc "
-              "%dx%dx%d cells = %d atoms, %d NVE steps, 300 K; rate = sum atoms*steps/main-loop time"
-              % (r["nproc"], r["binary"], cells[0], cells[1], cells[2], r["natoms"], r["steps"]))
+    sample = r["sample"]
     base.update({"value": r["value"], "ms_per_step": 1e3 * r["main_loop_s"] / r["steps"],
                  "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["nproc"], "kind": "reference",
                                   "sample": sample},
@@ -177,22 +239,40 @@ def reference_arm(args, rank, world):
 
 def workload_config(args):
     c = args.cells
-    return {"workload": "Al fcc EAM2 NVE slab, %dx%dx%d cubic cells = %d atoms per GPU, 300 K, "
-                        "timestep 0.1 (1.018 fs), nbl_margin 0.4 (BASELINE.json configs[1])"
-                        % (c[0], c[1], c[2], 4 * c[0] * c[1] * c[2]),
-            "atoms_per_gpu": 4 * c[0] * c[1] * c[2],
+    n = 4 * c[0] * c[1] * c[2]
+    if getattr(args, "ttm", False):
+        w = ("Al fcc EAM2 + 1-D TTM film (calc_forces, calc_ttm, move_atoms_ttm), %dx%dx%d cubic cells = %d atoms per "
+             "GPU, vacuum 10 a front and rear, pbc 0 1 1, 300 K, timestep 0.1, nbl_margin 0.4, FD cell ~16 A, "
+             "fd_n_timesteps %d (BASELINE.json configs[2] shape)" % (c[0], c[1], c[2], n, args.ttm_substeps))
+    else:
+        w = ("Al fcc EAM2 NVE slab, %dx%dx%d cubic cells = %d atoms per GPU, 300 K, timestep 0.1 (1.018 fs), "
+             "nbl_margin 0.4 (BASELINE.json configs[1])" % (c[0], c[1], c[2], n))
+    return {"workload": w, "atoms_per_gpu": n,
             "l2_policy": "inputs larger than L2 (neighbour list alone ~0.8 GB per 2M atoms)",
             "parallelism": "1 GPU" if args.gpus == 1 else "x-slab domain decomposition, %d GPUs" % args.gpus}
 
 
 # ----------------------------------------------------------------------------- our arm
 
-def build_system(cells, seed):
+def build_system(cells, rank=0, world=1, ttm=False):
+    """This rank's part of the global lattice: (cells.x * world) x cells.y x cells.z cubic cells
+    (weak scaling), cut where the library cuts the box (equal x slabs).  With --ttm the box gets
+    vacuum in front of and behind the film (pbc 0 1 1), so the cut does not fall on lattice
+    planes: the caller still filters with Imd.owned_mask.  Returns ids that are global indices."""
     from imd_b200 import synth
     spec = synth.AL
-    pos, box = synth.fcc_lattice(cells, spec.a)
-    mom = synth.maxwell_momenta(pos.shape[0], spec.mass, 0.0258, seed=seed)
-    return spec, pos, box, mom
+    a = spec.a
+    ncx = cells[0] * world
+    vac = 10 * a if ttm else 0.0
+    lx = ncx * a + 2 * vac
+    lo, hi = rank * lx / world, (rank + 1) * lx / world
+    i0 = max(0, int(np.floor((lo - vac) / a)) - 1)
+    i1 = min(ncx, int(np.ceil((hi - vac) / a)) + 1)
+    pos, box = synth.fcc_lattice((max(i1 - i0, 0), cells[1], cells[2]), a)
+    pos[:, 0] += i0 * a + vac
+    box[0, 0] = lx
+    ids = (np.arange(pos.shape[0], dtype=np.int64) + 4 * i0 * cells[1] * cells[2]).astype(np.int32)
+    return spec, pos, box, ids
 
 
 def our_arm(args, rank, local_rank, world):
@@ -206,15 +286,36 @@ def our_arm(args, rank, local_rank, world):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    spec, pos, box, mom = build_system(args.cells, 1234 + rank)
-    natoms = pos.shape[0]
+    spec, pos, box, ids = build_system(args.cells, rank, world, args.ttm)
+    natoms = 4 * args.cells[0] * args.cells[1] * args.cells[2]      # per GPU on average (exact for NVE)
     tables = synth.make_eam_tables(spec)
-    imd = host.Imd(local_rank)
+    comm = None
+    if world > 1:
+        from imd_b200 import capi
+        obj = [capi.Context.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(obj, src=0)
+        comm = (obj[0], rank, world)
+    imd = host.Imd(local_rank, comm)
     imd.setup_potentials(tables)
-    imd.make_box(box, (1, 1, 1), 0.4)
+    imd.make_box(box, (0, 1, 1) if args.ttm else (1, 1, 1), 0.4)
     imd.set_params(1, 0.1)
-    imd.set_atoms(pos, mom, spec.mass)
+    mask = imd.owned_mask(pos)
+    pos, ids = pos[mask], ids[mask]
+    mom = synth.maxwell_momenta(pos.shape[0], spec.mass, 0.0258, seed=1234 + rank)
+    imd.set_atoms(pos, mom, spec.mass, None, ids)
+    cnt = torch.tensor([pos.shape[0]], dtype=torch.int64, device="cuda")
+    if world > 1:
+        dist.all_reduce(cnt)
+    if int(cnt.item()) != natoms * world:
+        raise SystemExit("bench.py: slab generation lost atoms (%d != %d)" % (int(cnt.item()), natoms * world))
     ctx = imd.ctx
+    if args.ttm:
+        eos = synth.make_eos_tables()          # diag = None: all rectangles split the same way
+        gx = max(world, int(box[0, 0] / 16.0) // world * world)
+        tp = synth.TtmParams(ttmdimx=gx, fd_n_timesteps=args.ttm_substeps, fd_min_atoms=100, vlatdim=30,
+                             vlatbuffer=8, I0=5.0e15, laser_t_0=100e-15, laser_sigma_t=42.5e-15)
+        imd.init_ttm(tp, eos, world)
+    run = (lambda first, n: ctx.run_ttm(first, n, False)) if args.ttm else (lambda first, n: ctx.run_nve(first, n, False))
     stream = torch.cuda.ExternalStream(ctx.stream, device=local_rank)
 
     def barrier():
@@ -226,13 +327,13 @@ def our_arm(args, rank, local_rank, world):
     # ---- device-resident throughput
     sampler = ClockSampler(local_rank)
     sampler.start()                              # clocks under load: warm-up + timed region
-    ctx.run_nve(0, args.warmup, False)
+    run(0, args.warmup)
     barrier()
     l0 = ctx.launch_count
     nbl0 = ctx.nbl_count
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record(stream)
-    ctx.run_nve(args.warmup, args.steps, False)
+    run(args.warmup, args.steps)
     ev1.record(stream)
     barrier()
     clocks = sampler.stop()
@@ -247,17 +348,22 @@ def our_arm(args, rank, local_rank, world):
 
     # ---- end to end through the C ABI with host buffers (pinned)
     ke = max(1, min(args.steps, args.e2e_steps))
-    hp = torch.empty((natoms, 3), dtype=torch.float64).pin_memory()
-    hm = torch.empty((natoms, 3), dtype=torch.float64).pin_memory()
-    hf = torch.empty((natoms, 3), dtype=torch.float64).pin_memory()
-    he = torch.empty((natoms,), dtype=torch.float64).pin_memory()
+    cap = int(max(natoms, pos.shape[0]) * 1.25) + 1024   # the slab population changes when atoms migrate
+    hp = torch.empty((cap, 3), dtype=torch.float64).pin_memory()
+    hm = torch.empty((cap, 3), dtype=torch.float64).pin_memory()
+    hf = torch.empty((cap, 3), dtype=torch.float64).pin_memory()
+    he = torch.empty((cap,), dtype=torch.float64).pin_memory()
     np_p, np_m, np_f, np_e = hp.numpy(), hm.numpy(), hf.numpy(), he.numpy()
     ctx.download_into(np_p, np_m, np_f, np_e)
 
     def e2e_step(s):
-        ctx.update_atoms(np_p, np_m)             # H2D: this step's inputs
+        ctx.update_atoms(np_p, np_m)             # H2D: this step's inputs (first ctx.n rows)
         out = ctx.calc_forces(s)                 # D2H: energy sums
-        out2, _ = ctx.move_atoms_nve()
+        if args.ttm:
+            ctx.calc_ttm(args.warmup + args.steps + 2 + s)
+            out2, _ = ctx.move_atoms_ttm()
+        else:
+            out2, _ = ctx.move_atoms_nve()
         ctx.download_into(np_p, np_m, np_f, np_e)  # D2H: the step's results
         return out[0] + out2[0]
 
@@ -281,7 +387,7 @@ def our_arm(args, rank, local_rank, world):
     phases = None
     if rank == 0:
         ctx.set_profiling(True)
-        ctx.run_nve(0, args.profile_steps, False)
+        run(args.warmup + args.steps + 100, args.profile_steps)
         ms_ph, ln_ph = ctx.phase_times()
         ctx.set_profiling(False)
         phases = {k: {"ms_total": ms_ph[k], "launches": ln_ph[k]} for k in ms_ph if ln_ph[k]}
@@ -297,13 +403,10 @@ def our_arm(args, rank, local_rank, world):
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
-            nproc = max(1, host_cores())
-            r = run_reference_sample((28, 28, 28), 30, nproc)
+            r = reference_sample(args.cells, 1, reference_steps(args.cells, 1, 30))
             if r:
                 cpu = {"value": r["value"], "unit": UNIT, "cores": r["nproc"], "kind": "reference",
-                       "sample": "%d concurrent serial runs of the unmodified reference (%s), each Al fcc 28^3 cells "
-                                 "= %d atoms, %d NVE steps (%.1f s wall)" % (r["nproc"], r["binary"], r["natoms"],
-                                                                           r["steps"], r["wall_s"])}
+                       "sample": r["sample"]}
         except Exception as ex:                    # the baseline must not take the bench down
             cpu = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "failed: %s" % ex}
 
@@ -333,6 +436,8 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--profile-steps", type=int, default=5)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ttm", action="store_true", help="EAM + TTM step (BASELINE.json configs[2])")
+    ap.add_argument("--ttm-substeps", type=int, default=250, help="fd_n_timesteps (manual example: 250)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
