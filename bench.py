@@ -385,11 +385,13 @@ def our_arm(args, rank, local_rank, world):
     # ---- per-kernel times (CUDA events inside the library, separate short segment)
     roofline = None
     phases = None
+    # every rank runs the segment (the steps exchange halos); rank 0 reports its own kernel times
+    ctx.set_profiling(True)
+    run(args.warmup + args.steps + 100, args.profile_steps)
+    ms_ph, ln_ph = ctx.phase_times()
+    ctx.set_profiling(False)
+    barrier()
     if rank == 0:
-        ctx.set_profiling(True)
-        run(args.warmup + args.steps + 100, args.profile_steps)
-        ms_ph, ln_ph = ctx.phase_times()
-        ctx.set_profiling(False)
         phases = {k: {"ms_total": ms_ph[k], "launches": ln_ph[k]} for k in ms_ph if ln_ph[k]}
         p1_ms = ms_ph["eam_pass1"] / max(1, ln_ph["eam_pass1"])
         alg_bytes = (64 + 4 * N_H_AL) * natoms

@@ -136,6 +136,7 @@ struct EosView {
 
 struct TtmState {
   bool   inited = false;
+  size_t grid_smem_set = 0;          // dynamic smem opted in for k_ttm_grid
   imdcu_ttm_params p;
   int    G = 0, P = 1, L = 0, LD = 0;
   double fd_hx = 0, fd_vol = 0, neighvol = 0, omega_laser = 0, sigma_t_sq = 0;

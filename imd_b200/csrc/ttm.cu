@@ -18,6 +18,7 @@
 // swapped by index (l1/l2).  Compiled with -fmad=false: the Brent iteration must see the
 // same IEEE operations as the host code.
 #include "device.cuh"
+#include "ttm_math.cuh"
 
 #include <cmath>
 
@@ -140,82 +141,80 @@ __device__ double eos_te_from_r_ee(const EosView &ee, double r, double e)
 }
 
 // ----------------------------------------------------------------------------- wide-range models (imd_ttm.c:2191-2399)
-__device__ __forceinline__ double fermi_E(double ne)
+// MeanCharge (:2241-2280), getKappa (:2356-2399), getGamma (:2310-2335) and their helpers
+// fermi_E/fermi_T/omega_pl/r0/bMin/bMax/coulomb_log/numet/numax/nupl (:2191-2308) for ONE cell,
+// fused: the reference evaluates fermi_E(Ne), r0(Ni), fermi_T(Ni*Z) and the Coulomb logarithm
+// two to four times per cell with identical arguments; here once.  Every arithmetic operation
+// keeps the reference's order; pow/exp/log are the branch-free versions of ttm_math.cuh
+// (pow(x,1.5) and pow(x,2.5) through one sqrt), so that the ~12 transcendental chains of a cell
+// interleave in one thread.  z0p43 = pow(z0, 4/3) is hoisted out of the sub-step loop.
+struct WideRange { double Z, ne, kappa, gamma; };
+
+__device__ __forceinline__ WideRange wide_range(double temp_ev, double ti_ev, double dens, double z0, double am,
+                                                double z0p43, double omega_las, int la)
 {
-  return C_HBAR * C_HBAR * pow(3.0 * M_PI * M_PI * ne, 2.0 / 3.0) / 2.0 / C_EMASS;
-}
-__device__ __forceinline__ double fermi_T(double ne) { return 2.0 * fermi_E(ne) / (3.0 * C_BOLTZMAN); }
-__device__ __forceinline__ double omega_pl(double ne) { return sqrt(ne * C_ECHARGE * C_ECHARGE / C_EMASS / C_ECONST); }
-__device__ __forceinline__ double r0_(double ni) { return pow(3.0 / (4 * M_PI * ni), 1.0 / 3.0); }
-__device__ __forceinline__ double bMin(double Z, double Te)
-{
-  return DMAX(Z * C_ECHARGE * C_ECHARGE / (C_BOLTZMAN * Te), C_HBAR / sqrt(2 * C_EMASS * C_BOLTZMAN * Te));
-}
-__device__ double bMax(double omega_las, double Z, double ni, double Te, int la)
-{
-  const double ft = fermi_T(ni * Z);
+  WideRange w;
+  // ---- MeanCharge(temp [K], rho, z0, am)
+  {
+    double temp = temp_ev * 11604.5, rho = dens;
+    temp *= 1e-3; rho *= 1e-3;
+    const double YA1 = 0.003323, YA2 = 0.971832, YA3 = 0.926148e-5, YA4 = 3.10165, YB0 = -1.7630, YB1 = 1.43175,
+                 YB2 = 0.315463, YC1 = 0.036666667, YC2 = 0.983333333, YAL = 0.143139e2, YBE = 0.6624e0;
+    const double t0 = temp / z0p43;
+    const double r0 = rho / (z0 * am);
+    const double lt0 = plog(t0), lr0 = plog(r0);
+    const double ytf = t0 / (1.0 + t0);
+    const double ya = YA1 * pexp(YA2 * lt0) + YA3 * pexp(YA4 * lt0);
+    const double yb = -pexp(YB0 + YB1 * ytf + YB2 * ytf * ytf);
+    const double yc = YC1 * ytf + YC2;
+    const double yq1 = ya * pexp(yb * lr0);
+    const double yq = ppow(pexp(yc * lr0) + ppow(yq1, yc), 1.0 / yc);
+    const double yx = YAL * ppow(yq, YBE);
+    w.Z = z0 * yx / (1.0 + yx + sqrt(1.0 + 2.0 * yx));
+  }
+  const double Z = w.Z;
+  const double Ne = w.ne = Z * dens / (am * C_AMU);
+  // ---- shared by getKappa and getGamma (both start with Te *= 11604.5; Ti *= 11604.5)
+  const double Te = temp_ev * 11604.5, Ti = ti_ev * 11604.5;
+  const double Ni = Ne / Z;
+  const double EF = C_HBAR * C_HBAR * ppow(3.0 * M_PI * M_PI * Ne, 2.0 / 3.0) / 2.0 / C_EMASS;       // fermi_E(Ne)
+  const double TF = 4.828648689433765e+22 * EF;
+  const double VF = 1.481734876966785e+15 * sqrt(EF);
+  const double r0n = ppow(3.0 / (4 * M_PI * Ni), 1.0 / 3.0);                                           // r0(Ni)
+  const double vth = sqrt(VF * VF + C_BOLTZMAN * Te / C_EMASS);                                        // numax's root
+  // coulomb_log(omega_las, Z, Ni, Te, la) = MAX(2, log(bMax/bMin))
+  const double NiZ = Ni * Z;
+  const double ft = 2.0 * (C_HBAR * C_HBAR * ppow(3.0 * M_PI * M_PI * NiZ, 2.0 / 3.0) / 2.0 / C_EMASS) / (3.0 * C_BOLTZMAN);
   const double teff = sqrt(Te * Te + ft * ft);
-  if (la) return DMAX(r0_(ni), sqrt(C_BOLTZMAN * teff / (C_EMASS)) / DMAX(omega_las, omega_pl(ni * Z)));
-  return DMAX(r0_(ni), sqrt(C_BOLTZMAN * teff / (C_EMASS)) / omega_pl(ni * Z));
-}
-__device__ double coulomb_log(double omega_las, double Z, double ni, double Te, int la)
-{
-  return DMAX(2.0, log(bMax(omega_las, Z, ni, Te, la) / bMin(Z, Te)));
-}
-__device__ double mean_charge(double temp, double rho, double z0, double am)
-{
-  temp *= 1e-3; rho *= 1e-3;
-  const double YA1 = 0.003323, YA2 = 0.971832, YA3 = 0.926148e-5, YA4 = 3.10165, YB0 = -1.7630, YB1 = 1.43175,
-               YB2 = 0.315463, YC1 = 0.036666667, YC2 = 0.983333333, YAL = 0.143139e2, YBE = 0.6624e0;
-  const double t0 = temp / pow(z0, 4. / 3.);
-  const double r0 = rho / (z0 * am);
-  const double ytf = t0 / (1.0 + t0);
-  const double ya = YA1 * pow(t0, YA2) + YA3 * pow(t0, YA4);
-  const double yb = -exp(YB0 + YB1 * ytf + YB2 * ytf * ytf);
-  const double yc = YC1 * ytf + YC2;
-  const double yq1 = ya * pow(r0, yb);
-  const double yq = pow(pow(r0, yc) + pow(yq1, yc), 1.0 / yc);
-  const double yx = YAL * pow(yq, YBE);
-  return z0 * yx / (1.0 + yx + sqrt(1.0 + 2.0 * yx));
-}
-__device__ __forceinline__ double numet(double A1, double A2, double Te, double Ti, double TF)
-{
-  return 1.309202957843054e+11 * (A1 * Ti + A2 * Te * Te / TF);
-}
-__device__ __forceinline__ double numax(double A3, double vf, double Te, double ni)
-{
-  return A3 / r0_(ni) * sqrt(vf * vf + C_BOLTZMAN * Te / C_EMASS);
-}
-__device__ double nupl(double omega_las, double Z, double ni, double ne, double Te, int la)
-{
-  const double coulomb = coulomb_log(omega_las, Z, ni, Te, la);
-  return 1.863839656495274e-40 * Z * ne * coulomb / pow(C_BOLTZMAN * Te, 1.5);
-}
-__device__ double get_gamma(double Te, double Ti, double Ne, double Z, double omega_laser, int la)
-{
-  Te *= 11604.5; Ti *= 11604.5;
-  const double A1g = 50, A2g = 20, A3g = 0.25, m_atom = 26.9815;
-  const double Ni = Ne / Z;
-  const double EF = fermi_E(Ne);
-  const double TF = 4.828648689433765e+22 * EF;
-  const double VF = 1.481734876966785e+15 * sqrt(EF);
-  const double nu_eff = DMIN(numet(A1g, A2g, Te, Ti, TF), DMIN(numax(A3g, VF, Te, Ni), nupl(omega_laser, Z, Ni, Ne, Te, la)));
-  return 2.783313120645740e-74 / (m_atom * C_AMU) * Ne * nu_eff;
-}
-__device__ double get_kappa(double Te, double Ti, double Ne, double Z, double omega_laser, int la)
-{
-  Te *= 11604.5; Ti *= 11604.5;
-  const double A1t = 2.95, A2t = 0.5, A3t = 0.16, A4t = 1.2;
-  const double Ni = Ne / Z;
-  const double EF = fermi_E(Ne);
-  const double TF = 4.828648689433765e+22 * EF;
-  const double VF = 1.481734876966785e+15 * sqrt(EF);
-  const double nu_eff = DMIN(numet(A1t, A2t, Te, Ti, TF), numax(A3t, VF, Te, Ni));
-  const double coulomb = coulomb_log(omega_laser, Z, Ni, Te, la);
-  const double kappa_met = 6.884236239621913e-16 * Ne * Te / nu_eff;
-  const double kappa_pl = 4.428788911416808e+43 * pow(C_BOLTZMAN * Te, 2.5) / Z / coulomb;
-  const double kappa_wr = kappa_pl + (kappa_met - kappa_pl) * exp(-A4t * Te / TF);
-  return kappa_wr * 0.073768115942029;
+  const double wpl = sqrt(NiZ * C_ECHARGE * C_ECHARGE / C_EMASS / C_ECONST);                           // omega_pl(Ni*Z)
+  const double vte = sqrt(C_BOLTZMAN * teff / (C_EMASS));
+  const double bmax = la ? DMAX(r0n, vte / DMAX(omega_las, wpl)) : DMAX(r0n, vte / wpl);
+  const double kTe = C_BOLTZMAN * Te;
+  const double bmin = DMAX(Z * C_ECHARGE * C_ECHARGE / kTe, C_HBAR / sqrt(2 * C_EMASS * C_BOLTZMAN * Te));
+  const double coulomb = DMAX(2.0, plog(bmax / bmin));
+  const double skTe = sqrt(kTe);
+  const double kTe15 = kTe * skTe, kTe25 = kTe * kTe * skTe;                                           // pow(kTe,1.5), pow(kTe,2.5)
+  // ---- getGamma
+  {
+    const double A1g = 50, A2g = 20, A3g = 0.25, m_atom = 26.9815;
+    const double numet = 1.309202957843054e+11 * (A1g * Ti + A2g * Te * Te / TF);
+    const double numax = A3g / r0n * vth;
+    const double nupl = 1.863839656495274e-40 * Z * Ne * coulomb / kTe15;
+    const double nu_eff = DMIN(numet, DMIN(numax, nupl));
+    w.gamma = 2.783313120645740e-74 / (m_atom * C_AMU) * Ne * nu_eff;
+  }
+  // ---- getKappa
+  {
+    const double A1t = 2.95, A2t = 0.5, A3t = 0.16, A4t = 1.2;
+    const double numet = 1.309202957843054e+11 * (A1t * Ti + A2t * Te * Te / TF);
+    const double numax = A3t / r0n * vth;
+    const double nu_eff = DMIN(numet, numax);
+    const double kappa_met = 6.884236239621913e-16 * Ne * Te / nu_eff;
+    const double kappa_pl = 4.428788911416808e+43 * kTe25 / Z / coulomb;
+    const double kappa_wr = kappa_pl + (kappa_met - kappa_pl) * pexp(-A4t * Te / TF);
+    w.kappa = kappa_wr * 0.073768115942029;
+  }
+  return w;
 }
 
 // ----------------------------------------------------------------------------- device state
@@ -231,6 +230,7 @@ struct TtmArgs {
   imdcu_ttm_params p;
   double timestep, fd_hx, fd_vol, neighvol, omega_laser, sigma_t_sq;
   EosView cve, ee;
+  int eos_smem, pad_;                // tables are staged into dynamic shared memory
   TCell *lat, *vlat;                 // [2][P*LD], [2][vlatdim]
   int *isum; double *dsum;           // slab sums, see k_ttm_atoms1
   double *xiarr, *xiloc, *vcom, *src_e;
@@ -338,7 +338,7 @@ k_ttm_atoms2(int n, int G, double fd_hx, double atomic_weight, const double4 *__
 }
 
 // ----------------------------------------------------------------------------- grid kernel
-#define TTM_NT 1024
+#define TTM_NT 256
 
 __device__ __forceinline__ bool active_gt(const TCell &c, int mn) { return c.natoms >= mn && c.dens > RHOMIN; }
 __device__ __forceinline__ bool active_ge(const TCell &c, int mn) { return c.natoms >= mn && c.dens >= RHOMIN; }
@@ -376,44 +376,47 @@ __device__ int block_reduce_int(int v, int op /*1 min, 2 max*/, int *s_red)
 }
 
 // wide-range properties of one cell (the body of do_FILLMESH's active branch / the vlattice loop)
-__device__ void fill_props(const TtmArgs &a, TCell &c, int la)
+__device__ __forceinline__ void fill_props(const TtmArgs &a, const EosView &cve, TCell &c, int la, double z0p43)
 {
-  c.Z = mean_charge(c.temp * 11604.5, c.dens, a.p.atomic_charge, a.p.atomic_weight);
-  c.ne = c.Z * c.dens / (a.p.atomic_weight * C_AMU);
-  c.Ce = eos_cve_from_r_te(a.cve, c.dens, c.temp * 11604.5);
-  c.fd_k = get_kappa(c.temp, c.md_temp, c.ne, c.Z, a.omega_laser, la);
-  c.fd_g = get_gamma(c.temp, c.md_temp, c.ne, c.Z, a.omega_laser, la);
+  const double ce = eos_cve_from_r_te(cve, c.dens, c.temp * 11604.5);
+  const WideRange w = wide_range(c.temp, c.md_temp, c.dens, a.p.atomic_charge, a.p.atomic_weight, z0p43,
+                                 a.omega_laser, la);
+  c.Z = w.Z; c.ne = w.ne; c.Ce = ce; c.fd_k = w.kappa; c.fd_g = w.gamma;
 }
 
-// do_FILLMESH (imd_ttm.c:629-852) for the calling thread's cells + the virtual lattice
-__device__ void fillmesh(const TtmArgs &a, TCell *l1, TCell *l2, TCell *v1, TCell *v2, int last_active,
-                         int rv, int la, int *err)
+// do_FILLMESH (imd_ttm.c:629-852) for the calling thread's cells + the virtual lattice.  Lattice
+// cells and virtual cells share ONE call site of fill_props, so a warp holding both kinds does
+// not run the expensive part twice.
+__device__ __forceinline__ void fillmesh(const TtmArgs &a, const EosView &cve, const EosView &ee, double z0p43,
+                                         TCell *l1, TCell *l2, TCell *v1, TCell *v2, int last_active,
+                                         int rv, int la, int *err)
 {
   const int ncell = a.P * a.L, mn = a.p.fd_min_atoms;
   for (int c = threadIdx.x; c < ncell + a.p.vlatdim; c += blockDim.x) {
-    if (c < ncell) {
-      if (c > last_active) continue;
-      const int idx = (c / a.L) * a.LD + (c % a.L) + 1;
-      TCell &x = l1[idx], &y = l2[idx];
-      if (active_gt(x, mn)) {
-        fill_props(a, x, la);
-        y.ne = x.ne; y.Ce = x.Ce; y.fd_k = x.fd_k; y.fd_g = x.fd_g;
-        if (x.Ce < 0 || isnan(x.Ce)) atomicMax(err, 1);
-        if (isnan(x.fd_k) || x.fd_k < 0) atomicMax(err, 2);
-        if (isnan(x.fd_g) || x.fd_g < 0) atomicMax(err, 3);
-        if (a.steps < 1) {                                                 // :765-807
-          x.U = eos_ee_from_r_te(a.ee, x.dens, x.temp * 11604.5) * 26.9815 * C_AMU * C_J2eV;
-          y.U = x.U;
-          const double echeck = eos_ee_from_r_te(a.ee, x.dens, x.temp * 11604.5) * 26.9815 * C_AMU * C_J2eV;
-          const double tcheck = eos_te_from_r_ee(a.ee, x.dens, echeck / 26.9815 / C_AMU * C_eV2J) / 11604.5;
-          const double tinit = x.temp;
-          if (DABS(tcheck - tinit) > tinit * 0.01) atomicMax(err, 4);
-        }
-      } else { x.fd_k = 0.0; x.fd_g = 0.0; x.Z = 0.0; x.ne = 0.0; x.Ce = 0.0; x.temp = 0.0; }
-    } else if (rv >= 0 && rv < a.P) {                                      // :825-845
-      const int i = c - ncell;
-      fill_props(a, v1[i], la);
-      v2[i].Z = v1[i].Z; v2[i].ne = v1[i].ne; v2[i].fd_k = v1[i].fd_k; v2[i].fd_g = v1[i].fd_g;
+    TCell *t = nullptr, *t2 = nullptr;
+    const bool virt = c >= ncell;
+    if (!virt) {
+      if (c <= last_active) {
+        const int idx = (c / a.L) * a.LD + (c % a.L) + 1;
+        if (active_gt(l1[idx], mn)) { t = &l1[idx]; t2 = &l2[idx]; }
+        else { TCell &x = l1[idx]; x.fd_k = 0.0; x.fd_g = 0.0; x.Z = 0.0; x.ne = 0.0; x.Ce = 0.0; x.temp = 0.0; }
+      }
+    } else if (rv >= 0 && rv < a.P) { t = &v1[c - ncell]; t2 = &v2[c - ncell]; }   // :825-845
+    if (!t) continue;
+    fill_props(a, cve, *t, la, z0p43);
+    TCell &x = *t, &y = *t2;
+    if (virt) { y.Z = x.Z; y.ne = x.ne; y.fd_k = x.fd_k; y.fd_g = x.fd_g; continue; }
+    y.ne = x.ne; y.Ce = x.Ce; y.fd_k = x.fd_k; y.fd_g = x.fd_g;
+    if (x.Ce < 0 || isnan(x.Ce)) atomicMax(err, 1);
+    if (isnan(x.fd_k) || x.fd_k < 0) atomicMax(err, 2);
+    if (isnan(x.fd_g) || x.fd_g < 0) atomicMax(err, 3);
+    if (a.steps < 1) {                                                     // :765-807
+      x.U = eos_ee_from_r_te(ee, x.dens, x.temp * 11604.5) * 26.9815 * C_AMU * C_J2eV;
+      y.U = x.U;
+      const double echeck = eos_ee_from_r_te(ee, x.dens, x.temp * 11604.5) * 26.9815 * C_AMU * C_J2eV;
+      const double tcheck = eos_te_from_r_ee(ee, x.dens, echeck / 26.9815 / C_AMU * C_eV2J) / 11604.5;
+      const double tinit = x.temp;
+      if (DABS(tcheck - tinit) > tinit * 0.01) atomicMax(err, 4);
     }
   }
 }
@@ -433,6 +436,7 @@ __device__ void fill_ghosts(const TtmArgs &a, TCell *l1)
 __global__ void __launch_bounds__(TTM_NT)
 k_ttm_grid(TtmArgs a)
 {
+  extern __shared__ double s_dyn[];
   __shared__ double s_red[32];
   __shared__ int s_ired[32];
   __shared__ int s_last_active, s_rv, s_substeps;
@@ -445,6 +449,30 @@ k_ttm_grid(TtmArgs a)
   TCell *v1 = a.vlat + vcur * a.p.vlatdim, *v2 = a.vlat + (1 - vcur) * a.p.vlatdim;
   const int *natomsg = a.isum, *totneigh = a.isum + G, *fluxl = a.isum + 2 * G, *fluxr = a.isum + 3 * G;
   int *err = &sc->err;
+  // EOS tables: staged into shared memory when they fit (the binary searches and the four corner
+  // loads of every interpolation are dependent loads on the critical path of each sub-step)
+  EosView cve = a.cve, ee = a.ee;
+  if (a.eos_smem) {
+    double *d = s_dyn;
+    EosView *vs[2] = { &cve, &ee };
+    for (int w = 0; w < 2; w++) {
+      EosView &v = *vs[w];
+      const int nd = v.nx + v.ny + v.nx * v.ny;
+      for (int k = threadIdx.x; k < nd; k += blockDim.x) d[k] = v.x[k];       // x | y | z are contiguous
+      v.x = d; v.y = d + v.nx; v.z = d + v.nx + v.ny;
+      d += nd;
+    }
+    unsigned char *b = reinterpret_cast<unsigned char *>(d);
+    for (int w = 0; w < 2; w++) {
+      EosView &v = *vs[w];
+      const int ng = (v.nx - 1) * (v.ny - 1);
+      for (int k = threadIdx.x; k < ng; k += blockDim.x) b[k] = v.diag[k];
+      v.diag = b;
+      b += (ng + 7) & ~7;
+    }
+    __syncthreads();
+  }
+  const double z0p43 = pow(a.p.atomic_charge, 4. / 3.);                       // MeanCharge's pow(z0, 4/3)
 
   // ---------------------------------------------------------------- update_fd, grid part (:241-264, 341-363, 401-541)
   for (int r = threadIdx.x; r < P; r += blockDim.x) l1[r * LD].temp = l1[r * LD + L + 1].temp = 0;
@@ -514,7 +542,7 @@ k_ttm_grid(TtmArgs a)
         const double fl_g1 = g + 1 < G ? (double) fluxl[g + 1] : 0.0;
         const double fr_gm = g - 1 >= 0 ? (double) fluxr[g - 1] : 0.0;
         y.U = x.U * Nold / Nnew + 1.0 * (+fr_g * l1[idx + 1].U - fl_g1 * x.U + fl_g * l1[idx - 1].U - fr_gm * x.U) / Nnew;
-        if (active_gt(x, mn)) y.temp = eos_te_from_r_ee(a.ee, x.dens, y.U / (26.9815 * C_AMU * C_J2eV)) / 11604.5;
+        if (active_gt(x, mn)) y.temp = eos_te_from_r_ee(ee, x.dens, y.U / (26.9815 * C_AMU * C_J2eV)) / 11604.5;
       } else if (Nnew < 1) { y.U = 0.0; y.temp = 0.0; }
     }
     __syncthreads();
@@ -539,7 +567,7 @@ k_ttm_grid(TtmArgs a)
             x.temp = sqrt(e_nb / ((double) nn)); y.temp = x.temp;
             if (x.temp < a.p.Temin) y.temp = x.temp = x.md_temp;
           } else { x.temp = x.md_temp; y.temp = x.temp; }
-          x.U = y.U = eos_ee_from_r_te(a.ee, x.dens, x.temp * 11604.5) * 26.9815 * C_AMU * C_J2eV;
+          x.U = y.U = eos_ee_from_r_te(ee, x.dens, x.temp * 11604.5) * 26.9815 * C_AMU * C_J2eV;
         }
       }
     }
@@ -548,7 +576,7 @@ k_ttm_grid(TtmArgs a)
 
   // ---------------------------------------------------------------- do_FILLMESH, ghosts, CFL_maxdt (:103-108)
   int la = sc->laser_active;
-  fillmesh(a, l1, l2, v1, v2, last_active, rv, la, err);
+  fillmesh(a, cve, ee, z0p43, l1, l2, v1, v2, last_active, rv, la, err);
   __syncthreads();
   fill_ghosts(a, l1);
   __syncthreads();
@@ -644,7 +672,7 @@ k_ttm_grid(TtmArgs a)
     __syncthreads();
     cur = 1 - cur; vcur = 1 - vcur;
     { TCell *t = l1; l1 = l2; l2 = t; t = v1; v1 = v2; v2 = t; }
-    fillmesh(a, l1, l2, v1, v2, last_active, rv, la, err);
+    fillmesh(a, cve, ee, z0p43, l1, l2, v1, v2, last_active, rv, la, err);
     __syncthreads();
     fill_ghosts(a, l1);
     __syncthreads();
@@ -657,7 +685,7 @@ k_ttm_grid(TtmArgs a)
     TCell &x = l1[idx], &y = l2[idx];
     a.xiarr[c] = a.xiloc[idx];
     if (active_ge(x, mn)) {
-      x.U = eos_ee_from_r_te(a.ee, x.dens, x.temp * 11604.5) * 26.9815 * C_AMU * C_J2eV;
+      x.U = eos_ee_from_r_te(ee, x.dens, x.temp * 11604.5) * 26.9815 * C_AMU * C_J2eV;
       y.U = x.U;
       eel += x.U * ((double) x.natoms);
     }
@@ -832,7 +860,20 @@ int imdcu_ttm_step(imdcu_ctx *c, int steps, double out16[16])
   int nt = ((a.ncell_tot + 31) / 32) * 32;
   if (nt > TTM_NT) nt = TTM_NT;
   if (nt < 32) nt = 32;
-  k_ttm_grid<<<1, nt, 0, st>>>(a);
+  // dynamic shared memory for the two EOS tables (axes, values, diagonal flags)
+  size_t smem = 0;
+  for (int w = 0; w < 2; w++) {
+    const size_t nx = t.eos_nx[w], ny = t.eos_ny[w];
+    smem += (nx + ny + nx * ny) * sizeof(double) + (((nx - 1) * (ny - 1) + 7) & ~(size_t) 7);
+  }
+  a.eos_smem = smem <= 200 * 1024;
+  a.pad_ = 0;
+  if (!a.eos_smem) smem = 0;
+  if (smem != t.grid_smem_set) {
+    CU_CHECK(c, cudaFuncSetAttribute(k_ttm_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    t.grid_smem_set = smem;
+  }
+  k_ttm_grid<<<1, nt, smem, st>>>(a);
   c->count_launch();
   CU_CHECK(c, cudaGetLastError());
   if (out16) return ttm_read_scalars(c, out16);

@@ -1,0 +1,108 @@
+// imd_b200/csrc/ttm_math.cuh -- branch-free FP64 log / exp / pow for the FD-lattice kernel.
+//
+// The wide-range models of do_FILLMESH (imd_ttm.c:2191-2399) are a chain of ~18 pow() calls per
+// FD cell and sub-step, evaluated by very few threads: k_ttm_grid is a latency chain, not a
+// throughput kernel.  libdevice's pow() costs ~250 dependent instructions and its special-case
+// branches stop ptxas from interleaving independent calls.  These versions are straight-line
+// code (every operation explicit, fma() spelled out because ttm.cu is compiled -fmad=false), so
+// the independent calls of one cell are scheduled into each other's latency shadows.
+//
+// Domain: x > 0, finite and normal; |y log x| < 700.  Outside it the result is NaN (log) or
+// saturates (exp) -- do_FILLMESH then raises the same "NaN" errors as the reference.
+// Accuracy (checked on the host against libm, tests/test_ttm_math_cpu.py): pexp <= 1 ulp, plog <= 2 ulp
+// on their own; ppow(x, y) relative error <= 2^-51 * (1 + |y log x|), i.e. ~1e-14 for the
+// arguments met here -- far inside the 1e-10 parity tolerance of the FD-cell fields.
+#pragma once
+
+#if defined(__CUDACC__)
+#define TM_HD __host__ __device__ __forceinline__
+#else
+#define TM_HD static inline
+#endif
+
+#if defined(__CUDA_ARCH__)
+#define TM_D2LL(x) __double_as_longlong(x)
+#define TM_LL2D(x) __longlong_as_double(x)
+#define TM_FMA(a, b, c) fma((a), (b), (c))
+#define TM_RINT(x) rint(x)
+#else
+#include <cmath>
+#include <cstring>
+static inline long long TM_D2LL(double x) { long long r; memcpy(&r, &x, 8); return r; }
+static inline double TM_LL2D(long long x) { double r; memcpy(&r, &x, 8); return r; }
+#define TM_FMA(a, b, c) std::fma((a), (b), (c))
+#define TM_RINT(x) std::nearbyint(x)
+#endif
+
+// natural logarithm, x normal positive.  m in [sqrt(1/2), sqrt(2)), f = (m-1)/(m+1),
+// log m = 2 atanh f = 2f + 2f^3/3 + ... ; the quotient is refined once so that f carries
+// (almost) no rounding error of its own.
+TM_HD double plog(double x)
+{
+  const long long ix = TM_D2LL(x);
+  int e = (int) (ix >> 52) - 1023;
+  double m = TM_LL2D((ix & 0x000fffffffffffffLL) | 0x3ff0000000000000LL);       // [1, 2)
+  const bool up = m > 1.4142135623730951;
+  m = up ? m * 0.5 : m;
+  e = up ? e + 1 : e;
+  const double num = m - 1.0, den = m + 1.0;                                       // num exact
+  double f = num / den;
+  // residual of the quotient: num - f*den, with den = m + 1 exact to 1 rounding (err <= 2^-53)
+  const double r = TM_FMA(-f, den, num);
+  const double fl = r / den;                                                       // tail of f
+  const double f2 = f * f;
+  double p = 2.0 / 23.0;
+  p = TM_FMA(p, f2, 2.0 / 21.0);
+  p = TM_FMA(p, f2, 2.0 / 19.0);
+  p = TM_FMA(p, f2, 2.0 / 17.0);
+  p = TM_FMA(p, f2, 2.0 / 15.0);
+  p = TM_FMA(p, f2, 2.0 / 13.0);
+  p = TM_FMA(p, f2, 2.0 / 11.0);
+  p = TM_FMA(p, f2, 2.0 / 9.0);
+  p = TM_FMA(p, f2, 2.0 / 7.0);
+  p = TM_FMA(p, f2, 2.0 / 5.0);
+  p = TM_FMA(p, f2, 2.0 / 3.0);
+  const double de = (double) e;
+  // log x = e ln2_hi + 2f + (f f2 p + 2 fl + e ln2_lo)
+  const double ln2_hi = 6.93147180369123816490e-01, ln2_lo = 1.90821492927058770002e-10;
+  const double tail = TM_FMA(f * f2, p, TM_FMA(de, ln2_lo, 2.0 * fl));
+  const double res = TM_FMA(de, ln2_hi, 2.0 * f) + tail;
+  const bool ok = (ix > 0x000fffffffffffffLL) && (ix < 0x7ff0000000000000LL);   // positive, normal, finite
+  return ok ? res : TM_LL2D(0x7ff8000000000000LL);
+}
+
+// e^x, |x| < 700 (clamped beyond: the models never get there with finite inputs)
+TM_HD double pexp(double x)
+{
+  const bool isn = !(x == x);
+  x = x < -700.0 ? -700.0 : x;
+  x = x > 700.0 ? 700.0 : x;
+  const double k = TM_RINT(x * 1.4426950408889634);
+  const double ln2_hi = 6.93147180369123816490e-01, ln2_lo = 1.90821492927058770002e-10;
+  double r = TM_FMA(-k, ln2_hi, x);
+  r = TM_FMA(-k, ln2_lo, r);                                                       // |r| <= 0.3466
+  double p = 1.0 / 87178291200.0;                                                  // 1/14!
+  p = TM_FMA(p, r, 1.0 / 6227020800.0);
+  p = TM_FMA(p, r, 1.0 / 479001600.0);
+  p = TM_FMA(p, r, 1.0 / 39916800.0);
+  p = TM_FMA(p, r, 1.0 / 3628800.0);
+  p = TM_FMA(p, r, 1.0 / 362880.0);
+  p = TM_FMA(p, r, 1.0 / 40320.0);
+  p = TM_FMA(p, r, 1.0 / 5040.0);
+  p = TM_FMA(p, r, 1.0 / 720.0);
+  p = TM_FMA(p, r, 1.0 / 120.0);
+  p = TM_FMA(p, r, 1.0 / 24.0);
+  p = TM_FMA(p, r, 1.0 / 6.0);
+  p = TM_FMA(p, r, 0.5);
+  p = TM_FMA(p, r, 1.0);
+  p = TM_FMA(p, r, 1.0);
+  // scale by 2^k in two exact steps (k in [-1010, 1010])
+  const int ki = (int) k;
+  const int k1 = ki / 2, k2 = ki - k1;
+  const double s1 = TM_LL2D((long long) (k1 + 1023) << 52), s2 = TM_LL2D((long long) (k2 + 1023) << 52);
+  const double res = p * s1 * s2;
+  return isn ? x : res;
+}
+
+// x^y for x > 0
+TM_HD double ppow(double x, double y) { return pexp(y * plog(x)); }
