@@ -428,6 +428,170 @@ def our_arm(args, rank, local_rank, world):
     return 0
 
 
+# ----------------------------------------------------------------------------- 3-D TTM sweep (configs[4])
+
+def ttm3d_reference_sample(n, sweeps, nproc):
+    """nproc concurrent runs of oracle/_ref/ref3d_diff (the reference's do_DIFF + ttm_fill_ghost_layers,
+    one rank each; imd_ttm_3D.c has no parallel driver that runs here) on an n^3 lattice."""
+    from oracle import ttm3d_np as t3
+    exe = os.path.join(ROOT, "oracle", "_ref", "ref3d_diff")
+    if not os.path.exists(exe):
+        return None
+    work = tempfile.mkdtemp(prefix="imdbench_t3_")
+    try:
+        f = t3.make_case((n, n, n), seed=1, hole=False, pbc=(0, 1, 1))
+        with open(os.path.join(work, "in.bin"), "wb") as o:
+            np.array([n, n, n, 20, 250, 1, sweeps, 0, 1, 1, 0, 0], np.int32).tofile(o)
+            np.array([16.0, 16.0, 16.0, 0.1 / 250]).tofile(o)
+            for k in t3.FIELDS:
+                np.ascontiguousarray(f[k], dtype=np.float64).tofile(o)
+        env = dict(os.environ, SHMPI_NP="1", SHMPI_RING_MB="64")
+        t0 = time.perf_counter()
+        procs = [subprocess.Popen([exe, "in.bin", "out%d.bin" % p], cwd=work, env=env, stdout=subprocess.PIPE,
+                                  stderr=subprocess.STDOUT, text=True) for p in range(nproc)]
+        outs = [p.communicate()[0] for p in procs]
+        wall = time.perf_counter() - t0
+        rate = 0.0
+        for o, p in zip(outs, procs):
+            m = re.search(r"ref3d: (\d+) sweeps of (\d+) cells in ([0-9.eE+-]+) s", o)
+            if p.returncode != 0 or not m:
+                raise RuntimeError("ref3d_diff failed: " + o[-500:])
+            rate += int(m.group(1)) * int(m.group(2)) / float(m.group(3))
+        return {"value": rate, "nproc": nproc, "wall_s": wall,
+                "sample": "%d concurrent single-rank runs of the reference's do_DIFF + ttm_fill_ghost_layers "
+                          "(oracle/_ref/ref3d_diff, imd_ttm_3D.c compiled -O2), %d^3 cells, %d sweeps each (%.1f s wall)"
+                          % (nproc, n, sweeps, wall)}
+    finally:
+        shutil.rmtree(work, ignore_errors=True)
+
+
+def ttm3d_arm(args, rank, local_rank, world):
+    """BASELINE.json configs[4]: standalone 3-D TTM electron-temperature diffusion sweep, cell-updates/s.
+    One step = one sweep { do_DIFF; ttm_fill_ghost_layers } over the lattice; N GPUs = N replicas of the
+    lattice (the sweep of one lattice does not shard in this round: replicas only)."""
+    metric, unit = "TTM-3D cell-updates/s", "cell-updates/s"
+    nx, ny, nz = args.grid
+    cfg = {"workload": "3-D TTM diffusion sweep (do_DIFF + ttm_fill_ghost_layers), %dx%dx%d FD cells, film with "
+                       "vacuum front (1/8 inactive), pbc 0 1 1 (BASELINE.json configs[4])" % (nx, ny, nz),
+           "cells": nx * ny * nz, "l2_policy": "inputs larger than L2 (11 fields x %.1f GB)" % (nx * ny * nz * 8 / 1e9),
+           "parallelism": "1 GPU" if world == 1 else "%d independent replicas" % world}
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        r = ttm3d_reference_sample(128, max(2, min(args.steps, 10)), max(1, host_cores()))
+        base = {"metric": metric, "unit": unit, "impl": "reference", "n_gpus": args.gpus, "steps": args.steps,
+                "warmup": args.warmup, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+                "data": "synthetic", "config": cfg}
+        if r is None:
+            base["unavailable"] = "oracle/_ref/ref3d_diff not built"
+        else:
+            base.update({"value": r["value"], "ms_per_step": None,
+                         "cpu_baseline": {"value": r["value"], "unit": unit, "cores": r["nproc"], "kind": "reference",
+                                          "sample": r["sample"]},
+                         "e2e": {"value": r["value"], "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                         "gpu_launches": 0})
+        print(json.dumps(base))
+        return 0
+    import torch
+    import torch.distributed as dist
+    from imd_b200 import capi
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product path has no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    ctx = capi.Context(local_rank)
+    e = (nx + 2, ny + 2, nz + 2)
+    rng = np.random.default_rng(7 + rank)
+    nat = np.full(e, 60, np.int32)
+    nat[: max(1, nx // 8)] = 3
+    temp = (0.05 + 0.5 * rng.random(e, dtype=np.float32)).astype(np.float64)
+    fd_k = (10.0 + 20.0 * rng.random(e, dtype=np.float32)).astype(np.float64)
+    const = lambda v: np.full(e, v)                                                    # noqa: E731
+    ctx.ttm3d_init((nx, ny, nz), (16.0, 16.0, 16.0), (0, 1, 1), 20)
+    ctx.ttm3d_upload(natoms=nat, temp=temp, fd_k=fd_k, fd_g=const(3e-4), Ce=const(2.5e-3), md_temp=const(0.03),
+                     source=const(1e-4), U=const(1.0), xi=const(0.0), dens=const(2700.0))
+    del fd_k, nat
+    ctx.ttm3d_fill_ghost_layers()
+    tau = 0.1 / 250
+    stream = torch.cuda.ExternalStream(ctx.stream, device=local_rank)
+
+    def barrier():
+        ctx.synchronize()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ctx.ttm3d_diff(tau, 250, 1, args.warmup, want_eabs=False)
+    barrier()
+    l0 = ctx.launch_count
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    ctx.ttm3d_diff(tau, 250, 1, args.steps, want_eabs=False)
+    ev1.record(stream)
+    barrier()
+    clocks = sampler.stop()
+    launches = ctx.launch_count - l0
+    t = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    cells = nx * ny * nz
+    value = cells * world * args.steps / (ms * 1e-3)
+    # end to end with host buffers: upload Te, one sweep, download Te (pinned)
+    ht = torch.from_numpy(temp).pin_memory()
+    hn = ht.numpy()
+    ke = max(1, min(args.steps, args.e2e_steps, 5))
+    L = ctx.L
+    for _ in range(1):
+        ctx.ttm3d_upload(temp=hn); ctx.ttm3d_diff(tau, 250, 1, 1); L.imdcu_ttm3d_download(ctx.h, None, capi._dp(hn), None, None)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(ke):
+        ctx.ttm3d_upload(temp=hn)
+        ctx.ttm3d_diff(tau, 250, 1, 1)
+        L.imdcu_ttm3d_download(ctx.h, None, capi._dp(hn), None, None)
+    barrier()
+    dt = time.perf_counter() - t0
+    t = torch.tensor([dt], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = cells * world * ke / float(t.item())
+    # kernel-only time of k_ttm3d_diff (phase 7)
+    ctx.set_profiling(True)
+    ctx.ttm3d_diff(tau, 250, 1, args.profile_steps, want_eabs=False)
+    ms_ph, ln_ph = ctx.phase_times()
+    ctx.set_profiling(False)
+    k_ms = ms_ph["ttm"] / max(1, ln_ph["ttm"])
+    peak, peak_src = measured_peak_gbs()
+    alg = 108 * cells
+    ach = alg / (k_ms * 1e-3) / 1e9
+    roofline = {"kernel": "k_ttm3d_diff", "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                "traffic": None, "peak_source": peak_src, "alg_bytes_per_launch": alg, "ms_per_launch": k_ms,
+                "note": "108 B per cell update: 4 + 10 x 8 read, 3 x 8 written (SURVEY 8d)"}
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            r = ttm3d_reference_sample(128, 5, max(1, host_cores()))
+            if r:
+                cpu = {"value": r["value"], "unit": unit, "cores": r["nproc"], "kind": "reference", "sample": r["sample"]}
+        except Exception as ex:
+            cpu = {"value": None, "unit": unit, "cores": 0, "kind": "reference", "sample": "failed: %s" % ex}
+    if rank == 0:
+        print(json.dumps({"metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps,
+                          "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+                          "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cfg, "clocks": clocks,
+                          "e2e": {"value": e2e_value, "unit": unit, "h2d_bytes_per_step": int(np.prod(e)) * 8,
+                                  "d2h_bytes_per_step": int(np.prod(e)) * 8, "steps": ke},
+                          "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}))
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -440,11 +604,16 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ttm", action="store_true", help="EAM + TTM step (BASELINE.json configs[2])")
     ap.add_argument("--ttm-substeps", type=int, default=250, help="fd_n_timesteps (manual example: 250)")
+    ap.add_argument("--workload", default="md", choices=["md", "ttm3d"],
+                    help="md: EAM(+TTM) atom-steps/s (headline); ttm3d: standalone 3-D TTM sweep (configs[4])")
+    ap.add_argument("--grid", type=int, nargs=3, default=[512, 512, 512], help="FD cells for --workload ttm3d")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.workload == "ttm3d":
+        return ttm3d_arm(args, rank, local_rank, world)
     if args.impl == "reference":
         return reference_arm(args, rank, world)
     return our_arm(args, rank, local_rank, world)

@@ -82,6 +82,11 @@ def load():
         "imdcu_move_atoms_ttm": (C.c_int, [vp, c_dp, c_ip]),
         "imdcu_run_ttm": (C.c_int, [vp, C.c_int, C.c_int, c_dp]),
         "imdcu_download_ttm": (C.c_int, [vp, c_dp, c_dp, c_dp, c_dp]),
+        "imdcu_ttm3d_init": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, c_dp, c_ip, C.c_int]),
+        "imdcu_ttm3d_upload": (C.c_int, [vp, c_ip, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp]),
+        "imdcu_ttm3d_diff": (C.c_int, [vp, C.c_double, C.c_int, C.c_int, C.c_int, c_dp]),
+        "imdcu_ttm3d_fill_ghost_layers": (C.c_int, [vp]),
+        "imdcu_ttm3d_download": (C.c_int, [vp, c_ip, c_dp, c_dp, c_dp]),
         "imdcu_get_cell_grid": (C.c_int, [vp, c_ip, c_dp]),
         "imdcu_get_nblist_pairs": (C.c_int, [vp, c_lp, c_ip]),
         "imdcu_nbl_count": (C.c_int, [vp]),
@@ -266,6 +271,42 @@ class Context:
         self._ck(self.L.imdcu_download_ttm(self.h, _dp(cells), _dp(xi), _dp(vcom), _dp(vlat)))
         d = {k: cells[:, i].copy() for i, k in enumerate(TTM_FIELDS)}
         return dict(fields=d, xiarr=xi, vcom=vcom, vlat=vlat[:nv])
+
+    # ---- 3-D TTM lattice sweep (imd_ttm_3D.c); arrays are the extended lattice (nx+2, ny+2, nz+2)
+    T3_FIELDS = ("natoms", "temp", "fd_k", "fd_g", "Ce", "md_temp", "source", "U", "xi", "dens")
+
+    def ttm3d_init(self, shape, h, pbc, fd_min_atoms):
+        self._t3_shape = tuple(int(v) + 2 for v in shape)
+        hh = np.ascontiguousarray(h, np.float64); pp = np.ascontiguousarray(pbc, np.int32)
+        self._ck(self.L.imdcu_ttm3d_init(self.h, int(shape[0]), int(shape[1]), int(shape[2]), _dp(hh), _ip(pp),
+                                         int(fd_min_atoms)))
+
+    def ttm3d_upload(self, **fields):
+        args = []
+        for k in self.T3_FIELDS:
+            a = fields.get(k)
+            if a is not None:
+                a = np.ascontiguousarray(a, np.int32 if k == "natoms" else np.float64)
+                if a.shape != self._t3_shape:
+                    raise ValueError("ttm3d field %s has shape %s, expected the extended lattice %s" % (k, a.shape, self._t3_shape))
+            args.append(a)
+        self._ck(self.L.imdcu_ttm3d_upload(self.h, _ip(args[0]), *[_dp(a) for a in args[1:]]))
+
+    def ttm3d_diff(self, tau, diff_substeps, laser_active, nsweeps, want_eabs=True):
+        e = np.zeros(1)
+        self._ck(self.L.imdcu_ttm3d_diff(self.h, float(tau), int(diff_substeps), int(bool(laser_active)), int(nsweeps),
+                                         _dp(e) if want_eabs else None))
+        return float(e[0])
+
+    def ttm3d_fill_ghost_layers(self):
+        self._ck(self.L.imdcu_ttm3d_fill_ghost_layers(self.h))
+
+    def ttm3d_download(self, fields=("natoms", "temp", "U", "xi")):
+        sh = self._t3_shape
+        out = {k: np.empty(sh, np.int32 if k == "natoms" else np.float64) for k in fields}
+        g = out.get
+        self._ck(self.L.imdcu_ttm3d_download(self.h, _ip(g("natoms")), _dp(g("temp")), _dp(g("U")), _dp(g("xi"))))
+        return out
 
     # ---- inspection
     def cell_grid(self):

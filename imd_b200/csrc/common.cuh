@@ -160,6 +160,18 @@ struct TtmState {
   void  *h_scal = nullptr;          // pinned mirror
 };
 
+// ----------------------------------------------------------------------------- TTM (3-D sweep, ttm3d.cu)
+struct Ttm3dState {
+  bool   inited = false;
+  int    nx = 0, ny = 0, nz = 0, pbc[3] = {0, 0, 0}, fd_min_atoms = 0;
+  double h[3] = {0, 0, 0};
+  long long pz = 0, py = 0, total = 0;          // pitches and size of one field (elements)
+  int    cur = 0;                                // which temp buffer is l1
+  DevBuf<int>    natoms;
+  DevBuf<double> temp[2], fd_k, fd_g, Ce, md_temp, source, U, xi, dens, partials;
+  double *d_eabs = nullptr;
+};
+
 // ----------------------------------------------------------------------------- context
 struct imdcu_ctx {
   int          device = 0;
@@ -222,6 +234,7 @@ struct imdcu_ctx {
   int *h_flags = nullptr;                    // pinned
 
   TtmState ttm;
+  Ttm3dState ttm3d;
 
   // multi-GPU (x-slab decomposition, multi.cu); nranks == 1: everything below is unused
   struct Comm {
@@ -293,6 +306,7 @@ __device__ __host__ inline int imdcu_combine_code(int pc, int code)
   return (pc % 3 - 1 + code % 3 - 1 + 1) + 3 * ((pc / 3) % 3 - 1 + (code / 3) % 3 - 1 + 1) + 9 * (pc / 9 - 1 + code / 9 - 1 + 1);
 }
 void imdcu_ttm_release(imdcu_ctx *ctx);                                // ttm.cu
+void imdcu_ttm3d_release(imdcu_ctx *ctx);                              // ttm3d.cu
 TabView imdcu_tab_view(const DevTable &t);
 
 static inline int div_up(int64_t a, int64_t b) { return (int) ((a + b - 1) / b); }

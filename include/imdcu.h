@@ -157,6 +157,31 @@ int  imdcu_run_ttm(imdcu_ctx *ctx, int first_step, int nsteps, double *energies)
  * This is what ttm_writeout (imd_ttm.c:1683) needs on the host. */
 int  imdcu_download_ttm(imdcu_ctx *ctx, double *cells, double *xiarr, double *vcom, double *vlat);
 
+/* ------------------------------------------------------------------ 3-D TTM lattice sweep */
+/* The 3-D variant of the FD step (imd_ttm_3D.c; BASELINE.json configs[4]).  The lattice lives on
+ * the device as SoA fields of ttm_Element (types.h:441-492).  All host arrays are the EXTENDED
+ * lattice (nx+2)*(ny+2)*(nz+2), z fastest, exactly l1[i][j][k] with its ghost layer.
+ * imdcu_ttm3d_init  : the lattice set-up of init_ttm (imd_ttm_3D.c:1040-1083): interior size,
+ *                     fd_h, pbc_dirs, fd_min_atoms.  Needs only imdcu_create.
+ * imdcu_ttm3d_upload: fills both lattices (l1, l2) from host fields; NULL leaves a field as is.
+ * imdcu_ttm3d_diff  : nsweeps x { do_DIFF(tau) (imd_ttm_3D.c:1603-1829); ttm_fill_ghost_layers()
+ *                     (:3314-3504) } = the FD sub-step loop of calc_ttm (:193-200) with the
+ *                     wide-range properties frozen.  diff_substeps enters xi_fac (:1614).  Open
+ *                     directions get ghost natoms = 0 (the reference's surface-rank branch).
+ *                     *Eabs (may be NULL) = Eabs_local accumulated since init (:1648-1652).
+ * imdcu_ttm3d_fill_ghost_layers: ttm_fill_ghost_layers() on l1 alone, as calc_ttm calls it ahead of
+ *                     the sub-step loop (:67); uploaded ghost values are otherwise used as given.
+ * imdcu_ttm3d_download: natoms / temp / U / xi of l1 (any may be NULL). */
+int  imdcu_ttm3d_init(imdcu_ctx *ctx, int nx, int ny, int nz, const double h[3], const int pbc[3],
+                      int fd_min_atoms);
+int  imdcu_ttm3d_upload(imdcu_ctx *ctx, const int *natoms, const double *temp, const double *fd_k,
+                        const double *fd_g, const double *Ce, const double *md_temp,
+                        const double *source, const double *U, const double *xi, const double *dens);
+int  imdcu_ttm3d_diff(imdcu_ctx *ctx, double tau, int diff_substeps, int laser_active, int nsweeps,
+                      double *Eabs);
+int  imdcu_ttm3d_fill_ghost_layers(imdcu_ctx *ctx);
+int  imdcu_ttm3d_download(imdcu_ctx *ctx, int *natoms, double *temp, double *U, double *xi);
+
 /* ------------------------------------------------------------------ inspection (parity) */
 /* geometry chosen by imdcu_set_box: global_cell_dim and cellsz */
 int  imdcu_get_cell_grid(const imdcu_ctx *ctx, int gdim[3], double *cellsz);

@@ -1,7 +1,7 @@
 /* oracle/ref3d_driver.c -- TEST INFRASTRUCTURE.  Drives the UNMODIFIED 3-D TTM functions of the
  * reference (imd_ttm_3D.c: do_DIFF :1603-1829, ttm_fill_ghost_layers :3314-3504,
  * ttm_create_mpi_datatypes :2972-3312) on a lattice read from a file, so that the 3-D stencil
- * restatement (ttm3d_oracle.c) and the CUDA kernel (imd_b200/csrc/ttm3d.cu) can be pinned to the
+ * restatement (ttm3d_np.py) and the CUDA kernel (imd_b200/csrc/ttm3d.cu) can be pinned to the
  * reference's own code.  imd_ttm_3D.c is an orphan source (not in the reference's Makefile) and
  * has no driver of its own; this file only supplies what init_ttm would have set up: the
  * globals, the two lattices and their pointer tables (same layout as :1066-1083).
@@ -17,6 +17,7 @@
  *          double[4] = { hx, hy, hz, tau }
  *          double[10][(nx+2)(ny+2)(nz+2)] = natoms, temp, fd_k, fd_g, Ce, md_temp, source, U, xi, dens
  *          (extended lattice, z fastest; both lattices start from the same values)
+ * stdout : "ref3d: <nsweeps> sweeps of <cells> cells in <seconds> s" (the loop alone, for the CPU baseline)
  * out.bin: double[1] = Eabs_local; double[4][(nx+2)(ny+2)(nz+2)] = natoms, temp, U, xi of l1
  *          after nsweeps x { do_DIFF(tau); ttm_fill_ghost_layers(); }
  */
@@ -90,10 +91,13 @@ int main(int argc, char **argv)
   }
   fclose(in);
   ttm_create_mpi_datatypes();
+  const double t0 = MPI_Wtime();
   for (s = 0; s < hd[6]; s++) {
     do_DIFF(hv[3]);
     ttm_fill_ghost_layers();
   }
+  const double t1 = MPI_Wtime();
+  printf("ref3d: %d sweeps of %ld cells in %.6f s\n", (int) hd[6], (long) hd[0] * hd[1] * hd[2], t1 - t0);
   FILE *out = fopen(argv[2], "wb");
   if (!out) { perror(argv[2]); return 1; }
   fwrite(&Eabs_local, sizeof(double), 1, out);

@@ -16,27 +16,26 @@ AMU = 1.660539040200000e-27          # constants.h
 
 
 def fill_ghost_layers(f, pbc):
-    """ttm_fill_ghost_layers (:3314-3504) on one rank: x, then y, then z; the y planes carry the
-    x ghosts and the z planes the x and y ghosts (mpi_yplane_block / mpi_zplane_block span the
-    full extent of the earlier directions).  Transferred members: natoms, temp, fd_k (:2990-3006).
-    Non-periodic directions: ghost natoms = 0 over the interior of the face (:3384-3391)."""
+    """ttm_fill_ghost_layers (:3314-3504) on one rank.  Every plane type (mpi_xplane_block,
+    mpi_yplane_block, mpi_zplane_block, :3148-3312) spans only the INTERIOR of the other two
+    directions: faces are filled, edges and corners never (the 7-point stencil does not read
+    them).  Transferred members: natoms, temp, fd_k (:2990-3006).  Non-periodic direction: ghost
+    natoms = 0 over the face (:3384-3391) -- what the reference does on the surface ranks; its
+    single-rank y branch does nothing and its single-rank z branch blocks in MPI_Recv
+    (:3398-3451, :3467-3500), neither of which is restated."""
     nat, temp, k = f["natoms"], f["temp"], f["fd_k"]
     for ax in range(3):
-        def sl(i, interior_only):
-            s = [slice(None)] * 3
-            for a in range(3):
-                if a == ax:
-                    s[a] = i
-                elif interior_only or a > ax:
-                    s[a] = slice(1, -1)
+        def sl(i):
+            s = [slice(1, -1)] * 3
+            s[ax] = i
             return tuple(s)
         if pbc[ax]:
             for a in (nat, temp, k):
-                a[sl(-1, False)] = a[sl(1, False)]
-                a[sl(0, False)] = a[sl(-2, False)]
+                a[sl(-1)] = a[sl(1)]
+                a[sl(0)] = a[sl(-2)]
         else:
-            nat[sl(0, True)] = 0
-            nat[sl(-1, True)] = 0
+            nat[sl(0)] = 0
+            nat[sl(-1)] = 0
 
 
 def diff_sweep(f, h, tau, fd_min_atoms, diff_substeps, laser_active):
