@@ -71,9 +71,24 @@ extern "C" int imdcu_run_ttm(imdcu_ctx *c, int first_step, int nsteps, double *e
   RET_IF(check_ready(c));
   double f8[8], m8[8], t16[16];
   int valid = 0;
+  if (!c->ttm.inited) return c->fail(IMDCU_EINVAL, "imdcu_ttm_init has not been called");
+  // calc_ttm runs between the two EAM passes and its lattice kernel beside pass 2 (same inputs and
+  // results as the sequential calc_forces; calc_ttm; only the schedule differs).  With per-phase
+  // profiling on, the sequential order is kept so that the phase times stay separable.
+  static const bool no_overlap = [] { const char *e = getenv("IMDCU_TTM_OVERLAP"); return e && e[0] == '0'; }();
+  const bool fuse = !c->profiling && !no_overlap;
   for (int s = 0; s < nsteps; s++) {
-    RET_IF(imdcu_calc_forces(c, first_step + s, energies ? f8 : nullptr));
-    RET_IF(imdcu_ttm_step(c, first_step + s, (s == nsteps - 1) ? t16 : nullptr));   // errors surface at the end
+    double *t_out = (s == nsteps - 1) ? t16 : nullptr;                    // errors surface at the end
+    if (fuse) {
+      c->fuse_ttm_steps = first_step + s;
+      const int rc = imdcu_calc_forces(c, first_step + s, energies ? f8 : nullptr);
+      c->fuse_ttm_steps = -1;
+      RET_IF(rc);
+      RET_IF(imdcu_ttm_join(c, t_out));
+    } else {
+      RET_IF(imdcu_calc_forces(c, first_step + s, energies ? f8 : nullptr));
+      RET_IF(imdcu_ttm_step(c, first_step + s, t_out));
+    }
     RET_IF(imdcu_integrate_ttm(c, m8, &valid));
     if (energies) { energies[2 * s] = f8[0]; energies[2 * s + 1] = m8[0]; }
   }

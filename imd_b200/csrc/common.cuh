@@ -137,6 +137,9 @@ struct EosView {
 struct TtmState {
   bool   inited = false;
   size_t grid_smem_set = 0;          // dynamic smem opted in for k_ttm_grid
+  cudaStream_t stream2 = nullptr;    // k_ttm_grid beside k_eam_pass2 (imdcu_ttm_fork / imdcu_ttm_join)
+  cudaEvent_t  ev_fork = nullptr, ev_join = nullptr;
+  bool   forked = false;
   imdcu_ttm_params p;
   int    G = 0, P = 1, L = 0, LD = 0;
   double fd_hx = 0, fd_vol = 0, neighvol = 0, omega_laser = 0, sigma_t_sq = 0;
@@ -186,6 +189,7 @@ struct imdcu_ctx {
   std::vector<double> restrictions;          // host copy
   DevBuf<double> d_restrictions;
   int    pdecay = 0; double xipdecay = 0, ramp_start = 0, ramp_end = 1;
+  int    fuse_ttm_steps = -1;                // >= 0: imdcu_eam_forces forks calc_ttm(steps) between its passes
   bool   box_set = false, params_set = false;
 
   Geom   geom;
@@ -306,6 +310,8 @@ __device__ __host__ inline int imdcu_combine_code(int pc, int code)
   return (pc % 3 - 1 + code % 3 - 1 + 1) + 3 * ((pc / 3) % 3 - 1 + (code / 3) % 3 - 1 + 1) + 9 * (pc / 9 - 1 + code / 9 - 1 + 1);
 }
 void imdcu_ttm_release(imdcu_ctx *ctx);                                // ttm.cu
+int  imdcu_ttm_fork(imdcu_ctx *ctx, int steps);                        // ttm.cu
+int  imdcu_ttm_join(imdcu_ctx *ctx, double out16[16]);
 void imdcu_ttm3d_release(imdcu_ctx *ctx);                              // ttm3d.cu
 TabView imdcu_tab_view(const DevTable &t);
 

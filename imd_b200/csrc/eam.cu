@@ -255,6 +255,13 @@ static int run_passes(imdcu_ctx *c, EamArgs &a, size_t smem1, size_t smem2)
     k_set_dF<<<div_up(a.n, 256), 256, 0, c->stream>>>(a.n, a.dF, a.pos4);
     c->count_launch();
   }
+  // calc_ttm overlapped with pass 2 (imdcu_run_ttm): numneighs of this step exist now; the lattice
+  // kernel goes to a second stream and pass 2 leaves one CTA slot of the machine to it
+  const bool fuse = c->fuse_ttm_steps >= 0;
+  if (fuse) {
+    RET_IF(imdcu_ttm_fork(c, c->fuse_ttm_steps));
+    if (g2 == c->num_sms * (g2 / c->num_sms) && g2 > c->num_sms) g2 -= 1;
+  }
   RET_IF(imdcu_refresh_ghosts(c, false));          // F' (and positions again) to the images
   {
     PhaseTimer pt(c, 5);
@@ -308,6 +315,7 @@ int imdcu_eam_forces(imdcu_ctx *c, double out8[8])
     RET_IF(rc);
   } else {
     CU_CHECK(c, cudaMemsetAsync(c->d_results, 0, 4 * sizeof(double), c->stream));
+    if (c->fuse_ttm_steps >= 0) RET_IF(imdcu_ttm_fork(c, c->fuse_ttm_steps));
     if (c->comm.nranks > 1) RET_IF(imdcu_refresh_ghosts(c, false));   // the neighbours still expect the F' exchange
   }
   RET_IF(imdcu_multi_allreduce(c, c->d_results, 3, 0));               // MPI_Allreduce of imd_forces_nbl.c:997-1016

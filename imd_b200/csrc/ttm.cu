@@ -790,6 +790,7 @@ extern "C" int imdcu_ttm_init(imdcu_ctx *c, const imdcu_ttm_params *p)
 
 void imdcu_ttm_release(imdcu_ctx *c)
 {
+  if (c->ttm.stream2) { cudaStreamDestroy(c->ttm.stream2); cudaEventDestroy(c->ttm.ev_fork); cudaEventDestroy(c->ttm.ev_join); c->ttm.stream2 = nullptr; }
   TtmState &t = c->ttm;
   for (int w = 0; w < 2; w++) { t.eos_buf[w].release(); t.eos_diag[w].release(); }
   t.lat.release(); t.vlat.release(); t.isum.release(); t.dsum.release(); t.xiarr.release(); t.xiloc.release();
@@ -818,12 +819,10 @@ static int ttm_read_scalars(imdcu_ctx *c, double out16[16])
   return IMDCU_OK;
 }
 
-// calc_ttm (imd_ttm.c:75-156)
-int imdcu_ttm_step(imdcu_ctx *c, int steps, double out16[16])
+// update_fd's atom loops and their reductions (imd_ttm.c:269-395), on the context's stream
+static int ttm_atoms_part(imdcu_ctx *c, int steps)
 {
   TtmState &t = c->ttm;
-  if (!t.inited) return c->fail(IMDCU_EINVAL, "imdcu_ttm_init has not been called");
-  PhaseTimer pt(c, 7);
   cudaStream_t st = c->stream;
   const int n = (int) c->n, G = t.G;
   if (t.fdi.cap < (size_t) n) {
@@ -848,6 +847,14 @@ int imdcu_ttm_step(imdcu_ctx *c, int steps, double out16[16])
     c->count_launch();
   }
   RET_IF(imdcu_multi_allreduce(c, t.dsum.p + 3 * (size_t) G, G, 0));   // imd_ttm.c:395
+  return IMDCU_OK;
+}
+
+// the G-sized rest of calc_ttm: one launch of k_ttm_grid on stream `st`
+static int ttm_grid_part(imdcu_ctx *c, int steps, cudaStream_t st)
+{
+  TtmState &t = c->ttm;
+  const int G = t.G;
   TtmArgs a;
   a.G = G; a.P = t.P; a.L = t.L; a.LD = t.LD; a.steps = steps; a.ncell_tot = t.P * t.L + t.p.vlatdim;
   a.p = t.p;
@@ -876,6 +883,49 @@ int imdcu_ttm_step(imdcu_ctx *c, int steps, double out16[16])
   k_ttm_grid<<<1, nt, smem, st>>>(a);
   c->count_launch();
   CU_CHECK(c, cudaGetLastError());
+  return IMDCU_OK;
+}
+
+// calc_ttm (imd_ttm.c:75-156)
+int imdcu_ttm_step(imdcu_ctx *c, int steps, double out16[16])
+{
+  TtmState &t = c->ttm;
+  if (!t.inited) return c->fail(IMDCU_EINVAL, "imdcu_ttm_init has not been called");
+  {
+    PhaseTimer pt(c, 7);
+    RET_IF(ttm_atoms_part(c, steps));
+    RET_IF(ttm_grid_part(c, steps, c->stream));
+  }
+  if (out16) return ttm_read_scalars(c, out16);
+  return IMDCU_OK;
+}
+
+// calc_ttm overlapped with the second EAM pass (used by imdcu_run_ttm): called between the passes,
+// after numneighs of this step exist.  The atom loops run on the context's stream; the lattice
+// kernel (one CTA, ~2 ms of dependent FP64 latency, imd_ttm.c:401-541 + :103-148) is forked to a
+// second stream and runs beside k_eam_pass2, which leaves one CTA slot free for it.
+int imdcu_ttm_fork(imdcu_ctx *c, int steps)
+{
+  TtmState &t = c->ttm;
+  if (!t.inited) return c->fail(IMDCU_EINVAL, "imdcu_ttm_init has not been called");
+  if (!t.stream2) {
+    CU_CHECK(c, cudaStreamCreateWithFlags(&t.stream2, cudaStreamNonBlocking));
+    CU_CHECK(c, cudaEventCreateWithFlags(&t.ev_fork, cudaEventDisableTiming));
+    CU_CHECK(c, cudaEventCreateWithFlags(&t.ev_join, cudaEventDisableTiming));
+  }
+  RET_IF(ttm_atoms_part(c, steps));
+  CU_CHECK(c, cudaEventRecord(t.ev_fork, c->stream));
+  CU_CHECK(c, cudaStreamWaitEvent(t.stream2, t.ev_fork, 0));
+  RET_IF(ttm_grid_part(c, steps, t.stream2));
+  CU_CHECK(c, cudaEventRecord(t.ev_join, t.stream2));
+  t.forked = true;
+  return IMDCU_OK;
+}
+
+int imdcu_ttm_join(imdcu_ctx *c, double out16[16])
+{
+  TtmState &t = c->ttm;
+  if (t.forked) { CU_CHECK(c, cudaStreamWaitEvent(c->stream, t.ev_join, 0)); t.forked = false; }
   if (out16) return ttm_read_scalars(c, out16);
   return IMDCU_OK;
 }

@@ -129,6 +129,76 @@ k_ttm3d_diff(T3Args a)
   }
 }
 
+// Direct variant: one thread per cell, no marching, no shared memory.  All loads of a cell (own fields
+// and the six neighbours' temp / fd_k / natoms) are independent and issued together; neighbour reuse
+// is left to L1 (z, y within the CTA's 32 x 4 x 4 brick) and L2 (the 126 MB L2 holds many x planes),
+// latency is hidden by 2048 resident threads per SM instead of by a software pipeline.  Same
+// arithmetic, same results; which variant runs is decided by measurement (profiles/).
+constexpr int T3D_BX = 32, T3D_BY = 4, T3D_BZ = 4;
+
+__global__ void __launch_bounds__(T3D_BX * T3D_BY * T3D_BZ, 2)
+k_ttm3d_diff_direct(T3Args a)
+{
+  __shared__ double s_red[T3D_BX * T3D_BY * T3D_BZ / 32];
+  const int k = blockIdx.x * T3D_BX + threadIdx.x + 1;
+  const int j = blockIdx.y * T3D_BY + threadIdx.y + 1;
+  const int i = blockIdx.z * T3D_BZ + threadIdx.z + 1;
+  const bool inside = k <= a.nz && j <= a.ny && i <= a.nx;
+  const int mn = a.fd_min_atoms;
+  double eabs = 0.0;
+  if (inside) {
+    const long long c = t3_idx(a, i, j, k);
+    const int nc = a.natoms[c];
+    const double tc = a.temp_in[c];
+    const double src = a.source[c];
+    if (a.laser_active) eabs = src * a.fd_vol * a.tau;
+    if (nc >= mn) {
+      const long long qxm = c - a.py, qxp = c + a.py, qym = c - a.pz, qyp = c + a.pz, qzm = c - 1, qzp = c + 1;
+      const int nxm = a.natoms[qxm], nxp = a.natoms[qxp], nym = a.natoms[qym], nyp = a.natoms[qyp],
+                nzm = a.natoms[qzm], nzp = a.natoms[qzp];
+      const double txm = a.temp_in[qxm], txp = a.temp_in[qxp], tym = a.temp_in[qym], typ = a.temp_in[qyp],
+                   tzm = a.temp_in[qzm], tzp = a.temp_in[qzp];
+      const double kc = a.fd_k[c];
+      const double kxm = a.fd_k[qxm], kxp = a.fd_k[qxp], kym = a.fd_k[qym], kyp = a.fd_k[qyp],
+                   kzm = a.fd_k[qzm], kzp = a.fd_k[qzp];
+      const double ce = a.Ce[c], g = a.fd_g[c], ti = a.md_temp[c], u = a.U[c], xi = a.xi[c], dens = a.dens[c];
+      const bool oxm = nxm >= mn, oxp = nxp >= mn, oym = nym >= mn, oyp = nyp >= mn, ozm = nzm >= mn, ozp = nzp >= mn;
+      const double xmaxTe = oxp ? txp : tc, xminTe = oxm ? txm : tc;
+      const double ymaxTe = oyp ? typ : tc, yminTe = oym ? tym : tc;
+      const double zmaxTe = ozp ? tzp : tc, zminTe = ozm ? tzm : tc;
+      const double xmaxk = oxp ? kxp : kc, xmink = oxm ? kxm : kc;
+      const double ymaxk = oyp ? kyp : kc, ymink = oym ? kym : kc;
+      const double zmaxk = ozp ? kzp : kc, zmink = ozm ? kzm : kc;
+      const double t2 = a.tau / ce *
+          ((((kc + xmaxk) / 2 * (xmaxTe - tc) * a.invxsq)
+            - ((kc + xmink) / 2 * (tc - xminTe) * a.invxsq)
+            + ((kc + ymaxk) / 2 * (ymaxTe - tc) * a.invysq)
+            - ((kc + ymink) / 2 * (tc - yminTe) * a.invysq)
+            + ((kc + zmaxk) / 2 * (zmaxTe - tc) * a.invzsq)
+            - ((kc + zmink) / 2 * (tc - zminTe) * a.invzsq))
+           - g * (tc - ti)
+           + src) + tc;
+      a.temp_out[c] = t2;
+      a.U[c] = u + (t2 - tc) * ce * a.fd_vol / ((double) nc);
+      a.xi[c] = xi + (t2 - ti) * a.xi_fac * g / ti / dens;
+    } else {
+      a.temp_out[c] = tc;
+    }
+  }
+  if (a.partials) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) eabs += __shfl_down_sync(0xffffffffu, eabs, o);
+    const int tid = (threadIdx.z * T3D_BY + threadIdx.y) * T3D_BX + threadIdx.x;
+    if ((tid & 31) == 0) s_red[tid >> 5] = eabs;
+    __syncthreads();
+    if (tid == 0) {
+      double s = 0.0;
+      for (int w = 0; w < T3D_BX * T3D_BY * T3D_BZ / 32; w++) s += s_red[w];
+      a.partials[(blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x] = s;
+    }
+  }
+}
+
 __global__ void k_ttm3d_sum(const double *__restrict__ partials, int n, double *__restrict__ eabs)
 {
   __shared__ double s[256];
@@ -297,16 +367,25 @@ extern "C" int imdcu_ttm3d_diff(imdcu_ctx *c, double tau, int diff_substeps, int
   a.invxsq = 1.0 / (t.h[0] * t.h[0]); a.invysq = 1.0 / (t.h[1] * t.h[1]); a.invzsq = 1.0 / (t.h[2] * t.h[2]);
   a.natoms = t.natoms.p; a.fd_k = t.fd_k.p; a.fd_g = t.fd_g.p; a.Ce = t.Ce.p; a.md_temp = t.md_temp.p;
   a.source = t.source.p; a.dens = t.dens.p; a.U = t.U.p; a.xi = t.xi.p;
-  // x chunk: enough CTAs for >= 4 waves of 148 SMs x 4 resident CTAs, at least 8 planes per CTA
-  const int gx = div_up(t.nz, T3_BX), gy = div_up(t.ny, T3_BY);
-  int chunk = t.nx;
-  const long long want = (long long) c->num_sms * 16;
-  if ((long long) gx * gy < want) {
-    const int nch = (int) std::min<long long>(div_up((int) want, gx * gy), std::max(1, t.nx / 8));
-    chunk = div_up(t.nx, std::max(1, nch));
+  // variant: IMDCU_TTM3D=tiled selects the 2.5-D shared-memory kernel, default is the direct one
+  static const bool tiled = [] { const char *e = getenv("IMDCU_TTM3D"); return e && !strcmp(e, "tiled"); }();
+  dim3 grid, block;
+  if (tiled) {
+    // x chunk: enough CTAs for >= 4 waves of 148 SMs x 4 resident CTAs, at least 8 planes per CTA
+    const int gx = div_up(t.nz, T3_BX), gy = div_up(t.ny, T3_BY);
+    int chunk = t.nx;
+    const long long want = (long long) c->num_sms * 16;
+    if ((long long) gx * gy < want) {
+      const int nch = (int) std::min<long long>(div_up((int) want, gx * gy), std::max(1, t.nx / 8));
+      chunk = div_up(t.nx, std::max(1, nch));
+    }
+    a.chunk = chunk;
+    grid = dim3(gx, gy, div_up(t.nx, chunk)); block = dim3(T3_BX, T3_BY);
+  } else {
+    a.chunk = 0;
+    grid = dim3(div_up(t.nz, T3D_BX), div_up(t.ny, T3D_BY), div_up(t.nx, T3D_BZ)); block = dim3(T3D_BX, T3D_BY, T3D_BZ);
+    if (grid.y > 65535 || grid.z > 65535) return c->fail(IMDCU_EINVAL, "imdcu_ttm3d_diff: lattice too large for the launch grid");
   }
-  a.chunk = chunk;
-  const dim3 grid(gx, gy, div_up(t.nx, chunk)), block(T3_BX, T3_BY);
   const int nblocks = (int) (grid.x * grid.y * grid.z);
   a.partials = nullptr;
   if (a.laser_active) { CU_CHECK(c, t.partials.ensure((size_t) nblocks)); a.partials = t.partials.p; }
@@ -314,7 +393,8 @@ extern "C" int imdcu_ttm3d_diff(imdcu_ctx *c, double tau, int diff_substeps, int
     a.temp_in = t.temp[t.cur].p; a.temp_out = t.temp[1 - t.cur].p;
     {
       PhaseTimer pt(c, 7);
-      k_ttm3d_diff<<<grid, block, 0, c->stream>>>(a);
+      if (tiled) k_ttm3d_diff<<<grid, block, 0, c->stream>>>(a);
+      else k_ttm3d_diff_direct<<<grid, block, 0, c->stream>>>(a);
       c->count_launch();
     }
     if (a.partials) { k_ttm3d_sum<<<1, 256, 0, c->stream>>>(t.partials.p, nblocks, t.d_eabs); c->count_launch(); }
