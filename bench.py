@@ -11,8 +11,8 @@ included whenever check_nblist asks for them.  Workload at N=1: BASELINE.json co
 
 value : whole-job atom-steps/s with atoms resident in HBM (device-timed, CUDA events).
 e2e   : the same step driven through the C ABI with HOST buffers: every step uploads
-        positions+momenta from pinned host memory (imdcu_update_atoms) and downloads
-        positions, momenta, forces, per-atom energies and the energy sums.
+        positions+momenta from pinned host memory (imdcu_update_atoms) and downloads the
+        new positions+momenta (the next step's inputs) and the energy sums.
 roofline : dominant kernel (k_eam_pass1), algorithmic bytes (64 + 4*N_h per atom,
         SURVEY.md 8d) / its mean launch time measured live with CUDA events.
 cpu_baseline : the UNMODIFIED reference (oracle/_ref, author's flags), its own MPI build run
@@ -45,6 +45,16 @@ N_H_AL = 39                 # half-list neighbours per atom, Al r_c 6.3 + margin
 REF_FAST = os.path.join(ROOT, "oracle", "_ref", "imd_ref_eam_nve_nbl_fast")
 REF_IEEE = os.path.join(ROOT, "oracle", "_ref", "imd_ref_eam_nve_nbl")
 REF_MPI = os.path.join(ROOT, "oracle", "_ref", "imd_ref_mpi_eam_nve_nbl_fast")
+
+
+def measured_traffic(kernel, units):
+    """DRAM bytes per launch of `kernel` from the committed ncu capture (profiles/traffic.json),
+    scaled to this run's unit count; None when no capture exists."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[kernel]
+        return float(t["bytes_per_unit"]) * units, t["source"]
+    except Exception:
+        return None, None
 
 
 def measured_peak_gbs():
@@ -351,10 +361,8 @@ def our_arm(args, rank, local_rank, world):
     cap = int(max(natoms, pos.shape[0]) * 1.25) + 1024   # the slab population changes when atoms migrate
     hp = torch.empty((cap, 3), dtype=torch.float64).pin_memory()
     hm = torch.empty((cap, 3), dtype=torch.float64).pin_memory()
-    hf = torch.empty((cap, 3), dtype=torch.float64).pin_memory()
-    he = torch.empty((cap,), dtype=torch.float64).pin_memory()
-    np_p, np_m, np_f, np_e = hp.numpy(), hm.numpy(), hf.numpy(), he.numpy()
-    ctx.download_into(np_p, np_m, np_f, np_e)
+    np_p, np_m = hp.numpy(), hm.numpy()
+    ctx.download_into(np_p, np_m)
 
     def e2e_step(s):
         ctx.update_atoms(np_p, np_m)             # H2D: this step's inputs (first ctx.n rows)
@@ -364,7 +372,7 @@ def our_arm(args, rank, local_rank, world):
             out2, _ = ctx.move_atoms_ttm()
         else:
             out2, _ = ctx.move_atoms_nve()
-        ctx.download_into(np_p, np_m, np_f, np_e)  # D2H: the step's results
+        ctx.download_into(np_p, np_m)            # D2H: the step's results = the next step's inputs
         return out[0] + out2[0]
 
     for s in range(2):
@@ -380,7 +388,7 @@ def our_arm(args, rank, local_rank, world):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = natoms * world * ke / float(t.item())
     h2d = natoms * 48
-    d2h = natoms * 80 + 2 * 64
+    d2h = natoms * 48 + 2 * 64
 
     # ---- per-kernel times (CUDA events inside the library, separate short segment)
     roofline = None
@@ -397,10 +405,12 @@ def our_arm(args, rank, local_rank, world):
         alg_bytes = (64 + 4 * N_H_AL) * natoms
         peak, peak_src = measured_peak_gbs()
         achieved = alg_bytes / (p1_ms * 1e-3) / 1e9
+        traffic, traffic_src = measured_traffic("k_eam_pass1", natoms)
         roofline = {"kernel": "k_eam_pass1", "bound": "hbm", "achieved": achieved, "peak": peak,
-                    "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                    "alg_bytes_per_launch": alg_bytes, "ms_per_launch": p1_ms,
-                    "note": "FP64-pipe-bound kernel (about 45 DP instr per pair); HBM fraction is low by nature"}
+                    "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                    "peak_source": peak_src, "alg_bytes_per_launch": alg_bytes, "ms_per_launch": p1_ms,
+                    "note": "not HBM-bound: L1 data pipe 77 % (two random 24-byte table rows from shared memory and one "
+                            "32-byte gather per pair), FP64 pipe 33 %, DRAM 8 % (profiles/r01b_full_ncu.txt)"}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -467,14 +477,15 @@ def ttm3d_reference_sample(n, sweeps, nproc):
 
 def ttm3d_arm(args, rank, local_rank, world):
     """BASELINE.json configs[4]: standalone 3-D TTM electron-temperature diffusion sweep, cell-updates/s.
-    One step = one sweep { do_DIFF; ttm_fill_ghost_layers } over the lattice; N GPUs = N replicas of the
-    lattice (the sweep of one lattice does not shard in this round: replicas only)."""
+    One step = one sweep { do_DIFF; ttm_fill_ghost_layers } over the lattice; N GPUs = x slabs of a lattice
+    N times as long (weak scaling), ghost planes {natoms, temp, fd_k} over NCCL after every sweep."""
     metric, unit = "TTM-3D cell-updates/s", "cell-updates/s"
     nx, ny, nz = args.grid
     cfg = {"workload": "3-D TTM diffusion sweep (do_DIFF + ttm_fill_ghost_layers), %dx%dx%d FD cells, film with "
                        "vacuum front (1/8 inactive), pbc 0 1 1 (BASELINE.json configs[4])" % (nx, ny, nz),
            "cells": nx * ny * nz, "l2_policy": "inputs larger than L2 (11 fields x %.1f GB)" % (nx * ny * nz * 8 / 1e9),
-           "parallelism": "1 GPU" if world == 1 else "%d independent replicas" % world}
+           "parallelism": "1 GPU" if world == 1 else "x slabs of a %dx%dx%d lattice on %d GPUs, NCCL ghost planes"
+                          % (nx * world, ny, nz, world)}
     if args.impl == "reference":
         if rank != 0:
             return 0
@@ -501,10 +512,15 @@ def ttm3d_arm(args, rank, local_rank, world):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     ctx = capi.Context(local_rank)
+    if world > 1:
+        obj = [capi.Context.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(obj, src=0)
+        ctx.comm_init(obj[0], rank, world)
     e = (nx + 2, ny + 2, nz + 2)
     rng = np.random.default_rng(7 + rank)
     nat = np.full(e, 60, np.int32)
-    nat[: max(1, nx // 8)] = 3
+    if rank == 0:
+        nat[: max(1, nx // 8)] = 3                     # vacuum in front of the film (first slab only)
     temp = (0.05 + 0.5 * rng.random(e, dtype=np.float32)).astype(np.float64)
     fd_k = (10.0 + 20.0 * rng.random(e, dtype=np.float32)).astype(np.float64)
     const = lambda v: np.full(e, v)                                                    # noqa: E731
@@ -568,8 +584,9 @@ def ttm3d_arm(args, rank, local_rank, world):
     peak, peak_src = measured_peak_gbs()
     alg = 108 * cells
     ach = alg / (k_ms * 1e-3) / 1e9
-    roofline = {"kernel": "k_ttm3d_diff", "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                "traffic": None, "peak_source": peak_src, "alg_bytes_per_launch": alg, "ms_per_launch": k_ms,
+    traffic, traffic_src = measured_traffic("k_ttm3d_diff", cells)
+    roofline = {"kernel": "k_ttm3d_diff_direct", "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "alg_bytes_per_launch": alg, "ms_per_launch": k_ms,
                 "note": "108 B per cell update: 4 + 10 x 8 read, 3 x 8 written (SURVEY 8d)"}
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

@@ -313,6 +313,8 @@ void imdcu_ttm_release(imdcu_ctx *ctx);                                // ttm.cu
 int  imdcu_ttm_fork(imdcu_ctx *ctx, int steps);                        // ttm.cu
 int  imdcu_ttm_join(imdcu_ctx *ctx, double out16[16]);
 void imdcu_ttm3d_release(imdcu_ctx *ctx);                              // ttm3d.cu
+int  imdcu_multi_sendrecv_x(imdcu_ctx *ctx, int west, int east, const void *s_w, const void *s_e, void *r_e,
+                            void *r_w, size_t count, int is_int);         // multi.cu
 TabView imdcu_tab_view(const DevTable &t);
 
 static inline int div_up(int64_t a, int64_t b) { return (int) ((a + b - 1) / b); }

@@ -148,6 +148,22 @@ static int exchange(imdcu_ctx *c, const void *s_w, size_t n_sw, const void *s_e,
   return IMDCU_OK;
 }
 
+// plain x-neighbour exchange of equally sized buffers (3-D FD lattice planes, ttm3d.cu):
+// s_w -> west, s_e -> east, r_e <- east, r_w <- west; a neighbour < 0 is an open end.
+int imdcu_multi_sendrecv_x(imdcu_ctx *c, int west, int east, const void *s_w, const void *s_e, void *r_e, void *r_w,
+                           size_t count, int is_int)
+{
+  if (c->comm.nranks <= 1) return IMDCU_OK;
+  const ncclDataType_t dt = is_int ? ncclInt32 : ncclFloat64;
+  NCCL_CHECK(c, ncclGroupStart());
+  if (west >= 0) NCCL_CHECK(c, ncclSend(s_w, count, dt, west, comm_of(c), c->stream));
+  if (east >= 0) NCCL_CHECK(c, ncclSend(s_e, count, dt, east, comm_of(c), c->stream));
+  if (east >= 0) NCCL_CHECK(c, ncclRecv(r_e, count, dt, east, comm_of(c), c->stream));
+  if (west >= 0) NCCL_CHECK(c, ncclRecv(r_w, count, dt, west, comm_of(c), c->stream));
+  NCCL_CHECK(c, ncclGroupEnd());
+  return IMDCU_OK;
+}
+
 // ----------------------------------------------------------------------------- migration
 #define MIG_REC 10        // doubles per migrating atom: pos4, mom4, {type,vtype}, {id,fdi}
 

@@ -215,6 +215,7 @@ __global__ void k_ttm3d_sum(const double *__restrict__ partials, int n, double *
 // One thread per face cell; the six faces are disjoint, so one launch does all of them.
 struct T3Ghost {
   int nx, ny, nz, pbc[3];
+  int xmode[2];                                  // low / high x ghost plane: 0 open, 1 periodic (local copy), 2 filled by the x-neighbour rank
   long long pz, py;
   int *natoms; double *temp, *fd_k;
 };
@@ -236,8 +237,9 @@ k_ttm3d_ghosts(T3Ghost a)
     else { gi = si = u + 1; gj = sj = v + 1; gk = side ? a.nz + 1 : 0; sk = side ? 1 : a.nz; }
     const long long g = (long long) gi * a.py + (long long) gj * a.pz + T3_OFF + gk;
     const long long s = (long long) si * a.py + (long long) sj * a.pz + T3_OFF + sk;
-    if (a.pbc[ax]) { a.natoms[g] = a.natoms[s]; a.temp[g] = a.temp[s]; a.fd_k[g] = a.fd_k[s]; }
-    else a.natoms[g] = 0;
+    const int mode = ax == 0 ? a.xmode[side] : a.pbc[ax];
+    if (mode == 1) { a.natoms[g] = a.natoms[s]; a.temp[g] = a.temp[s]; a.fd_k[g] = a.fd_k[s]; }
+    else if (mode == 0) a.natoms[g] = 0;
   }
 }
 
@@ -325,17 +327,41 @@ extern "C" int imdcu_ttm3d_download(imdcu_ctx *c, int *natoms, double *temp, dou
   return IMDCU_OK;
 }
 
-static void t3_ghosts(imdcu_ctx *c)
+// x-neighbour ranks of the slab decomposition (cpu_dim = N 1 1): -1 at an open end
+static void t3_neighbours(const imdcu_ctx *c, int *west, int *east)
+{
+  const int r = c->comm.rank, N = c->comm.nranks, px = c->ttm3d.pbc[0];
+  *east = r + 1 < N ? r + 1 : (px ? 0 : -1);
+  *west = r - 1 >= 0 ? r - 1 : (px ? N - 1 : -1);
+}
+
+static int t3_ghosts(imdcu_ctx *c)
 {
   Ttm3dState &t = c->ttm3d;
   T3Ghost g;
   g.nx = t.nx; g.ny = t.ny; g.nz = t.nz; g.pz = t.pz; g.py = t.py;
   for (int d = 0; d < 3; d++) g.pbc[d] = t.pbc[d];
+  int west = -1, east = -1;
+  const bool multi = c->comm.nranks > 1;
+  if (multi) t3_neighbours(c, &west, &east);
+  g.xmode[0] = multi ? (west >= 0 ? 2 : 0) : t.pbc[0];
+  g.xmode[1] = multi ? (east >= 0 ? 2 : 0) : t.pbc[0];
   g.natoms = t.natoms.p; g.fd_k = t.fd_k.p; g.temp = t.temp[t.cur].p;
   const long long faces = 2 * ((long long) t.ny * t.nz + (long long) t.nx * t.nz + (long long) t.nx * t.ny);
   const int gblocks = (int) std::min<long long>((faces + 255) / 256, (long long) c->num_sms * 8);
   k_ttm3d_ghosts<<<gblocks, 256, 0, c->stream>>>(g);
   c->count_launch();
+  if (multi) {
+    // whole planes travel (their y/z ghost rows ride along): plane 1 -> west's plane nx+1, plane nx -> east's
+    // plane 0; the members the reference's mpi_element carries: natoms, temp, fd_k (imd_ttm_3D.c:2990-3006)
+    const size_t n = (size_t) t.py, lo = (size_t) t.py, hi = (size_t) t.py * t.nx, gh = (size_t) t.py * (t.nx + 1);
+    double *T = t.temp[t.cur].p, *K = t.fd_k.p;
+    int *N = t.natoms.p;
+    RET_IF(imdcu_multi_sendrecv_x(c, west, east, T + lo, T + hi, T + gh, T, n, 0));
+    RET_IF(imdcu_multi_sendrecv_x(c, west, east, K + lo, K + hi, K + gh, K, n, 0));
+    RET_IF(imdcu_multi_sendrecv_x(c, west, east, N + lo, N + hi, N + gh, N, n, 1));
+  }
+  return IMDCU_OK;
 }
 
 // ttm_fill_ghost_layers (imd_ttm_3D.c:3314-3504) on l1, as calc_ttm calls it ahead of the sub-step loop (:67)
@@ -343,7 +369,7 @@ extern "C" int imdcu_ttm3d_fill_ghost_layers(imdcu_ctx *c)
 {
   if (!c || !c->ttm3d.inited) return c ? c->fail(IMDCU_EINVAL, "imdcu_ttm3d_init has not been called") : IMDCU_EINVAL;
   cudaSetDevice(c->device);
-  t3_ghosts(c);
+  RET_IF(t3_ghosts(c));
   CU_CHECK(c, cudaGetLastError());
   return IMDCU_OK;
 }
@@ -399,7 +425,7 @@ extern "C" int imdcu_ttm3d_diff(imdcu_ctx *c, double tau, int diff_substeps, int
     }
     if (a.partials) { k_ttm3d_sum<<<1, 256, 0, c->stream>>>(t.partials.p, nblocks, t.d_eabs); c->count_launch(); }
     t.cur = 1 - t.cur;                             // l3 = l1; l1 = l2; l2 = l3 (:1822-1824)
-    t3_ghosts(c);
+    RET_IF(t3_ghosts(c));
   }
   CU_CHECK(c, cudaGetLastError());
   if (Eabs) {

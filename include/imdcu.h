@@ -169,6 +169,10 @@ int  imdcu_download_ttm(imdcu_ctx *ctx, double *cells, double *xiarr, double *vc
  *                     wide-range properties frozen.  diff_substeps enters xi_fac (:1614).  Open
  *                     directions get ghost natoms = 0 (the reference's surface-rank branch).
  *                     *Eabs (may be NULL) = Eabs_local accumulated since init (:1648-1652).
+ * Several GPUs: after imdcu_comm_init(nranks > 1) the lattice given here is this rank's x slab
+ *                     (cpu_dim = N 1 1): nx local planes, pbc[0] is the global flag; the x ghost
+ *                     planes then come from the x-neighbour ranks over NCCL after every sweep
+ *                     (the reference's mpi_xplane_block exchange, :3328-3341), Eabs stays per rank.
  * imdcu_ttm3d_fill_ghost_layers: ttm_fill_ghost_layers() on l1 alone, as calc_ttm calls it ahead of
  *                     the sub-step loop (:67); uploaded ghost values are otherwise used as given.
  * imdcu_ttm3d_download: natoms / temp / U / xi of l1 (any may be NULL). */

@@ -51,9 +51,44 @@ def make_imd(args, device, comm, spec, pos, box, pbc, mom, eos, tp):
     return imd
 
 
+def check_ttm3d(capi, dist, uid, rank, world, local):
+    """x-slab sharded 3-D sweep == the numpy restatement of the whole lattice, bit for bit."""
+    from oracle import ttm3d_np as t3
+    ok = True
+    ctx = capi.Context(local)
+    ctx.comm_init(uid, rank, world)              # one communicator (a unique id is good for one init)
+    for pbc in ((0, 1, 1), (1, 1, 1)):
+        nxl, ny, nz = 9, 21, 40
+        shape = (nxl * world, ny, nz)
+        f = t3.make_case(shape, seed=31, hole=True, pbc=pbc)
+        want = {k: v.copy() for k, v in f.items()}
+        e_want = t3.run(want, (16.0, 15.0, 17.0), 0.1 / 250, 20, 250, 1, 5, pbc)
+        ctx.ttm3d_init((nxl, ny, nz), (16.0, 15.0, 17.0), pbc, 20)
+        sl = slice(rank * nxl, (rank + 1) * nxl + 2)
+        ctx.ttm3d_upload(**{k: np.ascontiguousarray(v[sl]) for k, v in f.items()})
+        e = ctx.ttm3d_diff(0.1 / 250, 250, 1, 5)
+        out = ctx.ttm3d_download()
+        parts = [None] * world if rank == 0 else None
+        dist.gather_object((e, {k: v[1:-1] for k, v in out.items()}), parts, dst=0)
+        if rank == 0:
+            e_tot = sum(p[0] for p in parts)
+            for k in ("natoms", "temp", "U", "xi"):
+                got = np.concatenate([p[1][k] for p in parts])[:, 1:-1, 1:-1]
+                assert np.array_equal(got, want[k][1:-1, 1:-1, 1:-1]), (pbc, k)
+            assert abs(e_tot - e_want) <= 1e-12 * abs(e_want)
+            print("ttm3d pbc %s ok: %d ranks x %d planes, Eabs %.12e" % (pbc, world, nxl, e_tot))
+        dist.barrier()
+    ctx.close()
+    if rank == 0:
+        print("MULTI_GPU_CHECK PASSED world=%d ttm3d=1" % world)
+    dist.destroy_process_group()
+    return 0 if ok else 1
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--ttm", action="store_true")
+    ap.add_argument("--ttm3d", action="store_true", help="3-D FD lattice sharded in x slabs")
     ap.add_argument("--steps", type=int, default=40)
     args = ap.parse_args()
     import torch
@@ -65,6 +100,8 @@ def main():
     dist.init_process_group("gloo")
     obj = [capi.Context.comm_unique_id() if rank == 0 else None]
     dist.broadcast_object_list(obj, src=0)
+    if args.ttm3d:
+        return check_ttm3d(capi, dist, obj[0], rank, world, local)
     spec, pos, box, pbc, mom = build_system(args)
     eos, tp = None, None
     if args.ttm:

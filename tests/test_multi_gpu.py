@@ -16,14 +16,15 @@ def _ngpu():
     return torch.cuda.device_count()
 
 
-@pytest.mark.parametrize("ttm", [False, True])
-def test_two_ranks_equal_one_rank(ttm):
+@pytest.mark.parametrize("mode", ["nve", "ttm", "ttm3d"])
+def test_two_ranks_equal_one_rank(mode):
     if _ngpu() < 2:
         pytest.skip("needs 2 GPUs")
+    port = {"nve": "29532", "ttm": "29533", "ttm3d": "29534"}[mode]
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
-           "127.0.0.1", "--master-port", "29533" if ttm else "29532", os.path.join(ROOT, "tests", "multi_gpu_check.py")]
-    if ttm:
-        cmd.append("--ttm")
-    res = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=600)
+           "127.0.0.1", "--master-port", port, os.path.join(ROOT, "tests", "multi_gpu_check.py")]
+    if mode != "nve":
+        cmd.append("--" + mode)
+    res = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=300)
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
     assert "MULTI_GPU_CHECK PASSED" in res.stdout
