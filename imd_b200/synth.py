@@ -174,6 +174,93 @@ def make_eam_tables(spec: EamSpec, outdir: Optional[str] = None) -> Dict[str, Po
     }
 
 
+@dataclasses.dataclass
+class BinarySpec:
+    """Two-species EAM (ntypes = 2) on the L1_2 structure (Cu3Au type, generate_fcc(6),
+    imd_generate.c:483-490): every table column has its OWN r^2 grid (begin, end, step, length),
+    the rho columns are asymmetric (col it*ntypes+jt != col jt*ntypes+it), as potaccess.h and
+    imd_forces_nbl.c:557-572, 845-874 allow."""
+    name: str
+    a: float
+    sa: EamSpec
+    sb: EamSpec
+
+    @property
+    def masses(self):
+        return (self.sa.mass, self.sb.mass)
+
+
+NI3AL = BinarySpec("ni3al", a=3.57,
+                   sa=EamSpec("ni", a=3.52, r_c=4.80, E_c=4.45, phi_e=0.74, alpha=4.98, beta=6.41, gamma=8.86,
+                              mass=58.6934, rows=1700, r2_begin=1.0),
+                   sb=EamSpec("alb", a=4.05, r_c=5.40, E_c=3.36, phi_e=0.30, alpha=4.60, beta=5.40, gamma=7.6,
+                              mass=26.9815, rows=1900, r2_begin=1.2, rho_e=10.0))
+
+
+def binary_columns(b: BinarySpec):
+    """pair[4], rho[4], embed[2] column tuples (begin, end, step, values); column = it*2 + jt."""
+    def radial(spec, fn, r_c, rows, r2_begin):
+        r2 = np.linspace(r2_begin, r_c**2, rows)
+        step = (r_c**2 - r2_begin) / (rows - 1)
+        r = np.sqrt(r2)
+        return (r2_begin, r_c**2, step, fn(r) * _smooth(r, r_c))
+    sa, sb = b.sa, b.sb
+    phi = lambda s: (lambda r: s.phi_e * np.exp(-s.gamma * (r / s.r_e - 1.0)))          # noqa: E731
+    dens = lambda s, w: (lambda r: w * s.f_e * np.exp(-s.beta * (r / s.r_e - 1.0)))      # noqa: E731
+    rc_x = 0.5 * (sa.r_c + sb.r_c)
+    cross = lambda r: 0.5 * (phi(sa)(r) * 0.9 + phi(sb)(r) * 1.1)                        # noqa: E731
+    pair = [radial(sa, phi(sa), sa.r_c, sa.rows, sa.r2_begin),
+            radial(sa, cross, rc_x, 1800, 1.1), radial(sa, cross, rc_x, 1800, 1.1),
+            radial(sb, phi(sb), sb.r_c, sb.rows, sb.r2_begin)]
+    # rho column it*2+jt: density at an atom of type it from a neighbour of type jt
+    rho = [radial(sa, dens(sa, 1.0), sa.r_c, sa.rows, sa.r2_begin),
+           radial(sb, dens(sb, 0.85), 5.1, 1750, 1.15),
+           radial(sa, dens(sa, 1.2), 4.9, 1650, 1.05),
+           radial(sb, dens(sb, 1.0), sb.r_c, sb.rows, sb.r2_begin)]
+    emb = []
+    for s in (sa, sb):
+        rho_end = 3.0 * s.rho_e
+        x = np.linspace(0.0, rho_end, s.rows)
+        xx = np.maximum(x / s.rho_e, 1e-300)
+        ab, gb = s.alpha / s.beta, s.gamma / s.beta
+        F = -s.E_c * (1.0 - ab * np.log(xx)) * xx**ab - 6.0 * s.phi_e * xx**gb
+        F[0] = 0.0
+        emb.append((0.0, rho_end, rho_end / (s.rows - 1), F))
+    return pair, rho, emb
+
+
+def make_eam_tables_binary(b: BinarySpec, outdir: Optional[str] = None) -> Dict[str, PotTable]:
+    """Like make_eam_tables for ntypes = 2 (files <name>.pair/.rho/.emb with 4/4/2 columns)."""
+    pair, rho, emb = binary_columns(b)
+    out = {}
+    for key, cols, radial in (("pair", pair, True), ("rho", rho, True), ("emb", emb, False)):
+        bg, en, st, vals = [c[0] for c in cols], [c[1] for c in cols], [c[2] for c in cols], [c[3] for c in cols]
+        if outdir is not None:
+            os.makedirs(outdir, exist_ok=True)
+            path = os.path.join(outdir, "%s.%s" % (b.name, key))
+            write_pot_table2(path, bg, en, st, vals)
+            out[key] = read_pot_table2(path, len(cols), radial)
+        else:
+            out[key] = _table_from_columns(bg, en, st, vals, radial)
+    return out
+
+
+def l12_lattice(ncell: Sequence[int], a: float):
+    """L1_2 positions and types as generate_fcc(6) makes them (imd_generate.c:440-560): fcc sites,
+    corner atoms type 1, face atoms type 0."""
+    nx, ny, nz = ncell
+    pos, typ = [], []
+    bu = a / 2
+    for x in range(2 * nx):
+        for y in range(2 * ny):
+            for z in range(2 * nz):
+                if (x + y + z) % 2 == 1:
+                    continue
+                typ.append(0 if (x % 2 == 1 or y % 2 == 1 or z % 2 == 1) else 1)
+                pos.append(((x + 0.5) * bu, (y + 0.5) * bu, (z + 0.5) * bu))
+    return np.array(pos), np.array(typ, np.int32), np.diag([nx * a, ny * a, nz * a]).astype(np.float64)
+
+
 # ----------------------------------------------------------------------------- lattices
 
 def fcc_lattice(ncell: Sequence[int], a: float, dtype=np.float64) -> Tuple[np.ndarray, np.ndarray]:
@@ -212,17 +299,19 @@ def write_param_file(path: str, spec: EamSpec, box_param: Sequence[int], maxstep
                      outfiles: str, potdir: str = ".", pbc=(1, 1, 1), starttemp: float = 0.0258,
                      timestep: float = 0.1, nbl_margin: float = 0.5, seed: int = 4711,
                      eng_int: int = 1, extra: str = "", ensemble: str = "nve",
-                     cpu_dim=(1, 1, 1)) -> None:
+                     cpu_dim=(1, 1, 1), coordname: str = "_fcc", masses=None) -> None:
     """IMD parameter file for the serial reference binary (keywords of imd_param.c)."""
     txt = io.StringIO()
-    txt.write("coordname    _fcc\n")
+    txt.write("coordname    %s\n" % coordname)
     txt.write("outfiles     %s\n" % outfiles)
     txt.write("ensemble     %s\n" % ensemble)
     txt.write("maxsteps     %d\n" % maxsteps)
     txt.write("timestep     %.17g\n" % timestep)
-    txt.write("ntypes       1\ntotal_types  1\n")
-    txt.write("masses       %.17g\n" % spec.mass)
-    txt.write("types        0\n")
+    masses = [spec.mass] if masses is None else list(masses)
+    nt = len(masses)
+    txt.write("ntypes       %d\ntotal_types  %d\n" % (nt, nt))
+    txt.write("masses       %s\n" % " ".join("%.17g" % m for m in masses))
+    txt.write("types        %s\n" % " ".join(str(t) for t in range(nt)))
     txt.write("box_param    %d %d %d\n" % tuple(box_param))
     txt.write("box_unit     %.17g\n" % spec.a)
     txt.write("pbc_dirs     %d %d %d\n" % tuple(pbc))

@@ -31,6 +31,9 @@ CASES = {
     "cu_8x6x7_pbc": (synth.CU, (8, 6, 7), (1, 1, 1), 0.05, 12, (0, 12), 0.5),
     "cu_7x6x6_free_x": (synth.CU, (7, 6, 6), (0, 1, 1), 0.05, 12, (0, 12), 0.5),
     "al_5x5x5_pbc": (synth.AL, (5, 5, 5), (1, 1, 1), 0.05, 10, (0, 10), 0.4),
+    # two species (L1_2), every table column on its own r^2 grid, asymmetric rho columns
+    "ni3al_6x6x6_pbc": (synth.NI3AL, (6, 6, 6), (1, 1, 1), 0.08, 30, (0, 1, 15, 30), 0.5),
+    "ni3al_7x5x6_free_x": (synth.NI3AL, (7, 5, 6), (0, 1, 1), 0.05, 12, (0, 12), 0.4),
 }
 
 
@@ -60,11 +63,16 @@ def load_dump(d, step):
 def run_case(name, spec, box_param, pbc, starttemp, steps, dump_steps, margin, keep=None):
     work = tempfile.mkdtemp(prefix="imdgold_")
     try:
-        synth.make_eam_tables(spec, work)
+        binary = isinstance(spec, synth.BinarySpec)
+        if binary:
+            synth.make_eam_tables_binary(spec, work)
+        else:
+            synth.make_eam_tables(spec, work)
         os.makedirs(os.path.join(work, "out"))
         os.makedirs(os.path.join(work, "dump"))
         synth.write_param_file(os.path.join(work, "run.param"), spec, box_param, steps, "out/run",
-                               pbc=pbc, starttemp=starttemp, nbl_margin=margin, eng_int=1)
+                               pbc=pbc, starttemp=starttemp, nbl_margin=margin, eng_int=1,
+                               coordname="_l12" if binary else "_fcc", masses=spec.masses if binary else None)
         env = dict(os.environ, IMD_DUMP_DIR=os.path.join(work, "dump"),
                    IMD_DUMP_STEPS=",".join(str(s) for s in dump_steps))
         res = subprocess.run([REF_BIN, "-p", "run.param"], cwd=work, env=env,
@@ -98,8 +106,10 @@ def run_case(name, spec, box_param, pbc, starttemp, steps, dump_steps, margin, k
 def main():
     if not os.path.exists(REF_BIN):
         sys.exit("missing %s: run `make -C oracle ref` where /root/reference exists" % REF_BIN)
+    only = sys.argv[1:]
     for name, args in CASES.items():
-        run_case(name, *args)
+        if not only or name in only:
+            run_case(name, *args)
 
 
 if __name__ == "__main__":

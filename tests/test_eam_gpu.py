@@ -19,11 +19,11 @@ def rel_err(a, b, floor=1e-2):
     return np.max(np.abs(a - b)) / max(np.max(np.abs(b)), floor)
 
 
-def make_imd(box, pbc, tables, margin, timestep=0.1):
+def make_imd(box, pbc, tables, margin, timestep=0.1, ntypes=1):
     imd = host.Imd(0)
     imd.setup_potentials(tables)
     imd.make_box(box, pbc, margin)
-    imd.set_params(1, timestep)
+    imd.set_params(ntypes, timestep)
     return imd
 
 
@@ -52,7 +52,7 @@ def test_golden_cells_nblist_forces(case):
     for s in g.steps:
         if "s%d_nblpairs" % s not in g.z:
             continue
-        imd = make_imd(g.box, g.pbc, g.tables, g.margin, g.timestep)
+        imd = make_imd(g.box, g.pbc, g.tables, g.margin, g.timestep, g.ntypes)
         sc = g.step(s, "scalars")
         assert [int(x) for x in imd.global_cell_dim] == [int(x) for x in sc[4:7]]
         assert imd.cellsz == sc[7]
@@ -74,11 +74,13 @@ def test_golden_cells_nblist_forces(case):
         imd.close()
 
 
-def test_golden_trajectory():
+@pytest.mark.parametrize("case", ["cu_6x6x6_pbc", "ni3al_6x6x6_pbc"])
+def test_golden_trajectory(case):
     """NVE from the reference's step-0 state: calc_forces -> move_atoms -> check_nblist on the
-    device reproduces the reference's dumped states and its rebuild schedule."""
-    g = Golden("cu_6x6x6_pbc")
-    imd = make_imd(g.box, g.pbc, g.tables, g.margin, g.timestep)
+    device reproduces the reference's dumped states and its rebuild schedule (one and two species:
+    the second case runs the MULTI kernels, per-column table grids, two masses)."""
+    g = Golden(case)
+    imd = make_imd(g.box, g.pbc, g.tables, g.margin, g.timestep, g.ntypes)
     imd.set_atoms(g.step(0, "pre_pos"), g.step(0, "pre_mom"), g.step(0, "pre_mass"),
                   g.step(0, "pre_type"), g.step(0, "pre_id"))
     eng = g.z["eng"]

@@ -25,7 +25,7 @@ def test_cells_nblist_forces(case):
             continue      # only steps where the reference rebuilt its list fix the cell state
         ids = g.step(s, "pre_id")
         pos = np.ascontiguousarray(g.step(s, "pre_pos"))
-        orc = EamOracle(g.box, g.pbc, g.tables, g.margin)
+        orc = EamOracle(g.box, g.pbc, g.tables, g.margin, ntypes=g.ntypes)
         st = orc.state
         assert [st.gdim[0], st.gdim[1], st.gdim[2]] == [int(x) for x in g.step(s, "scalars")[4:7]]
         assert st.cellsz == g.step(s, "scalars")[7]

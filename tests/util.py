@@ -7,8 +7,9 @@ import numpy as np
 from imd_b200 import synth
 
 GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-GOLDEN_CASES = ["cu_6x6x6_pbc", "cu_8x6x7_pbc", "cu_7x6x6_free_x", "al_5x5x5_pbc"]
-SPECS = {"cu": synth.CU, "al": synth.AL}
+GOLDEN_CASES = ["cu_6x6x6_pbc", "cu_8x6x7_pbc", "cu_7x6x6_free_x", "al_5x5x5_pbc", "ni3al_6x6x6_pbc",
+                "ni3al_7x5x6_free_x"]
+SPECS = {"cu": synth.CU, "al": synth.AL, "ni3al": synth.NI3AL}
 
 
 class Golden:
@@ -16,7 +17,9 @@ class Golden:
         self.name = name
         self.z = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
         self.spec = SPECS[str(self.z["spec_name"])]
-        self.tables = synth.make_eam_tables(self.spec)
+        self.binary = isinstance(self.spec, synth.BinarySpec)
+        self.ntypes = 2 if self.binary else 1
+        self.tables = synth.make_eam_tables_binary(self.spec) if self.binary else synth.make_eam_tables(self.spec)
         self.pbc = self.z["pbc"]
         self.box = np.diag(self.z["box_param"].astype(np.float64) * self.spec.a)
         self.margin = float(self.z["nbl_margin"])
