@@ -18,7 +18,17 @@
 // (nothing here is a dense contraction).
 #include "device.cuh"
 
+#ifndef EAM_BLOCK
 #define EAM_BLOCK 512
+#endif
+#ifndef EAM_MINB
+#define EAM_MINB 2
+#endif
+#ifndef EAM_UNROLL
+#define EAM_UNROLL 2
+#endif
+#define EAM_PRAGMA_(x) _Pragma(#x)
+#define EAM_PRAGMA_UNROLL(n) EAM_PRAGMA_(unroll n)
 
 struct EamArgs {
   int n, ntypes, cap;
@@ -45,7 +55,7 @@ __device__ __forceinline__ double sub_sum(double v)
 // LPA lanes cooperate on one atom (1 for big systems, more to fill the GPU on small ones);
 // SMEM: tables staged in shared memory, else read through L1/L2; MULTI: ntypes > 1.
 template <int LPA, bool SMEM, bool MULTI>
-__global__ void __launch_bounds__(EAM_BLOCK)
+__global__ void __launch_bounds__(EAM_BLOCK, EAM_MINB)
 k_eam_pass1(EamArgs a)
 {
   extern __shared__ __align__(16) double s_tab[];
@@ -87,7 +97,7 @@ k_eam_pass1(EamArgs a)
       const int num = a.nbl_num[i];
       const int *slot = a.nbl_idx + ((size_t) (i >> 5) * a.cap) * 32 + (i & 31);
       if (MULTI) it = a.type[i];
-#pragma unroll 2
+EAM_PRAGMA_UNROLL(EAM_UNROLL)
       for (int k = sub; k < num; k += LPA) {
         const int j = slot[(size_t) k * 32];
         const double4 pj = ld256(&a.pos4[j]);
@@ -135,7 +145,7 @@ k_eam_pass1(EamArgs a)
 }
 
 template <int LPA, bool SMEM, bool MULTI>
-__global__ void __launch_bounds__(EAM_BLOCK)
+__global__ void __launch_bounds__(EAM_BLOCK, EAM_MINB)
 k_eam_pass2(EamArgs a)
 {
   extern __shared__ __align__(16) double s_tab[];
@@ -170,7 +180,7 @@ k_eam_pass2(EamArgs a)
       const int *slot = a.nbl_idx + ((size_t) (i >> 5) * a.cap) * 32 + (i & 31);
       int it = 0;
       if (MULTI) it = a.type[i];
-#pragma unroll 2
+EAM_PRAGMA_UNROLL(EAM_UNROLL)
       for (int k = sub; k < num; k += LPA) {
         const int j = slot[(size_t) k * 32];
         const double4 pj = ld256(&a.pos4[j]);
