@@ -189,6 +189,8 @@ struct imdcu_ctx {
   std::vector<double> restrictions;          // host copy
   DevBuf<double> d_restrictions;
   int    pdecay = 0; double xipdecay = 0, ramp_start = 0, ramp_end = 1;
+  double *fused_coef = nullptr;              // pair + rho rows interleaved (context.cu: imdcu_fused_table)
+  int    fused_state = 0;                    // 0 not looked at, 1 built, -1 tables do not share a grid
   int    fuse_ttm_steps = -1;                // >= 0: imdcu_eam_forces forks calc_ttm(steps) between its passes
   bool   box_set = false, params_set = false;
 
@@ -309,6 +311,7 @@ __device__ __host__ inline int imdcu_combine_code(int pc, int code)
 {
   return (pc % 3 - 1 + code % 3 - 1 + 1) + 3 * ((pc / 3) % 3 - 1 + (code / 3) % 3 - 1 + 1) + 9 * (pc / 9 - 1 + code / 9 - 1 + 1);
 }
+const double *imdcu_fused_table(imdcu_ctx *ctx);                       // context.cu
 void imdcu_ttm_release(imdcu_ctx *ctx);                                // ttm.cu
 int  imdcu_ttm_fork(imdcu_ctx *ctx, int steps);                        // ttm.cu
 int  imdcu_ttm_join(imdcu_ctx *ctx, double out16[16]);

@@ -69,6 +69,7 @@ extern "C" int imdcu_destroy(imdcu_ctx *c)
   c->d_gplan.release(); c->gcell_off.release(); c->ghost_src.release(); c->ghost_code.release();
   c->ghost_root.release(); c->ghost_tcode.release(); c->ghost_raw.release();
   c->nbl_idx.release(); c->nbl_num.release(); c->partials.release(); c->d_restrictions.release();
+  if (c->fused_coef) cudaFree(c->fused_coef);
   imdcu_ttm_release(c);
   imdcu_ttm3d_release(c);
   imdcu_multi_release(c);
@@ -104,6 +105,8 @@ extern "C" int imdcu_set_table(imdcu_ctx *c, int which, int ncols, int maxsteps,
     return c ? c->fail(IMDCU_EINVAL, "imdcu_set_table: bad argument") : IMDCU_EINVAL;
   cudaSetDevice(c->device);
   DevTable &t = c->tab[which];
+  if (c->fused_coef) { cudaFree(c->fused_coef); c->fused_coef = nullptr; }
+  c->fused_state = 0;
   if (t.coef) { cudaFree(t.coef); t.coef = nullptr; }
   if (t.begin) { cudaFree(t.begin); t.begin = nullptr; }
   t.ncols = ncols; t.nrows = maxsteps; t.maxsteps = maxsteps;
@@ -134,6 +137,30 @@ extern "C" int imdcu_set_table(imdcu_ctx *c, int which, int ncols, int maxsteps,
   t.end = t.begin + ncols; t.invstep = t.begin + 2 * ncols;
   t.set = true;
   return IMDCU_OK;
+}
+
+// pair and rho rows interleaved, {p0,dv,d2v | r0,drv,d2rv} per r^2 interval, when both tables are
+// single-column and tabulated on the same grid (k_eam_pass1_fused); nullptr otherwise
+const double *imdcu_fused_table(imdcu_ctx *c)
+{
+  if (c->fused_state != 0) return c->fused_state > 0 ? c->fused_coef : nullptr;
+  c->fused_state = -1;
+  static const bool off = [] { const char *e = getenv("IMDCU_FUSED_TABLE"); return e && e[0] == '0'; }();
+  const DevTable &p = c->tab[IMDCU_TAB_PAIR], &r = c->tab[IMDCU_TAB_RHO];
+  if (off || !p.set || !r.set || p.ncols != 1 || r.ncols != 1 || p.nrows != r.nrows) return nullptr;
+  if (p.h_begin[0] != r.h_begin[0] || p.h_end[0] != r.h_end[0] || p.h_invstep[0] != r.h_invstep[0] ||
+      p.h_len[0] != r.h_len[0])
+    return nullptr;
+  const size_t n = (size_t) p.nrows;
+  std::vector<double> pc(n * 3), rc(n * 3), f(n * 6);
+  if (cudaMemcpy(pc.data(), p.coef, n * 3 * sizeof(double), cudaMemcpyDeviceToHost) != cudaSuccess) return nullptr;
+  if (cudaMemcpy(rc.data(), r.coef, n * 3 * sizeof(double), cudaMemcpyDeviceToHost) != cudaSuccess) return nullptr;
+  for (size_t k = 0; k < n; k++)
+    for (int q = 0; q < 3; q++) { f[6 * k + q] = pc[3 * k + q]; f[6 * k + 3 + q] = rc[3 * k + q]; }
+  if (cudaMalloc(&c->fused_coef, f.size() * sizeof(double)) != cudaSuccess) { c->fused_coef = nullptr; return nullptr; }
+  if (cudaMemcpy(c->fused_coef, f.data(), f.size() * sizeof(double), cudaMemcpyHostToDevice) != cudaSuccess) return nullptr;
+  c->fused_state = 1;
+  return c->fused_coef;
 }
 
 // ----------------------------------------------------------------------------- params
