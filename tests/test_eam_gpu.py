@@ -97,12 +97,28 @@ def test_golden_trajectory(case):
     imd.close()
 
 
-@pytest.mark.parametrize("ncell,pbc,spec", [((9, 7, 8), (1, 1, 1), synth.CU),
-                                            ((12, 6, 6), (0, 1, 1), synth.AL),
-                                            ((6, 6, 6), (0, 0, 0), synth.CU)])
-def test_oracle_parity_seeded(ncell, pbc, spec):
+def tables_on_different_grids(spec):
+    """Single-species tables whose rho column is tabulated on another r^2 grid than the pair column:
+    the interleaved-row kernel (k_eam_pass1_fused) does not apply, the general one runs."""
+    pair, rho, emb = synth.eam_columns(spec)
+    r2 = np.linspace(1.1, 0.97 * spec.r_c**2, 1777)
+    r = np.sqrt(r2)
+    f = spec.f_e * np.exp(-spec.beta * (r / spec.r_e - 1.0)) * synth._smooth(r, np.sqrt(0.97) * spec.r_c)
+    rho = (1.1, 0.97 * spec.r_c**2, (0.97 * spec.r_c**2 - 1.1) / 1776, f)
+    mk = synth._table_from_columns
+    return {"pair": mk([pair[0]], [pair[1]], [pair[2]], [pair[3]], True),
+            "rho": mk([rho[0]], [rho[1]], [rho[2]], [rho[3]], True),
+            "emb": mk([emb[0]], [emb[1]], [emb[2]], [emb[3]], False)}
+
+
+@pytest.mark.parametrize("ncell,pbc,spec,same_grid", [((9, 7, 8), (1, 1, 1), synth.CU, True),
+                                                      ((12, 6, 6), (0, 1, 1), synth.AL, True),
+                                                      ((6, 6, 6), (0, 0, 0), synth.CU, True),
+                                                      ((8, 7, 6), (1, 1, 1), synth.CU, False),
+                                                      ((10, 5, 6), (0, 1, 1), synth.AL, False)])
+def test_oracle_parity_seeded(ncell, pbc, spec, same_grid):
     from oracle.binding import EamOracle
-    tables = synth.make_eam_tables(spec)
+    tables = synth.make_eam_tables(spec) if same_grid else tables_on_different_grids(spec)
     pos, box = synth.fcc_lattice(ncell, spec.a)
     rng = np.random.default_rng(7)
     pos = pos + rng.normal(0, 0.08, pos.shape)
