@@ -13,7 +13,7 @@ value : whole-job atom-steps/s with atoms resident in HBM (device-timed, CUDA ev
 e2e   : the same step driven through the C ABI with HOST buffers: every step uploads
         positions+momenta from pinned host memory (imdcu_update_atoms) and downloads the
         new positions+momenta (the next step's inputs) and the energy sums.
-roofline : dominant kernel (k_eam_pass1), algorithmic bytes (64 + 4*N_h per atom,
+roofline : dominant kernel (k_eam_pass1_fused), algorithmic bytes (64 + 4*N_h per atom,
         SURVEY.md 8d) / its mean launch time measured live with CUDA events.
 cpu_baseline : the UNMODIFIED reference (oracle/_ref, author's flags), its own MPI build run
         over oracle/shmpi with one rank per host core (cpu_dim P 1 1), a bounded sample of the
@@ -406,11 +406,11 @@ def our_arm(args, rank, local_rank, world):
         peak, peak_src = measured_peak_gbs()
         achieved = alg_bytes / (p1_ms * 1e-3) / 1e9
         traffic, traffic_src = measured_traffic("k_eam_pass1", natoms)
-        roofline = {"kernel": "k_eam_pass1", "bound": "hbm", "achieved": achieved, "peak": peak,
+        roofline = {"kernel": "k_eam_pass1_fused", "bound": "hbm", "achieved": achieved, "peak": peak,
                     "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                     "peak_source": peak_src, "alg_bytes_per_launch": alg_bytes, "ms_per_launch": p1_ms,
-                    "note": "not HBM-bound: L1 data pipe 77 % (two random 24-byte table rows from shared memory and one "
-                            "32-byte gather per pair), FP64 pipe 33 %, DRAM 8 % (profiles/r01b_full_ncu.txt)"}
+                    "note": "not HBM-bound: L1 data pipe 82 % busy (per pair one random 48-byte table row from shared "
+                            "memory and one 32-byte gather), FP64 pipe 28 %, DRAM 8 % (profiles/r01d_full_ncu.txt)"}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

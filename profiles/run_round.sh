@@ -20,4 +20,9 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --c
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_eam_pass1|k_eam_pass2|k_move_ttm|k_ttm_grid|k_ttm_atoms1|k_ttm_atoms2' \
   --launch-skip 12 -c 6 -f -o $out/${tag}_full \
   python bench.py --ttm --steps 4 --warmup 3 --e2e-steps 1 --profile-steps 1 --no-cpu-baseline > $out/${tag}_ncu_full.log 2>&1; echo "ncu full rc=$?"
+# 3-D TTM sweep (configs[4]): bench line, then one full capture of the sweep kernel
+timeout 600 python bench.py --workload ttm3d --steps 20 --warmup 3 > $out/${tag}_bench_ttm3d.json 2> $out/${tag}_bench_ttm3d.err; echo "ttm3d rc=$?"
+cat $out/${tag}_bench_ttm3d.json
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:k_ttm3d_diff --launch-skip 4 -c 1 -f -o $out/${tag}_ttm3d \
+  python bench.py --workload ttm3d --steps 3 --warmup 3 --e2e-steps 1 --profile-steps 1 --no-cpu-baseline > $out/${tag}_ncu_ttm3d.log 2>&1; echo "ncu ttm3d rc=$?"
 ls -la $out
