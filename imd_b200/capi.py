@@ -97,6 +97,7 @@ def load():
         "imdcu_stream": (vp, [vp]),
         "imdcu_synchronize": (C.c_int, [vp]),
         "imdcu_eval_table": (C.c_int, [vp, C.c_int, C.c_int, C.c_int64, c_dp, c_dp, c_dp]),
+        "imdcu_eval_ttm_math": (C.c_int, [vp, C.c_int, C.c_int64, c_dp, c_dp, c_dp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -306,6 +307,15 @@ class Context:
         out = {k: np.empty(sh, np.int32 if k == "natoms" else np.float64) for k in fields}
         g = out.get
         self._ck(self.L.imdcu_ttm3d_download(self.h, _ip(g("natoms")), _dp(g("temp")), _dp(g("U")), _dp(g("xi"))))
+        return out
+
+    def eval_ttm_math(self, op, a, b=None):
+        """op: 'log', 'exp', 'pow', 'div', 'sqrt', 'rcp' -- the device versions of ttm_math.cuh."""
+        code = {"log": 0, "exp": 1, "pow": 2, "div": 3, "sqrt": 4, "rcp": 5}[op]
+        a = np.ascontiguousarray(a, np.float64)
+        b = None if b is None else np.ascontiguousarray(b, np.float64)
+        out = np.empty_like(a)
+        self._ck(self.L.imdcu_eval_ttm_math(self.h, code, a.size, _dp(a), _dp(b), _dp(out)))
         return out
 
     # ---- inspection

@@ -320,4 +320,13 @@ int  imdcu_multi_sendrecv_x(imdcu_ctx *ctx, int west, int east, const void *s_w,
                             void *r_w, size_t count, int is_int);         // multi.cu
 TabView imdcu_tab_view(const DevTable &t);
 
+// host -> device copy ordered with the context's (non-blocking) stream: a plain cudaMemcpy from pageable
+// memory may return before its last DMA chunk has landed, and kernels on another stream would race it
+static inline cudaError_t imdcu_h2d(imdcu_ctx *c, void *dst, const void *src, size_t bytes)
+{
+  cudaError_t e = cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->stream);
+  if (e != cudaSuccess) return e;
+  return cudaStreamSynchronize(c->stream);
+}
+
 static inline int div_up(int64_t a, int64_t b) { return (int) ((a + b - 1) / b); }

@@ -129,11 +129,11 @@ extern "C" int imdcu_set_table(imdcu_ctx *c, int which, int ncols, int maxsteps,
       o[0] = p0; o[1] = dv; o[2] = d2v;
     }
   CU_CHECK(c, cudaMalloc(&t.coef, coef.size() * sizeof(double)));
-  CU_CHECK(c, cudaMemcpy(t.coef, coef.data(), coef.size() * sizeof(double), cudaMemcpyHostToDevice));
+  CU_CHECK(c, imdcu_h2d(c, t.coef, coef.data(), coef.size() * sizeof(double)));
   std::vector<double> info(3 * (size_t) ncols);
   for (int i = 0; i < ncols; i++) { info[i] = begin[i]; info[ncols + i] = end[i]; info[2 * ncols + i] = invstep[i]; }
   CU_CHECK(c, cudaMalloc(&t.begin, info.size() * sizeof(double)));
-  CU_CHECK(c, cudaMemcpy(t.begin, info.data(), info.size() * sizeof(double), cudaMemcpyHostToDevice));
+  CU_CHECK(c, imdcu_h2d(c, t.begin, info.data(), info.size() * sizeof(double)));
   t.end = t.begin + ncols; t.invstep = t.begin + 2 * ncols;
   t.set = true;
   return IMDCU_OK;
@@ -158,7 +158,7 @@ const double *imdcu_fused_table(imdcu_ctx *c)
   for (size_t k = 0; k < n; k++)
     for (int q = 0; q < 3; q++) { f[6 * k + q] = pc[3 * k + q]; f[6 * k + 3 + q] = rc[3 * k + q]; }
   if (cudaMalloc(&c->fused_coef, f.size() * sizeof(double)) != cudaSuccess) { c->fused_coef = nullptr; return nullptr; }
-  if (cudaMemcpy(c->fused_coef, f.data(), f.size() * sizeof(double), cudaMemcpyHostToDevice) != cudaSuccess) return nullptr;
+  if (imdcu_h2d(c, c->fused_coef, f.data(), f.size() * sizeof(double)) != cudaSuccess) return nullptr;
   c->fused_state = 1;
   return c->fused_coef;
 }
@@ -175,8 +175,8 @@ extern "C" int imdcu_set_params(imdcu_ctx *c, int ntypes, double timestep, int n
   c->restrictions.assign(3 * (size_t) nvtypes, 1.0);
   if (restrictions) c->restrictions.assign(restrictions, restrictions + 3 * (size_t) nvtypes);
   CU_CHECK(c, c->d_restrictions.ensure(c->restrictions.size()));
-  CU_CHECK(c, cudaMemcpy(c->d_restrictions.p, c->restrictions.data(),
-                         c->restrictions.size() * sizeof(double), cudaMemcpyHostToDevice));
+  CU_CHECK(c, imdcu_h2d(c, c->d_restrictions.p, c->restrictions.data(),
+                         c->restrictions.size() * sizeof(double)));
   c->params_set = true;
   return IMDCU_OK;
 }
@@ -304,8 +304,7 @@ extern "C" int imdcu_set_box(imdcu_ctx *c, const double box[9], const int pbc[3]
   CU_CHECK(c, c->d_gplan.ensure(c->gplan.size() + 1));
   CU_CHECK(c, c->gcell_off.ensure(c->gplan.size() + 2));
   if (!c->gplan.empty())
-    CU_CHECK(c, cudaMemcpy(c->d_gplan.p, c->gplan.data(), c->gplan.size() * sizeof(GhostCell),
-                           cudaMemcpyHostToDevice));
+    CU_CHECK(c, imdcu_h2d(c, c->d_gplan.p, c->gplan.data(), c->gplan.size() * sizeof(GhostCell)));
   c->box_set = true;
   c->have_valid_nbl = false;
   return IMDCU_OK;

@@ -147,7 +147,8 @@ __device__ double eos_te_from_r_ee(const EosView &ee, double r, double e)
 // two to four times per cell with identical arguments; here once.  Every arithmetic operation
 // keeps the reference's order; pow/exp/log are the branch-free versions of ttm_math.cuh
 // (pow(x,1.5) and pow(x,2.5) through one sqrt), so that the ~12 transcendental chains of a cell
-// interleave in one thread.  z0p43 = pow(z0, 4/3) is hoisted out of the sub-step loop.
+// interleave in one thread; divisions and square roots are the slow-path-free pdiv / psqrt (<= 1 ulp
+// from the IEEE operation).  z0p43 = pow(z0, 4/3) is hoisted out of the sub-step loop.
 struct WideRange { double Z, ne, kappa, gamma; };
 
 __device__ __forceinline__ WideRange wide_range(double temp_ev, double ti_ev, double dens, double z0, double am,
@@ -160,58 +161,58 @@ __device__ __forceinline__ WideRange wide_range(double temp_ev, double ti_ev, do
     temp *= 1e-3; rho *= 1e-3;
     const double YA1 = 0.003323, YA2 = 0.971832, YA3 = 0.926148e-5, YA4 = 3.10165, YB0 = -1.7630, YB1 = 1.43175,
                  YB2 = 0.315463, YC1 = 0.036666667, YC2 = 0.983333333, YAL = 0.143139e2, YBE = 0.6624e0;
-    const double t0 = temp / z0p43;
-    const double r0 = rho / (z0 * am);
+    const double t0 = pdiv(temp, z0p43);
+    const double r0 = pdiv(rho, z0 * am);
     const double lt0 = plog(t0), lr0 = plog(r0);
-    const double ytf = t0 / (1.0 + t0);
+    const double ytf = pdiv(t0, 1.0 + t0);
     const double ya = YA1 * pexp(YA2 * lt0) + YA3 * pexp(YA4 * lt0);
     const double yb = -pexp(YB0 + YB1 * ytf + YB2 * ytf * ytf);
     const double yc = YC1 * ytf + YC2;
     const double yq1 = ya * pexp(yb * lr0);
-    const double yq = ppow(pexp(yc * lr0) + ppow(yq1, yc), 1.0 / yc);
+    const double yq = ppow(pexp(yc * lr0) + ppow(yq1, yc), prcp(yc));
     const double yx = YAL * ppow(yq, YBE);
-    w.Z = z0 * yx / (1.0 + yx + sqrt(1.0 + 2.0 * yx));
+    w.Z = pdiv(z0 * yx, 1.0 + yx + psqrt(1.0 + 2.0 * yx));
   }
   const double Z = w.Z;
-  const double Ne = w.ne = Z * dens / (am * C_AMU);
+  const double Ne = w.ne = pdiv(Z * dens, am * C_AMU);
   // ---- shared by getKappa and getGamma (both start with Te *= 11604.5; Ti *= 11604.5)
   const double Te = temp_ev * 11604.5, Ti = ti_ev * 11604.5;
-  const double Ni = Ne / Z;
-  const double EF = C_HBAR * C_HBAR * ppow(3.0 * M_PI * M_PI * Ne, 2.0 / 3.0) / 2.0 / C_EMASS;       // fermi_E(Ne)
+  const double Ni = pdiv(Ne, Z);
+  const double EF = pdiv(C_HBAR * C_HBAR * ppow(3.0 * M_PI * M_PI * Ne, 2.0 / 3.0) / 2.0, C_EMASS);       // fermi_E(Ne)
   const double TF = 4.828648689433765e+22 * EF;
-  const double VF = 1.481734876966785e+15 * sqrt(EF);
-  const double r0n = ppow(3.0 / (4 * M_PI * Ni), 1.0 / 3.0);                                           // r0(Ni)
-  const double vth = sqrt(VF * VF + C_BOLTZMAN * Te / C_EMASS);                                        // numax's root
+  const double VF = 1.481734876966785e+15 * psqrt(EF);
+  const double r0n = ppow(pdiv(3.0, 4 * M_PI * Ni), 1.0 / 3.0);                                           // r0(Ni)
+  const double vth = psqrt(VF * VF + pdiv(C_BOLTZMAN * Te, C_EMASS));                                        // numax's root
   // coulomb_log(omega_las, Z, Ni, Te, la) = MAX(2, log(bMax/bMin))
   const double NiZ = Ni * Z;
-  const double ft = 2.0 * (C_HBAR * C_HBAR * ppow(3.0 * M_PI * M_PI * NiZ, 2.0 / 3.0) / 2.0 / C_EMASS) / (3.0 * C_BOLTZMAN);
-  const double teff = sqrt(Te * Te + ft * ft);
-  const double wpl = sqrt(NiZ * C_ECHARGE * C_ECHARGE / C_EMASS / C_ECONST);                           // omega_pl(Ni*Z)
-  const double vte = sqrt(C_BOLTZMAN * teff / (C_EMASS));
-  const double bmax = la ? DMAX(r0n, vte / DMAX(omega_las, wpl)) : DMAX(r0n, vte / wpl);
+  const double ft = pdiv(2.0 * pdiv(C_HBAR * C_HBAR * ppow(3.0 * M_PI * M_PI * NiZ, 2.0 / 3.0) / 2.0, C_EMASS), 3.0 * C_BOLTZMAN);
+  const double teff = psqrt(Te * Te + ft * ft);
+  const double wpl = psqrt(pdiv(pdiv(NiZ * C_ECHARGE * C_ECHARGE, C_EMASS), C_ECONST));                           // omega_pl(Ni*Z)
+  const double vte = psqrt(pdiv(C_BOLTZMAN * teff, C_EMASS));
+  const double bmax = la ? DMAX(r0n, pdiv(vte, DMAX(omega_las, wpl))) : DMAX(r0n, pdiv(vte, wpl));
   const double kTe = C_BOLTZMAN * Te;
-  const double bmin = DMAX(Z * C_ECHARGE * C_ECHARGE / kTe, C_HBAR / sqrt(2 * C_EMASS * C_BOLTZMAN * Te));
-  const double coulomb = DMAX(2.0, plog(bmax / bmin));
-  const double skTe = sqrt(kTe);
+  const double bmin = DMAX(pdiv(Z * C_ECHARGE * C_ECHARGE, kTe), pdiv(C_HBAR, psqrt(2 * C_EMASS * C_BOLTZMAN * Te)));
+  const double coulomb = DMAX(2.0, plog(pdiv(bmax, bmin)));
+  const double skTe = psqrt(kTe);
   const double kTe15 = kTe * skTe, kTe25 = kTe * kTe * skTe;                                           // pow(kTe,1.5), pow(kTe,2.5)
   // ---- getGamma
   {
     const double A1g = 50, A2g = 20, A3g = 0.25, m_atom = 26.9815;
-    const double numet = 1.309202957843054e+11 * (A1g * Ti + A2g * Te * Te / TF);
-    const double numax = A3g / r0n * vth;
-    const double nupl = 1.863839656495274e-40 * Z * Ne * coulomb / kTe15;
+    const double numet = 1.309202957843054e+11 * (A1g * Ti + pdiv(A2g * Te * Te, TF));
+    const double numax = pdiv(A3g, r0n) * vth;
+    const double nupl = pdiv(1.863839656495274e-40 * Z * Ne * coulomb, kTe15);
     const double nu_eff = DMIN(numet, DMIN(numax, nupl));
-    w.gamma = 2.783313120645740e-74 / (m_atom * C_AMU) * Ne * nu_eff;
+    w.gamma = pdiv(2.783313120645740e-74, m_atom * C_AMU) * Ne * nu_eff;
   }
   // ---- getKappa
   {
     const double A1t = 2.95, A2t = 0.5, A3t = 0.16, A4t = 1.2;
-    const double numet = 1.309202957843054e+11 * (A1t * Ti + A2t * Te * Te / TF);
-    const double numax = A3t / r0n * vth;
+    const double numet = 1.309202957843054e+11 * (A1t * Ti + pdiv(A2t * Te * Te, TF));
+    const double numax = pdiv(A3t, r0n) * vth;
     const double nu_eff = DMIN(numet, numax);
-    const double kappa_met = 6.884236239621913e-16 * Ne * Te / nu_eff;
-    const double kappa_pl = 4.428788911416808e+43 * kTe25 / Z / coulomb;
-    const double kappa_wr = kappa_pl + (kappa_met - kappa_pl) * pexp(-A4t * Te / TF);
+    const double kappa_met = pdiv(6.884236239621913e-16 * Ne * Te, nu_eff);
+    const double kappa_pl = pdiv(pdiv(4.428788911416808e+43 * kTe25, Z), coulomb);
+    const double kappa_wr = kappa_pl + (kappa_met - kappa_pl) * pexp(pdiv(-A4t * Te, TF));
     w.kappa = kappa_wr * 0.073768115942029;
   }
   return w;
@@ -723,12 +724,12 @@ extern "C" int imdcu_ttm_set_eos(imdcu_ctx *c, int which, int nx, int ny, const 
   const size_t nd = (size_t) nx + ny + (size_t) nx * ny, ng = (size_t) (nx - 1) * (ny - 1);
   CU_CHECK(c, t.eos_buf[which].ensure(nd));
   CU_CHECK(c, t.eos_diag[which].ensure(ng));
-  CU_CHECK(c, cudaMemcpy(t.eos_buf[which].p, x, nx * sizeof(double), cudaMemcpyHostToDevice));
-  CU_CHECK(c, cudaMemcpy(t.eos_buf[which].p + nx, y, ny * sizeof(double), cudaMemcpyHostToDevice));
-  CU_CHECK(c, cudaMemcpy(t.eos_buf[which].p + nx + ny, z, (size_t) nx * ny * sizeof(double), cudaMemcpyHostToDevice));
+  CU_CHECK(c, imdcu_h2d(c, t.eos_buf[which].p, x, nx * sizeof(double)));
+  CU_CHECK(c, imdcu_h2d(c, t.eos_buf[which].p + nx, y, ny * sizeof(double)));
+  CU_CHECK(c, imdcu_h2d(c, t.eos_buf[which].p + nx + ny, z, (size_t) nx * ny * sizeof(double)));
   if (diag) {
     for (size_t k = 0; k < ng; k++) if (diag[k] > 1) return c->fail(IMDCU_EINVAL, "imdcu_ttm_set_eos: diag entries must be 0 or 1");
-    CU_CHECK(c, cudaMemcpy(t.eos_diag[which].p, diag, ng, cudaMemcpyHostToDevice));
+    CU_CHECK(c, imdcu_h2d(c, t.eos_diag[which].p, diag, ng));
   } else CU_CHECK(c, cudaMemset(t.eos_diag[which].p, 0, ng));
   t.eos_nx[which] = nx; t.eos_ny[which] = ny; t.eos_set[which] = true;
   return IMDCU_OK;
@@ -770,7 +771,7 @@ extern "C" int imdcu_ttm_init(imdcu_ctx *c, const imdcu_ttm_params *p)
   std::vector<TCell> hv(2 * (size_t) nv);
   memset(hv.data(), 0, hv.size() * sizeof(TCell));
   for (int k = 0; k < 2 * nv; k++) { hv[k].dens = p->vlatdens; hv[k].temp = 0.0264; hv[k].md_temp = 0.0264; }   // :1036-1041
-  CU_CHECK(c, cudaMemcpy(t.vlat.p, hv.data(), hv.size() * sizeof(TCell), cudaMemcpyHostToDevice));
+  CU_CHECK(c, imdcu_h2d(c, t.vlat.p, hv.data(), hv.size() * sizeof(TCell)));
   if (!t.d_scal) {
     CU_CHECK(c, cudaMalloc(&t.d_scal, sizeof(TtmScal)));
     CU_CHECK(c, cudaMallocHost(&t.h_scal, sizeof(TtmScal)));
@@ -779,7 +780,7 @@ extern "C" int imdcu_ttm_init(imdcu_ctx *c, const imdcu_ttm_params *p)
   memset(&s0, 0, sizeof s0);
   s0.diff_substeps = 100;                                                         // globals.h:1187
   s0.max_dt_ttm = c->timestep / ((double) p->fd_n_timesteps);
-  CU_CHECK(c, cudaMemcpy(t.d_scal, &s0, sizeof s0, cudaMemcpyHostToDevice));
+  CU_CHECK(c, imdcu_h2d(c, t.d_scal, &s0, sizeof s0));
   if (c->n > 0) {
     CU_CHECK(c, t.fdi.ensure(c->key.cap)); CU_CHECK(c, t.fdi_alt.ensure(c->key.cap));
     CU_CHECK(c, cudaMemset(t.fdi.p, 0, c->key.cap * sizeof(int)));
@@ -927,6 +928,44 @@ int imdcu_ttm_join(imdcu_ctx *c, double out16[16])
   TtmState &t = c->ttm;
   if (t.forked) { CU_CHECK(c, cudaStreamWaitEvent(c->stream, t.ev_join, 0)); t.forked = false; }
   if (out16) return ttm_read_scalars(c, out16);
+  return IMDCU_OK;
+}
+
+// single-function probe of ttm_math.cuh on the device (parity tests): op 0 plog(a), 1 pexp(a),
+// 2 ppow(a,b), 3 pdiv(a,b), 4 psqrt(a), 5 prcp(a)
+__global__ void k_ttm_math_probe(int op, int64_t n, const double *__restrict__ a, const double *__restrict__ b,
+                                 double *__restrict__ out)
+{
+  const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double x = a[i], y = b ? b[i] : 0.0;
+  double r;
+  switch (op) {
+    case 0: r = plog(x); break;
+    case 1: r = pexp(x); break;
+    case 2: r = ppow(x, y); break;
+    case 3: r = pdiv(x, y); break;
+    case 4: r = psqrt(x); break;
+    default: r = prcp(x); break;
+  }
+  out[i] = r;
+}
+
+extern "C" int imdcu_eval_ttm_math(imdcu_ctx *c, int op, int64_t n, const double *a, const double *b, double *out)
+{
+  if (!c || op < 0 || op > 5 || n < 0 || !a || !out || ((op == 2 || op == 3) && !b))
+    return c ? c->fail(IMDCU_EINVAL, "imdcu_eval_ttm_math: bad argument") : IMDCU_EINVAL;
+  if (n == 0) return IMDCU_OK;
+  cudaSetDevice(c->device);
+  double *d = nullptr;
+  CU_CHECK(c, cudaMalloc(&d, 3 * (size_t) n * sizeof(double)));
+  imdcu_h2d(c, d, a, n * sizeof(double));
+  if (b) imdcu_h2d(c, d + n, b, n * sizeof(double));
+  k_ttm_math_probe<<<div_up(n, 256), 256, 0, c->stream>>>(op, n, d, b ? d + n : nullptr, d + 2 * n);
+  cudaStreamSynchronize(c->stream);
+  const cudaError_t e = cudaMemcpy(out, d + 2 * n, n * sizeof(double), cudaMemcpyDeviceToHost);
+  cudaFree(d);
+  CU_CHECK(c, e);
   return IMDCU_OK;
 }
 

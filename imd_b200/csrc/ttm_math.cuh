@@ -34,6 +34,54 @@ static inline double TM_LL2D(long long x) { double r; memcpy(&r, &x, 8); return 
 #define TM_RINT(x) std::nearbyint(x)
 #endif
 
+// 1/d, a/d and sqrt(x) without the IEEE slow paths (the hardware approximation refined by Newton
+// steps, a final residual correction): ~10 straight-line instructions instead of the ~35 of the
+// library routines with their special-case calls.  Arguments must be normal and finite with a
+// normal result (true for every use in the wide-range models); results agree with the IEEE
+// operations to <= 1 ulp (tests/test_ttm_gpu.py::test_device_math).  Host build: the plain operators.
+TM_HD double prcp(double d)
+{
+#if defined(__CUDA_ARCH__)
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
+  double e = TM_FMA(-d, y, 1.0);               // the approximation carries ~20 bits: 40 after one step, 80 after two
+  y = TM_FMA(y, e, y);
+  e = TM_FMA(-d, y, 1.0);
+  return TM_FMA(y, e, y);
+#else
+  return 1.0 / d;
+#endif
+}
+
+TM_HD double pdiv(double a, double d)
+{
+#if defined(__CUDA_ARCH__)
+  const double y = prcp(d);
+  const double q = a * y;
+  const double r = TM_FMA(-q, d, a);
+  return TM_FMA(r, y, q);
+#else
+  return a / d;
+#endif
+}
+
+TM_HD double psqrt(double x)
+{
+#if defined(__CUDA_ARCH__)
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  double g = x * y, h = 0.5 * y;
+  double r = TM_FMA(-h, g, 0.5);               // coupled Newton steps for g -> sqrt(x), h -> 1/(2 sqrt(x))
+  g = TM_FMA(g, r, g); h = TM_FMA(h, r, h);
+  r = TM_FMA(-h, g, 0.5);
+  g = TM_FMA(g, r, g); h = TM_FMA(h, r, h);
+  const double d = TM_FMA(-g, g, x);
+  return TM_FMA(d, h, g);
+#else
+  return std::sqrt(x);
+#endif
+}
+
 // natural logarithm, x normal positive.  m in [sqrt(1/2), sqrt(2)), f = (m-1)/(m+1),
 // log m = 2 atanh f = 2f + 2f^3/3 + ... ; the quotient is refined once so that f carries
 // (almost) no rounding error of its own.
@@ -46,10 +94,11 @@ TM_HD double plog(double x)
   m = up ? m * 0.5 : m;
   e = up ? e + 1 : e;
   const double num = m - 1.0, den = m + 1.0;                                       // num exact
-  double f = num / den;
+  const double rden = prcp(den);                                                   // den in [1.7, 2.42)
+  double f = num * rden;
   // residual of the quotient: num - f*den, with den = m + 1 exact to 1 rounding (err <= 2^-53)
   const double r = TM_FMA(-f, den, num);
-  const double fl = r / den;                                                       // tail of f
+  const double fl = r * rden;                                                      // tail of f
   const double f2 = f * f;
   double p = 2.0 / 23.0;
   p = TM_FMA(p, f2, 2.0 / 21.0);

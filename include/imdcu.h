@@ -211,6 +211,10 @@ int  imdcu_synchronize(imdcu_ctx *ctx);
 int  imdcu_eval_table(imdcu_ctx *ctx, int which, int col, int64_t n, const double *arg,
                       double *val, double *grad);
 
+/* single-function probe of the device log/exp/pow/div/sqrt used by the wide-range models
+ * (imd_ttm.c:2191-2399 call libm): op 0 log(a), 1 exp(a), 2 pow(a,b), 3 a/b, 4 sqrt(a), 5 1/a */
+int  imdcu_eval_ttm_math(imdcu_ctx *ctx, int op, int64_t n, const double *a, const double *b, double *out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -148,3 +148,26 @@ def test_ttm_error_paths():
     with pytest.raises(capi.ImdcuError):                 # calc_ttm before init
         imd.ctx.calc_ttm(0)
     imd.close()
+
+
+def test_device_math():
+    """log/exp/pow/div/sqrt/rcp of ttm_math.cuh as compiled for the device (hardware approximations
+    refined by Newton steps) against libm / IEEE over the magnitudes the wide-range models produce."""
+    from imd_b200 import capi
+    c = capi.Context(0)
+    rng = np.random.default_rng(5)
+    n = 300_000
+    ulps = lambda got, ref: np.abs(got - ref) / np.spacing(np.abs(ref))        # noqa: E731
+    x = np.exp(rng.uniform(-160, 160, n)) * rng.choice([1.0, 1.0], n)
+    y = np.exp(rng.uniform(-160, 160, n)) * rng.choice([-1.0, 1.0], n)
+    assert ulps(c.eval_ttm_math("div", x, y), x / y).max() <= 1.0
+    assert ulps(c.eval_ttm_math("rcp", y), 1.0 / y).max() <= 1.0
+    assert ulps(c.eval_ttm_math("sqrt", x), np.sqrt(x)).max() <= 1.0
+    assert ulps(c.eval_ttm_math("log", x), np.log(x)).max() <= 2.0
+    e = rng.uniform(-700, 700, n)
+    assert ulps(c.eval_ttm_math("exp", e), np.exp(e)).max() <= 1.0
+    xb = np.exp(rng.uniform(-60, 60, n))
+    yb = rng.uniform(-4, 4, n)
+    ref = np.power(xb, yb)
+    assert (np.abs(c.eval_ttm_math("pow", xb, yb) - ref) / ref <= 2.0 ** -51 * (1 + np.abs(yb * np.log(xb)))).all()
+    c.close()
