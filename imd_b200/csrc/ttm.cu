@@ -621,13 +621,14 @@ k_ttm_grid(TtmArgs a)
   const double xi_fac = 26.9815 * C_AMU / 3.0 * 1e30 / ((double) diff_substeps);
   const double invxsq = 1.0 / (a.fd_hx * a.fd_hx);
   const double Imp = 3.769911184307751e+02;
+  const double la_threshold = a.p.tmm_laser_threshold * sqrt(2 * a.p.I0 * Imp);      // imd_tmm.c:200-208, loop invariant
   double Ci = 8.589449886e+02;
   Ci *= a.p.vlatdens; Ci *= 11604.5; Ci *= 1e-30; Ci *= C_J2eV;
   for (int s = 0; s < diff_substeps; s++) {
     // analytic source (replaces do_tmm): I_t and the laser_active switch of imd_tmm.c:197-208
     const double dtl = tmm_time - a.p.laser_t_0;
-    const double I_t = a.p.I0 * exp(-(dtl * dtl) / a.sigma_t_sq);
-    la = !(sqrt(2.0 * I_t * Imp) < a.p.tmm_laser_threshold * sqrt(2 * a.p.I0 * Imp));
+    const double I_t = a.p.I0 * pexp(pdiv(-(dtl * dtl), a.sigma_t_sq));
+    la = !(sqrt(2.0 * I_t * Imp) < la_threshold);
     tmm_time += tau * 10.18 * 1.0e-15;
     for (int c = threadIdx.x; c < ncell + a.p.vlatdim; c += blockDim.x) {
       if (c < ncell) {
