@@ -248,94 +248,215 @@ __device__ __forceinline__ int slab_of(double x, double fd_hx, int G)
   return ig;
 }
 
-#define TTM_WIN 64                   // slabs privatised in shared memory per CTA
+#define TTM_ANT 256                  // threads per CTA in the atom -> slab kernels
+#define TTM_AU 4                     // atoms per lane in flight
 
-// update_fd, first atom loop.  Atoms are cell-sorted (x slowest), so a CTA's atoms fall into
-// a few neighbouring slabs: sums go to a shared-memory window first, one flush per CTA.
+__device__ __forceinline__ int warp_sum_i(int v)
+{
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// update_fd, first atom loop.  Atoms are cell-sorted (x slowest), so a contiguous range of atoms lies in
+// one slab, or -- where a slab boundary cuts through a plane of cells -- alternates between TWO.  Every
+// warp owns a contiguous range (lane-strided, coalesced) and every lane sums its atoms in registers, in
+// two slots (current slab, previous slab); a third slab evicts the older slot by atomics.  At the end
+// the warp reduces the slots of its two lowest slabs by shuffles, the CTA merges its warps in shared
+// memory and ONE thread issues the atomics.  With a few CTAs per SM a slab address sees some thousand
+// atomics per step.  (Measured: seven shared-memory atomics per atom, and later one set of global
+// atomics per slab CHANGE of a lane, both cost 0.3 ms per 2 M atoms -- same-address atomics serialise.)
 // isum = {natoms, totneighs, fluxl, fluxr}[G], dsum = {px, py, pz, mdtemp}[G]
-__global__ void __launch_bounds__(256)
+struct SlabAcc { int ig, n, nn, fl, fr; double px, py, pz; };
+
+__device__ __forceinline__ SlabAcc slab_fresh(int ig) { SlabAcc s = { ig, 0, 0, 0, 0, 0.0, 0.0, 0.0 }; return s; }
+
+__device__ __forceinline__ void slab_flush(const SlabAcc &s, int G, int *isum, double *dsum)
+{
+  if (s.ig < 0 || s.n == 0) return;
+  atomicAdd(&isum[s.ig], s.n); atomicAdd(&isum[G + s.ig], s.nn);
+  if (s.fl) atomicAdd(&isum[2 * G + s.ig], s.fl);
+  if (s.fr) atomicAdd(&isum[3 * G + s.ig], s.fr);
+  atomicAdd(&dsum[s.ig], s.px); atomicAdd(&dsum[G + s.ig], s.py); atomicAdd(&dsum[2 * G + s.ig], s.pz);
+}
+
+__device__ __forceinline__ void slab_add(SlabAcc &r, const SlabAcc &q)
+{
+  r.n += q.n; r.nn += q.nn; r.fl += q.fl; r.fr += q.fr; r.px += q.px; r.py += q.py; r.pz += q.pz;
+}
+
+// make slot a the one of slab ig (b keeps the other slab; a third slab evicts b)
+__device__ __forceinline__ void slab_select(SlabAcc &a, SlabAcc &b, int ig, int G, int *isum, double *dsum)
+{
+  if (ig == a.ig) return;
+  if (ig != b.ig) { slab_flush(b, G, isum, dsum); b = slab_fresh(ig); }
+  const SlabAcc t = a; a = b; b = t;
+}
+
+// the part of a lane's two slots that belongs to slab `target`, summed over the warp
+__device__ __forceinline__ SlabAcc slab_warp_sum(const SlabAcc &a, const SlabAcc &b, int target)
+{
+  const bool ua = a.ig == target, ub = b.ig == target;
+  SlabAcc t;
+  t.ig = target;
+  t.n = warp_sum_i(ua ? a.n : ub ? b.n : 0); t.nn = warp_sum_i(ua ? a.nn : ub ? b.nn : 0);
+  t.fl = warp_sum_i(ua ? a.fl : ub ? b.fl : 0); t.fr = warp_sum_i(ua ? a.fr : ub ? b.fr : 0);
+  t.px = warp_sum(ua ? a.px : ub ? b.px : 0.0); t.py = warp_sum(ua ? a.py : ub ? b.py : 0.0);
+  t.pz = warp_sum(ua ? a.pz : ub ? b.pz : 0.0);
+  return t;
+}
+
+__device__ __forceinline__ int warp_min_slab(int a, int b)
+{
+  int m = a >= 0 ? a : 0x7fffffff;
+  if (b >= 0 && b < m) m = b;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { const int v = __shfl_xor_sync(0xffffffffu, m, o); m = v < m ? v : m; }
+  return m;                                              // 0x7fffffff: no lane holds an atom
+}
+
+// the contiguous atom range of this warp: [b, e)
+__device__ __forceinline__ void warp_range(int n, long long &b, long long &e)
+{
+  const long long nw = (long long) gridDim.x * (TTM_ANT / 32);
+  const long long per = ((n + nw - 1) / nw + 31) / 32 * 32;
+  b = ((long long) blockIdx.x * (TTM_ANT / 32) + (threadIdx.x >> 5)) * per;
+  e = b + per < n ? b + per : n;
+}
+
+__global__ void __launch_bounds__(TTM_ANT)
 k_ttm_atoms1(int n, int G, double fd_hx, int steps, const double4 *__restrict__ pos4,
              const double4 *__restrict__ mom4, const int *__restrict__ type, const int *__restrict__ numneighs,
              int *__restrict__ fdi, int *__restrict__ isum, double *__restrict__ dsum)
 {
-  __shared__ int s_i[4][TTM_WIN];
-  __shared__ double s_d[3][TTM_WIN];
-  __shared__ int s_base;
-  for (int k = threadIdx.x; k < TTM_WIN; k += blockDim.x) {
-    s_i[0][k] = s_i[1][k] = s_i[2][k] = s_i[3][k] = 0;
-    s_d[0][k] = s_d[1][k] = s_d[2][k] = 0.0;
-  }
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  int ig = -1;
-  double4 p = make_double4(0, 0, 0, 0);
-  if (i < n && type[i] == 0) { ig = slab_of(pos4[i].x, fd_hx, G); p = mom4[i]; }
-  if (threadIdx.x == 0) s_base = 1 << 30;
-  __syncthreads();
-  if (ig >= 0) atomicMin(&s_base, ig);
-  __syncthreads();
-  const int base = s_base;
-  if (ig >= 0) {
-    const int nn = numneighs[i];
-    int fl = 0, fr = 0;
-    if (steps > 0) { const int old = fdi[i]; if (old > ig) fr = 1; else if (old < ig) fl = 1; }
-    fdi[i] = ig;
-    const int w = ig - base;
-    if (w < TTM_WIN) {
-      atomicAdd(&s_i[0][w], 1); atomicAdd(&s_i[1][w], nn);
-      if (fl) atomicAdd(&s_i[2][w], 1);
-      if (fr) atomicAdd(&s_i[3][w], 1);
-      atomicAdd(&s_d[0][w], p.x); atomicAdd(&s_d[1][w], p.y); atomicAdd(&s_d[2][w], p.z);
-    } else {
-      atomicAdd(&isum[ig], 1); atomicAdd(&isum[G + ig], nn);
-      if (fl) atomicAdd(&isum[2 * G + ig], 1);
-      if (fr) atomicAdd(&isum[3 * G + ig], 1);
-      atomicAdd(&dsum[ig], p.x); atomicAdd(&dsum[G + ig], p.y); atomicAdd(&dsum[2 * G + ig], p.z);
+  __shared__ SlabAcc s_w[2 * (TTM_ANT / 32)];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  long long b, e;
+  warp_range(n, b, e);
+  SlabAcc s = slab_fresh(-1), o = slab_fresh(-1);
+  for (long long i0 = b + lane; i0 < e; i0 += 32 * TTM_AU) {
+    int ty[TTM_AU], nn[TTM_AU], old[TTM_AU];
+    double x[TTM_AU];
+    double4 p[TTM_AU];
+#pragma unroll
+    for (int u = 0; u < TTM_AU; u++) {                   // all loads of the batch first
+      const long long i = i0 + u * 32;
+      const bool ok = i < e;
+      ty[u] = ok ? type[i] : -1;
+      x[u] = ok ? pos4[i].x : 0.0;
+      p[u] = ok ? mom4[i] : make_double4(0.0, 0.0, 0.0, 1.0);
+      nn[u] = ok ? numneighs[i] : 0;
+      old[u] = ok && steps > 0 ? fdi[i] : 0;
+    }
+#pragma unroll
+    for (int u = 0; u < TTM_AU; u++) {
+      if (ty[u] != 0) continue;
+      const int ig = slab_of(x[u], fd_hx, G);
+      slab_select(s, o, ig, G, isum, dsum);
+      if (steps > 0) { if (old[u] > ig) s.fr++; else if (old[u] < ig) s.fl++; }
+      fdi[i0 + u * 32] = ig;
+      s.n++; s.nn += nn[u];
+      s.px += p[u].x; s.py += p[u].y; s.pz += p[u].z;
     }
   }
+  // warp: the two lowest slabs by shuffle reduction, whatever else a lane holds by its own atomics
+  const int lo = warp_min_slab(s.ig, o.ig), hi = lo == 0x7fffffff ? lo : lo + 1;
+  if (s.ig >= 0 && s.ig != lo && s.ig != hi) slab_flush(s, G, isum, dsum);
+  if (o.ig >= 0 && o.ig != lo && o.ig != hi) slab_flush(o, G, isum, dsum);
+  SlabAcc t0 = slab_warp_sum(s, o, lo), t1 = slab_warp_sum(s, o, hi);
+  if (lo == 0x7fffffff) t0.ig = t1.ig = -1;
+  if (lane == 0) { s_w[2 * warp] = t0; s_w[2 * warp + 1] = t1; }
   __syncthreads();
-  for (int k = threadIdx.x; k < TTM_WIN; k += blockDim.x) {
-    const int g = base + k;
-    if (g < G && s_i[0][k] > 0) {
-      atomicAdd(&isum[g], s_i[0][k]); atomicAdd(&isum[G + g], s_i[1][k]);
-      if (s_i[2][k]) atomicAdd(&isum[2 * G + g], s_i[2][k]);
-      if (s_i[3][k]) atomicAdd(&isum[3 * G + g], s_i[3][k]);
-      atomicAdd(&dsum[g], s_d[0][k]); atomicAdd(&dsum[G + g], s_d[1][k]); atomicAdd(&dsum[2 * G + g], s_d[2][k]);
+  // CTA: warp ranges are consecutive in atom order, so the same two-slot merge works over the warps
+  if (threadIdx.x == 0) {
+    SlabAcc r = slab_fresh(-1), q = slab_fresh(-1);
+    for (int w = 0; w < 2 * (TTM_ANT / 32); w++) {
+      const SlabAcc v = s_w[w];
+      if (v.ig < 0 || v.n == 0) continue;
+      slab_select(r, q, v.ig, G, isum, dsum);
+      slab_add(r, v);
     }
+    slab_flush(r, G, isum, dsum); slab_flush(q, G, isum, dsum);
   }
 }
 
-// update_fd, second atom loop: md_temp sums with v_com = sum p / (natoms * atomic_weight)
-__global__ void __launch_bounds__(256)
+// update_fd, second atom loop: md_temp sums with v_com = sum p / (natoms * atomic_weight); same scheme
+struct TempAcc { int ig; double t, vx, vy, vz; };
+
+__device__ __forceinline__ void temp_select(TempAcc &a, TempAcc &b, int ig, int G, double atomic_weight,
+                                            const int *isum, double *dsum)
+{
+  if (ig == a.ig) return;
+  if (ig != b.ig) {
+    if (b.ig >= 0) atomicAdd(&dsum[3 * G + b.ig], b.t);
+    const double totmass = (double) isum[ig] * atomic_weight;        // > 0: an atom is in the slab
+    b.ig = ig; b.t = 0.0;
+    b.vx = dsum[ig] / totmass; b.vy = dsum[G + ig] / totmass; b.vz = dsum[2 * G + ig] / totmass;
+  }
+  const TempAcc t = a; a = b; b = t;
+}
+
+__global__ void __launch_bounds__(TTM_ANT)
 k_ttm_atoms2(int n, int G, double fd_hx, double atomic_weight, const double4 *__restrict__ mom4,
              const int *__restrict__ type, const int *__restrict__ fdi, const int *__restrict__ isum,
              double *__restrict__ dsum)
 {
-  __shared__ double s_d[TTM_WIN];
-  __shared__ int s_base;
-  for (int k = threadIdx.x; k < TTM_WIN; k += blockDim.x) s_d[k] = 0.0;
-  if (threadIdx.x == 0) s_base = 1 << 30;
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  int ig = -1;
-  if (i < n && type[i] == 0) ig = fdi[i];            // set by k_ttm_atoms1 from the same positions
-  __syncthreads();
-  if (ig >= 0) atomicMin(&s_base, ig);
-  __syncthreads();
-  const int base = s_base;
-  if (ig >= 0) {
-    const double4 p = mom4[i];
-    const double m = p.w;
-    const double totmass = (double) isum[ig] * atomic_weight;      // > 0: this atom is in the slab
-    const double vx = dsum[ig] / totmass, vy = dsum[G + ig] / totmass, vz = dsum[2 * G + ig] / totmass;
-    double d, t = 0.0;
-    d = p.x / m - vx; t += m * (d * d);
-    d = p.y / m - vy; t += m * (d * d);
-    d = p.z / m - vz; t += m * (d * d);
-    const int w = ig - base;
-    if (w < TTM_WIN) atomicAdd(&s_d[w], t); else atomicAdd(&dsum[3 * G + ig], t);
+  __shared__ int s_ig[2 * (TTM_ANT / 32)];
+  __shared__ double s_t[2 * (TTM_ANT / 32)];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  long long b, e;
+  warp_range(n, b, e);
+  TempAcc s = { -1, 0.0, 0.0, 0.0, 0.0 }, o = s;
+  for (long long i0 = b + lane; i0 < e; i0 += 32 * TTM_AU) {
+    int ty[TTM_AU], g[TTM_AU];
+    double4 p[TTM_AU];
+#pragma unroll
+    for (int u = 0; u < TTM_AU; u++) {
+      const long long i = i0 + u * 32;
+      const bool ok = i < e;
+      ty[u] = ok ? type[i] : -1;
+      g[u] = ok ? fdi[i] : 0;                            // set by k_ttm_atoms1 from the same positions
+      p[u] = ok ? mom4[i] : make_double4(0.0, 0.0, 0.0, 1.0);
+    }
+#pragma unroll
+    for (int u = 0; u < TTM_AU; u++) {
+      if (ty[u] != 0) continue;
+      temp_select(s, o, g[u], G, atomic_weight, isum, dsum);
+      const double m = p[u].w;
+      double d, t = 0.0;
+      d = p[u].x / m - s.vx; t += m * (d * d);
+      d = p[u].y / m - s.vy; t += m * (d * d);
+      d = p[u].z / m - s.vz; t += m * (d * d);
+      s.t += t;
+    }
+  }
+  const int lo = warp_min_slab(s.ig, o.ig), hi = lo == 0x7fffffff ? lo : lo + 1;
+  if (s.ig >= 0 && s.ig != lo && s.ig != hi) atomicAdd(&dsum[3 * G + s.ig], s.t);
+  if (o.ig >= 0 && o.ig != lo && o.ig != hi) atomicAdd(&dsum[3 * G + o.ig], o.t);
+  const double t0 = warp_sum(s.ig == lo ? s.t : o.ig == lo ? o.t : 0.0);
+  const double t1 = warp_sum(s.ig == hi ? s.t : o.ig == hi ? o.t : 0.0);
+  const unsigned h1 = __ballot_sync(0xffffffffu, s.ig == hi || o.ig == hi);
+  if (lane == 0) {
+    s_ig[2 * warp] = lo == 0x7fffffff ? -1 : lo; s_t[2 * warp] = t0;
+    s_ig[2 * warp + 1] = lo == 0x7fffffff || !h1 ? -1 : hi; s_t[2 * warp + 1] = t1;
   }
   __syncthreads();
-  for (int k = threadIdx.x; k < TTM_WIN; k += blockDim.x)
-    if (base + k < G && s_d[k] != 0.0) atomicAdd(&dsum[3 * G + base + k], s_d[k]);
+  if (threadIdx.x == 0) {
+    int ia = -1, ib = -1;
+    double ta = 0.0, tb = 0.0;
+    for (int w = 0; w < 2 * (TTM_ANT / 32); w++) {
+      const int ig = s_ig[w];
+      if (ig < 0) continue;
+      if (ig != ia) {
+        if (ig != ib) { if (ib >= 0) atomicAdd(&dsum[3 * G + ib], tb); ib = ig; tb = 0.0; }
+        const int ii = ia; ia = ib; ib = ii;
+        const double tt = ta; ta = tb; tb = tt;
+      }
+      ta += s_t[w];
+    }
+    if (ia >= 0) atomicAdd(&dsum[3 * G + ia], ta);
+    if (ib >= 0) atomicAdd(&dsum[3 * G + ib], tb);
+  }
 }
 
 // ----------------------------------------------------------------------------- grid kernel
@@ -833,9 +954,10 @@ static int ttm_atoms_part(imdcu_ctx *c, int steps)
   }
   CU_CHECK(c, cudaMemsetAsync(t.isum.p, 0, 4 * (size_t) G * sizeof(int), st));
   CU_CHECK(c, cudaMemsetAsync(t.dsum.p, 0, 4 * (size_t) G * sizeof(double), st));
-  const int nb = div_up(std::max(n, 1), 256);
+  // a few CTAs per SM, every warp a contiguous atom range of at least 32 * TTM_AU atoms
+  const int nb = std::max(1, std::min(c->num_sms * 4, div_up(n, TTM_ANT * TTM_AU)));
   if (n > 0) {
-    k_ttm_atoms1<<<nb, 256, 0, st>>>(n, G, t.fd_hx, steps, c->pos4.p, c->mom4.p, c->type.p, c->numneighs.p,
+    k_ttm_atoms1<<<nb, TTM_ANT, 0, st>>>(n, G, t.fd_hx, steps, c->pos4.p, c->mom4.p, c->type.p, c->numneighs.p,
                                      t.fdi.p, t.isum.p, t.dsum.p);
     c->count_launch();
   }
@@ -844,7 +966,7 @@ static int ttm_atoms_part(imdcu_ctx *c, int steps)
   RET_IF(imdcu_multi_allreduce(c, t.isum.p, 4 * G, 2));
   RET_IF(imdcu_multi_allreduce(c, t.dsum.p, 3 * G, 0));
   if (n > 0) {
-    k_ttm_atoms2<<<nb, 256, 0, st>>>(n, G, t.fd_hx, t.p.atomic_weight, c->mom4.p, c->type.p, t.fdi.p, t.isum.p,
+    k_ttm_atoms2<<<nb, TTM_ANT, 0, st>>>(n, G, t.fd_hx, t.p.atomic_weight, c->mom4.p, c->type.p, t.fdi.p, t.isum.p,
                                      t.dsum.p);
     c->count_launch();
   }
