@@ -82,6 +82,7 @@ def load():
         "imdcu_move_atoms_ttm": (C.c_int, [vp, c_dp, c_ip]),
         "imdcu_run_ttm": (C.c_int, [vp, C.c_int, C.c_int, c_dp]),
         "imdcu_download_ttm": (C.c_int, [vp, c_dp, c_dp, c_dp, c_dp]),
+        "imdcu_set_nrb": (C.c_int, [vp, C.c_double, C.c_int64, c_ip, c_ip, c_ip, c_dp, C.c_int]),
         "imdcu_ttm3d_init": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, c_dp, c_ip, C.c_int]),
         "imdcu_ttm3d_upload": (C.c_int, [vp, c_ip, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp]),
         "imdcu_ttm3d_diff": (C.c_int, [vp, C.c_double, C.c_int, C.c_int, C.c_int, c_dp]),
@@ -179,6 +180,15 @@ class Context:
 
     def set_pdecay(self, enabled, xipdecay=0.0, ramp_start=0.0, ramp_end=1.0):
         self._ck(self.L.imdcu_set_pdecay(self.h, int(enabled), xipdecay, ramp_start, ramp_end))
+
+    def set_nrb(self, nrb_k, ids, bnd, nrbi, refpos, startup_images=False):
+        """imdcu_set_nrb: entries for the boundary atoms and their listed neighbours (ids empty: off)."""
+        ids = np.ascontiguousarray(ids, np.int32); bnd = np.ascontiguousarray(bnd, np.int32)
+        nrbi = np.ascontiguousarray(nrbi, np.int32).reshape(-1, 12); refpos = np.ascontiguousarray(refpos, np.float64).reshape(-1, 3)
+        n = ids.shape[0]
+        if not (bnd.shape[0] == n and nrbi.shape[0] == n and refpos.shape[0] == n):
+            raise ValueError("set_nrb: ids, bnd, nrbi, refpos must have one row per entry")
+        self._ck(self.L.imdcu_set_nrb(self.h, float(nrb_k), n, _ip(ids), _ip(bnd), _ip(nrbi), _dp(refpos), int(bool(startup_images))))
 
     # ---- atoms
     def upload_atoms(self, pos, mom, mass, types=None, ids=None, vtypes=None):

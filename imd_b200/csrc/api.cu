@@ -18,15 +18,18 @@ static int check_ready(imdcu_ctx *c)
 // calc_forces (imd_forces_nbl.c:295-1054)
 extern "C" int imdcu_calc_forces(imdcu_ctx *c, int steps, double out8[8])
 {
-  (void) steps;
   RET_IF(check_ready(c));
   if (!c->have_valid_nbl) {
     RET_IF(imdcu_rebuild_cells(c));              // fix_cells (:304)
     RET_IF(imdcu_refresh_ghosts(c, true));       // send_cells(copy_cell) (:311)
     RET_IF(imdcu_build_nblist(c));               // make_nblist (:315)
+    RET_IF(imdcu_nrb_reindex(c, false));
   } else {
     RET_IF(imdcu_refresh_ghosts(c, false));
   }
+  // nrb_forces (:1019-1021) reads positions, momenta and the list, not the forces: it runs first, so
+  // that calc_ttm (forked between the EAM passes by imdcu_run_ttm) sees the new boundary momenta
+  RET_IF(imdcu_nrb_forces(c, steps));
   return imdcu_eam_forces(c, out8);
 }
 
@@ -131,7 +134,7 @@ extern "C" int imdcu_synchronize(imdcu_ctx *c)
   if (!c) return IMDCU_EINVAL;
   cudaSetDevice(c->device);
   CU_CHECK(c, cudaStreamSynchronize(c->stream));
-  return IMDCU_OK;
+  return imdcu_check_flags(c);
 }
 
 // ----------------------------------------------------------------------------- table probe

@@ -98,6 +98,7 @@ extern "C" int imdcu_upload_atoms(imdcu_ctx *c, int64_t n, const int32_t *id, co
   CU_CHECK(c, cudaStreamSynchronize(s));
   c->n = n; c->ng = 0;
   c->have_valid_nbl = false;
+  if (c->nrb.active) { RET_IF(imdcu_nrb_reindex(c, true)); CU_CHECK(c, cudaStreamSynchronize(s)); }
   return IMDCU_OK;
 }
 

@@ -175,6 +175,16 @@ struct Ttm3dState {
   double *d_eabs = nullptr;
 };
 
+// ----------------------------------------------------------------------------- NRB (nrb.cu)
+#define IMDCU_VTYPE_NRB (1 << 30)     // vtype bit: NRBBND > 0, the integrators leave the atom without a kick
+struct NrbState {
+  bool   active = false, startup_images = false;
+  int    nent = 0, maxid = 0;
+  double k = 0.0;                     // sqrt(nrb_k / 26.9815), imd_nrb.c:149
+  DevBuf<int>    ent_bnd, ent_nrbi, ent_index, slot_of_id;   // [nent], [12 nent], [nent], [maxid + 1]
+  DevBuf<double> ent_ref, ent_newp;                           // [3 nent]
+};
+
 // ----------------------------------------------------------------------------- context
 struct imdcu_ctx {
   int          device = 0;
@@ -241,6 +251,7 @@ struct imdcu_ctx {
 
   TtmState ttm;
   Ttm3dState ttm3d;
+  NrbState nrb;
 
   // multi-GPU (x-slab decomposition, multi.cu); nranks == 1: everything below is unused
   struct Comm {
@@ -316,6 +327,10 @@ void imdcu_ttm_release(imdcu_ctx *ctx);                                // ttm.cu
 int  imdcu_ttm_fork(imdcu_ctx *ctx, int steps);                        // ttm.cu
 int  imdcu_ttm_join(imdcu_ctx *ctx, double out16[16]);
 void imdcu_ttm3d_release(imdcu_ctx *ctx);                              // ttm3d.cu
+void imdcu_nrb_release(imdcu_ctx *ctx);                                // nrb.cu
+int  imdcu_nrb_reindex(imdcu_ctx *ctx, bool mark);                     // after a cell sort
+int  imdcu_nrb_forces(imdcu_ctx *ctx, int steps);                      // nrb_forces (imd_nrb.c:792)
+int  imdcu_check_flags(imdcu_ctx *ctx);                                // nblist.cu: device-side error flags
 int  imdcu_multi_sendrecv_x(imdcu_ctx *ctx, int west, int east, const void *s_w, const void *s_e, void *r_e,
                             void *r_w, size_t count, int is_int);         // multi.cu
 TabView imdcu_tab_view(const DevTable &t);

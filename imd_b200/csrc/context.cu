@@ -71,7 +71,7 @@ extern "C" int imdcu_destroy(imdcu_ctx *c)
   c->nbl_idx.release(); c->nbl_num.release(); c->partials.release(); c->d_restrictions.release();
   if (c->fused_coef) cudaFree(c->fused_coef);
   imdcu_ttm_release(c);
-  imdcu_ttm3d_release(c);
+  imdcu_ttm3d_release(c); imdcu_nrb_release(c);
   imdcu_multi_release(c);
   c->ghost_gid.release();
   for (int t = 0; t < 3; t++) {

@@ -23,13 +23,16 @@ k_move_nve(MoveArgs a)
     double4 p = a.mom4[i];
     const double4 f4 = a.frc4[i];
     double4 x = a.pos4[i];
-    const double *rs = a.restrictions + 3 * a.vtype[i];
+    const int vt = a.vtype[i];
+    const double *rs = a.restrictions + 3 * (vt & ~IMDCU_VTYPE_NRB);
     const double m = p.w;
     const double k1 = p.x * p.x + p.y * p.y + p.z * p.z;
-    double fx = f4.x * rs[0], fy = f4.y * rs[1], fz = f4.z * rs[2];
-    if (a.pdecay && x.x > a.ramp_start)
-      fx -= (p.x / m) * a.xipdecay * a.pd_a * (x.x - a.ramp_start) * (x.x - a.ramp_start);
-    p.x += a.timestep * fx; p.y += a.timestep * fy; p.z += a.timestep * fz;
+    if (!(vt & IMDCU_VTYPE_NRB)) {                       // NRB boundary atoms: no kick (imd_integrate.c:233-259)
+      double fx = f4.x * rs[0], fy = f4.y * rs[1], fz = f4.z * rs[2];
+      if (a.pdecay && x.x > a.ramp_start)
+        fx -= (p.x / m) * a.xipdecay * a.pd_a * (x.x - a.ramp_start) * (x.x - a.ramp_start);
+      p.x += a.timestep * fx; p.y += a.timestep * fy; p.z += a.timestep * fz;
+    }
     const double k2 = p.x * p.x + p.y * p.y + p.z * p.z;
     ekin[0] += (k1 + k2) / (4 * m);
     const double tmp = a.timestep / m;
@@ -55,7 +58,8 @@ k_move_ttm(MoveArgs a, const int *__restrict__ type, int G, double fd_hx,
     double4 p = a.mom4[i];
     const double4 f4 = a.frc4[i];
     double4 x = a.pos4[i];
-    const double *rs = a.restrictions + 3 * a.vtype[i];
+    const int vt = a.vtype[i];
+    const double *rs = a.restrictions + 3 * (vt & ~IMDCU_VTYPE_NRB);
     const double m = p.w;
     int ig = 0;
     double xi = 0.0;
@@ -66,13 +70,15 @@ k_move_ttm(MoveArgs a, const int *__restrict__ type, int G, double fd_hx,
       xi = xiarr[ig];
     }
     const double k1 = p.x * p.x + p.y * p.y + p.z * p.z;
-    double fx = f4.x * rs[0], fy = f4.y * rs[1], fz = f4.z * rs[2];
-    if (a.pdecay && x.x > a.ramp_start)
-      fx -= (p.x / m) * a.xipdecay * a.pd_a * (x.x - a.ramp_start) * (x.x - a.ramp_start);
-    const double vx = vcom[ig], vy = vcom[G + ig], vz = vcom[2 * G + ig];
-    p.x += a.timestep * (fx + xi * m * (p.x / m - vx));
-    p.y += a.timestep * (fy + xi * m * (p.y / m - vy));
-    p.z += a.timestep * (fz + xi * m * (p.z / m - vz));
+    if (!(vt & IMDCU_VTYPE_NRB)) {                       // NRB boundary atoms: no kick, no heating (:712-751)
+      double fx = f4.x * rs[0], fy = f4.y * rs[1], fz = f4.z * rs[2];
+      if (a.pdecay && x.x > a.ramp_start)
+        fx -= (p.x / m) * a.xipdecay * a.pd_a * (x.x - a.ramp_start) * (x.x - a.ramp_start);
+      const double vx = vcom[ig], vy = vcom[G + ig], vz = vcom[2 * G + ig];
+      p.x += a.timestep * (fx + xi * m * (p.x / m - vx));
+      p.y += a.timestep * (fy + xi * m * (p.y / m - vy));
+      p.z += a.timestep * (fz + xi * m * (p.z / m - vz));
+    }
     const double k2 = p.x * p.x + p.y * p.y + p.z * p.z;
     ekin[0] += (k1 + k2) / (4 * m);
     const double tmp = a.timestep / m;

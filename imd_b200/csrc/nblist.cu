@@ -60,11 +60,23 @@ k_nbl_build(Geom g, int n, const double4 *__restrict__ pos4, const int *__restri
   if (lane == 0 && mx > 0) atomicMax(&flags[1], mx);
 }
 
+// error flags that kernels raise between two list builds (the build resets them)
+int imdcu_check_flags(imdcu_ctx *c)
+{
+  CU_CHECK(c, cudaMemcpyAsync(c->h_flags, c->d_flags, 8 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CU_CHECK(c, cudaStreamSynchronize(c->stream));
+  if (c->h_flags[4]) return c->fail(IMDCU_EINVAL, "an atom crossed more than one x slab between two cell sorts");
+  if (c->h_flags[5]) return c->fail(IMDCU_EINVAL, "NRB: a listed neighbour of a boundary atom lives on another GPU");
+  if (c->h_flags[6]) return c->fail(IMDCU_EINVAL, "NRB: a listed neighbour of a boundary atom has no entry");
+  return IMDCU_OK;
+}
+
 int imdcu_build_nblist(imdcu_ctx *c)
 {
   PhaseTimer pt(c, 1);
   const int n = (int) c->n;
   cudaStream_t st = c->stream;
+  RET_IF(imdcu_check_flags(c));
   if (n == 0) { c->have_valid_nbl = true; c->nbl_count++; return IMDCU_OK; }
   const int nb = div_up(n, 128);
   const size_t ntiles = (size_t) div_up(n, 32);

@@ -105,6 +105,17 @@ class Imd:
             self.tot_pot_energy, self.tot_kin_energy = float(e[-1, 0]), float(e[-1, 1])
         return e
 
+    # init_nrb (imd_forces_nbl.c:281-282, first calc_forces): NRB state to the device
+    def set_nrb(self, nrb_k, state=None, startup_images=False):
+        """state: imd_b200.nrb.NrbState (from nrb.init_nrb, or filled from the reference's .nrb restart
+        data); None switches NRB off.  startup_images: see imdcu_set_nrb."""
+        if state is None:
+            e = np.zeros(0, np.int32)
+            self.ctx.set_nrb(1.0, e, e, np.zeros((0, 12), np.int32), np.zeros((0, 3)))
+            return
+        ids, bnd, nrbi, refpos = state.entries()
+        self.ctx.set_nrb(nrb_k, ids, bnd, nrbi, refpos, startup_images)
+
     # init_ttm + tmm_init (imd.c:237,245): EOS tables + TTM parameters
     def init_ttm(self, tp, eos, nranks_ref=1):
         self.ctx.ttm_set_eos(capi_EOS_CVE, eos["cve"])

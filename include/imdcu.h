@@ -115,6 +115,27 @@ int  imdcu_move_atoms_nve(imdcu_ctx *ctx, double out8[8], int *have_valid_nbl);
  * energies[2*s] = tot_pot_energy, energies[2*s+1] = tot_kin_energy (may be NULL). */
 int  imdcu_run_nve(imdcu_ctx *ctx, int first_step, int nsteps, double *energies);
 
+/* ------------------------------------------------------------------ non-reflecting boundary */
+/* The NRB state init_nrb leaves per atom (imd_nrb.c:125-768; cell members isnrbbnd, nrbid[12],
+ * refpos: makros.h:192-200,257), for every boundary atom (bnd = NRBBND 1..3) and every atom one of
+ * them lists as a lattice-site neighbour (bnd = 0):
+ *   id[nent]        atom numbers (NUMMER; the reference counts from 1, 0 marks an unset site)
+ *   bnd[nent]       NRBBND
+ *   nrbi[nent][12]  NRBI: atom numbers of the twelve fcc sites, 0 = unset (rows of bnd = 0 are ignored)
+ *   refpos[nent][3] REF_POS
+ * nrb_k is the parameter of that name (imd_param.c:2109; init_nrb takes sqrt(nrb_k / 26.9815)).
+ * Call after imdcu_upload_atoms.  From then on imdcu_calc_forces(steps) runs nrb_forces
+ * (imd_nrb.c:792-1129; call site imd_forces_nbl.c:1019-1021, steps > 1 only) and both integrators skip
+ * the kick of boundary atoms (imd_integrate.c:233-259, 712-751).  startup_images != 0 also reproduces
+ * what the reference does to boundary momenta for steps <= 1 (its send_forces adds the momenta of the
+ * buffer-cell copies, imd_comm_force_3d.c:1046-1052,1157-1168: momentum times the number of periodic
+ * y/z images of the atom's cell, for cpu_dim = (P,1,1)).  nent = 0 switches NRB off.
+ * Several GPUs: every rank passes the full table; a boundary atom and its listed neighbours must be
+ * owned by the same rank (they are a/2 apart in x; slabs are cells wide) -- otherwise the next
+ * list build or imdcu_synchronize returns an error. */
+int  imdcu_set_nrb(imdcu_ctx *ctx, double nrb_k, int64_t nent, const int32_t *id, const int32_t *bnd,
+                   const int32_t *nrbi, const double *refpos, int startup_images);
+
 /* ------------------------------------------------------------------ two-temperature model (1-D) */
 /* Run-time parameters of the 1-D TTM: the keywords of imd_param.c:1979-2092 and the globals
  * init_ttm / tmm_init derive from them (imd_ttm.c:955-1201, imd_tmm.c:98-190).

@@ -137,6 +137,30 @@ void __wrap_calc_forces(int steps)
 #endif
   }
 
+#ifdef NRB
+  /* per-atom NRB state as init_nrb left it (imd_nrb.c:125-768): boundary type, neighbour flag, the
+   * numbers of the 12 lattice sites, reference position; post_mom above is the momentum AFTER
+   * nrb_forces (imd_forces_nbl.c:1019-1021) */
+  {
+    FILE *fb = dump_open(dir, steps, "post_nrbbnd");
+    FILE *fg = dump_open(dir, steps, "post_nrbneigh");
+    FILE *fi = dump_open(dir, steps, "post_nrbi");
+    FILE *fr = dump_open(dir, steps, "post_refpos");
+    for (k = 0; k < ncells; k++) {
+      cell *p = CELLPTR(k);
+      for (i = 0; i < p->n; i++) {
+        int b = NRBBND(p, i), g = NRBNEIGH(p, i), id12[12], r;
+        double x[3];
+        for (r = 0; r < 12; r++) id12[r] = NRBI(p, i, r);
+        x[0] = REF_POS(p, i, X); x[1] = REF_POS(p, i, Y); x[2] = REF_POS(p, i, Z);
+        fwrite(&b, sizeof b, 1, fb); fwrite(&g, sizeof g, 1, fg);
+        fwrite(id12, sizeof(int), 12, fi); fwrite(x, sizeof(double), 3, fr);
+      }
+    }
+    fclose(fb); fclose(fg); fclose(fi); fclose(fr);
+  }
+#endif
+
   /* half neighbour list as (id_i, id_j) pairs, only when it was rebuilt now */
   if (nbl_count != nbl_before) {
     FILE *fp = dump_open(dir, steps, "post_nblpairs");

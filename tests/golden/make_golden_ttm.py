@@ -26,6 +26,7 @@ sys.path.insert(0, ROOT)
 from imd_b200 import synth  # noqa: E402
 
 REF_BIN = os.path.join(ROOT, "oracle", "_ref", "imd_ref_mpi_eam_ttm")
+REF_BIN_NRB = os.path.join(ROOT, "oracle", "_ref", "imd_ref_mpi_eam_ttm_nrb")   # + -DNRB -DREFPOS, imd_nrb.c
 NN_PROBE = os.path.join(ROOT, "oracle", "_ref", "nn_probe")
 
 CASES = {
@@ -39,6 +40,14 @@ CASES = {
                                                            fd_min_atoms=20, vlatbuffer=1), 30,
                               (0, 1, 10, 20, 30), 25.0, 15.0, 0.12,
                               "xipdecay 0.5\nramp_start 180.0\nramp_end 200.0\n"),
+    # non-reflecting rear boundary (imd_nrb.c): warm lattice + pulse, so that the boundary plane and
+    # its four neighbours per atom move; steps 0 and 1 run without nrb_forces (steps > 1 only)
+    "ttm_nrb_al_40x5x5_p2": ((40, 5, 5), 2, synth.TtmParams(ttmdimx=10, fd_n_timesteps=20, I0=2.0e16), 24,
+                              (0, 1, 2, 3, 12, 24), 20.0, 20.0, 0.05,
+                              "nrb_alat 4.05\nnrb_eps 0.3\nnrb_k 1.2\n"),
+    "ttm_nrb_al_56x5x6_p4": ((56, 5, 6), 4, synth.TtmParams(ttmdimx=16, fd_n_timesteps=20, I0=3.0e16), 20,
+                              (0, 2, 3, 10, 20), 20.0, 20.0, 0.08,
+                              "nrb_alat 4.05\nnrb_eps 0.3\nnrb_k 0.9\n"),
 }
 
 
@@ -59,13 +68,22 @@ def load_atoms(d, step, nranks):
     out["force"] = cat("post_force", np.float64, 3)
     out["numneighs"] = cat("post_numneighs", np.int32)
     out["scalars"] = rd(d, step, "post_scalars", 0, np.float64)
+    nrb = os.path.exists(os.path.join(d, "s%d.post_nrbbnd.r0.bin" % step))
+    if nrb:
+        out["pre_id"] = cat("pre_id", np.int32)
+        out["pre_mom"] = cat("pre_mom", np.float64, 3)[np.argsort(out["pre_id"], kind="stable")]
+        del out["pre_id"]
+        out["nrbbnd"] = cat("post_nrbbnd", np.int32)
+        out["nrbneigh"] = cat("post_nrbneigh", np.int32)
+        out["nrbi"] = cat("post_nrbi", np.int32, 12)
+        out["refpos"] = cat("post_refpos", np.float64, 3)
     # sort everything by atom id so that the fixture does not depend on the decomposition
     for tag in ("post",):
         o = np.argsort(out[tag + "_id"], kind="stable")
         for k in ("_id", "_pos", "_mom"):
             out[tag + k] = out[tag + k][o]
         if tag == "post":
-            for k in ("type", "mass", "force", "numneighs"):
+            for k in ("type", "mass", "force", "numneighs") + (("nrbbnd", "nrbneigh", "nrbi", "refpos") if nrb else ()):
                 out[k] = out[k][o]
     return out
 
@@ -139,13 +157,18 @@ def run_case(name, box_param, nranks, tp, steps, dump_steps, sfront, srear, star
         env = dict(os.environ, SHMPI_NP=str(nranks), IMD_DUMP_DIR="dump",
                    IMD_DUMP_STEPS=",".join(str(s) for s in dump_steps),
                    IMD_SRC_MU="%.17g" % tp.src_mu, IMD_SRC_ABS="%.17g" % tp.src_abs)
-        res = subprocess.run([REF_BIN, "-p", "run.param"], cwd=run, env=env, stdout=subprocess.PIPE,
+        res = subprocess.run([REF_BIN_NRB if "nrb_alat" in extra else REF_BIN, "-p", "run.param"], cwd=run, env=env, stdout=subprocess.PIPE,
                              stderr=subprocess.STDOUT, text=True, timeout=600)
         if res.returncode != 0:
             print(res.stdout[-3000:])
             raise RuntimeError("reference TTM run failed for %s" % name)
         for s in dump_steps:
             for k, v in load_atoms(os.path.join(run, "dump"), s, nranks).items():
+                if k in ("nrbbnd", "nrbneigh", "nrbi", "refpos"):      # static after init_nrb: kept once
+                    if "nrb_" + k in arrays:
+                        assert np.array_equal(arrays["nrb_" + k], v), "NRB state changed at step %d" % s
+                    arrays["nrb_" + k] = v
+                    continue
                 arrays["s%d_%s" % (s, k)] = v
             for k, v in load_ttm(os.path.join(run, "dump"), s, nranks).items():
                 arrays["s%d_ttm_%s" % (s, k)] = v

@@ -18,6 +18,7 @@ from imd_b200 import synth
 
 GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 TTM_CASES = ["ttm_al_56x6x6_p2", "ttm_al_56x6x6_p4", "ttm_al_48x5x5_p2_hot"]
+NRB_CASES = ["ttm_nrb_al_40x5x5_p2", "ttm_nrb_al_56x5x6_p4"]     # reference built with -DNRB -DREFPOS
 TTM_FIELDS = ["natoms", "natoms_old", "temp", "md_temp", "xi", "dens", "fd_k", "fd_g", "Z", "ne", "Ce", "U",
               "source"]
 TE_ABS_K = 5e-5             # K: a few times fminbnd's tolx
@@ -45,9 +46,22 @@ class TtmGolden:
         self.margin = float(z["nbl_margin"])
         self.pdecay = None
         extra = str(z["extra"])
-        if "xipdecay" in extra:
-            kv = dict(ln.split() for ln in extra.strip().splitlines())
+        kv = dict(ln.split() for ln in extra.strip().splitlines())
+        if "xipdecay" in kv:
             self.pdecay = (1, float(kv["xipdecay"]), float(kv["ramp_start"]), float(kv["ramp_end"]))
+        self.nrb = None
+        if "nrb_k" in kv:
+            self.nrb = dict(nrb_k=float(kv["nrb_k"]), nrb_alat=float(kv["nrb_alat"]), nrb_eps=float(kv["nrb_eps"]))
+
+    def nrb_state(self):
+        """NRB state of init_nrb (static), rows in atom-number order like atoms(s)."""
+        from imd_b200.nrb import NrbState
+        z = self.z
+        return NrbState(z["s0_post_id"], z["nrb_nrbbnd"], z["nrb_nrbneigh"], z["nrb_nrbi"], z["nrb_refpos"])
+
+    def pre_mom(self, s):
+        """momenta BEFORE calc_forces(s) (NRB cases: nrb_forces changes them inside calc_forces)."""
+        return self.z["s%d_pre_mom" % s]
 
     def atoms(self, s):
         z = self.z
