@@ -24,6 +24,8 @@ N > 1  : weak scaling -- every GPU owns an x slab of --cells cubic cells (cpu_di
 from __future__ import annotations
 
 import argparse
+import contextlib
+import io
 import json
 import os
 import re
@@ -254,6 +256,9 @@ def workload_config(args):
         w = ("Al fcc EAM2 + 1-D TTM film (calc_forces, calc_ttm, move_atoms_ttm), %dx%dx%d cubic cells = %d atoms per "
              "GPU, vacuum 10 a front and rear, pbc 0 1 1, 300 K, timestep 0.1, nbl_margin 0.4, FD cell ~16 A, "
              "fd_n_timesteps %d (BASELINE.json configs[2] shape)" % (c[0], c[1], c[2], n, args.ttm_substeps))
+        if getattr(args, "nrb", False):
+            w += (", non-reflecting rear boundary (nrb_forces on the last atomic layer, nrb_k 1.2; "
+                  "BASELINE.json configs[3] shape)")
     else:
         w = ("Al fcc EAM2 NVE slab, %dx%dx%d cubic cells = %d atoms per GPU, 300 K, timestep 0.1 (1.018 fs), "
              "nbl_margin 0.4 (BASELINE.json configs[1])" % (c[0], c[1], c[2], n))
@@ -281,8 +286,22 @@ def build_system(cells, rank=0, world=1, ttm=False):
     pos, box = synth.fcc_lattice((max(i1 - i0, 0), cells[1], cells[2]), a)
     pos[:, 0] += i0 * a + vac
     box[0, 0] = lx
-    ids = (np.arange(pos.shape[0], dtype=np.int64) + 4 * i0 * cells[1] * cells[2]).astype(np.int32)
+    ids = (np.arange(pos.shape[0], dtype=np.int64) + 4 * i0 * cells[1] * cells[2] + 1).astype(np.int32)
     return spec, pos, box, ids
+
+
+def rear_boundary_state(cells, world):
+    """NRB state of the film's rear (+x) surface: init_nrb (host mirror, imd_b200/nrb.py) on the last
+    lattice cell layer, which holds the boundary layer and the layer of its listed neighbours.  Every
+    rank builds the same table; only the rank that owns those atoms finds them."""
+    from imd_b200 import nrb, synth
+    spec = synth.AL
+    ncx = cells[0] * world
+    pos, box = synth.fcc_lattice((1, cells[1], cells[2]), spec.a)
+    pos[:, 0] += (ncx - 1) * spec.a + 10 * spec.a
+    box[0, 0] = ncx * spec.a + 20 * spec.a
+    ids = (np.arange(pos.shape[0], dtype=np.int64) + 4 * (ncx - 1) * cells[1] * cells[2] + 1).astype(np.int32)
+    return nrb.init_nrb(pos, ids, box, (0, 1, 1), spec.a, 0.3)
 
 
 def our_arm(args, rank, local_rank, world):
@@ -325,6 +344,11 @@ def our_arm(args, rank, local_rank, world):
         tp = synth.TtmParams(ttmdimx=gx, fd_n_timesteps=args.ttm_substeps, fd_min_atoms=100, vlatdim=30,
                              vlatbuffer=8, I0=5.0e15, laser_t_0=100e-15, laser_sigma_t=42.5e-15)
         imd.init_ttm(tp, eos, world)
+    if args.nrb:
+        st = rear_boundary_state(args.cells, world)
+        if int((st.bnd == 1).sum()) != 2 * args.cells[1] * args.cells[2]:
+            raise SystemExit("bench.py: NRB setup did not find the rear layer")
+        imd.set_nrb(1.2, st)
     run = (lambda first, n: ctx.run_ttm(first, n, False)) if args.ttm else (lambda first, n: ctx.run_nve(first, n, False))
     stream = torch.cuda.ExternalStream(ctx.stream, device=local_rank)
 
@@ -621,6 +645,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ttm", action="store_true", help="EAM + TTM step (BASELINE.json configs[2])")
     ap.add_argument("--ttm-substeps", type=int, default=250, help="fd_n_timesteps (manual example: 250)")
+    ap.add_argument("--nrb", action="store_true",
+                    help="with --ttm: non-reflecting rear boundary (BASELINE.json configs[3])")
     ap.add_argument("--workload", default="md", choices=["md", "ttm3d"],
                     help="md: EAM(+TTM) atom-steps/s (headline); ttm3d: standalone 3-D TTM sweep (configs[4])")
     ap.add_argument("--grid", type=int, nargs=3, default=[512, 512, 512], help="FD cells for --workload ttm3d")
@@ -629,11 +655,27 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    if args.workload == "ttm3d":
-        return ttm3d_arm(args, rank, local_rank, world)
-    if args.impl == "reference":
-        return reference_arm(args, rank, world)
-    return our_arm(args, rank, local_rank, world)
+    # stdout carries the ONE JSON line and nothing else: library chatter (NCCL prints its version to
+    # stdout when NCCL_DEBUG is set) goes to stderr while the run lasts
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    buf = io.StringIO()
+    try:
+        with contextlib.redirect_stdout(buf):
+            if args.workload == "ttm3d":
+                rc = ttm3d_arm(args, rank, local_rank, world)
+            elif args.impl == "reference":
+                rc = reference_arm(args, rank, world)
+            else:
+                rc = our_arm(args, rank, local_rank, world)
+    finally:
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        os.close(real_stdout)
+        sys.stdout.write(buf.getvalue())
+        sys.stdout.flush()
+    return rc
 
 
 if __name__ == "__main__":

@@ -29,6 +29,10 @@ def build_system(args):
     else:
         pos, box = synth.fcc_lattice((14, 6, 6), spec.a)
         pbc = (1, 1, 1)
+    args.nrb_state = None
+    if args.nrb:                                   # init_nrb on the perfect lattice, atom numbers from 1
+        from imd_b200 import nrb
+        args.nrb_state = nrb.init_nrb(pos, np.arange(1, pos.shape[0] + 1, dtype=np.int32), box, pbc, spec.a, 0.3)
     rng = np.random.default_rng(3)
     pos = pos + rng.normal(0, 0.04, pos.shape)
     n = pos.shape[0]
@@ -43,11 +47,13 @@ def make_imd(args, device, comm, spec, pos, box, pbc, mom, eos, tp):
     imd.make_box(box, pbc, 0.4 if args.ttm else 0.5)
     imd.set_params(1, 0.1)
     mask = imd.owned_mask(pos)
-    ids = np.arange(pos.shape[0], dtype=np.int32)
+    ids = np.arange(pos.shape[0], dtype=np.int32) + (1 if args.nrb else 0)
     n = int(mask.sum())
     imd.set_atoms(pos[mask], mom[mask], np.full(n, spec.mass), np.zeros(n, np.int32), ids[mask])
     if args.ttm:
         imd.init_ttm(tp, eos, 2)
+    if args.nrb:
+        imd.set_nrb(1.2, args.nrb_state, startup_images=True)
     return imd
 
 
@@ -88,9 +94,11 @@ def check_ttm3d(capi, dist, uid, rank, world, local):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--ttm", action="store_true")
+    ap.add_argument("--nrb", action="store_true", help="--ttm plus the non-reflecting rear boundary")
     ap.add_argument("--ttm3d", action="store_true", help="3-D FD lattice sharded in x slabs")
     ap.add_argument("--steps", type=int, default=40)
     args = ap.parse_args()
+    args.ttm = args.ttm or args.nrb
     import torch
     import torch.distributed as dist
     from imd_b200 import capi, synth
@@ -150,6 +158,10 @@ def main():
             assert np.abs(d).max() < 1e-10, np.abs(d).max()
             fs = np.abs(want["force"]).max()
             assert np.abs(got["force"] - want["force"]).max() < 1e-10 * fs
+            assert np.abs(got["mom"] - want["mom"]).max() < 1e-10 * np.abs(want["mom"]).max()
+            if args.nrb:                           # the boundary layer took the NRB momenta on both sides
+                b = args.nrb_state.bnd > 0
+                assert b.sum() > 0 and (s <= 1 or np.abs(got["mom"][b]).max() > 0)
             np.testing.assert_allclose(got["rho"], want["rho"], rtol=1e-11)
             np.testing.assert_allclose(e[0], er[0], rtol=1e-11)
             np.testing.assert_allclose(e[1], er[1], rtol=1e-9, atol=1e-9 * abs(er[0]))
@@ -177,7 +189,7 @@ def main():
     dist.gather_object(n_local, cnt, dst=0)
     if rank == 0:
         assert sum(cnt) == pos.shape[0]
-        print("MULTI_GPU_CHECK PASSED world=%d ttm=%d atoms per rank %s rebuilds %d" % (world, args.ttm, cnt, imd.nbl_count))
+        print("MULTI_GPU_CHECK PASSED world=%d ttm=%d atoms per rank %s rebuilds %d" % (world, args.ttm + args.nrb, cnt, imd.nbl_count))
     imd.close()
     if ref:
         ref.close()

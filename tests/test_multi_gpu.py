@@ -16,11 +16,11 @@ def _ngpu():
     return torch.cuda.device_count()
 
 
-@pytest.mark.parametrize("mode", ["nve", "ttm", "ttm3d"])
+@pytest.mark.parametrize("mode", ["nve", "ttm", "nrb", "ttm3d"])
 def test_two_ranks_equal_one_rank(mode):
     if _ngpu() < 2:
         pytest.skip("needs 2 GPUs")
-    port = {"nve": "29532", "ttm": "29533", "ttm3d": "29534"}[mode]
+    port = {"nve": "29532", "ttm": "29533", "ttm3d": "29534", "nrb": "29535"}[mode]
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
            "127.0.0.1", "--master-port", port, os.path.join(ROOT, "tests", "multi_gpu_check.py")]
     if mode != "nve":
