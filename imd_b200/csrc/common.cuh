@@ -157,6 +157,7 @@ struct TtmState {
   DevBuf<double> xiloc;             // [P*LD] xiarr_local
   DevBuf<double> vcom;              // [3*G]
   DevBuf<double> src_e;             // [P*LD] exp(-mu*depth) per cell
+  DevBuf<double> winv;              // [P*L + vlatdim][8] density-only terms of a cell, per MD step
   DevBuf<int>    fdi, fdi_alt;      // per atom: slab of the previous step (p->fdi)
   // device scalars: see ttm.cu (TtmScal)
   void  *d_scal = nullptr;
@@ -201,6 +202,8 @@ struct imdcu_ctx {
   int    pdecay = 0; double xipdecay = 0, ramp_start = 0, ramp_end = 1;
   double *fused_coef = nullptr;              // pair + rho rows interleaved (context.cu: imdcu_fused_table)
   int    fused_state = 0;                    // 0 not looked at, 1 built, -1 tables do not share a grid
+  bool   ttm_isolate = true;                 // forked k_ttm_grid takes a whole SM (IMDCU_TTM_ISOLATE)
+  size_t ttm_isolate_smem = 0;               // dynamic smem request that keeps k_eam_pass2 CTAs off that SM
   int    fuse_ttm_steps = -1;                // >= 0: imdcu_eam_forces forks calc_ttm(steps) between its passes
   bool   box_set = false, params_set = false;
 

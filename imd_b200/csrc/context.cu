@@ -38,6 +38,14 @@ extern "C" int imdcu_create(imdcu_ctx **out, int device)
   CREATE_CHECK(cudaGetDeviceProperties(&prop, device));
   c->num_sms = prop.multiProcessorCount;
   c->smem_optin = prop.sharedMemPerBlockOptin;
+  {
+    // an SM holds sharedMemPerMultiprocessor bytes, every CTA reserves 1 KB on top of its request; a CTA of
+    // k_eam_pass2 needs >= 24 KB (one table): asking for all but 16 KB keeps every such CTA away
+    const char *e = getenv("IMDCU_TTM_ISOLATE");
+    c->ttm_isolate = !(e && atoi(e) == 0);
+    size_t want = prop.sharedMemPerMultiprocessor > 18 * 1024 ? prop.sharedMemPerMultiprocessor - 18 * 1024 : 0;
+    c->ttm_isolate_smem = want < c->smem_optin ? want : c->smem_optin;
+  }
   CREATE_CHECK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   CREATE_CHECK(cudaEventCreate(&c->ev0));
   CREATE_CHECK(cudaEventCreate(&c->ev1));

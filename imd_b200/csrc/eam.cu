@@ -355,7 +355,8 @@ static int run_passes(imdcu_ctx *c, EamArgs &a, size_t smem1, size_t smem2)
   const bool fuse = c->fuse_ttm_steps >= 0;
   if (fuse) {
     RET_IF(imdcu_ttm_fork(c, c->fuse_ttm_steps));
-    if (g2 == c->num_sms * (g2 / c->num_sms) && g2 > c->num_sms) g2 -= 1;
+    // the lattice CTA gets an SM of its own (ttm.cu: ttm_grid_part), otherwise one CTA slot
+    if (g2 == c->num_sms * (g2 / c->num_sms) && g2 > c->num_sms) g2 -= c->ttm_isolate ? g2 / c->num_sms : 1;
   }
   RET_IF(imdcu_refresh_ghosts(c, false));          // F' (and positions again) to the images
   {

@@ -19,16 +19,12 @@
 // same IEEE operations as the host code.
 #include "device.cuh"
 #include "ttm_math.cuh"
+#include "ttm_models.cuh"
 
 #include <cmath>
 
 #define RHOMIN 2
 namespace {
-__constant__ const double C_ECONST = 8.841941282883075e-12;
-__constant__ const double C_HBAR = 1.054571800139113e-34;
-__constant__ const double C_EMASS = 9.109383560000000e-31;
-__constant__ const double C_BOLTZMAN = 1.380648520000000e-23;
-__constant__ const double C_ECHARGE = 1.602176620000000e-19;
 __constant__ const double C_AMU = 1.660539040200000e-27;
 __constant__ const double C_J2eV = 6.2415090744607626077762409809304458998869658961709711e18;
 __constant__ const double C_eV2J = 1.602176634E-19;
@@ -66,6 +62,37 @@ __device__ double eos_interp(const EosView &e, double x, double y)
   return z11 + (1.0 - u) * (z01 - z11) + (1.0 - v) * (z10 - z11);
 }
 
+// The same interpolation with the x bracket (i, u) given and the y bracket searched from a hint: during
+// the sub-step loop a cell's density is constant (x side evaluated once per MD step, eos_locate_x) and
+// its Te moves by less than a table row per sub-step (the walk below ends after 0-1 steps).  Index
+// semantics are eos_find's, so the result is bit-identical to eos_interp(e, x, y).
+__device__ __forceinline__ void eos_locate_x(const EosView &e, double x, int &i, double &u)
+{
+  i = eos_find(e.x, e.nx, x);
+  u = 0.0;
+  if (i >= 0) { const double x0 = e.x[i], x1 = e.x[i + 1]; u = (x - x0) / (x1 - x0); }
+}
+__device__ __forceinline__ double eos_interp_at(const EosView &e, int i, double u, double y, int &jh)
+{
+  const int ny = e.ny;
+  if (i < 0 || !(y >= e.y[0]) || !(y <= e.y[ny - 1])) return nan("");
+  int j = jh < 0 ? 0 : (jh > ny - 2 ? ny - 2 : jh);
+  while (j > 0 && y < e.y[j]) j--;
+  while (j < ny - 2 && y >= e.y[j + 1]) j++;
+  jh = j;
+  const double y0 = e.y[j], y1 = e.y[j + 1];
+  const double z00 = e.z[i * ny + j], z01 = e.z[i * ny + j + 1];
+  const double z10 = e.z[(i + 1) * ny + j], z11 = e.z[(i + 1) * ny + j + 1];
+  const double v = (y - y0) / (y1 - y0);
+  const int d = e.diag[i * (ny - 1) + j];
+  if (d == 0) {
+    if (v <= u) return z00 + u * (z10 - z00) + v * (z11 - z10);
+    return z00 + u * (z11 - z01) + v * (z01 - z00);
+  }
+  if (u + v <= 1.0) return z00 + u * (z10 - z00) + v * (z01 - z00);
+  return z11 + (1.0 - u) * (z01 - z11) + (1.0 - v) * (z10 - z11);
+}
+
 __device__ __forceinline__ double eos_ee_from_r_te(const EosView &ee, double r, double t)
 {
   return eos_interp(ee, r, sqrt(t));                                   // imd_ttm.c:2483-2529
@@ -76,7 +103,6 @@ __device__ __forceinline__ double eos_cve_from_r_te(const EosView &cve, double r
   z *= r; z *= 11604.5; z *= 1e-30; z *= C_J2eV;
   return z;
 }
-
 __device__ __forceinline__ double eeminfun(const EosView &ee, double x, double r, double e)
 {
   double a = eos_ee_from_r_te(ee, r, x) - e;
@@ -140,84 +166,6 @@ __device__ double eos_te_from_r_ee(const EosView &ee, double r, double e)
   return fminbnd_ref(ee, a, b, r, e);
 }
 
-// ----------------------------------------------------------------------------- wide-range models (imd_ttm.c:2191-2399)
-// MeanCharge (:2241-2280), getKappa (:2356-2399), getGamma (:2310-2335) and their helpers
-// fermi_E/fermi_T/omega_pl/r0/bMin/bMax/coulomb_log/numet/numax/nupl (:2191-2308) for ONE cell,
-// fused: the reference evaluates fermi_E(Ne), r0(Ni), fermi_T(Ni*Z) and the Coulomb logarithm
-// two to four times per cell with identical arguments; here once.  Every arithmetic operation
-// keeps the reference's order; pow/exp/log are the branch-free versions of ttm_math.cuh
-// (pow(x,1.5) and pow(x,2.5) through one sqrt), so that the ~12 transcendental chains of a cell
-// interleave in one thread; divisions and square roots are the slow-path-free pdiv / psqrt (<= 1 ulp
-// from the IEEE operation).  z0p43 = pow(z0, 4/3) is hoisted out of the sub-step loop.
-struct WideRange { double Z, ne, kappa, gamma; };
-
-__device__ __forceinline__ WideRange wide_range(double temp_ev, double ti_ev, double dens, double z0, double am,
-                                                double z0p43, double omega_las, int la)
-{
-  WideRange w;
-  // ---- MeanCharge(temp [K], rho, z0, am)
-  {
-    double temp = temp_ev * 11604.5, rho = dens;
-    temp *= 1e-3; rho *= 1e-3;
-    const double YA1 = 0.003323, YA2 = 0.971832, YA3 = 0.926148e-5, YA4 = 3.10165, YB0 = -1.7630, YB1 = 1.43175,
-                 YB2 = 0.315463, YC1 = 0.036666667, YC2 = 0.983333333, YAL = 0.143139e2, YBE = 0.6624e0;
-    const double t0 = pdiv(temp, z0p43);
-    const double r0 = pdiv(rho, z0 * am);
-    const double lt0 = plog(t0), lr0 = plog(r0);
-    const double ytf = pdiv(t0, 1.0 + t0);
-    const double ya = YA1 * pexp(YA2 * lt0) + YA3 * pexp(YA4 * lt0);
-    const double yb = -pexp(YB0 + YB1 * ytf + YB2 * ytf * ytf);
-    const double yc = YC1 * ytf + YC2;
-    const double yq1 = ya * pexp(yb * lr0);
-    const double yq = ppow(pexp(yc * lr0) + ppow(yq1, yc), prcp(yc));
-    const double yx = YAL * ppow(yq, YBE);
-    w.Z = pdiv(z0 * yx, 1.0 + yx + psqrt(1.0 + 2.0 * yx));
-  }
-  const double Z = w.Z;
-  const double Ne = w.ne = pdiv(Z * dens, am * C_AMU);
-  // ---- shared by getKappa and getGamma (both start with Te *= 11604.5; Ti *= 11604.5)
-  const double Te = temp_ev * 11604.5, Ti = ti_ev * 11604.5;
-  const double Ni = pdiv(Ne, Z);
-  const double EF = pdiv(C_HBAR * C_HBAR * ppow(3.0 * M_PI * M_PI * Ne, 2.0 / 3.0) / 2.0, C_EMASS);       // fermi_E(Ne)
-  const double TF = 4.828648689433765e+22 * EF;
-  const double VF = 1.481734876966785e+15 * psqrt(EF);
-  const double r0n = ppow(pdiv(3.0, 4 * M_PI * Ni), 1.0 / 3.0);                                           // r0(Ni)
-  const double vth = psqrt(VF * VF + pdiv(C_BOLTZMAN * Te, C_EMASS));                                        // numax's root
-  // coulomb_log(omega_las, Z, Ni, Te, la) = MAX(2, log(bMax/bMin))
-  const double NiZ = Ni * Z;
-  const double ft = pdiv(2.0 * pdiv(C_HBAR * C_HBAR * ppow(3.0 * M_PI * M_PI * NiZ, 2.0 / 3.0) / 2.0, C_EMASS), 3.0 * C_BOLTZMAN);
-  const double teff = psqrt(Te * Te + ft * ft);
-  const double wpl = psqrt(pdiv(pdiv(NiZ * C_ECHARGE * C_ECHARGE, C_EMASS), C_ECONST));                           // omega_pl(Ni*Z)
-  const double vte = psqrt(pdiv(C_BOLTZMAN * teff, C_EMASS));
-  const double bmax = la ? DMAX(r0n, pdiv(vte, DMAX(omega_las, wpl))) : DMAX(r0n, pdiv(vte, wpl));
-  const double kTe = C_BOLTZMAN * Te;
-  const double bmin = DMAX(pdiv(Z * C_ECHARGE * C_ECHARGE, kTe), pdiv(C_HBAR, psqrt(2 * C_EMASS * C_BOLTZMAN * Te)));
-  const double coulomb = DMAX(2.0, plog(pdiv(bmax, bmin)));
-  const double skTe = psqrt(kTe);
-  const double kTe15 = kTe * skTe, kTe25 = kTe * kTe * skTe;                                           // pow(kTe,1.5), pow(kTe,2.5)
-  // ---- getGamma
-  {
-    const double A1g = 50, A2g = 20, A3g = 0.25, m_atom = 26.9815;
-    const double numet = 1.309202957843054e+11 * (A1g * Ti + pdiv(A2g * Te * Te, TF));
-    const double numax = pdiv(A3g, r0n) * vth;
-    const double nupl = pdiv(1.863839656495274e-40 * Z * Ne * coulomb, kTe15);
-    const double nu_eff = DMIN(numet, DMIN(numax, nupl));
-    w.gamma = pdiv(2.783313120645740e-74, m_atom * C_AMU) * Ne * nu_eff;
-  }
-  // ---- getKappa
-  {
-    const double A1t = 2.95, A2t = 0.5, A3t = 0.16, A4t = 1.2;
-    const double numet = 1.309202957843054e+11 * (A1t * Ti + pdiv(A2t * Te * Te, TF));
-    const double numax = pdiv(A3t, r0n) * vth;
-    const double nu_eff = DMIN(numet, numax);
-    const double kappa_met = pdiv(6.884236239621913e-16 * Ne * Te, nu_eff);
-    const double kappa_pl = pdiv(pdiv(4.428788911416808e+43 * kTe25, Z), coulomb);
-    const double kappa_wr = kappa_pl + (kappa_met - kappa_pl) * pexp(pdiv(-A4t * Te, TF));
-    w.kappa = kappa_wr * 0.073768115942029;
-  }
-  return w;
-}
-
 // ----------------------------------------------------------------------------- device state
 struct TtmScal {                     // persists between MD steps (device), mirrored to the host on demand
   int    cur, vcur;                  // which lattice is l1 / which virtual lattice is vlattice1
@@ -234,7 +182,7 @@ struct TtmArgs {
   int eos_smem, pad_;                // tables are staged into dynamic shared memory
   TCell *lat, *vlat;                 // [2][P*LD], [2][vlatdim]
   int *isum; double *dsum;           // slab sums, see k_ttm_atoms1
-  double *xiarr, *xiloc, *vcom, *src_e;
+  double *xiarr, *xiloc, *vcom, *src_e, *winv;   // winv: [ncell_tot][WINV_N], see fill_inv
   TtmScal *scal;
 };
 
@@ -497,12 +445,29 @@ __device__ int block_reduce_int(int v, int op /*1 min, 2 max*/, int *s_red)
   return r;
 }
 
-// wide-range properties of one cell (the body of do_FILLMESH's active branch / the vlattice loop)
-__device__ __forceinline__ void fill_props(const TtmArgs &a, const EosView &cve, TCell &c, int la, double z0p43)
+// per cell and MD step: what depends on the cell's density only (constant during the sub-step loop):
+// the density terms of the wide-range models and the x bracket of the Ce table
+#define WINV_N 8
+__device__ __forceinline__ void fill_inv(const TtmArgs &a, const EosView &cve, const TCell &c, double *wi)
 {
-  const double ce = eos_cve_from_r_te(cve, c.dens, c.temp * 11604.5);
-  const WideRange w = wide_range(c.temp, c.md_temp, c.dens, a.p.atomic_charge, a.p.atomic_weight, z0p43,
-                                 a.omega_laser, la);
+  const WideRangeInv v = wide_range_inv(c.dens, a.p.atomic_charge, a.p.atomic_weight);
+  int i; double u;
+  eos_locate_x(cve, c.dens, i, u);
+  wi[0] = v.lr0; wi[1] = v.ni; wi[2] = v.r0n; wi[3] = v.g_r0n; wi[4] = v.t_r0n;
+  wi[5] = (double) i; wi[6] = u; wi[7] = 0.0;
+}
+
+// wide-range properties of one cell (the body of do_FILLMESH's active branch / the vlattice loop)
+__device__ __forceinline__ void fill_props(const TtmArgs &a, const EosView &cve, TCell &c, int la, double z0p43,
+                                           double *wi)
+{
+  WideRangeInv v;
+  v.lr0 = wi[0]; v.ni = wi[1]; v.r0n = wi[2]; v.g_r0n = wi[3]; v.t_r0n = wi[4];
+  int jh = (int) wi[7];
+  double ce = eos_interp_at(cve, (int) wi[5], wi[6], c.temp * 11604.5, jh);       // EOS_cve_from_r_te, imd_ttm.c:2531-2592
+  wi[7] = (double) jh;
+  ce *= c.dens; ce *= 11604.5; ce *= 1e-30; ce *= C_J2eV;
+  const WideRange w = wide_range(c.temp, c.md_temp, v, a.p.atomic_charge, z0p43, a.omega_laser, la);
   c.Z = w.Z; c.ne = w.ne; c.Ce = ce; c.fd_k = w.kappa; c.fd_g = w.gamma;
 }
 
@@ -511,7 +476,7 @@ __device__ __forceinline__ void fill_props(const TtmArgs &a, const EosView &cve,
 // not run the expensive part twice.
 __device__ __forceinline__ void fillmesh(const TtmArgs &a, const EosView &cve, const EosView &ee, double z0p43,
                                          TCell *l1, TCell *l2, TCell *v1, TCell *v2, int last_active,
-                                         int rv, int la, int *err)
+                                         int rv, int la, int *err, bool first)
 {
   const int ncell = a.P * a.L, mn = a.p.fd_min_atoms;
   for (int c = threadIdx.x; c < ncell + a.p.vlatdim; c += blockDim.x) {
@@ -525,7 +490,9 @@ __device__ __forceinline__ void fillmesh(const TtmArgs &a, const EosView &cve, c
       }
     } else if (rv >= 0 && rv < a.P) { t = &v1[c - ncell]; t2 = &v2[c - ncell]; }   // :825-845
     if (!t) continue;
-    fill_props(a, cve, *t, la, z0p43);
+    double *wi = a.winv + (size_t) c * WINV_N;
+    if (first) fill_inv(a, cve, *t, wi);                                   // first FILLMESH of this MD step
+    fill_props(a, cve, *t, la, z0p43, wi);
     TCell &x = *t, &y = *t2;
     if (virt) { y.Z = x.Z; y.ne = x.ne; y.fd_k = x.fd_k; y.fd_g = x.fd_g; continue; }
     y.ne = x.ne; y.Ce = x.Ce; y.fd_k = x.fd_k; y.fd_g = x.fd_g;
@@ -698,7 +665,7 @@ k_ttm_grid(TtmArgs a)
 
   // ---------------------------------------------------------------- do_FILLMESH, ghosts, CFL_maxdt (:103-108)
   int la = sc->laser_active;
-  fillmesh(a, cve, ee, z0p43, l1, l2, v1, v2, last_active, rv, la, err);
+  fillmesh(a, cve, ee, z0p43, l1, l2, v1, v2, last_active, rv, la, err, true);
   __syncthreads();
   fill_ghosts(a, l1);
   __syncthreads();
@@ -745,6 +712,7 @@ k_ttm_grid(TtmArgs a)
   const double la_threshold = a.p.tmm_laser_threshold * sqrt(2 * a.p.I0 * Imp);      // imd_tmm.c:200-208, loop invariant
   double Ci = 8.589449886e+02;
   Ci *= a.p.vlatdens; Ci *= 11604.5; Ci *= 1e-30; Ci *= C_J2eV;
+  const double tau_ci = tau / Ci;
   for (int s = 0; s < diff_substeps; s++) {
     // analytic source (replaces do_tmm): I_t and the laser_active switch of imd_tmm.c:197-208
     const double dtl = tmm_time - a.p.laser_t_0;
@@ -767,11 +735,11 @@ k_ttm_grid(TtmArgs a)
         double xmaxTe = xmax.temp, xminTe = xmin.temp, xmaxk = xmax.fd_k, xmink = xmin.fd_k;
         if (rv == r) { xmaxTe = v1[0].temp; xmaxk = v1[0].fd_k; }           // :1548-1552
         const double Ce = x.Ce;
-        y.temp = tau / Ce * ((((x.fd_k + xmaxk) / 2 * (xmaxTe - x.temp) * invxsq)
+        y.temp = pdiv(tau, Ce) * ((((x.fd_k + xmaxk) / 2 * (xmaxTe - x.temp) * invxsq)
                               - ((x.fd_k + xmink) / 2 * (x.temp - xminTe) * invxsq))
                              - x.fd_g * (x.temp - x.md_temp) + src) + x.temp;
-        y.U = x.U + (y.temp - x.temp) * Ce * a.fd_vol / ((double) x.natoms);
-        const double dxi = (y.temp - x.md_temp) * xi_fac * x.fd_g / x.md_temp / x.dens;
+        y.U = x.U + pdiv((y.temp - x.temp) * Ce * a.fd_vol, (double) x.natoms);
+        const double dxi = pdiv(pdiv((y.temp - x.md_temp) * xi_fac * x.fd_g, x.md_temp), x.dens);
         x.xi += dxi;
         y.xi = x.xi;
         a.xiloc[idx] += dxi;
@@ -785,17 +753,17 @@ k_ttm_grid(TtmArgs a)
         if (i < nv - 1) { xmaxk = v1[i + 1].fd_k; xmaxTe = v1[i + 1].temp; }
         else { xmaxk = v1[i].fd_k; xmaxTe = v1[i].temp; }
         const double Ce = v1[i].Ce;
-        v2[i].temp = tau / Ce * (((v1[i].fd_k + xmaxk) / 2 * (xmaxTe - v1[i].temp) * invxsq)
+        v2[i].temp = pdiv(tau, Ce) * (((v1[i].fd_k + xmaxk) / 2 * (xmaxTe - v1[i].temp) * invxsq)
                                  - ((v1[i].fd_k + xmink) / 2 * (v1[i].temp - xminTe) * invxsq)
                                  - v1[i].fd_g * (v1[i].temp - v1[i].md_temp)) + v1[i].temp;
-        const double dT = tau / Ci * v1[i].fd_g * (v1[i].temp - v1[i].md_temp);
+        const double dT = tau_ci * v1[i].fd_g * (v1[i].temp - v1[i].md_temp);
         v2[i].md_temp = v1[i].md_temp + dT;
       }
     }
     __syncthreads();
     cur = 1 - cur; vcur = 1 - vcur;
     { TCell *t = l1; l1 = l2; l2 = t; t = v1; v1 = v2; v2 = t; }
-    fillmesh(a, cve, ee, z0p43, l1, l2, v1, v2, last_active, rv, la, err);
+    fillmesh(a, cve, ee, z0p43, l1, l2, v1, v2, last_active, rv, la, err, false);
     __syncthreads();
     fill_ghosts(a, l1);
     __syncthreads();
@@ -886,6 +854,7 @@ extern "C" int imdcu_ttm_init(imdcu_ctx *c, const imdcu_ttm_params *p)
   CU_CHECK(c, t.isum.ensure(4 * (size_t) t.G)); CU_CHECK(c, t.dsum.ensure(4 * (size_t) t.G));
   CU_CHECK(c, t.xiarr.ensure(t.G)); CU_CHECK(c, t.xiloc.ensure(nl)); CU_CHECK(c, t.vcom.ensure(3 * (size_t) t.G));
   CU_CHECK(c, t.src_e.ensure(nl));
+  CU_CHECK(c, t.winv.ensure(((size_t) t.P * t.L + nv) * 8));
   CU_CHECK(c, cudaMemset(t.lat.p, 0, 2 * (size_t) nl * sizeof(TCell)));
   CU_CHECK(c, cudaMemset(t.xiarr.p, 0, t.G * sizeof(double)));
   CU_CHECK(c, cudaMemset(t.xiloc.p, 0, nl * sizeof(double)));
@@ -917,7 +886,7 @@ void imdcu_ttm_release(imdcu_ctx *c)
   TtmState &t = c->ttm;
   for (int w = 0; w < 2; w++) { t.eos_buf[w].release(); t.eos_diag[w].release(); }
   t.lat.release(); t.vlat.release(); t.isum.release(); t.dsum.release(); t.xiarr.release(); t.xiloc.release();
-  t.vcom.release(); t.src_e.release(); t.fdi.release(); t.fdi_alt.release();
+  t.vcom.release(); t.src_e.release(); t.winv.release(); t.fdi.release(); t.fdi_alt.release();
   if (t.d_scal) cudaFree(t.d_scal);
   if (t.h_scal) cudaFreeHost(t.h_scal);
   t.d_scal = t.h_scal = nullptr;
@@ -986,7 +955,7 @@ static int ttm_grid_part(imdcu_ctx *c, int steps, cudaStream_t st)
   a.omega_laser = t.omega_laser; a.sigma_t_sq = t.sigma_t_sq;
   a.cve = eos_view(t, 0); a.ee = eos_view(t, 1);
   a.lat = t.lat.p; a.vlat = t.vlat.p; a.isum = t.isum.p; a.dsum = t.dsum.p;
-  a.xiarr = t.xiarr.p; a.xiloc = t.xiloc.p; a.vcom = t.vcom.p; a.src_e = t.src_e.p;
+  a.xiarr = t.xiarr.p; a.xiloc = t.xiloc.p; a.vcom = t.vcom.p; a.src_e = t.src_e.p; a.winv = t.winv.p;
   a.scal = (TtmScal *) t.d_scal;
   int nt = ((a.ncell_tot + 31) / 32) * 32;
   if (nt > TTM_NT) nt = TTM_NT;
@@ -1000,7 +969,12 @@ static int ttm_grid_part(imdcu_ctx *c, int steps, cudaStream_t st)
   a.eos_smem = smem <= 200 * 1024;
   a.pad_ = 0;
   if (!a.eos_smem) smem = 0;
-  if (smem != t.grid_smem_set) {
+  // Beside k_eam_pass2 (imdcu_ttm_fork) the lattice CTA asks for so much shared memory that no CTA of
+  // the force kernel fits next to it: sharing an SM with 16 warps that keep the L1 data pipe 80 % busy
+  // stretches every dependent load and barrier of this latency chain.  Pass 2 leaves that SM alone
+  // (eam.cu: run_passes).  IMDCU_TTM_ISOLATE=0 switches it off.
+  if (st != c->stream && c->ttm_isolate && smem < c->ttm_isolate_smem) smem = c->ttm_isolate_smem;
+  if (smem > t.grid_smem_set) {
     CU_CHECK(c, cudaFuncSetAttribute(k_ttm_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     t.grid_smem_set = smem;
   }

@@ -100,17 +100,14 @@ TM_HD double plog(double x)
   const double r = TM_FMA(-f, den, num);
   const double fl = r * rden;                                                      // tail of f
   const double f2 = f * f;
-  double p = 2.0 / 23.0;
-  p = TM_FMA(p, f2, 2.0 / 21.0);
-  p = TM_FMA(p, f2, 2.0 / 19.0);
-  p = TM_FMA(p, f2, 2.0 / 17.0);
-  p = TM_FMA(p, f2, 2.0 / 15.0);
-  p = TM_FMA(p, f2, 2.0 / 13.0);
-  p = TM_FMA(p, f2, 2.0 / 11.0);
-  p = TM_FMA(p, f2, 2.0 / 9.0);
-  p = TM_FMA(p, f2, 2.0 / 7.0);
-  p = TM_FMA(p, f2, 2.0 / 5.0);
-  p = TM_FMA(p, f2, 2.0 / 3.0);
+  // sum_{k=0..10} 2/(2k+3) f2^k by Estrin's scheme: dependent depth 4 instead of 11 (the kernel is a
+  // latency chain; the independent partial sums fill each other's latency shadows)
+  const double z2 = f2 * f2, z4 = z2 * z2, z8 = z4 * z4;
+  const double a0 = TM_FMA(2.0 / 5.0, f2, 2.0 / 3.0), a1 = TM_FMA(2.0 / 9.0, f2, 2.0 / 7.0);
+  const double a2 = TM_FMA(2.0 / 13.0, f2, 2.0 / 11.0), a3 = TM_FMA(2.0 / 17.0, f2, 2.0 / 15.0);
+  const double a4 = TM_FMA(2.0 / 21.0, f2, 2.0 / 19.0);
+  const double b0 = TM_FMA(a1, z2, a0), b1 = TM_FMA(a3, z2, a2), b2 = TM_FMA(2.0 / 23.0, z2, a4);
+  const double p = TM_FMA(b2, z8, TM_FMA(b1, z4, b0));
   const double de = (double) e;
   // log x = e ln2_hi + 2f + (f f2 p + 2 fl + e ln2_lo)
   const double ln2_hi = 6.93147180369123816490e-01, ln2_lo = 1.90821492927058770002e-10;
@@ -130,21 +127,15 @@ TM_HD double pexp(double x)
   const double ln2_hi = 6.93147180369123816490e-01, ln2_lo = 1.90821492927058770002e-10;
   double r = TM_FMA(-k, ln2_hi, x);
   r = TM_FMA(-k, ln2_lo, r);                                                       // |r| <= 0.3466
-  double p = 1.0 / 87178291200.0;                                                  // 1/14!
-  p = TM_FMA(p, r, 1.0 / 6227020800.0);
-  p = TM_FMA(p, r, 1.0 / 479001600.0);
-  p = TM_FMA(p, r, 1.0 / 39916800.0);
-  p = TM_FMA(p, r, 1.0 / 3628800.0);
-  p = TM_FMA(p, r, 1.0 / 362880.0);
-  p = TM_FMA(p, r, 1.0 / 40320.0);
-  p = TM_FMA(p, r, 1.0 / 5040.0);
-  p = TM_FMA(p, r, 1.0 / 720.0);
-  p = TM_FMA(p, r, 1.0 / 120.0);
-  p = TM_FMA(p, r, 1.0 / 24.0);
-  p = TM_FMA(p, r, 1.0 / 6.0);
-  p = TM_FMA(p, r, 0.5);
-  p = TM_FMA(p, r, 1.0);
-  p = TM_FMA(p, r, 1.0);
+  // e^r = 1 + (r + r^2 Q(r)), Q = sum_{k=0..12} r^k/(k+2)! by Estrin's scheme (depth 5 instead of 14)
+  const double r2 = r * r, r4 = r2 * r2, r8 = r4 * r4;
+  const double a0 = TM_FMA(1.0 / 6.0, r, 0.5), a1 = TM_FMA(1.0 / 120.0, r, 1.0 / 24.0);
+  const double a2 = TM_FMA(1.0 / 5040.0, r, 1.0 / 720.0), a3 = TM_FMA(1.0 / 362880.0, r, 1.0 / 40320.0);
+  const double a4 = TM_FMA(1.0 / 39916800.0, r, 1.0 / 3628800.0), a5 = TM_FMA(1.0 / 6227020800.0, r, 1.0 / 479001600.0);
+  const double b0 = TM_FMA(a1, r2, a0), b1 = TM_FMA(a3, r2, a2), b2 = TM_FMA(a5, r2, a4);
+  const double d0 = TM_FMA(b1, r4, b0), d1 = TM_FMA(1.0 / 87178291200.0, r4, b2);
+  const double q = TM_FMA(d1, r8, d0);
+  const double p = TM_FMA(r2, q, r) + 1.0;
   // scale by 2^k in two exact steps (k in [-1010, 1010])
   const int ki = (int) k;
   const int k1 = ki / 2, k2 = ki - k1;
