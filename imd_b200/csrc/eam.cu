@@ -18,14 +18,26 @@
 // (nothing here is a dense contraction).
 #include "device.cuh"
 
-#ifndef EAM_BLOCK
-#define EAM_BLOCK 512
+// CTA shapes (measured on a B200, 2.05 M Al atoms, profiles/r01g_eam_variants.txt): ONE CTA per SM with
+// one copy of the tables and the rest of the 228 KB as L1 beats two CTAs of 512 threads; pass 1 likes
+// 72 registers (896 threads), pass 2 needs no more than 64 (1024 threads).
+#ifndef EAM_BLOCK1             /* pass 1 */
+#define EAM_BLOCK1 896
 #endif
-#ifndef EAM_MINB
-#define EAM_MINB 2
+#ifndef EAM_MINB1
+#define EAM_MINB1 1
+#endif
+#ifndef EAM_BLOCK2             /* pass 2 */
+#define EAM_BLOCK2 1024
+#endif
+#ifndef EAM_MINB2
+#define EAM_MINB2 1
 #endif
 #ifndef EAM_UNROLL
 #define EAM_UNROLL 2
+#endif
+#ifndef EAM_ABLATE
+#define EAM_ABLATE 0           /* timing experiments on k_eam_pass1_fused (profiles/eam_ablate.sh), 0 = product */
 #endif
 #define EAM_PRAGMA_(x) _Pragma(#x)
 #define EAM_PRAGMA_UNROLL(n) EAM_PRAGMA_(unroll n)
@@ -53,10 +65,55 @@ __device__ __forceinline__ double sub_sum(double v)
   return v;
 }
 
+// Software pipeline over one lane's share of a neighbour row.  A pair costs a chain of two dependent
+// loads (list slot from HBM, then the gathered 32-byte record) ahead of ~45 FP64 instructions; written
+// as a plain loop the compiler keeps that chain serial per iteration and only the eight warps of a
+// scheduler overlap it.  Here the slot indices run three iterations ahead and the record of pair k+1
+// is requested before pair k is evaluated.
+template <int LPA, bool MULTI>
+struct NbrPipe {
+  const int *sp;            // my first slot
+  int cnt;                  // my number of slots
+  int j2, j3, tn;           // indices of iterations k+1, k+2; type of the record in flight
+  double4 pn;               // record in flight
+  static constexpr size_t ST = (size_t) LPA * 32;
+  __device__ __forceinline__ NbrPipe(const double4 *pos4, const int *type, const int *slot, int num, int sub)
+  {
+    sp = slot + (size_t) sub * 32;
+    cnt = num > sub ? (num - sub + LPA - 1) / LPA : 0;
+    const int j1 = cnt > 0 ? sp[0] : 0;
+    j2 = cnt > 1 ? sp[ST] : 0;
+    j3 = cnt > 2 ? sp[2 * ST] : 0;
+    tn = 0;
+    if (cnt > 0) { pn = rec(pos4, j1); if (MULTI) tn = type[j1]; }
+    else pn = make_double4(0, 0, 0, 0);
+    jc = 0; jn = j1;
+  }
+  int jc, jn;               // index of the record returned last / in flight (timing experiments only)
+  __device__ __forceinline__ double4 rec(const double4 *pos4, int j)
+  {
+#if EAM_ABLATE == 2      /* timing experiment: no position gather */
+    return make_double4(0.35 * (j & 7), 0.3 * ((j >> 3) & 7), 0.4 * ((j >> 6) & 7) + 1.1, 0.0);
+#else
+    return ld256(&pos4[j]);
+#endif
+  }
+  __device__ __forceinline__ double4 next(const double4 *pos4, const int *type, int k, int &jt)
+  {
+    const double4 pj = pn;
+    if (MULTI) jt = tn;
+    if (EAM_ABLATE) { jc = jn; jn = j2; }
+    if (k + 1 < cnt) { pn = rec(pos4, j2); if (MULTI) tn = type[j2]; }
+    j2 = j3;
+    if (k + 3 < cnt) j3 = sp[(size_t) (k + 3) * ST];
+    return pj;
+  }
+};
+
 // LPA lanes cooperate on one atom (1 for big systems, more to fill the GPU on small ones);
 // SMEM: tables staged in shared memory, else read through L1/L2; MULTI: ntypes > 1.
 template <int LPA, bool SMEM, bool MULTI>
-__global__ void __launch_bounds__(EAM_BLOCK, EAM_MINB)
+__global__ void __launch_bounds__(EAM_BLOCK1, EAM_MINB1)
 k_eam_pass1(EamArgs a)
 {
   extern __shared__ __align__(16) double s_tab[];
@@ -83,7 +140,7 @@ k_eam_pass1(EamArgs a)
   TabCol tp0 = tab_col(a.pair, pair_c, 0), tr0 = tab_col(a.rhot, rho_c, 0);
   const double pair_end0 = a.pair.end[0];
 
-  const int apb = EAM_BLOCK / LPA;                       // atoms per CTA iteration
+  const int apb = EAM_BLOCK1 / LPA;                       // atoms per CTA iteration
   const int sub = threadIdx.x % LPA;
   double acc[2] = {0.0, 0.0};                            // epot, virial
   int is_short = 0;
@@ -98,16 +155,15 @@ k_eam_pass1(EamArgs a)
       const int num = a.nbl_num[i];
       const int *slot = a.nbl_idx + ((size_t) (i >> 5) * a.cap) * 32 + (i & 31);
       if (MULTI) it = a.type[i];
+      NbrPipe<LPA, MULTI> np(a.pos4, a.type, slot, num, sub);
 EAM_PRAGMA_UNROLL(EAM_UNROLL)
-      for (int k = sub; k < num; k += LPA) {
-        const int j = slot[(size_t) k * 32];
-        const double4 pj = ld256(&a.pos4[j]);
+      for (int k = 0; k < np.cnt; k++) {
+        int jt = 0;
+        const double4 pj = np.next(a.pos4, a.type, k, jt);
         const double dx = pj.x - pi.x, dy = pj.y - pi.y, dz = pj.z - pi.z;
         const double r2 = r2_exact(dx, dy, dz);
         TabCol tp = tp0, tr = tr0;
-        int jt = 0;
         if (MULTI) {
-          jt = a.type[j];
           const int col = it * a.ntypes + jt;
           tp = tab_col(a.pair, pair_c, col);
           tr = tab_col(a.rhot, rho_c, col);
@@ -136,7 +192,8 @@ EAM_PRAGMA_UNROLL(EAM_UNROLL)
       ee += pot;
       a.frc4[i] = make_double4(fx, fy, fz, ee);
       a.rho[i] = rh;
-      a.dF[i] = dF;                // merged into pos4.w by k_set_dF before the image refresh
+      a.dF[i] = dF;
+      a.pos4[i].w = dF;            // pass 2 gathers F' with the position; pass 1 reads only x,y,z of other atoms
       if (a.count_ttm) a.numneighs[i] = nn;
       acc[0] += ee; acc[1] += vir;
     }
@@ -151,7 +208,7 @@ EAM_PRAGMA_UNROLL(EAM_UNROLL)
 // 24-byte rows read as six 8-byte loads: the kernel is bound by the L1 data pipe, and this is a
 // third fewer shared-memory wavefronts.  Same operations per function as PAIR_INT2 / VAL_FUNC2.
 template <int LPA>
-__global__ void __launch_bounds__(EAM_BLOCK, EAM_MINB)
+__global__ void __launch_bounds__(EAM_BLOCK1, EAM_MINB1)
 k_eam_pass1_fused(EamArgs a)
 {
   extern __shared__ __align__(16) double s_tab[];
@@ -170,10 +227,13 @@ k_eam_pass1_fused(EamArgs a)
   const TabCol tp = tab_col(a.pair, s_tab, 0);           // begin, end, invstep (identical for the rho column)
   const double rho_end = a.rhot.end[0];
   const double two_invstep = 2 * tp.invstep;
-  const int apb = EAM_BLOCK / LPA;
+  const int apb = EAM_BLOCK1 / LPA;
   const int sub = threadIdx.x % LPA;
   double acc[2] = {0.0, 0.0};
   int is_short = 0;
+#if EAM_ABLATE
+  const double zero = (double) (a.n < 0);
+#endif
   for (int base = blockIdx.x * apb; base < a.n; base += gridDim.x * apb) {
     const int i = base + threadIdx.x / LPA;
     const bool live = i < a.n;
@@ -183,18 +243,41 @@ k_eam_pass1_fused(EamArgs a)
       const double4 pi = a.pos4[i];
       const int num = a.nbl_num[i];
       const int *slot = a.nbl_idx + ((size_t) (i >> 5) * a.cap) * 32 + (i & 31);
+      NbrPipe<LPA, false> np(a.pos4, a.type, slot, num, sub);
 EAM_PRAGMA_UNROLL(EAM_UNROLL)
-      for (int k = sub; k < num; k += LPA) {
-        const int j = slot[(size_t) k * 32];
-        const double4 pj = ld256(&a.pos4[j]);
+      for (int k = 0; k < np.cnt; k++) {
+        int jt_unused = 0;
+#if EAM_ABLATE == 2
+        double4 pj = np.next(a.pos4, a.type, k, jt_unused);
+        pj.x += pi.x; pj.y += pi.y; pj.z += pi.z;
+#else
+        const double4 pj = np.next(a.pos4, a.type, k, jt_unused);
+#endif
         const double dx = pj.x - pi.x, dy = pj.y - pi.y, dz = pj.z - pi.z;
         const double r2 = r2_exact(dx, dy, dz);
+#if EAM_ABLATE == 3      /* extra shared-memory gather of 32 bytes, records at 32-byte stride */
+        { const double2 *g2 = reinterpret_cast<const double2 *>(s_tab) + 2 * (size_t) (np.jc & 2047);
+          const double2 u0 = g2[0], u1 = g2[1]; rh += zero * (u0.x + u0.y + u1.x + u1.y); }
+#elif EAM_ABLATE == 5    /* extra shared-memory gather of 32 bytes, two arrays at 16-byte stride */
+        { const double2 *g2 = reinterpret_cast<const double2 *>(s_tab) + (size_t) (np.jc & 2047);
+          const double2 u0 = g2[0], u1 = g2[2048]; rh += zero * (u0.x + u0.y + u1.x + u1.y); }
+#elif EAM_ABLATE == 6    /* extra global gather, 32 lanes within 16 consecutive records (4 lines) */
+        { const int j2 = (i & ~31) + (np.jc & 15); const double4 u = ld256(&a.pos4[j2]); rh += zero * (u.x + u.y + u.z + u.w); }
+#elif EAM_ABLATE == 7    /* extra global gather, 32 lanes within 64 consecutive records (16 lines) */
+        { const int j2 = (i & ~31) + (np.jc & 63); const double4 u = ld256(&a.pos4[j2]); rh += zero * (u.x + u.y + u.z + u.w); }
+#elif EAM_ABLATE == 4    /* extra global gather of 32 bytes */
+        { const int j2 = np.jc + 64 < a.n ? np.jc + 64 : np.jc; const double4 u = ld256(&a.pos4[j2]); rh += zero * (u.x + u.y + u.z + u.w); }
+#endif
         if (r2 <= tp.end) {                                // pair: r2 <= end, rho: r2 < end (same end)
           if (a.count_ttm) nn++;
           int kk; double chi;
           tab_index(tp, r2, kk, chi, is_short);
+#if EAM_ABLATE == 1      /* no table rows */
+          const double2 q0 = make_double2(chi, 0.1), q1 = make_double2(0.01 * chi, 0.2), q2 = make_double2(chi, 0.001 * kk);
+#else
           const double2 *row = reinterpret_cast<const double2 *>(s_tab + 6 * (size_t) kk);
           const double2 q0 = row[0], q1 = row[1], q2 = row[2];   // {p0,dv} {d2v,r0} {drv,d2rv}
+#endif
           const double h = 0.5 * chi * (chi - 1);
           const double pot = q0.x + chi * q0.y + h * q1.x;
           const double grad = two_invstep * (q0.y + (chi - 0.5) * q1.x);
@@ -213,11 +296,15 @@ EAM_PRAGMA_UNROLL(EAM_UNROLL)
     if (live && sub == 0) {
       double pot, dF; int idummy = 0;
       TabCol te = tab_col(a.emb, a.emb.coef, 0);
+#if EAM_ABLATE == 1 || EAM_ABLATE == 2
+      fx *= zero; fy *= zero; fz *= zero; ee *= zero; vir *= zero; rh = rh * zero + 1.0; nn = 78;
+#endif
       pair_int2(te, rh, pot, dF, idummy);
       ee += pot;
       a.frc4[i] = make_double4(fx, fy, fz, ee);
       a.rho[i] = rh;
       a.dF[i] = dF;
+      a.pos4[i].w = dF;
       if (a.count_ttm) a.numneighs[i] = nn;
       acc[0] += ee; acc[1] += vir;
     }
@@ -227,7 +314,7 @@ EAM_PRAGMA_UNROLL(EAM_UNROLL)
 }
 
 template <int LPA, bool SMEM, bool MULTI>
-__global__ void __launch_bounds__(EAM_BLOCK, EAM_MINB)
+__global__ void __launch_bounds__(EAM_BLOCK2, EAM_MINB2)
 k_eam_pass2(EamArgs a)
 {
   extern __shared__ __align__(16) double s_tab[];
@@ -247,7 +334,7 @@ k_eam_pass2(EamArgs a)
     rho_c = s_tab;
   }
   const TabCol tr0 = tab_col(a.rhot, rho_c, 0);
-  const int apb = EAM_BLOCK / LPA;
+  const int apb = EAM_BLOCK2 / LPA;
   const int sub = threadIdx.x % LPA;
   double acc[1] = {0.0};
   int is_short = 0;
@@ -262,10 +349,11 @@ k_eam_pass2(EamArgs a)
       const int *slot = a.nbl_idx + ((size_t) (i >> 5) * a.cap) * 32 + (i & 31);
       int it = 0;
       if (MULTI) it = a.type[i];
+      NbrPipe<LPA, MULTI> np(a.pos4, a.type, slot, num, sub);
 EAM_PRAGMA_UNROLL(EAM_UNROLL)
-      for (int k = sub; k < num; k += LPA) {
-        const int j = slot[(size_t) k * 32];
-        const double4 pj = ld256(&a.pos4[j]);
+      for (int k = 0; k < np.cnt; k++) {
+        int jt = 0;
+        const double4 pj = np.next(a.pos4, a.type, k, jt);
         const double dx = pj.x - pi.x, dy = pj.y - pi.y, dz = pj.z - pi.z;
         const double r2 = r2_exact(dx, dy, dz);
         if (!MULTI) {
@@ -277,7 +365,6 @@ EAM_PRAGMA_UNROLL(EAM_UNROLL)
             vir -= 0.5 * (dx * gx + dy * gy + dz * gz);
           }
         } else {
-          const int jt = a.type[j];
           const int col1 = jt * a.ntypes + it, col2 = it * a.ntypes + jt;
           const TabCol t1 = tab_col(a.rhot, rho_c, col1), t2 = tab_col(a.rhot, rho_c, col2);
           if (r2 < t1.end || r2 < t2.end) {
@@ -305,22 +392,15 @@ EAM_PRAGMA_UNROLL(EAM_UNROLL)
   grid_reduce<1, 0>(acc, a.partials, a.ticket + 1, a.results + 2);
 }
 
-__global__ void __launch_bounds__(256)
-k_set_dF(int n, const double *__restrict__ dF, double4 *__restrict__ pos4)
-{
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) pos4[i].w = dF[i];
-}
-
 // ----------------------------------------------------------------------------- dispatch
 
 template <typename K>
-static int launch_cfg(imdcu_ctx *c, K kern, size_t smem, int *grid)
+static int launch_cfg(imdcu_ctx *c, K kern, int block, size_t smem, int *grid)
 {
   if (smem > 48 * 1024)
     CU_CHECK(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
   int per_sm = 0;
-  CU_CHECK(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, EAM_BLOCK, smem));
+  CU_CHECK(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, block, smem));
   if (per_sm < 1) return c->fail(IMDCU_ECUDA, "EAM kernel does not fit on an SM");
   *grid = c->num_sms * per_sm;
   return IMDCU_OK;
@@ -330,24 +410,18 @@ template <int LPA, bool SMEM, bool MULTI>
 static int run_passes(imdcu_ctx *c, EamArgs &a, size_t smem1, size_t smem2)
 {
   int g1 = 0, g2 = 0;
-  const int apb = EAM_BLOCK / LPA;
   const bool fused = SMEM && !MULTI && a.fused;
-  if (fused) RET_IF(launch_cfg(c, k_eam_pass1_fused<LPA>, smem1, &g1));
-  else RET_IF(launch_cfg(c, k_eam_pass1<LPA, SMEM, MULTI>, smem1, &g1));
-  RET_IF(launch_cfg(c, k_eam_pass2<LPA, SMEM, MULTI>, smem2, &g2));
-  g1 = std::min(g1, div_up(a.n, apb));
-  g2 = std::min(g2, div_up(a.n, apb));
+  if (fused) RET_IF(launch_cfg(c, k_eam_pass1_fused<LPA>, EAM_BLOCK1, smem1, &g1));
+  else RET_IF(launch_cfg(c, k_eam_pass1<LPA, SMEM, MULTI>, EAM_BLOCK1, smem1, &g1));
+  RET_IF(launch_cfg(c, k_eam_pass2<LPA, SMEM, MULTI>, EAM_BLOCK2, smem2, &g2));
+  g1 = std::min(g1, div_up(a.n, EAM_BLOCK1 / LPA));
+  g2 = std::min(g2, div_up(a.n, EAM_BLOCK2 / LPA));
   CU_CHECK(c, c->partials.ensure((size_t) std::max(g1, g2) * 4 + 64));
   a.partials = c->partials.p;
   {
     PhaseTimer pt(c, 3);
-    if (fused) k_eam_pass1_fused<LPA><<<g1, EAM_BLOCK, smem1, c->stream>>>(a);
-    else k_eam_pass1<LPA, SMEM, MULTI><<<g1, EAM_BLOCK, smem1, c->stream>>>(a);
-    c->count_launch();
-  }
-  {
-    PhaseTimer pt(c, 4);
-    k_set_dF<<<div_up(a.n, 256), 256, 0, c->stream>>>(a.n, a.dF, a.pos4);
+    if (fused) k_eam_pass1_fused<LPA><<<g1, EAM_BLOCK1, smem1, c->stream>>>(a);
+    else k_eam_pass1<LPA, SMEM, MULTI><<<g1, EAM_BLOCK1, smem1, c->stream>>>(a);
     c->count_launch();
   }
   // calc_ttm overlapped with pass 2 (imdcu_run_ttm): numneighs of this step exist now; the lattice
@@ -356,12 +430,12 @@ static int run_passes(imdcu_ctx *c, EamArgs &a, size_t smem1, size_t smem2)
   if (fuse) {
     RET_IF(imdcu_ttm_fork(c, c->fuse_ttm_steps));
     // the lattice CTA gets an SM of its own (ttm.cu: ttm_grid_part), otherwise one CTA slot
-    if (g2 == c->num_sms * (g2 / c->num_sms) && g2 > c->num_sms) g2 -= c->ttm_isolate ? g2 / c->num_sms : 1;
+    if (g2 == c->num_sms * (g2 / c->num_sms) && g2 >= c->num_sms) g2 -= c->ttm_isolate ? g2 / c->num_sms : 1;
   }
   RET_IF(imdcu_refresh_ghosts(c, false));          // F' (and positions again) to the images
   {
     PhaseTimer pt(c, 5);
-    k_eam_pass2<LPA, SMEM, MULTI><<<g2, EAM_BLOCK, smem2, c->stream>>>(a);
+    k_eam_pass2<LPA, SMEM, MULTI><<<g2, EAM_BLOCK2, smem2, c->stream>>>(a);
     c->count_launch();
   }
   CU_CHECK(c, cudaGetLastError());

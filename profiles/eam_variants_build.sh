@@ -1,0 +1,16 @@
+#!/bin/bash
+# build library variants that differ in the macros given to eam.cu (timing experiments):
+#   bash profiles/eam_variants_build.sh name1 "-DEAM_ABLATE=1" name2 "-DEAM_BLOCK=256" ...
+# -> imd_b200/variants/libimdcu_<name>.so  (run on the GPU box by profiles/eam_variants_run.sh)
+set -e
+cd "$(dirname "$0")/../imd_b200/csrc"
+make -j8 > /dev/null
+mkdir -p ../variants
+FLAGS="-O3 -std=c++17 -lineinfo -gencode arch=compute_100a,code=sm_100a -Xcompiler -fPIC,-ffp-contract=off,-Wall"
+while [ $# -ge 2 ]; do
+  name=$1; defs=$2; shift 2
+  nvcc $FLAGS $defs -c eam.cu -o /tmp/eam_$name.o
+  objs=$(ls *.o | grep -v '^eam.o$')
+  nvcc -gencode arch=compute_100a,code=sm_100a -shared -o ../variants/libimdcu_$name.so $objs /tmp/eam_$name.o -lcudart -ldl
+  echo built $name "($defs)"
+done
