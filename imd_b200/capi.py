@@ -15,6 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libimdcu.so")
 
 NPHASE = 8
+INTERP_MODES = {"3point": 0, "4point": 1, "spline": 2}
 PHASE_NAMES = ["bin_sort", "nbl_build", "ghost_refresh", "eam_pass1", "embed", "eam_pass2",
                "integrate", "ttm"]
 
@@ -64,6 +65,8 @@ def load():
         "imdcu_last_error": (C.c_char_p, [vp]),
         "imdcu_set_box": (C.c_int, [vp, c_dp, c_ip, C.c_double, C.c_double, c_ip]),
         "imdcu_set_table": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, c_dp, c_dp, c_dp, c_dp, c_ip, c_dp]),
+        "imdcu_set_interp": (C.c_int, [vp, C.c_int]),
+        "imdcu_set_table2": (C.c_int, [vp, C.c_int, c_dp]),
         "imdcu_set_params": (C.c_int, [vp, C.c_int, C.c_double, C.c_int, c_dp]),
         "imdcu_set_pdecay": (C.c_int, [vp, C.c_int, C.c_double, C.c_double, C.c_double]),
         "imdcu_upload_atoms": (C.c_int, [vp, C.c_int64, c_ip, c_ip, c_ip, c_dp, c_dp, c_dp]),
@@ -161,12 +164,19 @@ class Context:
         return dict(rank=v[0].value, nranks=v[1].value, xoff=v[2].value, ldimx=v[3].value)
 
     # ---- set-up
+    def set_interp(self, mode):
+        """Table interpolation of the run: "3point" (default), "4point", "spline" (potaccess.h:24-36)."""
+        self._ck(self.L.imdcu_set_interp(self.h, INTERP_MODES[mode] if isinstance(mode, str) else int(mode)))
+
     def set_table(self, which: int, pt):
         begin = np.ascontiguousarray(pt.begin, np.float64); end = np.ascontiguousarray(pt.end, np.float64)
         step = np.ascontiguousarray(pt.step, np.float64); inv = np.ascontiguousarray(pt.invstep, np.float64)
         ln = np.ascontiguousarray(pt.len, np.int32); tab = np.ascontiguousarray(pt.table, np.float64)
         self._ck(self.L.imdcu_set_table(self.h, which, pt.ncols, pt.maxsteps, _dp(begin), _dp(end), _dp(step),
                                         _dp(inv), _ip(ln), _dp(tab)))
+        if getattr(pt, "table2", None) is not None:
+            tab2 = np.ascontiguousarray(pt.table2, np.float64)
+            self._ck(self.L.imdcu_set_table2(self.h, which, _dp(tab2)))
 
     def set_box(self, box, pbc, nbl_margin, nbl_size=1.3, divisor=None):
         box = np.ascontiguousarray(box, np.float64).reshape(9)

@@ -138,14 +138,15 @@ extern "C" int imdcu_synchronize(imdcu_ctx *c)
 }
 
 // ----------------------------------------------------------------------------- table probe
-__global__ void k_eval_table(TabView v, int col, int64_t n, const double *__restrict__ arg,
+__global__ void k_eval_table(TabView v, int interp, int col, int64_t n, const double *__restrict__ arg,
                              double *__restrict__ val, double *__restrict__ grad)
 {
   int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  TabCol t = tab_col(v, v.coef, col);
   double p, g; int is_short = 0;
-  pair_int2(t, arg[i], p, g, is_short);
+  if (interp == IMDCU_INTERP_4POINT) raw_pair_int<1>(raw_col(v, col), arg[i], p, g, is_short);
+  else if (interp == IMDCU_INTERP_SPLINE) raw_pair_int<2>(raw_col(v, col), arg[i], p, g, is_short);
+  else pair_int2(tab_col(v, v.coef, col), arg[i], p, g, is_short);
   val[i] = p; grad[i] = g;
 }
 
@@ -159,7 +160,9 @@ extern "C" int imdcu_eval_table(imdcu_ctx *c, int which, int col, int64_t n, con
   double *d = nullptr;
   CU_CHECK(c, cudaMalloc(&d, 3 * n * sizeof(double)));
   CU_CHECK(c, cudaMemcpyAsync(d, arg, n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
-  k_eval_table<<<div_up(n, 256), 256, 0, c->stream>>>(imdcu_tab_view(c->tab[which]), col, n, d, d + n, d + 2 * n);
+  if (c->interp == IMDCU_INTERP_SPLINE && !c->tab[which].raw2)
+    return c->fail(IMDCU_EINVAL, "imdcu_eval_table: spline mode needs imdcu_set_table2");
+  k_eval_table<<<div_up(n, 256), 256, 0, c->stream>>>(imdcu_tab_view(c->tab[which]), c->interp, col, n, d, d + n, d + 2 * n);
   c->count_launch();
   CU_CHECK(c, cudaMemcpyAsync(val, d + n, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   CU_CHECK(c, cudaMemcpyAsync(grad, d + 2 * n, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));

@@ -84,7 +84,8 @@ struct DevBuf {
 struct DevTable {
   int     ncols = 0, nrows = 0;       // nrows = maxsteps
   double *coef = nullptr;             // [ncols][nrows][3]
-  double *begin = nullptr, *end = nullptr, *invstep = nullptr;   // [ncols] (device)
+  double *begin = nullptr, *end = nullptr, *invstep = nullptr, *step = nullptr;   // [ncols] (device)
+  double *raw = nullptr, *raw2 = nullptr;   // 4-point / spline modes: table and table2 as handed in, [(nrows+2)][ncols]
   std::vector<double> h_begin, h_end, h_step, h_invstep, h_table;
   std::vector<int>    h_len;
   int     maxsteps = 0;
@@ -94,7 +95,8 @@ struct DevTable {
 
 struct TabView {                      // passed by value to kernels
   const double *coef;                 // global coefficient rows
-  const double *begin, *end, *invstep;
+  const double *begin, *end, *invstep, *step;
+  const double *raw, *raw2;           // 4-point / spline modes (row-major, row stride ncols)
   int ncols, nrows;
 };
 
@@ -196,6 +198,7 @@ struct imdcu_ctx {
 
   // parameters
   int    ntypes = 1, nvtypes = 1;
+  int    interp = IMDCU_INTERP_3POINT;       // table interpolation of the run (imdcu_set_interp)
   double timestep = 0.0, nbl_margin = 0.0, nbl_size = 1.3;
   std::vector<double> restrictions;          // host copy
   DevBuf<double> d_restrictions;

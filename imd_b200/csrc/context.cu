@@ -85,6 +85,8 @@ extern "C" int imdcu_destroy(imdcu_ctx *c)
   for (int t = 0; t < 3; t++) {
     if (c->tab[t].coef) cudaFree(c->tab[t].coef);
     if (c->tab[t].begin) cudaFree(c->tab[t].begin);
+    if (c->tab[t].raw) cudaFree(c->tab[t].raw);
+    if (c->tab[t].raw2) cudaFree(c->tab[t].raw2);
   }
   cudaFree(c->d_results); cudaFreeHost(c->h_results);
   cudaFree(c->d_ticket); cudaFree(c->d_flags); cudaFreeHost(c->h_flags);
@@ -99,7 +101,8 @@ extern "C" int imdcu_destroy(imdcu_ctx *c)
 TabView imdcu_tab_view(const DevTable &t)
 {
   TabView v;
-  v.coef = t.coef; v.begin = t.begin; v.end = t.end; v.invstep = t.invstep;
+  v.coef = t.coef; v.begin = t.begin; v.end = t.end; v.invstep = t.invstep; v.step = t.step;
+  v.raw = t.raw; v.raw2 = t.raw2;
   v.ncols = t.ncols; v.nrows = t.nrows;
   return v;
 }
@@ -117,6 +120,8 @@ extern "C" int imdcu_set_table(imdcu_ctx *c, int which, int ncols, int maxsteps,
   c->fused_state = 0;
   if (t.coef) { cudaFree(t.coef); t.coef = nullptr; }
   if (t.begin) { cudaFree(t.begin); t.begin = nullptr; }
+  if (t.raw) { cudaFree(t.raw); t.raw = nullptr; }
+  if (t.raw2) { cudaFree(t.raw2); t.raw2 = nullptr; }
   t.ncols = ncols; t.nrows = maxsteps; t.maxsteps = maxsteps;
   t.h_begin.assign(begin, begin + ncols); t.h_end.assign(end, end + ncols);
   t.h_step.assign(step, step + ncols); t.h_invstep.assign(invstep, invstep + ncols);
@@ -138,12 +143,44 @@ extern "C" int imdcu_set_table(imdcu_ctx *c, int which, int ncols, int maxsteps,
     }
   CU_CHECK(c, cudaMalloc(&t.coef, coef.size() * sizeof(double)));
   CU_CHECK(c, imdcu_h2d(c, t.coef, coef.data(), coef.size() * sizeof(double)));
-  std::vector<double> info(3 * (size_t) ncols);
-  for (int i = 0; i < ncols; i++) { info[i] = begin[i]; info[ncols + i] = end[i]; info[2 * ncols + i] = invstep[i]; }
+  std::vector<double> info(4 * (size_t) ncols);
+  for (int i = 0; i < ncols; i++) {
+    info[i] = begin[i]; info[ncols + i] = end[i]; info[2 * ncols + i] = invstep[i]; info[3 * ncols + i] = step[i];
+  }
   CU_CHECK(c, cudaMalloc(&t.begin, info.size() * sizeof(double)));
   CU_CHECK(c, imdcu_h2d(c, t.begin, info.data(), info.size() * sizeof(double)));
-  t.end = t.begin + ncols; t.invstep = t.begin + 2 * ncols;
+  t.end = t.begin + ncols; t.invstep = t.begin + 2 * ncols; t.step = t.begin + 3 * ncols;
+  if (c->interp != IMDCU_INTERP_3POINT) {      // these modes read the table as the reference does
+    CU_CHECK(c, cudaMalloc(&t.raw, t.h_table.size() * sizeof(double)));
+    CU_CHECK(c, imdcu_h2d(c, t.raw, t.h_table.data(), t.h_table.size() * sizeof(double)));
+  }
   t.set = true;
+  return IMDCU_OK;
+}
+
+extern "C" int imdcu_set_interp(imdcu_ctx *c, int mode)
+{
+  if (!c || mode < IMDCU_INTERP_3POINT || mode > IMDCU_INTERP_SPLINE)
+    return c ? c->fail(IMDCU_EINVAL, "imdcu_set_interp: bad mode") : IMDCU_EINVAL;
+  for (int t = 0; t < 3; t++)
+    if (c->tab[t].set && mode != c->interp)
+      return c->fail(IMDCU_EINVAL, "imdcu_set_interp: call before imdcu_set_table");
+  c->interp = mode;
+  return IMDCU_OK;
+}
+
+extern "C" int imdcu_set_table2(imdcu_ctx *c, int which, const double *table2)
+{
+  if (!c || which < 0 || which > 2 || !table2)
+    return c ? c->fail(IMDCU_EINVAL, "imdcu_set_table2: bad argument") : IMDCU_EINVAL;
+  DevTable &t = c->tab[which];
+  if (!t.set || c->interp != IMDCU_INTERP_SPLINE)
+    return c->fail(IMDCU_EINVAL, "imdcu_set_table2: spline mode and imdcu_set_table first");
+  cudaSetDevice(c->device);
+  if (t.raw2) { cudaFree(t.raw2); t.raw2 = nullptr; }
+  const size_t n = (size_t) (t.maxsteps + 2) * t.ncols;
+  CU_CHECK(c, cudaMalloc(&t.raw2, n * sizeof(double)));
+  CU_CHECK(c, imdcu_h2d(c, t.raw2, table2, n * sizeof(double)));
   return IMDCU_OK;
 }
 

@@ -87,6 +87,58 @@ __device__ __forceinline__ TabCol tab_col(const TabView &v, const double *coef_b
   return t;
 }
 
+// The other two interpolation modes of potaccess.h read the table as the reference does (rows
+// k-1..k+2, or rows k, k+1 of table and table2), straight from global memory through L1: they are
+// the reference's compile-time options FOURPOINT / SPLINE, not the hot configuration.
+struct RawCol {
+  const double *t, *t2;      // column `col` of row 0
+  double begin, end, invstep, step;
+  int inc;
+};
+__device__ __forceinline__ RawCol raw_col(const TabView &v, int col)
+{
+  RawCol c;
+  c.t = v.raw + col; c.t2 = v.raw2 ? v.raw2 + col : nullptr;
+  c.begin = v.begin[col]; c.end = v.end[col]; c.invstep = v.invstep[col]; c.step = v.step[col];
+  c.inc = v.ncols;
+  return c;
+}
+// INTERP 1: PAIR_INT3 (potaccess.h:365-413), INTERP 2: PAIR_INT_SP (:421-457); VAL_FUNC* / DERIV_FUNC*
+// of a mode evaluate the same expressions, callers drop what they do not need
+template <int INTERP>
+__device__ __forceinline__ void raw_pair_int(const RawCol &c, double r2, double &pot, double &grad, int &is_short)
+{
+  double r2a = fmin(r2, c.end);
+  r2a = r2a - c.begin;
+  if (r2a < 0) { r2a = 0; is_short = 1; }
+  const double istep = c.invstep;
+  r2a = r2a * istep;
+  if (INTERP == 1) {
+    int k = (int) r2a; if (k < 1) k = 1;
+    const double chi = r2a - (double) k;
+    const double fac0 = -(1.0 / 6.0) * chi * (chi - 1.0) * (chi - 2.0);
+    const double fac1 = 0.5 * (chi * chi - 1.0) * (chi - 2.0);
+    const double fac2 = -0.5 * chi * (chi + 1.0) * (chi - 2.0);
+    const double fac3 = (1.0 / 6.0) * chi * (chi * chi - 1.0);
+    const double dfac0 = -(1.0 / 6.0) * ((3.0 * chi - 6.0) * chi + 2.0);
+    const double dfac1 = 0.5 * ((3.0 * chi - 4.0) * chi - 1.0);
+    const double dfac2 = -0.5 * ((3.0 * chi - 2.0) * chi - 2.0);
+    const double dfac3 = 1.0 / 6.0 * (3.0 * chi * chi - 1.0);
+    const double *p = c.t + (size_t) (k - 1) * c.inc;
+    const double p0 = __ldg(p), p1 = __ldg(p + c.inc), p2 = __ldg(p + 2 * c.inc), p3 = __ldg(p + 3 * c.inc);
+    pot = fac0 * p0 + fac1 * p1 + fac2 * p2 + fac3 * p3;
+    grad = 2 * istep * (dfac0 * p0 + dfac1 * p1 + dfac2 * p2 + dfac3 * p3);
+  } else {
+    const int k = (int) r2a;
+    const double b = r2a - (double) k, a = 1.0 - b;
+    const size_t o = (size_t) k * c.inc;
+    const double p1 = __ldg(c.t + o), d21 = __ldg(c.t2 + o), p2 = __ldg(c.t + o + c.inc), d22 = __ldg(c.t2 + o + c.inc);
+    const double a2 = a * a - 1, b2 = b * b - 1, st6 = c.step / 6;
+    pot = a * p1 + b * p2 + (a * a2 * d21 + b * b2 * d22) * st6 * c.step;
+    grad = 2 * ((p2 - p1) * istep + ((3 * b2 + 2) * d22 - (3 * a2 + 2) * d21) * st6);
+  }
+}
+
 // ----------------------------------------------------------------------------- reductions
 __device__ __forceinline__ double warp_sum(double v)
 {

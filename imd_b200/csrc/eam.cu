@@ -112,7 +112,8 @@ struct NbrPipe {
 
 // LPA lanes cooperate on one atom (1 for big systems, more to fill the GPU on small ones);
 // SMEM: tables staged in shared memory, else read through L1/L2; MULTI: ntypes > 1.
-template <int LPA, bool SMEM, bool MULTI>
+// INTERP: 0 three-point rows (the hot configuration), 1 four-point, 2 spline (raw tables through L1)
+template <int LPA, bool SMEM, bool MULTI, int INTERP>
 __global__ void __launch_bounds__(EAM_BLOCK1, EAM_MINB1)
 k_eam_pass1(EamArgs a)
 {
@@ -162,21 +163,34 @@ EAM_PRAGMA_UNROLL(EAM_UNROLL)
         const double4 pj = np.next(a.pos4, a.type, k, jt);
         const double dx = pj.x - pi.x, dy = pj.y - pi.y, dz = pj.z - pi.z;
         const double r2 = r2_exact(dx, dy, dz);
-        TabCol tp = tp0, tr = tr0;
-        if (MULTI) {
-          const int col = it * a.ntypes + jt;
-          tp = tab_col(a.pair, pair_c, col);
-          tr = tab_col(a.rhot, rho_c, col);
-        }
         if (a.count_ttm && r2 <= pair_end0 && it == 0 && jt == 0) nn++;
-        if (r2 <= tp.end) {
+        if (INTERP == 0) {
+          TabCol tp = tp0, tr = tr0;
+          if (MULTI) {
+            const int col = it * a.ntypes + jt;
+            tp = tab_col(a.pair, pair_c, col);
+            tr = tab_col(a.rhot, rho_c, col);
+          }
+          if (r2 <= tp.end) {
+            double pot, grad;
+            pair_int2(tp, r2, pot, grad, is_short);
+            fx += dx * grad; fy += dy * grad; fz += dz * grad;
+            ee += 0.5 * pot;
+            vir -= 0.5 * (r2 * grad);
+          }
+          if (r2 < tr.end) rh += val_func2(tr, r2, is_short);
+        } else {
+          const int col = it * a.ntypes + jt;
+          const RawCol cp = raw_col(a.pair, col), cr = raw_col(a.rhot, col);
           double pot, grad;
-          pair_int2(tp, r2, pot, grad, is_short);
-          fx += dx * grad; fy += dy * grad; fz += dz * grad;
-          ee += 0.5 * pot;
-          vir -= 0.5 * (r2 * grad);
+          if (r2 <= cp.end) {
+            raw_pair_int<INTERP == 0 ? 1 : INTERP>(cp, r2, pot, grad, is_short);
+            fx += dx * grad; fy += dy * grad; fz += dz * grad;
+            ee += 0.5 * pot;
+            vir -= 0.5 * (r2 * grad);
+          }
+          if (r2 < cr.end) { raw_pair_int<INTERP == 0 ? 1 : INTERP>(cr, r2, pot, grad, is_short); rh += pot; }
         }
-        if (r2 < tr.end) rh += val_func2(tr, r2, is_short);
       }
     }
     if (LPA > 1) {
@@ -187,8 +201,8 @@ EAM_PRAGMA_UNROLL(EAM_UNROLL)
     if (live && sub == 0) {
       // embedding energy and its derivative (imd_forces_nbl.c:758-760); table via L1/L2
       double pot, dF; int idummy = 0;
-      TabCol te = tab_col(a.emb, a.emb.coef, it);
-      pair_int2(te, rh, pot, dF, idummy);
+      if (INTERP == 0) pair_int2(tab_col(a.emb, a.emb.coef, it), rh, pot, dF, idummy);
+      else raw_pair_int<INTERP == 0 ? 1 : INTERP>(raw_col(a.emb, it), rh, pot, dF, idummy);
       ee += pot;
       a.frc4[i] = make_double4(fx, fy, fz, ee);
       a.rho[i] = rh;
@@ -313,7 +327,7 @@ EAM_PRAGMA_UNROLL(EAM_UNROLL)
   grid_reduce<2, 0>(acc, a.partials, a.ticket, a.results);
 }
 
-template <int LPA, bool SMEM, bool MULTI>
+template <int LPA, bool SMEM, bool MULTI, int INTERP>
 __global__ void __launch_bounds__(EAM_BLOCK2, EAM_MINB2)
 k_eam_pass2(EamArgs a)
 {
@@ -364,6 +378,18 @@ EAM_PRAGMA_UNROLL(EAM_UNROLL)
             fx += gx; fy += gy; fz += gz;
             vir -= 0.5 * (dx * gx + dy * gy + dz * gz);
           }
+        } else if (INTERP != 0) {
+          const int col1 = jt * a.ntypes + it, col2 = it * a.ntypes + jt;
+          const RawCol t1 = raw_col(a.rhot, col1), t2 = raw_col(a.rhot, col2);
+          if (r2 < t1.end || r2 < t2.end) {
+            double v, ri, rj;
+            raw_pair_int<INTERP == 0 ? 1 : INTERP>(t1, r2, v, ri, is_short);
+            if (col1 == col2) rj = ri; else raw_pair_int<INTERP == 0 ? 1 : INTERP>(t2, r2, v, rj, is_short);
+            const double grad = 0.5 * (pi.w * rj + pj.w * ri);
+            const double gx = dx * grad, gy = dy * grad, gz = dz * grad;
+            fx += gx; fy += gy; fz += gz;
+            vir -= 0.5 * (dx * gx + dy * gy + dz * gz);
+          }
         } else {
           const int col1 = jt * a.ntypes + it, col2 = it * a.ntypes + jt;
           const TabCol t1 = tab_col(a.rhot, rho_c, col1), t2 = tab_col(a.rhot, rho_c, col2);
@@ -406,14 +432,14 @@ static int launch_cfg(imdcu_ctx *c, K kern, int block, size_t smem, int *grid)
   return IMDCU_OK;
 }
 
-template <int LPA, bool SMEM, bool MULTI>
+template <int LPA, bool SMEM, bool MULTI, int INTERP = 0>
 static int run_passes(imdcu_ctx *c, EamArgs &a, size_t smem1, size_t smem2)
 {
   int g1 = 0, g2 = 0;
-  const bool fused = SMEM && !MULTI && a.fused;
+  const bool fused = SMEM && !MULTI && INTERP == 0 && a.fused;
   if (fused) RET_IF(launch_cfg(c, k_eam_pass1_fused<LPA>, EAM_BLOCK1, smem1, &g1));
-  else RET_IF(launch_cfg(c, k_eam_pass1<LPA, SMEM, MULTI>, EAM_BLOCK1, smem1, &g1));
-  RET_IF(launch_cfg(c, k_eam_pass2<LPA, SMEM, MULTI>, EAM_BLOCK2, smem2, &g2));
+  else RET_IF(launch_cfg(c, k_eam_pass1<LPA, SMEM, MULTI, INTERP>, EAM_BLOCK1, smem1, &g1));
+  RET_IF(launch_cfg(c, k_eam_pass2<LPA, SMEM, MULTI, INTERP>, EAM_BLOCK2, smem2, &g2));
   g1 = std::min(g1, div_up(a.n, EAM_BLOCK1 / LPA));
   g2 = std::min(g2, div_up(a.n, EAM_BLOCK2 / LPA));
   CU_CHECK(c, c->partials.ensure((size_t) std::max(g1, g2) * 4 + 64));
@@ -421,7 +447,7 @@ static int run_passes(imdcu_ctx *c, EamArgs &a, size_t smem1, size_t smem2)
   {
     PhaseTimer pt(c, 3);
     if (fused) k_eam_pass1_fused<LPA><<<g1, EAM_BLOCK1, smem1, c->stream>>>(a);
-    else k_eam_pass1<LPA, SMEM, MULTI><<<g1, EAM_BLOCK1, smem1, c->stream>>>(a);
+    else k_eam_pass1<LPA, SMEM, MULTI, INTERP><<<g1, EAM_BLOCK1, smem1, c->stream>>>(a);
     c->count_launch();
   }
   // calc_ttm overlapped with pass 2 (imdcu_run_ttm): numneighs of this step exist now; the lattice
@@ -435,7 +461,7 @@ static int run_passes(imdcu_ctx *c, EamArgs &a, size_t smem1, size_t smem2)
   RET_IF(imdcu_refresh_ghosts(c, false));          // F' (and positions again) to the images
   {
     PhaseTimer pt(c, 5);
-    k_eam_pass2<LPA, SMEM, MULTI><<<g2, EAM_BLOCK2, smem2, c->stream>>>(a);
+    k_eam_pass2<LPA, SMEM, MULTI, INTERP><<<g2, EAM_BLOCK2, smem2, c->stream>>>(a);
     c->count_launch();
   }
   CU_CHECK(c, cudaGetLastError());
@@ -447,6 +473,12 @@ static int run_lpa(imdcu_ctx *c, EamArgs &a)
 {
   const size_t pb = c->tab[IMDCU_TAB_PAIR].coef_bytes(), rb = c->tab[IMDCU_TAB_RHO].coef_bytes();
   const bool multi = c->ntypes > 1;
+  if (c->interp == IMDCU_INTERP_4POINT) return run_passes<LPA, false, true, 1>(c, a, 0, 0);
+  if (c->interp == IMDCU_INTERP_SPLINE) {
+    for (int t = 0; t < 3; t++)
+      if (!c->tab[t].raw2) return c->fail(IMDCU_EINVAL, "spline mode: imdcu_set_table2 missing for a table");
+    return run_passes<LPA, false, true, 2>(c, a, 0, 0);
+  }
   // two CTAs of 512 threads per SM when the tables allow it (<= ~110 KB per CTA)
   const bool smem_ok = (pb + rb + 1024 <= c->smem_optin) && (pb % 16 == 0) && (rb % 16 == 0);
   if (smem_ok) {
@@ -467,7 +499,7 @@ int imdcu_eam_forces(imdcu_ctx *c, double out8[8])
   a.pair = imdcu_tab_view(c->tab[IMDCU_TAB_PAIR]);
   a.rhot = imdcu_tab_view(c->tab[IMDCU_TAB_RHO]);
   a.emb = imdcu_tab_view(c->tab[IMDCU_TAB_EMBED]);
-  a.fused = imdcu_fused_table(c);
+  a.fused = c->interp == IMDCU_INTERP_3POINT ? imdcu_fused_table(c) : nullptr;
   a.partials = nullptr; a.ticket = c->d_ticket; a.results = c->d_results; a.flags = c->d_flags;
   a.count_ttm = 1;
   if (a.n > 0) {

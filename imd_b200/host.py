@@ -49,6 +49,9 @@ class Imd:
 
     # setup_potentials (imd_potential.c:43): pair_pot, rho_h_tab, embed_pot
     def setup_potentials(self, tables):
+        # the reference's compile-time FOURPOINT / SPLINE (read_pot_table finishes the tables accordingly,
+        # imd_potential.c:268-275) is a property of the tables handed in
+        self.ctx.set_interp(getattr(tables["pair"], "interp", "3point"))
         self.ctx.set_table(TAB_PAIR, tables["pair"])
         self.ctx.set_table(TAB_RHO, tables["rho"])
         self.ctx.set_table(TAB_EMBED, tables["emb"])

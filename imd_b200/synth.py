@@ -34,15 +34,45 @@ class PotTable:
     len: np.ndarray        # [ncols] int32
     maxsteps: int
     table: np.ndarray      # [(maxsteps+2), ncols] float64, C order
+    table2: Optional[np.ndarray] = None   # spline mode only: second derivatives, same shape (init_spline)
+    interp: str = "3point"                # "3point" | "4point" | "spline" (potaccess.h:24-36)
 
     @property
     def ncols(self) -> int:
         return int(self.begin.shape[0])
 
 
-def _table_from_columns(begin, end, step, cols, radial: bool) -> PotTable:
+def init_spline(tab: np.ndarray, ln, step, radial: bool) -> np.ndarray:
+    """Second-derivative table of the spline mode and the extra row of ``tab`` (in place), the
+    recurrences of init_spline (imd_potential.c:1201-1248) in the reference's operation order."""
+    nrows, ncols = tab.shape
+    tab2 = np.zeros_like(tab)
+    for col in range(ncols):
+        y, y2 = tab[:, col], tab2[:, col]
+        n, st = int(ln[col]), float(step[col])
+        u = np.zeros(nrows)
+        y2[0] = u[0] = 0.0
+        for i in range(1, n - 1):
+            p = 0.5 * y2[i - 1] + 2.0
+            y2[i] = -0.5 / p
+            u[i] = (y[i + 1] - 2 * y[i] + y[i - 1]) / st
+            u[i] = (6.0 * u[i] / (2 * st) - 0.5 * u[i - 1]) / p
+        if radial:
+            qn = 0.5
+            un = (3.0 / st) * (y[n - 2] - y[n - 1]) / st
+        else:
+            qn = un = 0.0
+        y2[n - 1] = (un - qn * u[n - 2]) / (qn * y2[n - 2] + 1.0)
+        for k in range(n - 2, -1, -1):
+            y2[k] = y2[k] * y2[k + 1] + u[k]
+        y[n] = 2 * y[n - 1] - y[n - 2] + (st * st) * y2[n - 1]
+        y2[n] = 2 * y2[n - 1] - y2[n - 2]
+    return tab2
+
+
+def _table_from_columns(begin, end, step, cols, radial: bool, interp: str = "3point") -> PotTable:
     """Assemble a PotTable from per-column value arrays exactly as read_pot_table2 +
-    init_threepoint do (imd_potential.c:394-466, 1260-1276)."""
+    init_threepoint / init_fourpoint / init_spline do (imd_potential.c:394-466, 1167-1276)."""
     ncols = len(cols)
     begin = np.asarray(begin, dtype=np.float64)
     end = np.asarray(end, dtype=np.float64)
@@ -61,12 +91,22 @@ def _table_from_columns(begin, end, step, cols, radial: bool) -> PotTable:
             delta = tab[ln[i] - 1, i]
             if delta != 0.0:
                 tab[: ln[i], i] -= delta
-    for i in range(ncols):
-        n = int(ln[i])
-        y = tab[:, i]
-        y[n] = 3 * y[n - 1] - 3 * y[n - 2] + y[n - 3]
-        y[n + 1] = 6 * y[n - 1] - 8 * y[n - 2] + 3 * y[n - 3]
-    return PotTable(begin, end, step, invstep, ln, maxsteps, np.ascontiguousarray(tab))
+    tab2 = None
+    if interp == "spline":
+        tab2 = init_spline(tab, ln, step, radial)
+    else:
+        for i in range(ncols):
+            n = int(ln[i])
+            y = tab[:, i]
+            if interp == "4point":         # init_fourpoint, imd_potential.c:1175-1191
+                y[n] = 4 * y[n - 1] - 6 * y[n - 2] + 4 * y[n - 3] - y[n - 4]
+                y[n + 1] = 10 * y[n - 1] - 20 * y[n - 2] + 15 * y[n - 3] - 4 * y[n - 4]
+            else:                          # init_threepoint, imd_potential.c:1260-1276
+                assert interp == "3point", interp
+                y[n] = 3 * y[n - 1] - 3 * y[n - 2] + y[n - 3]
+                y[n + 1] = 6 * y[n - 1] - 8 * y[n - 2] + 3 * y[n - 3]
+    return PotTable(begin, end, step, invstep, ln, maxsteps, np.ascontiguousarray(tab),
+                    None if tab2 is None else np.ascontiguousarray(tab2), interp)
 
 
 def write_pot_table2(path: str, begin, end, step, cols) -> None:
@@ -82,7 +122,7 @@ def write_pot_table2(path: str, begin, end, step, cols) -> None:
                 f.write("%.16e\n" % v)
 
 
-def read_pot_table2(path: str, ncols: int, radial: bool) -> PotTable:
+def read_pot_table2(path: str, ncols: int, radial: bool, interp: str = "3point") -> PotTable:
     """Reader for format 2 with the semantics of read_pot_table2 (imd_potential.c:394)."""
     with open(path) as f:
         lines = [ln for ln in f if not ln.startswith("#")]
@@ -96,7 +136,7 @@ def read_pot_table2(path: str, ncols: int, radial: bool) -> PotTable:
     for i in range(ncols):
         cols.append(vals[p: p + ln[i]])
         p += ln[i]
-    return _table_from_columns(begin, end, step, cols, radial)
+    return _table_from_columns(begin, end, step, cols, radial, interp)
 
 
 @dataclasses.dataclass
@@ -154,7 +194,7 @@ def eam_columns(spec: EamSpec):
             (0.0, rho_end, rstep, F))
 
 
-def make_eam_tables(spec: EamSpec, outdir: Optional[str] = None) -> Dict[str, PotTable]:
+def make_eam_tables(spec: EamSpec, outdir: Optional[str] = None, interp: str = "3point") -> Dict[str, PotTable]:
     """Tables for ntypes=1.  When ``outdir`` is given the three IMD format-2 files
     ``<name>.pair/.rho/.emb`` are written and the tables are re-read from the files, so
     that the in-memory values are exactly what the reference parses from the same text."""
@@ -165,12 +205,12 @@ def make_eam_tables(spec: EamSpec, outdir: Optional[str] = None) -> Dict[str, Po
         for key, (b, e, s, c), radial in (("pair", pair, True), ("rho", rho, True), ("emb", emb, False)):
             path = os.path.join(outdir, "%s.%s" % (spec.name, key))
             write_pot_table2(path, [b], [e], [s], [c])
-            out[key] = read_pot_table2(path, 1, radial)
+            out[key] = read_pot_table2(path, 1, radial, interp)
         return out
     return {
-        "pair": _table_from_columns([pair[0]], [pair[1]], [pair[2]], [pair[3]], True),
-        "rho": _table_from_columns([rho[0]], [rho[1]], [rho[2]], [rho[3]], True),
-        "emb": _table_from_columns([emb[0]], [emb[1]], [emb[2]], [emb[3]], False),
+        "pair": _table_from_columns([pair[0]], [pair[1]], [pair[2]], [pair[3]], True, interp),
+        "rho": _table_from_columns([rho[0]], [rho[1]], [rho[2]], [rho[3]], True, interp),
+        "emb": _table_from_columns([emb[0]], [emb[1]], [emb[2]], [emb[3]], False, interp),
     }
 
 
@@ -229,7 +269,7 @@ def binary_columns(b: BinarySpec):
     return pair, rho, emb
 
 
-def make_eam_tables_binary(b: BinarySpec, outdir: Optional[str] = None) -> Dict[str, PotTable]:
+def make_eam_tables_binary(b: BinarySpec, outdir: Optional[str] = None, interp: str = "3point") -> Dict[str, PotTable]:
     """Like make_eam_tables for ntypes = 2 (files <name>.pair/.rho/.emb with 4/4/2 columns)."""
     pair, rho, emb = binary_columns(b)
     out = {}
@@ -239,9 +279,9 @@ def make_eam_tables_binary(b: BinarySpec, outdir: Optional[str] = None) -> Dict[
             os.makedirs(outdir, exist_ok=True)
             path = os.path.join(outdir, "%s.%s" % (b.name, key))
             write_pot_table2(path, bg, en, st, vals)
-            out[key] = read_pot_table2(path, len(cols), radial)
+            out[key] = read_pot_table2(path, len(cols), radial, interp)
         else:
-            out[key] = _table_from_columns(bg, en, st, vals, radial)
+            out[key] = _table_from_columns(bg, en, st, vals, radial, interp)
     return out
 
 

@@ -76,6 +76,19 @@ int  imdcu_set_box(imdcu_ctx *ctx, const double box[9], const int pbc_dirs[3],
 int  imdcu_set_table(imdcu_ctx *ctx, int which, int ncols, int maxsteps,
                      const double *begin, const double *end, const double *step,
                      const double *invstep, const int *len, const double *table);
+/* Table interpolation of the whole run.  The reference chooses it at compile time (make-target
+ * substrings 4point / spline -> -DFOURPOINT / -DSPLINE, Makefile:917-923; potaccess.h:24-36):
+ *   IMDCU_INTERP_3POINT  PAIR_INT2 / VAL_FUNC2 / DERIV_FUNC2     (potaccess.h:323-354,465-495,591-621), default
+ *   IMDCU_INTERP_4POINT  PAIR_INT3 / VAL_FUNC3 / DERIV_FUNC3     (:365-413,503-540,630-667)
+ *   IMDCU_INTERP_SPLINE  PAIR_INT_SP / VAL_FUNC_SP / DERIV_FUNC_SP (:421-457,547-583,675-711)
+ * Call before imdcu_set_table; the tables must then be the ones init_fourpoint / init_spline
+ * finished (imd_potential.c:1175-1248), and in spline mode every table needs its second-derivative
+ * table (pot_table_t.table2, same shape as table) through imdcu_set_table2. */
+#define IMDCU_INTERP_3POINT 0
+#define IMDCU_INTERP_4POINT 1
+#define IMDCU_INTERP_SPLINE 2
+int  imdcu_set_interp(imdcu_ctx *ctx, int mode);
+int  imdcu_set_table2(imdcu_ctx *ctx, int which, const double *table2);
 /* ntypes, timestep, restrictions[3*nvtypes] (globals.h; imd_integrate.c:208-213) */
 int  imdcu_set_params(imdcu_ctx *ctx, int ntypes, double timestep,
                       int nvtypes, const double *restrictions);

@@ -21,7 +21,7 @@ c_ip = C.POINTER(C.c_int)
 class OrcTable(C.Structure):
     _fields_ = [("ncols", C.c_int), ("maxsteps", C.c_int),
                 ("begin", c_dp), ("end", c_dp), ("step", c_dp), ("invstep", c_dp),
-                ("len", c_ip), ("table", c_dp)]
+                ("len", c_ip), ("table", c_dp), ("table2", c_dp)]
 
 
 def build(force: bool = False) -> str:
@@ -53,6 +53,8 @@ def lib():
         L.orc_export_pairs.restype = C.c_long
         L.orc_export_pairs.argtypes = [C.c_void_p, c_ip]
         L.orc_pair_int2.argtypes = [C.POINTER(OrcTable), C.c_int, C.c_int, C.c_double, c_dp, c_dp, c_ip]
+        L.orc_pair_int.argtypes = [C.POINTER(OrcTable), C.c_int, C.c_int, C.c_double, c_dp, c_dp, c_ip]
+        L.orc_set_interp.argtypes = [C.c_int]
         _LIB = L
     return _LIB
 
@@ -65,6 +67,9 @@ def _ip(a):
     return a.ctypes.data_as(c_ip)
 
 
+INTERP_MODES = {"3point": 0, "4point": 1, "spline": 2}
+
+
 class Table:
     """Keeps the numpy buffers alive next to the C struct."""
 
@@ -73,8 +78,11 @@ class Table:
         self._keep = [np.ascontiguousarray(x, dtype=np.float64) for x in (pt.begin, pt.end, pt.step, pt.invstep)]
         self._len = np.ascontiguousarray(pt.len, dtype=np.int32)
         self._tab = np.ascontiguousarray(pt.table, dtype=np.float64)
+        self._tab2 = None if getattr(pt, "table2", None) is None else np.ascontiguousarray(pt.table2, dtype=np.float64)
         self.c = OrcTable(pt.ncols, pt.maxsteps, _dp(self._keep[0]), _dp(self._keep[1]),
-                          _dp(self._keep[2]), _dp(self._keep[3]), _ip(self._len), _dp(self._tab))
+                          _dp(self._keep[2]), _dp(self._keep[3]), _ip(self._len), _dp(self._tab),
+                          None if self._tab2 is None else _dp(self._tab2))
+        self.interp = INTERP_MODES[getattr(pt, "interp", "3point")]
 
     def pair_int(self, r2, col=0):
         L = lib()
@@ -82,8 +90,9 @@ class Table:
         pot = np.empty_like(r2)
         grad = np.empty_like(r2)
         p, g, s = C.c_double(), C.c_double(), C.c_int(0)
+        L.orc_set_interp(self.interp)
         for i, x in enumerate(r2):
-            L.orc_pair_int2(C.byref(self.c), col, self.pt.ncols, float(x), C.byref(p), C.byref(g), C.byref(s))
+            L.orc_pair_int(C.byref(self.c), col, self.pt.ncols, float(x), C.byref(p), C.byref(g), C.byref(s))
             pot[i], grad[i] = p.value, g.value
         return pot, grad
 
@@ -145,6 +154,7 @@ class EamOracle:
         types = np.ascontiguousarray(types, dtype=np.int32)
         force = np.empty((n, 3)); epot = np.empty(n); rho = np.empty(n); dF = np.empty(n)
         nn = np.empty(n, dtype=np.int32); out8 = np.zeros(8)
+        self.L.orc_set_interp(self.pair.interp)      # the mode of the tables handed in (a global of the C library)
         self.L.orc_calc_forces(self.s, _dp(pos), _ip(types), self.ntypes,
                                C.byref(self.pair.c), C.byref(self.rho.c), C.byref(self.emb.c),
                                _dp(force), _dp(epot), _dp(rho), _dp(dF), _ip(nn), _dp(out8))

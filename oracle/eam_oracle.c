@@ -78,6 +78,121 @@ void orc_init_threepoint(orc_table *pt)
   }
 }
 
+/* imd_potential.c:1175-1191 */
+void orc_init_fourpoint(orc_table *pt)
+{
+  int col, nc = pt->ncols;
+  for (col = 0; col < nc; col++) {
+    double *y = pt->table + col;
+    long n = pt->len[col];
+    y[n * nc]       =  4 * y[(n - 1) * nc] -  6 * y[(n - 2) * nc] +  4 * y[(n - 3) * nc] -     y[(n - 4) * nc];
+    y[(n + 1) * nc] = 10 * y[(n - 1) * nc] - 20 * y[(n - 2) * nc] + 15 * y[(n - 3) * nc] - 4 * y[(n - 4) * nc];
+  }
+}
+
+/* imd_potential.c:1201-1248 */
+void orc_init_spline(orc_table *pt, int radial)
+{
+  int col, nc = pt->ncols;
+  long size = pt->maxsteps + 2, i, k;
+  double *u = (double *) calloc((size_t) size, sizeof(double));
+  for (col = 0; col < nc; col++) {
+    double *y2 = pt->table2 + col, *y = pt->table + col;
+    long n = pt->len[col];
+    double step = pt->step[col], p, qn, un;
+    y2[0] = u[0] = 0;
+    for (i = 1; i < n - 1; i++) {
+      p = 0.5 * y2[(i - 1) * nc] + 2.0;
+      y2[i * nc] = -0.5 / p;
+      u[i] = (y[(i + 1) * nc] - 2 * y[i * nc] + y[(i - 1) * nc]) / step;
+      u[i] = (6.0 * u[i] / (2 * step) - 0.5 * u[i - 1]) / p;
+    }
+    if (radial) { qn = 0.5; un = (3.0 / step) * (y[(n - 2) * nc] - y[(n - 1) * nc]) / step; }
+    else qn = un = 0.0;
+    y2[(n - 1) * nc] = (un - qn * u[n - 2]) / (qn * y2[(n - 2) * nc] + 1.0);
+    for (k = n - 2; k >= 0; k--) y2[k * nc] = y2[k * nc] * y2[(k + 1) * nc] + u[k];
+    y[n * nc]  = 2 * y[(n - 1) * nc] - y[(n - 2) * nc] + (step * step) * y2[(n - 1) * nc];
+    y2[n * nc] = 2 * y2[(n - 1) * nc] - y2[(n - 2) * nc];
+  }
+  free(u);
+}
+
+/* potaccess.h:365-413 (value and twice the derivative, cubic through rows k-1..k+2) */
+static void pair_int3(const orc_table *pt, int col, int inc, double r2,
+                      double *pot, double *grad, int *is_short)
+{
+  double r2a, istep, chi, p0, p1, p2, p3;
+  double fac0, fac1, fac2, fac3, dfac0, dfac1, dfac2, dfac3;
+  const double *ptr;
+  int k;
+  r2a = (r2 < pt->end[col]) ? r2 : pt->end[col];
+  r2a = r2a - pt->begin[col];
+  if (r2a < 0) { r2a = 0; *is_short = 1; }
+  istep = pt->invstep[col];
+  r2a = r2a * istep;
+  k = (int) r2a; if (k < 1) k = 1;
+  chi = r2a - k;
+  fac0 = -(1.0 / 6.0) * chi * (chi - 1.0) * (chi - 2.0);
+  fac1 =        0.5 * (chi * chi - 1.0) * (chi - 2.0);
+  fac2 =       -0.5 * chi * (chi + 1.0) * (chi - 2.0);
+  fac3 =  (1.0 / 6.0) * chi * (chi * chi - 1.0);
+  dfac0 = -(1.0 / 6.0) * ((3.0 * chi - 6.0) * chi + 2.0);
+  dfac1 =        0.5 * ((3.0 * chi - 4.0) * chi - 1.0);
+  dfac2 =       -0.5 * ((3.0 * chi - 2.0) * chi - 2.0);
+  dfac3 =    1.0 / 6.0 * (3.0 * chi * chi - 1.0);
+  ptr = row_ptr(pt, k - 1, col, inc);
+  p0 = ptr[0]; p1 = ptr[inc]; p2 = ptr[2 * inc]; p3 = ptr[3 * inc];
+  *pot = fac0 * p0 + fac1 * p1 + fac2 * p2 + fac3 * p3;
+  *grad = 2 * istep * (dfac0 * p0 + dfac1 * p1 + dfac2 * p2 + dfac3 * p3);
+}
+
+/* potaccess.h:421-457 */
+static void pair_int_sp(const orc_table *pt, int col, int inc, double r2,
+                        double *pot, double *grad, int *is_short)
+{
+  double r2a, a, b, a2, b2, istep, step, st6, p1, p2, d21, d22;
+  long k;
+  r2a = (r2 < pt->end[col]) ? r2 : pt->end[col];
+  r2a = r2a - pt->begin[col];
+  if (r2a < 0) { r2a = 0; *is_short = 1; }
+  istep = pt->invstep[col];
+  step = pt->step[col];
+  r2a = r2a * istep;
+  k = (int) r2a;
+  b = r2a - k;
+  a = 1.0 - b;
+  k = k * inc + col;
+  p1 = pt->table[k]; d21 = pt->table2[k];
+  k += inc;
+  p2 = pt->table[k]; d22 = pt->table2[k];
+  a2 = a * a - 1;
+  b2 = b * b - 1;
+  st6 = step / 6;
+  *pot = a * p1 + b * p2 + (a * a2 * d21 + b * b2 * d22) * st6 * step;
+  *grad = 2 * ((p2 - p1) * istep + ((3 * b2 + 2) * d22 - (3 * a2 + 2) * d21) * st6);
+}
+
+static int g_interp = 0;
+void orc_set_interp(int mode) { g_interp = mode; }
+
+void orc_pair_int(const orc_table *pt, int col, int inc, double r2, double *pot, double *grad, int *is_short)
+{
+  if (g_interp == 1) pair_int3(pt, col, inc, r2, pot, grad, is_short);
+  else if (g_interp == 2) pair_int_sp(pt, col, inc, r2, pot, grad, is_short);
+  else orc_pair_int2(pt, col, inc, r2, pot, grad, is_short);
+}
+/* VAL_FUNC* and DERIV_FUNC* evaluate the same expressions as the PAIR_INT* of their mode */
+void orc_val_func(const orc_table *pt, int col, int inc, double r2, double *val, int *is_short)
+{
+  double g;
+  orc_pair_int(pt, col, inc, r2, val, &g, is_short);
+}
+void orc_deriv_func(const orc_table *pt, int col, int inc, double r2, double *grad, int *is_short)
+{
+  double v;
+  orc_pair_int(pt, col, inc, r2, &v, grad, is_short);
+}
+
 /* ---------------------------------------------------------------- state */
 
 orc_state *orc_create(void)
@@ -401,7 +516,7 @@ int orc_calc_forces(orc_state *s, const double *pos, const int *type, int ntypes
             r2 = d[0] * d[0] + d[1] * d[1] + d[2] * d[2];
             if (r2 <= pair->end[0] && it == 0 && jt == 0) { nbttm++; nnb[b] += 1; }   /* :473-481 */
             if (r2 <= pair->end[col]) {
-              orc_pair_int2(pair, col, inc, r2, &pot, &grad, &is_short);
+              orc_pair_int(pair, col, inc, r2, &pot, &grad, &is_short);
               tot_pot_energy += pot;
               f[0] = d[0] * grad; f[1] = d[1] * grad; f[2] = d[2] * grad;
               kraft[3 * b] -= f[0]; kraft[3 * b + 1] -= f[1]; kraft[3 * b + 2] -= f[2];
@@ -412,13 +527,13 @@ int orc_calc_forces(orc_state *s, const double *pos, const int *type, int ntypes
               virial -= r2 * grad;
             }
             if (r2 < rho->end[col]) {
-              orc_val_func2(rho, col, inc, r2, &rho_h, &is_short);
+              orc_val_func(rho, col, inc, r2, &rho_h, &is_short);
               eam_r += rho_h;
             }
             if (it == jt) {
               if (r2 < rho->end[col]) erho[b] += rho_h;
             } else if (r2 < rho->end[col2]) {
-              orc_val_func2(rho, col2, inc, r2, &rho_h, &is_short);
+              orc_val_func(rho, col2, inc, r2, &rho_h, &is_short);
               erho[b] += rho_h;
             }
           }
@@ -438,7 +553,7 @@ int orc_calc_forces(orc_state *s, const double *pos, const int *type, int ntypes
         int c1 = cidx(s, i, j, k), a;
         for (a = s->cl_off[c1]; a < s->cl_off[c1 + 1]; a++) {
           double pot;
-          orc_pair_int2(embed, type[s->cell_atom[a]], ntypes, erho[a], &pot, &edF[a], &idummy);
+          orc_pair_int(embed, type[s->cell_atom[a]], ntypes, erho[a], &pot, &edF[a], &idummy);
           poteng[a] += pot;
           tot_pot_energy += pot;
         }
@@ -465,9 +580,9 @@ int orc_calc_forces(orc_state *s, const double *pos, const int *type, int ntypes
             r2 = d[0] * d[0] + d[1] * d[1] + d[2] * d[2];
             if ((r2 < rho->end[col1]) || (r2 < rho->end[col2])) {
               double grad, rho_i_strich, rho_j_strich;
-              orc_deriv_func2(rho, col1, inc, r2, &rho_i_strich, &is_short);
+              orc_deriv_func(rho, col1, inc, r2, &rho_i_strich, &is_short);
               if (col1 == col2) rho_j_strich = rho_i_strich;
-              else orc_deriv_func2(rho, col2, inc, r2, &rho_j_strich, &is_short);
+              else orc_deriv_func(rho, col2, inc, r2, &rho_j_strich, &is_short);
               grad = 0.5 * (edF[a] * rho_j_strich + edF[b] * rho_i_strich);
               f[0] = d[0] * grad; f[1] = d[1] * grad; f[2] = d[2] * grad;
               kraft[3 * b] -= f[0]; kraft[3 * b + 1] -= f[1]; kraft[3 * b + 2] -= f[2];

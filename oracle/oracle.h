@@ -24,6 +24,7 @@ typedef struct {
   double *begin, *end, *step, *invstep;
   int    *len;
   double *table;            /* (maxsteps+2) rows x ncols, row-major, padded rows filled */
+  double *table2;           /* spline mode: second derivatives (init_spline), else NULL */
 } orc_table;
 
 typedef struct {
@@ -60,6 +61,19 @@ void orc_deriv_func2(const orc_table *pt, int col, int inc, double r2,
                      double *grad, int *is_short);
 /* imd_potential.c:1260-1276 */
 void orc_init_threepoint(orc_table *pt);
+
+/* The reference picks its table interpolation at compile time (potaccess.h:24-36, make-target
+   substrings 4point / spline); here it is a mode of the library: 0 three-point (default),
+   1 four-point (PAIR_INT3 / VAL_FUNC3 / DERIV_FUNC3, potaccess.h:365-413,503-540,630-667),
+   2 spline (PAIR_INT_SP / VAL_FUNC_SP / DERIV_FUNC_SP, :421-457,547-583,675-711). */
+void orc_set_interp(int mode);
+void orc_pair_int(const orc_table *pt, int col, int inc, double r2,
+                  double *pot, double *grad, int *is_short);
+void orc_val_func(const orc_table *pt, int col, int inc, double r2, double *val, int *is_short);
+void orc_deriv_func(const orc_table *pt, int col, int inc, double r2, double *grad, int *is_short);
+/* imd_potential.c:1175-1191 and :1201-1248 (table2 must hold (maxsteps+2)*ncols doubles) */
+void orc_init_fourpoint(orc_table *pt);
+void orc_init_spline(orc_table *pt, int radial);
 
 orc_state *orc_create(void);
 void orc_destroy(orc_state *s);

@@ -34,7 +34,16 @@ CASES = {
     # two species (L1_2), every table column on its own r^2 grid, asymmetric rho columns
     "ni3al_6x6x6_pbc": (synth.NI3AL, (6, 6, 6), (1, 1, 1), 0.08, 30, (0, 1, 15, 30), 0.5),
     "ni3al_7x5x6_free_x": (synth.NI3AL, (7, 5, 6), (0, 1, 1), 0.05, 12, (0, 12), 0.4),
+    # the other two table-interpolation modes of potaccess.h (reference built with -DFOURPOINT / -DSPLINE)
+    "cu_6x6x6_pbc_4point": (synth.CU, (6, 6, 6), (1, 1, 1), 0.10, 20, (0, 1, 20), 0.5),
+    "cu_6x6x6_pbc_spline": (synth.CU, (6, 6, 6), (1, 1, 1), 0.10, 20, (0, 1, 20), 0.5),
+    "ni3al_6x5x5_free_x_4point": (synth.NI3AL, (6, 5, 5), (0, 1, 1), 0.08, 12, (0, 12), 0.5),
+    "ni3al_6x5x5_free_x_spline": (synth.NI3AL, (6, 5, 5), (0, 1, 1), 0.08, 12, (0, 12), 0.5),
 }
+
+
+def interp_of(name):
+    return "4point" if name.endswith("_4point") else "spline" if name.endswith("_spline") else "3point"
 
 
 def load_dump(d, step):
@@ -75,7 +84,9 @@ def run_case(name, spec, box_param, pbc, starttemp, steps, dump_steps, margin, k
                                coordname="_l12" if binary else "_fcc", masses=spec.masses if binary else None)
         env = dict(os.environ, IMD_DUMP_DIR=os.path.join(work, "dump"),
                    IMD_DUMP_STEPS=",".join(str(s) for s in dump_steps))
-        res = subprocess.run([REF_BIN, "-p", "run.param"], cwd=work, env=env,
+        interp = interp_of(name)
+        ref_bin = REF_BIN if interp == "3point" else REF_BIN + "_" + interp
+        res = subprocess.run([ref_bin, "-p", "run.param"], cwd=work, env=env,
                              stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
         if res.returncode != 0:
             print(res.stdout[-3000:])
@@ -93,6 +104,7 @@ def run_case(name, spec, box_param, pbc, starttemp, steps, dump_steps, margin, k
         arrays["nbl_margin"] = np.array(margin)
         arrays["timestep"] = np.array(0.1)
         arrays["spec_name"] = np.array(spec.name)
+        arrays["interp"] = np.array(interp)
         out = os.path.join(ROOT, "tests", "golden", name + ".npz")
         np.savez_compressed(out, **arrays)
         print("%-18s atoms %6d  -> %s (%.0f kB)" % (name, arrays["s0_pre_id"].shape[0], out,

@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 
 from oracle.binding import EamOracle
-from tests.util import GOLDEN_CASES, Golden, canon_pairs
+from tests.util import GOLDEN_CASES, INTERP_CASES, Golden, canon_pairs
 
 RTOL = 1e-10
 
@@ -17,7 +17,7 @@ def rel_err(a, b):
     return np.max(np.abs(a - b)) / scale
 
 
-@pytest.mark.parametrize("case", GOLDEN_CASES)
+@pytest.mark.parametrize("case", GOLDEN_CASES + INTERP_CASES)
 def test_cells_nblist_forces(case):
     g = Golden(case)
     for s in g.steps:

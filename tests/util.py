@@ -9,6 +9,8 @@ from imd_b200 import synth
 GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 GOLDEN_CASES = ["cu_6x6x6_pbc", "cu_8x6x7_pbc", "cu_7x6x6_free_x", "al_5x5x5_pbc", "ni3al_6x6x6_pbc",
                 "ni3al_7x5x6_free_x"]
+INTERP_CASES = ["cu_6x6x6_pbc_4point", "cu_6x6x6_pbc_spline", "ni3al_6x5x5_free_x_4point",
+                "ni3al_6x5x5_free_x_spline"]     # potaccess.h FOURPOINT / SPLINE modes
 SPECS = {"cu": synth.CU, "al": synth.AL, "ni3al": synth.NI3AL}
 
 
@@ -19,7 +21,9 @@ class Golden:
         self.spec = SPECS[str(self.z["spec_name"])]
         self.binary = isinstance(self.spec, synth.BinarySpec)
         self.ntypes = 2 if self.binary else 1
-        self.tables = synth.make_eam_tables_binary(self.spec) if self.binary else synth.make_eam_tables(self.spec)
+        self.interp = str(self.z["interp"]) if "interp" in self.z.files else "3point"
+        self.tables = (synth.make_eam_tables_binary(self.spec, interp=self.interp) if self.binary
+                       else synth.make_eam_tables(self.spec, interp=self.interp))
         self.pbc = self.z["pbc"]
         self.box = np.diag(self.z["box_param"].astype(np.float64) * self.spec.a)
         self.margin = float(self.z["nbl_margin"])
