@@ -32,6 +32,14 @@ __device__ __forceinline__ double4 ld256(const double4 *p)
   return v;
 }
 
+// the same through the non-coherent path; only for arrays no thread writes while the kernel runs
+__device__ __forceinline__ double4 ld256nc(const double4 *p)
+{
+  double4 v;
+  asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(v.x), "=d"(v.y), "=d"(v.z), "=d"(v.w) : "l"(p));
+  return v;
+}
+
 // ----------------------------------------------------------------------------- tables
 // 3-point (quadratic in the argument) table access, potaccess.h:323-354.  `c` points to
 // the coefficient rows {p0, dv, d2v} of one column (shared or global memory).

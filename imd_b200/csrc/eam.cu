@@ -39,6 +39,17 @@
 #ifndef EAM_ABLATE
 #define EAM_ABLATE 0           /* timing experiments on k_eam_pass1_fused (profiles/eam_ablate.sh), 0 = product */
 #endif
+#ifndef EAM_IDX_CS
+#define EAM_IDX_CS 0           /* 1: list slots with ld.global.cs (streaming, evict first) */
+#endif
+#ifndef EAM_GATHER_NC
+#define EAM_GATHER_NC 0        /* 1: pass 2 gathers through the non-coherent path (ld.global.nc) */
+#endif
+#if EAM_IDX_CS
+#define LD_SLOT(p) __ldcs(p)
+#else
+#define LD_SLOT(p) (*(p))
+#endif
 #define EAM_PRAGMA_(x) _Pragma(#x)
 #define EAM_PRAGMA_UNROLL(n) EAM_PRAGMA_(unroll n)
 
@@ -70,7 +81,7 @@ __device__ __forceinline__ double sub_sum(double v)
 // as a plain loop the compiler keeps that chain serial per iteration and only the eight warps of a
 // scheduler overlap it.  Here the slot indices run three iterations ahead and the record of pair k+1
 // is requested before pair k is evaluated.
-template <int LPA, bool MULTI>
+template <int LPA, bool MULTI, bool NC = false>
 struct NbrPipe {
   const int *sp;            // my first slot
   int cnt;                  // my number of slots
@@ -81,9 +92,9 @@ struct NbrPipe {
   {
     sp = slot + (size_t) sub * 32;
     cnt = num > sub ? (num - sub + LPA - 1) / LPA : 0;
-    const int j1 = cnt > 0 ? sp[0] : 0;
-    j2 = cnt > 1 ? sp[ST] : 0;
-    j3 = cnt > 2 ? sp[2 * ST] : 0;
+    const int j1 = cnt > 0 ? LD_SLOT(sp) : 0;
+    j2 = cnt > 1 ? LD_SLOT(sp + ST) : 0;
+    j3 = cnt > 2 ? LD_SLOT(sp + 2 * ST) : 0;
     tn = 0;
     if (cnt > 0) { pn = rec(pos4, j1); if (MULTI) tn = type[j1]; }
     else pn = make_double4(0, 0, 0, 0);
@@ -95,7 +106,7 @@ struct NbrPipe {
 #if EAM_ABLATE == 2      /* timing experiment: no position gather */
     return make_double4(0.35 * (j & 7), 0.3 * ((j >> 3) & 7), 0.4 * ((j >> 6) & 7) + 1.1, 0.0);
 #else
-    return ld256(&pos4[j]);
+    return NC ? ld256nc(&pos4[j]) : ld256(&pos4[j]);
 #endif
   }
   __device__ __forceinline__ double4 next(const double4 *pos4, const int *type, int k, int &jt)
@@ -105,7 +116,7 @@ struct NbrPipe {
     if (EAM_ABLATE) { jc = jn; jn = j2; }
     if (k + 1 < cnt) { pn = rec(pos4, j2); if (MULTI) tn = type[j2]; }
     j2 = j3;
-    if (k + 3 < cnt) j3 = sp[(size_t) (k + 3) * ST];
+    if (k + 3 < cnt) j3 = LD_SLOT(sp + (size_t) (k + 3) * ST);
     return pj;
   }
 };
@@ -363,7 +374,7 @@ k_eam_pass2(EamArgs a)
       const int *slot = a.nbl_idx + ((size_t) (i >> 5) * a.cap) * 32 + (i & 31);
       int it = 0;
       if (MULTI) it = a.type[i];
-      NbrPipe<LPA, MULTI> np(a.pos4, a.type, slot, num, sub);
+      NbrPipe<LPA, MULTI, EAM_GATHER_NC != 0> np(a.pos4, a.type, slot, num, sub);
 EAM_PRAGMA_UNROLL(EAM_UNROLL)
       for (int k = 0; k < np.cnt; k++) {
         int jt = 0;

@@ -32,6 +32,22 @@ k_nbl_build(Geom g, int n, const double4 *__restrict__ pos4, const int *__restri
           const int c2 = c + (l * ey + m) * ez + q;
           const int b = cell_begin[c2], e = b + cell_count[c2];
           const bool lexneg = (l < 0) || (l == 0 && m < 0) || (l == 0 && m == 0 && q < 0);
+          if (!(lexneg && e > n)) {
+            // plain candidates, four records requested ahead of their distance tests
+            for (int j = b; j < e; j += 4) {
+              const int j1 = min(j + 1, e - 1), j2 = min(j + 2, e - 1), j3 = min(j + 3, e - 1);
+              const double4 q0 = ld256(&pos4[j]), q1 = ld256(&pos4[j1]), q2 = ld256(&pos4[j2]), q3 = ld256(&pos4[j3]);
+              const double r0 = r2_exact(q0.x - pi.x, q0.y - pi.y, q0.z - pi.z);
+              const double r1 = r2_exact(q1.x - pi.x, q1.y - pi.y, q1.z - pi.z);
+              const double r2 = r2_exact(q2.x - pi.x, q2.y - pi.y, q2.z - pi.z);
+              const double r3 = r2_exact(q3.x - pi.x, q3.y - pi.y, q3.z - pi.z);
+              if (j != i && r0 < g.cellsz) { if (!COUNT_ONLY && cnt < cap) slot[(size_t) cnt * 32] = j; cnt++; }
+              if (j + 1 < e && j + 1 != i && r1 < g.cellsz) { if (!COUNT_ONLY && cnt < cap) slot[(size_t) cnt * 32] = j + 1; cnt++; }
+              if (j + 2 < e && j + 2 != i && r2 < g.cellsz) { if (!COUNT_ONLY && cnt < cap) slot[(size_t) cnt * 32] = j + 2; cnt++; }
+              if (j + 3 < e && j + 3 != i && r3 < g.cellsz) { if (!COUNT_ONLY && cnt < cap) slot[(size_t) cnt * 32] = j + 3; cnt++; }
+            }
+            continue;
+          }
           for (int j = b; j < e; j++) {
             if (j == i) continue;
             double dx, dy, dz;
