@@ -133,6 +133,7 @@ extern "C" int imdcu_synchronize(imdcu_ctx *c)
 {
   if (!c) return IMDCU_EINVAL;
   cudaSetDevice(c->device);
+  RET_IF(imdcu_join_upload(c));
   CU_CHECK(c, cudaStreamSynchronize(c->stream));
   return imdcu_check_flags(c);
 }

@@ -69,6 +69,8 @@ extern "C" int imdcu_upload_atoms(imdcu_ctx *c, int64_t n, const int32_t *id, co
     return c ? c->fail(IMDCU_EINVAL, "imdcu_upload_atoms: bad argument") : IMDCU_EINVAL;
   if (n >= (int64_t) 1 << 30) return c->fail(IMDCU_EINVAL, "imdcu_upload_atoms: more than 2^30 atoms per rank");
   cudaSetDevice(c->device);
+  RET_IF(imdcu_join_upload(c));
+  CU_CHECK(c, cudaStreamSynchronize(c->up_stream));          // buffers may be reallocated below
   RET_IF(ensure_atom_capacity(c, n));
   std::vector<int> ht((size_t) n), hv((size_t) n), hi((size_t) n);
   for (int64_t i = 0; i < n; i++) {
@@ -102,6 +104,18 @@ extern "C" int imdcu_upload_atoms(imdcu_ctx *c, int64_t n, const int32_t *id, co
   return IMDCU_OK;
 }
 
+// the two halves of k_unpack_in for imdcu_update_atoms (st: 3 doubles per atom)
+__global__ void __launch_bounds__(256)
+k_unpack_xyz(int n, const double *__restrict__ st, double4 *__restrict__ dst)
+{
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double *p = st + 3 * (size_t) i;
+  double4 x = dst[i];
+  x.x = p[0]; x.y = p[1]; x.z = p[2];
+  dst[i] = x;
+}
+
 // positions and momenta of the SAME atoms in the device's current order (the order of the
 // last imdcu_download_atoms): the neighbour list stays valid, check_nblist decides later.
 extern "C" int imdcu_update_atoms(imdcu_ctx *c, const double *pos, const double *mom)
@@ -110,12 +124,20 @@ extern "C" int imdcu_update_atoms(imdcu_ctx *c, const double *pos, const double 
   cudaSetDevice(c->device);
   const int64_t n = c->n;
   if (n == 0) return IMDCU_OK;
-  cudaStream_t s = c->stream;
+  cudaStream_t s = c->stream, u = c->up_stream;
   double *st = c->stage.p;
+  RET_IF(imdcu_join_upload(c));
+  // calc_forces needs the positions only: the momenta go over a second stream and are awaited by the
+  // first thing that touches mom4 (imdcu_join_upload), so their copy runs beside the force passes
+  CU_CHECK(c, cudaEventRecord(c->ev_up0, s));                 // staging and mom4 are free once earlier work is done
+  CU_CHECK(c, cudaStreamWaitEvent(u, c->ev_up0, 0));
   CU_CHECK(c, cudaMemcpyAsync(st, pos, 3 * n * sizeof(double), cudaMemcpyHostToDevice, s));
-  CU_CHECK(c, cudaMemcpyAsync(st + 3 * n, mom, 3 * n * sizeof(double), cudaMemcpyHostToDevice, s));
-  k_unpack_in<<<div_up(n, 256), 256, 0, s>>>((int) n, st, 0, c->pos4.p, c->mom4.p);
-  c->count_launch();
+  k_unpack_xyz<<<div_up(n, 256), 256, 0, s>>>((int) n, st, c->pos4.p);
+  CU_CHECK(c, cudaMemcpyAsync(st + 3 * n, mom, 3 * n * sizeof(double), cudaMemcpyHostToDevice, u));
+  k_unpack_xyz<<<div_up(n, 256), 256, 0, u>>>((int) n, st + 3 * n, c->mom4.p);
+  CU_CHECK(c, cudaEventRecord(c->ev_up, u));
+  c->up_pending = true;
+  c->count_launch(2);
   CU_CHECK(c, cudaGetLastError());
   return IMDCU_OK;
 }
@@ -131,6 +153,7 @@ extern "C" int imdcu_download_atoms(imdcu_ctx *c, int32_t *id, int32_t *type, do
   const int64_t n = c->n;
   cudaStream_t s = c->stream;
   if (n == 0) return IMDCU_OK;
+  RET_IF(imdcu_join_upload(c));
   double *st = c->stage.p;
   const int nb = div_up(n, 256);
   if (pos || mom || force || epot) {

@@ -205,6 +205,7 @@ int imdcu_refresh_ghosts(imdcu_ctx *c, bool at_build)
 
 int imdcu_rebuild_cells(imdcu_ctx *c)
 {
+  RET_IF(imdcu_join_upload(c));
   PhaseTimer pt(c, 0);
   int n = (int) c->n;
   cudaStream_t st = c->stream;

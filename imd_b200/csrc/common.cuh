@@ -192,6 +192,9 @@ struct NrbState {
 struct imdcu_ctx {
   int          device = 0;
   cudaStream_t stream = nullptr;
+  cudaStream_t up_stream = nullptr;          // imdcu_update_atoms: the momenta travel beside the force passes
+  cudaEvent_t  ev_up = nullptr, ev_up0 = nullptr;
+  bool         up_pending = false;
   std::string  err;
   int          num_sms = 148;
   size_t       smem_optin = 0;
@@ -308,6 +311,17 @@ struct PhaseTimer {                 // CUDA-event bracket on the context's strea
     c->cur_phase = -1;
   }
 };
+
+// momenta uploaded by imdcu_update_atoms on the second stream must have landed before anything reads or
+// writes mom4 (cell sort, nrb_forces, update_fd, integrators, downloads): those call this first
+static inline int imdcu_join_upload(imdcu_ctx *c)
+{
+  if (c->up_pending) {
+    c->up_pending = false;
+    CU_CHECK(c, cudaStreamWaitEvent(c->stream, c->ev_up, 0));
+  }
+  return IMDCU_OK;
+}
 
 // ----------------------------------------------------------------------------- internal API
 int imdcu_rebuild_cells(imdcu_ctx *ctx);                 // cells.cu: wrap, bin, sort, ghosts

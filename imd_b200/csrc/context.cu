@@ -47,6 +47,9 @@ extern "C" int imdcu_create(imdcu_ctx **out, int device)
     c->ttm_isolate_smem = want < c->smem_optin ? want : c->smem_optin;
   }
   CREATE_CHECK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  CREATE_CHECK(cudaStreamCreateWithFlags(&c->up_stream, cudaStreamNonBlocking));
+  CREATE_CHECK(cudaEventCreateWithFlags(&c->ev_up, cudaEventDisableTiming));
+  CREATE_CHECK(cudaEventCreateWithFlags(&c->ev_up0, cudaEventDisableTiming));
   CREATE_CHECK(cudaEventCreate(&c->ev0));
   CREATE_CHECK(cudaEventCreate(&c->ev1));
   CREATE_CHECK(cudaMalloc(&c->d_results, 32 * sizeof(double)));
@@ -68,6 +71,8 @@ extern "C" int imdcu_destroy(imdcu_ctx *c)
   if (!c) return IMDCU_EINVAL;
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
+  cudaStreamSynchronize(c->up_stream);
+  cudaEventDestroy(c->ev_up); cudaEventDestroy(c->ev_up0); cudaStreamDestroy(c->up_stream);
   c->pos4.release(); c->pos4_alt.release(); c->mom4.release(); c->mom4_alt.release();
   c->frc4.release(); c->rho.release(); c->dF.release(); c->refx.release(); c->refy.release(); c->refz.release();
   c->type.release(); c->type_alt.release(); c->vtype.release(); c->vtype_alt.release();

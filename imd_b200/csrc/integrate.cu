@@ -103,6 +103,7 @@ int imdcu_integrate_ttm(imdcu_ctx *c, double out8[8], int *valid)
 
 static int integrate(imdcu_ctx *c, double out8[8], int *valid, bool ttm)
 {
+  RET_IF(imdcu_join_upload(c));
   PhaseTimer pt(c, 6);
   MoveArgs a;
   a.n = (int) c->n;

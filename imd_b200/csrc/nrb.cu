@@ -242,6 +242,7 @@ int imdcu_nrb_forces(imdcu_ctx *c, int steps)
   NrbState &t = c->nrb;
   if (!t.active) return IMDCU_OK;
   if (steps <= 1 && !t.startup_images) return IMDCU_OK;
+  RET_IF(imdcu_join_upload(c));
   NrbArgs a;
   a.nent = t.nent; a.n = (int) c->n; a.maxid = t.maxid; a.cap = c->nbl_cap;
   a.k = t.k;

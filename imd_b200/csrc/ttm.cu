@@ -917,6 +917,7 @@ static int ttm_atoms_part(imdcu_ctx *c, int steps)
   TtmState &t = c->ttm;
   cudaStream_t st = c->stream;
   const int n = (int) c->n, G = t.G;
+  RET_IF(imdcu_join_upload(c));
   if (t.fdi.cap < (size_t) n) {
     CU_CHECK(c, t.fdi.ensure(c->key.cap)); CU_CHECK(c, t.fdi_alt.ensure(c->key.cap));
     CU_CHECK(c, cudaMemsetAsync(t.fdi.p, 0, c->key.cap * sizeof(int), st));

@@ -83,6 +83,38 @@ def test_full_loop_matches_reference(name):
     imd.close()
 
 
+def test_host_buffer_steps_equal_resident_steps():
+    """imdcu_update_atoms uploads the momenta on a second stream beside the force passes; every reader of
+    the momenta (cell sort, update_fd, NRB, integrators, downloads) waits for them.  A run that hands
+    positions and momenta through host buffers every step must therefore equal the resident run bit for
+    bit -- atoms and FD lattice -- across neighbour-list rebuilds."""
+    g = TtmGolden("ttm_al_48x5x5_p2_hot")
+    nsteps = 30
+
+    def run(through_host):
+        imd = make_imd(g)
+        n = imd.natoms
+        hp, hm = np.empty((n, 3)), np.empty((n, 3))
+        imd.ctx.download_into(hp, hm)
+        for s in range(nsteps):
+            if through_host:
+                imd.ctx.update_atoms(hp, hm)
+            imd.calc_forces(s)
+            imd.calc_ttm(s)
+            imd.move_atoms_ttm()
+            if through_host:
+                imd.ctx.download_into(hp, hm)
+        out = imd.atoms(fields=("id", "pos", "mom")), {k: np.array(v) for k, v in imd.ttm_lattice()["fields"].items()}, imd.nbl_count
+        imd.close()
+        return out
+
+    (a, lat_a, nb_a), (b, lat_b, nb_b) = run(False), run(True)
+    assert nb_a == nb_b and nb_a >= 2, (nb_a, nb_b)
+    assert np.array_equal(a["pos"], b["pos"]) and np.array_equal(a["mom"], b["mom"])
+    for k in lat_a:
+        assert np.array_equal(lat_a[k], lat_b[k], equal_nan=True), k
+
+
 def test_against_oracle_seeded_film():
     """A film the reference never saw (different size, seed, slab count, emulated rank count):
     device vs CPU oracle, step by step for a few steps."""
