@@ -433,8 +433,9 @@ def our_arm(args, rank, local_rank, world):
         roofline = {"kernel": "k_eam_pass1_fused", "bound": "hbm", "achieved": achieved, "peak": peak,
                     "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                     "peak_source": peak_src, "alg_bytes_per_launch": alg_bytes, "ms_per_launch": p1_ms,
-                    "note": "not HBM-bound: L1 data pipe 82 % busy (per pair one random 48-byte table row from shared "
-                            "memory and one 32-byte gather), FP64 pipe 28 %, DRAM 8 % (profiles/r01d_full_ncu.txt)"}
+                    "note": "not HBM-bound: L1 data pipe 92 % busy (per pair one random 48-byte table row from shared "
+                            "memory, 46 % of those wavefronts bank conflicts, and one 32-byte gather), FP64 pipe 35 %, "
+                            "DRAM 12 % (profiles/r01g_full_ncu.txt, ablations in profiles/r01g_eam_variants.txt)"}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

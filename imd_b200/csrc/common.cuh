@@ -195,6 +195,7 @@ struct imdcu_ctx {
   cudaStream_t up_stream = nullptr;          // imdcu_update_atoms: the momenta travel beside the force passes
   cudaEvent_t  ev_up = nullptr, ev_up0 = nullptr;
   bool         up_pending = false;
+  bool         force_sums_pending = false;   // multi-GPU: Epot/virial sums ride on the integrator's all-reduce
   std::string  err;
   int          num_sms = 148;
   size_t       smem_optin = 0;

@@ -532,7 +532,11 @@ int imdcu_eam_forces(imdcu_ctx *c, double out8[8])
     if (c->fuse_ttm_steps >= 0) RET_IF(imdcu_ttm_fork(c, c->fuse_ttm_steps));
     if (c->comm.nranks > 1) RET_IF(imdcu_refresh_ghosts(c, false));   // the neighbours still expect the F' exchange
   }
-  RET_IF(imdcu_multi_allreduce(c, c->d_results, 3, 0));               // MPI_Allreduce of imd_forces_nbl.c:997-1016
+  // MPI_Allreduce of imd_forces_nbl.c:997-1016.  When the caller does not read the sums now (the main-loop
+  // entry points without an energy buffer) they are reduced together with the integrator's sums, one
+  // all-reduce per step instead of three.
+  if (out8 || c->comm.nranks <= 1) { RET_IF(imdcu_multi_allreduce(c, c->d_results, 3, 0)); c->force_sums_pending = false; }
+  else c->force_sums_pending = true;
   if (out8) {
     CU_CHECK(c, cudaMemcpyAsync(c->h_results, c->d_results, 4 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     CU_CHECK(c, cudaStreamSynchronize(c->stream));

@@ -94,6 +94,13 @@ k_move_ttm(MoveArgs a, const int *__restrict__ type, int G, double fd_hx,
 
 static int integrate(imdcu_ctx *c, double out8[8], int *valid, bool ttm);
 
+// results[5] = this rank's max displacement^2 -> results[6] = 1 if it asks for a new list
+__global__ void k_nbl_flag(double *results, double lim)
+{
+  results[3] = 0.0;
+  results[6] = results[5] > lim ? 1.0 : 0.0;
+}
+
 int imdcu_integrate_nve(imdcu_ctx *c, double out8[8], int *valid) { return integrate(c, out8, valid, false); }
 int imdcu_integrate_ttm(imdcu_ctx *c, double out8[8], int *valid)
 {
@@ -120,15 +127,24 @@ static int integrate(imdcu_ctx *c, double out8[8], int *valid, bool ttm)
   else k_move_nve<<<grid, 256, 0, c->stream>>>(a);
   c->count_launch();
   CU_CHECK(c, cudaGetLastError());
-  RET_IF(imdcu_multi_allreduce(c, c->d_results + 4, 1, 0));           // tot_kin_energy (imd_integrate.c:790-808)
-  RET_IF(imdcu_multi_allreduce(c, c->d_results + 5, 1, 1));           // check_nblist's MAX (imd_forces_nbl.c:1085)
-  CU_CHECK(c, cudaMemcpyAsync(c->h_results + 4, c->d_results + 4, 2 * sizeof(double),
+  // check_nblist: invalidate when max displacement^2 > (0.5*nbl_margin)^2 on any rank
+  const double lim = (0.5 * c->nbl_margin) * (0.5 * c->nbl_margin);
+  const bool multi = c->comm.nranks > 1;
+  if (multi) {
+    // tot_kin_energy (imd_integrate.c:790-808) and check_nblist's MPI_MAX (imd_forces_nbl.c:1085) in ONE sum:
+    // the maximum is only compared with the limit, so every rank contributes a 0/1 flag instead; pending
+    // force sums (slots 0..2) ride along.  Slots 3 and 5 are reduced too and not used.
+    k_nbl_flag<<<1, 1, 0, c->stream>>>(c->d_results, lim);
+    c->count_launch();
+    if (c->force_sums_pending) RET_IF(imdcu_multi_allreduce(c, c->d_results, 7, 0));
+    else RET_IF(imdcu_multi_allreduce(c, c->d_results + 4, 3, 0));
+    c->force_sums_pending = false;
+  }
+  CU_CHECK(c, cudaMemcpyAsync(c->h_results + 4, c->d_results + 4, 3 * sizeof(double),
                               cudaMemcpyDeviceToHost, c->stream));
   CU_CHECK(c, cudaStreamSynchronize(c->stream));
   if (out8) { for (int k = 0; k < 8; k++) out8[k] = 0.0; out8[0] = c->h_results[4]; }
-  // check_nblist: invalidate when max displacement^2 > (0.5*nbl_margin)^2
-  const double lim = (0.5 * c->nbl_margin) * (0.5 * c->nbl_margin);
-  if (c->h_results[5] > lim) c->have_valid_nbl = false;
+  if (multi ? c->h_results[6] > 0.5 : c->h_results[5] > lim) c->have_valid_nbl = false;
   if (valid) *valid = c->have_valid_nbl ? 1 : 0;
   return IMDCU_OK;
 }
