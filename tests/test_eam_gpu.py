@@ -177,3 +177,47 @@ def test_energy_conservation_and_momentum():
     assert drift < 2e-5, drift
     assert imd.nbl_count >= 1
     imd.close()
+
+
+def test_full_size_properties_and_kernel_variants():
+    """BASELINE.json configs[1] at full size (Al, 80^3 cubic cells = 2 048 000 atoms): the hot instantiations
+    (one lane per atom, interleaved-row pass 1, pipelined neighbour loop) against (a) size-independent
+    properties -- sum F = 0, momentum and NVE energy conserved -- and (b) the four-lanes-per-atom general
+    instantiations that the golden tests exercise at small sizes, on the same resident atoms."""
+    import os
+    spec = synth.AL
+    tables = synth.make_eam_tables(spec)
+    pos, box = synth.fcc_lattice((80, 80, 80), spec.a)
+    rng = np.random.default_rng(11)
+    pos = pos + rng.normal(0.0, 0.04, pos.shape)
+    mom = synth.maxwell_momenta(pos.shape[0], spec.mass, 0.0258, seed=7)
+    imd = make_imd(box, (1, 1, 1), tables, 0.4)
+    imd.set_atoms(pos, mom, spec.mass)
+    imd.calc_forces(0)
+    a = imd.atoms(("id", "force", "epot", "rho", "dF"))
+    e_hot = imd.tot_pot_energy
+    fscale = np.abs(a["force"]).max()
+    assert np.abs(a["force"].sum(axis=0)).max() < 1e-9 * np.abs(a["force"]).sum()
+    old = {k: os.environ.get(k) for k in ("IMDCU_LPA", "IMDCU_FUSED_TABLE")}
+    try:
+        os.environ["IMDCU_LPA"] = "4"
+        imd.calc_forces(0)
+        b = imd.atoms(("id", "force", "epot", "rho", "dF"))
+        e_lpa = imd.tot_pot_energy
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+    assert np.abs(a["force"] - b["force"]).max() < 1e-11 * fscale
+    for key in ("epot", "rho", "dF"):
+        assert rel_err(a[key], b[key]) < 1e-12, key
+    assert abs(e_hot - e_lpa) < 1e-12 * abs(e_hot)
+    e = imd.main_loop(25)
+    got = imd.atoms(("id", "mom"))
+    assert np.abs(got["mom"].sum(axis=0) - mom.sum(axis=0)).max() < 1e-6
+    etot = e[1:, 0] + e[1:, 1]
+    assert np.abs(etot - etot[0]).max() / pos.shape[0] < 2e-5
+    assert imd.nbl_count >= 1
+    imd.close()
