@@ -55,6 +55,9 @@ def lib():
         L.orc_pair_int2.argtypes = [C.POINTER(OrcTable), C.c_int, C.c_int, C.c_double, c_dp, c_dp, c_ip]
         L.orc_pair_int.argtypes = [C.POINTER(OrcTable), C.c_int, C.c_int, C.c_double, c_dp, c_dp, c_ip]
         L.orc_set_interp.argtypes = [C.c_int]
+        L.orc_init_fourpoint.argtypes = [C.POINTER(OrcTable)]
+        L.orc_init_spline.argtypes = [C.POINTER(OrcTable), C.c_int]
+        L.orc_init_threepoint.argtypes = [C.POINTER(OrcTable)]
         _LIB = L
     return _LIB
 

@@ -80,3 +80,31 @@ def test_trajectory_matches_reference():
         if orc.max_displacement2(pos, ref_pos) > (0.5 * g.margin) ** 2:
             valid = False
     orc.close()
+
+
+@pytest.mark.parametrize("interp", ["3point", "4point", "spline"])
+def test_table_finish_host_mirror_equals_oracle(interp):
+    """imd_b200/synth.py finishes the tables the way read_pot_table does for the mode (init_threepoint /
+    init_fourpoint / init_spline, imd_potential.c:1167-1276); the C restatement does the same from the raw
+    columns.  Both must give the same bits (extra rows and, for splines, the second-derivative table)."""
+    import ctypes as C
+    from oracle import binding
+    from imd_b200 import synth
+    L = binding.lib()
+    for tables in (synth.make_eam_tables(synth.CU, interp=interp), synth.make_eam_tables_binary(synth.NI3AL, interp=interp)):
+        for key, radial in (("pair", 1), ("rho", 1), ("emb", 0)):
+            pt = tables[key]
+            t = binding.Table(pt)
+            raw = np.array(pt.table, copy=True)
+            for c in range(pt.ncols):
+                raw[pt.len[c]:, c] = 0.0                 # what read_pot_table2 leaves behind the data
+            t._tab[...] = raw
+            if interp == "spline":
+                t._tab2[...] = 0.0
+                L.orc_init_spline(C.byref(t.c), radial)
+                assert np.array_equal(t._tab2, pt.table2)
+            elif interp == "4point":
+                L.orc_init_fourpoint(C.byref(t.c))
+            else:
+                L.orc_init_threepoint(C.byref(t.c))
+            assert np.array_equal(t._tab, pt.table), (interp, key)
