@@ -428,6 +428,29 @@ def make_eos_tables(nrho: int = 48, nt: int = 96, z_free: float = 3.0, a_weight:
     return {"cve": EosTable(rho, t_geo, cve), "ee": EosTable(rho, ts, ee), "phase": EosTable(rho, ti, phase)}
 
 
+def make_tmm_tables(nbb: int = 64):
+    """Synthetic stand-ins for the two data files do_tmm reads (imd_tmm.c:117-118; missing blobs upstream):
+    eps_bb [nbb,3] = lambda (micrometres, ascending), Re, Im of the interband permittivity -- a Lorentzian
+    bump around 0.8 um like aluminium's parallel-band absorption; K12 [1500,2] = the collision integrals
+    K1, K2 at nu = (i+1)/30, smooth curves that join the asymptotes coded in tmm_K1/tmm_K2 (:667-696)."""
+    lam = np.linspace(0.2, 2.0, nbb)
+    w, w0, g = 1.0 / lam, 1.0 / 0.8, 0.25
+    lor = 3.0 / (w0 * w0 - w * w - 1j * g * w)
+    eps_bb = np.stack([lam, lor.real, lor.imag], axis=1)
+    nu = (np.arange(1500) + 1.0) / 30.0
+    k1 = 1.0 / (1.0 + 8.0 * nu * nu / 315.0)
+    k2 = 1.0 / (1.0 + nu * nu / 6.0)
+    return {"eps_bb": eps_bb, "K12": np.stack([k1, k2], axis=1)}
+
+
+def write_tmm_files(tabs, outdir: str) -> None:
+    """alu_eps_bb.dat (3 columns) and K12.dat (2 columns), one row per line (tmm_read_arr counts newlines)."""
+    for fn, key in (("alu_eps_bb.dat", "eps_bb"), ("K12.dat", "K12")):
+        with open(os.path.join(outdir, fn), "w") as f:
+            for row in tabs[key]:
+                f.write(" ".join("%.17g" % v for v in row) + "\n")
+
+
 def write_eos_files(tabs: Dict[str, EosTable], outdir: str) -> None:
     """The file names init_ttm opens relative to the run directory's parent (imd_ttm.c:1130-1132)."""
     tabs["cve"].write(os.path.join(outdir, "EOS_cve_from_r_te.txt"))
@@ -454,11 +477,13 @@ class TtmParams:
     src_mu: float = 1.0 / 80.0              # 1/Angstrom, analytic Beer-Lambert source
     src_abs: float = 0.1
     Temin: float = 1e-3                     # globals.h:1196
+    tmm_threshold: float = 10.0             # tmm_absorption_threshold: exp(-x) of the field is "absorbed"
+    use_tmm: int = 0                        # 1: the reference's transfer-matrix source (do_tmm), 0: analytic
 
     def param_text(self) -> str:
         return ("fd_ext 1 1 1\nfd_n_timesteps %d\nttm_int 100000000\nfd_min_atoms %d\nttmdimx %d\n"
                 "vlatdim %d\nvlatbuffer %d\natomic_weight %.17g\natomic_charge %.17g\nI0 %.17g\n"
-                "lambda %.17g\nlaser_t_0 %.17g\nlaser_sigma_t %.17g\ntmm_threshold 10.0\n"
+                "lambda %.17g\nlaser_t_0 %.17g\nlaser_sigma_t %.17g\ntmm_threshold %.17g\n"
                 % (self.fd_n_timesteps, self.fd_min_atoms, self.ttmdimx, self.vlatdim, self.vlatbuffer,
                    self.atomic_weight, self.atomic_charge, self.I0, self.lam, self.laser_t_0,
-                   self.laser_sigma_t))
+                   self.laser_sigma_t, self.tmm_threshold))

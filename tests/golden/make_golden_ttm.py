@@ -27,6 +27,7 @@ from imd_b200 import synth  # noqa: E402
 
 REF_BIN = os.path.join(ROOT, "oracle", "_ref", "imd_ref_mpi_eam_ttm")
 REF_BIN_NRB = os.path.join(ROOT, "oracle", "_ref", "imd_ref_mpi_eam_ttm_nrb")   # + -DNRB -DREFPOS, imd_nrb.c
+REF_BIN_TMM = os.path.join(ROOT, "oracle", "_ref", "imd_ref_mpi_eam_ttm_tmm")   # do_tmm / tmm_init NOT replaced
 NN_PROBE = os.path.join(ROOT, "oracle", "_ref", "nn_probe")
 
 CASES = {
@@ -45,6 +46,13 @@ CASES = {
     "ttm_nrb_al_40x5x5_p2": ((40, 5, 5), 2, synth.TtmParams(ttmdimx=10, fd_n_timesteps=20, I0=2.0e16), 24,
                               (0, 1, 2, 3, 12, 24), 20.0, 20.0, 0.05,
                               "nrb_alat 4.05\nnrb_eps 0.3\nnrb_k 1.2\n"),
+    # the reference's own transfer-matrix source (imd_tmm.c) on synthetic alu_eps_bb.dat / K12.dat
+    "ttm_tmm_al_96x5x5_p2": ((96, 5, 5), 2, synth.TtmParams(ttmdimx=26, fd_n_timesteps=20, I0=2.0e16, tmm_threshold=5.0,
+                                                           use_tmm=1), 14,
+                              (0, 1, 2, 3, 7, 14), 20.0, 20.0, 0.0258, ""),
+    "ttm_tmm_al_96x5x5_p4": ((96, 5, 5), 4, synth.TtmParams(ttmdimx=28, fd_n_timesteps=25, I0=6.0e16, tmm_threshold=6.0,
+                                                           use_tmm=1, laser_t_0=20e-15), 12,
+                              (0, 2, 4, 8, 12), 20.0, 20.0, 0.05, ""),
     "ttm_nrb_al_56x5x6_p4": ((56, 5, 6), 4, synth.TtmParams(ttmdimx=16, fd_n_timesteps=20, I0=3.0e16), 20,
                               (0, 2, 3, 10, 20), 20.0, 20.0, 0.08,
                               "nrb_alat 4.05\nnrb_eps 0.3\nnrb_k 0.9\n"),
@@ -140,6 +148,8 @@ def run_case(name, box_param, nranks, tp, steps, dump_steps, sfront, srear, star
         synth.make_eam_tables(spec, work)
         eos = synth.make_eos_tables()
         synth.write_eos_files(eos, work)
+        if tp.use_tmm:
+            synth.write_tmm_files(synth.make_tmm_tables(), work)
         rng = np.random.default_rng(7)
         arrays = {}
         for key, fn in (("cve", "EOS_cve_from_r_te.txt"), ("ee", "EOS_ee_from_r_tesqrt.txt")):
@@ -157,7 +167,7 @@ def run_case(name, box_param, nranks, tp, steps, dump_steps, sfront, srear, star
         env = dict(os.environ, SHMPI_NP=str(nranks), IMD_DUMP_DIR="dump",
                    IMD_DUMP_STEPS=",".join(str(s) for s in dump_steps),
                    IMD_SRC_MU="%.17g" % tp.src_mu, IMD_SRC_ABS="%.17g" % tp.src_abs)
-        res = subprocess.run([REF_BIN_NRB if "nrb_alat" in extra else REF_BIN, "-p", "run.param"], cwd=run, env=env, stdout=subprocess.PIPE,
+        res = subprocess.run([REF_BIN_TMM if tp.use_tmm else REF_BIN_NRB if "nrb_alat" in extra else REF_BIN, "-p", "run.param"], cwd=run, env=env, stdout=subprocess.PIPE,
                              stderr=subprocess.STDOUT, text=True, timeout=600)
         if res.returncode != 0:
             print(res.stdout[-3000:])
