@@ -186,6 +186,11 @@ class OrcEos(C.Structure):
                 ("diag", C.POINTER(C.c_ubyte))]
 
 
+class OrcTmmParams(C.Structure):
+    _fields_ = [("tmm_threshold", C.c_double), ("laser_t_1", C.c_double), ("laser_sigma_t1", C.c_double),
+                ("nbb", C.c_int), ("nk", C.c_int), ("eps_bb", c_dp), ("K12", c_dp), ("phase", OrcEos)]
+
+
 class OrcTtmParams(C.Structure):
     _fields_ = [("G", C.c_int), ("P", C.c_int), ("fd_n_timesteps", C.c_int), ("fd_min_atoms", C.c_int),
                 ("vlatdim", C.c_int), ("vlatbuffer", C.c_int),
@@ -270,6 +275,17 @@ class TtmOracle:
         self.t = self.L.orc_ttm_create(C.byref(self.par), C.byref(self.cve.c), C.byref(self.ee.c))
         if not self.t:
             raise RuntimeError("orc_ttm_create failed (ttmdimx % nranks != 0?)")
+        if getattr(tp, "use_tmm", 0):
+            # the reference's own transfer-matrix source (do_tmm) on the synthetic data files
+            from imd_b200 import synth
+            tabs = synth.make_tmm_tables()
+            self.phase = Eos(eos["phase"])
+            self._bb = np.ascontiguousarray(tabs["eps_bb"], np.float64)
+            self._k12 = np.ascontiguousarray(tabs["K12"], np.float64)
+            self.tmm = OrcTmmParams(tp.tmm_threshold, 0.0, 0.0, self._bb.shape[0], self._k12.shape[0],
+                                    _dp(self._bb), _dp(self._k12), self.phase.c)
+            self.L.orc_ttm_set_tmm.argtypes = [C.c_void_p, C.POINTER(OrcTmmParams)]
+            self.L.orc_ttm_set_tmm(self.t, C.byref(self.tmm))
 
     def close(self):
         if getattr(self, "t", None):

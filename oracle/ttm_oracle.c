@@ -2,6 +2,7 @@
  * TTM (imd_ttm.c) and move_atoms_ttm; see ttm_oracle.h for scope and parity status. */
 #include "ttm_oracle.h"
 
+#include <complex.h>
 #include <math.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -226,6 +227,10 @@ struct orc_ttm {
   double max_dt_ttm, tmm_time, Eabs, tot_elec_energy;
   int    diff_substeps, laser_active, steps;
   int    last_active_cell_global, cur_vlattice_proc;
+  int    use_tmm;                    /* orc_ttm_set_tmm called */
+  orc_tmm_params tmm;
+  double *tmm_Qabs;                  /* [G], persists between calls like the reference's global array */
+  double tmm_refl, tmm_trans;
   char   err[512];
 };
 
@@ -269,9 +274,18 @@ orc_ttm *orc_ttm_create(const orc_ttm_params *p, const orc_eos *cve, const orc_e
   return t;
 }
 
+void orc_ttm_set_tmm(orc_ttm *t, const orc_tmm_params *q)
+{
+  t->use_tmm = 1;
+  t->tmm = *q;
+  free(t->tmm_Qabs);
+  t->tmm_Qabs = calloc(t->G, sizeof(double));
+}
+
 void orc_ttm_destroy(orc_ttm *t)
 {
   if (!t) return;
+  free(t->tmm_Qabs);
   free(t->l1); free(t->l2); free(t->v1); free(t->v2); free(t->xiarr_local); free(t->xiarr_global);
   free(t->vcomx); free(t->vcomy); free(t->vcomz); free(t->mdtemp);
   free(t->natomsglobal); free(t->totneighs); free(t->fluxl); free(t->fluxr);
@@ -522,6 +536,192 @@ static void cfl_maxdt(orc_ttm *t)
   t->max_dt_ttm *= 0.9;
 }
 
+
+/* ------------------------------------------------------------------ transfer-matrix source (imd_tmm.c) */
+/* tmm_K1 / tmm_K2 (imd_tmm.c:667-696); note (int) nu * 30 - 1: the cast binds to nu alone */
+static double tmm_K(const orc_ttm *t, double nu, int which)
+{
+  const double *K12 = t->tmm.K12;
+  if (nu < 1.0 / 30.0) return 1;
+  if (nu < 50) {
+    int i = (int) nu * 30 - 1;
+    if (i < 0) i = 0;
+    if (i > 1498) i = 1498;
+    return K12[2 * i + which] + (30 * nu - i - 1) * (K12[2 * (i + 1) + which] - K12[2 * i + which]);
+  }
+  if (which == 0) return 315.0 / 8.0 / (nu * nu) - 675675.0 / 64.0 / (nu * nu * nu * nu);
+  return 6.0 / (nu * nu) - 720.0 / (nu * nu * nu * nu);
+}
+
+/* nupl as called from tmm_get_epsilon: the file-level nupl/coulomb_log of imd_ttm.c with the global laser_active */
+static double nupl_(double omega_las, double Z, double ni, double ne, double Te, int la)
+{
+  return nupl(omega_las, Z, ni, ne, Te, la);
+}
+
+/* tmm_get_epsilon (imd_tmm.c:503-570) */
+static void tmm_get_epsilon(const orc_ttm *t, double lambda, double Te, double Ti, double Z, double Ne,
+                            double *re, double *img)
+{
+  Te *= 11604.52500617; Ti *= 11604.52500617;
+  const double complex un = 1, im = I;
+  const double LIGHTSPEED = 2.998e8;                       /* globals.h:325 */
+  double omega_las = (2.0 * M_PI * LIGHTSPEED / lambda);
+  double Ncr = ECONST * EMASS * omega_las * omega_las / ECHARGE / ECHARGE;    /* ne_cr, imd_ttm.c:2219 */
+  double Ni = Ne / Z;
+  double EF = fermi_E(Ne);
+  double TF = 2.0 * EF / (3.0 * BOLTZMAN);
+  double VF = sqrt(2 * EF / EMASS);
+  const double A1p = 4.41, A2p = 0.8, A3p = 0.7, A4p = 0.2;
+  const double *bb = t->tmm.eps_bb;
+  int il = 0, ir = 0, id;
+  for (id = 0; lambda * 1e6 > bb[3 * id]; id++) { il = id; ir = id + 1; }
+  double nu_met = numet(A1p, A2p, Te, Ti, TF);
+  double nu_max = numax(A3p, VF, Te, Ni);
+  double nu_pl = nupl_(omega_las, Z, Ni, Ne, Te, t->laser_active);
+  double ksi = 0.75 * sqrt(M_PI) * nu_pl / omega_las;
+  double complex ebl = bb[3 * il + 1] + I * bb[3 * il + 2], ebr = bb[3 * ir + 1] + I * bb[3 * ir + 2];
+  double complex epsilon_bb = ebl + (ebr - ebl) / (bb[3 * ir] - bb[3 * il]) * (lambda * 1e6 - bb[3 * il]);
+  int phase = ((int) orc_eos_interp(&t->tmm.phase, Ni * 26.9815 * AMU, Ti));
+  if (fabs(phase) == 3 || fabs(phase) == 4 || fabs(phase) == 5) epsilon_bb = 0 * I * 0;
+  double complex epsilon_met = epsilon_bb + un - Ne / Ncr / (un + im * DMIN(nu_met, nu_max) / omega_las);
+  double complex epsilon_pl = un - Ne / Ncr * (tmm_K(t, ksi, 0) - im * nu_pl / omega_las * tmm_K(t, ksi, 1));
+  double complex epsilon_wr = epsilon_pl + (epsilon_met - epsilon_pl) * exp(-A4p * Te / TF);
+  *re = creal(epsilon_wr);
+  *img = cimag(epsilon_wr);
+}
+
+/* EE (imd_tmm.c:72-98) */
+static double tmm_EE(double z, double delta, double complex kl, double complex Bplus, double complex Bminus)
+{
+  double complex im = 0 + I * 1;
+  double phi1 = creal(delta * z * kl * im);
+  double phi2 = cimag(delta * z * kl * im);
+  double complex eiphi = exp(phi1) * cos(phi2) + I * exp(phi1) * sin(phi2);
+  double complex Ez = (Bplus * eiphi + Bminus / eiphi);
+  return creal(Ez) * creal(Ez) + cimag(Ez) * cimag(Ez) + 0 * 0 + 0 * 0;
+}
+
+/* Runge5 (imd_tmm.c:37-69): adaptive Simpson-like quadrature of EE over z in [0,1] */
+static double tmm_runge5(double delta, double complex kl, double complex Bplus, double complex Bminus)
+{
+  double dx = 1, cur_xpos = 0, result = 0;
+  const double errval = 1e-5;
+  double k1, k3, k4, k5;
+  while (cur_xpos < 1 && dx > 1e-5) {
+    k1 = dx / 3.0 * tmm_EE(cur_xpos, delta, kl, Bplus, Bminus);
+    k3 = dx / 3.0 * tmm_EE(cur_xpos + dx / 3.0, delta, kl, Bplus, Bminus);
+    k4 = dx / 3.0 * tmm_EE(cur_xpos + 0.5 * dx, delta, kl, Bplus, Bminus);
+    k5 = dx / 3.0 * tmm_EE(cur_xpos + dx, delta, kl, Bplus, Bminus);
+    double ERR = k1 - 4.5 * k3 + 4 * k4 - 0.5 * k5;
+    if (ERR < 5.0 / 32 * errval) { result += 0.5 * (k1 + 4 * k4 + k5); cur_xpos += dx; dx *= 1.1; }
+    else if (ERR > 5 * errval) { dx *= 0.5; continue; }
+    else { result += 0.5 * (k1 + 4 * k4 + k5); cur_xpos += dx; }
+    if (cur_xpos + dx > 1) dx = 1 - cur_xpos;
+  }
+  return result;
+}
+
+static void tmm_matmul(const double complex *a, const double complex *b, double complex *p)
+{
+  p[0] = a[0] * b[0] + a[2] * b[1];
+  p[1] = a[1] * b[0] + a[3] * b[1];
+  p[2] = a[0] * b[2] + a[2] * b[3];
+  p[3] = a[1] * b[2] + a[3] * b[3];
+}
+
+
+/* do_tmm (imd_tmm.c:193-445).  The P ranks of the reference fill disjoint parts of the permittivity
+ * arrays, rank 0 reduces them and solves, MPI_Scatter hands every rank its part of tmm_Qabs: here the
+ * arrays are global from the start.  Kept as in the reference: nothing happens for steps < 2; when the
+ * field is below the threshold the function returns WITHOUT touching the sources (they keep their last
+ * values); only tmm_Qabs[0..ecut) is rewritten, entries beyond keep what an earlier call left. */
+static int do_tmm_ref(orc_ttm *t)
+{
+  const double Imp = 3.769911184307751e+02;
+  const int G = t->G, L = t->L;
+  double I_t = t->p.I0 * exp(-pow(t->tmm_time - t->p.laser_t_0, 2) / t->laser_sigma_t_squared);
+  I_t += t->p.I0 * exp(-pow(t->tmm_time - t->tmm.laser_t_1, 2) / (t->tmm.laser_sigma_t1 * t->tmm.laser_sigma_t1));
+  if (t->steps < 2) return 0;
+  if (sqrt(2.0 * I_t * Imp) < t->p.tmm_laser_threshold * sqrt(2 * t->p.I0 * Imp)) { t->laser_active = 0; return 0; }
+  t->laser_active = 1;
+
+  double *eps_re = calloc(G, sizeof(double)), *eps_im = calloc(G, sizeof(double));
+  int *active = calloc(G, sizeof(int));
+  double complex *km = calloc(G, sizeof(double complex));
+  for (int r = 0; r < t->P; r++) for (int i = 1; i <= L; i++) {
+    const tcell *c = &CELL(t->l1, r, i);
+    const int ig = iglobal_of(t, r, i);
+    if (c->natoms < t->p.fd_min_atoms || c->dens < RHOMIN) continue;
+    tmm_get_epsilon(t, t->p.lambda, c->temp, c->md_temp, c->Z, c->ne, &eps_re[ig], &eps_im[ig]);
+    active[ig] = 1;
+  }
+  double k0 = 2.0 * M_PI / t->p.lambda;
+  k0 /= 1e10;
+  double complex Cinv[4], Pmat[4], tmpmat[4], tmpmat2[4], Emat[4];
+  double complex kl, kr, eiphi, BR = 0.0 + I * 0, BT = 0.0 + I * 0, B0 = 1.0 + I * 0;
+  double phi1, phi2, dx;
+  int ecut = 0;
+  const double ecut_thresh = exp(-t->tmm.tmm_threshold);
+  km[0] = k0;
+  for (int i = 1; i < G - 1; i++)
+    km[i] = active[i] == 0 ? k0 : k0 * csqrt(eps_re[i] + I * eps_im[i]);
+  Emat[0] = 1.0 + I * 0; Emat[1] = 0; Emat[2] = 0; Emat[3] = 1.0 + I * 0.0;
+  int tooshort = 1;
+  for (int i = 0; i < G - 1; i++) {
+    dx = i == 0 ? 1e10 : t->fd_hx;
+    kl = km[i]; kr = km[i + 1];
+    phi1 = creal(dx * kl * I); phi2 = cimag(dx * kl * I);
+    eiphi = exp(phi1) * cos(phi2) + I * exp(phi1) * sin(phi2);
+    Pmat[0] = eiphi; Pmat[2] = 1.0 / eiphi; Pmat[1] = eiphi; Pmat[3] = -Pmat[2];
+    Cinv[0] = 0.5; Cinv[2] = 0.5 * kl / kr; Cinv[1] = 0.5; Cinv[3] = -Cinv[2];
+    tmm_matmul(Cinv, Pmat, tmpmat);
+    tmm_matmul(tmpmat, Emat, tmpmat2);
+    for (int j = 0; j < 4; j++) Emat[j] = tmpmat2[j];
+    BR = -Emat[1] * B0 / Emat[3];
+    BT = Emat[0] * B0 + Emat[2] * BR;
+    if (creal(BT) * creal(BT) + cimag(BT) * cimag(BT) < ecut_thresh) { tooshort = 0; ecut = i + 1; break; }
+  }
+  if (tooshort) {
+    snprintf(t->err, sizeof t->err, "Sample is too short for TMM.Consider reducing tmm_threshold.");
+    free(eps_re); free(eps_im); free(active); free(km);
+    return -1;
+  }
+  {
+    double complex tmpr0 = BR / B0;
+    t->tmm_refl = creal(tmpr0) * creal(tmpr0) + cimag(tmpr0) * cimag(tmpr0);
+    t->tmm_trans = creal(BT) * creal(BT) + cimag(BT) * cimag(BT);
+  }
+  double complex *Bplus = calloc(ecut + 1, sizeof(double complex)), *Bminus = calloc(ecut + 1, sizeof(double complex));
+  double complex Fvec[2], tmpvec[2];
+  Fvec[0] = B0; Fvec[1] = BR; Bplus[0] = B0; Bminus[0] = BR;
+  for (int i = 0; i < ecut; i++) {
+    dx = i == 0 ? 1e10 : t->fd_hx;
+    kl = km[i]; kr = km[i + 1];
+    phi1 = creal(dx * kl * I); phi2 = cimag(dx * kl * I);
+    eiphi = exp(phi1) * cos(phi2) + I * exp(phi1) * sin(phi2);
+    Pmat[0] = eiphi; Pmat[2] = 1.0 / eiphi; Pmat[1] = eiphi; Pmat[3] = -Pmat[2];
+    Cinv[0] = 0.5; Cinv[2] = 0.5 * kl / kr; Cinv[1] = 0.5; Cinv[3] = -Cinv[2];
+    tmm_matmul(Cinv, Pmat, tmpmat);
+    tmpvec[0] = tmpmat[0] * Fvec[0] + tmpmat[2] * Fvec[1];       /* matmul on a 2-vector: first column only */
+    tmpvec[1] = tmpmat[1] * Fvec[0] + tmpmat[3] * Fvec[1];
+    Fvec[0] = tmpvec[0]; Fvec[1] = tmpvec[1];
+    Bplus[i + 1] = Fvec[0]; Bminus[i + 1] = Fvec[1];
+  }
+  for (int i = 0; i < ecut; i++) {
+    dx = i == 0 ? 1e10 : t->fd_hx;
+    kl = km[i];
+    t->tmm_Qabs[i] = I_t * k0 * eps_im[i] * tmm_runge5(dx, kl, Bplus[i], Bminus[i]);
+    t->tmm_Qabs[i] *= 1e10;
+    t->tmm_Qabs[i] *= 6.3538562638e-26;
+  }
+  free(Bplus); free(Bminus);
+  for (int r = 0; r < t->P; r++) for (int i = 1; i <= L; i++)
+    CELL(t->l1, r, i).source = CELL(t->l2, r, i).source = t->tmm_Qabs[iglobal_of(t, r, i)];
+  free(eps_re); free(eps_im); free(active); free(km);
+  return 0;
+}
+
 /* the analytic source that replaces do_tmm on both sides (oracle/ref_hooks_ttm.c) */
 static void do_source(orc_ttm *t)
 {
@@ -615,7 +815,7 @@ int orc_ttm_step(orc_ttm *t, int steps, long n, const double *pos, const double 
   { int q = (int) (t->p.timestep / t->max_dt_ttm); t->diff_substeps = t->p.fd_n_timesteps > q ? t->p.fd_n_timesteps : q; }
   const double tau = t->p.timestep / ((double) t->diff_substeps);
   for (int s = 0; s < t->diff_substeps; s++) {
-    do_source(t);
+    if (t->use_tmm) { if (do_tmm_ref(t)) return -1; } else do_source(t);
     t->tmm_time += tau * 10.18 * 1.0e-15;
     if (do_diff(t, tau)) return -1;
     if (do_fillmesh(t)) return -1;

@@ -43,6 +43,19 @@ typedef struct {
 
 typedef struct orc_ttm orc_ttm;
 
+/* The reference's own laser source: transfer-matrix solution of the Helmholtz equation over the FD
+ * cells with a wide-range permittivity (do_tmm, tmm_get_epsilon, Runge5, EE, tmm_K1/K2; imd_tmm.c:37-98,
+ * 193-445, 503-570, 667-696).  eps_bb[nbb][3] = rows of alu_eps_bb.dat, K12[nk][2] = rows of K12.dat,
+ * phase = EOS_phase_from_r_ti table.  Without this call the analytic source of ref_hooks_ttm.c is used. */
+typedef struct {
+  double tmm_threshold;             /* tmm_absorption_threshold */
+  double laser_t_1, laser_sigma_t1; /* second pulse (globals.h:491-495), 0 0 = none */
+  int    nbb, nk;
+  const double *eps_bb, *K12;
+  orc_eos phase;
+} orc_tmm_params;
+void orc_ttm_set_tmm(orc_ttm *t, const orc_tmm_params *q);
+
 orc_ttm *orc_ttm_create(const orc_ttm_params *p, const orc_eos *cve, const orc_eos *ee);
 void     orc_ttm_destroy(orc_ttm *t);
 
