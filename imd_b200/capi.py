@@ -81,6 +81,7 @@ def load():
         "imdcu_comm_rank": (C.c_int, [vp, c_ip, c_ip, c_ip, c_ip]),
         "imdcu_ttm_set_eos": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, c_dp, c_dp, c_dp, C.POINTER(C.c_ubyte)]),
         "imdcu_ttm_init": (C.c_int, [vp, C.POINTER(TtmParamsC)]),
+        "imdcu_ttm_set_tmm": (C.c_int, [vp, C.c_double, C.c_double, C.c_double, C.c_int, c_dp, C.c_int, c_dp]),
         "imdcu_calc_ttm": (C.c_int, [vp, C.c_int, c_dp]),
         "imdcu_move_atoms_ttm": (C.c_int, [vp, c_dp, c_ip]),
         "imdcu_run_ttm": (C.c_int, [vp, C.c_int, C.c_int, c_dp]),
@@ -261,6 +262,12 @@ class Context:
         d = None if tab.diag is None else np.ascontiguousarray(tab.diag, np.uint8)
         dp = None if d is None else d.ctypes.data_as(C.POINTER(C.c_ubyte))
         self._ck(self.L.imdcu_ttm_set_eos(self.h, which, x.size, y.size, _dp(x), _dp(y), _dp(z), dp))
+
+    def ttm_set_tmm(self, tmm_threshold, eps_bb, K12, laser_t_1=0.0, laser_sigma_t1=0.0):
+        """The reference's transfer-matrix source (do_tmm): eps_bb [nbb,3], K12 [>=1500,2] as tmm_init reads them."""
+        bb = np.ascontiguousarray(eps_bb, np.float64); k12 = np.ascontiguousarray(K12, np.float64)
+        self._ck(self.L.imdcu_ttm_set_tmm(self.h, float(tmm_threshold), float(laser_t_1), float(laser_sigma_t1),
+                                          bb.shape[0], _dp(bb), k12.shape[0], _dp(k12)))
 
     def ttm_init(self, tp, nranks_ref=1):
         """tp: imd_b200.synth.TtmParams."""

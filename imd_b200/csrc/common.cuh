@@ -146,10 +146,15 @@ struct TtmState {
   int    G = 0, P = 1, L = 0, LD = 0;
   double fd_hx = 0, fd_vol = 0, neighvol = 0, omega_laser = 0, sigma_t_sq = 0;
   // EOS tables (device)
-  DevBuf<double> eos_buf[2];
-  DevBuf<unsigned char> eos_diag[2];
-  int    eos_nx[2] = {0, 0}, eos_ny[2] = {0, 0};
-  bool   eos_set[2] = {false, false};
+  DevBuf<double> eos_buf[3];
+  DevBuf<unsigned char> eos_diag[3];
+  int    eos_nx[3] = {0, 0, 0}, eos_ny[3] = {0, 0, 0};
+  bool   eos_set[3] = {false, false, false};
+  // do_tmm (imdcu_ttm_set_tmm): data tables, scratch and the persistent tmm_Qabs
+  bool   use_tmm = false;
+  double tmm_threshold = 0, laser_t_1 = 0, laser_sigma_t1 = 0;
+  int    tmm_nbb = 0, tmm_nk = 0;
+  DevBuf<double> tmm_tab, tmm_buf;
   // lattices: lat[0], lat[1] = [P*LD] TCell each; vlat[0], vlat[1] = [vlatdim]
   DevBuf<TCell> lat, vlat;
   // slab sums: ints {natoms, totneighs, fluxl, fluxr}[G], doubles {px,py,pz,mdtemp}[G]

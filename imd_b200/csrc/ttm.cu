@@ -166,6 +166,8 @@ __device__ double eos_te_from_r_ee(const EosView &ee, double r, double e)
   return fminbnd_ref(ee, a, b, r, e);
 }
 
+#include "tmm.cuh"
+
 // ----------------------------------------------------------------------------- device state
 struct TtmScal {                     // persists between MD steps (device), mirrored to the host on demand
   int    cur, vcur;                  // which lattice is l1 / which virtual lattice is vlattice1
@@ -184,7 +186,14 @@ struct TtmArgs {
   int *isum; double *dsum;           // slab sums, see k_ttm_atoms1
   double *xiarr, *xiloc, *vcom, *src_e, *winv;   // winv: [ncell_tot][WINV_N], see fill_inv
   TtmScal *scal;
+  // do_tmm (tmm.cuh)
+  int use_tmm, pad2_;
+  double tmm_threshold, laser_t_1, sigma_t1_sq;
+  TmmTables tmm;
+  EosView phase;                     // global memory
+  double *tmm_buf;                   // [TMM_BUF_PER_CELL][G+2]: eps_re, eps_im, active, km(2), M(8), Bplus(2), Bminus(2), Qabs
 };
+#define TMM_BUF_PER_CELL 18
 
 // ----------------------------------------------------------------------------- atom kernels
 // slab index of an atom (imd_ttm.c:277-279)
@@ -528,7 +537,7 @@ k_ttm_grid(TtmArgs a)
   extern __shared__ double s_dyn[];
   __shared__ double s_red[32];
   __shared__ int s_ired[32];
-  __shared__ int s_last_active, s_rv, s_substeps;
+  __shared__ int s_last_active, s_rv, s_substeps, s_ecut;
   __shared__ double s_maxdt;
   const int G = a.G, P = a.P, L = a.L, LD = a.LD, ncell = P * L, mn = a.p.fd_min_atoms;
   const int nl = P * LD;
@@ -713,19 +722,118 @@ k_ttm_grid(TtmArgs a)
   double Ci = 8.589449886e+02;
   Ci *= a.p.vlatdens; Ci *= 11604.5; Ci *= 1e-30; Ci *= C_J2eV;
   const double tau_ci = tau / Ci;
+  // do_tmm scratch (global memory, L1/L2 resident): see TtmArgs::tmm_buf
+  const int GG = a.G + 2;
+  double *q_re = a.tmm_buf, *q_im = q_re + GG, *q_act = q_im + GG, *q_km = q_act + GG, *q_M = q_km + 2 * GG,
+         *q_Bp = q_M + 8 * GG, *q_Bm = q_Bp + 2 * GG, *q_Q = q_Bm + 2 * GG;
   for (int s = 0; s < diff_substeps; s++) {
-    // analytic source (replaces do_tmm): I_t and the laser_active switch of imd_tmm.c:197-208
-    const double dtl = tmm_time - a.p.laser_t_0;
-    const double I_t = a.p.I0 * pexp(pdiv(-(dtl * dtl), a.sigma_t_sq));
-    la = !(sqrt(2.0 * I_t * Imp) < la_threshold);
+    double I_t;
+    if (!a.use_tmm) {
+      // analytic source (stands in for do_tmm where its data files are missing): I_t and the laser_active
+      // switch of imd_tmm.c:197-208
+      const double dtl = tmm_time - a.p.laser_t_0;
+      I_t = a.p.I0 * pexp(pdiv(-(dtl * dtl), a.sigma_t_sq));
+      la = !(sqrt(2.0 * I_t * Imp) < la_threshold);
+    } else {
+      // do_tmm (imd_tmm.c:193-445).  Nothing happens for steps < 2; below the field threshold the sources keep
+      // their last values; only tmm_Qabs[0, ecut) is rewritten.
+      const double d0 = tmm_time - a.p.laser_t_0, d1 = tmm_time - a.laser_t_1;
+      I_t = a.p.I0 * exp(-(d0 * d0) / a.sigma_t_sq);
+      I_t += a.p.I0 * exp(-(d1 * d1) / a.sigma_t1_sq);
+      if (a.steps >= 2) {
+        if (sqrt(2.0 * I_t * Imp) < la_threshold) la = 0;
+        else {
+          la = 1;
+          const int G = a.G;
+          double k0 = 2.0 * TMC_PI / a.p.lambda;
+          k0 /= 1e10;
+          // permittivity of the active cells (every rank its own cells, then MPI_Reduce, :209-252)
+          for (int c = threadIdx.x; c < ncell; c += blockDim.x) {
+            const TCell &x = l1[(c / L) * LD + c % L + 1];
+            if (x.natoms < mn || x.dens < RHOMIN) { q_re[c] = 0.0; q_im[c] = 0.0; q_act[c] = 0.0; continue; }
+            const double Ni = x.ne / x.Z;
+            double pr = Ni * 26.9815 * C_AMU, pt = x.md_temp * 11604.52500617;      // EOS_phase_from_r_ti clamps (DEBUG_LEVEL > 0)
+            pr = DMAX(DMIN(pr, a.phase.x[a.phase.nx - 1]), a.phase.x[0]);
+            pt = DMAX(DMIN(pt, a.phase.y[a.phase.ny - 1]), a.phase.y[0]);
+            const int phase = (int) eos_interp(a.phase, pr, pt);
+            const cplx e = tmm_get_epsilon(a.tmm, a.p.lambda, x.temp, x.md_temp, x.Z, x.ne, phase);
+            q_re[c] = e.re; q_im[c] = e.im; q_act[c] = 1.0;
+          }
+          __syncthreads();
+          for (int c = threadIdx.x; c < G; c += blockDim.x) {                      // km (:278-287); km[G-1] stays 0
+            cplx k = cmk(k0, 0.0);
+            if (c == G - 1) k = cmk(0.0, 0.0);
+            else if (c > 0 && q_act[c] != 0.0) k = cscale(k0, csqrtc(cmk(q_re[c], q_im[c])));
+            q_km[2 * c] = k.re; q_km[2 * c + 1] = k.im;
+          }
+          __syncthreads();
+          // Cinv * Pmat of every interface, in parallel: the transcendental part of loops 2 and 3
+          for (int i = threadIdx.x; i < G - 1; i += blockDim.x) {
+            cplx M[4];
+            tmm_interface(i == 0 ? 1e10 : a.fd_hx, cmk(q_km[2 * i], q_km[2 * i + 1]), cmk(q_km[2 * i + 2], q_km[2 * i + 3]), M);
+#pragma unroll
+            for (int j = 0; j < 4; j++) { q_M[8 * i + 2 * j] = M[j].re; q_M[8 * i + 2 * j + 1] = M[j].im; }
+          }
+          __syncthreads();
+          if (threadIdx.x == 0) {
+            // loop 2 (:292-334): E = (Cinv P) E until the transmitted field is below exp(-tmm_threshold)
+            const double ecut_thresh = exp(-a.tmm_threshold);
+            cplx E0 = cmk(1.0, 0.0), E1 = cmk(0.0, 0.0), E2 = cmk(0.0, 0.0), E3 = cmk(1.0, 0.0), BR = cmk(0.0, 0.0);
+            int ecut = -1;
+            for (int i = 0; i < G - 1; i++) {
+              const double *m = q_M + 8 * i;
+              const cplx M0 = cmk(m[0], m[1]), M1 = cmk(m[2], m[3]), M2 = cmk(m[4], m[5]), M3 = cmk(m[6], m[7]);
+              const cplx n0 = cadd(cmul(M0, E0), cmul(M2, E1)), n1 = cadd(cmul(M1, E0), cmul(M3, E1));
+              const cplx n2 = cadd(cmul(M0, E2), cmul(M2, E3)), n3 = cadd(cmul(M1, E2), cmul(M3, E3));
+              E0 = n0; E1 = n1; E2 = n2; E3 = n3;
+              BR = cdivc(cneg(E1), E3);                                             // -Emat[1]*B0/Emat[3], B0 = 1
+              const cplx BT = cadd(E0, cmul(E2, BR));
+              if (cabs2(BT) < ecut_thresh) { ecut = i + 1; break; }
+            }
+            if (ecut < 0) { atomicMax(err, 6); ecut = 0; }
+            // loop 3 (:353-385): forward and backward amplitudes at the left edge of every cell up to ecut
+            cplx F0 = cmk(1.0, 0.0), F1 = BR;
+            q_Bp[0] = 1.0; q_Bp[1] = 0.0; q_Bm[0] = BR.re; q_Bm[1] = BR.im;
+            for (int i = 0; i < ecut; i++) {
+              const double *m = q_M + 8 * i;
+              const cplx M0 = cmk(m[0], m[1]), M1 = cmk(m[2], m[3]), M2 = cmk(m[4], m[5]), M3 = cmk(m[6], m[7]);
+              const cplx t0 = cadd(cmul(M0, F0), cmul(M2, F1)), t1 = cadd(cmul(M1, F0), cmul(M3, F1));
+              F0 = t0; F1 = t1;
+              q_Bp[2 * i + 2] = F0.re; q_Bp[2 * i + 3] = F0.im; q_Bm[2 * i + 2] = F1.re; q_Bm[2 * i + 3] = F1.im;
+            }
+            s_ecut = ecut;
+          }
+          __syncthreads();
+          // loop 4 (:389-408): absorbed power per cell; a cell without absorption gives I_t k0 0 (finite) = 0
+          for (int i = threadIdx.x; i < s_ecut; i += blockDim.x) {
+            double R = 0.0;
+            if (q_im[i] != 0.0)
+              R = tmm_runge5(i == 0 ? 1e10 : a.fd_hx, cmk(q_km[2 * i], q_km[2 * i + 1]), cmk(q_Bp[2 * i], q_Bp[2 * i + 1]),
+                             cmk(q_Bm[2 * i], q_Bm[2 * i + 1]));
+            double Q = I_t * k0 * q_im[i] * R;
+            Q *= 1e10;
+            Q *= 6.3538562638e-26;
+            q_Q[i] = Q;
+          }
+          __syncthreads();
+          for (int c = threadIdx.x; c < ncell; c += blockDim.x) {                  // MPI_Scatter + node.source (:414-420)
+            const int idx = (c / L) * LD + c % L + 1;
+            l1[idx].source = l2[idx].source = q_Q[c];
+          }
+        }
+      }
+    }
     tmm_time += tau * 10.18 * 1.0e-15;
     for (int c = threadIdx.x; c < ncell + a.p.vlatdim; c += blockDim.x) {
       if (c < ncell) {
         const int r = c / L, idx = r * LD + c % L + 1;
         TCell &x = l1[idx], &y = l2[idx];
         double src = 0.0;
-        if (la && a.src_e[idx] >= 0.0) { src = I_t * a.p.src_abs * a.p.src_mu * a.src_e[idx]; src *= 1e10; src *= 6.3538562638e-26; }
-        x.source = y.source = src;
+        if (a.use_tmm) src = x.source;
+        else {
+          if (la && a.src_e[idx] >= 0.0) { src = I_t * a.p.src_abs * a.p.src_mu * a.src_e[idx]; src *= 1e10; src *= 6.3538562638e-26; }
+          x.source = y.source = src;
+        }
         if (c > last_active) continue;                                   // do_DIFF (:1506-1598)
         if (la) eabs += src * a.fd_vol * tau;
         if (x.natoms < mn || x.dens < RHOMIN) continue;
@@ -805,7 +913,7 @@ static EosView eos_view(const TtmState &t, int w)
 extern "C" int imdcu_ttm_set_eos(imdcu_ctx *c, int which, int nx, int ny, const double *x, const double *y,
                                  const double *z, const unsigned char *diag)
 {
-  if (!c || which < 0 || which > 1 || nx < 2 || ny < 2 || !x || !y || !z)
+  if (!c || which < 0 || which > 2 || nx < 2 || ny < 2 || !x || !y || !z)
     return c ? c->fail(IMDCU_EINVAL, "imdcu_ttm_set_eos: bad argument") : IMDCU_EINVAL;
   for (int i = 1; i < nx; i++) if (!(x[i] > x[i - 1])) return c->fail(IMDCU_EINVAL, "imdcu_ttm_set_eos: x axis is not increasing (the table must be rectilinear)");
   for (int j = 1; j < ny; j++) if (!(y[j] > y[j - 1])) return c->fail(IMDCU_EINVAL, "imdcu_ttm_set_eos: y axis is not increasing (the table must be rectilinear)");
@@ -825,7 +933,25 @@ extern "C" int imdcu_ttm_set_eos(imdcu_ctx *c, int which, int nx, int ny, const 
   return IMDCU_OK;
 }
 
-// init_ttm (imd_ttm.c:955-1201) + tmm_init as far as the analytic source needs it
+extern "C" int imdcu_ttm_set_tmm(imdcu_ctx *c, double tmm_threshold, double laser_t_1, double laser_sigma_t1,
+                                 int nbb, const double *eps_bb, int nk, const double *K12)
+{
+  if (!c || nbb < 2 || nk < 1500 || !eps_bb || !K12)
+    return c ? c->fail(IMDCU_EINVAL, "imdcu_ttm_set_tmm: bad argument (K12 needs 1500 rows, imd_tmm.c:674)") : IMDCU_EINVAL;
+  for (int i = 1; i < nbb; i++)
+    if (!(eps_bb[3 * i] > eps_bb[3 * (i - 1)])) return c->fail(IMDCU_EINVAL, "imdcu_ttm_set_tmm: eps_bb wavelengths must ascend");
+  cudaSetDevice(c->device);
+  TtmState &t = c->ttm;
+  CU_CHECK(c, t.tmm_tab.ensure(3 * (size_t) nbb + 2 * (size_t) nk));
+  CU_CHECK(c, imdcu_h2d(c, t.tmm_tab.p, eps_bb, 3 * (size_t) nbb * sizeof(double)));
+  CU_CHECK(c, imdcu_h2d(c, t.tmm_tab.p + 3 * (size_t) nbb, K12, 2 * (size_t) nk * sizeof(double)));
+  t.tmm_nbb = nbb; t.tmm_nk = nk;
+  t.tmm_threshold = tmm_threshold; t.laser_t_1 = laser_t_1; t.laser_sigma_t1 = laser_sigma_t1;
+  t.use_tmm = true;
+  return IMDCU_OK;
+}
+
+// init_ttm (imd_ttm.c:955-1201) + tmm_init
 extern "C" int imdcu_ttm_init(imdcu_ctx *c, const imdcu_ttm_params *p)
 {
   if (!c || !p) return c ? c->fail(IMDCU_EINVAL, "imdcu_ttm_init: bad argument") : IMDCU_EINVAL;
@@ -833,6 +959,14 @@ extern "C" int imdcu_ttm_init(imdcu_ctx *c, const imdcu_ttm_params *p)
     return c->fail(IMDCU_EINVAL, "imdcu_ttm_init: set box, params and tables first");
   TtmState &t = c->ttm;
   if (!t.eos_set[0] || !t.eos_set[1]) return c->fail(IMDCU_EINVAL, "imdcu_ttm_init: EOS tables not set");
+  if (t.use_tmm && !t.eos_set[2]) return c->fail(IMDCU_EINVAL, "imdcu_ttm_init: do_tmm needs the phase table (IMDCU_EOS_PHASE)");
+  if (t.use_tmm) {
+    const double lam_um = p->lambda * 1e6;          // tmm_get_epsilon's table walk must end inside the table
+    std::vector<double> l0(1), l1(1);
+    CU_CHECK(c, cudaMemcpy(l0.data(), t.tmm_tab.p, sizeof(double), cudaMemcpyDeviceToHost));
+    CU_CHECK(c, cudaMemcpy(l1.data(), t.tmm_tab.p + 3 * (size_t) (t.tmm_nbb - 1), sizeof(double), cudaMemcpyDeviceToHost));
+    if (!(lam_um > l0[0]) || !(lam_um <= l1[0])) return c->fail(IMDCU_EINVAL, "imdcu_ttm_init: lambda outside the eps_bb table");
+  }
   if (p->ttmdimx < 1 || p->nranks_ref < 1 || p->ttmdimx % p->nranks_ref != 0)
     return c->fail(IMDCU_EINVAL, "global_fd_dim.x mod num_cpus != 0.");            // imd_ttm.c:964-967
   if (p->fd_n_timesteps < 1 || p->vlatdim < 0 || p->vlatdim > 4096)
@@ -854,6 +988,10 @@ extern "C" int imdcu_ttm_init(imdcu_ctx *c, const imdcu_ttm_params *p)
   CU_CHECK(c, t.isum.ensure(4 * (size_t) t.G)); CU_CHECK(c, t.dsum.ensure(4 * (size_t) t.G));
   CU_CHECK(c, t.xiarr.ensure(t.G)); CU_CHECK(c, t.xiloc.ensure(nl)); CU_CHECK(c, t.vcom.ensure(3 * (size_t) t.G));
   CU_CHECK(c, t.src_e.ensure(nl));
+  if (t.use_tmm) {
+    CU_CHECK(c, t.tmm_buf.ensure(TMM_BUF_PER_CELL * (size_t) (t.G + 2)));
+    CU_CHECK(c, cudaMemset(t.tmm_buf.p, 0, TMM_BUF_PER_CELL * (size_t) (t.G + 2) * sizeof(double)));
+  }
   CU_CHECK(c, t.winv.ensure(((size_t) t.P * t.L + nv) * 8));
   CU_CHECK(c, cudaMemset(t.lat.p, 0, 2 * (size_t) nl * sizeof(TCell)));
   CU_CHECK(c, cudaMemset(t.xiarr.p, 0, t.G * sizeof(double)));
@@ -886,6 +1024,7 @@ void imdcu_ttm_release(imdcu_ctx *c)
   TtmState &t = c->ttm;
   for (int w = 0; w < 2; w++) { t.eos_buf[w].release(); t.eos_diag[w].release(); }
   t.lat.release(); t.vlat.release(); t.isum.release(); t.dsum.release(); t.xiarr.release(); t.xiloc.release();
+  t.tmm_tab.release(); t.tmm_buf.release(); t.eos_buf[2].release(); t.eos_diag[2].release();
   t.vcom.release(); t.src_e.release(); t.winv.release(); t.fdi.release(); t.fdi_alt.release();
   if (t.d_scal) cudaFree(t.d_scal);
   if (t.h_scal) cudaFreeHost(t.h_scal);
@@ -905,8 +1044,9 @@ static int ttm_read_scalars(imdcu_ctx *c, double out16[16])
   out16[10] = s->tmm_time; out16[11] = s->err;
   if (s->err) {
     static const char *msg[] = {"", "ERROR during CfromT in FILLMESH", "fd_k is NaN", "fd_g is NaN",
-                                "EOS Plausibility check failed, TfromU != Tinit", "Te got NaN or Inf in diffloop"};
-    return c->fail(IMDCU_EINVAL, std::string("calc_ttm: ") + msg[s->err < 6 ? s->err : 0]);
+                                "EOS Plausibility check failed, TfromU != Tinit", "Te got NaN or Inf in diffloop",
+                                "Sample is too short for TMM.Consider reducing tmm_threshold."};
+    return c->fail(IMDCU_EINVAL, std::string("calc_ttm: ") + msg[s->err < 7 ? s->err : 0]);
   }
   return IMDCU_OK;
 }
@@ -958,6 +1098,11 @@ static int ttm_grid_part(imdcu_ctx *c, int steps, cudaStream_t st)
   a.lat = t.lat.p; a.vlat = t.vlat.p; a.isum = t.isum.p; a.dsum = t.dsum.p;
   a.xiarr = t.xiarr.p; a.xiloc = t.xiloc.p; a.vcom = t.vcom.p; a.src_e = t.src_e.p; a.winv = t.winv.p;
   a.scal = (TtmScal *) t.d_scal;
+  a.use_tmm = t.use_tmm ? 1 : 0;
+  a.tmm_threshold = t.tmm_threshold; a.laser_t_1 = t.laser_t_1; a.sigma_t1_sq = t.laser_sigma_t1 * t.laser_sigma_t1;
+  a.tmm.nbb = t.tmm_nbb; a.tmm.nk = t.tmm_nk; a.tmm.eps_bb = t.tmm_tab.p; a.tmm.K12 = t.tmm_tab.p + 3 * (size_t) t.tmm_nbb;
+  a.tmm_buf = t.tmm_buf.p;
+  if (t.use_tmm) a.phase = eos_view(t, 2); else a.phase = a.cve;
   int nt = ((a.ncell_tot + 31) / 32) * 32;
   if (nt > TTM_NT) nt = TTM_NT;
   if (nt < 32) nt = 32;

@@ -11,7 +11,7 @@ from __future__ import annotations
 
 import numpy as np
 
-from . import capi
+from . import capi, synth
 
 TAB_PAIR, TAB_RHO, TAB_EMBED = 0, 1, 2
 capi_EOS_CVE, capi_EOS_EE = 0, 1
@@ -120,9 +120,14 @@ class Imd:
         self.ctx.set_nrb(nrb_k, ids, bnd, nrbi, refpos, startup_images)
 
     # init_ttm + tmm_init (imd.c:237,245): EOS tables + TTM parameters
-    def init_ttm(self, tp, eos, nranks_ref=1):
+    def init_ttm(self, tp, eos, nranks_ref=1, tmm_tables=None):
         self.ctx.ttm_set_eos(capi_EOS_CVE, eos["cve"])
         self.ctx.ttm_set_eos(capi_EOS_EE, eos["ee"])
+        if getattr(tp, "use_tmm", 0):
+            # tmm_init (imd.c:245): the two data files of do_tmm and the phase table it looks up
+            tabs = tmm_tables if tmm_tables is not None else synth.make_tmm_tables()
+            self.ctx.ttm_set_eos(2, eos["phase"])
+            self.ctx.ttm_set_tmm(tp.tmm_threshold, tabs["eps_bb"], tabs["K12"])
         self.ctx.ttm_init(tp, nranks_ref)
 
     # calc_ttm (imd_main_3d.c:534)

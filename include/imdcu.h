@@ -166,6 +166,7 @@ typedef struct {
 
 #define IMDCU_EOS_CVE 0   /* EOS_cve_from_r_te.txt    : (rho [kg/m^3], Te [K])       -> J/(K kg) */
 #define IMDCU_EOS_EE  1   /* EOS_ee_from_r_tesqrt.txt : (rho [kg/m^3], sqrt(Te [K])) -> J/kg     */
+#define IMDCU_EOS_PHASE 2 /* EOS_phase_from_r_ti.txt  : (rho [kg/m^3], Ti [K])       -> phase id; only do_tmm reads it */
 /* One EOS interpolation table (nn_read_table, imd_interpol.c:1170-1271).  The point set must be
  * rectilinear: x[nx], y[ny], z[nx*ny] with x the outer index.  diag[(nx-1)*(ny-1)] tells which
  * diagonal the reference's Delaunay triangulation (libnn delaunay_build) put into each grid
@@ -173,6 +174,14 @@ typedef struct {
  * lpi_interpolate_point at imd_ttm.c:2517,2568. */
 int  imdcu_ttm_set_eos(imdcu_ctx *ctx, int which, int nx, int ny, const double *x, const double *y,
                        const double *z, const unsigned char *diag);
+/* The reference's own laser source instead of the analytic one: do_tmm (imd_tmm.c:193-445), the
+ * transfer-matrix solution of the Helmholtz equation over the FD cells with the wide-range permittivity
+ * of tmm_get_epsilon (:503-570), evaluated in every diffusion sub-step.  eps_bb[nbb][3] = the rows of
+ * alu_eps_bb.dat (lambda [um] ascending, Re, Im), K12[nk][2] = the rows of K12.dat (nk >= 1500), as
+ * tmm_init reads them (:117-118); tmm_threshold = tmm_absorption_threshold; laser_t_1 / laser_sigma_t1 =
+ * the second pulse (0 0: none).  Needs IMDCU_EOS_PHASE.  Call before imdcu_ttm_init. */
+int  imdcu_ttm_set_tmm(imdcu_ctx *ctx, double tmm_threshold, double laser_t_1, double laser_sigma_t1,
+                       int nbb, const double *eps_bb, int nk, const double *K12);
 /* init_ttm + tmm_init (imd.c:237,245).  Needs box, tables, params and both EOS tables. */
 int  imdcu_ttm_init(imdcu_ctx *ctx, const imdcu_ttm_params *p);
 /* calc_ttm (imd_ttm.c:75-156) for MD step `steps`, after imdcu_calc_forces of the same step

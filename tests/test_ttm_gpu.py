@@ -5,7 +5,7 @@ import numpy as np
 import pytest
 
 from imd_b200 import host, synth
-from tests.ttm_util import (REL_STEP0, TE_ABS_K, TTM_CASES, TTM_FIELDS, TtmGolden, compare_cells)
+from tests.ttm_util import (REL_STEP0, TE_ABS_K, TMM_CASES, TTM_CASES, TTM_FIELDS, TtmGolden, compare_cells)
 
 pytestmark = pytest.mark.gpu
 
@@ -50,7 +50,7 @@ def test_calc_ttm_step0_matches_reference(name):
     imd.close()
 
 
-@pytest.mark.parametrize("name", TTM_CASES)
+@pytest.mark.parametrize("name", TTM_CASES + TMM_CASES)
 def test_full_loop_matches_reference(name):
     """calc_forces -> calc_ttm -> move_atoms_ttm on the device for the whole reference run,
     compared at every dumped step: atoms, numneighs (bit exact) and the FD lattice."""
