@@ -256,6 +256,8 @@ def workload_config(args):
         w = ("Al fcc EAM2 + 1-D TTM film (calc_forces, calc_ttm, move_atoms_ttm), %dx%dx%d cubic cells = %d atoms per "
              "GPU, vacuum 10 a front and rear, pbc 0 1 1, 300 K, timestep 0.1, nbl_margin 0.4, FD cell ~16 A, "
              "fd_n_timesteps %d (BASELINE.json configs[2] shape)" % (c[0], c[1], c[2], n, args.ttm_substeps))
+        if getattr(args, "tmm", False):
+            w += ", laser source by do_tmm (transfer-matrix Helmholtz solver per sub-step, synthetic eps_bb/K12 tables)"
         if getattr(args, "nrb", False):
             w += (", non-reflecting rear boundary (nrb_forces on the last atomic layer, nrb_k 1.2; "
                   "BASELINE.json configs[3] shape)")
@@ -342,7 +344,8 @@ def our_arm(args, rank, local_rank, world):
         eos = synth.make_eos_tables()          # diag = None: all rectangles split the same way
         gx = max(world, int(box[0, 0] / 16.0) // world * world)
         tp = synth.TtmParams(ttmdimx=gx, fd_n_timesteps=args.ttm_substeps, fd_min_atoms=100, vlatdim=30,
-                             vlatbuffer=8, I0=5.0e15, laser_t_0=100e-15, laser_sigma_t=42.5e-15)
+                             vlatbuffer=8, I0=5.0e15, laser_t_0=100e-15, laser_sigma_t=42.5e-15,
+                             use_tmm=1 if args.tmm else 0, tmm_threshold=4.0)
         imd.init_ttm(tp, eos, world)
     if args.nrb:
         st = rear_boundary_state(args.cells, world)
@@ -646,6 +649,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ttm", action="store_true", help="EAM + TTM step (BASELINE.json configs[2])")
     ap.add_argument("--ttm-substeps", type=int, default=250, help="fd_n_timesteps (manual example: 250)")
+    ap.add_argument("--tmm", action="store_true",
+                    help="with --ttm: the reference's transfer-matrix laser source (do_tmm) instead of the analytic one")
     ap.add_argument("--nrb", action="store_true",
                     help="with --ttm: non-reflecting rear boundary (BASELINE.json configs[3])")
     ap.add_argument("--workload", default="md", choices=["md", "ttm3d"],
