@@ -19,22 +19,22 @@ __device__ __forceinline__ cplx cmul(cplx a, cplx b) { return cmk(a.re * b.re - 
 __device__ __forceinline__ cplx cscale(double s, cplx a) { return cmk(s * a.re, s * a.im); }
 __device__ __forceinline__ cplx cdivc(cplx a, cplx b)
 {
-  const double d = b.re * b.re + b.im * b.im;
-  return cmk((a.re * b.re + a.im * b.im) / d, (a.im * b.re - a.re * b.im) / d);
+  const double r = prcp(b.re * b.re + b.im * b.im);          // one reciprocal for both parts (<= 1 ulp each)
+  return cmk((a.re * b.re + a.im * b.im) * r, (a.im * b.re - a.re * b.im) * r);
 }
 __device__ __forceinline__ cplx crdiv(double s, cplx b)          // real / complex
 {
-  const double d = b.re * b.re + b.im * b.im;
-  return cmk((s * b.re) / d, (-s * b.im) / d);
+  const double r = prcp(b.re * b.re + b.im * b.im);
+  return cmk((s * b.re) * r, (-s * b.im) * r);
 }
 __device__ __forceinline__ double cabs2(cplx a) { return a.re * a.re + a.im * a.im; }
 __device__ __forceinline__ cplx csqrtc(cplx z)                   // glibc csqrt, finite non-zero operands
 {
   if (z.im == 0.0) return z.re < 0.0 ? cmk(0.0, copysign(sqrt(-z.re), z.im)) : cmk(fabs(sqrt(z.re)), copysign(0.0, z.im));
-  const double d = hypot(z.re, z.im);
+  const double d = psqrt(z.re * z.re + z.im * z.im);         // permittivities: no overflow to guard against
   double r, s;
-  if (z.re > 0) { r = sqrt(0.5 * (d + z.re)); s = 0.5 * (z.im / r); }
-  else { s = sqrt(0.5 * (d - z.re)); r = fabs(0.5 * (z.im / s)); }
+  if (z.re > 0) { r = psqrt(0.5 * (d + z.re)); s = 0.5 * pdiv(z.im, r); }
+  else { s = psqrt(0.5 * (d - z.re)); r = fabs(0.5 * pdiv(z.im, s)); }
   return cmk(r, copysign(s, z.im));
 }
 // exp(phi1) cos(phi2) + I exp(phi1) sin(phi2) with phi1 = creal(dx kl I) = -dx Im kl, phi2 = dx Re kl
@@ -43,7 +43,7 @@ __device__ __forceinline__ cplx tmm_eiphi(double dx, cplx kl)
   const double phi1 = -(dx * kl.im), phi2 = dx * kl.re;
   double sn, cs;
   sincos(phi2, &sn, &cs);
-  const double e = exp(phi1);
+  const double e = pexp(phi1);
   return cmk(e * cs, e * sn);
 }
 
@@ -74,47 +74,52 @@ __device__ __forceinline__ double tmm_K(const TmmTables &t, double nu, int which
 // ones of imd_ttm.c:2191-2308, written out; laser_active is 1 here (do_tmm has just set it).
 __device__ __forceinline__ double tmm_fermi_E(double ne)
 {
-  return TMC_HBAR * TMC_HBAR * pow(3.0 * TMC_PI * TMC_PI * ne, 2.0 / 3.0) / 2.0 / TMC_EMASS;
+  return pdiv(TMC_HBAR * TMC_HBAR * ppow(3.0 * TMC_PI * TMC_PI * ne, 2.0 / 3.0) / 2.0, TMC_EMASS);
 }
-__device__ inline cplx tmm_get_epsilon(const TmmTables &t, double lambda, double Te, double Ti, double Z, double Ne,
-                                       int phase)
+// the interband permittivity at the laser wavelength: table walk and linear interpolation of
+// tmm_get_epsilon (:524-527, :547), the same in every call of a run
+__device__ inline cplx tmm_eps_bb(const TmmTables &t, double lambda)
 {
-  Te *= 11604.52500617; Ti *= 11604.52500617;
-  const double omega_las = (2.0 * TMC_PI * 2.998e8 / lambda);                    // LIGHTSPEED, globals.h:325
-  const double Ncr = TMC_ECONST * TMC_EMASS * omega_las * omega_las / TMC_ECHARGE / TMC_ECHARGE;
-  const double Ni = Ne / Z;
-  const double EF = tmm_fermi_E(Ne);
-  const double TF = 2.0 * EF / (3.0 * TMC_BOLTZMAN);
-  const double VF = sqrt(2 * EF / TMC_EMASS);
-  const double A1p = 4.41, A2p = 0.8, A3p = 0.7, A4p = 0.2;
   int il = 0, ir = 0;
   for (int id = 0; lambda * 1e6 > t.eps_bb[3 * id]; id++) { il = id; ir = id + 1; }
-  const double nu_met = 1.309202957843054e+11 * (A1p * Ti + A2p * Te * Te / TF);
-  const double r0n = pow(3.0 / (4 * TMC_PI * Ni), 1.0 / 3.0);
-  const double nu_max = A3p / r0n * sqrt(VF * VF + TMC_BOLTZMAN * Te / TMC_EMASS);
-  // coulomb_log(omega_las, Z, Ni, Te) with laser_active
-  const double ft = 2.0 * tmm_fermi_E(Ni * Z) / (3.0 * TMC_BOLTZMAN);
-  const double teff = sqrt(Te * Te + ft * ft);
-  const double wpl = sqrt(Ni * Z * TMC_ECHARGE * TMC_ECHARGE / TMC_EMASS / TMC_ECONST);
-  const double bmax = TM_MAX(r0n, sqrt(TMC_BOLTZMAN * teff / (TMC_EMASS)) / TM_MAX(omega_las, wpl));
-  const double bmin = TM_MAX(Z * TMC_ECHARGE * TMC_ECHARGE / (TMC_BOLTZMAN * Te),
-                             TMC_HBAR / sqrt(2 * TMC_EMASS * TMC_BOLTZMAN * Te));
-  const double coulomb = TM_MAX(2.0, log(bmax / bmin));
-  const double nu_pl = 1.863839656495274e-40 * Z * Ne * coulomb / pow(TMC_BOLTZMAN * Te, 1.5);
-  const double ksi = 0.75 * sqrt(TMC_PI) * nu_pl / omega_las;
   const cplx ebl = cmk(t.eps_bb[3 * il + 1], t.eps_bb[3 * il + 2]), ebr = cmk(t.eps_bb[3 * ir + 1], t.eps_bb[3 * ir + 2]);
   const double dl = t.eps_bb[3 * ir] - t.eps_bb[3 * il], xl = lambda * 1e6 - t.eps_bb[3 * il];
   cplx d = csub(ebr, ebl);
   d = cmk(d.re / dl, d.im / dl);
-  cplx epsilon_bb = cadd(ebl, cmk(d.re * xl, d.im * xl));
-  const int ap = phase < 0 ? -phase : phase;
-  if (ap == 3 || ap == 4 || ap == 5) epsilon_bb = cmk(0.0, 0.0);
-  const double nn = Ne / Ncr;
+  return cadd(ebl, cmk(d.re * xl, d.im * xl));
+}
+// epsilon_bb: tmm_eps_bb, or 0 where the phase table says 3, 4 or 5 (:549-552).  Divisions, roots, pow/log/exp
+// are the branch-free versions of ttm_math.cuh (<= 1-2 ulp), like in the wide-range models of do_FILLMESH.
+__device__ inline cplx tmm_get_epsilon(const TmmTables &t, double lambda, double Te, double Ti, double Z, double Ne,
+                                       cplx epsilon_bb)
+{
+  Te *= 11604.52500617; Ti *= 11604.52500617;
+  const double omega_las = (2.0 * TMC_PI * 2.998e8 / lambda);                    // LIGHTSPEED, globals.h:325
+  const double Ncr = TMC_ECONST * TMC_EMASS * omega_las * omega_las / TMC_ECHARGE / TMC_ECHARGE;
+  const double Ni = pdiv(Ne, Z);
+  const double EF = tmm_fermi_E(Ne);
+  const double TF = pdiv(2.0 * EF, 3.0 * TMC_BOLTZMAN);
+  const double VF = psqrt(pdiv(2 * EF, TMC_EMASS));
+  const double A1p = 4.41, A2p = 0.8, A3p = 0.7, A4p = 0.2;
+  const double nu_met = 1.309202957843054e+11 * (A1p * Ti + pdiv(A2p * Te * Te, TF));
+  const double r0n = ppow(pdiv(3.0, 4 * TMC_PI * Ni), 1.0 / 3.0);
+  const double kTe = TMC_BOLTZMAN * Te;
+  const double nu_max = pdiv(A3p, r0n) * psqrt(VF * VF + pdiv(kTe, TMC_EMASS));
+  // coulomb_log(omega_las, Z, Ni, Te) with laser_active
+  const double ft = pdiv(2.0 * tmm_fermi_E(Ni * Z), 3.0 * TMC_BOLTZMAN);
+  const double teff = psqrt(Te * Te + ft * ft);
+  const double wpl = psqrt(pdiv(pdiv(Ni * Z * TMC_ECHARGE * TMC_ECHARGE, TMC_EMASS), TMC_ECONST));
+  const double bmax = TM_MAX(r0n, pdiv(psqrt(pdiv(TMC_BOLTZMAN * teff, TMC_EMASS)), TM_MAX(omega_las, wpl)));
+  const double bmin = TM_MAX(pdiv(Z * TMC_ECHARGE * TMC_ECHARGE, kTe), pdiv(TMC_HBAR, psqrt(2 * TMC_EMASS * kTe)));
+  const double coulomb = TM_MAX(2.0, plog(pdiv(bmax, bmin)));
+  const double nu_pl = pdiv(1.863839656495274e-40 * Z * Ne * coulomb, kTe * psqrt(kTe));      // pow(kTe, 1.5)
+  const double ksi = pdiv(0.75 * sqrt(TMC_PI) * nu_pl, omega_las);
+  const double nn = pdiv(Ne, Ncr);
   // epsilon_met = epsilon_bb + 1 - Ne/Ncr / (1 + i MIN(nu_met, nu_max)/omega_las)
-  const cplx met = csub(cadd(epsilon_bb, cmk(1.0, 0.0)), crdiv(nn, cmk(1.0, TM_MIN(nu_met, nu_max) / omega_las)));
+  const cplx met = csub(cadd(epsilon_bb, cmk(1.0, 0.0)), crdiv(nn, cmk(1.0, pdiv(TM_MIN(nu_met, nu_max), omega_las))));
   // epsilon_pl = 1 - Ne/Ncr (K1(ksi) - i nu_pl/omega_las K2(ksi))
-  const cplx pl = csub(cmk(1.0, 0.0), cscale(nn, cmk(tmm_K(t, ksi, 0), -(nu_pl / omega_las * tmm_K(t, ksi, 1)))));
-  const double w = exp(-A4p * Te / TF);
+  const cplx pl = csub(cmk(1.0, 0.0), cscale(nn, cmk(tmm_K(t, ksi, 0), -(pdiv(nu_pl, omega_las) * tmm_K(t, ksi, 1)))));
+  const double w = pexp(pdiv(-A4p * Te, TF));
   return cadd(pl, cscale(w, csub(met, pl)));
 }
 
@@ -146,9 +151,8 @@ __device__ inline double tmm_runge5(double delta, cplx kl, cplx Bplus, cplx Bmin
 }
 
 // tmpmat = Cinv * Pmat of one interface (imd_tmm.c:299-313): M = {m0, m1, m2, m3}, column-major like matmul
-__device__ __forceinline__ void tmm_interface(double dx, cplx kl, cplx kr, cplx M[4])
+__device__ __forceinline__ void tmm_interface(cplx e, cplx kl, cplx kr, cplx M[4])      // e = tmm_eiphi(dx, kl)
 {
-  const cplx e = tmm_eiphi(dx, kl);
   const cplx P0 = e, P2 = crdiv(1.0, e), P1 = e, P3 = cneg(P2);
   const cplx C0 = cmk(0.5, 0.0), C1 = cmk(0.5, 0.0);
   const cplx C2 = cdivc(cscale(0.5, kl), kr), C3 = cneg(C2);

@@ -166,6 +166,9 @@ __device__ double eos_te_from_r_ee(const EosView &ee, double r, double e)
   return fminbnd_ref(ee, a, b, r, e);
 }
 
+#ifndef TMM_SKIP
+#define TMM_SKIP 0            /* timing experiments on the do_tmm sections, 0 = product */
+#endif
 #include "tmm.cuh"
 
 // ----------------------------------------------------------------------------- device state
@@ -191,9 +194,9 @@ struct TtmArgs {
   double tmm_threshold, laser_t_1, sigma_t1_sq;
   TmmTables tmm;
   EosView phase;                     // global memory
-  double *tmm_buf;                   // [TMM_BUF_PER_CELL][G+2]: eps_re, eps_im, active, km(2), M(8), Bplus(2), Bminus(2), Qabs
+  double *tmm_buf;                   // [TMM_BUF_PER_CELL][G+2]: eps_re, eps_im, active, km(2), M(8), Bplus(2), Bminus(2), Qabs, phase flag
 };
-#define TMM_BUF_PER_CELL 18
+#define TMM_BUF_PER_CELL 19
 
 // ----------------------------------------------------------------------------- atom kernels
 // slab index of an atom (imd_ttm.c:277-279)
@@ -726,6 +729,32 @@ k_ttm_grid(TtmArgs a)
   const int GG = a.G + 2;
   double *q_re = a.tmm_buf, *q_im = q_re + GG, *q_act = q_im + GG, *q_km = q_act + GG, *q_M = q_km + 2 * GG,
          *q_Bp = q_M + 8 * GG, *q_Bm = q_Bp + 2 * GG, *q_Q = q_Bm + 2 * GG;
+  // the vacuum in front of the sample is "cell 0" with dx = 1e10 A (imd_tmm.c:297): its phase factor
+  // exp(i k0 1e10) -- a sincos of 7.85e6 rad -- is the same in every sub-step
+  cplx eiphi0 = cmk(1.0, 0.0), eps_bb = cmk(0.0, 0.0);
+  double *q_ph = q_Q + GG;           // 1 where the phase table removes the interband term
+  if (a.use_tmm) {
+    double k0 = 2.0 * TMC_PI / a.p.lambda; k0 /= 1e10;
+    eiphi0 = tmm_eiphi(1e10, cmk(k0, 0.0));
+    eps_bb = tmm_eps_bb(a.tmm, a.p.lambda);
+    // phase = (int) EOS_phase_from_r_ti(Ni 26.9815 AMU, Ti [K]) (:548): Ni = ne/Z = dens/(A AMU) and Ti do not change
+    // during the sub-steps, so the lookup is made once per MD step
+    for (int c = threadIdx.x; c < ncell; c += blockDim.x) {
+      const TCell &x = l1[(c / L) * LD + c % L + 1];
+      double flag = 0.0;
+      if (!(x.natoms < mn || x.dens < RHOMIN)) {
+        const double Ni = x.ne / x.Z;
+        double pr = Ni * 26.9815 * C_AMU, pt = x.md_temp * 11604.52500617;      // EOS_phase_from_r_ti clamps (DEBUG_LEVEL > 0)
+        pr = DMAX(DMIN(pr, a.phase.x[a.phase.nx - 1]), a.phase.x[0]);
+        pt = DMAX(DMIN(pt, a.phase.y[a.phase.ny - 1]), a.phase.y[0]);
+        int ph = (int) eos_interp(a.phase, pr, pt);
+        ph = ph < 0 ? -ph : ph;
+        flag = (ph == 3 || ph == 4 || ph == 5) ? 1.0 : 0.0;
+      }
+      q_ph[c] = flag;
+    }
+    __syncthreads();
+  }
   for (int s = 0; s < diff_substeps; s++) {
     double I_t;
     if (!a.use_tmm) {
@@ -751,12 +780,12 @@ k_ttm_grid(TtmArgs a)
           for (int c = threadIdx.x; c < ncell; c += blockDim.x) {
             const TCell &x = l1[(c / L) * LD + c % L + 1];
             if (x.natoms < mn || x.dens < RHOMIN) { q_re[c] = 0.0; q_im[c] = 0.0; q_act[c] = 0.0; continue; }
-            const double Ni = x.ne / x.Z;
-            double pr = Ni * 26.9815 * C_AMU, pt = x.md_temp * 11604.52500617;      // EOS_phase_from_r_ti clamps (DEBUG_LEVEL > 0)
-            pr = DMAX(DMIN(pr, a.phase.x[a.phase.nx - 1]), a.phase.x[0]);
-            pt = DMAX(DMIN(pt, a.phase.y[a.phase.ny - 1]), a.phase.y[0]);
-            const int phase = (int) eos_interp(a.phase, pr, pt);
-            const cplx e = tmm_get_epsilon(a.tmm, a.p.lambda, x.temp, x.md_temp, x.Z, x.ne, phase);
+#if TMM_SKIP == 1
+            const cplx e = cmk(-40.0 - x.temp, 12.0 + x.temp);
+#else
+            const cplx e = tmm_get_epsilon(a.tmm, a.p.lambda, x.temp, x.md_temp, x.Z, x.ne,
+                                           q_ph[c] != 0.0 ? cmk(0.0, 0.0) : eps_bb);
+#endif
             q_re[c] = e.re; q_im[c] = e.im; q_act[c] = 1.0;
           }
           __syncthreads();
@@ -770,7 +799,12 @@ k_ttm_grid(TtmArgs a)
           // Cinv * Pmat of every interface, in parallel: the transcendental part of loops 2 and 3
           for (int i = threadIdx.x; i < G - 1; i += blockDim.x) {
             cplx M[4];
-            tmm_interface(i == 0 ? 1e10 : a.fd_hx, cmk(q_km[2 * i], q_km[2 * i + 1]), cmk(q_km[2 * i + 2], q_km[2 * i + 3]), M);
+            const cplx kl = cmk(q_km[2 * i], q_km[2 * i + 1]);
+#if TMM_SKIP == 2
+            M[0] = kl; M[1] = cmk(0.5, 0.1); M[2] = cmk(0.1, 0.2); M[3] = cmk(0.9, 0.0);
+#else
+            tmm_interface(i == 0 ? eiphi0 : tmm_eiphi(a.fd_hx, kl), kl, cmk(q_km[2 * i + 2], q_km[2 * i + 3]), M);
+#endif
 #pragma unroll
             for (int j = 0; j < 4; j++) { q_M[8 * i + 2 * j] = M[j].re; q_M[8 * i + 2 * j + 1] = M[j].im; }
           }
@@ -780,16 +814,18 @@ k_ttm_grid(TtmArgs a)
             const double ecut_thresh = exp(-a.tmm_threshold);
             cplx E0 = cmk(1.0, 0.0), E1 = cmk(0.0, 0.0), E2 = cmk(0.0, 0.0), E3 = cmk(1.0, 0.0), BR = cmk(0.0, 0.0);
             int ecut = -1;
-            for (int i = 0; i < G - 1; i++) {
+            for (int i = 0; i < (TMM_SKIP == 3 ? 1 : G - 1); i++) {
               const double *m = q_M + 8 * i;
               const cplx M0 = cmk(m[0], m[1]), M1 = cmk(m[2], m[3]), M2 = cmk(m[4], m[5]), M3 = cmk(m[6], m[7]);
               const cplx n0 = cadd(cmul(M0, E0), cmul(M2, E1)), n1 = cadd(cmul(M1, E0), cmul(M3, E1));
               const cplx n2 = cadd(cmul(M0, E2), cmul(M2, E3)), n3 = cadd(cmul(M1, E2), cmul(M3, E3));
               E0 = n0; E1 = n1; E2 = n2; E3 = n3;
-              BR = cdivc(cneg(E1), E3);                                             // -Emat[1]*B0/Emat[3], B0 = 1
-              const cplx BT = cadd(E0, cmul(E2, BR));
-              if (cabs2(BT) < ecut_thresh) { ecut = i + 1; break; }
+              // BR = -Emat[1] B0/Emat[3], BT = Emat[0] B0 + Emat[2] BR = det(Emat)/Emat[3] with B0 = 1: the stop test
+              // |BT|^2 < thresh needs no quotient, BR itself only once the loop has stopped
+              const cplx det = csub(cmul(E0, E3), cmul(E2, E1));
+              if (cabs2(det) < ecut_thresh * cabs2(E3)) { ecut = i + 1; break; }
             }
+            BR = cdivc(cneg(E1), E3);
             if (ecut < 0) { atomicMax(err, 6); ecut = 0; }
             // loop 3 (:353-385): forward and backward amplitudes at the left edge of every cell up to ecut
             cplx F0 = cmk(1.0, 0.0), F1 = BR;
@@ -807,7 +843,7 @@ k_ttm_grid(TtmArgs a)
           // loop 4 (:389-408): absorbed power per cell; a cell without absorption gives I_t k0 0 (finite) = 0
           for (int i = threadIdx.x; i < s_ecut; i += blockDim.x) {
             double R = 0.0;
-            if (q_im[i] != 0.0)
+            if (q_im[i] != 0.0 && TMM_SKIP != 4)
               R = tmm_runge5(i == 0 ? 1e10 : a.fd_hx, cmk(q_km[2 * i], q_km[2 * i + 1]), cmk(q_Bp[2 * i], q_Bp[2 * i + 1]),
                              cmk(q_Bm[2 * i], q_Bm[2 * i + 1]));
             double Q = I_t * k0 * q_im[i] * R;

@@ -6,11 +6,13 @@ set -e
 cd "$(dirname "$0")/../imd_b200/csrc"
 make -j8 > /dev/null
 mkdir -p ../variants
-FLAGS="-O3 -std=c++17 -lineinfo -gencode arch=compute_100a,code=sm_100a -Xcompiler -fPIC,-ffp-contract=off,-Wall"
+SRC=${SRC:-eam.cu}            # SRC=ttm.cu EXTRA=-fmad=false for the lattice kernel
+BASE=${SRC%.cu}
+FLAGS="$EXTRA -O3 -std=c++17 -lineinfo -gencode arch=compute_100a,code=sm_100a -Xcompiler -fPIC,-ffp-contract=off,-Wall"
 while [ $# -ge 2 ]; do
   name=$1; defs=$2; shift 2
-  nvcc $FLAGS $defs -c eam.cu -o /tmp/eam_$name.o
-  objs=$(ls *.o | grep -v '^eam.o$')
-  nvcc -gencode arch=compute_100a,code=sm_100a -shared -o ../variants/libimdcu_$name.so $objs /tmp/eam_$name.o -lcudart -ldl
+  nvcc $FLAGS $defs -c $SRC -o /tmp/${BASE}_$name.o
+  objs=$(ls *.o | grep -v "^$BASE.o\$")
+  nvcc -gencode arch=compute_100a,code=sm_100a -shared -o ../variants/libimdcu_$name.so $objs /tmp/${BASE}_$name.o -lcudart -ldl
   echo built $name "($defs)"
 done
