@@ -184,7 +184,7 @@ struct TtmArgs {
   imdcu_ttm_params p;
   double timestep, fd_hx, fd_vol, neighvol, omega_laser, sigma_t_sq;
   EosView cve, ee;
-  int eos_smem, pad_;                // tables are staged into dynamic shared memory
+  int eos_smem, lat_smem;            // EOS tables / the lattices are staged into dynamic shared memory
   TCell *lat, *vlat;                 // [2][P*LD], [2][vlatdim]
   int *isum; double *dsum;           // slab sums, see k_ttm_atoms1
   double *xiarr, *xiloc, *vcom, *src_e, *winv;   // winv: [ncell_tot][WINV_N], see fill_inv
@@ -553,6 +553,7 @@ k_ttm_grid(TtmArgs a)
   // EOS tables: staged into shared memory when they fit (the binary searches and the four corner
   // loads of every interpolation are dependent loads on the critical path of each sub-step)
   EosView cve = a.cve, ee = a.ee;
+  size_t dyn_used = 0;
   if (a.eos_smem) {
     double *d = s_dyn;
     EosView *vs[2] = { &cve, &ee };
@@ -572,6 +573,32 @@ k_ttm_grid(TtmArgs a)
       b += (ng + 7) & ~7;
     }
     __syncthreads();
+    dyn_used = (size_t) (b - reinterpret_cast<unsigned char *>(s_dyn));
+  }
+  // Both lattices and both virtual lattices live in shared memory for the whole launch: every sub-step reads the
+  // cells the previous one wrote, and written lines are not kept in L1, so from global memory each of those
+  // reads is an L2 round trip on the critical path (long-scoreboard stalls 5.2 per issue at G = 207).
+  TCell *g_lat = a.lat, *g_vlat = a.vlat;
+  double *xiloc = a.xiloc, *tmm_base = a.tmm_buf;
+  const int nvl = a.p.vlatdim > 0 ? a.p.vlatdim : 1;
+  if (a.lat_smem) {
+    TCell *sl = reinterpret_cast<TCell *>(reinterpret_cast<unsigned char *>(s_dyn) + ((dyn_used + 15) & ~(size_t) 15));
+    TCell *sv = sl + 2 * nl;
+    for (int k = threadIdx.x; k < 2 * nl; k += blockDim.x) sl[k] = g_lat[k];
+    for (int k = threadIdx.x; k < 2 * nvl; k += blockDim.x) sv[k] = g_vlat[k];
+    l1 = sl + cur * nl; l2 = sl + (1 - cur) * nl;
+    v1 = sv + vcur * a.p.vlatdim; v2 = sv + (1 - vcur) * a.p.vlatdim;
+    g_lat = sl; g_vlat = sv;                     // base pointers of whichever copy is live
+    // per-cell xi sums of this step (thread private in effect, but read-modify-write in every sub-step) and the
+    // scratch arrays of do_tmm; of the latter only tmm_Qabs outlives the launch
+    xiloc = reinterpret_cast<double *>(sv + 2 * nvl);
+    if (a.use_tmm) {
+      tmm_base = xiloc + nl;
+      double *qs = tmm_base + 17 * (size_t) (a.G + 2);
+      const double *qg = a.tmm_buf + 17 * (size_t) (a.G + 2);
+      for (int k = threadIdx.x; k < a.G + 2; k += blockDim.x) qs[k] = qg[k];
+    }
+    __syncthreads();
   }
   const double z0p43 = pow(a.p.atomic_charge, 4. / 3.);                       // MeanCharge's pow(z0, 4/3)
 
@@ -588,7 +615,7 @@ k_ttm_grid(TtmArgs a)
     x.source = y.source = 0.0;
     x.natoms_old = y.natoms_old = x.natoms;
     x.xi = y.xi = 0.0;
-    a.xiloc[idx] = 0.0;
+    xiloc[idx] = 0.0;
     x.natoms = natomsg[g]; y.natoms = x.natoms;
     if (x.natoms > 0) {
       x.dens = ((double) totneigh[g]) / ((double) x.natoms) * a.p.atomic_weight / a.neighvol * 1660.53907;
@@ -727,7 +754,7 @@ k_ttm_grid(TtmArgs a)
   const double tau_ci = tau / Ci;
   // do_tmm scratch (global memory, L1/L2 resident): see TtmArgs::tmm_buf
   const int GG = a.G + 2;
-  double *q_re = a.tmm_buf, *q_im = q_re + GG, *q_act = q_im + GG, *q_km = q_act + GG, *q_M = q_km + 2 * GG,
+  double *q_re = tmm_base, *q_im = q_re + GG, *q_act = q_im + GG, *q_km = q_act + GG, *q_M = q_km + 2 * GG,
          *q_Bp = q_M + 8 * GG, *q_Bm = q_Bp + 2 * GG, *q_Q = q_Bm + 2 * GG;
   // the vacuum in front of the sample is "cell 0" with dx = 1e10 A (imd_tmm.c:297): its phase factor
   // exp(i k0 1e10) -- a sincos of 7.85e6 rad -- is the same in every sub-step
@@ -886,7 +913,7 @@ k_ttm_grid(TtmArgs a)
         const double dxi = pdiv(pdiv((y.temp - x.md_temp) * xi_fac * x.fd_g, x.md_temp), x.dens);
         x.xi += dxi;
         y.xi = x.xi;
-        a.xiloc[idx] += dxi;
+        xiloc[idx] += dxi;
         if (isnan(y.temp) || isinf(y.temp)) atomicMax(err, 5);
       } else if (rv >= 0 && rv < P) {                                      // virtual lattice (:1602-1657)
         const int i = c - ncell, nv = a.p.vlatdim;
@@ -918,7 +945,7 @@ k_ttm_grid(TtmArgs a)
   for (int c = threadIdx.x; c < ncell; c += blockDim.x) {
     const int idx = (c / L) * LD + c % L + 1;
     TCell &x = l1[idx], &y = l2[idx];
-    a.xiarr[c] = a.xiloc[idx];
+    a.xiarr[c] = xiloc[idx];
     if (active_ge(x, mn)) {
       x.U = eos_ee_from_r_te(ee, x.dens, x.temp * 11604.5) * 26.9815 * C_AMU * C_J2eV;
       y.U = x.U;
@@ -927,6 +954,16 @@ k_ttm_grid(TtmArgs a)
   }
   eel = block_reduce(eel, 0, s_red);
   eabs = block_reduce(eabs, 0, s_red);
+  if (a.lat_smem) {
+    __syncthreads();
+    for (int k = threadIdx.x; k < 2 * nl; k += blockDim.x) a.lat[k] = g_lat[k];
+    for (int k = threadIdx.x; k < 2 * nvl; k += blockDim.x) a.vlat[k] = g_vlat[k];
+    if (a.use_tmm) {
+      const double *qs = tmm_base + 17 * (size_t) (a.G + 2);
+      double *qg = a.tmm_buf + 17 * (size_t) (a.G + 2);
+      for (int k = threadIdx.x; k < a.G + 2; k += blockDim.x) qg[k] = qs[k];
+    }
+  }
   if (threadIdx.x == 0) {
     sc->cur = cur; sc->vcur = vcur;
     sc->diff_substeps = diff_substeps; sc->laser_active = la;
@@ -1149,8 +1186,15 @@ static int ttm_grid_part(imdcu_ctx *c, int steps, cudaStream_t st)
     smem += (nx + ny + nx * ny) * sizeof(double) + (((nx - 1) * (ny - 1) + 7) & ~(size_t) 7);
   }
   a.eos_smem = smem <= 200 * 1024;
-  a.pad_ = 0;
   if (!a.eos_smem) smem = 0;
+  {
+    static const bool off = [] { const char *e = getenv("IMDCU_TTM_LAT_SMEM"); return e && e[0] == '0'; }();
+    const size_t nvl = t.p.vlatdim > 0 ? t.p.vlatdim : 1;
+    const size_t lat_bytes = (2 * (size_t) t.P * t.LD + 2 * nvl) * sizeof(TCell) + 16 + (size_t) t.P * t.LD * sizeof(double) +
+                             (t.use_tmm ? TMM_BUF_PER_CELL * (size_t) (t.G + 2) * sizeof(double) : 0);
+    a.lat_smem = !off && smem + lat_bytes <= 210 * 1024;
+    if (a.lat_smem) smem += lat_bytes;
+  }
   // Beside k_eam_pass2 (imdcu_ttm_fork) the lattice CTA asks for so much shared memory that no CTA of
   // the force kernel fits next to it: sharing an SM with 16 warps that keep the L1 data pipe 80 % busy
   // stretches every dependent load and barrier of this latency chain.  Pass 2 leaves that SM alone
