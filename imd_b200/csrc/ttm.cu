@@ -836,35 +836,70 @@ k_ttm_grid(TtmArgs a)
             for (int j = 0; j < 4; j++) { q_M[8 * i + 2 * j] = M[j].re; q_M[8 * i + 2 * j + 1] = M[j].im; }
           }
           __syncthreads();
-          if (threadIdx.x == 0) {
-            // loop 2 (:292-334): E = (Cinv P) E until the transmitted field is below exp(-tmm_threshold)
+          if (threadIdx.x < 32) {
+            // loops 2 and 3 (:292-334, :353-385) are prefix products E_i = M_i ... M_0 of the interface matrices: warp 0
+            // scans them 32 cells at a time (five shuffle steps instead of 32 dependent 2x2 complex products), tests
+            // |BT_i|^2 = |det E_i|^2 / |E_i[3]|^2 < exp(-tmm_threshold) on every lane, and gets the amplitudes of loop 3
+            // as E_i (B0, BR)^T.  Same products as the reference's recurrences, associated as a tree.
+            const int lane = threadIdx.x;
             const double ecut_thresh = exp(-a.tmm_threshold);
-            cplx E0 = cmk(1.0, 0.0), E1 = cmk(0.0, 0.0), E2 = cmk(0.0, 0.0), E3 = cmk(1.0, 0.0), BR = cmk(0.0, 0.0);
+            cplx C[4] = { cmk(1.0, 0.0), cmk(0.0, 0.0), cmk(0.0, 0.0), cmk(1.0, 0.0) };      // carry: product of earlier chunks
+            cplx BR = cmk(0.0, 0.0);
             int ecut = -1;
-            for (int i = 0; i < (TMM_SKIP == 3 ? 1 : G - 1); i++) {
-              const double *m = q_M + 8 * i;
-              const cplx M0 = cmk(m[0], m[1]), M1 = cmk(m[2], m[3]), M2 = cmk(m[4], m[5]), M3 = cmk(m[6], m[7]);
-              const cplx n0 = cadd(cmul(M0, E0), cmul(M2, E1)), n1 = cadd(cmul(M1, E0), cmul(M3, E1));
-              const cplx n2 = cadd(cmul(M0, E2), cmul(M2, E3)), n3 = cadd(cmul(M1, E2), cmul(M3, E3));
-              E0 = n0; E1 = n1; E2 = n2; E3 = n3;
-              // BR = -Emat[1] B0/Emat[3], BT = Emat[0] B0 + Emat[2] BR = det(Emat)/Emat[3] with B0 = 1: the stop test
-              // |BT|^2 < thresh needs no quotient, BR itself only once the loop has stopped
+            for (int base = 0; base < G - 1 && ecut < 0; base += 32) {
+              const int i = base + lane;
+              const bool valid = i < G - 1;
+              cplx Pm[4] = { cmk(1.0, 0.0), cmk(0.0, 0.0), cmk(0.0, 0.0), cmk(1.0, 0.0) };
+              if (valid) {
+                const double *m = q_M + 8 * i;
+                Pm[0] = cmk(m[0], m[1]); Pm[1] = cmk(m[2], m[3]); Pm[2] = cmk(m[4], m[5]); Pm[3] = cmk(m[6], m[7]);
+              }
+#pragma unroll
+              for (int o = 1; o < 32; o <<= 1) {
+                cplx O[4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                  O[j].re = __shfl_up_sync(0xffffffffu, Pm[j].re, o);
+                  O[j].im = __shfl_up_sync(0xffffffffu, Pm[j].im, o);
+                }
+                if (lane >= o) {                                                       // P_i <- P_i * P_(i-o)
+                  const cplx n0 = cadd(cmul(Pm[0], O[0]), cmul(Pm[2], O[1])), n1 = cadd(cmul(Pm[1], O[0]), cmul(Pm[3], O[1]));
+                  const cplx n2 = cadd(cmul(Pm[0], O[2]), cmul(Pm[2], O[3])), n3 = cadd(cmul(Pm[1], O[2]), cmul(Pm[3], O[3]));
+                  Pm[0] = n0; Pm[1] = n1; Pm[2] = n2; Pm[3] = n3;
+                }
+              }
+              // E_i = P_i * carry
+              const cplx E0 = cadd(cmul(Pm[0], C[0]), cmul(Pm[2], C[1])), E1 = cadd(cmul(Pm[1], C[0]), cmul(Pm[3], C[1]));
+              const cplx E2 = cadd(cmul(Pm[0], C[2]), cmul(Pm[2], C[3])), E3 = cadd(cmul(Pm[1], C[2]), cmul(Pm[3], C[3]));
               const cplx det = csub(cmul(E0, E3), cmul(E2, E1));
-              if (cabs2(det) < ecut_thresh * cabs2(E3)) { ecut = i + 1; break; }
+              const bool hit = valid && cabs2(det) < ecut_thresh * cabs2(E3);
+              const unsigned mask = __ballot_sync(0xffffffffu, hit);
+              const int src = mask ? __ffs(mask) - 1 : 31;
+              if (valid) {                                                              // E_i replaces M_i (read back below)
+                double *m = q_M + 8 * i;
+                m[0] = E0.re; m[1] = E0.im; m[2] = E1.re; m[3] = E1.im; m[4] = E2.re; m[5] = E2.im; m[6] = E3.re; m[7] = E3.im;
+              }
+              const cplx br = cdivc(cneg(E1), E3);                                      // -Emat[1] B0 / Emat[3], B0 = 1
+              BR.re = __shfl_sync(0xffffffffu, br.re, src); BR.im = __shfl_sync(0xffffffffu, br.im, src);
+              if (mask) ecut = base + src + 1;
+              else {
+                C[0].re = __shfl_sync(0xffffffffu, E0.re, 31); C[0].im = __shfl_sync(0xffffffffu, E0.im, 31);
+                C[1].re = __shfl_sync(0xffffffffu, E1.re, 31); C[1].im = __shfl_sync(0xffffffffu, E1.im, 31);
+                C[2].re = __shfl_sync(0xffffffffu, E2.re, 31); C[2].im = __shfl_sync(0xffffffffu, E2.im, 31);
+                C[3].re = __shfl_sync(0xffffffffu, E3.re, 31); C[3].im = __shfl_sync(0xffffffffu, E3.im, 31);
+              }
             }
-            BR = cdivc(cneg(E1), E3);
-            if (ecut < 0) { atomicMax(err, 6); ecut = 0; }
-            // loop 3 (:353-385): forward and backward amplitudes at the left edge of every cell up to ecut
-            cplx F0 = cmk(1.0, 0.0), F1 = BR;
-            q_Bp[0] = 1.0; q_Bp[1] = 0.0; q_Bm[0] = BR.re; q_Bm[1] = BR.im;
-            for (int i = 0; i < ecut; i++) {
+            if (ecut < 0) {                                                             // "Sample is too short for TMM"
+              if (lane == 0) atomicMax(err, 6);
+              ecut = 0;
+            }
+            __syncwarp();
+            if (lane == 0) { q_Bp[0] = 1.0; q_Bp[1] = 0.0; q_Bm[0] = BR.re; q_Bm[1] = BR.im; s_ecut = ecut; }
+            for (int i = lane; i < ecut; i += 32) {                                     // Bplus/Bminus[i+1] = E_i (B0, BR)^T
               const double *m = q_M + 8 * i;
-              const cplx M0 = cmk(m[0], m[1]), M1 = cmk(m[2], m[3]), M2 = cmk(m[4], m[5]), M3 = cmk(m[6], m[7]);
-              const cplx t0 = cadd(cmul(M0, F0), cmul(M2, F1)), t1 = cadd(cmul(M1, F0), cmul(M3, F1));
-              F0 = t0; F1 = t1;
+              const cplx F0 = cadd(cmk(m[0], m[1]), cmul(cmk(m[4], m[5]), BR)), F1 = cadd(cmk(m[2], m[3]), cmul(cmk(m[6], m[7]), BR));
               q_Bp[2 * i + 2] = F0.re; q_Bp[2 * i + 3] = F0.im; q_Bm[2 * i + 2] = F1.re; q_Bm[2 * i + 3] = F1.im;
             }
-            s_ecut = ecut;
           }
           __syncthreads();
           // loop 4 (:389-408): absorbed power per cell; a cell without absorption gives I_t k0 0 (finite) = 0

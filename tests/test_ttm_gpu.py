@@ -179,6 +179,36 @@ def test_ttm_error_paths():
         imd.ctx.ttm_init(g.tp, 5)
     with pytest.raises(capi.ImdcuError):                 # calc_ttm before init
         imd.ctx.calc_ttm(0)
+    # do_tmm: K12 needs its 1500 rows, wavelengths must ascend, the phase table must be there, lambda inside eps_bb
+    tabs = synth.make_tmm_tables()
+    with pytest.raises(capi.ImdcuError):
+        imd.ctx.ttm_set_tmm(5.0, tabs["eps_bb"], tabs["K12"][:100])
+    with pytest.raises(capi.ImdcuError):
+        imd.ctx.ttm_set_tmm(5.0, tabs["eps_bb"][::-1], tabs["K12"])
+    imd.ctx.ttm_set_tmm(5.0, tabs["eps_bb"], tabs["K12"])
+    with pytest.raises(capi.ImdcuError):                 # IMDCU_EOS_PHASE missing
+        imd.ctx.ttm_init(g.tp, 2)
+    imd.ctx.ttm_set_eos(2, g.eos["phase"])
+    import dataclasses
+    with pytest.raises(capi.ImdcuError):                 # 5 um is outside the interband table
+        imd.ctx.ttm_init(dataclasses.replace(g.tp, lam=5e-6), 2)
+    imd.ctx.ttm_init(g.tp, 2)
+    imd.close()
+
+
+def test_tmm_sample_too_short():
+    """The reference stops with "Sample is too short for TMM" when the field never drops below
+    exp(-tmm_threshold) inside the FD lattice (imd_tmm.c:335-345); the library reports the same at calc_ttm."""
+    import dataclasses
+    from imd_b200 import capi
+    g = TtmGolden(TMM_CASES[0])
+    g.tp = dataclasses.replace(g.tp, tmm_threshold=40.0)
+    imd = make_imd(g)
+    with pytest.raises(capi.ImdcuError, match="too short"):
+        for s in range(4):
+            imd.calc_forces(s)
+            imd.calc_ttm(s)
+            imd.move_atoms_ttm()
     imd.close()
 
 
