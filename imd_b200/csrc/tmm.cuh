@@ -10,25 +10,29 @@
 
 #include "ttm_models.cuh"
 
+#ifndef __CUDACC__                   /* host build of the header (tests/test_tmm_cpu.py) */
+#include <cmath>
+#endif
+
 struct cplx { double re, im; };
-__device__ __forceinline__ cplx cmk(double re, double im) { cplx z; z.re = re; z.im = im; return z; }
-__device__ __forceinline__ cplx cadd(cplx a, cplx b) { return cmk(a.re + b.re, a.im + b.im); }
-__device__ __forceinline__ cplx csub(cplx a, cplx b) { return cmk(a.re - b.re, a.im - b.im); }
-__device__ __forceinline__ cplx cneg(cplx a) { return cmk(-a.re, -a.im); }
-__device__ __forceinline__ cplx cmul(cplx a, cplx b) { return cmk(a.re * b.re - a.im * b.im, a.re * b.im + a.im * b.re); }
-__device__ __forceinline__ cplx cscale(double s, cplx a) { return cmk(s * a.re, s * a.im); }
-__device__ __forceinline__ cplx cdivc(cplx a, cplx b)
+TM_HD cplx cmk(double re, double im) { cplx z; z.re = re; z.im = im; return z; }
+TM_HD cplx cadd(cplx a, cplx b) { return cmk(a.re + b.re, a.im + b.im); }
+TM_HD cplx csub(cplx a, cplx b) { return cmk(a.re - b.re, a.im - b.im); }
+TM_HD cplx cneg(cplx a) { return cmk(-a.re, -a.im); }
+TM_HD cplx cmul(cplx a, cplx b) { return cmk(a.re * b.re - a.im * b.im, a.re * b.im + a.im * b.re); }
+TM_HD cplx cscale(double s, cplx a) { return cmk(s * a.re, s * a.im); }
+TM_HD cplx cdivc(cplx a, cplx b)
 {
   const double r = prcp(b.re * b.re + b.im * b.im);          // one reciprocal for both parts (<= 1 ulp each)
   return cmk((a.re * b.re + a.im * b.im) * r, (a.im * b.re - a.re * b.im) * r);
 }
-__device__ __forceinline__ cplx crdiv(double s, cplx b)          // real / complex
+TM_HD cplx crdiv(double s, cplx b)          // real / complex
 {
   const double r = prcp(b.re * b.re + b.im * b.im);
   return cmk((s * b.re) * r, (-s * b.im) * r);
 }
-__device__ __forceinline__ double cabs2(cplx a) { return a.re * a.re + a.im * a.im; }
-__device__ __forceinline__ cplx csqrtc(cplx z)                   // glibc csqrt, finite non-zero operands
+TM_HD double cabs2(cplx a) { return a.re * a.re + a.im * a.im; }
+TM_HD cplx csqrtc(cplx z)                   // glibc csqrt, finite non-zero operands
 {
   if (z.im == 0.0) return z.re < 0.0 ? cmk(0.0, copysign(sqrt(-z.re), z.im)) : cmk(fabs(sqrt(z.re)), copysign(0.0, z.im));
   const double d = psqrt(z.re * z.re + z.im * z.im);         // permittivities: no overflow to guard against
@@ -38,7 +42,7 @@ __device__ __forceinline__ cplx csqrtc(cplx z)                   // glibc csqrt,
   return cmk(r, copysign(s, z.im));
 }
 // exp(phi1) cos(phi2) + I exp(phi1) sin(phi2) with phi1 = creal(dx kl I) = -dx Im kl, phi2 = dx Re kl
-__device__ __forceinline__ cplx tmm_eiphi(double dx, cplx kl)
+TM_HD cplx tmm_eiphi(double dx, cplx kl)
 {
   const double phi1 = -(dx * kl.im), phi2 = dx * kl.re;
   double sn, cs;
@@ -54,7 +58,7 @@ struct TmmTables {                   // device pointers
 };
 
 // tmm_K1 (which = 0) / tmm_K2 (which = 1); (int) nu * 30 - 1 as written in the reference
-__device__ __forceinline__ double tmm_K(const TmmTables &t, double nu, int which)
+TM_HD double tmm_K(const TmmTables &t, double nu, int which)
 {
   if (nu < 1.0 / 30.0) return 1;
   if (nu < 50) {
@@ -72,13 +76,13 @@ __device__ __forceinline__ double tmm_K(const TmmTables &t, double nu, int which
 // tmm_get_epsilon (imd_tmm.c:503-570); `phase` = (int) EOS_phase_from_r_ti(Ni 26.9815 AMU, Ti [K]) from the caller.
 // Helpers fermi_E / fermi_T / omega_pl / r0 / bMin / bMax / coulomb_log / numet / numax / nupl are the file-level
 // ones of imd_ttm.c:2191-2308, written out; laser_active is 1 here (do_tmm has just set it).
-__device__ __forceinline__ double tmm_fermi_E(double ne)
+TM_HD double tmm_fermi_E(double ne)
 {
   return pdiv(TMC_HBAR * TMC_HBAR * ppow(3.0 * TMC_PI * TMC_PI * ne, 2.0 / 3.0) / 2.0, TMC_EMASS);
 }
 // the interband permittivity at the laser wavelength: table walk and linear interpolation of
 // tmm_get_epsilon (:524-527, :547), the same in every call of a run
-__device__ inline cplx tmm_eps_bb(const TmmTables &t, double lambda)
+TM_HD cplx tmm_eps_bb(const TmmTables &t, double lambda)
 {
   int il = 0, ir = 0;
   for (int id = 0; lambda * 1e6 > t.eps_bb[3 * id]; id++) { il = id; ir = id + 1; }
@@ -90,7 +94,7 @@ __device__ inline cplx tmm_eps_bb(const TmmTables &t, double lambda)
 }
 // epsilon_bb: tmm_eps_bb, or 0 where the phase table says 3, 4 or 5 (:549-552).  Divisions, roots, pow/log/exp
 // are the branch-free versions of ttm_math.cuh (<= 1-2 ulp), like in the wide-range models of do_FILLMESH.
-__device__ inline cplx tmm_get_epsilon(const TmmTables &t, double lambda, double Te, double Ti, double Z, double Ne,
+TM_HD cplx tmm_get_epsilon(const TmmTables &t, double lambda, double Te, double Ti, double Z, double Ne,
                                        cplx epsilon_bb)
 {
   Te *= 11604.52500617; Ti *= 11604.52500617;
@@ -124,7 +128,7 @@ __device__ inline cplx tmm_get_epsilon(const TmmTables &t, double lambda, double
 }
 
 // EE (imd_tmm.c:72-98): |Bplus e^{i k z delta} + Bminus e^{-i k z delta}|^2
-__device__ __forceinline__ double tmm_EE(double z, double delta, cplx kl, cplx Bplus, cplx Bminus)
+TM_HD double tmm_EE(double z, double delta, cplx kl, cplx Bplus, cplx Bminus)
 {
   const cplx e = tmm_eiphi(delta * z, kl);
   const cplx Ez = cadd(cmul(Bplus, e), cdivc(Bminus, e));
@@ -132,7 +136,7 @@ __device__ __forceinline__ double tmm_EE(double z, double delta, cplx kl, cplx B
 }
 
 // Runge5 (imd_tmm.c:37-69)
-__device__ inline double tmm_runge5(double delta, cplx kl, cplx Bplus, cplx Bminus)
+TM_HD double tmm_runge5(double delta, cplx kl, cplx Bplus, cplx Bminus)
 {
   double dx = 1, cur_xpos = 0, result = 0;
   const double errval = 1e-5;
@@ -151,7 +155,7 @@ __device__ inline double tmm_runge5(double delta, cplx kl, cplx Bplus, cplx Bmin
 }
 
 // tmpmat = Cinv * Pmat of one interface (imd_tmm.c:299-313): M = {m0, m1, m2, m3}, column-major like matmul
-__device__ __forceinline__ void tmm_interface(cplx e, cplx kl, cplx kr, cplx M[4])      // e = tmm_eiphi(dx, kl)
+TM_HD void tmm_interface(cplx e, cplx kl, cplx kr, cplx M[4])      // e = tmm_eiphi(dx, kl)
 {
   const cplx P0 = e, P2 = crdiv(1.0, e), P1 = e, P3 = cneg(P2);
   const cplx C0 = cmk(0.5, 0.0), C1 = cmk(0.5, 0.0);

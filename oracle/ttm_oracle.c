@@ -722,6 +722,35 @@ static int do_tmm_ref(orc_ttm *t)
   return 0;
 }
 
+/* probes for the host test of imd_b200/csrc/tmm.cuh (tests/test_tmm_cpu.py) */
+void orc_tmm_probe_epsilon(orc_ttm *t, double Te, double Ti, double Z, double Ne, double out2[2])
+{
+  const int la = t->laser_active;
+  t->laser_active = 1;                     /* do_tmm sets it before the permittivities are evaluated */
+  tmm_get_epsilon(t, t->p.lambda, Te, Ti, Z, Ne, &out2[0], &out2[1]);
+  t->laser_active = la;
+}
+double orc_tmm_probe_runge5(double delta, const double kl[2], const double bp[2], const double bm[2])
+{
+  return tmm_runge5(delta, kl[0] + I * kl[1], bp[0] + I * bp[1], bm[0] + I * bm[1]);
+}
+/* one interface: tmpmat = Cinv * Pmat (imd_tmm.c:299-313), out[8] = re/im of the four entries */
+void orc_tmm_probe_interface(double dx, const double kl_[2], const double kr_[2], double out[8])
+{
+  double complex kl = kl_[0] + I * kl_[1], kr = kr_[0] + I * kr_[1], Cinv[4], Pmat[4], M[4];
+  double phi1 = creal(dx * kl * I), phi2 = cimag(dx * kl * I);
+  double complex eiphi = exp(phi1) * cos(phi2) + I * exp(phi1) * sin(phi2);
+  Pmat[0] = eiphi; Pmat[2] = 1.0 / eiphi; Pmat[1] = eiphi; Pmat[3] = -Pmat[2];
+  Cinv[0] = 0.5; Cinv[2] = 0.5 * kl / kr; Cinv[1] = 0.5; Cinv[3] = -Cinv[2];
+  tmm_matmul(Cinv, Pmat, M);
+  for (int j = 0; j < 4; j++) { out[2 * j] = creal(M[j]); out[2 * j + 1] = cimag(M[j]); }
+}
+void orc_tmm_probe_csqrt(const double z[2], double out[2])
+{
+  double complex r = csqrt(z[0] + I * z[1]);
+  out[0] = creal(r); out[1] = cimag(r);
+}
+
 /* the analytic source that replaces do_tmm on both sides (oracle/ref_hooks_ttm.c) */
 static void do_source(orc_ttm *t)
 {
