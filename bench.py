@@ -4,10 +4,13 @@
     python bench.py --gpus 1 --steps K --warmup W            # our arm
     python bench.py --impl reference --gpus N --steps K ...   # the reference's CPU code
 
-A "step" is one MD step of the main-loop segment calc_forces -> move_atoms -> check_nblist
-(imd_main_3d.c:406,564,812) over the whole synthetic system, neighbour-list rebuilds
-included whenever check_nblist asks for them.  Workload at N=1: BASELINE.json configs[1],
-"Al fcc EAM2 2M-atom slab NVE on 1 B200" (80^3 cubic cells = 2 048 000 atoms, 300 K).
+A "step" is one MD step of the main-loop segment calc_forces -> calc_ttm -> move_atoms_ttm ->
+check_nblist (imd_main_3d.c:406,534,564,812) over the whole synthetic system, neighbour-list
+rebuilds included whenever check_nblist asks for them.  Default workload (the one BASELINE.json's
+metric is quoted on): N=1 is configs[2], "Al slab 4M atoms + TTM coupling on 1 B200" (film of
+100^3 cubic cells = 4 000 000 atoms, 1-D FD lattice along the laser axis, 250 sub-steps, pulse source);
+N>1 is configs[3]: the film grows with N (4 M atoms per GPU, 32 M on 8), x slabs over NCCL, non-reflecting
+rear boundary.  --workload nve gives configs[1] (Al 80^3 = 2 048 000 atoms NVE), --workload ttm3d configs[4].
 
 value : whole-job atom-steps/s with atoms resident in HBM (device-timed, CUDA events).
 e2e   : the same step driven through the C ABI with HOST buffers: every step uploads
@@ -41,12 +44,20 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-METRIC = "EAM+TTM atom-steps/s"
+METRIC = "EAM+TTM atom-steps/s"          # --workload ttm (default); --workload nve reports "EAM NVE atom-steps/s"
 UNIT = "atom-steps/s"
+
+
+def metric_name(args):
+    return METRIC if args.ttm else "EAM NVE atom-steps/s"
 N_H_AL = 39                 # half-list neighbours per atom, Al r_c 6.3 + margin 0.4
 REF_FAST = os.path.join(ROOT, "oracle", "_ref", "imd_ref_eam_nve_nbl_fast")
 REF_IEEE = os.path.join(ROOT, "oracle", "_ref", "imd_ref_eam_nve_nbl")
 REF_MPI = os.path.join(ROOT, "oracle", "_ref", "imd_ref_mpi_eam_nve_nbl_fast")
+REF_TTM = os.path.join(ROOT, "oracle", "_ref", "imd_ref_mpi_eam_ttm_fast")          # -DMPI -DTTM -DTTM1D -DTMM -DPDECAY
+REF_TTM_NRB = os.path.join(ROOT, "oracle", "_ref", "imd_ref_mpi_eam_ttm_nrb_fast")  # + -DNRB -DREFPOS
+VAC_CELLS = 10              # vacuum in front of and behind the film, in lattice constants
+FD_CELL = 16.0              # Angstrom: target width of an FD cell (ttmdimx = box_x / FD_CELL, rounded to the rank count)
 
 
 def measured_traffic(kernel, units):
@@ -157,21 +168,21 @@ def run_reference_sample(box_cells, steps, nproc, use_fast=True):
         shutil.rmtree(work, ignore_errors=True)
 
 
-def run_reference_mpi(cells_per_rank, steps, nproc):
-    """The reference's own MPI build (cpu_dim nproc 1 1, x slabs like the GPU decomposition) over
+def run_reference_mpi(global_cells, steps, cpu_dim):
+    """The reference's own MPI build (cpu_dim = x slabs like the GPU decomposition, or IMD's 3-D process grid) over
     oracle/shmpi; throughput from the reference's own main-loop timer (imd.c:387-392, MPI_Wtime)."""
     from imd_b200 import synth
     if not os.path.exists(REF_MPI):
         return None
     spec = synth.AL
+    nproc = cpu_dim[0] * cpu_dim[1] * cpu_dim[2]
     work = tempfile.mkdtemp(prefix="imdbench_mpi_")
     try:
         synth.make_eam_tables(spec, work)
         os.makedirs(os.path.join(work, "out"))
-        cx, cy, cz = cells_per_rank
-        synth.write_param_file(os.path.join(work, "run.param"), spec, (cx * nproc, cy, cz), steps, "out/run",
+        synth.write_param_file(os.path.join(work, "run.param"), spec, tuple(global_cells), steps, "out/run",
                                potdir=".", pbc=(1, 1, 1), starttemp=0.0258, nbl_margin=0.4, eng_int=0,
-                               cpu_dim=(nproc, 1, 1))
+                               cpu_dim=tuple(cpu_dim))
         env = dict(os.environ, SHMPI_NP=str(nproc), SHMPI_RING_MB="4")
         t0 = time.perf_counter()
         res = subprocess.run([REF_MPI, "-p", "run.param"], cwd=work, env=env, stdout=subprocess.PIPE,
@@ -183,26 +194,138 @@ def run_reference_mpi(cells_per_rank, steps, nproc):
             raise RuntimeError("reference MPI run failed:\n" + res.stdout[-1500:])
         tm, nsteps, natoms = float(m.group(1)), int(n.group(1)), int(n.group(2))
         return {"value": natoms * nsteps / tm, "natoms": natoms, "steps": nsteps, "nproc": nproc,
-                "main_loop_s": tm, "wall_s": wall, "binary": os.path.basename(REF_MPI), "mode": "mpi"}
+                "main_loop_s": tm, "wall_s": wall, "binary": os.path.basename(REF_MPI), "mode": "mpi",
+                "cpu_dim": list(cpu_dim)}
     finally:
         shutil.rmtree(work, ignore_errors=True)
 
 
-def reference_sample(cells, world, steps):
-    """The reference on the bench workload itself: global lattice (cells.x * world) x cells.y x cells.z,
-    MPI build on as many ranks as divide the x extent (>= 5 lattice cells = 20 A per rank, <= cores,
-    <= 40); concurrent serial runs of a 24^3 sample as the fallback."""
-    cores = max(1, host_cores())
-    gx = cells[0] * world
-    nproc = max([p for p in range(1, min(cores, 40) + 1) if gx % p == 0 and gx // p >= 5] or [1])
+def grid3(nproc, cells):
+    """IMD-style 3-D process grid for nproc ranks: the factorisation (px, py, pz) with px*py*pz = nproc that divides
+    the lattice and minimises the surface of a rank's sub-box (what imd's users pick by hand for cpu_dim)."""
+    best = None
+    for px in range(1, nproc + 1):
+        if nproc % px or cells[0] % px:
+            continue
+        for py in range(1, nproc // px + 1):
+            if (nproc // px) % py or cells[1] % py:
+                continue
+            pz = nproc // px // py
+            if cells[2] % pz:
+                continue
+            lx, ly, lz = cells[0] / px, cells[1] / py, cells[2] / pz
+            if min(lx, ly, lz) < 4:                      # >= 4 lattice constants = 16 A > one MD cell per rank
+                continue
+            surf = lx * ly + ly * lz + lx * lz
+            if best is None or surf < best[0]:
+                best = (surf, (px, py, pz))
+    return best[1] if best else None
+
+
+def film_geometry(cells, world):
+    """Global film of the EAM+TTM workload: (cells.x * world) x cells.y x cells.z lattice cells, VAC_CELLS of vacuum
+    in front and behind; ttmdimx ~ box_x / 16 A rounded to a multiple of 8 * world (so that the reference's
+    P = 2, 4, 8 ... ranks and the GPUs' x slabs all divide it)."""
+    from imd_b200 import synth
+    a = synth.AL.a
+    ncx = cells[0] * world
+    lx = (ncx + 2 * VAC_CELLS) * a
+    unit = 8 * world
+    gx = max(unit, int(round(lx / FD_CELL / unit)) * unit)
+    return ncx, lx, gx
+
+
+def run_reference_ttm(cells, world, steps, nproc, nrb, substeps):
+    """The reference's own EAM + TTM(1-D) MPI build (imd_ttm.c:75-156 per step, move_atoms_ttm) over oracle/shmpi on
+    the bench film: ensemble ttm, pbc 0 1 1, shiftx_front/rear vacuum, the same FD lattice, sub-step count and pulse
+    as the GPU arm (analytic Beer-Lambert source on both sides, ref_hooks_ttm.c).  TTM1D talks to ranks myid +- 1
+    (imd_ttm.c:884-939, 3290-3333): cpu_dim must be P 1 1, P >= 2."""
+    from imd_b200 import synth
+    binary = REF_TTM_NRB if nrb else REF_TTM
+    if not os.path.exists(binary):
+        return None
+    spec = synth.AL
+    ncx, lx, gx = film_geometry(cells, world)
+    work = tempfile.mkdtemp(prefix="imdbench_ttm_")
     try:
-        r = run_reference_mpi((gx // nproc, cells[1], cells[2]), steps, nproc) if nproc >= 2 else None
+        synth.make_eam_tables(spec, work)
+        synth.write_eos_files(synth.make_eos_tables(), work)
+        run = os.path.join(work, "w")
+        os.makedirs(os.path.join(run, "out"))
+        tp = bench_ttm_params(gx, substeps, False)
+        ex = tp.param_text() + "shiftx_front %.17g\nshiftx_rear %.17g\n" % (VAC_CELLS * spec.a, VAC_CELLS * spec.a)
+        if nrb:
+            ex += "nrb_alat %.17g\nnrb_eps 0.3\nnrb_k 1.2\n" % spec.a
+        synth.write_param_file(os.path.join(run, "run.param"), spec, (ncx, cells[1], cells[2]), steps, "out/run",
+                               potdir="..", pbc=(0, 1, 1), starttemp=0.0258, nbl_margin=0.4, eng_int=0, extra=ex,
+                               ensemble="ttm", cpu_dim=(nproc, 1, 1))
+        env = dict(os.environ, SHMPI_NP=str(nproc), SHMPI_RING_MB="4",
+                   IMD_SRC_MU="%.17g" % tp.src_mu, IMD_SRC_ABS="%.17g" % tp.src_abs)
+        env.pop("IMD_DUMP_DIR", None)
+        t0 = time.perf_counter()
+        res = subprocess.run([binary, "-p", "run.param"], cwd=run, env=env, stdout=subprocess.PIPE,
+                             stderr=subprocess.STDOUT, text=True, timeout=1500)
+        wall = time.perf_counter() - t0
+        m = re.search(r"([0-9.eE+-]+) seconds excluding setup time", res.stdout)
+        n = re.search(r"Did (\d+) steps with (\d+) atoms", res.stdout)
+        if res.returncode != 0 or not m or not n:
+            raise RuntimeError("reference TTM run failed:\n" + res.stdout[-1500:])
+        tm, nsteps, natoms = float(m.group(1)), int(n.group(1)), int(n.group(2))
+        return {"value": natoms * nsteps / tm, "natoms": natoms, "steps": nsteps, "nproc": nproc,
+                "main_loop_s": tm, "wall_s": wall, "binary": os.path.basename(binary), "mode": "mpi",
+                "cpu_dim": [nproc, 1, 1], "ttmdimx": gx}
+    finally:
+        shutil.rmtree(work, ignore_errors=True)
+
+
+def bench_ttm_params(gx, substeps, tmm):
+    from imd_b200 import synth
+    return synth.TtmParams(ttmdimx=gx, fd_n_timesteps=substeps, fd_min_atoms=100, vlatdim=30, vlatbuffer=8, I0=5.0e15,
+                           laser_t_0=100e-15, laser_sigma_t=42.5e-15, use_tmm=1 if tmm else 0, tmm_threshold=4.0)
+
+
+def reference_sample(args, world, steps):
+    """The reference on the bench workload itself, with all the host cores it can use.
+    EAM+TTM film: the -DTTM MPI build on P x-slab ranks, P = the largest divisor of ttmdimx <= cores (TTM1D needs
+    cpu_dim P 1 1).  NVE slab: the -DNVE MPI build, x slabs (cpu_dim P 1 1) AND IMD's 3-D process grid, the faster
+    of the two is reported; concurrent serial runs of a 24^3 sample as the fallback."""
+    cores = max(1, host_cores())
+    cells = args.cells
+    if args.ttm:
+        ncx, lx, gx = film_geometry(cells, world)
+        nproc = max([p for p in range(2, min(cores, 64) + 1) if gx % p == 0] or [2])
+        r = run_reference_ttm(cells, world, steps, nproc, args.nrb, args.ttm_substeps)
         if r:
-            r["sample"] = ("the reference's MPI build (%s, author's flags) over oracle/shmpi, %d ranks (cpu_dim %d 1 1) on %d "
-                           "host cores, Al fcc %dx%dx%d cells = %d atoms, %d NVE steps, 300 K (main loop %.1f s, wall %.1f s)"
-                           % (r["binary"], nproc, nproc, cores, gx, cells[1], cells[2], r["natoms"], r["steps"],
-                              r["main_loop_s"], r["wall_s"]))
-            return r
+            r["sample"] = ("the reference's own EAM+TTM MPI build (%s: -DMPI -DNBL -DEAM2 -DTTM -DTTM1D -DTMM -DPDECAY%s, author's "
+                           "flags -O3 -mavx2 -ffast-math) over oracle/shmpi, %d ranks (cpu_dim %d 1 1, the only layout TTM1D "
+                           "supports) on %d host cores, Al film %dx%dx%d cells = %d atoms, ttmdimx %d, fd_n_timesteps %d, "
+                           "%d steps (main loop %.1f s, wall %.1f s)"
+                           % (r["binary"], " -DNRB -DREFPOS" if args.nrb else "", nproc, nproc, cores, ncx, cells[1], cells[2],
+                              r["natoms"], gx, args.ttm_substeps, r["steps"], r["main_loop_s"], r["wall_s"]))
+        return r
+    gx = cells[0] * world
+    gcells = (gx, cells[1], cells[2])
+    nproc = max([p for p in range(1, min(cores, 64) + 1) if gx % p == 0 and gx // p >= 4] or [1])
+    tried = []
+    try:
+        cands = [(nproc, 1, 1)] if nproc >= 2 else []
+        n3 = max([p for p in range(2, min(cores, 64) + 1) if grid3(p, gcells)] or [0])
+        if n3 >= 2 and grid3(n3, gcells) not in cands:
+            cands.append(grid3(n3, gcells))
+        best = None
+        for cd in cands:
+            r = run_reference_mpi(gcells, steps, cd)
+            if r:
+                tried.append("cpu_dim %d %d %d: %.3g atom-steps/s" % (cd[0], cd[1], cd[2], r["value"]))
+                if best is None or r["value"] > best["value"]:
+                    best = r
+        if best:
+            cd = best["cpu_dim"]
+            best["sample"] = ("the reference's MPI build (%s, author's flags) over oracle/shmpi on %d host cores, Al fcc %dx%dx%d "
+                              "cells = %d atoms, %d NVE steps, 300 K; tried %s; reported cpu_dim %d %d %d = %d ranks "
+                              "(main loop %.1f s)" % (best["binary"], cores, gx, cells[1], cells[2], best["natoms"], best["steps"],
+                                                      "; ".join(tried), cd[0], cd[1], cd[2], best["nproc"], best["main_loop_s"]))
+            return best
     except Exception as ex:                               # fall through to the serial form
         sys.stderr.write("bench: MPI reference failed (%s); using concurrent serial runs\n" % ex)
     r = run_reference_sample((24, 24, 24), steps, cores)
@@ -230,8 +353,8 @@ def reference_arm(args, rank, world):
     if rank != 0:
         return 0
     steps = reference_steps(args.cells, max(1, args.gpus), args.steps + args.warmup)
-    r = reference_sample(args.cells, max(1, args.gpus), steps)
-    base = {"metric": METRIC, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus,
+    r = reference_sample(args, max(1, args.gpus), steps)
+    base = {"metric": metric_name(args), "unit": UNIT, "impl": "reference", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": workload_config(args)}
@@ -255,12 +378,13 @@ def workload_config(args):
     if getattr(args, "ttm", False):
         w = ("Al fcc EAM2 + 1-D TTM film (calc_forces, calc_ttm, move_atoms_ttm), %dx%dx%d cubic cells = %d atoms per "
              "GPU, vacuum 10 a front and rear, pbc 0 1 1, 300 K, timestep 0.1, nbl_margin 0.4, FD cell ~16 A, "
-             "fd_n_timesteps %d (BASELINE.json configs[2] shape)" % (c[0], c[1], c[2], n, args.ttm_substeps))
+             "fd_n_timesteps %d, 100 fs pulse source (BASELINE.json configs[%d])"
+             % (c[0], c[1], c[2], n, args.ttm_substeps, 2 if args.gpus <= 1 else 3))
         if getattr(args, "tmm", False):
             w += ", laser source by do_tmm (transfer-matrix Helmholtz solver per sub-step, synthetic eps_bb/K12 tables)"
         if getattr(args, "nrb", False):
             w += (", non-reflecting rear boundary (nrb_forces on the last atomic layer, nrb_k 1.2; "
-                  "BASELINE.json configs[3] shape)")
+                  "%d atoms in all)" % (n * max(1, args.gpus)))
     else:
         w = ("Al fcc EAM2 NVE slab, %dx%dx%d cubic cells = %d atoms per GPU, 300 K, timestep 0.1 (1.018 fs), "
              "nbl_margin 0.4 (BASELINE.json configs[1])" % (c[0], c[1], c[2], n))
@@ -280,7 +404,7 @@ def build_system(cells, rank=0, world=1, ttm=False):
     spec = synth.AL
     a = spec.a
     ncx = cells[0] * world
-    vac = 10 * a if ttm else 0.0
+    vac = VAC_CELLS * a if ttm else 0.0
     lx = ncx * a + 2 * vac
     lo, hi = rank * lx / world, (rank + 1) * lx / world
     i0 = max(0, int(np.floor((lo - vac) / a)) - 1)
@@ -300,8 +424,8 @@ def rear_boundary_state(cells, world):
     spec = synth.AL
     ncx = cells[0] * world
     pos, box = synth.fcc_lattice((1, cells[1], cells[2]), spec.a)
-    pos[:, 0] += (ncx - 1) * spec.a + 10 * spec.a
-    box[0, 0] = ncx * spec.a + 20 * spec.a
+    pos[:, 0] += (ncx - 1) * spec.a + VAC_CELLS * spec.a
+    box[0, 0] = ncx * spec.a + 2 * VAC_CELLS * spec.a
     ids = (np.arange(pos.shape[0], dtype=np.int64) + 4 * (ncx - 1) * cells[1] * cells[2] + 1).astype(np.int32)
     return nrb.init_nrb(pos, ids, box, (0, 1, 1), spec.a, 0.3)
 
@@ -342,10 +466,8 @@ def our_arm(args, rank, local_rank, world):
     ctx = imd.ctx
     if args.ttm:
         eos = synth.make_eos_tables()          # diag = None: all rectangles split the same way
-        gx = max(world, int(box[0, 0] / 16.0) // world * world)
-        tp = synth.TtmParams(ttmdimx=gx, fd_n_timesteps=args.ttm_substeps, fd_min_atoms=100, vlatdim=30,
-                             vlatbuffer=8, I0=5.0e15, laser_t_0=100e-15, laser_sigma_t=42.5e-15,
-                             use_tmm=1 if args.tmm else 0, tmm_threshold=4.0)
+        _, _, gx = film_geometry(args.cells, world)
+        tp = bench_ttm_params(gx, args.ttm_substeps, args.tmm)
         imd.init_ttm(tp, eos, world)
     if args.nrb:
         st = rear_boundary_state(args.cells, world)
@@ -429,21 +551,33 @@ def our_arm(args, rank, local_rank, world):
     if rank == 0:
         phases = {k: {"ms_total": ms_ph[k], "launches": ln_ph[k]} for k in ms_ph if ln_ph[k]}
         p1_ms = ms_ph["eam_pass1"] / max(1, ln_ph["eam_pass1"])
-        alg_bytes = (64 + 4 * N_H_AL) * natoms
+        p2_ms = ms_ph["eam_pass2"] / max(1, ln_ph["eam_pass2"])
+        n_loc = ctx.n                                  # atoms this rank owns (= natoms on one GPU)
+        alg_bytes = (64 + 4 * N_H_AL) * n_loc          # SURVEY 8d, pass 1: 64 + 4 N_h bytes per atom
+        alg_flops = 2 * N_H_AL * 75 * n_loc            # ~75 FP64 flops per pair evaluation in pass 1, both sides
         peak, peak_src = measured_peak_gbs()
         achieved = alg_bytes / (p1_ms * 1e-3) / 1e9
-        traffic, traffic_src = measured_traffic("k_eam_pass1", natoms)
-        roofline = {"kernel": "k_eam_pass1_fused", "bound": "hbm", "achieved": achieved, "peak": peak,
+        fp64_peak = ctx.probe_fp64()
+        fp64_ach = alg_flops / (p1_ms * 1e-3) / 1e9
+        traffic, traffic_src = measured_traffic("k_eam_pass1", n_loc)
+        roofline = {"kernel": "k_eam_pass1_fused", "bound": "l1", "achieved": achieved, "peak": peak,
                     "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                     "peak_source": peak_src, "alg_bytes_per_launch": alg_bytes, "ms_per_launch": p1_ms,
-                    "note": "not HBM-bound: L1 data pipe 92 % busy (per pair one random 48-byte table row from shared "
-                            "memory, 46 % of those wavefronts bank conflicts, and one 32-byte gather), FP64 pipe 35 %, "
-                            "DRAM 12 % (profiles/r01g_full_ncu.txt, ablations in profiles/r01g_eam_variants.txt)"}
+                    "fp64": {"achieved": fp64_ach, "peak": fp64_peak, "unit": "GFLOP/s", "frac": fp64_ach / fp64_peak,
+                             "alg_flops_per_launch": alg_flops,
+                             "peak_source": "measured in this run (imdcu_probe_fp64: independent DFMA chains on every SM)"},
+                    "pass2": {"kernel": "k_eam_pass2", "ms_per_launch": p2_ms,
+                              "achieved": (80 + 4 * N_H_AL) * n_loc / (p2_ms * 1e-3) / 1e9,
+                              "frac": (80 + 4 * N_H_AL) * n_loc / (p2_ms * 1e-3) / 1e9 / peak},
+                    "note": "binding unit by ncu: the L1 data pipe (l1tex__data_pipe_lsu_wavefronts ~90 % of peak: per pair one "
+                            "random 48-byte table row from shared memory and one 32-byte gather); HBM and FP64 fractions are "
+                            "reported against their measured peaks, the north star's >= 0.60 of HBM is NOT met by the force "
+                            "kernels (profiles/r02_*.txt, DESIGN.md section 3)"}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
-            r = reference_sample(args.cells, 1, reference_steps(args.cells, 1, 30))
+            r = reference_sample(args, 1, reference_steps(args.cells, 1, 30))
             if r:
                 cpu = {"value": r["value"], "unit": UNIT, "cores": r["nproc"], "kind": "reference",
                        "sample": r["sample"]}
@@ -451,7 +585,7 @@ def our_arm(args, rank, local_rank, world):
             cpu = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "failed: %s" % ex}
 
     if rank == 0:
-        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        line = {"metric": metric_name(args), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": workload_config(args), "clocks": clocks,
@@ -643,21 +777,35 @@ def main():
     ap.add_argument("--steps", type=int, default=40)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--cells", type=int, nargs=3, default=[80, 80, 80], help="cubic fcc cells per GPU")
+    ap.add_argument("--cells", type=int, nargs=3, default=None,
+                    help="cubic fcc cells per GPU (default 100 100 100 for the EAM+TTM film, 80 80 80 for --workload nve)")
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--profile-steps", type=int, default=5)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--ttm", action="store_true", help="EAM + TTM step (BASELINE.json configs[2])")
+    ap.add_argument("--ttm", action="store_true", help="same as --workload ttm (kept for older command lines)")
     ap.add_argument("--ttm-substeps", type=int, default=250, help="fd_n_timesteps (manual example: 250)")
     ap.add_argument("--tmm", action="store_true",
                     help="with --ttm: the reference's transfer-matrix laser source (do_tmm) instead of the analytic one")
     ap.add_argument("--nrb", action="store_true",
-                    help="with --ttm: non-reflecting rear boundary (BASELINE.json configs[3])")
-    ap.add_argument("--workload", default="md", choices=["md", "ttm3d"],
-                    help="md: EAM(+TTM) atom-steps/s (headline); ttm3d: standalone 3-D TTM sweep (configs[4])")
+                    help="EAM+TTM film: non-reflecting rear boundary (default on several GPUs = BASELINE.json configs[3])")
+    ap.add_argument("--no-nrb", action="store_true", help="EAM+TTM film on several GPUs without the NRB")
+    ap.add_argument("--workload", default="ttm", choices=["ttm", "nve", "md", "ttm3d"],
+                    help="ttm (default): EAM+TTM film, the workload BASELINE.json's metric names (configs[2] on 1 GPU, "
+                         "configs[3] on several); nve: Al NVE slab (configs[1]); md: nve unless --ttm is given; "
+                         "ttm3d: standalone 3-D TTM sweep (configs[4])")
     ap.add_argument("--grid", type=int, nargs=3, default=[512, 512, 512], help="FD cells for --workload ttm3d")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.workload == "ttm":
+        args.ttm = True
+    elif args.workload == "nve":
+        args.ttm = False
+    if args.cells is None:
+        args.cells = [100, 100, 100] if args.ttm else [80, 80, 80]
+    if args.ttm and args.gpus > 1 and not args.no_nrb:
+        args.nrb = True
+    if not args.ttm:
+        args.nrb = args.tmm = False
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -69,6 +69,7 @@ def load():
         "imdcu_set_table2": (C.c_int, [vp, C.c_int, c_dp]),
         "imdcu_set_params": (C.c_int, [vp, C.c_int, C.c_double, C.c_int, c_dp]),
         "imdcu_set_pdecay": (C.c_int, [vp, C.c_int, C.c_double, C.c_double, C.c_double]),
+        "imdcu_set_tuning": (C.c_int, [vp, C.c_char_p, C.c_int]),
         "imdcu_upload_atoms": (C.c_int, [vp, C.c_int64, c_ip, c_ip, c_ip, c_dp, c_dp, c_dp]),
         "imdcu_num_atoms": (C.c_int64, [vp]),
         "imdcu_update_atoms": (C.c_int, [vp, c_dp, c_dp]),
@@ -95,12 +96,14 @@ def load():
         "imdcu_get_cell_grid": (C.c_int, [vp, c_ip, c_dp]),
         "imdcu_get_nblist_pairs": (C.c_int, [vp, c_lp, c_ip]),
         "imdcu_nbl_count": (C.c_int, [vp]),
+        "imdcu_short_distance": (C.c_int, [vp]),
         "imdcu_invalidate_nblist": (C.c_int, [vp]),
         "imdcu_launch_count": (C.c_int64, [vp]),
         "imdcu_set_profiling": (C.c_int, [vp, C.c_int]),
         "imdcu_get_phase_times": (C.c_int, [vp, c_dp, c_lp]),
         "imdcu_stream": (vp, [vp]),
         "imdcu_synchronize": (C.c_int, [vp]),
+        "imdcu_probe_fp64": (C.c_int, [vp, c_dp]),
         "imdcu_eval_table": (C.c_int, [vp, C.c_int, C.c_int, C.c_int64, c_dp, c_dp, c_dp]),
         "imdcu_eval_ttm_math": (C.c_int, [vp, C.c_int, C.c_int64, c_dp, c_dp, c_dp]),
     }
@@ -191,6 +194,11 @@ class Context:
 
     def set_pdecay(self, enabled, xipdecay=0.0, ramp_start=0.0, ramp_end=1.0):
         self._ck(self.L.imdcu_set_pdecay(self.h, int(enabled), xipdecay, ramp_start, ramp_end))
+
+    def set_tuning(self, **knobs):
+        """imdcu_set_tuning: lpa=0|1|2|4|8, fused_table=0|1, ttm_overlap=0|1, ..."""
+        for k, v in knobs.items():
+            self._ck(self.L.imdcu_set_tuning(self.h, k.encode(), int(v)))
 
     def set_nrb(self, nrb_k, ids, bnd, nrbi, refpos, startup_images=False):
         """imdcu_set_nrb: entries for the boundary atoms and their listed neighbours (ids empty: off)."""
@@ -362,6 +370,13 @@ class Context:
     def nbl_count(self):
         return int(self.L.imdcu_nbl_count(self.h))
 
+    def short_distance(self):
+        """True if a table was evaluated below its first argument since the last call (is_short)."""
+        rc = self.L.imdcu_short_distance(self.h)
+        if rc < 0:
+            self._ck(rc)
+        return rc > 0
+
     def invalidate_nblist(self):
         self._ck(self.L.imdcu_invalidate_nblist(self.h))
 
@@ -383,6 +398,12 @@ class Context:
 
     def synchronize(self):
         self._ck(self.L.imdcu_synchronize(self.h))
+
+    def probe_fp64(self):
+        """measured FP64-FMA rate of this GPU in GFLOP/s"""
+        v = C.c_double(0.0)
+        self._ck(self.L.imdcu_probe_fp64(self.h, C.byref(v)))
+        return v.value
 
     def eval_table(self, which, arg, col=0):
         arg = np.ascontiguousarray(arg, np.float64)

@@ -15,10 +15,31 @@ static int check_ready(imdcu_ctx *c)
   return IMDCU_OK;
 }
 
+// Leaving a hot-path entry point with an error: work forked to the second stream is joined, and on several
+// GPUs a failure the other ranks do not know about aborts the communicator (their pending collectives then
+// fail instead of hanging; multi.cu).
+static int leave(imdcu_ctx *c, int rc)
+{
+  if (rc == IMDCU_OK) return rc;
+  const std::string msg = c->err;
+  if (c->ttm.forked) { cudaStreamSynchronize(c->ttm.stream2); c->ttm.forked = false; }
+  c->fuse_ttm_steps = -1;
+  imdcu_multi_abort(c);
+  c->err = msg;
+  return rc;
+}
+
+static int calc_forces_impl(imdcu_ctx *c, int steps, double out8[8]);
+
 // calc_forces (imd_forces_nbl.c:295-1054)
 extern "C" int imdcu_calc_forces(imdcu_ctx *c, int steps, double out8[8])
 {
   RET_IF(check_ready(c));
+  return leave(c, calc_forces_impl(c, steps, out8));
+}
+
+static int calc_forces_impl(imdcu_ctx *c, int steps, double out8[8])
+{
   if (!c->have_valid_nbl) {
     RET_IF(imdcu_rebuild_cells(c));              // fix_cells (:304)
     RET_IF(imdcu_refresh_ghosts(c, true));       // send_cells(copy_cell) (:311)
@@ -37,65 +58,89 @@ extern "C" int imdcu_calc_forces(imdcu_ctx *c, int steps, double out8[8])
 extern "C" int imdcu_move_atoms_nve(imdcu_ctx *c, double out8[8], int *have_valid_nbl)
 {
   RET_IF(check_ready(c));
-  return imdcu_integrate_nve(c, out8, have_valid_nbl);
+  return leave(c, imdcu_integrate_nve(c, out8, have_valid_nbl));
 }
 
 // main-loop segment (imd_main_3d.c:151-916 restricted to the hot calls)
-extern "C" int imdcu_run_nve(imdcu_ctx *c, int first_step, int nsteps, double *energies)
+static int run_nve_impl(imdcu_ctx *c, int first_step, int nsteps, double *energies)
 {
-  RET_IF(check_ready(c));
   double f8[8], m8[8];
   int valid = 0;
   for (int s = 0; s < nsteps; s++) {
-    RET_IF(imdcu_calc_forces(c, first_step + s, energies ? f8 : nullptr));
+    RET_IF(calc_forces_impl(c, first_step + s, energies ? f8 : nullptr));
     RET_IF(imdcu_integrate_nve(c, m8, &valid));
     if (energies) { energies[2 * s] = f8[0]; energies[2 * s + 1] = m8[0]; }
   }
   return IMDCU_OK;
 }
 
+extern "C" int imdcu_run_nve(imdcu_ctx *c, int first_step, int nsteps, double *energies)
+{
+  RET_IF(check_ready(c));
+  return leave(c, run_nve_impl(c, first_step, nsteps, energies));
+}
+
 // calc_ttm (imd_main_3d.c:534 -> imd_ttm.c:75)
 extern "C" int imdcu_calc_ttm(imdcu_ctx *c, int steps, double out16[16])
 {
   RET_IF(check_ready(c));
-  return imdcu_ttm_step(c, steps, out16);
+  return leave(c, imdcu_ttm_step(c, steps, out16));
 }
 
 // move_atoms_ttm + check_nblist (imd_main_3d.c:564, :812)
 extern "C" int imdcu_move_atoms_ttm(imdcu_ctx *c, double out8[8], int *have_valid_nbl)
 {
   RET_IF(check_ready(c));
-  return imdcu_integrate_ttm(c, out8, have_valid_nbl);
+  return leave(c, imdcu_integrate_ttm(c, out8, have_valid_nbl));
 }
 
 // main-loop segment with the TTM (imd_main_3d.c:406,534,564,812)
+static int run_ttm_impl(imdcu_ctx *c, int first_step, int nsteps, double *energies);
+
 extern "C" int imdcu_run_ttm(imdcu_ctx *c, int first_step, int nsteps, double *energies)
 {
   RET_IF(check_ready(c));
+  return leave(c, run_ttm_impl(c, first_step, nsteps, energies));
+}
+
+static int run_ttm_impl(imdcu_ctx *c, int first_step, int nsteps, double *energies)
+{
   double f8[8], m8[8], t16[16];
   int valid = 0;
   if (!c->ttm.inited) return c->fail(IMDCU_EINVAL, "imdcu_ttm_init has not been called");
   // calc_ttm runs between the two EAM passes and its lattice kernel beside pass 2 (same inputs and
   // results as the sequential calc_forces; calc_ttm; only the schedule differs).  With per-phase
   // profiling on, the sequential order is kept so that the phase times stay separable.
-  static const bool no_overlap = [] { const char *e = getenv("IMDCU_TTM_OVERLAP"); return e && e[0] == '0'; }();
-  const bool fuse = !c->profiling && !no_overlap;
+  const bool fuse = !c->profiling && c->tune.ttm_overlap;
   for (int s = 0; s < nsteps; s++) {
     double *t_out = (s == nsteps - 1) ? t16 : nullptr;                    // errors surface at the end
     if (fuse) {
       c->fuse_ttm_steps = first_step + s;
-      const int rc = imdcu_calc_forces(c, first_step + s, energies ? f8 : nullptr);
+      const int rc = calc_forces_impl(c, first_step + s, energies ? f8 : nullptr);
       c->fuse_ttm_steps = -1;
       RET_IF(rc);
       RET_IF(imdcu_ttm_join(c, t_out));
     } else {
-      RET_IF(imdcu_calc_forces(c, first_step + s, energies ? f8 : nullptr));
+      RET_IF(calc_forces_impl(c, first_step + s, energies ? f8 : nullptr));
       RET_IF(imdcu_ttm_step(c, first_step + s, t_out));
     }
     RET_IF(imdcu_integrate_ttm(c, m8, &valid));
     if (energies) { energies[2 * s] = f8[0]; energies[2 * s + 1] = m8[0]; }
   }
   return IMDCU_OK;
+}
+
+// is_short of the EAM passes since the last call (the reference's "short distance" warning,
+// imd_forces_nbl.c:673,992); reads the device flags and clears the count
+extern "C" int imdcu_short_distance(imdcu_ctx *c)
+{
+  if (!c) return IMDCU_EINVAL;
+  cudaSetDevice(c->device);
+  const int rc = imdcu_check_flags(c);
+  if (rc != IMDCU_OK) return rc;
+  const int w = c->short_warn;
+  c->short_warn = 0;
+  return w;
 }
 
 extern "C" int imdcu_nbl_count(const imdcu_ctx *c) { return c ? c->nbl_count : -1; }
@@ -169,5 +214,40 @@ extern "C" int imdcu_eval_table(imdcu_ctx *c, int which, int col, int64_t n, con
   CU_CHECK(c, cudaMemcpyAsync(grad, d + 2 * n, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   CU_CHECK(c, cudaStreamSynchronize(c->stream));
   cudaFree(d);
+  return IMDCU_OK;
+}
+
+// ----------------------------------------------------------------------------- FP64 peak probe
+// Dependent-free DFMA chains, eight per thread, every SM full: the FP64-FMA rate this GPU sustains, the
+// denominator of the FP64 fraction bench.py reports for the EAM passes (SURVEY 8d asks for HBM AND FP64).
+__global__ void __launch_bounds__(1024)
+k_fp64_probe(double *out, int iters, double a, double b)
+{
+  double x0 = threadIdx.x * 1e-3, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+  for (int i = 0; i < iters; i++) {
+    x0 = fma(x0, a, b); x1 = fma(x1, a, b); x2 = fma(x2, a, b); x3 = fma(x3, a, b);
+    x4 = fma(x4, a, b); x5 = fma(x5, a, b); x6 = fma(x6, a, b); x7 = fma(x7, a, b);
+  }
+  const double s = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+  if (s == 12345.678) out[0] = s;                       // keeps the chains alive, never true for these inputs
+}
+
+extern "C" int imdcu_probe_fp64(imdcu_ctx *c, double *gflops)
+{
+  if (!c || !gflops) return IMDCU_EINVAL;
+  cudaSetDevice(c->device);
+  const int iters = 1 << 15, grid = c->num_sms * 2, block = 1024;
+  double best = 0.0;
+  for (int rep = 0; rep < 4; rep++) {
+    CU_CHECK(c, cudaEventRecord(c->ev0, c->stream));
+    k_fp64_probe<<<grid, block, 0, c->stream>>>(c->d_results + 24, iters, 0.999999, 1e-7);
+    c->count_launch();
+    CU_CHECK(c, cudaEventRecord(c->ev1, c->stream));
+    CU_CHECK(c, cudaEventSynchronize(c->ev1));
+    float ms = 0; CU_CHECK(c, cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    const double gf = 2.0 * 8.0 * (double) iters * grid * block / (ms * 1e-3) / 1e9;
+    if (rep > 0 && gf > best) best = gf;
+  }
+  *gflops = best;
   return IMDCU_OK;
 }

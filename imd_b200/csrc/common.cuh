@@ -202,6 +202,8 @@ struct imdcu_ctx {
   bool         up_pending = false;
   bool         force_sums_pending = false;   // multi-GPU: Epot/virial sums ride on the integrator's all-reduce
   std::string  err;
+  bool         err_agreed = false;           // multi-GPU: every rank knows about the error being returned (multi.cu)
+  int          short_warn = 0;               // is_short of the EAM passes seen since the last imdcu_short_distance()
   int          num_sms = 148;
   size_t       smem_optin = 0;
 
@@ -218,6 +220,14 @@ struct imdcu_ctx {
   size_t ttm_isolate_smem = 0;               // dynamic smem request that keeps k_eam_pass2 CTAs off that SM
   int    fuse_ttm_steps = -1;                // >= 0: imdcu_eam_forces forks calc_ttm(steps) between its passes
   bool   box_set = false, params_set = false;
+  // kernel-selection knobs (imdcu_set_tuning; the IMDCU_* environment variables give the defaults at create)
+  struct Tune {
+    int lpa = 0;                             // lanes per atom of the EAM passes: 0 = by system size, 1/2/4/8
+    int fused_table = 1;                     // k_eam_pass1_fused when the pair and rho tables share their grid
+    int ttm_overlap = 1;                     // imdcu_run_ttm: lattice kernel beside EAM pass 2
+    int ttm_lat_smem = 1;                    // k_ttm_grid keeps the lattices in shared memory
+    int ttm3d_tiled = 0;                     // 3-D sweep: 2.5-D tiled kernel instead of the direct one
+  } tune;
 
   Geom   geom;
   DevTable tab[3];
@@ -344,6 +354,8 @@ int  imdcu_multi_ghost_build(imdcu_ctx *ctx);                // x-stage ghost at
 int  imdcu_multi_ghost_refresh(imdcu_ctx *ctx);              // x-stage positions / F' every step
 int  imdcu_multi_allreduce(imdcu_ctx *ctx, void *buf, int count, int kind);   // kind 0 sum f64, 1 max f64, 2 sum i32
 void imdcu_multi_release(imdcu_ctx *ctx);
+int  imdcu_multi_agree(imdcu_ctx *ctx, int local_rc);        // rank-local error -> the same return on every rank
+void imdcu_multi_abort(imdcu_ctx *ctx);                      // un-agreed failure: abort the communicator
 __device__ __host__ inline int imdcu_combine_code(int pc, int code)
 {
   return (pc % 3 - 1 + code % 3 - 1 + 1) + 3 * ((pc / 3) % 3 - 1 + (code / 3) % 3 - 1 + 1) + 9 * (pc / 9 - 1 + code / 9 - 1 + 1);

@@ -46,6 +46,15 @@ extern "C" int imdcu_create(imdcu_ctx **out, int device)
     size_t want = prop.sharedMemPerMultiprocessor > 18 * 1024 ? prop.sharedMemPerMultiprocessor - 18 * 1024 : 0;
     c->ttm_isolate_smem = want < c->smem_optin ? want : c->smem_optin;
   }
+  {
+    auto env_int = [](const char *name, int dflt) { const char *e = getenv(name); return e && *e ? atoi(e) : dflt; };
+    c->tune.lpa = env_int("IMDCU_LPA", 0);
+    c->tune.fused_table = env_int("IMDCU_FUSED_TABLE", 1);
+    c->tune.ttm_overlap = env_int("IMDCU_TTM_OVERLAP", 1);
+    c->tune.ttm_lat_smem = env_int("IMDCU_TTM_LAT_SMEM", 1);
+    const char *e3 = getenv("IMDCU_TTM3D");
+    c->tune.ttm3d_tiled = e3 && !strcmp(e3, "tiled");
+  }
   CREATE_CHECK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   CREATE_CHECK(cudaStreamCreateWithFlags(&c->up_stream, cudaStreamNonBlocking));
   CREATE_CHECK(cudaEventCreateWithFlags(&c->ev_up, cudaEventDisableTiming));
@@ -193,9 +202,10 @@ extern "C" int imdcu_set_table2(imdcu_ctx *c, int which, const double *table2)
 // single-column and tabulated on the same grid (k_eam_pass1_fused); nullptr otherwise
 const double *imdcu_fused_table(imdcu_ctx *c)
 {
+  if (!c->tune.fused_table) return nullptr;
   if (c->fused_state != 0) return c->fused_state > 0 ? c->fused_coef : nullptr;
   c->fused_state = -1;
-  static const bool off = [] { const char *e = getenv("IMDCU_FUSED_TABLE"); return e && e[0] == '0'; }();
+  const bool off = !c->tune.fused_table;
   const DevTable &p = c->tab[IMDCU_TAB_PAIR], &r = c->tab[IMDCU_TAB_RHO];
   if (off || !p.set || !r.set || p.ncols != 1 || r.ncols != 1 || p.nrows != r.nrows) return nullptr;
   if (p.h_begin[0] != r.h_begin[0] || p.h_end[0] != r.h_end[0] || p.h_invstep[0] != r.h_invstep[0] ||
@@ -211,6 +221,22 @@ const double *imdcu_fused_table(imdcu_ctx *c)
   if (imdcu_h2d(c, c->fused_coef, f.data(), f.size() * sizeof(double)) != cudaSuccess) return nullptr;
   c->fused_state = 1;
   return c->fused_coef;
+}
+
+// ----------------------------------------------------------------------------- tuning
+extern "C" int imdcu_set_tuning(imdcu_ctx *c, const char *key, int value)
+{
+  if (!c || !key) return IMDCU_EINVAL;
+  const std::string k(key);
+  if (k == "lpa") {
+    if (value != 0 && value != 1 && value != 2 && value != 4 && value != 8) return c->fail(IMDCU_EINVAL, "lpa: 0, 1, 2, 4 or 8");
+    c->tune.lpa = value;
+  } else if (k == "fused_table") c->tune.fused_table = value != 0;
+  else if (k == "ttm_overlap") c->tune.ttm_overlap = value != 0;
+  else if (k == "ttm_lat_smem") c->tune.ttm_lat_smem = value != 0;
+  else if (k == "ttm3d_tiled") c->tune.ttm3d_tiled = value != 0;
+  else return c->fail(IMDCU_EINVAL, "imdcu_set_tuning: unknown key " + k);
+  return IMDCU_OK;
 }
 
 // ----------------------------------------------------------------------------- params

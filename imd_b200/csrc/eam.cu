@@ -516,8 +516,8 @@ int imdcu_eam_forces(imdcu_ctx *c, double out8[8])
   if (a.n > 0) {
     // lanes per atom: keep at least ~2 resident waves of threads on the machine
     const int64_t want = (int64_t) c->num_sms * 2048;
-    int rc, force_lpa = 0;
-    if (const char *e = getenv("IMDCU_LPA")) force_lpa = atoi(e);      // tuning knob
+    int rc;
+    const int force_lpa = c->tune.lpa;                                 // imdcu_set_tuning("lpa")
     if (force_lpa == 1) rc = run_lpa<1>(c, a);
     else if (force_lpa == 2) rc = run_lpa<2>(c, a);
     else if (force_lpa == 4) rc = run_lpa<4>(c, a);

@@ -14,6 +14,7 @@
 // z,y,x exchange.
 #include "device.cuh"
 
+#include <cub/cub.cuh>
 #include <dlfcn.h>
 #include <nccl.h>
 
@@ -26,6 +27,7 @@ struct NcclApi {
   ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
   ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
   ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*CommAbort)(ncclComm_t) = nullptr;
   ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
@@ -45,7 +47,7 @@ bool nccl_load(std::string *why)
   g_nccl.field = reinterpret_cast<decltype(g_nccl.field)>(dlsym(h, name));               \
   if (!g_nccl.field) { if (why) *why = std::string("libnccl lacks ") + name; return false; }
   NCCL_SYM(GetUniqueId, "ncclGetUniqueId") NCCL_SYM(CommInitRank, "ncclCommInitRank")
-  NCCL_SYM(CommDestroy, "ncclCommDestroy") NCCL_SYM(Send, "ncclSend") NCCL_SYM(Recv, "ncclRecv")
+  NCCL_SYM(CommDestroy, "ncclCommDestroy") NCCL_SYM(CommAbort, "ncclCommAbort") NCCL_SYM(Send, "ncclSend") NCCL_SYM(Recv, "ncclRecv")
   NCCL_SYM(AllReduce, "ncclAllReduce") NCCL_SYM(GroupStart, "ncclGroupStart") NCCL_SYM(GroupEnd, "ncclGroupEnd")
   NCCL_SYM(GetErrorString, "ncclGetErrorString")
 #undef NCCL_SYM
@@ -56,6 +58,7 @@ bool nccl_load(std::string *why)
 #define ncclGetUniqueId g_nccl.GetUniqueId
 #define ncclCommInitRank g_nccl.CommInitRank
 #define ncclCommDestroy g_nccl.CommDestroy
+#define ncclCommAbort g_nccl.CommAbort
 #define ncclSend g_nccl.Send
 #define ncclRecv g_nccl.Recv
 #define ncclAllReduce g_nccl.AllReduce
@@ -126,10 +129,42 @@ void imdcu_multi_release(imdcu_ctx *c)
 int imdcu_multi_allreduce(imdcu_ctx *c, void *buf, int count, int kind)
 {
   if (c->comm.nranks <= 1 || count <= 0) return IMDCU_OK;
-  const ncclDataType_t dt = kind == 2 ? ncclInt32 : ncclFloat64;
-  const ncclRedOp_t op = kind == 1 ? ncclMax : ncclSum;
+  if (!c->comm.nccl) return c->fail(IMDCU_ENCCL, "the NCCL communicator was aborted after an error on this rank");
+  const ncclDataType_t dt = (kind == 2 || kind == 3) ? ncclInt32 : ncclFloat64;
+  const ncclRedOp_t op = (kind == 1 || kind == 3) ? ncclMax : ncclSum;
   NCCL_CHECK(c, ncclAllReduce(buf, buf, (size_t) count, dt, op, comm_of(c), c->stream));
   return IMDCU_OK;
+}
+
+// Error agreement: a rank-local failure (an atom left through an open end, a full neighbour table, a raised
+// device flag) must not let this rank leave the step while its peers queue the next collective -- that would
+// hang the job instead of failing it.  Every rank contributes its local code; all ranks return together.
+// Used on the rebuild path only (one tiny all-reduce + the host sync that path already has).
+int imdcu_multi_agree(imdcu_ctx *c, int local_rc)
+{
+  imdcu_ctx::Comm &m = c->comm;
+  if (m.nranks <= 1) return local_rc;
+  if (!m.nccl) return local_rc != IMDCU_OK ? local_rc : c->fail(IMDCU_ENCCL, "the NCCL communicator was aborted");
+  const std::string local_msg = c->err;
+  m.h_migcnt[7] = local_rc != IMDCU_OK ? 1 : 0;
+  CU_CHECK(c, cudaMemcpyAsync(m.d_migcnt + 7, m.h_migcnt + 7, sizeof(int), cudaMemcpyHostToDevice, c->stream));
+  RET_IF(imdcu_multi_allreduce(c, m.d_migcnt + 7, 1, 3));
+  CU_CHECK(c, cudaMemcpyAsync(m.h_migcnt + 7, m.d_migcnt + 7, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CU_CHECK(c, cudaStreamSynchronize(c->stream));
+  c->err_agreed = true;
+  if (local_rc != IMDCU_OK) { c->err = local_msg; return local_rc; }
+  if (m.h_migcnt[7]) return c->fail(IMDCU_EINVAL, "another rank reported an error in this step (see its message)");
+  c->err_agreed = false;
+  return IMDCU_OK;
+}
+
+// A failure that was NOT agreed on (a CUDA or NCCL error in the middle of a step): tear the communicator down so
+// that the peers' pending collectives fail instead of waiting forever.
+void imdcu_multi_abort(imdcu_ctx *c)
+{
+  imdcu_ctx::Comm &m = c->comm;
+  if (m.nranks > 1 && m.nccl && g_nccl.ok && !c->err_agreed) { ncclCommAbort((ncclComm_t) m.nccl); m.nccl = nullptr; }
+  c->err_agreed = false;
 }
 
 // one exchange with the x-neighbours: what goes west is received by the west neighbour as ITS
@@ -139,6 +174,7 @@ static int exchange(imdcu_ctx *c, const void *s_w, size_t n_sw, const void *s_e,
                     void *r_e, size_t n_re, void *r_w, size_t n_rw, ncclDataType_t dt)
 {
   const imdcu_ctx::Comm &m = c->comm;
+  if (!m.nccl) return c->fail(IMDCU_ENCCL, "the NCCL communicator was aborted after an error on this rank");
   NCCL_CHECK(c, ncclGroupStart());
   if (m.west >= 0 && n_sw) NCCL_CHECK(c, ncclSend(s_w, n_sw, dt, m.west, comm_of(c), c->stream));
   if (m.east >= 0 && n_se) NCCL_CHECK(c, ncclSend(s_e, n_se, dt, m.east, comm_of(c), c->stream));
@@ -178,18 +214,30 @@ k_mig_count(int n, int ncell_ext, const int *__restrict__ key, int *__restrict__
   if (threadIdx.x == 0) { if (w) atomicAdd(&cnt[0], w); if (e) atomicAdd(&cnt[1], e); }
 }
 
+// leaver flags for the slot scan: a record's slot is the number of leavers to the same side in front of it in
+// the (deterministic) cell-sorted order -- an atomic counter would make the arrival order, and with it the
+// intra-cell order and every FP64 summation order downstream, vary from run to run
+__global__ void __launch_bounds__(256)
+k_mig_flags(int n, int ncell_ext, const int *__restrict__ key, int *__restrict__ fw, int *__restrict__ fe)
+{
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int k = key[i];
+  fw[i] = k == ncell_ext; fe[i] = k == ncell_ext + 1;
+}
+
 __global__ void __launch_bounds__(256)
 k_mig_pack(int n, int ncell_ext, const int *__restrict__ key, const double4 *__restrict__ pos4,
            const double4 *__restrict__ mom4, const int *__restrict__ type, const int *__restrict__ vtype,
            const int *__restrict__ id, const int *__restrict__ fdi, double *__restrict__ rec_w,
-           double *__restrict__ rec_e, int *__restrict__ cnt)
+           double *__restrict__ rec_e, const int *__restrict__ slot_w, const int *__restrict__ slot_e)
 {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const int k = key[i];
   if (k < ncell_ext) return;
   const int side = k - ncell_ext;
-  const int slot = atomicAdd(&cnt[2 + side], 1);
+  const int slot = side == 0 ? slot_w[i] : slot_e[i];
   double *o = (side == 0 ? rec_w : rec_e) + (size_t) slot * MIG_REC;
   const double4 p = pos4[i], q = mom4[i];
   o[0] = p.x; o[1] = p.y; o[2] = p.z; o[3] = p.w;
@@ -252,16 +300,28 @@ int imdcu_multi_migrate(imdcu_ctx *c, int *n_total)
   const int out_w = hc[0], out_e = hc[1];
   const int in_e = m.east >= 0 ? hc[4] : 0, in_w = m.west >= 0 ? hc[5] : 0;
   const int narr = in_e + in_w;
-  if ((out_w && m.west < 0) || (out_e && m.east < 0)) return c->fail(IMDCU_EINVAL, "atom left the box through an open x end");
+  {
+    int rc = IMDCU_OK;
+    if ((out_w && m.west < 0) || (out_e && m.east < 0)) rc = c->fail(IMDCU_EINVAL, "atom left the box through an open x end");
+    RET_IF(imdcu_multi_agree(c, rc));                 // all ranks leave together, nobody waits in the payload exchange
+  }
   if (out_w + out_e + narr > 0) {
     CU_CHECK(c, m.mig_send.ensure((size_t) (out_w + out_e) * MIG_REC + 16, 1.5));
     CU_CHECK(c, m.mig_recv.ensure((size_t) narr * MIG_REC + 16, 1.5));
     double *rw = m.mig_send.p, *re = m.mig_send.p + (size_t) out_w * MIG_REC;
     const bool have_fdi = c->ttm.inited && c->ttm.fdi.cap >= (size_t) n;
     if (out_w + out_e > 0) {
+      // slots by exclusive scan of the leaver flags (scratch: the sort's output buffers, free until the sort)
+      int *fw = c->key_alt.p, *fe = c->perm_alt.p;
+      size_t scan_bytes = 0;
+      cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, fw, fw, n, st);
+      CU_CHECK(c, c->cub_tmp.ensure(scan_bytes + 256));
+      k_mig_flags<<<div_up(n, 256), 256, 0, st>>>(n, c->ncell_ext, c->key.p, fw, fe);
+      CU_CHECK(c, cub::DeviceScan::ExclusiveSum(c->cub_tmp.p, scan_bytes, fw, fw, n, st));
+      CU_CHECK(c, cub::DeviceScan::ExclusiveSum(c->cub_tmp.p, scan_bytes, fe, fe, n, st));
       k_mig_pack<<<div_up(n, 256), 256, 0, st>>>(n, c->ncell_ext, c->key.p, c->pos4.p, c->mom4.p, c->type.p, c->vtype.p,
-                                                 c->id.p, have_fdi ? c->ttm.fdi.p : nullptr, rw, re, dc);
-      c->count_launch();
+                                                 c->id.p, have_fdi ? c->ttm.fdi.p : nullptr, rw, re, fw, fe);
+      c->count_launch(4);
     }
     RET_IF(exchange(c, rw, (size_t) out_w * MIG_REC, re, (size_t) out_e * MIG_REC, m.mig_recv.p, (size_t) in_e * MIG_REC,
                     m.mig_recv.p + (size_t) in_e * MIG_REC, (size_t) in_w * MIG_REC, ncclFloat64));

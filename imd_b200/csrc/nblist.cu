@@ -81,19 +81,24 @@ int imdcu_check_flags(imdcu_ctx *c)
 {
   CU_CHECK(c, cudaMemcpyAsync(c->h_flags, c->d_flags, 8 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
   CU_CHECK(c, cudaStreamSynchronize(c->stream));
+  // is_short of the EAM passes (potaccess.h:331-333: argument below the table begin, clamped): the reference
+  // prints "short distance" after calc_forces (imd_forces_nbl.c:673,992); here it is kept as a warning count
+  if (c->h_flags[2] || c->h_flags[3]) {
+    c->short_warn += 1;
+    CU_CHECK(c, cudaMemsetAsync(c->d_flags + 2, 0, 2 * sizeof(int), c->stream));
+  }
   if (c->h_flags[4]) return c->fail(IMDCU_EINVAL, "an atom crossed more than one x slab between two cell sorts");
   if (c->h_flags[5]) return c->fail(IMDCU_EINVAL, "NRB: a listed neighbour of a boundary atom lives on another GPU");
   if (c->h_flags[6]) return c->fail(IMDCU_EINVAL, "NRB: a listed neighbour of a boundary atom has no entry");
   return IMDCU_OK;
 }
 
-int imdcu_build_nblist(imdcu_ctx *c)
+static int build_nblist_local(imdcu_ctx *c)
 {
-  PhaseTimer pt(c, 1);
   const int n = (int) c->n;
   cudaStream_t st = c->stream;
   RET_IF(imdcu_check_flags(c));
-  if (n == 0) { c->have_valid_nbl = true; c->nbl_count++; return IMDCU_OK; }
+  if (n == 0) return IMDCU_OK;
   const int nb = div_up(n, 128);
   const size_t ntiles = (size_t) div_up(n, 32);
   auto run = [&](bool count_only) -> int {
@@ -130,6 +135,15 @@ int imdcu_build_nblist(imdcu_ctx *c)
     if (c->h_flags[1] > c->nbl_cap) return c->fail(IMDCU_EOVERFLOW, "neighbor table full - increase nbl_size");
   }
   c->last_max_neigh = c->h_flags[1];
+  return IMDCU_OK;
+}
+
+int imdcu_build_nblist(imdcu_ctx *c)
+{
+  PhaseTimer pt(c, 1);
+  // the build itself runs no collective, so a rank may fail or redo it locally; the outcome is agreed on once,
+  // here, so that a rank with a raised flag or a full table does not leave its peers in the next halo exchange
+  RET_IF(imdcu_multi_agree(c, build_nblist_local(c)));
   c->have_valid_nbl = true;
   c->nbl_count++;
   return IMDCU_OK;

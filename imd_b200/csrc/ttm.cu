@@ -1223,7 +1223,7 @@ static int ttm_grid_part(imdcu_ctx *c, int steps, cudaStream_t st)
   a.eos_smem = smem <= 200 * 1024;
   if (!a.eos_smem) smem = 0;
   {
-    static const bool off = [] { const char *e = getenv("IMDCU_TTM_LAT_SMEM"); return e && e[0] == '0'; }();
+    const bool off = !c->tune.ttm_lat_smem;
     const size_t nvl = t.p.vlatdim > 0 ? t.p.vlatdim : 1;
     const size_t lat_bytes = (2 * (size_t) t.P * t.LD + 2 * nvl) * sizeof(TCell) + 16 + (size_t) t.P * t.LD * sizeof(double) +
                              (t.use_tmm ? TMM_BUF_PER_CELL * (size_t) (t.G + 2) * sizeof(double) : 0);

@@ -394,7 +394,7 @@ extern "C" int imdcu_ttm3d_diff(imdcu_ctx *c, double tau, int diff_substeps, int
   a.natoms = t.natoms.p; a.fd_k = t.fd_k.p; a.fd_g = t.fd_g.p; a.Ce = t.Ce.p; a.md_temp = t.md_temp.p;
   a.source = t.source.p; a.dens = t.dens.p; a.U = t.U.p; a.xi = t.xi.p;
   // variant: IMDCU_TTM3D=tiled selects the 2.5-D shared-memory kernel, default is the direct one
-  static const bool tiled = [] { const char *e = getenv("IMDCU_TTM3D"); return e && !strcmp(e, "tiled"); }();
+  const bool tiled = c->tune.ttm3d_tiled != 0;
   dim3 grid, block;
   if (tiled) {
     // x chunk: enough CTAs for >= 4 waves of 148 SMs x 4 resident CTAs, at least 8 planes per CTA

@@ -96,6 +96,14 @@ int  imdcu_set_params(imdcu_ctx *ctx, int ntypes, double timestep,
 int  imdcu_set_pdecay(imdcu_ctx *ctx, int enabled, double xipdecay,
                       double ramp_start, double ramp_end);
 
+/* Kernel-selection knobs (no reference counterpart; results are the same for every setting, the
+ * parity tests run all of them): "lpa" lanes per atom of the EAM passes (0 = chosen by system size,
+ * else 1, 2, 4, 8), "fused_table" (1: interleaved pair+rho rows in pass 1 when both tables share their
+ * r^2 grid), "ttm_overlap" (1: imdcu_run_ttm runs the lattice kernel beside EAM pass 2),
+ * "ttm_lat_smem", "ttm3d_tiled".  The IMDCU_LPA / IMDCU_FUSED_TABLE / ... environment variables set
+ * the defaults when the context is created. */
+int  imdcu_set_tuning(imdcu_ctx *ctx, const char *key, int value);
+
 /* ------------------------------------------------------------------ atoms */
 /* Upload all owned atoms (AoS pos/mom as ORT/IMPULS, makros.h:143-145).  Invalidates
  * the neighbour list (have_valid_nbl = 0, globals.h:179). */
@@ -236,6 +244,9 @@ int  imdcu_get_cell_grid(const imdcu_ctx *ctx, int gdim[3], double *cellsz);
  * of make_nblist up to order); call with pairs==NULL to get the count in *npairs. */
 int  imdcu_get_nblist_pairs(imdcu_ctx *ctx, int64_t *npairs, int32_t *pairs);
 int  imdcu_nbl_count(const imdcu_ctx *ctx);            /* globals.h:178 nbl_count */
+/* > 0: since the last call a table was evaluated below its first argument (is_short, potaccess.h:331-333; the
+ * reference warns "short distance" after calc_forces, imd_forces_nbl.c:673,992); < 0: error code */
+int  imdcu_short_distance(imdcu_ctx *ctx);
 int  imdcu_invalidate_nblist(imdcu_ctx *ctx);           /* have_valid_nbl = 0      */
 /* kernel launches issued by this context so far (for bench.py's gpu_launches) */
 int64_t imdcu_launch_count(const imdcu_ctx *ctx);
@@ -248,6 +259,10 @@ int  imdcu_get_phase_times(imdcu_ctx *ctx, double ms[IMDCU_NPHASE], int64_t laun
 /* the CUDA stream all work of this context is enqueued on (cudaStream_t as void*) */
 void *imdcu_stream(const imdcu_ctx *ctx);
 int  imdcu_synchronize(imdcu_ctx *ctx);
+
+/* FP64-FMA rate this GPU sustains, in GFLOP/s (a short kernel of independent DFMA chains on every SM): the
+ * denominator of the FP64-pipe fraction reported beside the HBM fraction for the EAM passes */
+int  imdcu_probe_fp64(imdcu_ctx *ctx, double *gflops);
 
 /* single-function probe of the device table access (parity test of potaccess.h):
  * evaluates PAIR_INT2 on `which` for n arguments on the GPU */

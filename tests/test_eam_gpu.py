@@ -19,8 +19,14 @@ def rel_err(a, b, floor=1e-2):
     return np.max(np.abs(a - b)) / max(np.max(np.abs(b)), floor)
 
 
-def make_imd(box, pbc, tables, margin, timestep=0.1, ntypes=1):
+# kernel instantiations (imdcu_set_tuning): lanes per atom of the EAM passes x interleaved-row pass 1.
+# lpa = 1 with fused = 1 is what bench.py times (k_eam_pass1_fused<1>, k_eam_pass2<1,...>); 0 = by system size
+VARIANTS = [(0, 1), (1, 1), (1, 0), (2, 1), (4, 1), (4, 0), (8, 0)]
+
+
+def make_imd(box, pbc, tables, margin, timestep=0.1, ntypes=1, lpa=0, fused=1):
     imd = host.Imd(0)
+    imd.ctx.set_tuning(lpa=lpa, fused_table=fused)
     imd.setup_potentials(tables)
     imd.make_box(box, pbc, margin)
     imd.set_params(ntypes, timestep)
@@ -47,13 +53,14 @@ def test_table_access_matches_oracle(interp):
     imd.close()
 
 
+@pytest.mark.parametrize("lpa,fused", VARIANTS)
 @pytest.mark.parametrize("case", GOLDEN_CASES + INTERP_CASES)
-def test_golden_cells_nblist_forces(case):
+def test_golden_cells_nblist_forces(case, lpa, fused):
     g = Golden(case)
     for s in g.steps:
         if "s%d_nblpairs" % s not in g.z:
             continue
-        imd = make_imd(g.box, g.pbc, g.tables, g.margin, g.timestep, g.ntypes)
+        imd = make_imd(g.box, g.pbc, g.tables, g.margin, g.timestep, g.ntypes, lpa, fused)
         sc = g.step(s, "scalars")
         assert [int(x) for x in imd.global_cell_dim] == [int(x) for x in sc[4:7]]
         assert imd.cellsz == sc[7]
@@ -80,16 +87,23 @@ def test_golden_cells_nblist_forces(case):
 
 @pytest.mark.parametrize("case", ["cu_6x6x6_pbc", "ni3al_6x6x6_pbc", "cu_6x6x6_pbc_4point", "cu_6x6x6_pbc_spline",
                                   "ni3al_6x5x5_free_x_spline"])
-def test_golden_trajectory(case):
+@pytest.mark.parametrize("lpa", [0, 1])
+def test_golden_trajectory(case, lpa):
     """NVE from the reference's step-0 state: calc_forces -> move_atoms -> check_nblist on the
     device reproduces the reference's dumped states and its rebuild schedule (one and two species:
     the second case runs the MULTI kernels, per-column table grids, two masses)."""
     g = Golden(case)
-    imd = make_imd(g.box, g.pbc, g.tables, g.margin, g.timestep, g.ntypes)
+    imd = make_imd(g.box, g.pbc, g.tables, g.margin, g.timestep, g.ntypes, lpa, 1)
     imd.set_atoms(g.step(0, "pre_pos"), g.step(0, "pre_mom"), g.step(0, "pre_mass"),
                   g.step(0, "pre_type"), g.step(0, "pre_id"))
+    # the reference's .eng (write_eng_file, imd_io.c:2290-2420, built with -DHPO: %.16e): one row per step,
+    # columns time, Epot = tot_pot_energy / natoms, temperature = 2 tot_kin_energy / nactive, pressure, volume
     eng = g.z["eng"]
-    for step in range(0, max(g.steps) + 1):
+    n = g.step(0, "pre_id").shape[0]
+    nsteps = max(g.steps) + 1
+    assert eng.shape[0] == nsteps
+    mine = np.zeros((nsteps, 2))
+    for step in range(0, nsteps):
         count0 = imd.nbl_count
         imd.calc_forces(step)
         if step in g.steps:
@@ -98,7 +112,19 @@ def test_golden_trajectory(case):
             assert (imd.nbl_count != count0) == ("s%d_nblpairs" % step in g.z), step
             assert abs(imd.tot_pot_energy - g.step(step, "scalars")[0]) < 1e-9 * abs(g.step(step, "scalars")[0])
         imd.move_atoms()
-    assert eng.shape[0] >= 2
+        mine[step] = imd.tot_pot_energy / n, 2.0 * imd.tot_kin_energy / (3 * n)
+    # NVE energy drift equal to the reference's (north_star): Etot per atom = Epot + 3/2 T, step by step.
+    # A trajectory is chaotic, so the bound grows with the step; observed <= 2e-12 after 40 steps.
+    etot_ref = eng[:, 1] + 1.5 * eng[:, 2]
+    etot = mine[:, 0] + 1.5 * mine[:, 1]
+    err_pot = np.abs(mine[:, 0] - eng[:, 1]).max() / np.abs(eng[:, 1]).max()
+    err_kin = np.abs(mine[:, 1] - eng[:, 2]).max() / np.abs(eng[:, 2]).max()
+    drift_ref, drift = etot_ref - etot_ref[0], etot - etot[0]
+    err_drift = np.abs(drift - drift_ref).max()
+    print("%s lpa=%d: Epot/atom rel err %.2e, T rel err %.2e, drift ref %.3e mine %.3e, |d drift| %.2e eV/atom"
+          % (case, lpa, err_pot, err_kin, np.abs(drift_ref).max(), np.abs(drift).max(), err_drift))
+    assert err_pot < 1e-9 and err_kin < 1e-8
+    assert err_drift < 1e-9 * np.abs(etot_ref[0]), (err_drift, np.abs(drift_ref).max())
     imd.close()
 
 
@@ -121,7 +147,8 @@ def tables_on_different_grids(spec):
                                                       ((6, 6, 6), (0, 0, 0), synth.CU, True),
                                                       ((8, 7, 6), (1, 1, 1), synth.CU, False),
                                                       ((10, 5, 6), (0, 1, 1), synth.AL, False)])
-def test_oracle_parity_seeded(ncell, pbc, spec, same_grid):
+@pytest.mark.parametrize("lpa", [0, 1, 2])
+def test_oracle_parity_seeded(ncell, pbc, spec, same_grid, lpa):
     from oracle.binding import EamOracle
     tables = synth.make_eam_tables(spec) if same_grid else tables_on_different_grids(spec)
     pos, box = synth.fcc_lattice(ncell, spec.a)
@@ -129,7 +156,7 @@ def test_oracle_parity_seeded(ncell, pbc, spec, same_grid):
     pos = pos + rng.normal(0, 0.08, pos.shape)
     mom = synth.maxwell_momenta(pos.shape[0], spec.mass, 0.05, seed=3)
     margin = 0.4
-    imd = make_imd(box, pbc, tables, margin)
+    imd = make_imd(box, pbc, tables, margin, lpa=lpa)
     imd.set_atoms(pos, mom, spec.mass)
     orc = EamOracle(box, pbc, tables, margin)
     p = pos.copy()
@@ -184,7 +211,6 @@ def test_full_size_properties_and_kernel_variants():
     (one lane per atom, interleaved-row pass 1, pipelined neighbour loop) against (a) size-independent
     properties -- sum F = 0, momentum and NVE energy conserved -- and (b) the four-lanes-per-atom general
     instantiations that the golden tests exercise at small sizes, on the same resident atoms."""
-    import os
     spec = synth.AL
     tables = synth.make_eam_tables(spec)
     pos, box = synth.fcc_lattice((80, 80, 80), spec.a)
@@ -198,18 +224,11 @@ def test_full_size_properties_and_kernel_variants():
     e_hot = imd.tot_pot_energy
     fscale = np.abs(a["force"]).max()
     assert np.abs(a["force"].sum(axis=0)).max() < 1e-9 * np.abs(a["force"]).sum()
-    old = {k: os.environ.get(k) for k in ("IMDCU_LPA", "IMDCU_FUSED_TABLE")}
-    try:
-        os.environ["IMDCU_LPA"] = "4"
-        imd.calc_forces(0)
-        b = imd.atoms(("id", "force", "epot", "rho", "dF"))
-        e_lpa = imd.tot_pot_energy
-    finally:
-        for k, v in old.items():
-            if v is None:
-                os.environ.pop(k, None)
-            else:
-                os.environ[k] = v
+    imd.ctx.set_tuning(lpa=4, fused_table=0)
+    imd.calc_forces(0)
+    b = imd.atoms(("id", "force", "epot", "rho", "dF"))
+    e_lpa = imd.tot_pot_energy
+    imd.ctx.set_tuning(lpa=0, fused_table=1)
     assert np.abs(a["force"] - b["force"]).max() < 1e-11 * fscale
     for key in ("epot", "rho", "dF"):
         assert rel_err(a[key], b[key]) < 1e-12, key
@@ -221,3 +240,41 @@ def test_full_size_properties_and_kernel_variants():
     assert np.abs(etot - etot[0]).max() / pos.shape[0] < 2e-5
     assert imd.nbl_count >= 1
     imd.close()
+
+
+@pytest.mark.parametrize("ncell,pbc", [((64, 64, 64), (1, 1, 1)), ((100, 48, 48), (0, 1, 1))])
+def test_full_size_hot_kernels_vs_oracle(ncell, pbc):
+    """The instantiations bench.py times -- one lane per atom, k_eam_pass1_fused<1> + k_eam_pass2<1,...>, chosen by
+    system size (n >= 148 x 2048) -- against the CPU restatement of make_nblist / calc_forces
+    (imd_forces_nbl.c:136-287, 419-985) on the WHOLE system: ~1 M Al atoms, bulk and film."""
+    from oracle.binding import EamOracle
+    spec = synth.AL
+    tables = synth.make_eam_tables(spec)
+    pos, box = synth.fcc_lattice(ncell, spec.a)
+    if not pbc[0]:
+        pos[:, 0] += 5 * spec.a
+        box[0, 0] += 10 * spec.a
+    rng = np.random.default_rng(21)
+    pos = pos + rng.normal(0.0, 0.06, pos.shape)
+    mom = synth.maxwell_momenta(pos.shape[0], spec.mass, 0.0258, seed=9)
+    assert pos.shape[0] >= 148 * 2048
+    imd = make_imd(box, pbc, tables, 0.4)
+    imd.set_atoms(pos, mom, spec.mass)
+    imd.calc_forces(0)
+    got = imd.atoms(("id", "pos", "cell", "force", "epot", "rho", "dF", "numneighs"))
+    orc = EamOracle(box, pbc, tables, 0.4)
+    p = pos.copy()
+    cells = orc.fix_cells(p)
+    orc.make_nblist()
+    ref = orc.calc_forces(p, np.zeros(pos.shape[0], np.int32))
+    assert np.array_equal(got["pos"], p)
+    assert np.array_equal(got["cell"], cells)
+    assert np.array_equal(got["numneighs"], ref["numneighs"])          # every pair inside the cutoff, both sides
+    errs = {k: rel_err(got[k], ref[k]) for k in ("force", "epot", "rho", "dF")}
+    e_rel = abs(imd.tot_pot_energy - ref["tot_pot_energy"]) / abs(ref["tot_pot_energy"])
+    print("full size %s: %d atoms, rel err %s, Epot %.2e" % (ncell, pos.shape[0], errs, e_rel))
+    for k, v in errs.items():
+        assert v < RTOL, (k, v)
+    assert e_rel < RTOL
+    imd.close()
+    orc.close()

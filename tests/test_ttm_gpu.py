@@ -5,7 +5,7 @@ import numpy as np
 import pytest
 
 from imd_b200 import host, synth
-from tests.ttm_util import (REL_STEP0, TE_ABS_K, TMM_CASES, TTM_CASES, TTM_FIELDS, TtmGolden, compare_cells)
+from tests.ttm_util import (REL_STEP0, REL_TE, TE_ABS_K, TMM_CASES, TTM_CASES, TTM_FIELDS, TtmGolden, compare_cells)
 
 pytestmark = pytest.mark.gpu
 
@@ -280,3 +280,48 @@ def test_full_size_fused_schedule_equals_sequential_calls():
     for k, tol in (("md_temp", 1e-9), ("dens", 1e-9), ("temp", 2e-7), ("U", 2e-7), ("xi", 1e-5)):
         ref = np.abs(lb[k][act]).max() + 1e-300
         assert np.abs(la[k][act] - lb[k][act]).max() < tol * ref, k
+
+
+def test_full_size_calc_ttm_vs_oracle():
+    """BASELINE.json configs[2] at full size (Al film, 100^3 cubic cells = 4 000 000 atoms, 250 sub-steps, pulse on):
+    calc_ttm on the device against the CPU restatement of imd_ttm.c (update_fd, do_ADV, FILLMESH, CFL, do_DIFF) fed
+    with the SAME atom state every step -- the device's positions, momenta and numneighs (the latter checked
+    bit for bit against the oracle's make_nblist/calc_forces at ~1 M atoms in test_eam_gpu.py).  This is the
+    lattice kernel and the atom->slab kernels at the size bench.py times, not a self-comparison."""
+    from oracle.binding import TtmOracle
+    spec = synth.AL
+    tables = synth.make_eam_tables(spec)
+    pos, box = synth.film_lattice((100, 100, 100), spec.a, 10 * spec.a, 10 * spec.a)
+    n = pos.shape[0]
+    mom = synth.maxwell_momenta(n, spec.mass, 0.0258, seed=3)
+    eos = synth.make_eos_tables()
+    gx = int(box[0, 0] / 16.0)
+    tp = synth.TtmParams(ttmdimx=gx, fd_n_timesteps=250, fd_min_atoms=100, vlatdim=30, vlatbuffer=8,
+                         I0=5.0e15, laser_t_0=3e-15, laser_sigma_t=42.5e-15)       # pulse peak inside the 3 steps
+    P = 2
+    imd = host.Imd(0)
+    imd.setup_potentials(tables)
+    imd.make_box(box, (0, 1, 1), 0.4)
+    imd.set_params(1, 0.1)
+    imd.set_atoms(pos, mom, spec.mass)
+    imd.init_ttm(tp, eos, P)
+    ttm = TtmOracle(tp, eos, box, float(tables["pair"].end[0]), 0.1, P)
+    mass = np.full(n, spec.mass); types = np.zeros(n, np.int32)
+    fdi = np.zeros(n, np.int32)
+    for s in range(3):
+        imd.calc_forces(s)
+        a = imd.atoms(fields=("id", "pos", "mom", "numneighs"))
+        ttm.step(s, a["pos"], a["mom"], mass, types, a["numneighs"], fdi)
+        sc, osc = imd.calc_ttm(s), ttm.scalars()
+        assert int(sc["diff_substeps"]) == int(osc["diff_substeps"])
+        assert int(sc["last_active_cell_global"]) == int(osc["last_active_cell_global"])
+        assert int(sc["laser_active"]) == int(osc["laser_active"])
+        np.testing.assert_allclose(sc["Eabs"], osc["Eabs"], rtol=1e-9)
+        lat, oc, oa = imd.ttm_lattice(), ttm.cells(), ttm.arrays()
+        compare_cells(lat["fields"], oc, s, int(osc["last_active_cell_global"]), "full size 4M")
+        np.testing.assert_allclose(lat["xiarr"], oa["xiarr"], rtol=REL_TE if s else REL_STEP0,
+                                   atol=(REL_TE if s else 1e-14) * np.abs(oa["xiarr"]).max())
+        np.testing.assert_allclose(lat["vcom"], oa["vcom"], rtol=0, atol=1e-9 * np.abs(oa["vcom"]).max())
+        imd.move_atoms_ttm()
+    assert int(lat["fields"]["natoms"].max()) > 100000
+    imd.close(); ttm.close()
