@@ -183,7 +183,8 @@ def run_reference_mpi(global_cells, steps, cpu_dim):
         synth.write_param_file(os.path.join(work, "run.param"), spec, tuple(global_cells), steps, "out/run",
                                potdir=".", pbc=(1, 1, 1), starttemp=0.0258, nbl_margin=0.4, eng_int=0,
                                cpu_dim=tuple(cpu_dim))
-        env = dict(os.environ, SHMPI_NP=str(nproc), SHMPI_RING_MB="4")
+        ring_mb = max(4, int(4 * global_cells[1] * global_cells[2] * 2 * 80 * 2 / 1e6) + 1)
+        env = dict(os.environ, SHMPI_NP=str(nproc), SHMPI_RING_MB=str(ring_mb))
         t0 = time.perf_counter()
         res = subprocess.run([REF_MPI, "-p", "run.param"], cwd=work, env=env, stdout=subprocess.PIPE,
                              stderr=subprocess.STDOUT, text=True, timeout=900)
@@ -259,7 +260,9 @@ def run_reference_ttm(cells, world, steps, nproc, nrb, substeps):
         synth.write_param_file(os.path.join(run, "run.param"), spec, (ncx, cells[1], cells[2]), steps, "out/run",
                                potdir="..", pbc=(0, 1, 1), starttemp=0.0258, nbl_margin=0.4, eng_int=0, extra=ex,
                                ensemble="ttm", cpu_dim=(nproc, 1, 1))
-        env = dict(os.environ, SHMPI_NP=str(nproc), SHMPI_RING_MB="4",
+        # shmpi ring per rank pair (virtual, touched where used): one yz plane of cells as 10 doubles per atom, x2
+        ring_mb = max(4, int(4 * cells[1] * cells[2] * 2 * 80 * 2 / 1e6) + 1)
+        env = dict(os.environ, SHMPI_NP=str(nproc), SHMPI_RING_MB=str(ring_mb),
                    IMD_SRC_MU="%.17g" % tp.src_mu, IMD_SRC_ABS="%.17g" % tp.src_abs)
         env.pop("IMD_DUMP_DIR", None)
         t0 = time.perf_counter()

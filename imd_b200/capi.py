@@ -60,6 +60,7 @@ def load():
     vp = C.c_void_p
     sig = {
         "imdcu_abi_version": (C.c_int, []),
+        "imdcu_device_count": (C.c_int, [c_ip]),
         "imdcu_create": (C.c_int, [C.POINTER(vp), C.c_int]),
         "imdcu_destroy": (C.c_int, [vp]),
         "imdcu_last_error": (C.c_char_p, [vp]),
@@ -74,6 +75,7 @@ def load():
         "imdcu_num_atoms": (C.c_int64, [vp]),
         "imdcu_update_atoms": (C.c_int, [vp, c_dp, c_dp]),
         "imdcu_download_atoms": (C.c_int, [vp, c_ip, c_ip, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_ip, c_ip]),
+        "imdcu_download_vtypes": (C.c_int, [vp, c_ip]),
         "imdcu_calc_forces": (C.c_int, [vp, C.c_int, c_dp]),
         "imdcu_move_atoms_nve": (C.c_int, [vp, c_dp, c_ip]),
         "imdcu_run_nve": (C.c_int, [vp, C.c_int, C.c_int, c_dp]),

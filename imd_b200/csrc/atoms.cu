@@ -194,3 +194,17 @@ extern "C" int imdcu_download_atoms(imdcu_ctx *c, int32_t *id, int32_t *type, do
   }
   return IMDCU_OK;
 }
+
+// VSORTE of every owned atom in the device's current order (the writers print it, imd_io_3d.c:778); the
+// internal NRB bit is masked off
+extern "C" int imdcu_download_vtypes(imdcu_ctx *c, int32_t *vtype)
+{
+  if (!c || !vtype) return c ? c->fail(IMDCU_EINVAL, "imdcu_download_vtypes: bad argument") : IMDCU_EINVAL;
+  cudaSetDevice(c->device);
+  const int64_t n = c->n;
+  if (n == 0) return IMDCU_OK;
+  CU_CHECK(c, cudaMemcpyAsync(vtype, c->vtype.p, n * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CU_CHECK(c, cudaStreamSynchronize(c->stream));
+  for (int64_t i = 0; i < n; i++) vtype[i] &= ~IMDCU_VTYPE_NRB;
+  return IMDCU_OK;
+}

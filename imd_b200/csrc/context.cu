@@ -12,6 +12,20 @@ extern "C" const char *imdcu_last_error(const imdcu_ctx *ctx)
   return ctx ? ctx->err.c_str() : g_create_error.c_str();
 }
 
+extern "C" int imdcu_device_count(int *n)
+{
+  if (!n) return IMDCU_EINVAL;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess) {
+    g_create_error = std::string("no CUDA device: ") + cudaGetErrorString(e) + " (libimdcu has no CPU fallback)";
+    *n = 0;
+    return IMDCU_ENODEVICE;
+  }
+  *n = ndev;
+  return IMDCU_OK;
+}
+
 extern "C" int imdcu_create(imdcu_ctx **out, int device)
 {
   if (!out) return IMDCU_EINVAL;

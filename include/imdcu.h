@@ -44,6 +44,8 @@ typedef struct imdcu_ctx imdcu_ctx;
 
 /* ------------------------------------------------------------------ life cycle */
 int  imdcu_abi_version(void);
+/* number of CUDA devices this process sees (a host with one rank per GPU picks rank % count) */
+int  imdcu_device_count(int *n);
 /* device: CUDA ordinal.  Replaces nothing in the reference (there is no device). */
 int  imdcu_create(imdcu_ctx **ctx, int device);
 int  imdcu_destroy(imdcu_ctx *ctx);
@@ -120,6 +122,9 @@ int  imdcu_update_atoms(imdcu_ctx *ctx, const double *pos, const double *mom);
 int  imdcu_download_atoms(imdcu_ctx *ctx, int32_t *id, int32_t *type, double *mass,
                           double *pos, double *mom, double *force, double *epot,
                           double *rho, double *dF, int32_t *numneighs, int32_t *cell3);
+
+/* VSORTE of the owned atoms, same order as imdcu_download_atoms (write_atoms_config prints it, imd_io_3d.c:778) */
+int  imdcu_download_vtypes(imdcu_ctx *ctx, int32_t *vtype);
 
 /* ------------------------------------------------------------------ hot path */
 /* calc_forces (imd_forces_nbl.c:295-1054): rebuilds cells + neighbour list when the

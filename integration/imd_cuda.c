@@ -1,0 +1,464 @@
+/* integration/imd_cuda.c -- the IMD-side half of the drop-in: the host stays IMD's own C program.
+ *
+ * This file is compiled WITH THE REFERENCE'S HEADERS and linked with the reference's own host objects
+ * (parameter parser, potential readers, generators, writers, timers, main loop: compiled in place from the
+ * reference tree by integration/Makefile, nothing copied) and with libimdcu.so.  It takes the place of
+ *
+ *     imd_forces_nbl.c   calc_forces, check_nblist, make_nblist, estimate_nblist_size, deallocate_nblist
+ *     imd_integrate.c    move_atoms_nve (:35-561), move_atoms_ttm (:581-811)   [the other ensembles stay]
+ *     imd_ttm.c          init_ttm (:955), calc_ttm (:75), ttm_writeout (:1683), ttm_read (:1983)
+ *     imd_tmm.c          tmm_init (:98)                       [do_tmm runs inside the device lattice kernel]
+ *
+ * behind the reference's own names and call sites: calc_forces(steps) imd_main_3d.c:406, calc_ttm() :534,
+ * move_atoms() :564 (function pointer set in imd_param.c:382,439), check_nblist() :812, init_ttm / tmm_init
+ * imd.c:237,245, ttm_writeout imd_main_3d.c:735.  Make-target spelling: the reference selects sources by
+ * substrings of the target name (Makefile:141-291,425-460); this is the substring "cuda"
+ * (imd_eam_nve_nbl_cuda, imd_mpi_eam_ttm_tmm_nbl_cuda), see integration/Makefile and INTEGRATION.md.
+ *
+ * Data flow: atoms live on the device from the first calc_forces on.  cell_array (types.h:188-349) is
+ * refilled by imdcu_sync_to_host() before every writer (write_config, write_config_select, write_distrib,
+ * write_pictures are entered through the one-line wrappers at the end of this file), so .chkpt, .force,
+ * .dist files are written by the reference's own writers in the reference's own formats; .eng needs only
+ * the global sums and .ttm only the FD lattice, which is assembled on rank 0 from the device.
+ * There is no CPU fallback: every entry point either runs on the GPU or stops with imderror().
+ */
+#include "imd.h"
+#include "imdcu.h"
+#ifdef TTM
+#include "nn_interpol/nn.h"
+#include "nn_interpol/delaunay.h"
+#endif
+
+static imdcu_ctx *cu = NULL;
+static int cu_resident = 0;          /* atoms have been handed to the device            */
+static int cu_host_stale = 0;        /* the device is ahead of cell_array               */
+static long cu_syncs = 0;
+
+static void cu_fail(const char *where, int rc)
+{
+  char msg[1024];
+  snprintf(msg, sizeof msg, "%s: %s (imdcu code %d)", where, imdcu_last_error(cu), rc);
+  error(msg);                                        /* imderror, imd_misc.c:78-98 */
+}
+#define CK(call) do { int rc_ = (call); if (rc_ != IMDCU_OK) cu_fail(#call, rc_); } while (0)
+
+static void *cu_alloc(size_t bytes)
+{
+  void *p = malloc(bytes > 0 ? bytes : 1);
+  if (p == NULL) error("imd_cuda: out of host memory");
+  return p;
+}
+
+/* ------------------------------------------------------------------ TTM set-up state (host side) */
+#ifdef TTM
+static int     cu_ttm_analytic = 0;          /* analytic Beer-Lambert source instead of do_tmm              */
+static double  cu_src_mu = 1.0 / 80.0, cu_src_abs = 0.1;
+static double *cu_bb = NULL, *cu_k12 = NULL; /* rows of alu_eps_bb.dat / K12.dat (tmm_init, imd_tmm.c:117-118) */
+static int     cu_bb_rows = 0, cu_k12_rows = 0;
+static int     cu_ttm_P = 1;                 /* rank layout of the reference the FD lattice reproduces */
+
+/* nn_read_table leaves a scattered point set + the Delaunay triangulation of libnn.  Our tables are
+ * rectilinear (is x js header): hand x[], y[], z[][] and, per grid rectangle, which diagonal the
+ * triangulation chose (the reference's lpi_interpolate_point interpolates on those triangles). */
+static void cu_eos_to_device(int which, nn_interp *nn, const char *fname)
+{
+  FILE *f;
+  int is = 0, js = 0, i, j, t, k;
+  double *x, *y, *z;
+  unsigned char *diag;
+  /* the grid shape is in the file header only (imd_interpol.c:1195-1196); every rank can read it */
+  f = fopen(fname, "r");
+  if (f == NULL || fscanf(f, "%d %d", &is, &js) != 2) error_str("imd_cuda: cannot read the header of %s", (char *) fname);
+  fclose(f);
+  if (is < 2 || js < 2 || is * js != nn->npoints) error_str("imd_cuda: %s is not an is x js table", (char *) fname);
+  x = cu_alloc(is * sizeof *x); y = cu_alloc(js * sizeof *y); z = cu_alloc((size_t) is * js * sizeof *z);
+  diag = calloc((size_t) (is - 1) * (js - 1), 1);
+  for (i = 0; i < is; i++) x[i] = nn->points[i * js].x;
+  for (j = 0; j < js; j++) y[j] = nn->points[j].y;
+  for (i = 0; i < is * js; i++) z[i] = nn->points[i].z;
+  for (t = 0; t < nn->d->ntriangles; t++) {
+    int *v = nn->d->triangles[t].vids, imin = is, jmin = js, has00 = 0, has11 = 0;
+    for (k = 0; k < 3; k++) { if (v[k] / js < imin) imin = v[k] / js; if (v[k] % js < jmin) jmin = v[k] % js; }
+    for (k = 0; k < 3; k++) {
+      int di = v[k] / js - imin, dj = v[k] % js - jmin;
+      if (di > 1 || dj > 1) error_str("imd_cuda: the triangulation of %s is not a split of the grid rectangles", (char *) fname);
+      if (di == 0 && dj == 0) has00 = 1;
+      if (di == 1 && dj == 1) has11 = 1;
+    }
+    if (imin < is - 1 && jmin < js - 1) diag[imin * (js - 1) + jmin] = (has00 && has11) ? 0 : 1;
+  }
+  CK(imdcu_ttm_set_eos(cu, which, is, js, x, y, z, diag));
+  free(x); free(y); free(z); free(diag);
+}
+
+/* a whitespace-separated table of numbers, `cols` per row (alu_eps_bb.dat: 3, K12.dat: 2) */
+static double *cu_read_rows(const char *fname, int cols, int *rows)
+{
+  FILE *f = fopen(fname, "r");
+  double v, *a = NULL;
+  long n = 0, cap = 0;
+  if (f == NULL) return NULL;
+  while (fscanf(f, "%lf", &v) == 1) {
+    if (n == cap) { cap = cap ? 2 * cap : 4096; a = realloc(a, cap * sizeof *a); if (a == NULL) error("imd_cuda: out of memory"); }
+    a[n++] = v;
+  }
+  fclose(f);
+  *rows = (int) (n / cols);
+  return a;
+}
+#endif /* TTM */
+
+/* ------------------------------------------------------------------ attach: everything the device needs */
+static void cu_attach(void)
+{
+  double box[9];
+  int pbc[3], cd[3] = {1, 1, 1}, ndev = 0, dev;
+  const char *e;
+  if (cu != NULL) return;
+  CK(imdcu_device_count(&ndev));
+  dev = myid % (ndev > 0 ? ndev : 1);                 /* one rank per GPU, ranks of a node in order */
+  if ((e = getenv("IMDCU_DEVICE")) != NULL) dev = atoi(e);
+  { int rc = imdcu_create(&cu, dev); if (rc != IMDCU_OK) cu_fail("imdcu_create", rc); }
+#ifdef MPI
+  if (cpu_dim.y != 1 || cpu_dim.z != 1)
+    error("imd_cuda: the device path decomposes along x only: use cpu_dim N 1 1 (one rank per GPU)");
+  {
+    char id[128];
+    memset(id, 0, sizeof id);
+    if (num_cpus > 1) {
+      if (myid == 0 && imdcu_comm_unique_id(id) != IMDCU_OK) error("imd_cuda: ncclGetUniqueId failed");
+      MPI_Bcast(id, 128, MPI_CHAR, 0, cpugrid);
+    }
+    CK(imdcu_comm_init(cu, id, myid, num_cpus));
+  }
+#endif
+  /* make-target substrings 4point / spline (Makefile:917-923) are a mode of the library */
+#if defined(FOURPOINT)
+  CK(imdcu_set_interp(cu, IMDCU_INTERP_4POINT));
+#elif defined(SPLINE)
+  CK(imdcu_set_interp(cu, IMDCU_INTERP_SPLINE));
+#endif
+  /* pot_table_t (types.h:537-549) as read_pot_table + init_threepoint left it (imd_potential.c:161-466,1260) */
+  CK(imdcu_set_table(cu, IMDCU_TAB_PAIR, pair_pot.ncols, pair_pot.maxsteps, pair_pot.begin, pair_pot.end,
+                     pair_pot.step, pair_pot.invstep, pair_pot.len, pair_pot.table));
+  CK(imdcu_set_table(cu, IMDCU_TAB_RHO, rho_h_tab.ncols, rho_h_tab.maxsteps, rho_h_tab.begin, rho_h_tab.end,
+                     rho_h_tab.step, rho_h_tab.invstep, rho_h_tab.len, rho_h_tab.table));
+  CK(imdcu_set_table(cu, IMDCU_TAB_EMBED, embed_pot.ncols, embed_pot.maxsteps, embed_pot.begin, embed_pot.end,
+                     embed_pot.step, embed_pot.invstep, embed_pot.len, embed_pot.table));
+#ifdef SPLINE
+  CK(imdcu_set_table2(cu, IMDCU_TAB_PAIR, pair_pot.table2));
+  CK(imdcu_set_table2(cu, IMDCU_TAB_RHO, rho_h_tab.table2));
+  CK(imdcu_set_table2(cu, IMDCU_TAB_EMBED, embed_pot.table2));
+#endif
+  box[0] = box_x.x; box[1] = box_x.y; box[2] = box_x.z;
+  box[3] = box_y.x; box[4] = box_y.y; box[5] = box_y.z;
+  box[6] = box_z.x; box[7] = box_z.y; box[8] = box_z.z;
+  pbc[0] = pbc_dirs.x; pbc[1] = pbc_dirs.y; pbc[2] = pbc_dirs.z;
+#ifdef TTM
+  cd[0] = fd_ext.x; cd[1] = fd_ext.y; cd[2] = fd_ext.z;     /* init_cells: cd = cpu_dim * fd_ext (imd_geom_3d.c:168-176) */
+#endif
+  CK(imdcu_set_box(cu, box, pbc, nbl_margin, nbl_size, cd));
+  {
+    int g[3]; double cs;
+    CK(imdcu_get_cell_grid(cu, g, &cs));
+    if (g[0] != global_cell_dim.x || g[1] != global_cell_dim.y || g[2] != global_cell_dim.z) {
+      char msg[256];
+      snprintf(msg, sizeof msg, "imd_cuda: the device cell grid %d %d %d differs from init_cells' %d %d %d", g[0], g[1], g[2],
+               global_cell_dim.x, global_cell_dim.y, global_cell_dim.z);
+      error(msg);
+    }
+  }
+  CK(imdcu_set_params(cu, ntypes, timestep, vtypes, (double *) restrictions));
+#ifdef PDECAY
+  CK(imdcu_set_pdecay(cu, 1, xipdecay, ramp_start, ramp_end));
+#endif
+#ifdef TTM
+  {
+    imdcu_ttm_params tp;
+    memset(&tp, 0, sizeof tp);
+    tp.ttmdimx = ttmdimx; tp.nranks_ref = cu_ttm_P;
+    tp.fd_n_timesteps = fd_n_timesteps; tp.fd_min_atoms = fd_min_atoms; tp.vlatdim = vlatdim; tp.vlatbuffer = vlatbuffer;
+    tp.vlatdens = vlatdens; tp.atomic_weight = atomic_weight; tp.atomic_charge = atomic_charge; tp.Temin = Temin;
+    tp.I0 = I0; tp.lambda = lambda; tp.laser_t_0 = laser_t_0; tp.laser_sigma_t = laser_sigma_t;
+    tp.tmm_laser_threshold = tmm_laser_threshold; tp.src_mu = cu_src_mu; tp.src_abs = cu_src_abs;
+    cu_eos_to_device(IMDCU_EOS_CVE, &intp_cve_from_r_te, "../EOS_cve_from_r_te.txt");
+    cu_eos_to_device(IMDCU_EOS_EE, &intp_ee_from_r_tesqrt, "../EOS_ee_from_r_tesqrt.txt");
+    if (!cu_ttm_analytic) {
+      cu_eos_to_device(IMDCU_EOS_PHASE, &intp_phase_from_r_ti, "../EOS_phase_from_r_ti.txt");
+      CK(imdcu_ttm_set_tmm(cu, tmm_absorption_threshold, laser_t_1, laser_sigma_t1, cu_bb_rows, cu_bb, cu_k12_rows, cu_k12));
+    }
+    CK(imdcu_ttm_init(cu, &tp));
+  }
+#endif
+  if (myid == 0) {
+    printf("imd_cuda: hot path on CUDA device %d through libimdcu.so (ABI %d)%s\n", dev, imdcu_abi_version(),
+           num_cpus > 1 ? ", x slabs over NCCL" : "");
+    fflush(stdout);
+  }
+}
+
+/* ------------------------------------------------------------------ cell_array -> device */
+static void cu_upload(void)
+{
+  long n = 0, m = 0;
+  int k, i;
+  int32_t *id, *type, *vtype;
+  double *mass, *pos, *mom;
+  for (k = 0; k < NCELLS; k++) n += CELLPTR(k)->n;
+  id = cu_alloc(n * sizeof *id); type = cu_alloc(n * sizeof *type); vtype = cu_alloc(n * sizeof *vtype);
+  mass = cu_alloc(n * sizeof *mass); pos = cu_alloc(3 * n * sizeof *pos); mom = cu_alloc(3 * n * sizeof *mom);
+  for (k = 0; k < NCELLS; k++) {
+    cell *p = CELLPTR(k);
+    for (i = 0; i < p->n; i++, m++) {
+      id[m] = NUMMER(p, i); type[m] = SORTE(p, i); vtype[m] = VSORTE(p, i); mass[m] = MASSE(p, i);
+      pos[3 * m] = ORT(p, i, X); pos[3 * m + 1] = ORT(p, i, Y); pos[3 * m + 2] = ORT(p, i, Z);
+      mom[3 * m] = IMPULS(p, i, X); mom[3 * m + 1] = IMPULS(p, i, Y); mom[3 * m + 2] = IMPULS(p, i, Z);
+    }
+  }
+  CK(imdcu_upload_atoms(cu, n, id, type, vtype, mass, pos, mom));
+  free(id); free(type); free(vtype); free(mass); free(pos); free(mom);
+  cu_resident = 1;
+  cu_host_stale = 0;
+}
+
+/* ------------------------------------------------------------------ device -> cell_array
+ * Called before every writer.  Every cell is emptied and refilled: an atom goes to the cell cell_coord
+ * (imd_geom_3d.c:1077) gives for its current position, like fix_cells would put it (imd_fix_cells_3d.c:43).
+ * An atom that has left this rank's slab since the device's last cell sort stays with this rank (clamped to
+ * the nearest boundary cell) -- the writers only need every atom exactly once. */
+void imdcu_sync_to_host(void)
+{
+  long n, m;
+  int k;
+  int32_t *id, *type, *vtype, *nn;
+  double *mass, *pos, *mom, *frc, *epot, *rho, *dF;
+  if (cu == NULL || !cu_resident || !cu_host_stale) return;
+  n = (long) imdcu_num_atoms(cu);
+  id = cu_alloc(n * sizeof *id); type = cu_alloc(n * sizeof *type); vtype = cu_alloc(n * sizeof *vtype);
+  nn = cu_alloc(n * sizeof *nn); mass = cu_alloc(n * sizeof *mass);
+  pos = cu_alloc(3 * n * sizeof *pos); mom = cu_alloc(3 * n * sizeof *mom); frc = cu_alloc(3 * n * sizeof *frc);
+  epot = cu_alloc(n * sizeof *epot); rho = cu_alloc(n * sizeof *rho); dF = cu_alloc(n * sizeof *dF);
+  CK(imdcu_download_atoms(cu, id, type, mass, pos, mom, frc, epot, rho, dF, nn, NULL));
+  CK(imdcu_download_vtypes(cu, vtype));
+  for (k = 0; k < nallcells; k++) cell_array[k].n = 0;
+  for (m = 0; m < n; m++) {
+    ivektor c = cell_coord(pos[3 * m], pos[3 * m + 1], pos[3 * m + 2]);
+    cell *to;
+    int i;
+    c = local_cell_coord(c);
+    if (c.x < 1) c.x = 1; else if (c.x > cell_dim.x - 2) c.x = cell_dim.x - 2;
+    if (c.y < 1) c.y = 1; else if (c.y > cell_dim.y - 2) c.y = cell_dim.y - 2;
+    if (c.z < 1) c.z = 1; else if (c.z > cell_dim.z - 2) c.z = cell_dim.z - 2;
+    to = PTR_3D_VV(cell_array, c, cell_dim);
+    if (to->n >= to->n_max) alloc_cell(to, to->n_max + incrsz);
+    i = to->n++;
+    NUMMER(to, i) = id[m]; SORTE(to, i) = type[m]; VSORTE(to, i) = vtype[m]; MASSE(to, i) = mass[m];
+    ORT(to, i, X) = pos[3 * m]; ORT(to, i, Y) = pos[3 * m + 1]; ORT(to, i, Z) = pos[3 * m + 2];
+    IMPULS(to, i, X) = mom[3 * m]; IMPULS(to, i, Y) = mom[3 * m + 1]; IMPULS(to, i, Z) = mom[3 * m + 2];
+    KRAFT(to, i, X) = frc[3 * m]; KRAFT(to, i, Y) = frc[3 * m + 1]; KRAFT(to, i, Z) = frc[3 * m + 2];
+    POTENG(to, i) = epot[m];
+    EAM_RHO(to, i) = rho[m]; EAM_DF(to, i) = dF[m];
+#ifdef TTM
+    NUMNEIGHS(to, i) = nn[m];
+#endif
+  }
+  free(id); free(type); free(vtype); free(nn); free(mass); free(pos); free(mom); free(frc); free(epot); free(rho); free(dF);
+  cu_host_stale = 0;
+  cu_syncs++;
+}
+
+/* ------------------------------------------------------------------ the hot-path entry points */
+
+void calc_forces(int steps)                          /* replaces imd_forces_nbl.c:295-1054 */
+{
+  double out8[8];
+  cu_attach();
+  if (!cu_resident) cu_upload();
+  if (!have_valid_nbl) CK(imdcu_invalidate_nblist(cu));   /* the host asked for a new list (imd_main_3d.c:273) */
+  CK(imdcu_calc_forces(cu, steps, out8));
+  tot_pot_energy = out8[0]; virial = out8[1];
+#ifdef P_AXIAL
+  vir_xx = out8[2]; vir_yy = out8[3]; vir_zz = out8[4];
+#endif
+  if (imdcu_short_distance(cu) > 0 && myid == 0) fprintf(stderr, "Short distance, pair, step %d!\n", steps);
+  have_valid_nbl = 1;
+  nbl_count = imdcu_nbl_count(cu);
+  nfc++;
+  cu_host_stale = 1;
+#ifdef FORCE
+  /* write_config_select(.., "force", ..) runs right after calc_forces (imd_main_3d.c:430): the wrapper syncs */
+#endif
+}
+
+void move_atoms_nve(void)                            /* replaces imd_integrate.c:35-561 */
+{
+  double out8[8];
+  int valid = 0;
+  if (cu == NULL || !cu_resident) error("imd_cuda: move_atoms_nve before the first calc_forces");
+  CK(imdcu_move_atoms_nve(cu, out8, &valid));
+  tot_kin_energy = out8[0];
+  have_valid_nbl = valid;                            /* check_nblist is fused into the integrator kernel */
+  cu_host_stale = 1;
+}
+
+void check_nblist(void)                              /* imd_forces_nbl.c:1062-1092: have_valid_nbl is already set */
+{
+}
+
+/* the list lives on the device; these reference entry points have nothing left to do on the host */
+void make_nblist(void) { have_valid_nbl = 0; }
+int  estimate_nblist_size(void) { return 0; }
+void deallocate_nblist(void) { have_valid_nbl = 0; }
+
+#ifndef TTM
+void move_atoms_ttm(void)                            /* as the reference's own stub for a non-TTM binary (imd_integrate.c:814) */
+{
+  if (myid == 0) error("the chosen ensemble TTM is not supported by this binary");
+}
+#endif
+
+#ifdef TTM
+/* init_ttm (imd_ttm.c:955-1201): derived globals other host code reads, the arrays ttm_writeout prints, the EOS
+ * tables through the reference's own reader.  The lattice itself is set up on the device at attach time. */
+void init_ttm(void)
+{
+  const char *e;
+  int i;
+  global_fd_dim.x = ttmdimx;
+  cu_ttm_P = num_cpus;
+  if ((e = getenv("IMDCU_TTM_REF_RANKS")) != NULL) cu_ttm_P = atoi(e);   /* reproduce a reference run on P ranks */
+  if (cu_ttm_P < 1 || global_fd_dim.x % cu_ttm_P != 0) error("global_fd_dim.x mod num_cpus != 0.");
+  local_fd_dim.x = global_fd_dim.x / cu_ttm_P + 2;
+  local_fd_dim.y = 3; local_fd_dim.z = 3;
+  fd_h.x = box_x.x / global_fd_dim.x; fd_h.y = box_y.y; fd_h.z = box_z.z;
+  fd_vol = fd_h.x * fd_h.y * fd_h.z;
+  max_dt_ttm = timestep / ((double) fd_n_timesteps);
+  neighvol = pow(sqrt(pair_pot.end[0]), 3.0) * 4.0 / 3.0 * M_PI;
+  xiarr_global = cu_alloc(global_fd_dim.x * sizeof(double));
+  vcomxglobal = cu_alloc(global_fd_dim.x * sizeof(double));
+  vcomyglobal = cu_alloc(global_fd_dim.x * sizeof(double));
+  vcomzglobal = cu_alloc(global_fd_dim.x * sizeof(double));
+  for (i = 0; i < global_fd_dim.x; i++) xiarr_global[i] = vcomxglobal[i] = vcomyglobal[i] = vcomzglobal[i] = 0.0;
+  if (myid == 0) {
+    printf("***************************************************\n");
+    printf("*     TWO-TEMPERATURE MODEL (device resident)     *\n");
+    printf("***************************************************\n");
+    printf("Global FD cell array dimension: %d \n", global_fd_dim.x);
+    printf("fd_h.x:%f A, fd_h.y:%f A,fd_h.z:%f A\n", fd_h.x, fd_h.y, fd_h.z);
+    printf("FD lattice laid out like a reference run on %d rank(s)\n", cu_ttm_P);
+  }
+  nn_read_table(&intp_cve_from_r_te, "../EOS_cve_from_r_te.txt");
+  nn_read_table(&intp_ee_from_r_tesqrt, "../EOS_ee_from_r_tesqrt.txt");
+  if (imdrestart > 0)
+    error("imd_cuda: restart of the FD lattice from a .ttm file (ttm_read, imd_ttm.c:1983) is not supported yet");
+}
+
+/* tmm_init (imd_tmm.c:98-190): the two data files of do_tmm.  Without them (they are missing blobs upstream)
+ * IMD_SRC_MU / IMD_SRC_ABS select the analytic Beer-Lambert source the parity builds of the reference use. */
+int tmm_init(void)
+{
+  const char *e;
+  laser_sigma_t_squared = laser_sigma_t * laser_sigma_t;
+  laser_sigma_t1_squared = laser_sigma_t1 * laser_sigma_t1;
+  omega_laser = 2.0 * M_PI * c0 / lambda;
+  laser_spot_area = (fd_h.y * 1e-10 * fd_h.z * 1e-10);
+  laser_active = false;
+  if ((e = getenv("IMD_SRC_MU")) != NULL) { cu_ttm_analytic = 1; cu_src_mu = atof(e); }
+  if ((e = getenv("IMD_SRC_ABS")) != NULL) { cu_ttm_analytic = 1; cu_src_abs = atof(e); }
+  if (!cu_ttm_analytic) {
+    cu_bb = cu_read_rows("../alu_eps_bb.dat", 3, &cu_bb_rows);
+    cu_k12 = cu_read_rows("../K12.dat", 2, &cu_k12_rows);
+    if (cu_bb == NULL || cu_k12 == NULL)
+      error("imd_cuda: ../alu_eps_bb.dat / ../K12.dat not found (set IMD_SRC_MU and IMD_SRC_ABS for the analytic source)");
+    nn_read_table(&intp_phase_from_r_ti, "../EOS_phase_from_r_ti.txt");
+  }
+  if (myid == 0)
+    printf("imd_cuda: laser source = %s, I0:%.4e W/m^2, t0:%.4e, sigma_t:%.4e\n",
+           cu_ttm_analytic ? "analytic Beer-Lambert" : "transfer-matrix method (do_tmm on the device)", I0, laser_t_0, laser_sigma_t);
+  return 0;
+}
+
+void calc_ttm(void)                                  /* replaces imd_ttm.c:75-156 */
+{
+  double o[16];
+  if (cu == NULL || !cu_resident) error("imd_cuda: calc_ttm before the first calc_forces");
+  CK(imdcu_calc_ttm(cu, steps, o));
+  diff_substeps = (int) o[0]; max_dt_ttm = o[1];
+  last_active_cell_global = last_active_cell_local = (int) o[2];
+  cur_vlattice_proc = (int) o[3];
+  Eabs_global = o[4]; Eabs_local = myid == 0 ? o[4] : 0.0;
+  /* write_eng_file sums tot_elec_energy_local over the ranks (imd_io.c:2345); the device lattice is replicated */
+  tot_elec_energy_local = myid == 0 ? o[5] : 0.0;
+  laser_active = (o[9] != 0.0);
+  tmm_time = o[10];
+}
+
+void move_atoms_ttm(void)                            /* replaces imd_integrate.c:581-811 */
+{
+  double out8[8];
+  int valid = 0;
+  if (cu == NULL || !cu_resident) error("imd_cuda: move_atoms_ttm before the first calc_forces");
+  CK(imdcu_move_atoms_ttm(cu, out8, &valid));
+  tot_kin_energy = out8[0];
+  have_valid_nbl = valid;
+  cu_host_stale = 1;
+}
+
+/* ttm_writeout (imd_ttm.c:1683-1969): <outfiles>.<number>.ttm, one line per FD cell, then the virtual lattice
+ * (natoms = -2).  The device lattice is complete on every rank, so rank 0 writes it without a gather. */
+void ttm_writeout(int number)
+{
+  const int G = global_fd_dim.x, per = G / cu_ttm_P;
+  double *cells, *xi, *vcom, *vlat;
+  char fname[512];
+  FILE *out;
+  int i;
+  if (cu == NULL || !cu_resident) return;
+  cells = cu_alloc((size_t) G * 13 * sizeof *cells); xi = cu_alloc(G * sizeof *xi);
+  vcom = cu_alloc((size_t) 3 * G * sizeof *vcom); vlat = cu_alloc((size_t) (vlatdim > 0 ? vlatdim : 1) * 6 * sizeof *vlat);
+  CK(imdcu_download_ttm(cu, cells, xi, vcom, vlat));
+  for (i = 0; i < G; i++) {
+    xiarr_global[i] = xi[i]; vcomxglobal[i] = vcom[i]; vcomyglobal[i] = vcom[G + i]; vcomzglobal[i] = vcom[2 * G + i];
+  }
+  if (myid == 0) {
+    snprintf(fname, sizeof fname, "%s.%d.ttm", outfilename, number);
+    out = fopen(fname, "w");
+    if (out == NULL) error("Cannot open ttm file for writing.\n");
+    fprintf(out, "#x y z natoms temp md_temp U xi source dens vx vy vz fd_k fd_g Z proc Ce\n");
+    for (i = 0; i < G; i++) {
+      const double *c = cells + 13 * (size_t) i;     /* natoms natoms_old temp md_temp xi dens fd_k fd_g Z ne Ce U source */
+      fprintf(out, "%d %d %d %d %e %e %e %e %e %e %e %e %e %e %e %e %d %f\n", i, 0, 0, (int) c[0], c[2], c[3], c[11], c[4],
+              c[12], c[5], vcom[i], vcom[G + i], vcom[2 * G + i], c[6], c[7], c[8], i / per, c[10]);
+    }
+    for (i = 0; i < vlatdim; i++) {
+      const double *v = vlat + 6 * (size_t) i;       /* temp md_temp fd_k fd_g Ce Z */
+      fprintf(out, "%d %d %d %d %e %e %e %e %e %e %e %e %e %e %e %e %d %f\n", i + last_active_cell_global + 1, 0, 0, -2,
+              v[0], v[1], 0.0, 0.0, 0.0, vlatdens, 0.0, 0.0, 0.0, v[2], v[3], v[5], cur_vlattice_proc, v[4]);
+    }
+    fclose(out);
+  }
+  free(cells); free(xi); free(vcom); free(vlat);
+}
+
+void ttm_read(int number)
+{
+  error("imd_cuda: ttm_read (restart of the FD lattice) is not supported yet");
+}
+#endif /* TTM */
+
+/* ------------------------------------------------------------------ writers: cell_array must be current.
+ * Linked with -Wl,--wrap=write_config,--wrap=write_config_select,--wrap=write_distrib,--wrap=write_pictures;
+ * a maintainer editing the reference would put the one call in front of these calls in imd_main_3d.c:702-735
+ * under #ifdef IMDCUDA instead. */
+void __real_write_config(int fzhlr, int steps);
+void __wrap_write_config(int fzhlr, int steps) { imdcu_sync_to_host(); __real_write_config(fzhlr, steps); }
+void __real_write_config_select(int fzhlr, char *suffix, void (*write_atoms_fun)(FILE *), void (*write_header_fun)(FILE *));
+void __wrap_write_config_select(int fzhlr, char *suffix, void (*write_atoms_fun)(FILE *), void (*write_header_fun)(FILE *))
+{
+  imdcu_sync_to_host();
+  __real_write_config_select(fzhlr, suffix, write_atoms_fun, write_header_fun);
+}
+void __real_write_distrib(int steps);
+void __wrap_write_distrib(int steps) { imdcu_sync_to_host(); __real_write_distrib(steps); }
+void __real_write_pictures(int steps);
+void __wrap_write_pictures(int steps) { imdcu_sync_to_host(); __real_write_pictures(steps); }
