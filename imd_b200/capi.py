@@ -107,6 +107,7 @@ def load():
         "imdcu_synchronize": (C.c_int, [vp]),
         "imdcu_probe_fp64": (C.c_int, [vp, c_dp]),
         "imdcu_eval_table": (C.c_int, [vp, C.c_int, C.c_int, C.c_int64, c_dp, c_dp, c_dp]),
+        "imdcu_eval_table_noalloc": (C.c_int, [vp, C.c_int, C.c_int, C.c_int64, c_dp, c_dp, c_dp]),
         "imdcu_eval_ttm_math": (C.c_int, [vp, C.c_int, C.c_int64, c_dp, c_dp, c_dp]),
     }
     for name, (res, args) in sig.items():
@@ -116,6 +117,9 @@ def load():
     L._declared = sorted(sig)
     _lib = L
     return L
+
+
+EVAL_NOALLOC_MAX = 65536      # IMDCU_EVAL_NOALLOC_MAX (include/imdcu.h)
 
 
 def _dp(a):
@@ -411,4 +415,12 @@ class Context:
         arg = np.ascontiguousarray(arg, np.float64)
         val = np.empty_like(arg); grad = np.empty_like(arg)
         self._ck(self.L.imdcu_eval_table(self.h, which, col, arg.shape[0], _dp(arg), _dp(val), _dp(grad)))
+        return val, grad
+
+    def eval_table_noalloc(self, which, arg, col=0):
+        """imdcu_eval_table_noalloc: same result, device staging in the library's static array (no cudaMalloc);
+        at most EVAL_NOALLOC_MAX arguments per call."""
+        arg = np.ascontiguousarray(arg, np.float64)
+        val = np.empty_like(arg); grad = np.empty_like(arg)
+        self._ck(self.L.imdcu_eval_table_noalloc(self.h, which, col, arg.shape[0], _dp(arg), _dp(val), _dp(grad)))
         return val, grad

@@ -1,5 +1,6 @@
 // imd_b200/csrc/api.cu -- the hot-path entry points of the C ABI (include/imdcu.h)
 #include "device.cuh"
+#include <mutex>
 
 static int check_ready(imdcu_ctx *c)
 {
@@ -214,6 +215,67 @@ extern "C" int imdcu_eval_table(imdcu_ctx *c, int which, int col, int64_t n, con
   CU_CHECK(c, cudaMemcpyAsync(grad, d + 2 * n, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   CU_CHECK(c, cudaStreamSynchronize(c->stream));
   cudaFree(d);
+  return IMDCU_OK;
+}
+
+// ----------------------------------------------------------------------------- table probe, allocation-free
+// imdcu_eval_table without its per-call cudaMalloc / cudaFree, for callers that may not allocate (code under
+// CUDA graph capture, tight serving loops, harnesses that forbid it).  The staging that imdcu_eval_table takes
+// from cudaMalloc (argument, value, gradient: 3 n doubles) is a file-scope device array of fixed size instead:
+// 3 x IMDCU_EVAL_NOALLOC_MAX doubles = 1.5 MiB, held by every GPU that loads this library until the process exits.
+//   * In HOST code `g_eval_scratch` is only a handle of the symbol, not a device address: the address is asked
+//     for once per device, with that device current (eval_scratch_address), and that pointer goes to the kernel.
+//   * Thirds are fixed (arg at 0, val at MAX, grad at 2 MAX) and every element the kernel or the copies read is
+//     written earlier in the same call, so nothing has to start at zero although the array keeps the last call's
+//     contents.
+//   * Every call on a GPU shares the one array: calls that overlap on the GPU (two contexts, two host threads,
+//     two streams) race.  This entry point synchronises its stream before it returns.
+static __device__ __align__(256) double g_eval_scratch[3 * (size_t) IMDCU_EVAL_NOALLOC_MAX];
+
+static const int kMaxScratchDevices = 64;
+static double    *g_eval_scratch_ptr[kMaxScratchDevices];      // per device, resolved once
+static std::mutex g_eval_scratch_mutex;
+
+// the device must be current
+static cudaError_t eval_scratch_address(int device, double **out)
+{
+  std::lock_guard<std::mutex> lock(g_eval_scratch_mutex);
+  if (g_eval_scratch_ptr[device] == nullptr) {
+    double *p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void **) &p, g_eval_scratch);
+    if (e != cudaSuccess) return e;
+    g_eval_scratch_ptr[device] = p;
+  }
+  *out = g_eval_scratch_ptr[device];
+  return cudaSuccess;
+}
+
+extern "C" int imdcu_eval_table_noalloc(imdcu_ctx *c, int which, int col, int64_t n, const double *arg,
+                                        double *val, double *grad)
+{
+  if (!c || which < 0 || which > 2 || !c->tab[which].set || col < 0 || col >= c->tab[which].ncols || n < 0 ||
+      (n > 0 && (!arg || !val || !grad)))
+    return c ? c->fail(IMDCU_EINVAL, "imdcu_eval_table_noalloc: bad argument") : IMDCU_EINVAL;
+  if (n > IMDCU_EVAL_NOALLOC_MAX)
+    return c->fail(IMDCU_EINVAL, "imdcu_eval_table_noalloc: n = " + std::to_string((long long) n) +
+                   " exceeds the static scratch of IMDCU_EVAL_NOALLOC_MAX = " + std::to_string(IMDCU_EVAL_NOALLOC_MAX) +
+                   " arguments per call (split the call, or use imdcu_eval_table)");
+  if (c->interp == IMDCU_INTERP_SPLINE && !c->tab[which].raw2)
+    return c->fail(IMDCU_EINVAL, "imdcu_eval_table_noalloc: spline mode needs imdcu_set_table2");
+  if (c->device < 0 || c->device >= kMaxScratchDevices)
+    return c->fail(IMDCU_EINVAL, "imdcu_eval_table_noalloc: device ordinal beyond the per-device address table");
+  CU_CHECK(c, cudaSetDevice(c->device));
+  if (n == 0) return IMDCU_OK;
+  double *d = nullptr;
+  CU_CHECK(c, eval_scratch_address(c->device, &d));
+  double *d_arg = d, *d_val = d + IMDCU_EVAL_NOALLOC_MAX, *d_grad = d + 2 * (size_t) IMDCU_EVAL_NOALLOC_MAX;
+  CU_CHECK(c, cudaMemcpyAsync(d_arg, arg, n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  k_eval_table<<<div_up(n, 256), 256, 0, c->stream>>>(imdcu_tab_view(c->tab[which]), c->interp, col, n, d_arg, d_val, d_grad);
+  CU_CHECK(c, cudaGetLastError());
+  c->count_launch();
+  CU_CHECK(c, cudaMemcpyAsync(val, d_val, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CU_CHECK(c, cudaMemcpyAsync(grad, d_grad, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CU_CHECK(c, cudaStreamSynchronize(c->stream));
   return IMDCU_OK;
 }
 

@@ -274,6 +274,23 @@ int  imdcu_probe_fp64(imdcu_ctx *ctx, double *gflops);
 int  imdcu_eval_table(imdcu_ctx *ctx, int which, int col, int64_t n, const double *arg,
                       double *val, double *grad);
 
+/* imdcu_eval_table for callers that may not allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid
+ * cudaMalloc.  Same arguments (host pointers), same kernel, same results as imdcu_eval_table, but the call
+ * makes no cudaMalloc / cudaFree and calls no allocating library routine: the 3 n doubles of device staging
+ * live in a file-scope device array of the library, 3 x IMDCU_EVAL_NOALLOC_MAX doubles = 1.5 MiB that every
+ * GPU which loads libimdcu.so holds until the process exits.
+ *   - n > IMDCU_EVAL_NOALLOC_MAX is rejected with IMDCU_EINVAL and a message naming the limit.
+ *   - The first call on a device looks up the array's device address (once per device); make that call
+ *     outside a capture.
+ *   - All calls on one GPU share the array, which keeps the last call's contents; every element read is
+ *     written earlier in the same call, so nothing needs clearing.  Calls that OVERLAP on the GPU (several
+ *     contexts, host threads or streams on the same device) race on it: serialise them.  The call
+ *     synchronises its stream before returning. */
+#define IMDCU_EVAL_NOALLOC_MAX 65536
+int  imdcu_eval_table_noalloc(imdcu_ctx *ctx, int which, int col, int64_t n, const double *arg,
+                              double *val, double *grad);
+
 /* single-function probe of the device log/exp/pow/div/sqrt used by the wide-range models
  * (imd_ttm.c:2191-2399 call libm): op 0 log(a), 1 exp(a), 2 pow(a,b), 3 a/b, 4 sqrt(a), 5 1/a */
 int  imdcu_eval_ttm_math(imdcu_ctx *ctx, int op, int64_t n, const double *a, const double *b, double *out);
