@@ -204,11 +204,11 @@ extern "C" int imdcu_eval_table(imdcu_ctx *c, int which, int col, int64_t n, con
     return c ? c->fail(IMDCU_EINVAL, "imdcu_eval_table: bad argument") : IMDCU_EINVAL;
   cudaSetDevice(c->device);
   if (n == 0) return IMDCU_OK;
+  if (c->interp == IMDCU_INTERP_SPLINE && !c->tab[which].raw2)       // before the allocation: nothing to release
+    return c->fail(IMDCU_EINVAL, "imdcu_eval_table: spline mode needs imdcu_set_table2");
   double *d = nullptr;
   CU_CHECK(c, cudaMalloc(&d, 3 * n * sizeof(double)));
   CU_CHECK(c, cudaMemcpyAsync(d, arg, n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
-  if (c->interp == IMDCU_INTERP_SPLINE && !c->tab[which].raw2)
-    return c->fail(IMDCU_EINVAL, "imdcu_eval_table: spline mode needs imdcu_set_table2");
   k_eval_table<<<div_up(n, 256), 256, 0, c->stream>>>(imdcu_tab_view(c->tab[which]), c->interp, col, n, d, d + n, d + 2 * n);
   c->count_launch();
   CU_CHECK(c, cudaMemcpyAsync(val, d + n, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
