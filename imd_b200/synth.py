@@ -368,6 +368,25 @@ def write_param_file(path: str, spec: EamSpec, box_param: Sequence[int], maxstep
         f.write(txt.getvalue())
 
 
+def write_config_file(path: str, pos: np.ndarray, mom: np.ndarray, mass, box: np.ndarray, types=None) -> None:
+    """IMD ASCII configuration as read_atoms parses it (imd_io_3d.c:52-600; header as write_config writes it,
+    imd_io.c:3357-3460): number type mass x y z vx vy vz.  The reader multiplies the velocities by the mass, so
+    v = p / m is written; %.17g keeps every double.  With `box_from_header 1` the box comes from the #X #Y #Z
+    lines (read_atoms then adds shiftx_front + shiftx_rear to box_x.x and shiftx_front to every x)."""
+    n = pos.shape[0]
+    mass = np.broadcast_to(np.asarray(mass, np.float64), (n,))
+    types = np.zeros(n, np.int32) if types is None else np.asarray(types, np.int32)
+    with open(path, "w") as f:
+        f.write("#F A 1 1 1 3 3 0\n#C number type mass x y z vx vy vz\n")
+        for tag, row in zip("XYZ", np.asarray(box, np.float64)):
+            f.write("#%s %.17g %.17g %.17g\n" % (tag, row[0], row[1], row[2]))
+        f.write("#E\n")
+        for i in range(n):
+            f.write("%d %d %.17g %.17g %.17g %.17g %.17g %.17g %.17g\n"
+                    % (i + 1, types[i], mass[i], pos[i, 0], pos[i, 1], pos[i, 2],
+                       mom[i, 0] / mass[i], mom[i, 1] / mass[i], mom[i, 2] / mass[i]))
+
+
 # ----------------------------------------------------------------------------- TTM inputs
 
 AMU = 1.66053907e-27
