@@ -107,6 +107,8 @@ def load():
         "imdcu_synchronize": (C.c_int, [vp]),
         "imdcu_probe_fp64": (C.c_int, [vp, c_dp]),
         "imdcu_eval_table": (C.c_int, [vp, C.c_int, C.c_int, C.c_int64, c_dp, c_dp, c_dp]),
+        "imdcu_distrib": (C.c_int, [vp, C.POINTER(C.c_int), c_dp, c_dp, C.POINTER(C.c_float), C.POINTER(C.c_float),
+                                    C.POINTER(C.c_float), C.POINTER(C.c_float)]),
         "imdcu_eval_table_noalloc": (C.c_int, [vp, C.c_int, C.c_int, C.c_int64, c_dp, c_dp, c_dp]),
         "imdcu_eval_ttm_math": (C.c_int, [vp, C.c_int, C.c_int64, c_dp, c_dp, c_dp]),
     }
@@ -410,6 +412,17 @@ class Context:
         v = C.c_double(0.0)
         self._ck(self.L.imdcu_probe_fp64(self.h, C.byref(v)))
         return v.value
+
+    def distrib(self, dim, ll, ur):
+        """imdcu_distrib: per-bin sums (float32) of this rank's atoms: num, ekin, epot, vxavg."""
+        d = (C.c_int * 3)(*[int(x) for x in dim])
+        lo = np.ascontiguousarray(ll, np.float64); hi = np.ascontiguousarray(ur, np.float64)
+        size = int(dim[0]) * int(dim[1]) * int(dim[2])
+        out = {k: np.zeros(size, np.float32) for k in ("num", "ekin", "epot", "vxavg")}
+        fp = lambda a: a.ctypes.data_as(C.POINTER(C.c_float))  # noqa: E731
+        self._ck(self.L.imdcu_distrib(self.h, d, _dp(lo), _dp(hi), fp(out["num"]), fp(out["ekin"]), fp(out["epot"]),
+                                      fp(out["vxavg"])))
+        return out
 
     def eval_table(self, which, arg, col=0):
         arg = np.ascontiguousarray(arg, np.float64)

@@ -243,6 +243,8 @@ struct imdcu_ctx {
   DevBuf<int>     key, key_alt, perm, perm_alt;
   DevBuf<unsigned char> cub_tmp;
   DevBuf<double>  stage;                     // host<->device staging (atoms.cu)
+  DevBuf<double>  dist_sums;                 // spatial distributions (distrib.cu): [4][dist_size] sums
+  DevBuf<float>   dist_out;                  //   the same as float, as they cross the ABI
 
   // cells (extended grid)
   int  ncell_ext = 0;

@@ -101,6 +101,7 @@ extern "C" int imdcu_destroy(imdcu_ctx *c)
   c->type.release(); c->type_alt.release(); c->vtype.release(); c->vtype_alt.release();
   c->id.release(); c->id_alt.release(); c->numneighs.release();
   c->key.release(); c->key_alt.release(); c->perm.release(); c->perm_alt.release();
+  c->dist_sums.release(); c->dist_out.release();
   c->cub_tmp.release(); c->stage.release(); c->cell_begin.release(); c->cell_count.release();
   c->d_gplan.release(); c->gcell_off.release(); c->ghost_src.release(); c->ghost_code.release();
   c->ghost_root.release(); c->ghost_tcode.release(); c->ghost_raw.release();

@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define IMDCU_ABI_VERSION 2
+#define IMDCU_ABI_VERSION 3
 
 #define IMDCU_OK            0
 #define IMDCU_EINVAL       -1   /* bad argument / call order                       */
@@ -125,6 +125,17 @@ int  imdcu_download_atoms(imdcu_ctx *ctx, int32_t *id, int32_t *type, double *ma
 
 /* VSORTE of the owned atoms, same order as imdcu_download_atoms (write_atoms_config prints it, imd_io_3d.c:778) */
 int  imdcu_download_vtypes(imdcu_ctx *ctx, int32_t *vtype);
+
+/* Spatial distributions on the device (write_distrib, imd_distrib.c:33-218): the per-rank part of
+ * make_distrib_density (:377-411) and of make_write_distrib_select's atom loop (:678-716) with dist_Ekin_fun
+ * (:219), dist_Epot_fun (:230) and dist_vxavg_fun (:364).  dim / ll / ur are dist_dim, dist_ll, dist_ur; the bin
+ * of an atom is (int)(dim / (ur - ll) * (x - ll)) per direction with C's truncation, flat index
+ * (nx * dim[1] + ny) * dim[2] + nz, atoms outside are skipped.  Output: per-bin SUMS over this rank's atoms
+ * (count, p.p / 2m, POTENG, p_x / m), accumulated in double and returned as float like the reference's arrays
+ * before its MPI_Reduce; any pointer may be NULL.  Division by the count, the reduction over ranks and the file
+ * formats stay the host's (:720-800).  dist_int output then downloads 4 dist_size floats instead of every atom. */
+int  imdcu_distrib(imdcu_ctx *ctx, const int dim[3], const double ll[3], const double ur[3],
+                   float *num, float *ekin, float *epot, float *vxavg);
 
 /* ------------------------------------------------------------------ hot path */
 /* calc_forces (imd_forces_nbl.c:295-1054): rebuilds cells + neighbour list when the

@@ -24,7 +24,7 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(L, n), "missing export %s" % n
     # and the binding declares all of them
     assert set(names) == set(L._declared), set(names) ^ set(L._declared)
-    assert L.imdcu_abi_version() == 2
+    assert L.imdcu_abi_version() == 3
 
 
 def test_no_cpu_fallback():

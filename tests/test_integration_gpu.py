@@ -108,7 +108,8 @@ def test_chkpt_written_by_cuda_build_restarts_in_reference(tmp_path):
     the file equals the reference's own checkpoint of that step, and the PLAIN reference restarted from it
     (-r 1) lands on the uninterrupted reference run."""
     steps, at = 40, 20
-    extra = "checkpt_int  %d\n" % at
+    extra = ("checkpt_int  %d\ndist_int %d\ndist_dim 5 4 3\ndist_Ekin_flag 1\ndist_Epot_flag 1\ndist_dens_flag 1\n"
+             % (at, at))
     wa, wb = str(tmp_path / "ref"), str(tmp_path / "cuda")
     for w in (wa, wb):
         os.makedirs(w)
@@ -123,6 +124,14 @@ def test_chkpt_written_by_cuda_build_restarts_in_reference(tmp_path):
     err = (np.abs(ca[:, 3:] - cb[:, 3:]).max(axis=0) / scale).max()
     print("run.1.chkpt (step %d), CUDA build vs reference: max rel err over columns %.2e" % (at, err))
     assert err < 1e-8
+    # write_distrib (imd_distrib.c:33-218) of the same steps, the reference's own writer behind sync_to_host:
+    # binary float32 after the header; the count (density) is exact, the averages are float sums in cell order
+    for n in (0, 1, 2):
+        for key, tol in (("dens", 0.0), ("Ekin", 1e-5), ("Epot", 1e-5)):
+            fa, fb = (np.frombuffer(open(os.path.join(w, "out", "run.%d.%s" % (n, key)), "rb").read().split(b"#E\n", 1)[1],
+                                    dtype="<f4") for w in (wa, wb))
+            assert fa.shape == fb.shape == (60,)
+            assert np.abs(fa - fb).max() <= tol * np.abs(fa).max(), (n, key, np.abs(fa - fb).max())
     eng_full = eng_of(wa)
     rc = run(REF_BIN, wb, "-r", "1")                                # the reference continues the CUDA build's run
     assert rc.returncode == 0, rc.stdout[-3000:]
