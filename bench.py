@@ -16,7 +16,7 @@ value : whole-job atom-steps/s with atoms resident in HBM (device-timed, CUDA ev
 e2e   : the same step driven through the C ABI with HOST buffers: every step uploads
         positions+momenta from pinned host memory (imdcu_update_atoms) and downloads the
         new positions+momenta (the next step's inputs) and the energy sums.
-roofline : dominant kernel (k_eam_pass1_fused), algorithmic bytes (64 + 4*N_h per atom,
+roofline : dominant kernel (k_eam_pass1_rep4), algorithmic bytes (64 + 4*N_h per atom,
         SURVEY.md 8d) / its mean launch time measured live with CUDA events.
 cpu_baseline : the UNMODIFIED reference (oracle/_ref, author's flags), its own MPI build run
         over oracle/shmpi with one rank per host core (cpu_dim P 1 1), a bounded sample of the
@@ -563,7 +563,8 @@ def our_arm(args, rank, local_rank, world):
         fp64_peak = ctx.probe_fp64()
         fp64_ach = alg_flops / (p1_ms * 1e-3) / 1e9
         traffic, traffic_src = measured_traffic("k_eam_pass1", n_loc)
-        roofline = {"kernel": "k_eam_pass1_fused", "bound": "l1", "achieved": achieved, "peak": peak,
+        p1_kernel = {"0": "k_eam_pass1", "1": "k_eam_pass1_fused"}.get(os.environ.get("IMDCU_FUSED_TABLE", "2"), "k_eam_pass1_rep4")
+        roofline = {"kernel": p1_kernel, "bound": "l1", "achieved": achieved, "peak": peak,
                     "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                     "peak_source": peak_src, "alg_bytes_per_launch": alg_bytes, "ms_per_launch": p1_ms,
                     "fp64": {"achieved": fp64_ach, "peak": fp64_peak, "unit": "GFLOP/s", "frac": fp64_ach / fp64_peak,
@@ -572,10 +573,10 @@ def our_arm(args, rank, local_rank, world):
                     "pass2": {"kernel": "k_eam_pass2", "ms_per_launch": p2_ms,
                               "achieved": (80 + 4 * N_H_AL) * n_loc / (p2_ms * 1e-3) / 1e9,
                               "frac": (80 + 4 * N_H_AL) * n_loc / (p2_ms * 1e-3) / 1e9 / peak},
-                    "note": "binding unit by ncu: the L1 data pipe (l1tex__data_pipe_lsu_wavefronts ~90 % of peak: per pair one "
-                            "random 48-byte table row from shared memory and one 32-byte gather); HBM and FP64 fractions are "
-                            "reported against their measured peaks, the north star's >= 0.60 of HBM is NOT met by the force "
-                            "kernels (profiles/r02_*.txt, DESIGN.md section 3)"}
+                    "note": "binding unit by ncu: the L1 data pipe (l1tex__data_pipe_lsu_wavefronts 92 % of peak: per pair three "
+                            "16-byte table rows from shared memory and one 32-byte gather), with issue slots 53 % and the FP64 "
+                            "pipe 44 % busy; HBM and FP64 fractions are reported against their measured peaks, the north star's "
+                            ">= 0.60 of HBM is NOT met by the force kernels (profiles/r02f_rep4_ncu.txt, DESIGN.md section 3)"}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

@@ -216,6 +216,9 @@ struct imdcu_ctx {
   int    pdecay = 0; double xipdecay = 0, ramp_start = 0, ramp_end = 1;
   double *fused_coef = nullptr;              // pair + rho rows interleaved (context.cu: imdcu_fused_table)
   int    fused_state = 0;                    // 0 not looked at, 1 built, -1 tables do not share a grid
+  double *rep4_tab = nullptr;                // raw {pair, rho} rows, four bank-staggered copies (imdcu_rep4_table)
+  int    rep4_state = 0;
+  size_t rep4_bytes = 0;
   bool   ttm_isolate = true;                 // forked k_ttm_grid takes a whole SM (IMDCU_TTM_ISOLATE)
   size_t ttm_isolate_smem = 0;               // dynamic smem request that keeps k_eam_pass2 CTAs off that SM
   int    fuse_ttm_steps = -1;                // >= 0: imdcu_eam_forces forks calc_ttm(steps) between its passes
@@ -223,7 +226,8 @@ struct imdcu_ctx {
   // kernel-selection knobs (imdcu_set_tuning; the IMDCU_* environment variables give the defaults at create)
   struct Tune {
     int lpa = 0;                             // lanes per atom of the EAM passes: 0 = by system size, 1/2/4/8
-    int fused_table = 1;                     // k_eam_pass1_fused when the pair and rho tables share their grid
+    int rep4_block = 896;                    // threads per CTA of k_eam_pass1_rep4 (896 or 768)
+    int fused_table = 2;                     // pass 1 when the pair and rho tables share their grid: 1 k_eam_pass1_fused, 2 k_eam_pass1_rep4, 0 general kernel
     int ttm_overlap = 1;                     // imdcu_run_ttm: lattice kernel beside EAM pass 2
     int ttm_lat_smem = 1;                    // k_ttm_grid keeps the lattices in shared memory
     int ttm3d_tiled = 0;                     // 3-D sweep: 2.5-D tiled kernel instead of the direct one
@@ -363,6 +367,7 @@ __device__ __host__ inline int imdcu_combine_code(int pc, int code)
   return (pc % 3 - 1 + code % 3 - 1 + 1) + 3 * ((pc / 3) % 3 - 1 + (code / 3) % 3 - 1 + 1) + 9 * (pc / 9 - 1 + code / 9 - 1 + 1);
 }
 const double *imdcu_fused_table(imdcu_ctx *ctx);                       // context.cu
+const double *imdcu_rep4_table(imdcu_ctx *ctx, size_t *bytes);         // context.cu
 void imdcu_ttm_release(imdcu_ctx *ctx);                                // ttm.cu
 int  imdcu_ttm_fork(imdcu_ctx *ctx, int steps);                        // ttm.cu
 int  imdcu_ttm_join(imdcu_ctx *ctx, double out16[16]);

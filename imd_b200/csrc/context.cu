@@ -63,7 +63,8 @@ extern "C" int imdcu_create(imdcu_ctx **out, int device)
   {
     auto env_int = [](const char *name, int dflt) { const char *e = getenv(name); return e && *e ? atoi(e) : dflt; };
     c->tune.lpa = env_int("IMDCU_LPA", 0);
-    c->tune.fused_table = env_int("IMDCU_FUSED_TABLE", 1);
+    c->tune.fused_table = env_int("IMDCU_FUSED_TABLE", 2);
+    c->tune.rep4_block = env_int("IMDCU_REP4_BLOCK", 896);
     c->tune.ttm_overlap = env_int("IMDCU_TTM_OVERLAP", 1);
     c->tune.ttm_lat_smem = env_int("IMDCU_TTM_LAT_SMEM", 1);
     const char *e3 = getenv("IMDCU_TTM3D");
@@ -107,6 +108,7 @@ extern "C" int imdcu_destroy(imdcu_ctx *c)
   c->ghost_root.release(); c->ghost_tcode.release(); c->ghost_raw.release();
   c->nbl_idx.release(); c->nbl_num.release(); c->partials.release(); c->d_restrictions.release();
   if (c->fused_coef) cudaFree(c->fused_coef);
+  if (c->rep4_tab) cudaFree(c->rep4_tab);
   imdcu_ttm_release(c);
   imdcu_ttm3d_release(c); imdcu_nrb_release(c);
   imdcu_multi_release(c);
@@ -147,6 +149,8 @@ extern "C" int imdcu_set_table(imdcu_ctx *c, int which, int ncols, int maxsteps,
   DevTable &t = c->tab[which];
   if (c->fused_coef) { cudaFree(c->fused_coef); c->fused_coef = nullptr; }
   c->fused_state = 0;
+  if (c->rep4_tab) { cudaFree(c->rep4_tab); c->rep4_tab = nullptr; }
+  c->rep4_state = 0;
   if (t.coef) { cudaFree(t.coef); t.coef = nullptr; }
   if (t.begin) { cudaFree(t.begin); t.begin = nullptr; }
   if (t.raw) { cudaFree(t.raw); t.raw = nullptr; }
@@ -238,6 +242,36 @@ const double *imdcu_fused_table(imdcu_ctx *c)
   return c->fused_coef;
 }
 
+// Raw pair and rho values {pair[k], rho[k]} as 16-byte rows, FOUR copies interleaved in every 128-byte line:
+// row k of copy r sits at 16-byte slot 8 (k >> 1) + 2 r + (k & 1).  A lane reads copy (lane & 3), so the shared-memory
+// bank group of its three loads (rows k, k+1, k+2 of PAIR_INT2, potaccess.h:344-346) is fixed by the lane and the
+// parity of k instead of being random in k: two lanes of a quarter warp share a copy and collide only when their
+// rows have the same parity (k_eam_pass1_rep4).  Same conditions as imdcu_fused_table; *bytes = size to stage.
+const double *imdcu_rep4_table(imdcu_ctx *c, size_t *bytes)
+{
+  *bytes = c->rep4_bytes;
+  if (c->rep4_state != 0) return c->rep4_state > 0 ? c->rep4_tab : nullptr;
+  c->rep4_state = -1;
+  const DevTable &p = c->tab[IMDCU_TAB_PAIR], &r = c->tab[IMDCU_TAB_RHO];
+  if (!p.set || !r.set || p.ncols != 1 || r.ncols != 1 || p.nrows != r.nrows) return nullptr;
+  if (p.h_begin[0] != r.h_begin[0] || p.h_end[0] != r.h_end[0] || p.h_invstep[0] != r.h_invstep[0] ||
+      p.h_len[0] != r.h_len[0])
+    return nullptr;
+  const size_t rows = (size_t) p.maxsteps + 2, lines = (rows + 1) / 2;
+  std::vector<double> f(lines * 16, 0.0);
+  for (size_t k = 0; k < rows; k++)
+    for (int rep = 0; rep < 4; rep++) {
+      const size_t slot = 8 * (k >> 1) + 2 * rep + (k & 1);
+      f[2 * slot] = p.h_table[k]; f[2 * slot + 1] = r.h_table[k];
+    }
+  if (cudaMalloc(&c->rep4_tab, f.size() * sizeof(double)) != cudaSuccess) { c->rep4_tab = nullptr; return nullptr; }
+  if (imdcu_h2d(c, c->rep4_tab, f.data(), f.size() * sizeof(double)) != cudaSuccess) return nullptr;
+  c->rep4_bytes = f.size() * sizeof(double);
+  *bytes = c->rep4_bytes;
+  c->rep4_state = 1;
+  return c->rep4_tab;
+}
+
 // ----------------------------------------------------------------------------- tuning
 extern "C" int imdcu_set_tuning(imdcu_ctx *c, const char *key, int value)
 {
@@ -246,7 +280,14 @@ extern "C" int imdcu_set_tuning(imdcu_ctx *c, const char *key, int value)
   if (k == "lpa") {
     if (value != 0 && value != 1 && value != 2 && value != 4 && value != 8) return c->fail(IMDCU_EINVAL, "lpa: 0, 1, 2, 4 or 8");
     c->tune.lpa = value;
-  } else if (k == "fused_table") c->tune.fused_table = value != 0;
+  } else if (k == "fused_table") {
+    if (value < 0 || value > 2) return c->fail(IMDCU_EINVAL, "fused_table: 0 (general kernel), 1 (48-byte rows), 2 (raw rows, four bank-staggered replicas)");
+    c->tune.fused_table = value;
+  }
+  else if (k == "rep4_block") {
+    if (value != 896 && value != 768) return c->fail(IMDCU_EINVAL, "rep4_block: 896 or 768");
+    c->tune.rep4_block = value;
+  }
   else if (k == "ttm_overlap") c->tune.ttm_overlap = value != 0;
   else if (k == "ttm_lat_smem") c->tune.ttm_lat_smem = value != 0;
   else if (k == "ttm3d_tiled") c->tune.ttm3d_tiled = value != 0;

@@ -64,6 +64,8 @@ struct EamArgs {
   int *numneighs;                // [n]
   TabView pair, rhot, emb;
   const double *fused;           // [nrows][6] {p0,dv,d2v | r0,drv,d2rv}: pair + rho rows on a common r^2 grid, or null
+  const double *rep4;            // raw {pair[k], rho[k]} rows, four bank-staggered copies (context.cu: imdcu_rep4_table), or null
+  unsigned rep4_bytes;
   double *partials; unsigned int *ticket; double *results; int *flags;
   int count_ttm;                 // fill numneighs
 };
@@ -338,6 +340,96 @@ EAM_PRAGMA_UNROLL(EAM_UNROLL)
   grid_reduce<2, 0>(acc, a.partials, a.ticket, a.results);
 }
 
+// Pass 1 as k_eam_pass1_fused, but with fewer shared-memory bank conflicts: the table holds the RAW values
+// {pair[k], rho[k]} as 16-byte rows in four interleaved copies (imdcu_rep4_table), a lane reads rows k, k+1, k+2 of
+// copy (lane & 3) and forms dv = p1 - p0, d2v = p2 - 2 p1 + p0 itself -- the macro's own operations
+// (potaccess.h:344-349), so the results equal the precomputed rows bit for bit.  Slot of row k in copy r:
+// 8 (k >> 1) + 2 r + (k & 1), i.e. the bank group of a load is 2 r + parity: two lanes of a quarter warp share a copy
+// and conflict only when their rows have equal parity, where 48-byte rows at random k collide ~2.1-fold.
+template <int LPA, int BLOCK>
+__global__ void __launch_bounds__(BLOCK, 1)
+k_eam_pass1_rep4(EamArgs a)
+{
+  extern __shared__ __align__(16) double s_tab[];
+  __shared__ __align__(8) unsigned long long s_bar;
+  {
+    const size_t fb = a.rep4_bytes;
+    if (threadIdx.x == 0) mbar_init(&s_bar, 1);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      mbar_expect_tx(&s_bar, (unsigned) fb);
+      for (size_t off = 0; off < fb; off += 65536)
+        bulk_g2s((char *) s_tab + off, (const char *) a.rep4 + off, (unsigned) (fb - off < 65536 ? fb - off : 65536), &s_bar);
+    }
+    mbar_wait(&s_bar, 0);
+  }
+  const TabCol tp = tab_col(a.pair, s_tab, 0);           // begin, end, invstep (identical for the rho column)
+  const double rho_end = a.rhot.end[0];
+  const double two_invstep = 2 * tp.invstep;
+  const double2 *tab = reinterpret_cast<const double2 *>(s_tab) + 2 * (threadIdx.x & 3);   // my copy
+  const int apb = BLOCK / LPA;
+  const int sub = threadIdx.x % LPA;
+  double acc[2] = {0.0, 0.0};
+  int is_short = 0;
+  for (int base = blockIdx.x * apb; base < a.n; base += gridDim.x * apb) {
+    const int i = base + threadIdx.x / LPA;
+    const bool live = i < a.n;
+    double fx = 0, fy = 0, fz = 0, ee = 0, vir = 0, rh = 0;
+    int nn = 0;
+    if (live) {
+      const double4 pi = a.pos4[i];
+      const int num = a.nbl_num[i];
+      const int *slot = a.nbl_idx + ((size_t) (i >> 5) * a.cap) * 32 + (i & 31);
+      NbrPipe<LPA, false> np(a.pos4, a.type, slot, num, sub);
+EAM_PRAGMA_UNROLL(EAM_UNROLL)
+      for (int k = 0; k < np.cnt; k++) {
+        int jt_unused = 0;
+        const double4 pj = np.next(a.pos4, a.type, k, jt_unused);
+        const double dx = pj.x - pi.x, dy = pj.y - pi.y, dz = pj.z - pi.z;
+        const double r2 = r2_exact(dx, dy, dz);
+        if (r2 <= tp.end) {                                // pair: r2 <= end, rho: r2 < end (same end)
+          if (a.count_ttm) nn++;
+          int kk; double chi;
+          tab_index(tp, r2, kk, chi, is_short);
+          const int odd = kk & 1;
+          const double2 *row = tab + 8 * (kk >> 1) + odd;
+          const double2 t0 = row[0], t1 = row[odd ? 7 : 1], t2 = row[8];   // rows kk, kk+1, kk+2: {pair, rho}
+          const double dv = t1.x - t0.x, d2v = (t2.x - 2 * t1.x) + t0.x;
+          const double h = 0.5 * chi * (chi - 1);
+          const double pot = t0.x + chi * dv + h * d2v;
+          const double grad = two_invstep * (dv + (chi - 0.5) * d2v);
+          fx += dx * grad; fy += dy * grad; fz += dz * grad;
+          ee += 0.5 * pot;
+          vir -= 0.5 * (r2 * grad);
+          if (r2 < rho_end) {
+            const double drv = t1.y - t0.y, d2rv = (t2.y - 2 * t1.y) + t0.y;
+            rh += t0.y + chi * drv + h * d2rv;
+          }
+        }
+      }
+    }
+    if (LPA > 1) {
+      fx = sub_sum<LPA>(fx); fy = sub_sum<LPA>(fy); fz = sub_sum<LPA>(fz);
+      ee = sub_sum<LPA>(ee); vir = sub_sum<LPA>(vir); rh = sub_sum<LPA>(rh);
+      nn = (int) sub_sum<LPA>((double) nn);
+    }
+    if (live && sub == 0) {
+      double pot, dF; int idummy = 0;
+      TabCol te = tab_col(a.emb, a.emb.coef, 0);
+      pair_int2(te, rh, pot, dF, idummy);
+      ee += pot;
+      a.frc4[i] = make_double4(fx, fy, fz, ee);
+      a.rho[i] = rh;
+      a.dF[i] = dF;
+      a.pos4[i].w = dF;
+      if (a.count_ttm) a.numneighs[i] = nn;
+      acc[0] += ee; acc[1] += vir;
+    }
+  }
+  if (is_short) a.flags[2] = 1;
+  grid_reduce<2, 0>(acc, a.partials, a.ticket, a.results);
+}
+
 template <int LPA, bool SMEM, bool MULTI, int INTERP>
 __global__ void __launch_bounds__(EAM_BLOCK2, EAM_MINB2)
 k_eam_pass2(EamArgs a)
@@ -448,16 +540,27 @@ static int run_passes(imdcu_ctx *c, EamArgs &a, size_t smem1, size_t smem2)
 {
   int g1 = 0, g2 = 0;
   const bool fused = SMEM && !MULTI && INTERP == 0 && a.fused;
-  if (fused) RET_IF(launch_cfg(c, k_eam_pass1_fused<LPA>, EAM_BLOCK1, smem1, &g1));
+  const bool rep4 = fused && a.rep4 && a.rep4_bytes + 1024 <= c->smem_optin;
+  // block size of the rep4 kernel: 896 threads leave 72 registers (40 bytes spilled), 768 threads 80 registers (no spill); ptxas budgets registers
+  // for the thread count rounded up to a multiple of 128, so nothing in between helps
+  const int b4 = (LPA == 1 && c->tune.rep4_block == 768) ? 768 : EAM_BLOCK1;
+  if (rep4) {
+    smem1 = a.rep4_bytes;
+    if (LPA == 1 && b4 == 768) RET_IF(launch_cfg(c, k_eam_pass1_rep4<1, 768>, 768, smem1, &g1));
+    else RET_IF(launch_cfg(c, k_eam_pass1_rep4<LPA, EAM_BLOCK1>, EAM_BLOCK1, smem1, &g1));
+  }
+  else if (fused) RET_IF(launch_cfg(c, k_eam_pass1_fused<LPA>, EAM_BLOCK1, smem1, &g1));
   else RET_IF(launch_cfg(c, k_eam_pass1<LPA, SMEM, MULTI, INTERP>, EAM_BLOCK1, smem1, &g1));
   RET_IF(launch_cfg(c, k_eam_pass2<LPA, SMEM, MULTI, INTERP>, EAM_BLOCK2, smem2, &g2));
-  g1 = std::min(g1, div_up(a.n, EAM_BLOCK1 / LPA));
+  g1 = std::min(g1, div_up(a.n, (rep4 ? b4 : EAM_BLOCK1) / LPA));
   g2 = std::min(g2, div_up(a.n, EAM_BLOCK2 / LPA));
   CU_CHECK(c, c->partials.ensure((size_t) std::max(g1, g2) * 4 + 64));
   a.partials = c->partials.p;
   {
     PhaseTimer pt(c, 3);
-    if (fused) k_eam_pass1_fused<LPA><<<g1, EAM_BLOCK1, smem1, c->stream>>>(a);
+    if (rep4 && LPA == 1 && b4 == 768) k_eam_pass1_rep4<1, 768><<<g1, 768, smem1, c->stream>>>(a);
+    else if (rep4) k_eam_pass1_rep4<LPA, EAM_BLOCK1><<<g1, EAM_BLOCK1, smem1, c->stream>>>(a);
+    else if (fused) k_eam_pass1_fused<LPA><<<g1, EAM_BLOCK1, smem1, c->stream>>>(a);
     else k_eam_pass1<LPA, SMEM, MULTI, INTERP><<<g1, EAM_BLOCK1, smem1, c->stream>>>(a);
     c->count_launch();
   }
@@ -511,6 +614,12 @@ int imdcu_eam_forces(imdcu_ctx *c, double out8[8])
   a.rhot = imdcu_tab_view(c->tab[IMDCU_TAB_RHO]);
   a.emb = imdcu_tab_view(c->tab[IMDCU_TAB_EMBED]);
   a.fused = c->interp == IMDCU_INTERP_3POINT ? imdcu_fused_table(c) : nullptr;
+  a.rep4 = nullptr; a.rep4_bytes = 0;
+  if (a.fused && c->tune.fused_table == 2) {
+    size_t rb = 0;
+    a.rep4 = imdcu_rep4_table(c, &rb);
+    a.rep4_bytes = (unsigned) rb;
+  }
   a.partials = nullptr; a.ticket = c->d_ticket; a.results = c->d_results; a.flags = c->d_flags;
   a.count_ttm = 1;
   if (a.n > 0) {

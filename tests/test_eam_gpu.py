@@ -20,11 +20,12 @@ def rel_err(a, b, floor=1e-2):
 
 
 # kernel instantiations (imdcu_set_tuning): lanes per atom of the EAM passes x interleaved-row pass 1.
-# lpa = 1 with fused = 1 is what bench.py times (k_eam_pass1_fused<1>, k_eam_pass2<1,...>); 0 = by system size
-VARIANTS = [(0, 1), (1, 1), (1, 0), (2, 1), (4, 1), (4, 0), (8, 0)]
+# lpa = 1 with fused = 2 is what bench.py times (k_eam_pass1_rep4<1,896>: raw table rows in four bank-staggered
+# copies; k_eam_pass2<1,...>); fused = 1: k_eam_pass1_fused (48-byte rows), 0: the general kernel; lpa 0 = by system size
+VARIANTS = [(0, 1), (1, 1), (1, 0), (2, 1), (4, 1), (4, 0), (8, 0), (1, 2), (4, 2), (0, 2)]
 
 
-def make_imd(box, pbc, tables, margin, timestep=0.1, ntypes=1, lpa=0, fused=1):
+def make_imd(box, pbc, tables, margin, timestep=0.1, ntypes=1, lpa=0, fused=2):
     imd = host.Imd(0)
     imd.ctx.set_tuning(lpa=lpa, fused_table=fused)
     imd.setup_potentials(tables)
@@ -224,11 +225,23 @@ def test_full_size_properties_and_kernel_variants():
     e_hot = imd.tot_pot_energy
     fscale = np.abs(a["force"]).max()
     assert np.abs(a["force"].sum(axis=0)).max() < 1e-9 * np.abs(a["force"]).sum()
+    # k_eam_pass1_rep4 (raw rows, dv / d2v formed in the kernel with the macro's operations) at both CTA sizes:
+    # the same operations in the same order as the interleaved-row kernel
+    for blk in (896, 768):
+        imd.ctx.set_tuning(lpa=0, fused_table=2, rep4_block=blk)
+        imd.calc_forces(0)
+        r = imd.atoms(("id", "force", "epot", "rho", "dF"))
+        same = all(np.array_equal(a[k], r[k]) for k in ("force", "epot", "rho", "dF"))
+        print("k_eam_pass1_rep4, %d threads: bit-identical to k_eam_pass1_fused: %s" % (blk, same))
+        assert np.abs(a["force"] - r["force"]).max() < 1e-13 * fscale
+        for key in ("epot", "rho", "dF"):
+            assert rel_err(a[key], r[key]) < 1e-14, (key, blk)
+        assert abs(imd.tot_pot_energy - e_hot) < 1e-13 * abs(e_hot)
     imd.ctx.set_tuning(lpa=4, fused_table=0)
     imd.calc_forces(0)
     b = imd.atoms(("id", "force", "epot", "rho", "dF"))
     e_lpa = imd.tot_pot_energy
-    imd.ctx.set_tuning(lpa=0, fused_table=1)
+    imd.ctx.set_tuning(lpa=0, fused_table=2)
     assert np.abs(a["force"] - b["force"]).max() < 1e-11 * fscale
     for key in ("epot", "rho", "dF"):
         assert rel_err(a[key], b[key]) < 1e-12, key
