@@ -398,18 +398,40 @@ def workload_config(args):
 
 # ----------------------------------------------------------------------------- our arm
 
-def build_system(cells, rank=0, world=1, ttm=False):
-    """This rank's part of the global lattice: (cells.x * world) x cells.y x cells.z cubic cells
-    (weak scaling), cut where the library cuts the box (equal x slabs).  With --ttm the box gets
-    vacuum in front of and behind the film (pbc 0 1 1), so the cut does not fall on lattice
-    planes: the caller still filters with Imd.owned_mask.  Returns ids that are global indices."""
+def system_box(cells, world=1, ttm=False):
+    """Global box of the weak-scaling run: (cells.x * world) x cells.y x cells.z cubic cells, with --ttm vacuum in
+    front of and behind the film along x."""
+    from imd_b200 import synth
+    a = synth.AL.a
+    vac = VAC_CELLS * a if ttm else 0.0
+    return np.diag([cells[0] * world * a + 2 * vac, cells[1] * a, cells[2] * a]).astype(np.float64)
+
+
+def layer_histogram(cells, world, ttm, gdimx):
+    """Atoms per global x cell layer of the lattice build_system makes, without making it: an fcc cell has two atomic
+    planes along x, at (i + 0.25) a and (i + 0.75) a, of 2 cells.y cells.z atoms each (input of imdcu_balance_cuts)."""
+    from imd_b200 import synth
+    a = synth.AL.a
+    vac = VAC_CELLS * a if ttm else 0.0
+    ncx = cells[0] * world
+    lx = ncx * a + 2 * vac
+    x = (np.arange(ncx)[:, None] + np.array([0.25, 0.75])[None, :]).reshape(-1) * a + vac
+    layer = np.clip((gdimx * (x / lx)).astype(np.int64), 0, gdimx - 1)
+    return np.bincount(layer, minlength=gdimx) * (2 * cells[1] * cells[2])
+
+
+def build_system(cells, rank=0, world=1, ttm=False, x_lo=None, x_hi=None):
+    """This rank's part of the global lattice: the cubic cells that touch [x_lo, x_hi) (default: the rank's
+    equal-width slab) plus one cell either side; the caller still filters with Imd.owned_mask, because the cuts of
+    the library lie on cell-layer boundaries, not on lattice planes.  Returns ids that are global indices."""
     from imd_b200 import synth
     spec = synth.AL
     a = spec.a
     ncx = cells[0] * world
     vac = VAC_CELLS * a if ttm else 0.0
     lx = ncx * a + 2 * vac
-    lo, hi = rank * lx / world, (rank + 1) * lx / world
+    lo = rank * lx / world if x_lo is None else x_lo
+    hi = (rank + 1) * lx / world if x_hi is None else x_hi
     i0 = max(0, int(np.floor((lo - vac) / a)) - 1)
     i1 = min(ncx, int(np.ceil((hi - vac) / a)) + 1)
     pos, box = synth.fcc_lattice((max(i1 - i0, 0), cells[1], cells[2]), a)
@@ -444,8 +466,9 @@ def our_arm(args, rank, local_rank, world):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    spec, pos, box, ids = build_system(args.cells, rank, world, args.ttm)
-    natoms = 4 * args.cells[0] * args.cells[1] * args.cells[2]      # per GPU on average (exact for NVE)
+    spec = synth.AL
+    box = system_box(args.cells, world, args.ttm)
+    natoms = 4 * args.cells[0] * args.cells[1] * args.cells[2]      # per GPU on average
     tables = synth.make_eam_tables(spec)
     comm = None
     if world > 1:
@@ -457,6 +480,17 @@ def our_arm(args, rank, local_rank, world):
     imd.setup_potentials(tables)
     imd.make_box(box, (0, 1, 1) if args.ttm else (1, 1, 1), 0.4)
     imd.set_params(1, 0.1)
+    xcut = None
+    if world > 1 and not args.equal_slabs:
+        # slabs of equal atom count on cell-layer boundaries: the film's vacuum would leave the end ranks
+        # of equal-width slabs short of atoms and the step time is the slowest rank's
+        from imd_b200 import capi
+        g = int(imd.global_cell_dim[0])
+        xcut = capi.balance_cuts(world, layer_histogram(args.cells, world, args.ttm, g), 2)
+        imd.set_cuts(xcut)
+    w = box[0, 0] / int(imd.global_cell_dim[0])
+    spec, pos, box, ids = build_system(args.cells, rank, world, args.ttm, imd.slab["xoff"] * w,
+                                       (imd.slab["xoff"] + imd.slab["ldimx"]) * w)
     mask = imd.owned_mask(pos)
     pos, ids = pos[mask], ids[mask]
     mom = synth.maxwell_momenta(pos.shape[0], spec.mass, 0.0258, seed=1234 + rank)
@@ -466,6 +500,14 @@ def our_arm(args, rank, local_rank, world):
         dist.all_reduce(cnt)
     if int(cnt.item()) != natoms * world:
         raise SystemExit("bench.py: slab generation lost atoms (%d != %d)" % (int(cnt.item()), natoms * world))
+    slabs = None
+    if world > 1:
+        per = [torch.zeros(1, dtype=torch.int64, device="cuda") for _ in range(world)]
+        dist.all_gather(per, torch.tensor([pos.shape[0]], dtype=torch.int64, device="cuda"))
+        per = [int(t.item()) for t in per]
+        slabs = {"kind": "equal width" if xcut is None else "equal atom count (imdcu_balance_cuts)",
+                 "x_cuts": None if xcut is None else [int(x) for x in xcut], "cell_layers": int(imd.global_cell_dim[0]),
+                 "atoms_per_rank_min": min(per), "atoms_per_rank_max": max(per)}
     ctx = imd.ctx
     if args.ttm:
         eos = synth.make_eos_tables()          # diag = None: all rectangles split the same way
@@ -597,6 +639,8 @@ def our_arm(args, rank, local_rank, world):
                         "steps": ke},
                 "gpu_launches": int(launches), "nbl_rebuilds": int(rebuilds),
                 "roofline": roofline, "cpu_baseline": cpu, "phases": phases}
+        if slabs:
+            line["slabs"] = slabs
         print(json.dumps(line))
     imd.close()
     if world > 1:
@@ -785,6 +829,7 @@ def main():
                     help="cubic fcc cells per GPU (default 100 100 100 for the EAM+TTM film, 80 80 80 for --workload nve)")
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--profile-steps", type=int, default=5)
+    ap.add_argument("--equal-slabs", action="store_true", help="N > 1: the reference's equal-width x slabs instead of slabs of equal atom count")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ttm", action="store_true", help="same as --workload ttm (kept for older command lines)")
     ap.add_argument("--ttm-substeps", type=int, default=250, help="fd_n_timesteps (manual example: 250)")

@@ -82,6 +82,8 @@ def load():
         "imdcu_comm_unique_id": (C.c_int, [C.c_char_p]),
         "imdcu_comm_init": (C.c_int, [vp, C.c_char_p, C.c_int, C.c_int]),
         "imdcu_comm_rank": (C.c_int, [vp, c_ip, c_ip, c_ip, c_ip]),
+        "imdcu_balance_cuts": (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_int64), C.c_int, c_ip]),
+        "imdcu_comm_set_cuts": (C.c_int, [vp, c_ip]),
         "imdcu_ttm_set_eos": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, c_dp, c_dp, c_dp, C.POINTER(C.c_ubyte)]),
         "imdcu_ttm_init": (C.c_int, [vp, C.POINTER(TtmParamsC)]),
         "imdcu_ttm_set_tmm": (C.c_int, [vp, C.c_double, C.c_double, C.c_double, C.c_int, c_dp, C.c_int, c_dp]),
@@ -122,6 +124,17 @@ def load():
 
 
 EVAL_NOALLOC_MAX = 65536      # IMDCU_EVAL_NOALLOC_MAX (include/imdcu.h)
+
+
+def balance_cuts(nranks, atoms_per_layer, min_layers=1):
+    """imdcu_balance_cuts (host arithmetic, no GPU): slab boundaries of equal atom count on cell-layer boundaries."""
+    h = np.ascontiguousarray(atoms_per_layer, np.int64)
+    x = np.zeros(nranks + 1, np.int32)
+    rc = load().imdcu_balance_cuts(int(nranks), int(h.shape[0]), h.ctypes.data_as(C.POINTER(C.c_int64)), int(min_layers),
+                                   x.ctypes.data_as(C.POINTER(C.c_int32)))
+    if rc != 0:
+        raise ValueError("imdcu_balance_cuts: bad argument (rc %d)" % rc)
+    return x
 
 
 def _dp(a):
@@ -169,6 +182,11 @@ class Context:
 
     def comm_init(self, uid: bytes, rank: int, nranks: int):
         self._ck(self.L.imdcu_comm_init(self.h, uid, int(rank), int(nranks)))
+
+    def comm_set_cuts(self, xcut):
+        """imdcu_comm_set_cuts: slab boundaries (global x cell layers), after set_box, before upload_atoms."""
+        x = np.ascontiguousarray(xcut, np.int32)
+        self._ck(self.L.imdcu_comm_set_cuts(self.h, _ip(x)))
 
     def comm_rank(self):
         v = [C.c_int32(0) for _ in range(4)]

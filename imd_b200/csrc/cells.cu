@@ -48,7 +48,7 @@ k_wrap_key(Geom g, int n, int nranks, int ncell_ext, double4 *__restrict__ pos4,
   int li = cc[0] - g.xoff;
   perm[i] = i;
   if (nranks > 1) {
-    if (g.pbc[0]) { if (li > g.gdim[0] / 2) li -= g.gdim[0]; else if (li < -(g.gdim[0] / 2)) li += g.gdim[0]; }
+    li = slab_local_x(g, cc[0]);
     if (li < 0) { key[i] = ncell_ext; return; }
     if (li >= g.ldim[0]) { key[i] = ncell_ext + 1; return; }
   } else { if (li < 0) li = 0; else if (li >= g.ldim[0]) li = g.ldim[0] - 1; }

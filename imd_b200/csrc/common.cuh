@@ -216,6 +216,7 @@ struct imdcu_ctx {
   int    pdecay = 0; double xipdecay = 0, ramp_start = 0, ramp_end = 1;
   double *fused_coef = nullptr;              // pair + rho rows interleaved (context.cu: imdcu_fused_table)
   int    fused_state = 0;                    // 0 not looked at, 1 built, -1 tables do not share a grid
+  std::vector<int> xcut;                     // [nranks+1] global x cell layers where the slabs begin (context.cu)
   double *rep4_tab = nullptr;                // raw {pair, rho} rows, four bank-staggered copies (imdcu_rep4_table)
   int    rep4_state = 0;
   size_t rep4_bytes = 0;

@@ -383,6 +383,8 @@ static void build_ghost_plan(imdcu_ctx *c)
   c->gstage_cells[3] = (int) c->gplan.size();
 }
 
+static int apply_slabs(imdcu_ctx *c);
+
 extern "C" int imdcu_set_box(imdcu_ctx *c, const double box[9], const int pbc[3],
                              double nbl_margin, double nbl_size, const int divisor[3])
 {
@@ -422,13 +424,25 @@ extern "C" int imdcu_set_box(imdcu_ctx *c, const double box[9], const int pbc[3]
     g.ldim[d] = g.gdim[d];
     g.edim[d] = g.ldim[d] + 2;
   }
+  // x slabs of equal cell-layer count, rank r owns [r*l, (r+1)*l) (imd_geom_mpi_3d.c:119-128); imdcu_comm_set_cuts
+  // replaces them by slabs of equal atom count
+  c->xcut.assign((size_t) c->comm.nranks + 1, 0);
+  for (int r = 0; r <= c->comm.nranks; r++) c->xcut[r] = (int) ((long long) r * g.gdim[0] / c->comm.nranks);
+  return apply_slabs(c);
+}
+
+// this rank's slab [xcut[rank], xcut[rank+1]) of global x cell layers -> local cell grid, ghost plan, cell arrays
+static int apply_slabs(imdcu_ctx *c)
+{
+  Geom &g = c->geom;
   g.xoff = 0;
-  if (c->comm.nranks > 1) {                      // x slabs of equal cell-layer count, rank r owns [r*l, (r+1)*l)
-    g.ldim[0] = g.gdim[0] / c->comm.nranks;
-    g.edim[0] = g.ldim[0] + 2;
-    g.xoff = c->comm.rank * g.ldim[0];
-    if (g.pbc[0] && c->comm.nranks == 2 && g.ldim[0] < 1) return c->fail(IMDCU_EINVAL, "x slab too thin");
+  g.ldim[0] = g.gdim[0];
+  if (c->comm.nranks > 1) {
+    g.xoff = c->xcut[c->comm.rank];
+    g.ldim[0] = c->xcut[c->comm.rank + 1] - g.xoff;
+    if (g.ldim[0] < 1) return c->fail(IMDCU_EINVAL, "x slab too thin");
   }
+  g.edim[0] = g.ldim[0] + 2;
   c->ncell_ext = g.edim[0] * g.edim[1] * g.edim[2];
   build_ghost_plan(c);
   CU_CHECK(c, c->cell_begin.ensure(c->ncell_ext + 1));
@@ -440,6 +454,53 @@ extern "C" int imdcu_set_box(imdcu_ctx *c, const double box[9], const int pbc[3]
   c->box_set = true;
   c->have_valid_nbl = false;
   return IMDCU_OK;
+}
+
+// Slab boundaries by atom count (the static part of what the reference's load balancer does for its
+// x direction, imd_main_3d.c:864-914): cut r is put on the cell-layer boundary where the running atom count comes
+// closest to r/nranks of the total, every slab keeping at least min_layers layers.  Pure host arithmetic, every
+// rank computes the same cuts from the same (all-reduced) histogram.
+extern "C" int imdcu_balance_cuts(int nranks, int gdimx, const int64_t *atoms_per_layer, int min_layers, int *xcut)
+{
+  if (nranks < 1 || gdimx < 1 || !atoms_per_layer || !xcut) return IMDCU_EINVAL;
+  if (min_layers < 1) min_layers = 1;
+  if ((long long) nranks * min_layers > gdimx) return IMDCU_EINVAL;
+  std::vector<long long> pre((size_t) gdimx + 1, 0);
+  for (int l = 0; l < gdimx; l++) {
+    if (atoms_per_layer[l] < 0) return IMDCU_EINVAL;
+    pre[l + 1] = pre[l] + atoms_per_layer[l];
+  }
+  const long long total = pre[gdimx];
+  xcut[0] = 0; xcut[nranks] = gdimx;
+  for (int r = 1; r < nranks; r++) {
+    const int lo = xcut[r - 1] + min_layers, hi = gdimx - (nranks - r) * min_layers;
+    int best = lo;
+    // |pre[cut] * nranks - r * total| is minimal; the first such layer boundary on ties
+    long long bestd = -1;
+    for (int cut = lo; cut <= hi; cut++) {
+      long long d = pre[cut] * nranks - (long long) r * total;
+      if (d < 0) d = -d;
+      if (bestd < 0 || d < bestd) { bestd = d; best = cut; }
+    }
+    xcut[r] = best;
+  }
+  return IMDCU_OK;
+}
+
+// Use these slab boundaries (global x cell layers, xcut[0] = 0 < ... < xcut[nranks] = global_cell_dim.x) instead of
+// equal ones.  After imdcu_set_box, before the atoms are uploaded; the same array on every rank.
+extern "C" int imdcu_comm_set_cuts(imdcu_ctx *c, const int *xcut)
+{
+  if (!c || !xcut) return c ? c->fail(IMDCU_EINVAL, "imdcu_comm_set_cuts: bad argument") : IMDCU_EINVAL;
+  if (!c->box_set) return c->fail(IMDCU_EINVAL, "imdcu_comm_set_cuts: call imdcu_set_box first");
+  if (c->n > 0) return c->fail(IMDCU_EINVAL, "imdcu_comm_set_cuts: atoms are already uploaded");
+  const int nr = c->comm.nranks;
+  if (xcut[0] != 0 || xcut[nr] != c->geom.gdim[0]) return c->fail(IMDCU_EINVAL, "imdcu_comm_set_cuts: xcut[0] = 0 and xcut[nranks] = global_cell_dim.x required");
+  for (int r = 0; r < nr; r++)
+    if (xcut[r + 1] <= xcut[r]) return c->fail(IMDCU_EINVAL, "imdcu_comm_set_cuts: every slab needs at least one cell layer");
+  cudaSetDevice(c->device);
+  c->xcut.assign(xcut, xcut + nr + 1);
+  return apply_slabs(c);
 }
 
 extern "C" int imdcu_get_cell_grid(const imdcu_ctx *c, int gdim[3], double *cellsz)

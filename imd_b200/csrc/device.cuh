@@ -40,6 +40,22 @@ __device__ __forceinline__ double4 ld256nc(const double4 *p)
   return v;
 }
 
+// ----------------------------------------------------------------------------- x slabs
+// Global x cell layer -> layer index relative to this rank's slab [xoff, xoff + ldim): [0, ldim) owned, < 0 belongs
+// to the west side, >= ldim to the east side.  Across a periodic x boundary the offset is taken modulo gdim.x and an
+// outside layer is given to the NEARER side (atoms move less than a layer between two sorts); slabs may have any
+// widths (imdcu_comm_set_cuts), also more than half of the box.
+__device__ __forceinline__ int slab_local_x(const Geom &g, int cx)
+{
+  int li = cx - g.xoff;
+  if (g.pbc[0]) {
+    li %= g.gdim[0];
+    if (li < 0) li += g.gdim[0];
+    if (li >= g.ldim[0] && g.gdim[0] - li < li - g.ldim[0] + 1) li -= g.gdim[0];
+  }
+  return li;
+}
+
 // ----------------------------------------------------------------------------- tables
 // 3-point (quadratic in the argument) table access, potaccess.h:323-354.  `c` points to
 // the coefficient rows {p0, dv, d2v} of one column (shared or global memory).

@@ -272,8 +272,7 @@ k_mig_unpack(Geom g, int n0, int narr, int ncell_ext, const double *__restrict__
     if (cidx >= g.gdim[d]) cidx = g.gdim[d] - 1; else if (cidx < 0) cidx = 0;
     cc[d] = cidx;
   }
-  int li = cc[0] - g.xoff;
-  if (g.pbc[0]) { if (li > g.gdim[0] / 2) li -= g.gdim[0]; else if (li < -(g.gdim[0] / 2)) li += g.gdim[0]; }
+  int li = slab_local_x(g, cc[0]);
   if (li < 0 || li >= g.ldim[0]) { flags[4] = 1; li = li < 0 ? 0 : g.ldim[0] - 1; }   // moved more than one slab
   key[i] = ((li + 1) * g.edim[1] + (cc[1] + 1)) * g.edim[2] + (cc[2] + 1);
   perm[i] = i;

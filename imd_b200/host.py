@@ -17,19 +17,27 @@ TAB_PAIR, TAB_RHO, TAB_EMBED = 0, 1, 2
 capi_EOS_CVE, capi_EOS_EE = 0, 1
 
 
-def slab_rank_of_atoms(pos, box, pbc_x, gdim_x, nranks):
-    """Owner rank of every atom for the x-slab decomposition cpu_dim = nranks 1 1: global cell
-    layer by cell_coord (imd_geom_3d.c:1077-1097), rank r owns layers [r*l, (r+1)*l), l = gdim_x/nranks
-    (imd_geom_mpi_3d.c:119-128).  Host-side helper: which atoms a rank uploads."""
+def x_layer_of_atoms(pos, box, pbc_x, gdim_x):
+    """Global x cell layer of every atom by cell_coord (imd_geom_3d.c:1077-1097)."""
     tbox_x = np.linalg.inv(np.asarray(box, np.float64).reshape(3, 3))[:, 0]
     s = np.asarray(pos, np.float64) @ tbox_x
     if pbc_x:
         s = s - np.floor(s)
     g = int(gdim_x)
-    if g % nranks != 0:
-        raise ValueError("global_cell_dim.x %d is not a multiple of the number of ranks %d" % (g, nranks))
-    cx = np.clip((g * s).astype(np.int64), 0, g - 1)
-    return (cx // (g // nranks)).astype(np.int32)
+    return np.clip((g * s).astype(np.int64), 0, g - 1)
+
+
+def slab_rank_of_atoms(pos, box, pbc_x, gdim_x, nranks, xcut=None):
+    """Owner rank of every atom for the x-slab decomposition cpu_dim = nranks 1 1: rank r owns the global cell
+    layers [xcut[r], xcut[r+1]); without cuts the reference's equal slabs [r*l, (r+1)*l), l = gdim_x/nranks
+    (imd_geom_mpi_3d.c:119-128).  Host-side helper: which atoms a rank uploads."""
+    g = int(gdim_x)
+    if xcut is None:
+        if g % nranks != 0:
+            raise ValueError("global_cell_dim.x %d is not a multiple of the number of ranks %d" % (g, nranks))
+        xcut = np.arange(nranks + 1) * (g // nranks)
+    cx = x_layer_of_atoms(pos, box, pbc_x, g)
+    return (np.searchsorted(np.asarray(xcut), cx, side="right") - 1).astype(np.int32)
 
 
 class Imd:
@@ -69,7 +77,13 @@ class Imd:
         host puts one slab off migrates at the first rebuild)."""
         if self.nranks == 1:
             return np.ones(pos.shape[0], bool)
-        return slab_rank_of_atoms(pos, self.box, self.pbc_dirs[0], self.global_cell_dim[0], self.nranks) == self.rank
+        cx = x_layer_of_atoms(pos, self.box, self.pbc_dirs[0], self.global_cell_dim[0])
+        return (cx >= self.slab["xoff"]) & (cx < self.slab["xoff"] + self.slab["ldimx"])
+
+    def set_cuts(self, xcut):
+        """Slabs of equal atom count (imdcu_comm_set_cuts): after make_box, before set_atoms."""
+        self.ctx.comm_set_cuts(xcut)
+        self.slab = self.ctx.comm_rank()
 
     def set_params(self, ntypes=1, timestep=0.1, restrictions=None):
         self.ctx.set_params(ntypes, timestep, restrictions)

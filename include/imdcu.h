@@ -63,6 +63,15 @@ const char *imdcu_last_error(const imdcu_ctx *ctx);   /* ctx may be NULL: create
 int  imdcu_comm_unique_id(char id[128]);
 int  imdcu_comm_init(imdcu_ctx *ctx, const char id[128], int rank, int nranks);
 int  imdcu_comm_rank(const imdcu_ctx *ctx, int *rank, int *nranks, int *xoff, int *ldimx);
+/* Slabs of equal ATOM count instead of equal width (the static part of the reference's load balancing
+ * along x, imd_main_3d.c:864-914 -- a film has vacuum in front and behind, equal-width slabs leave the end ranks
+ * short of atoms).  imdcu_balance_cuts is host arithmetic only (no context, no GPU): from the number of atoms per
+ * global x cell layer (the host's histogram, summed over the ranks) it puts cut r on the layer boundary where the
+ * running count is closest to r/nranks of the total, every slab keeping >= min_layers layers; xcut has nranks + 1
+ * entries, xcut[0] = 0, xcut[nranks] = gdimx.  imdcu_comm_set_cuts installs such boundaries: after imdcu_set_box,
+ * before imdcu_upload_atoms, the same array on every rank; imdcu_comm_rank then reports the new [xoff, xoff+ldimx). */
+int  imdcu_balance_cuts(int nranks, int gdimx, const int64_t *atoms_per_layer, int min_layers, int *xcut);
+int  imdcu_comm_set_cuts(imdcu_ctx *ctx, const int *xcut);
 
 /* ------------------------------------------------------------------ set-up */
 /* Box and cell grid.  Replaces make_box (imd_geom_3d.c:52-108) and init_cells

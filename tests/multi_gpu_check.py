@@ -46,6 +46,15 @@ def make_imd(args, device, comm, spec, pos, box, pbc, mom, eos, tp):
     imd.setup_potentials(synth.make_eam_tables(spec))
     imd.make_box(box, pbc, 0.4 if args.ttm else 0.5)
     imd.set_params(1, 0.1)
+    if args.cuts and comm is not None:
+        # slabs by atom count (imdcu_balance_cuts on the histogram of atoms per x cell layer) for the film, whose
+        # vacuum makes equal-width slabs uneven; a deliberately lopsided cut for the uniform periodic bulk
+        from imd_b200 import capi
+        g = int(imd.global_cell_dim[0])
+        hist = np.bincount(host.x_layer_of_atoms(pos, box, pbc[0], g), minlength=g)
+        xcut = capi.balance_cuts(comm[2], hist, 1) if args.ttm else np.array([0, max(1, g // 3), g], np.int32)
+        imd.set_cuts(xcut)
+        args.cut_info = "cuts %s of %d layers" % (list(int(x) for x in xcut), g)
     mask = imd.owned_mask(pos)
     ids = np.arange(pos.shape[0], dtype=np.int32) + (1 if args.nrb else 0)
     n = int(mask.sum())
@@ -97,7 +106,9 @@ def main():
     ap.add_argument("--nrb", action="store_true", help="--ttm plus the non-reflecting rear boundary")
     ap.add_argument("--ttm3d", action="store_true", help="3-D FD lattice sharded in x slabs")
     ap.add_argument("--steps", type=int, default=40)
+    ap.add_argument("--cuts", action="store_true", help="x slabs of equal atom count / uneven width (imdcu_comm_set_cuts)")
     args = ap.parse_args()
+    args.cut_info = ""
     args.ttm = args.ttm or args.nrb
     import torch
     import torch.distributed as dist
@@ -189,7 +200,8 @@ def main():
     dist.gather_object(n_local, cnt, dst=0)
     if rank == 0:
         assert sum(cnt) == pos.shape[0]
-        print("MULTI_GPU_CHECK PASSED world=%d ttm=%d atoms per rank %s rebuilds %d" % (world, args.ttm + args.nrb, cnt, imd.nbl_count))
+        print("MULTI_GPU_CHECK PASSED world=%d ttm=%d atoms per rank %s rebuilds %d %s"
+              % (world, args.ttm + args.nrb, cnt, imd.nbl_count, args.cut_info))
     imd.close()
     if ref:
         ref.close()

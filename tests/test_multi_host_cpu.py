@@ -6,6 +6,7 @@ import socket
 import sys
 
 import numpy as np
+import pytest
 import torch.multiprocessing as mp
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -62,3 +63,40 @@ def test_slab_partition_matches_layer_arithmetic():
     assert host.slab_rank_of_atoms(pos, box, 0, 8, 4).tolist() == [0, 0, 0, 1, 2, 3, 0, 3]
     # periodic: wrap
     assert host.slab_rank_of_atoms(pos, box, 1, 8, 4).tolist() == [0, 0, 0, 1, 2, 3, 3, 0]
+
+
+def test_balance_cuts_film_with_vacuum():
+    """imdcu_balance_cuts (host arithmetic of the library): a film with 30 % vacuum cut into slabs of equal
+    atom count on cell-layer boundaries -- spread of atoms per rank <= 3 %, where equal-width slabs leave the end
+    ranks short; degenerate inputs."""
+    from imd_b200 import capi, host
+    from imd_b200 import synth
+    spec = synth.AL
+    pos, box = synth.film_lattice((400, 2, 2), spec.a, 0.15 * 400 * spec.a / 0.7, 0.15 * 400 * spec.a / 0.7)   # 30 % vacuum
+    g = 320                                                     # cell layers of ~7.2 A
+    layer = host.x_layer_of_atoms(pos, box, 0, g)
+    hist = np.bincount(layer, minlength=g)
+    for nranks in (2, 4, 8):
+        xcut = capi.balance_cuts(nranks, hist, 2)
+        assert xcut[0] == 0 and xcut[-1] == g and np.all(np.diff(xcut) >= 2)
+        per = np.array([hist[a:b].sum() for a, b in zip(xcut[:-1], xcut[1:])])
+        assert per.sum() == pos.shape[0]
+        spread = (per.max() - per.min()) / per.mean()
+        equal = np.array([hist[r * g // nranks:(r + 1) * g // nranks].sum() for r in range(nranks)])
+        print("ranks %d: cuts %s atoms %s spread %.3f (equal-width slabs: %.3f)"
+              % (nranks, [int(x) for x in xcut], [int(x) for x in per], spread, (equal.max() - equal.min()) / equal.mean()))
+        # cuts sit on layer boundaries: the spread cannot be asked to be finer than one layer of atoms
+        assert spread <= 1.01 * hist.max() / per.mean()
+        if nranks <= 4:
+            assert spread <= 0.03                                # >= 56 material layers per rank here
+        # the owner of every atom by these cuts is the slab its layer falls into
+        owner = host.slab_rank_of_atoms(pos, box, 0, g, nranks, xcut)
+        assert np.array_equal(np.bincount(owner, minlength=nranks), per)
+    # a uniform system keeps the reference's equal slabs
+    assert list(capi.balance_cuts(4, np.full(16, 100), 1)) == [0, 4, 8, 12, 16]
+    # everything in one layer: the minimum slab width still holds
+    one = np.zeros(12, np.int64); one[5] = 1000
+    x = capi.balance_cuts(3, one, 2)
+    assert x[0] == 0 and x[-1] == 12 and np.all(np.diff(x) >= 2)
+    with pytest.raises(ValueError):
+        capi.balance_cuts(8, np.ones(10, np.int64), 2)           # 8 slabs of 2 layers do not fit into 10
