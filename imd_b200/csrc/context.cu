@@ -65,6 +65,7 @@ extern "C" int imdcu_create(imdcu_ctx **out, int device)
     c->tune.lpa = env_int("IMDCU_LPA", 0);
     c->tune.fused_table = env_int("IMDCU_FUSED_TABLE", 2);
     c->tune.rep4_block = env_int("IMDCU_REP4_BLOCK", 896);
+    c->tune.nbl_filter = env_int("IMDCU_NBL_FILTER", 0);
     c->tune.ttm_overlap = env_int("IMDCU_TTM_OVERLAP", 1);
     c->tune.ttm_lat_smem = env_int("IMDCU_TTM_LAT_SMEM", 1);
     const char *e3 = getenv("IMDCU_TTM3D");
@@ -81,6 +82,7 @@ extern "C" int imdcu_create(imdcu_ctx **out, int device)
   CREATE_CHECK(cudaMallocHost(&c->h_results, 32 * sizeof(double)));
   CREATE_CHECK(cudaMalloc(&c->d_ticket, 8 * sizeof(unsigned int)));
   CREATE_CHECK(cudaMemset(c->d_ticket, 0, 8 * sizeof(unsigned int)));
+  CREATE_CHECK(cudaMalloc(&c->d_xmax, sizeof(unsigned int)));
   CREATE_CHECK(cudaMalloc(&c->d_flags, 8 * sizeof(int)));
   CREATE_CHECK(cudaMemset(c->d_flags, 0, 8 * sizeof(int)));
   CREATE_CHECK(cudaMallocHost(&c->h_flags, 8 * sizeof(int)));
@@ -120,6 +122,7 @@ extern "C" int imdcu_destroy(imdcu_ctx *c)
     if (c->tab[t].raw2) cudaFree(c->tab[t].raw2);
   }
   cudaFree(c->d_results); cudaFreeHost(c->h_results);
+  cudaFree(c->d_xmax); c->posf.release();
   cudaFree(c->d_ticket); cudaFree(c->d_flags); cudaFreeHost(c->h_flags);
   cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1);
   cudaStreamDestroy(c->stream);
@@ -284,6 +287,7 @@ extern "C" int imdcu_set_tuning(imdcu_ctx *c, const char *key, int value)
     if (value < 0 || value > 2) return c->fail(IMDCU_EINVAL, "fused_table: 0 (general kernel), 1 (48-byte rows), 2 (raw rows, four bank-staggered replicas)");
     c->tune.fused_table = value;
   }
+  else if (k == "nbl_filter") c->tune.nbl_filter = value != 0;
   else if (k == "rep4_block") {
     if (value != 896 && value != 768) return c->fail(IMDCU_EINVAL, "rep4_block: 896 or 768");
     c->tune.rep4_block = value;

@@ -76,6 +76,129 @@ k_nbl_build(Geom g, int n, const double4 *__restrict__ pos4, const int *__restri
   if (lane == 0 && mx > 0) atomicMax(&flags[1], mx);
 }
 
+// ----------------------------------------------------------------------------- two-phase build
+// The build above is bound by FP64: ~27 x 18 candidates per Al atom, nine double-precision operations each, to
+// keep one in eleven.  Two phases instead:
+//   A  every candidate is tested in SINGLE precision against cellsz + margin and appended to the atom's own column
+//      of the list when it passes; the margin bounds the error of the float test, so no pair can be lost:
+//        |r2_float - r2| <= 2 sqrt(3) r 2^-23 X + 2^-22 r^2   for |coordinates| <= X, r <= sqrt(cellsz),
+//      X is MEASURED at every rebuild (k_posf), so atoms that fly far out of an open box only widen the margin;
+//   B  the lane walks its own ~80 entries and keeps, in place and in order, those that pass the reference's exact
+//      test (r2 < cellsz with SPROD3D rounding, makros.h:361).
+// Candidates keep their order and phase B decides with the same arithmetic as k_nbl_build, so the list -- order
+// included -- is identical to k_nbl_build's.  Pairs the reference meets from the image side (lexneg ghost cells)
+// go through the exact path at once and are marked (~j) so that phase B keeps them as they are.
+__global__ void __launch_bounds__(256)
+k_posf(int ntot, const double4 *__restrict__ pos4, float4 *__restrict__ posf, unsigned int *__restrict__ xmax_bits)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  float m = 0.0f;
+  if (i < ntot) {
+    const double4 p = pos4[i];
+    posf[i] = make_float4((float) p.x, (float) p.y, (float) p.z, 0.0f);
+    m = (float) fmax(fmax(fabs(p.x), fabs(p.y)), fabs(p.z));
+    m = m * 1.0000002f;                                   // the conversion may have rounded down
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0 && m > 0.0f) atomicMax(xmax_bits, __float_as_uint(m));   // non-negative floats order as ints
+}
+
+template <bool COUNT_ONLY>
+__global__ void __launch_bounds__(128)
+k_nbl_build2(Geom g, int n, const double4 *__restrict__ pos4, const float4 *__restrict__ posf,
+             const unsigned int *__restrict__ xmax_bits, const int *__restrict__ key,
+             const int *__restrict__ cell_begin, const int *__restrict__ cell_count,
+             const int *__restrict__ gtcode, const double *__restrict__ graw,
+             int cap, int *__restrict__ idx, int *__restrict__ num, int *__restrict__ flags)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  int cnt = 0, kept = 0;
+  if (i < n) {
+    const double xmax = (double) __uint_as_float(*xmax_bits);
+    const double rc = sqrt(g.cellsz);
+    // 4 > 2 sqrt(3), 2^-20 > 2^-22: the bound with room to spare, then rounded up into float
+    const float lim = (float) ((g.cellsz + 4.0 * rc * 1.1920928955078125e-7 * xmax + 9.5367431640625e-7 * g.cellsz) * 1.000001);
+    const double4 pi = pos4[i];
+    const float4 pf = posf[i];
+    const int c = key[i];
+    const int ey = g.edim[1], ez = g.edim[2];
+    int *slot = idx + ((size_t) (i >> 5) * cap) * 32 + lane;
+    for (int l = -1; l <= 1; l++)
+      for (int m = -1; m <= 1; m++)
+        for (int q = -1; q <= 1; q++) {
+          const int c2 = c + (l * ey + m) * ez + q;
+          const int b = cell_begin[c2], e = b + cell_count[c2];
+          const bool lexneg = (l < 0) || (l == 0 && m < 0) || (l == 0 && m == 0 && q < 0);
+          if (!(lexneg && e > n)) {
+            for (int j = b; j < e; j += 4) {               // phase A: four candidates per round
+              const int j1 = min(j + 1, e - 1), j2 = min(j + 2, e - 1), j3 = min(j + 3, e - 1);
+              const float4 q0 = posf[j], q1 = posf[j1], q2 = posf[j2], q3 = posf[j3];
+              float dx = q0.x - pf.x, dy = q0.y - pf.y, dz = q0.z - pf.z;
+              const float r0 = dx * dx + dy * dy + dz * dz;
+              dx = q1.x - pf.x; dy = q1.y - pf.y; dz = q1.z - pf.z;
+              const float r1 = dx * dx + dy * dy + dz * dz;
+              dx = q2.x - pf.x; dy = q2.y - pf.y; dz = q2.z - pf.z;
+              const float r2 = dx * dx + dy * dy + dz * dz;
+              dx = q3.x - pf.x; dy = q3.y - pf.y; dz = q3.z - pf.z;
+              const float r3 = dx * dx + dy * dy + dz * dz;
+              if (j != i && r0 < lim) { if (!COUNT_ONLY && cnt < cap) slot[(size_t) cnt * 32] = j; cnt++; }
+              if (j + 1 < e && j + 1 != i && r1 < lim) { if (!COUNT_ONLY && cnt < cap) slot[(size_t) cnt * 32] = j + 1; cnt++; }
+              if (j + 2 < e && j + 2 != i && r2 < lim) { if (!COUNT_ONLY && cnt < cap) slot[(size_t) cnt * 32] = j + 2; cnt++; }
+              if (j + 3 < e && j + 3 != i && r3 < lim) { if (!COUNT_ONLY && cnt < cap) slot[(size_t) cnt * 32] = j + 3; cnt++; }
+            }
+            continue;
+          }
+          for (int j = b; j < e; j++) {                    // boundary cells with images: exact at once, as k_nbl_build
+            if (j == i) continue;
+            double dx, dy, dz;
+            if (j >= n && lexneg) {
+              double x = pi.x, y = pi.y, z = pi.z;
+              apply_shift(g, gtcode[j - n], -1.0, x, y, z);
+              const double *r = graw + 3 * (size_t) (j - n);
+              dx = x - r[0]; dy = y - r[1]; dz = z - r[2];
+            } else {
+              const double4 pj = ld256(&pos4[j]);
+              dx = pj.x - pi.x; dy = pj.y - pi.y; dz = pj.z - pi.z;
+            }
+            if (r2_exact(dx, dy, dz) < g.cellsz) {
+              if (!COUNT_ONLY && cnt < cap) slot[(size_t) cnt * 32] = ~j;
+              cnt++;
+            }
+          }
+        }
+    if (!COUNT_ONLY) {                                     // phase B: exact test of my own entries, compacted in place
+      // four entries per round: their slots, then their records, are requested together (a round is two dependent
+      // memory latencies, not eight); an entry is written back at or below its own position, so reading ahead is safe
+      const int m = min(cnt, cap);
+      for (int k = 0; k < m; k += 4) {
+        int j[4]; double4 pj[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) j[u] = slot[(size_t) min(k + u, m - 1) * 32];
+#pragma unroll
+        for (int u = 0; u < 4; u++) pj[u] = ld256(&pos4[j[u] < 0 ? ~j[u] : j[u]]);
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          if (k + u >= m) break;
+          const bool marked = j[u] < 0;
+          const int jj = marked ? ~j[u] : j[u];
+          if (marked || r2_exact(pj[u].x - pi.x, pj[u].y - pi.y, pj[u].z - pi.z) < g.cellsz) {
+            slot[(size_t) kept * 32] = jj; kept++;
+          }
+        }
+      }
+      num[i] = kept;
+    } else num[i] = cnt;
+  }
+  // table sizing and the "neighbor table full" test look at the candidates of phase A (an upper bound of the
+  // list length, within a fraction of a percent of it)
+  int mx = cnt;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if (lane == 0 && mx > 0) atomicMax(&flags[1], mx);
+}
+
 // error flags that kernels raise between two list builds (the build resets them)
 int imdcu_check_flags(imdcu_ctx *c)
 {
@@ -101,9 +224,24 @@ static int build_nblist_local(imdcu_ctx *c)
   if (n == 0) return IMDCU_OK;
   const int nb = div_up(n, 128);
   const size_t ntiles = (size_t) div_up(n, 32);
+  const bool two_phase = c->tune.nbl_filter != 0;
+  if (two_phase) {                           // single-precision copies of owned atoms and images, max |coordinate|
+    const int ntot = n + (int) c->ng;
+    CU_CHECK(c, c->posf.ensure((size_t) ntot + 64));
+    CU_CHECK(c, cudaMemsetAsync(c->d_xmax, 0, sizeof(unsigned int), st));
+    k_posf<<<div_up(ntot, 256), 256, 0, st>>>(ntot, c->pos4.p, c->posf.p, c->d_xmax);
+    c->count_launch();
+  }
   auto run = [&](bool count_only) -> int {
     CU_CHECK(c, cudaMemsetAsync(c->d_flags, 0, 8 * sizeof(int), st));
-    if (count_only)
+    if (two_phase && count_only)
+      k_nbl_build2<true><<<nb, 128, 0, st>>>(c->geom, n, c->pos4.p, c->posf.p, c->d_xmax, c->key.p, c->cell_begin.p,
+                                              c->cell_count.p, c->ghost_tcode.p, c->ghost_raw.p, 0, nullptr, c->nbl_num.p, c->d_flags);
+    else if (two_phase)
+      k_nbl_build2<false><<<nb, 128, 0, st>>>(c->geom, n, c->pos4.p, c->posf.p, c->d_xmax, c->key.p, c->cell_begin.p,
+                                               c->cell_count.p, c->ghost_tcode.p, c->ghost_raw.p, c->nbl_cap, c->nbl_idx.p,
+                                               c->nbl_num.p, c->d_flags);
+    else if (count_only)
       k_nbl_build<true><<<nb, 128, 0, st>>>(c->geom, n, c->pos4.p, c->key.p, c->cell_begin.p, c->cell_count.p,
                                              c->ghost_tcode.p, c->ghost_raw.p, 0, nullptr, c->nbl_num.p, c->d_flags);
     else

@@ -129,6 +129,28 @@ def test_golden_trajectory(case, lpa):
     imd.close()
 
 
+@pytest.mark.parametrize("case", GOLDEN_CASES)
+def test_two_phase_nblist_equals_exact_build(case):
+    """The two-phase list build (float filter with a measured error margin, then the exact test: k_nbl_build2) gives
+    the list of the exact-only build (k_nbl_build) -- same pairs in the same order, hence bit-identical forces --
+    on periodic images, free surfaces and two species."""
+    g = Golden(case)
+    s = g.steps[0]
+    out = {}
+    for filt in (0, 1):
+        imd = make_imd(g.box, g.pbc, g.tables, g.margin, g.timestep, g.ntypes)
+        imd.ctx.set_tuning(nbl_filter=filt)
+        imd.set_atoms(g.step(s, "pre_pos"), g.step(s, "pre_mom"), g.step(s, "pre_mass"),
+                      g.step(s, "pre_type"), g.step(s, "pre_id"))
+        imd.calc_forces(s)
+        out[filt] = (canon_pairs(imd.nblist_pairs()), imd.atoms(("id", "force", "epot", "rho", "numneighs")))
+        imd.close()
+    assert np.array_equal(out[0][0], out[1][0])
+    assert np.array_equal(out[1][0], canon_pairs(g.step(s, "nblpairs")))             # and the reference's
+    for key in ("force", "epot", "rho", "numneighs"):
+        assert np.array_equal(out[0][1][key], out[1][1][key]), key
+
+
 def tables_on_different_grids(spec):
     """Single-species tables whose rho column is tabulated on another r^2 grid than the pair column:
     the interleaved-row kernel (k_eam_pass1_fused) does not apply, the general one runs."""
@@ -237,6 +259,14 @@ def test_full_size_properties_and_kernel_variants():
         for key in ("epot", "rho", "dF"):
             assert rel_err(a[key], r[key]) < 1e-14, (key, blk)
         assert abs(imd.tot_pot_energy - e_hot) < 1e-13 * abs(e_hot)
+    # the exact-only list build on the same atoms: same list, order included -> bit-identical results
+    imd.ctx.set_tuning(lpa=0, fused_table=2, rep4_block=896, nbl_filter=0)
+    imd.ctx.invalidate_nblist()
+    imd.calc_forces(0)
+    r = imd.atoms(("id", "force", "epot", "rho", "dF"))
+    assert all(np.array_equal(a[k], r[k]) for k in ("force", "epot", "rho", "dF")), "two-phase list differs from the exact build"
+    imd.ctx.set_tuning(nbl_filter=1)
+    imd.ctx.invalidate_nblist()
     imd.ctx.set_tuning(lpa=4, fused_table=0)
     imd.calc_forces(0)
     b = imd.atoms(("id", "force", "epot", "rho", "dF"))
