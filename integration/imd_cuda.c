@@ -350,7 +350,7 @@ void init_ttm(void)
   nn_read_table(&intp_cve_from_r_te, "../EOS_cve_from_r_te.txt");
   nn_read_table(&intp_ee_from_r_tesqrt, "../EOS_ee_from_r_tesqrt.txt");
   if (imdrestart > 0)
-    error("imd_cuda: restart of the FD lattice from a .ttm file (ttm_read, imd_ttm.c:1983) is not supported yet");
+    error("imd_cuda: restart of the FD lattice from a .ttm file (ttm_read, imd_ttm.c:1983) is not provided: the reference's own TTM restart resets the electronic state (DESIGN.md 9.4)");
 }
 
 /* tmm_init (imd_tmm.c:98-190): the two data files of do_tmm.  Without them (they are missing blobs upstream)
@@ -442,7 +442,7 @@ void ttm_writeout(int number)
 
 void ttm_read(int number)
 {
-  error("imd_cuda: ttm_read (restart of the FD lattice) is not supported yet");
+  error("imd_cuda: ttm_read (restart of the FD lattice) is not provided: the reference's own TTM restart resets the electronic state (DESIGN.md 9.4)");
 }
 #endif /* TTM */
 
