@@ -584,6 +584,20 @@ def our_arm(args, rank, local_rank, world):
     h2d = natoms * 48
     d2h = natoms * 48 + 2 * 64
 
+    # ---- diagnostic: wall time of every step, one library call per step (each call ends with the integrator's
+    # synchronise), with the list-rebuild counter: shows what a rebuild costs and how even the other steps are
+    if args.per_step > 0:
+        rows = []
+        first = args.warmup + args.steps + 1000
+        for s in range(args.per_step):
+            barrier()
+            t0 = time.perf_counter()
+            run(first + s, 1)
+            torch.cuda.synchronize()
+            rows.append((round((time.perf_counter() - t0) * 1e3, 3), int(ctx.nbl_count)))
+        if rank == 0:
+            sys.stderr.write("PER_STEP_MS " + json.dumps(rows) + "\n")
+
     # ---- per-kernel times (CUDA events inside the library, separate short segment)
     roofline = None
     phases = None
@@ -829,6 +843,7 @@ def main():
                     help="cubic fcc cells per GPU (default 100 100 100 for the EAM+TTM film, 80 80 80 for --workload nve)")
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--profile-steps", type=int, default=5)
+    ap.add_argument("--per-step", type=int, default=0, help="diagnostic: also time this many single steps, printed to stderr")
     ap.add_argument("--equal-slabs", action="store_true", help="N > 1: the reference's equal-width x slabs instead of slabs of equal atom count")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ttm", action="store_true", help="same as --workload ttm (kept for older command lines)")

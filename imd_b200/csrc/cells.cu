@@ -200,6 +200,7 @@ int imdcu_refresh_ghosts(imdcu_ctx *c, bool at_build)
   }
   CU_CHECK(c, cudaGetLastError());
   if (at_build && multi) RET_IF(imdcu_multi_ghost_build(c));
+  if (at_build) imdcu_dbg_mark(c, "ghost_refresh+build");
   return IMDCU_OK;
 }
 
@@ -211,13 +212,16 @@ int imdcu_rebuild_cells(imdcu_ctx *c)
   cudaStream_t st = c->stream;
   const bool multi = c->comm.nranks > 1;
   if (n == 0 && !multi) { c->ng = 0; return IMDCU_OK; }
+  imdcu_dbg_mark(c, nullptr);
 
   if (n > 0) {
     k_wrap_key<<<div_up(n, 256), 256, 0, st>>>(c->geom, n, c->comm.nranks, c->ncell_ext, c->pos4.p, c->key.p, c->perm.p);
     c->count_launch();
   }
   int n_sort = n;                                   // elements to sort (stayers + movers + arrivals)
+  imdcu_dbg_mark(c, "wrap_key");
   if (multi) RET_IF(imdcu_multi_migrate(c, &n_sort));
+  imdcu_dbg_mark(c, "migrate");
   const int n_new = (int) c->n;                     // owned atoms after migration (set by multi_migrate)
 
   // radix sort (key, perm) over just the bits a cell index (+ 2 sentinels) needs
@@ -228,7 +232,9 @@ int imdcu_rebuild_cells(imdcu_ctx *c)
   size_t scan_bytes = 0;
   const int nplan = (int) c->gplan.size();
   cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, c->gcell_off.p, c->gcell_off.p, nplan + 1, st);
-  CU_CHECK(c, c->cub_tmp.ensure(std::max(tmp_bytes, scan_bytes) + 256));
+  // headroom: the sort's temporary storage grows with the element count, and on several GPUs that count reaches a new
+  // maximum at many rebuilds (arrivals); without slack each of them is a cudaMalloc + cudaFree that the other ranks wait for
+  CU_CHECK(c, c->cub_tmp.ensure(std::max(tmp_bytes, scan_bytes) + 256, 1.25));
   if (n_sort > 0) {
     CU_CHECK(c, cub::DeviceRadixSort::SortPairs(c->cub_tmp.p, tmp_bytes, c->key.p, c->key_alt.p, c->perm.p,
                                                 c->perm_alt.p, n_sort, 0, bits, st));
@@ -258,6 +264,7 @@ int imdcu_rebuild_cells(imdcu_ctx *c)
   }
   k_cell_fix_count<<<div_up(c->ncell_ext, 256), 256, 0, st>>>(c->ncell_ext, c->cell_begin.p, c->cell_count.p);
   c->count_launch();
+  imdcu_dbg_mark(c, "sort+gather+bounds");
 
   // ghost cells: counts stage by stage, offsets by one exclusive scan over the plan
   c->ng = 0;

@@ -14,6 +14,7 @@
 #include <cstring>
 #include <string>
 #include <vector>
+#include <chrono>
 
 #include "../../include/imdcu.h"
 
@@ -216,6 +217,10 @@ struct imdcu_ctx {
   int    pdecay = 0; double xipdecay = 0, ramp_start = 0, ramp_end = 1;
   double *fused_coef = nullptr;              // pair + rho rows interleaved (context.cu: imdcu_fused_table)
   int    fused_state = 0;                    // 0 not looked at, 1 built, -1 tables do not share a grid
+  // IMDCU_DEBUG_REBUILD=1: wall-clock marks along the rebuild path (imdcu_dbg_mark synchronises at each), printed per rank
+  int    dbg_rebuild = 0;
+  std::chrono::steady_clock::time_point dbg_t;
+  std::string dbg_line;
   std::vector<int> xcut;                     // [nranks+1] global x cell layers where the slabs begin (context.cu)
   double *rep4_tab = nullptr;                // raw {pair, rho} rows, four bank-staggered copies (imdcu_rep4_table)
   int    rep4_state = 0;
@@ -371,6 +376,7 @@ __device__ __host__ inline int imdcu_combine_code(int pc, int code)
 {
   return (pc % 3 - 1 + code % 3 - 1 + 1) + 3 * ((pc / 3) % 3 - 1 + (code / 3) % 3 - 1 + 1) + 9 * (pc / 9 - 1 + code / 9 - 1 + 1);
 }
+void imdcu_dbg_mark(imdcu_ctx *ctx, const char *label, bool flush = false);   // context.cu
 const double *imdcu_fused_table(imdcu_ctx *ctx);                       // context.cu
 const double *imdcu_rep4_table(imdcu_ctx *ctx, size_t *bytes);         // context.cu
 void imdcu_ttm_release(imdcu_ctx *ctx);                                // ttm.cu

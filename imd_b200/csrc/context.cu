@@ -66,6 +66,7 @@ extern "C" int imdcu_create(imdcu_ctx **out, int device)
     c->tune.fused_table = env_int("IMDCU_FUSED_TABLE", 2);
     c->tune.rep4_block = env_int("IMDCU_REP4_BLOCK", 896);
     c->tune.nbl_filter = env_int("IMDCU_NBL_FILTER", 0);
+    c->dbg_rebuild = env_int("IMDCU_DEBUG_REBUILD", 0);
     c->tune.ttm_overlap = env_int("IMDCU_TTM_OVERLAP", 1);
     c->tune.ttm_lat_smem = env_int("IMDCU_TTM_LAT_SMEM", 1);
     const char *e3 = getenv("IMDCU_TTM3D");
@@ -273,6 +274,22 @@ const double *imdcu_rep4_table(imdcu_ctx *c, size_t *bytes)
   *bytes = c->rep4_bytes;
   c->rep4_state = 1;
   return c->rep4_tab;
+}
+
+// Diagnostic (IMDCU_DEBUG_REBUILD=1): time since the previous mark, after synchronising the stream, so that a rebuild
+// can be attributed to its parts on every rank; label == nullptr starts a new line.
+void imdcu_dbg_mark(imdcu_ctx *c, const char *label, bool flush)
+{
+  if (!c->dbg_rebuild) return;
+  cudaStreamSynchronize(c->stream);
+  const auto now = std::chrono::steady_clock::now();
+  if (label) {
+    char buf[96];
+    snprintf(buf, sizeof buf, " %s %.3f", label, std::chrono::duration<double, std::milli>(now - c->dbg_t).count());
+    c->dbg_line += buf;
+  } else c->dbg_line.clear();
+  c->dbg_t = std::chrono::steady_clock::now();
+  if (flush) { fprintf(stderr, "REBUILD rank %d n %lld ng %lld:%s\n", c->comm.rank, (long long) c->n, (long long) c->ng, c->dbg_line.c_str()); c->dbg_line.clear(); }
 }
 
 // ----------------------------------------------------------------------------- tuning

@@ -296,6 +296,7 @@ int imdcu_multi_migrate(imdcu_ctx *c, int *n_total)
   RET_IF(exchange(c, dc + 0, 1, dc + 1, 1, dc + 4, 1, dc + 5, 1, ncclInt32));
   CU_CHECK(c, cudaMemcpyAsync(hc, dc, 8 * sizeof(int), cudaMemcpyDeviceToHost, st));
   CU_CHECK(c, cudaStreamSynchronize(st));
+  imdcu_dbg_mark(c, "mig.counts");
   const int out_w = hc[0], out_e = hc[1];
   const int in_e = m.east >= 0 ? hc[4] : 0, in_w = m.west >= 0 ? hc[5] : 0;
   const int narr = in_e + in_w;
@@ -303,6 +304,7 @@ int imdcu_multi_migrate(imdcu_ctx *c, int *n_total)
     int rc = IMDCU_OK;
     if ((out_w && m.west < 0) || (out_e && m.east < 0)) rc = c->fail(IMDCU_EINVAL, "atom left the box through an open x end");
     RET_IF(imdcu_multi_agree(c, rc));                 // all ranks leave together, nobody waits in the payload exchange
+    imdcu_dbg_mark(c, "mig.agree");
   }
   if (out_w + out_e + narr > 0) {
     CU_CHECK(c, m.mig_send.ensure((size_t) (out_w + out_e) * MIG_REC + 16, 1.5));
@@ -314,7 +316,7 @@ int imdcu_multi_migrate(imdcu_ctx *c, int *n_total)
       int *fw = c->key_alt.p, *fe = c->perm_alt.p;
       size_t scan_bytes = 0;
       cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, fw, fw, n, st);
-      CU_CHECK(c, c->cub_tmp.ensure(scan_bytes + 256));
+      CU_CHECK(c, c->cub_tmp.ensure(scan_bytes + 256, 1.25));
       k_mig_flags<<<div_up(n, 256), 256, 0, st>>>(n, c->ncell_ext, c->key.p, fw, fe);
       CU_CHECK(c, cub::DeviceScan::ExclusiveSum(c->cub_tmp.p, scan_bytes, fw, fw, n, st));
       CU_CHECK(c, cub::DeviceScan::ExclusiveSum(c->cub_tmp.p, scan_bytes, fe, fe, n, st));

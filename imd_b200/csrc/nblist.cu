@@ -258,14 +258,16 @@ static int build_nblist_local(imdcu_ctx *c)
     int cap = (int) (c->nbl_size * maxn) + 1;
     cap = (cap + 3) & ~3;
     c->nbl_cap = cap;
-    CU_CHECK(c, c->nbl_idx.ensure(ntiles * (size_t) cap * 32));
+    CU_CHECK(c, c->nbl_idx.ensure(ntiles * (size_t) cap * 32, 1.03));
     return IMDCU_OK;
   };
   if (c->nbl_cap == 0) {                     // first build: estimate_nblist_size
     RET_IF(run(true));
     RET_IF(grow(c->h_flags[1]));
   }
-  CU_CHECK(c, c->nbl_idx.ensure(ntiles * (size_t) c->nbl_cap * 32));
+  // 3 % headroom: with migration the number of owned atoms creeps up, and every new maximum would otherwise
+  // reallocate the whole list (cudaMalloc + cudaFree of ~1.6 GB at 4 M atoms) in the middle of a rebuild
+  CU_CHECK(c, c->nbl_idx.ensure(ntiles * (size_t) c->nbl_cap * 32, 1.03));
   RET_IF(run(false));
   if (c->h_flags[1] > c->nbl_cap) {          // "neighbor table full": grow and redo once
     RET_IF(grow(c->h_flags[1]));
@@ -281,7 +283,10 @@ int imdcu_build_nblist(imdcu_ctx *c)
   PhaseTimer pt(c, 1);
   // the build itself runs no collective, so a rank may fail or redo it locally; the outcome is agreed on once,
   // here, so that a rank with a raised flag or a full table does not leave its peers in the next halo exchange
-  RET_IF(imdcu_multi_agree(c, build_nblist_local(c)));
+  const int rc_local = build_nblist_local(c);
+  imdcu_dbg_mark(c, "nbl_build");
+  RET_IF(imdcu_multi_agree(c, rc_local));
+  imdcu_dbg_mark(c, "agree", true);
   c->have_valid_nbl = true;
   c->nbl_count++;
   return IMDCU_OK;
