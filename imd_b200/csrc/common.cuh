@@ -232,8 +232,8 @@ struct imdcu_ctx {
   // kernel-selection knobs (imdcu_set_tuning; the IMDCU_* environment variables give the defaults at create)
   struct Tune {
     int lpa = 0;                             // lanes per atom of the EAM passes: 0 = by system size, 1/2/4/8
-    int nbl_filter = 0;                      // neighbour-list build: 0 exact tests only (default), 1 two phases (float filter, then
-                                             // the exact test): same list, measured no faster
+    int nbl_filter = 1;                      // neighbour-list build: 1 float classifier with the exact test in the uncertain
+                                             // shell (k_nbl_build2, default), 0 exact tests only (k_nbl_build): same list
     int rep4_block = 896;                    // threads per CTA of k_eam_pass1_rep4 (896 or 768)
     int fused_table = 2;                     // pass 1 when the pair and rho tables share their grid: 1 k_eam_pass1_fused, 2 k_eam_pass1_rep4, 0 general kernel
     int ttm_overlap = 1;                     // imdcu_run_ttm: lattice kernel beside EAM pass 2

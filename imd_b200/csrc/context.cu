@@ -65,7 +65,7 @@ extern "C" int imdcu_create(imdcu_ctx **out, int device)
     c->tune.lpa = env_int("IMDCU_LPA", 0);
     c->tune.fused_table = env_int("IMDCU_FUSED_TABLE", 2);
     c->tune.rep4_block = env_int("IMDCU_REP4_BLOCK", 896);
-    c->tune.nbl_filter = env_int("IMDCU_NBL_FILTER", 0);
+    c->tune.nbl_filter = env_int("IMDCU_NBL_FILTER", 1);
     c->dbg_rebuild = env_int("IMDCU_DEBUG_REBUILD", 0);
     c->tune.ttm_overlap = env_int("IMDCU_TTM_OVERLAP", 1);
     c->tune.ttm_lat_smem = env_int("IMDCU_TTM_LAT_SMEM", 1);

@@ -76,18 +76,18 @@ k_nbl_build(Geom g, int n, const double4 *__restrict__ pos4, const int *__restri
   if (lane == 0 && mx > 0) atomicMax(&flags[1], mx);
 }
 
-// ----------------------------------------------------------------------------- two-phase build
-// The build above is bound by FP64: ~27 x 18 candidates per Al atom, nine double-precision operations each, to
-// keep one in eleven.  Two phases instead:
-//   A  every candidate is tested in SINGLE precision against cellsz + margin and appended to the atom's own column
-//      of the list when it passes; the margin bounds the error of the float test, so no pair can be lost:
-//        |r2_float - r2| <= 2 sqrt(3) r 2^-23 X + 2^-22 r^2   for |coordinates| <= X, r <= sqrt(cellsz),
-//      X is MEASURED at every rebuild (k_posf), so atoms that fly far out of an open box only widen the margin;
-//   B  the lane walks its own ~80 entries and keeps, in place and in order, those that pass the reference's exact
-//      test (r2 < cellsz with SPROD3D rounding, makros.h:361).
-// Candidates keep their order and phase B decides with the same arithmetic as k_nbl_build, so the list -- order
-// included -- is identical to k_nbl_build's.  Pairs the reference meets from the image side (lexneg ghost cells)
-// go through the exact path at once and are marked (~j) so that phase B keeps them as they are.
+// ----------------------------------------------------------------------------- build with a float classifier
+// k_nbl_build is bound by FP64: ~27 x 18 candidates per Al atom, eight double-precision operations each (1.5 ms of
+// FP64 pipe time per 4 M atoms), to keep one in eleven.  k_nbl_build2 classifies every candidate in SINGLE precision:
+//     r2_float <  cellsz - margin   the pair is in range            (no FP64)
+//     r2_float >= cellsz + margin   it is not                       (no FP64)
+//     otherwise                     the reference's exact test decides (r2 < cellsz with SPROD3D rounding, makros.h:361)
+// The margin bounds the error of the float test,
+//     |r2_float - r2| <= 2 sqrt(3) r 2^-23 X + 2^-21.3 r^2     for |coordinates| <= X and r <= sqrt(cellsz) + a little,
+// and X is MEASURED at every rebuild (k_posf), so atoms that fly far out of an open box only widen the shell.  Inside
+// the bound the float decision equals the exact one, so the list -- order included -- is k_nbl_build's.  The shell holds
+// ~5e-5 of the candidates: the exact branch is rare enough that its divergence does not show.  Pairs the reference meets
+// from the image side (lexneg ghost cells, boundary cells only) keep the exact path.
 __global__ void __launch_bounds__(256)
 k_posf(int ntot, const double4 *__restrict__ pos4, float4 *__restrict__ posf, unsigned int *__restrict__ xmax_bits)
 {
@@ -114,17 +114,25 @@ k_nbl_build2(Geom g, int n, const double4 *__restrict__ pos4, const float4 *__re
 {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31;
-  int cnt = 0, kept = 0;
+  int cnt = 0;
   if (i < n) {
     const double xmax = (double) __uint_as_float(*xmax_bits);
     const double rc = sqrt(g.cellsz);
-    // 4 > 2 sqrt(3), 2^-20 > 2^-22: the bound with room to spare, then rounded up into float
-    const float lim = (float) ((g.cellsz + 4.0 * rc * 1.1920928955078125e-7 * xmax + 9.5367431640625e-7 * g.cellsz) * 1.000001);
+    // 4 > 2 sqrt(3) and 2^-20 > 2^-21.3: the bound with room to spare; lo is rounded down, hi up
+    const double marg = 4.0 * rc * 1.1920928955078125e-7 * xmax + 9.5367431640625e-7 * g.cellsz;
+    const float lo = (float) ((g.cellsz - marg) * 0.999999), hi = (float) ((g.cellsz + marg) * 1.000001);
     const double4 pi = pos4[i];
     const float4 pf = posf[i];
     const int c = key[i];
     const int ey = g.edim[1], ez = g.edim[2];
     int *slot = idx + ((size_t) (i >> 5) * cap) * 32 + lane;
+    // in the shell between lo and hi the exact test decides
+    auto in_range = [&](float r2f, int j) -> bool {
+      if (r2f < lo) return true;
+      if (!(r2f < hi)) return false;
+      const double4 pj = ld256(&pos4[j]);
+      return r2_exact(pj.x - pi.x, pj.y - pi.y, pj.z - pi.z) < g.cellsz;
+    };
     for (int l = -1; l <= 1; l++)
       for (int m = -1; m <= 1; m++)
         for (int q = -1; q <= 1; q++) {
@@ -132,7 +140,7 @@ k_nbl_build2(Geom g, int n, const double4 *__restrict__ pos4, const float4 *__re
           const int b = cell_begin[c2], e = b + cell_count[c2];
           const bool lexneg = (l < 0) || (l == 0 && m < 0) || (l == 0 && m == 0 && q < 0);
           if (!(lexneg && e > n)) {
-            for (int j = b; j < e; j += 4) {               // phase A: four candidates per round
+            for (int j = b; j < e; j += 4) {               // four candidates per round
               const int j1 = min(j + 1, e - 1), j2 = min(j + 2, e - 1), j3 = min(j + 3, e - 1);
               const float4 q0 = posf[j], q1 = posf[j1], q2 = posf[j2], q3 = posf[j3];
               float dx = q0.x - pf.x, dy = q0.y - pf.y, dz = q0.z - pf.z;
@@ -143,14 +151,14 @@ k_nbl_build2(Geom g, int n, const double4 *__restrict__ pos4, const float4 *__re
               const float r2 = dx * dx + dy * dy + dz * dz;
               dx = q3.x - pf.x; dy = q3.y - pf.y; dz = q3.z - pf.z;
               const float r3 = dx * dx + dy * dy + dz * dz;
-              if (j != i && r0 < lim) { if (!COUNT_ONLY && cnt < cap) slot[(size_t) cnt * 32] = j; cnt++; }
-              if (j + 1 < e && j + 1 != i && r1 < lim) { if (!COUNT_ONLY && cnt < cap) slot[(size_t) cnt * 32] = j + 1; cnt++; }
-              if (j + 2 < e && j + 2 != i && r2 < lim) { if (!COUNT_ONLY && cnt < cap) slot[(size_t) cnt * 32] = j + 2; cnt++; }
-              if (j + 3 < e && j + 3 != i && r3 < lim) { if (!COUNT_ONLY && cnt < cap) slot[(size_t) cnt * 32] = j + 3; cnt++; }
+              if (j != i && r0 < hi && in_range(r0, j)) { if (!COUNT_ONLY && cnt < cap) slot[(size_t) cnt * 32] = j; cnt++; }
+              if (j + 1 < e && j + 1 != i && r1 < hi && in_range(r1, j + 1)) { if (!COUNT_ONLY && cnt < cap) slot[(size_t) cnt * 32] = j + 1; cnt++; }
+              if (j + 2 < e && j + 2 != i && r2 < hi && in_range(r2, j + 2)) { if (!COUNT_ONLY && cnt < cap) slot[(size_t) cnt * 32] = j + 2; cnt++; }
+              if (j + 3 < e && j + 3 != i && r3 < hi && in_range(r3, j + 3)) { if (!COUNT_ONLY && cnt < cap) slot[(size_t) cnt * 32] = j + 3; cnt++; }
             }
             continue;
           }
-          for (int j = b; j < e; j++) {                    // boundary cells with images: exact at once, as k_nbl_build
+          for (int j = b; j < e; j++) {                    // boundary cells with images: the exact path of k_nbl_build
             if (j == i) continue;
             double dx, dy, dz;
             if (j >= n && lexneg) {
@@ -163,36 +171,13 @@ k_nbl_build2(Geom g, int n, const double4 *__restrict__ pos4, const float4 *__re
               dx = pj.x - pi.x; dy = pj.y - pi.y; dz = pj.z - pi.z;
             }
             if (r2_exact(dx, dy, dz) < g.cellsz) {
-              if (!COUNT_ONLY && cnt < cap) slot[(size_t) cnt * 32] = ~j;
+              if (!COUNT_ONLY && cnt < cap) slot[(size_t) cnt * 32] = j;
               cnt++;
             }
           }
         }
-    if (!COUNT_ONLY) {                                     // phase B: exact test of my own entries, compacted in place
-      // four entries per round: their slots, then their records, are requested together (a round is two dependent
-      // memory latencies, not eight); an entry is written back at or below its own position, so reading ahead is safe
-      const int m = min(cnt, cap);
-      for (int k = 0; k < m; k += 4) {
-        int j[4]; double4 pj[4];
-#pragma unroll
-        for (int u = 0; u < 4; u++) j[u] = slot[(size_t) min(k + u, m - 1) * 32];
-#pragma unroll
-        for (int u = 0; u < 4; u++) pj[u] = ld256(&pos4[j[u] < 0 ? ~j[u] : j[u]]);
-#pragma unroll
-        for (int u = 0; u < 4; u++) {
-          if (k + u >= m) break;
-          const bool marked = j[u] < 0;
-          const int jj = marked ? ~j[u] : j[u];
-          if (marked || r2_exact(pj[u].x - pi.x, pj[u].y - pi.y, pj[u].z - pi.z) < g.cellsz) {
-            slot[(size_t) kept * 32] = jj; kept++;
-          }
-        }
-      }
-      num[i] = kept;
-    } else num[i] = cnt;
+    num[i] = cnt;
   }
-  // table sizing and the "neighbor table full" test look at the candidates of phase A (an upper bound of the
-  // list length, within a fraction of a percent of it)
   int mx = cnt;
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));

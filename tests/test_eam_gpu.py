@@ -130,10 +130,10 @@ def test_golden_trajectory(case, lpa):
 
 
 @pytest.mark.parametrize("case", GOLDEN_CASES)
-def test_two_phase_nblist_equals_exact_build(case):
-    """The two-phase list build (float filter with a measured error margin, then the exact test: k_nbl_build2) gives
-    the list of the exact-only build (k_nbl_build) -- same pairs in the same order, hence bit-identical forces --
-    on periodic images, free surfaces and two species."""
+def test_filtered_nblist_equals_exact_build(case):
+    """The list build with the single-precision classifier (k_nbl_build2: float r^2 against cellsz -+ a measured error
+    margin, the exact test in the shell between) gives the list of the exact-only build (k_nbl_build) -- same pairs in
+    the same order, hence bit-identical forces -- on periodic images, free surfaces and two species."""
     g = Golden(case)
     s = g.steps[0]
     out = {}
@@ -264,7 +264,7 @@ def test_full_size_properties_and_kernel_variants():
     imd.ctx.invalidate_nblist()
     imd.calc_forces(0)
     r = imd.atoms(("id", "force", "epot", "rho", "dF"))
-    assert all(np.array_equal(a[k], r[k]) for k in ("force", "epot", "rho", "dF")), "two-phase list differs from the exact build"
+    assert all(np.array_equal(a[k], r[k]) for k in ("force", "epot", "rho", "dF")), "the filtered list differs from the exact build"
     imd.ctx.set_tuning(nbl_filter=1)
     imd.ctx.invalidate_nblist()
     imd.ctx.set_tuning(lpa=4, fused_table=0)
