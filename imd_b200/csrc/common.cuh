@@ -238,6 +238,7 @@ struct imdcu_ctx {
     int fused_table = 2;                     // pass 1 when the pair and rho tables share their grid: 1 k_eam_pass1_fused, 2 k_eam_pass1_rep4, 0 general kernel
     int ttm_overlap = 1;                     // imdcu_run_ttm: lattice kernel beside EAM pass 2
     int ttm_lat_smem = 1;                    // k_ttm_grid keeps the lattices in shared memory
+    int ttm3d_variant = 9;                   // direct 3-D sweep kernel: brick shape / CTAs per SM / loads up front (ttm3d.cu: T3D_VARIANTS)
     int ttm3d_tiled = 0;                     // 3-D sweep: 2.5-D tiled kernel instead of the direct one
   } tune;
 

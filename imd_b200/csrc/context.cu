@@ -67,6 +67,7 @@ extern "C" int imdcu_create(imdcu_ctx **out, int device)
     c->tune.rep4_block = env_int("IMDCU_REP4_BLOCK", 896);
     c->tune.nbl_filter = env_int("IMDCU_NBL_FILTER", 1);
     c->dbg_rebuild = env_int("IMDCU_DEBUG_REBUILD", 0);
+    c->tune.ttm3d_variant = env_int("IMDCU_TTM3D_VARIANT", 9);
     c->tune.ttm_overlap = env_int("IMDCU_TTM_OVERLAP", 1);
     c->tune.ttm_lat_smem = env_int("IMDCU_TTM_LAT_SMEM", 1);
     const char *e3 = getenv("IMDCU_TTM3D");
@@ -312,6 +313,7 @@ extern "C" int imdcu_set_tuning(imdcu_ctx *c, const char *key, int value)
   else if (k == "ttm_overlap") c->tune.ttm_overlap = value != 0;
   else if (k == "ttm_lat_smem") c->tune.ttm_lat_smem = value != 0;
   else if (k == "ttm3d_tiled") c->tune.ttm3d_tiled = value != 0;
+  else if (k == "ttm3d_variant") c->tune.ttm3d_variant = value;
   else return c->fail(IMDCU_EINVAL, "imdcu_set_tuning: unknown key " + k);
   return IMDCU_OK;
 }

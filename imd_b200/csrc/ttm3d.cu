@@ -134,34 +134,60 @@ k_ttm3d_diff(T3Args a)
 // is left to L1 (z, y within the CTA's 32 x 4 x 4 brick) and L2 (the 126 MB L2 holds many x planes),
 // latency is hidden by 2048 resident threads per SM instead of by a software pipeline.  Same
 // arithmetic, same results; which variant runs is decided by measurement (profiles/).
-constexpr int T3D_BX = 32, T3D_BY = 4, T3D_BZ = 4;
+constexpr int T3D_BX = 32;
 
-__global__ void __launch_bounds__(T3D_BX * T3D_BY * T3D_BZ, 2)
+// loads the compiler may not sink into the `active cell` branch (SPEC variants: every load of a cell is in flight before
+// natoms[c] is known, one memory round trip per thread instead of two; an inactive cell wastes its neighbour loads)
+__device__ __forceinline__ double t3_ld(const double *p)
+{
+  double v; asm volatile("ld.global.f64 %0, [%1];" : "=d"(v) : "l"(p)); return v;
+}
+__device__ __forceinline__ int t3_ldi(const int *p)
+{
+  int v; asm volatile("ld.global.s32 %0, [%1];" : "=r"(v) : "l"(p)); return v;
+}
+
+// BY x BZ rows of 32 cells per CTA, MINB CTAs per SM (sets the register budget), SPEC as above.  Same arithmetic in
+// every instantiation; which one runs is decided by measurement (imdcu_set_tuning("ttm3d_variant")).
+template <int BY, int BZ, int MINB, bool SPEC>
+__global__ void __launch_bounds__(T3D_BX * BY * BZ, MINB)
 k_ttm3d_diff_direct(T3Args a)
 {
-  __shared__ double s_red[T3D_BX * T3D_BY * T3D_BZ / 32];
+  __shared__ double s_red[T3D_BX * BY * BZ / 32];
   const int k = blockIdx.x * T3D_BX + threadIdx.x + 1;
-  const int j = blockIdx.y * T3D_BY + threadIdx.y + 1;
-  const int i = blockIdx.z * T3D_BZ + threadIdx.z + 1;
+  const int j = blockIdx.y * BY + threadIdx.y + 1;
+  const int i = blockIdx.z * BZ + threadIdx.z + 1;
   const bool inside = k <= a.nz && j <= a.ny && i <= a.nx;
   const int mn = a.fd_min_atoms;
   double eabs = 0.0;
   if (inside) {
     const long long c = t3_idx(a, i, j, k);
-    const int nc = a.natoms[c];
-    const double tc = a.temp_in[c];
-    const double src = a.source[c];
+    const long long qxm = c - a.py, qxp = c + a.py, qym = c - a.pz, qyp = c + a.pz, qzm = c - 1, qzp = c + 1;
+    int nc, nxm, nxp, nym, nyp, nzm, nzp;
+    double tc, src, txm, txp, tym, typ, tzm, tzp, kc, kxm, kxp, kym, kyp, kzm, kzp, ce, g, ti, u, xi, dens;
+    if (SPEC) {
+      nc = t3_ldi(a.natoms + c); tc = t3_ld(a.temp_in + c); src = t3_ld(a.source + c);
+      nxm = t3_ldi(a.natoms + qxm); nxp = t3_ldi(a.natoms + qxp); nym = t3_ldi(a.natoms + qym);
+      nyp = t3_ldi(a.natoms + qyp); nzm = t3_ldi(a.natoms + qzm); nzp = t3_ldi(a.natoms + qzp);
+      txm = t3_ld(a.temp_in + qxm); txp = t3_ld(a.temp_in + qxp); tym = t3_ld(a.temp_in + qym);
+      typ = t3_ld(a.temp_in + qyp); tzm = t3_ld(a.temp_in + qzm); tzp = t3_ld(a.temp_in + qzp);
+      kc = t3_ld(a.fd_k + c);
+      kxm = t3_ld(a.fd_k + qxm); kxp = t3_ld(a.fd_k + qxp); kym = t3_ld(a.fd_k + qym);
+      kyp = t3_ld(a.fd_k + qyp); kzm = t3_ld(a.fd_k + qzm); kzp = t3_ld(a.fd_k + qzp);
+      ce = t3_ld(a.Ce + c); g = t3_ld(a.fd_g + c); ti = t3_ld(a.md_temp + c); u = t3_ld(a.U + c);
+      xi = t3_ld(a.xi + c); dens = t3_ld(a.dens + c);
+    } else {
+      nc = a.natoms[c]; tc = a.temp_in[c]; src = a.source[c];
+    }
     if (a.laser_active) eabs = src * a.fd_vol * a.tau;
     if (nc >= mn) {
-      const long long qxm = c - a.py, qxp = c + a.py, qym = c - a.pz, qyp = c + a.pz, qzm = c - 1, qzp = c + 1;
-      const int nxm = a.natoms[qxm], nxp = a.natoms[qxp], nym = a.natoms[qym], nyp = a.natoms[qyp],
-                nzm = a.natoms[qzm], nzp = a.natoms[qzp];
-      const double txm = a.temp_in[qxm], txp = a.temp_in[qxp], tym = a.temp_in[qym], typ = a.temp_in[qyp],
-                   tzm = a.temp_in[qzm], tzp = a.temp_in[qzp];
-      const double kc = a.fd_k[c];
-      const double kxm = a.fd_k[qxm], kxp = a.fd_k[qxp], kym = a.fd_k[qym], kyp = a.fd_k[qyp],
-                   kzm = a.fd_k[qzm], kzp = a.fd_k[qzp];
-      const double ce = a.Ce[c], g = a.fd_g[c], ti = a.md_temp[c], u = a.U[c], xi = a.xi[c], dens = a.dens[c];
+      if (!SPEC) {
+        nxm = a.natoms[qxm]; nxp = a.natoms[qxp]; nym = a.natoms[qym]; nyp = a.natoms[qyp]; nzm = a.natoms[qzm]; nzp = a.natoms[qzp];
+        txm = a.temp_in[qxm]; txp = a.temp_in[qxp]; tym = a.temp_in[qym]; typ = a.temp_in[qyp]; tzm = a.temp_in[qzm]; tzp = a.temp_in[qzp];
+        kc = a.fd_k[c];
+        kxm = a.fd_k[qxm]; kxp = a.fd_k[qxp]; kym = a.fd_k[qym]; kyp = a.fd_k[qyp]; kzm = a.fd_k[qzm]; kzp = a.fd_k[qzp];
+        ce = a.Ce[c]; g = a.fd_g[c]; ti = a.md_temp[c]; u = a.U[c]; xi = a.xi[c]; dens = a.dens[c];
+      }
       const bool oxm = nxm >= mn, oxp = nxp >= mn, oym = nym >= mn, oyp = nyp >= mn, ozm = nzm >= mn, ozp = nzp >= mn;
       const double xmaxTe = oxp ? txp : tc, xminTe = oxm ? txm : tc;
       const double ymaxTe = oyp ? typ : tc, yminTe = oym ? tym : tc;
@@ -188,14 +214,49 @@ k_ttm3d_diff_direct(T3Args a)
   if (a.partials) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) eabs += __shfl_down_sync(0xffffffffu, eabs, o);
-    const int tid = (threadIdx.z * T3D_BY + threadIdx.y) * T3D_BX + threadIdx.x;
+    const int tid = (threadIdx.z * BY + threadIdx.y) * T3D_BX + threadIdx.x;
     if ((tid & 31) == 0) s_red[tid >> 5] = eabs;
     __syncthreads();
     if (tid == 0) {
       double s = 0.0;
-      for (int w = 0; w < T3D_BX * T3D_BY * T3D_BZ / 32; w++) s += s_red[w];
+      for (int w = 0; w < T3D_BX * BY * BZ / 32; w++) s += s_red[w];
       a.partials[(blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x] = s;
     }
+  }
+}
+
+// the instantiations that exist (ttm3d_variant): {BY, BZ, MINB, SPEC}
+static const int T3D_VARIANTS[][4] = {
+  {4, 4, 2, 0},      // 0: 512 threads, 64 registers (a few spilled): the round-1 kernel
+  {4, 4, 2, 1},      // 1: the same with every load issued before natoms[c] is known
+  {4, 2, 3, 0},      // 2: 256 threads, 3 CTAs per SM: 80 registers, 768 resident threads
+  {4, 2, 3, 1},      // 3
+  {4, 2, 4, 1},      // 4: 256 threads, 4 CTAs per SM: 64 registers
+  {2, 2, 6, 1},      // 5: 128 threads, 6 CTAs per SM: 80 registers
+  {4, 2, 2, 1},      // 6: 256 threads, 2 CTAs per SM: up to 128 registers, 512 resident threads
+  {4, 1, 8, 1},      // 7: 128 threads (one x plane of 4 rows), 8 CTAs per SM: 64 registers
+  {2, 4, 4, 1},      // 8: 256 threads as 2 rows x 4 planes
+  {8, 1, 4, 1},      // 9: 256 threads as 8 rows of one plane                              <- default (measured best)
+  {4, 2, 5, 1},      // 10: 256 threads, 5 CTAs per SM: 48 registers, 1280 resident threads
+  {2, 2, 8, 1},      // 11: 128 threads as 2 rows x 2 planes, 8 CTAs per SM
+};
+static const int T3D_NVARIANTS = (int) (sizeof(T3D_VARIANTS) / sizeof(T3D_VARIANTS[0]));
+
+static void t3d_launch(int variant, dim3 grid, dim3 block, cudaStream_t st, const T3Args &a)
+{
+  switch (variant) {
+    case 1: k_ttm3d_diff_direct<4, 4, 2, true><<<grid, block, 0, st>>>(a); break;
+    case 2: k_ttm3d_diff_direct<4, 2, 3, false><<<grid, block, 0, st>>>(a); break;
+    case 3: k_ttm3d_diff_direct<4, 2, 3, true><<<grid, block, 0, st>>>(a); break;
+    case 4: k_ttm3d_diff_direct<4, 2, 4, true><<<grid, block, 0, st>>>(a); break;
+    case 5: k_ttm3d_diff_direct<2, 2, 6, true><<<grid, block, 0, st>>>(a); break;
+    case 6: k_ttm3d_diff_direct<4, 2, 2, true><<<grid, block, 0, st>>>(a); break;
+    case 7: k_ttm3d_diff_direct<4, 1, 8, true><<<grid, block, 0, st>>>(a); break;
+    case 8: k_ttm3d_diff_direct<2, 4, 4, true><<<grid, block, 0, st>>>(a); break;
+    case 9: k_ttm3d_diff_direct<8, 1, 4, true><<<grid, block, 0, st>>>(a); break;
+    case 10: k_ttm3d_diff_direct<4, 2, 5, true><<<grid, block, 0, st>>>(a); break;
+    case 11: k_ttm3d_diff_direct<2, 2, 8, true><<<grid, block, 0, st>>>(a); break;
+    default: k_ttm3d_diff_direct<4, 4, 2, false><<<grid, block, 0, st>>>(a); break;
   }
 }
 
@@ -395,6 +456,7 @@ extern "C" int imdcu_ttm3d_diff(imdcu_ctx *c, double tau, int diff_substeps, int
   a.source = t.source.p; a.dens = t.dens.p; a.U = t.U.p; a.xi = t.xi.p;
   // variant: IMDCU_TTM3D=tiled selects the 2.5-D shared-memory kernel, default is the direct one
   const bool tiled = c->tune.ttm3d_tiled != 0;
+  const int variant = (c->tune.ttm3d_variant >= 0 && c->tune.ttm3d_variant < T3D_NVARIANTS) ? c->tune.ttm3d_variant : 0;
   dim3 grid, block;
   if (tiled) {
     // x chunk: enough CTAs for >= 4 waves of 148 SMs x 4 resident CTAs, at least 8 planes per CTA
@@ -409,7 +471,8 @@ extern "C" int imdcu_ttm3d_diff(imdcu_ctx *c, double tau, int diff_substeps, int
     grid = dim3(gx, gy, div_up(t.nx, chunk)); block = dim3(T3_BX, T3_BY);
   } else {
     a.chunk = 0;
-    grid = dim3(div_up(t.nz, T3D_BX), div_up(t.ny, T3D_BY), div_up(t.nx, T3D_BZ)); block = dim3(T3D_BX, T3D_BY, T3D_BZ);
+    const int *tv = T3D_VARIANTS[variant];
+    grid = dim3(div_up(t.nz, T3D_BX), div_up(t.ny, tv[0]), div_up(t.nx, tv[1])); block = dim3(T3D_BX, tv[0], tv[1]);
     if (grid.y > 65535 || grid.z > 65535) return c->fail(IMDCU_EINVAL, "imdcu_ttm3d_diff: lattice too large for the launch grid");
   }
   const int nblocks = (int) (grid.x * grid.y * grid.z);
@@ -420,7 +483,7 @@ extern "C" int imdcu_ttm3d_diff(imdcu_ctx *c, double tau, int diff_substeps, int
     {
       PhaseTimer pt(c, 7);
       if (tiled) k_ttm3d_diff<<<grid, block, 0, c->stream>>>(a);
-      else k_ttm3d_diff_direct<<<grid, block, 0, c->stream>>>(a);
+      else t3d_launch(variant, grid, block, c->stream, a);
       c->count_launch();
     }
     if (a.partials) { k_ttm3d_sum<<<1, 256, 0, c->stream>>>(t.partials.p, nblocks, t.d_eabs); c->count_launch(); }
