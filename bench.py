@@ -236,13 +236,13 @@ def film_geometry(cells, world):
     return ncx, lx, gx
 
 
-def run_reference_ttm(cells, world, steps, nproc, nrb, substeps):
+def run_reference_ttm(cells, world, steps, nproc, nrb, substeps, binary=None, env_extra=None):
     """The reference's own EAM + TTM(1-D) MPI build (imd_ttm.c:75-156 per step, move_atoms_ttm) over oracle/shmpi on
     the bench film: ensemble ttm, pbc 0 1 1, shiftx_front/rear vacuum, the same FD lattice, sub-step count and pulse
     as the GPU arm (analytic Beer-Lambert source on both sides, ref_hooks_ttm.c).  TTM1D talks to ranks myid +- 1
     (imd_ttm.c:884-939, 3290-3333): cpu_dim must be P 1 1, P >= 2."""
     from imd_b200 import synth
-    binary = REF_TTM_NRB if nrb else REF_TTM
+    binary = binary or (REF_TTM_NRB if nrb else REF_TTM)
     if not os.path.exists(binary):
         return None
     spec = synth.AL
@@ -265,6 +265,7 @@ def run_reference_ttm(cells, world, steps, nproc, nrb, substeps):
         env = dict(os.environ, SHMPI_NP=str(nproc), SHMPI_RING_MB=str(ring_mb),
                    IMD_SRC_MU="%.17g" % tp.src_mu, IMD_SRC_ABS="%.17g" % tp.src_abs)
         env.pop("IMD_DUMP_DIR", None)
+        env.update(env_extra or {})
         t0 = time.perf_counter()
         res = subprocess.run([binary, "-p", "run.param"], cwd=run, env=env, stdout=subprocess.PIPE,
                              stderr=subprocess.STDOUT, text=True, timeout=1500)
@@ -276,9 +277,39 @@ def run_reference_ttm(cells, world, steps, nproc, nrb, substeps):
         tm, nsteps, natoms = float(m.group(1)), int(n.group(1)), int(n.group(2))
         return {"value": natoms * nsteps / tm, "natoms": natoms, "steps": nsteps, "nproc": nproc,
                 "main_loop_s": tm, "wall_s": wall, "binary": os.path.basename(binary), "mode": "mpi",
-                "cpu_dim": [nproc, 1, 1], "ttmdimx": gx}
+                "cpu_dim": [nproc, 1, 1], "ttmdimx": gx,
+                "stdout_tail": "\n".join(ln for ln in res.stdout.splitlines() if "IMD_CUDA_TIMING" in ln or "imd_cuda:" in ln)}
     finally:
         shutil.rmtree(work, ignore_errors=True)
+
+
+IMD_CUDA_TTM = os.path.join(ROOT, "integration", "_bin", "imd_mpi_eam_ttm_tmm_nbl_cuda")
+
+
+def run_imd_cuda_binary(cells, steps, substeps):
+    """IMD ITSELF with the CUDA hot path (integration/imd_cuda.c: the reference's own host program, parameter parser,
+    generator and main loop, linked against libimdcu.so) on the bench film, one rank on one GPU: the same parameter
+    file the reference arm gets except cpu_dim 1 1 1.  Atoms stay on the device; per step only the global sums come
+    back.  Timed by IMD's own main-loop timer (MPI_Wtime: wall clock), like the reference arm.  That timer also
+    holds what happens ONCE inside the first calc_forces (CUDA context, cell_array packed and uploaded, the count pass
+    of the first list build: ~1.2 s, and it varies between runs); the stub reports the duration of that first call
+    (IMD_CUDA_TIMING=1) and the rate is the other steps over the rest of the timer."""
+    r = run_reference_ttm(cells, 1, steps, 1, False, substeps, binary=IMD_CUDA_TTM, env_extra={"IMD_CUDA_TIMING": "1"})
+    if not r:
+        return None
+    m = re.search(r"first calc_forces ([0-9.eE+-]+) s; per step calc_forces ([0-9.eE+-]+) ms, calc_ttm ([0-9.eE+-]+) ms, "
+                  r"move_atoms ([0-9.eE+-]+) ms", r.get("stdout_tail", ""))
+    if not m:
+        raise RuntimeError("IMD-with-CUDA run printed no IMD_CUDA_TIMING line: %s" % r.get("stdout_tail", "")[-300:])
+    first, in_lib = float(m.group(1)), float(m.group(2)) + float(m.group(3)) + float(m.group(4))
+    rest, nrest = r["main_loop_s"] - first, r["steps"] - 1
+    return {"value": r["natoms"] * nrest / rest, "steps": nrest, "ms_per_step": 1e3 * rest / nrest, "first_call_s": first,
+            "ms_per_step_in_library": in_lib, "binary": r["binary"],
+            "sample": ("integration/_bin/%s (IMD's own host + libimdcu.so), 1 rank on 1 GPU, the bench film, %d steps: "
+                       "IMD's main-loop timer %.3f s, of which the first calc_forces %.3f s (CUDA context, cell_array "
+                       "packed and uploaded, first list build; not part of the rate); the other %d steps %.3f ms each, "
+                       "%.3f ms of that inside libimdcu.so" % (r["binary"], r["steps"], r["main_loop_s"], first, nrest,
+                                                                1e3 * rest / nrest, in_lib))}
 
 
 def bench_ttm_params(gx, substeps, tmm):
@@ -655,8 +686,20 @@ def our_arm(args, rank, local_rank, world):
                 "roofline": roofline, "cpu_baseline": cpu, "phases": phases}
         if slabs:
             line["slabs"] = slabs
-        print(json.dumps(line))
     imd.close()
+    if rank == 0:
+        # second end-to-end figure: the drop-in binary itself (the number a user of the reference sees)
+        if world == 1 and args.ttm and not args.nrb and not args.tmm and not args.no_cpu_baseline and args.imd_binary_steps > 0:
+            try:
+                torch.cuda.synchronize()
+                rb = run_imd_cuda_binary(args.cells, args.imd_binary_steps, args.ttm_substeps)
+                if rb:
+                    line["e2e_imd_binary"] = {"value": rb["value"], "unit": UNIT, "ms_per_step": rb["ms_per_step"],
+                                              "ms_per_step_in_library": rb["ms_per_step_in_library"],
+                                              "first_call_s": rb["first_call_s"], "sample": rb["sample"]}
+            except Exception as ex:
+                line["e2e_imd_binary"] = {"value": None, "unit": UNIT, "sample": "failed: %s" % str(ex)[-300:]}
+        print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
     return 0
@@ -843,6 +886,8 @@ def main():
                     help="cubic fcc cells per GPU (default 100 100 100 for the EAM+TTM film, 80 80 80 for --workload nve)")
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--profile-steps", type=int, default=5)
+    ap.add_argument("--imd-binary-steps", type=int, default=400,
+                    help="N = 1: steps of the extra run of IMD-with-CUDA (integration/_bin), 0 = skip")
     ap.add_argument("--per-step", type=int, default=0, help="diagnostic: also time this many single steps, printed to stderr")
     ap.add_argument("--equal-slabs", action="store_true", help="N > 1: the reference's equal-width x slabs instead of slabs of equal atom count")
     ap.add_argument("--no-cpu-baseline", action="store_true")

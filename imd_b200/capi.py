@@ -87,6 +87,7 @@ def load():
         "imdcu_ttm_set_eos": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, c_dp, c_dp, c_dp, C.POINTER(C.c_ubyte)]),
         "imdcu_ttm_init": (C.c_int, [vp, C.POINTER(TtmParamsC)]),
         "imdcu_ttm_set_tmm": (C.c_int, [vp, C.c_double, C.c_double, C.c_double, C.c_int, c_dp, C.c_int, c_dp]),
+        "imdcu_calc_forces_ttm": (C.c_int, [vp, C.c_int, c_dp, c_dp]),
         "imdcu_calc_ttm": (C.c_int, [vp, C.c_int, c_dp]),
         "imdcu_move_atoms_ttm": (C.c_int, [vp, c_dp, c_ip]),
         "imdcu_run_ttm": (C.c_int, [vp, C.c_int, C.c_int, c_dp]),
@@ -310,6 +311,12 @@ class Context:
                          tp.vlatdens, tp.atomic_weight, tp.atomic_charge, tp.Temin, tp.I0, tp.lam, tp.laser_t_0,
                          tp.laser_sigma_t, tp.tmm_laser_threshold, tp.src_mu, tp.src_abs)
         self._ck(self.L.imdcu_ttm_init(self.h, C.byref(par)))
+
+    def calc_forces_ttm(self, steps):
+        """imdcu_calc_forces_ttm: calc_forces + calc_ttm in one call (lattice kernel beside EAM pass 2)."""
+        o8 = np.zeros(8); o16 = np.zeros(16)
+        self._ck(self.L.imdcu_calc_forces_ttm(self.h, int(steps), _dp(o8), _dp(o16)))
+        return o8, dict(zip(TTM_SCALARS, o16))
 
     def calc_ttm(self, steps, want_scalars=True):
         out = np.zeros(16) if want_scalars else None

@@ -88,6 +88,25 @@ extern "C" int imdcu_calc_ttm(imdcu_ctx *c, int steps, double out16[16])
   return leave(c, imdcu_ttm_step(c, steps, out16));
 }
 
+// calc_forces + calc_ttm of one main-loop iteration in ONE call (imd_main_3d.c:406 and :534; nothing that touches the
+// atoms lies between them): calc_ttm's atom kernels run between the two EAM passes and its lattice kernel beside the
+// second one, as in imdcu_run_ttm.  Same inputs and results as imdcu_calc_forces followed by imdcu_calc_ttm.
+extern "C" int imdcu_calc_forces_ttm(imdcu_ctx *c, int steps, double out8[8], double out16[16])
+{
+  RET_IF(check_ready(c));
+  if (!c->ttm.inited) return c->fail(IMDCU_EINVAL, "imdcu_ttm_init has not been called");
+  if (c->profiling || !c->tune.ttm_overlap) {
+    const int rc = calc_forces_impl(c, steps, out8);
+    if (rc != IMDCU_OK) return leave(c, rc);
+    return leave(c, imdcu_ttm_step(c, steps, out16));
+  }
+  c->fuse_ttm_steps = steps;
+  const int rc = calc_forces_impl(c, steps, out8);
+  c->fuse_ttm_steps = -1;
+  if (rc != IMDCU_OK) return leave(c, rc);
+  return leave(c, imdcu_ttm_join(c, out16));
+}
+
 // move_atoms_ttm + check_nblist (imd_main_3d.c:564, :812)
 extern "C" int imdcu_move_atoms_ttm(imdcu_ctx *c, double out8[8], int *have_valid_nbl)
 {

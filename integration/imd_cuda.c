@@ -34,6 +34,20 @@ static int cu_resident = 0;          /* atoms have been handed to the device    
 static int cu_host_stale = 0;        /* the device is ahead of cell_array               */
 static long cu_syncs = 0;
 
+/* IMD_CUDA_TIMING=1: wall time spent inside the three hot entry points, printed by rank 0 when the program ends */
+#include <sys/time.h>
+static double cu_t_forces = 0, cu_t_ttm = 0, cu_t_move = 0, cu_t_first = 0;
+static long   cu_n_forces = 0;
+static int    cu_timing = -1;
+static double cu_now(void) { struct timeval tv; gettimeofday(&tv, NULL); return tv.tv_sec + 1e-6 * tv.tv_usec; }
+static void cu_report(void)
+{
+  if (cu_timing > 0 && myid == 0 && cu_n_forces > 1)
+    fprintf(stderr, "IMD_CUDA_TIMING calls %ld: first calc_forces %.3f s; per step calc_forces %.3f ms, calc_ttm %.3f ms, "
+            "move_atoms %.3f ms\n", cu_n_forces, cu_t_first, 1e3 * cu_t_forces / (cu_n_forces - 1),
+            1e3 * cu_t_ttm / cu_n_forces, 1e3 * cu_t_move / cu_n_forces);
+}
+
 static void cu_fail(const char *where, int rc)
 {
   char msg[1024];
@@ -56,6 +70,8 @@ static double  cu_src_mu = 1.0 / 80.0, cu_src_abs = 0.1;
 static double *cu_bb = NULL, *cu_k12 = NULL; /* rows of alu_eps_bb.dat / K12.dat (tmm_init, imd_tmm.c:117-118) */
 static int     cu_bb_rows = 0, cu_k12_rows = 0;
 static int     cu_ttm_P = 1;                 /* rank layout of the reference the FD lattice reproduces */
+static double  cu_ttm_out[16];               /* calc_ttm's scalars, computed together with calc_forces          */
+static int     cu_ttm_cached = 0;
 
 /* nn_read_table leaves a scattered point set + the Delaunay triangulation of libnn.  Our tables are
  * rectilinear (is x js header): hand x[], y[], z[][] and, per grid rectangle, which diagonal the
@@ -272,10 +288,20 @@ void imdcu_sync_to_host(void)
 void calc_forces(int steps)                          /* replaces imd_forces_nbl.c:295-1054 */
 {
   double out8[8];
+  double t0;
+  if (cu_timing < 0) { cu_timing = getenv("IMD_CUDA_TIMING") != NULL; if (cu_timing) atexit(cu_report); }
+  t0 = cu_timing ? cu_now() : 0.0;
   cu_attach();
   if (!cu_resident) cu_upload();
   if (!have_valid_nbl) CK(imdcu_invalidate_nblist(cu));   /* the host asked for a new list (imd_main_3d.c:273) */
+#ifdef TTM
+  /* calc_ttm() follows at imd_main_3d.c:534 with nothing in between that touches the atoms: both in one call, so that
+   * the lattice kernel runs beside the second EAM pass; calc_ttm() below hands out the cached scalars */
+  CK(imdcu_calc_forces_ttm(cu, steps, out8, cu_ttm_out));
+  cu_ttm_cached = 1;
+#else
   CK(imdcu_calc_forces(cu, steps, out8));
+#endif
   tot_pot_energy = out8[0]; virial = out8[1];
 #ifdef P_AXIAL
   vir_xx = out8[2]; vir_yy = out8[3]; vir_zz = out8[4];
@@ -285,6 +311,7 @@ void calc_forces(int steps)                          /* replaces imd_forces_nbl.
   nbl_count = imdcu_nbl_count(cu);
   nfc++;
   cu_host_stale = 1;
+  if (cu_timing) { if (cu_n_forces == 0) cu_t_first = cu_now() - t0; else cu_t_forces += cu_now() - t0; cu_n_forces++; }
 #ifdef FORCE
   /* write_config_select(.., "force", ..) runs right after calc_forces (imd_main_3d.c:430): the wrapper syncs */
 #endif
@@ -380,9 +407,11 @@ int tmm_init(void)
 
 void calc_ttm(void)                                  /* replaces imd_ttm.c:75-156 */
 {
-  double o[16];
+  double *o = cu_ttm_out;
+  double t0 = cu_timing > 0 ? cu_now() : 0.0;
   if (cu == NULL || !cu_resident) error("imd_cuda: calc_ttm before the first calc_forces");
-  CK(imdcu_calc_ttm(cu, steps, o));
+  if (!cu_ttm_cached) CK(imdcu_calc_ttm(cu, steps, o));     /* a call without calc_forces in front: the separate entry */
+  cu_ttm_cached = 0;
   diff_substeps = (int) o[0]; max_dt_ttm = o[1];
   last_active_cell_global = last_active_cell_local = (int) o[2];
   cur_vlattice_proc = (int) o[3];
@@ -391,17 +420,20 @@ void calc_ttm(void)                                  /* replaces imd_ttm.c:75-15
   tot_elec_energy_local = myid == 0 ? o[5] : 0.0;
   laser_active = (o[9] != 0.0);
   tmm_time = o[10];
+  if (cu_timing > 0) cu_t_ttm += cu_now() - t0;
 }
 
 void move_atoms_ttm(void)                            /* replaces imd_integrate.c:581-811 */
 {
   double out8[8];
   int valid = 0;
+  double t0 = cu_timing > 0 ? cu_now() : 0.0;
   if (cu == NULL || !cu_resident) error("imd_cuda: move_atoms_ttm before the first calc_forces");
   CK(imdcu_move_atoms_ttm(cu, out8, &valid));
   tot_kin_energy = out8[0];
   have_valid_nbl = valid;
   cu_host_stale = 1;
+  if (cu_timing > 0) cu_t_move += cu_now() - t0;
 }
 
 /* ttm_writeout (imd_ttm.c:1683-1969): <outfiles>.<number>.ttm, one line per FD cell, then the virtual lattice

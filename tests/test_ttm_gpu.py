@@ -325,3 +325,47 @@ def test_full_size_calc_ttm_vs_oracle():
         imd.move_atoms_ttm()
     assert int(lat["fields"]["natoms"].max()) > 100000
     imd.close(); ttm.close()
+
+
+def test_fused_forces_ttm_call_equals_the_two_calls():
+    """imdcu_calc_forces_ttm (calc_forces + calc_ttm in one call, lattice kernel beside EAM pass 2: what the IMD stub
+    uses) against imdcu_calc_forces followed by imdcu_calc_ttm, step by step on the same golden start: scalars, atoms
+    and FD lattice bit for bit."""
+    g = TtmGolden(TTM_CASES[0])
+    runs = []
+    for fused in (False, True):
+        a = g.atoms(0)
+        imd = host.Imd(0)
+        imd.setup_potentials(g.tables)
+        imd.make_box(g.box, (0, 1, 1), g.margin)
+        imd.set_params(1, g.timestep)
+        if g.pdecay:
+            imd.ctx.set_pdecay(*g.pdecay)
+        imd.set_atoms(a["pos"], a["mom"], a["mass"], a["type"], a["id"])
+        imd.init_ttm(g.tp, g.eos, g.nranks)
+        hist = []
+        for step in range(8):
+            if fused:
+                o8, sc = imd.ctx.calc_forces_ttm(step)
+            else:
+                o8 = imd.ctx.calc_forces(step)
+                sc = imd.ctx.calc_ttm(step)
+            imd.ctx.move_atoms_ttm()
+            hist.append((o8.copy(), dict(sc)))
+        runs.append((hist, imd.atoms(("id", "pos", "mom", "force")), imd.ttm_lattice()))
+        imd.close()
+    (h0, a0, l0), (h1, a1, l1) = runs
+    for (o0, s0), (o1, s1) in zip(h0, h1):
+        assert np.array_equal(o0, o1)
+        assert all(s0[k] == s1[k] or (np.isnan(s0[k]) and np.isnan(s1[k])) for k in s0), (s0, s1)
+    for k in ("pos", "mom", "force"):
+        assert np.array_equal(a0[k], a1[k]), k
+    def same_bits(x0, x1, key):                                   # FD cells, xi, v_com, virtual lattice: the same bits
+        if isinstance(x0, dict):
+            assert set(x0) == set(x1), key
+            for k in x0:
+                same_bits(x0[k], x1[k], "%s.%s" % (key, k))
+        else:
+            x0, x1 = np.asarray(x0), np.asarray(x1)
+            assert x0.shape == x1.shape and x0.tobytes() == x1.tobytes(), key
+    same_bits(l0, l1, "lattice")
