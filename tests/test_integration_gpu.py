@@ -265,3 +265,95 @@ def test_ttm_cuda_binary_equals_reference_ttm_build(tmp_path):
             print("  .ttm column %-8s worst relative difference %.2e  (%s)" % (cols[col], worst[col], where[col]))
     print(".ttm files 0..%d: worst relative difference %.2e" % (steps // ttm_int, worst.max()))
     assert worst.max() < 5e-6
+
+
+def _ngpu():
+    import torch
+    return torch.cuda.device_count()
+
+
+@needs_mpi_bins
+@pytest.mark.gpu
+def test_mpi_cuda_binary_on_two_gpus_equals_serial_reference(tmp_path):
+    """imd_mpi_eam_nve_nbl_cuda on TWO ranks, one GPU each (cpu_dim 2 1 1: IMD distributes the atoms, the stub hands
+    each rank's cell_array to its device, x slabs over NCCL with the unique id broadcast by MPI_Bcast) against the
+    serial reference started from the same configuration file."""
+    if _ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    steps = 30
+    work = str(tmp_path)
+    synth.make_eam_tables(synth.CU, work)
+    pos, box = synth.fcc_lattice((12, 6, 6), synth.CU.a)
+    synth.write_config_file(os.path.join(work, "start.conf"), pos, synth.maxwell_momenta(pos.shape[0], synth.CU.mass, 0.1),
+                            synth.CU.mass, box)
+    runs = {}
+    for name, ranks in (("ref", 1), ("cuda", 2)):
+        w = os.path.join(work, name)
+        os.makedirs(os.path.join(w, "out"))
+        synth.write_param_file(os.path.join(w, "run.param"), synth.CU, (12, 6, 6), steps, "out/run", potdir="..",
+                               pbc=(1, 1, 1), starttemp=0.1, nbl_margin=0.5, eng_int=1, extra="box_from_header 1\n",
+                               cpu_dim=(ranks, 1, 1), coordname="../start.conf")
+        runs[name] = w
+    ra, rb = run(REF_BIN, runs["ref"]), run_mpi(CUDA_MPI_NVE, runs["cuda"], 2)
+    assert ra.returncode == 0, ra.stdout[-3000:]
+    assert rb.returncode == 0, rb.stdout[-3000:]
+    assert "x slabs over NCCL" in rb.stdout
+    ea, eb = eng_of(runs["ref"]), eng_of(runs["cuda"])
+    assert ea.shape == eb.shape
+    err_pot = np.abs(ea[:, 1] - eb[:, 1]).max() / np.abs(ea[:, 1]).max()
+    err_kin = np.abs(ea[:, 2] - eb[:, 2]).max() / np.abs(ea[:, 2]).max()
+    print("imd_mpi_eam_nve_nbl_cuda on 2 GPUs vs serial reference: Epot rel %.2e, T rel %.2e" % (err_pot, err_kin))
+    assert err_pot < 1e-9 and err_kin < 1e-8
+
+
+@needs_mpi_bins
+@pytest.mark.gpu
+def test_ttm_cuda_binary_on_two_gpus_equals_reference_ttm_build(tmp_path):
+    """imd_mpi_eam_ttm_tmm_nbl_cuda on two ranks / two GPUs against the reference's TTM build on two ranks: the SAME
+    parameter file for both (cpu_dim 2 1 1), .eng and .ttm files compared as in the one-GPU test."""
+    if _ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    from imd_b200 import synth as sy
+    steps, ttm_int = 12, 6
+    tp = sy.TtmParams(ttmdimx=16, fd_n_timesteps=20)
+    work = str(tmp_path)
+    sy.make_eam_tables(sy.AL, work)
+    sy.write_eos_files(sy.make_eos_tables(), work)
+    pos, box = sy.fcc_lattice((56, 6, 6), sy.AL.a)
+    sy.write_config_file(os.path.join(work, "start.conf"), pos, sy.maxwell_momenta(pos.shape[0], sy.AL.mass, 0.0258),
+                         sy.AL.mass, box)
+    runs = {}
+    for name in ("ref", "cuda"):
+        w = os.path.join(work, name)
+        os.makedirs(os.path.join(w, "out"))
+        ex = tp.param_text() + "box_from_header 1\nshiftx_front 20\nshiftx_rear 20\nttm_int %d\n" % ttm_int
+        sy.write_param_file(os.path.join(w, "run.param"), sy.AL, (56, 6, 6), steps, "out/run", potdir="..",
+                            pbc=(0, 1, 1), starttemp=0.0258, nbl_margin=0.4, eng_int=1, extra=ex, ensemble="ttm",
+                            cpu_dim=(2, 1, 1), coordname="../start.conf")
+        runs[name] = w
+    src = {"IMD_SRC_MU": "%.17g" % tp.src_mu, "IMD_SRC_ABS": "%.17g" % tp.src_abs}
+    ra, rb = run_mpi(REF_MPI_TTM, runs["ref"], 2, src), run_mpi(CUDA_MPI_TTM, runs["cuda"], 2, src)
+    assert ra.returncode == 0, ra.stdout[-3000:]
+    assert rb.returncode == 0, rb.stdout[-3000:]
+    assert "x slabs over NCCL" in rb.stdout
+    ea, eb = eng_of(runs["ref"]), eng_of(runs["cuda"])
+    assert ea.shape == eb.shape and ea.shape[1] >= 6
+    err_pot = np.abs(ea[:, 1] - eb[:, 1]).max() / np.abs(ea[:, 1]).max()
+    err_kin = np.abs(ea[:, 2] - eb[:, 2]).max() / np.abs(ea[:, 2]).max()
+    err_el = (np.abs(ea[:, 5] - eb[:, 5]) / np.abs(ea[:, 5])).max()
+    print("imd_mpi_eam_ttm_tmm_nbl_cuda on 2 GPUs vs reference TTM build: Epot rel %.2e, T rel %.2e, E_el rel %.2e"
+          % (err_pot, err_kin, err_el))
+    assert err_pot < 1e-8 and err_kin < 1e-7 and err_el < 2e-6
+    worst = 0.0
+    for n in range(1, steps // ttm_int + 1):                     # file 0: rank 0's uninitialised virtual lattice (see above)
+        ta = read_ttm(os.path.join(runs["ref"], "out", "run.%d.ttm" % n))
+        tb = read_ttm(os.path.join(runs["cuda"], "out", "run.%d.ttm" % n))
+        assert ta.shape == tb.shape, (n, ta.shape, tb.shape)
+        assert np.array_equal(ta[:, [0, 1, 2, 3, 16]], tb[:, [0, 1, 2, 3, 16]]), n
+        num = np.abs(ta - tb)
+        rel = np.where(np.abs(ta) > 1e-12, num / np.maximum(np.abs(ta), 1e-30), num)
+        for col in (10, 11, 12):
+            rel[:, col] = num[:, col] / max(np.abs(ta[:, col]).max(), 1e-30)
+        worst = max(worst, rel.max())
+    print(".ttm files 1..%d on 2 GPUs: worst relative difference %.2e" % (steps // ttm_int, worst))
+    assert worst < 5e-6
