@@ -80,3 +80,41 @@ def test_full_size_distrib_conserves_the_global_sums():
         sc = max(np.abs(d1[k]).max(), 1e-30)
         assert np.abs(a3 - d1[k]).max() <= 1e-5 * sc, k
     imd.close()
+
+
+def test_error_returns_of_the_round_2_entry_points():
+    """Bad arguments and wrong call order come back as IMDCU_EINVAL with a message, nothing exits or hangs:
+    imdcu_distrib, imdcu_comm_set_cuts, imdcu_set_tuning, imdcu_calc_forces_ttm."""
+    from imd_b200 import capi
+    imd = host.Imd(0)
+    imd.setup_potentials(synth.make_eam_tables(synth.CU))
+    with pytest.raises(capi.ImdcuError) as e:                    # cuts before the box exists
+        imd.ctx.comm_set_cuts([0, 4])
+    assert "imdcu_set_box first" in str(e.value)
+    imd.make_box(np.diag([30.0, 30.0, 30.0]), (1, 1, 1), 0.5)
+    imd.set_params(1, 0.1)
+    g = int(imd.global_cell_dim[0])
+    imd.ctx.comm_set_cuts([0, g])                                # one rank: the only valid cut array
+    with pytest.raises(capi.ImdcuError) as e:
+        imd.ctx.comm_set_cuts([0, g - 1])
+    assert "xcut[nranks] = global_cell_dim.x" in str(e.value)
+    pos, _ = synth.fcc_lattice((8, 8, 8), synth.CU.a)
+    imd.set_atoms(pos, synth.maxwell_momenta(pos.shape[0], synth.CU.mass, 0.05), synth.CU.mass)
+    with pytest.raises(capi.ImdcuError) as e:                    # and not once the atoms are there
+        imd.ctx.comm_set_cuts([0, g])
+    assert "already uploaded" in str(e.value)
+    imd.calc_forces(0)
+    with pytest.raises(capi.ImdcuError) as e:                    # empty or inverted histogram box
+        imd.ctx.distrib((4, 0, 1), (0, 0, 0), (30, 30, 30))
+    assert "dist_dim >= 1" in str(e.value)
+    with pytest.raises(capi.ImdcuError):
+        imd.ctx.distrib((4, 1, 1), (0, 0, 0), (30, 0, 30))
+    for key, val in (("fused_table", 3), ("rep4_block", 512), ("lpa", 3), ("no_such_knob", 1)):
+        with pytest.raises(capi.ImdcuError):
+            imd.ctx.set_tuning(**{key: val})
+    with pytest.raises(capi.ImdcuError) as e:                    # the fused TTM call without a TTM
+        imd.ctx.calc_forces_ttm(0)
+    assert "imdcu_ttm_init" in str(e.value)
+    d = imd.ctx.distrib((2, 2, 2), (0, 0, 0), (30, 30, 30))     # still usable after the rejected calls
+    assert d["num"].sum() == pos.shape[0]
+    imd.close()
