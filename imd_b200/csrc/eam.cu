@@ -36,9 +36,6 @@
 #ifndef EAM_UNROLL
 #define EAM_UNROLL 2
 #endif
-#ifndef EAM_ABLATE
-#define EAM_ABLATE 0           /* timing experiments on k_eam_pass1_fused (profiles/eam_ablate.sh), 0 = product */
-#endif
 #ifndef EAM_IDX_CS
 #define EAM_IDX_CS 0           /* 1: list slots with ld.global.cs (streaming, evict first) */
 #endif
@@ -100,22 +97,15 @@ struct NbrPipe {
     tn = 0;
     if (cnt > 0) { pn = rec(pos4, j1); if (MULTI) tn = type[j1]; }
     else pn = make_double4(0, 0, 0, 0);
-    jc = 0; jn = j1;
   }
-  int jc, jn;               // index of the record returned last / in flight (timing experiments only)
   __device__ __forceinline__ double4 rec(const double4 *pos4, int j)
   {
-#if EAM_ABLATE == 2      /* timing experiment: no position gather */
-    return make_double4(0.35 * (j & 7), 0.3 * ((j >> 3) & 7), 0.4 * ((j >> 6) & 7) + 1.1, 0.0);
-#else
     return NC ? ld256nc(&pos4[j]) : ld256(&pos4[j]);
-#endif
   }
   __device__ __forceinline__ double4 next(const double4 *pos4, const int *type, int k, int &jt)
   {
     const double4 pj = pn;
     if (MULTI) jt = tn;
-    if (EAM_ABLATE) { jc = jn; jn = j2; }
     if (k + 1 < cnt) { pn = rec(pos4, j2); if (MULTI) tn = type[j2]; }
     j2 = j3;
     if (k + 3 < cnt) j3 = LD_SLOT(sp + (size_t) (k + 3) * ST);
@@ -258,9 +248,6 @@ k_eam_pass1_fused(EamArgs a)
   const int sub = threadIdx.x % LPA;
   double acc[2] = {0.0, 0.0};
   int is_short = 0;
-#if EAM_ABLATE
-  const double zero = (double) (a.n < 0);
-#endif
   for (int base = blockIdx.x * apb; base < a.n; base += gridDim.x * apb) {
     const int i = base + threadIdx.x / LPA;
     const bool live = i < a.n;
@@ -274,37 +261,15 @@ k_eam_pass1_fused(EamArgs a)
 EAM_PRAGMA_UNROLL(EAM_UNROLL)
       for (int k = 0; k < np.cnt; k++) {
         int jt_unused = 0;
-#if EAM_ABLATE == 2
-        double4 pj = np.next(a.pos4, a.type, k, jt_unused);
-        pj.x += pi.x; pj.y += pi.y; pj.z += pi.z;
-#else
         const double4 pj = np.next(a.pos4, a.type, k, jt_unused);
-#endif
         const double dx = pj.x - pi.x, dy = pj.y - pi.y, dz = pj.z - pi.z;
         const double r2 = r2_exact(dx, dy, dz);
-#if EAM_ABLATE == 3      /* extra shared-memory gather of 32 bytes, records at 32-byte stride */
-        { const double2 *g2 = reinterpret_cast<const double2 *>(s_tab) + 2 * (size_t) (np.jc & 2047);
-          const double2 u0 = g2[0], u1 = g2[1]; rh += zero * (u0.x + u0.y + u1.x + u1.y); }
-#elif EAM_ABLATE == 5    /* extra shared-memory gather of 32 bytes, two arrays at 16-byte stride */
-        { const double2 *g2 = reinterpret_cast<const double2 *>(s_tab) + (size_t) (np.jc & 2047);
-          const double2 u0 = g2[0], u1 = g2[2048]; rh += zero * (u0.x + u0.y + u1.x + u1.y); }
-#elif EAM_ABLATE == 6    /* extra global gather, 32 lanes within 16 consecutive records (4 lines) */
-        { const int j2 = (i & ~31) + (np.jc & 15); const double4 u = ld256(&a.pos4[j2]); rh += zero * (u.x + u.y + u.z + u.w); }
-#elif EAM_ABLATE == 7    /* extra global gather, 32 lanes within 64 consecutive records (16 lines) */
-        { const int j2 = (i & ~31) + (np.jc & 63); const double4 u = ld256(&a.pos4[j2]); rh += zero * (u.x + u.y + u.z + u.w); }
-#elif EAM_ABLATE == 4    /* extra global gather of 32 bytes */
-        { const int j2 = np.jc + 64 < a.n ? np.jc + 64 : np.jc; const double4 u = ld256(&a.pos4[j2]); rh += zero * (u.x + u.y + u.z + u.w); }
-#endif
         if (r2 <= tp.end) {                                // pair: r2 <= end, rho: r2 < end (same end)
           if (a.count_ttm) nn++;
           int kk; double chi;
           tab_index(tp, r2, kk, chi, is_short);
-#if EAM_ABLATE == 1      /* no table rows */
-          const double2 q0 = make_double2(chi, 0.1), q1 = make_double2(0.01 * chi, 0.2), q2 = make_double2(chi, 0.001 * kk);
-#else
           const double2 *row = reinterpret_cast<const double2 *>(s_tab + 6 * (size_t) kk);
           const double2 q0 = row[0], q1 = row[1], q2 = row[2];   // {p0,dv} {d2v,r0} {drv,d2rv}
-#endif
           const double h = 0.5 * chi * (chi - 1);
           const double pot = q0.x + chi * q0.y + h * q1.x;
           const double grad = two_invstep * (q0.y + (chi - 0.5) * q1.x);
@@ -323,9 +288,6 @@ EAM_PRAGMA_UNROLL(EAM_UNROLL)
     if (live && sub == 0) {
       double pot, dF; int idummy = 0;
       TabCol te = tab_col(a.emb, a.emb.coef, 0);
-#if EAM_ABLATE == 1 || EAM_ABLATE == 2
-      fx *= zero; fy *= zero; fz *= zero; ee *= zero; vir *= zero; rh = rh * zero + 1.0; nn = 78;
-#endif
       pair_int2(te, rh, pot, dF, idummy);
       ee += pot;
       a.frc4[i] = make_double4(fx, fy, fz, ee);
