@@ -210,7 +210,11 @@ EAM_PRAGMA_UNROLL(EAM_UNROLL)
       a.frc4[i] = make_double4(fx, fy, fz, ee);
       a.rho[i] = rh;
       a.dF[i] = dF;
-      a.pos4[i].w = dF;            // pass 2 gathers F' with the position; pass 1 reads only x,y,z of other atoms
+      // Pass 2 gathers F' with the position.  This store overlaps, in time, with other CTAs' 256-bit loads of the same
+      // record.  In the PTX memory model a vector access is a set of scalar accesses: those to x, y, z never meet a
+      // store during this kernel (nothing writes them), and the one to w meets this store but pass 1 never uses the
+      // w it loaded -- old or new, the value is dead.  Pass 2 reads w only after this kernel has finished.
+      a.pos4[i].w = dF;
       if (a.count_ttm) a.numneighs[i] = nn;
       acc[0] += ee; acc[1] += vir;
     }
@@ -293,7 +297,7 @@ EAM_PRAGMA_UNROLL(EAM_UNROLL)
       a.frc4[i] = make_double4(fx, fy, fz, ee);
       a.rho[i] = rh;
       a.dF[i] = dF;
-      a.pos4[i].w = dF;
+      a.pos4[i].w = dF;            // benign overlap with other CTAs' record loads: see k_eam_pass1
       if (a.count_ttm) a.numneighs[i] = nn;
       acc[0] += ee; acc[1] += vir;
     }
@@ -383,7 +387,7 @@ EAM_PRAGMA_UNROLL(EAM_UNROLL)
       a.frc4[i] = make_double4(fx, fy, fz, ee);
       a.rho[i] = rh;
       a.dF[i] = dF;
-      a.pos4[i].w = dF;
+      a.pos4[i].w = dF;            // benign overlap with other CTAs' record loads: see k_eam_pass1
       if (a.count_ttm) a.numneighs[i] = nn;
       acc[0] += ee; acc[1] += vir;
     }
