@@ -370,6 +370,7 @@ int  imdcu_multi_ghost_counts(imdcu_ctx *ctx);               // x-stage ghost ce
 int  imdcu_multi_ghost_build(imdcu_ctx *ctx);                // x-stage ghost atoms + metadata at a rebuild
 int  imdcu_multi_ghost_refresh(imdcu_ctx *ctx);              // x-stage positions / F' every step
 int  imdcu_multi_allreduce(imdcu_ctx *ctx, void *buf, int count, int kind);   // kind 0 sum f64, 1 max f64, 2 sum i32
+int  imdcu_multi_allreduce2(imdcu_ctx *ctx, void *buf_a, int count_a, int kind_a, void *buf_b, int count_b, int kind_b);
 void imdcu_multi_release(imdcu_ctx *ctx);
 int  imdcu_multi_agree(imdcu_ctx *ctx, int local_rc);        // rank-local error -> the same return on every rank
 void imdcu_multi_abort(imdcu_ctx *ctx);                      // un-agreed failure: abort the communicator

@@ -136,6 +136,21 @@ int imdcu_multi_allreduce(imdcu_ctx *c, void *buf, int count, int kind)
   return IMDCU_OK;
 }
 
+// Two independent all-reduces as ONE NCCL launch (grouped collectives are fused): the integer and the double slab sums
+// of update_fd (imd_ttm.c:325-334), which the reference reduces with eight MPI_Allreduce calls.
+int imdcu_multi_allreduce2(imdcu_ctx *c, void *buf_a, int count_a, int kind_a, void *buf_b, int count_b, int kind_b)
+{
+  if (c->comm.nranks <= 1) return IMDCU_OK;
+  if (!c->comm.nccl) return c->fail(IMDCU_ENCCL, "the NCCL communicator was aborted after an error on this rank");
+  const ncclDataType_t da = (kind_a == 2 || kind_a == 3) ? ncclInt32 : ncclFloat64, db = (kind_b == 2 || kind_b == 3) ? ncclInt32 : ncclFloat64;
+  const ncclRedOp_t oa = (kind_a == 1 || kind_a == 3) ? ncclMax : ncclSum, ob = (kind_b == 1 || kind_b == 3) ? ncclMax : ncclSum;
+  NCCL_CHECK(c, ncclGroupStart());
+  if (count_a > 0) NCCL_CHECK(c, ncclAllReduce(buf_a, buf_a, (size_t) count_a, da, oa, comm_of(c), c->stream));
+  if (count_b > 0) NCCL_CHECK(c, ncclAllReduce(buf_b, buf_b, (size_t) count_b, db, ob, comm_of(c), c->stream));
+  NCCL_CHECK(c, ncclGroupEnd());
+  return IMDCU_OK;
+}
+
 // Error agreement: a rank-local failure (an atom left through an open end, a full neighbour table, a raised
 // device flag) must not let this rank leave the step while its peers queue the next collective -- that would
 // hang the job instead of failing it.  Every rank contributes its local code; all ranks return together.

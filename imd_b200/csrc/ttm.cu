@@ -1181,8 +1181,7 @@ static int ttm_atoms_part(imdcu_ctx *c, int steps)
   }
   // the 7 MPI_Allreduce of imd_ttm.c:325-334 as two calls on the packed buffers; afterwards every
   // GPU holds the global slab sums and advances the identical (replicated) FD lattice
-  RET_IF(imdcu_multi_allreduce(c, t.isum.p, 4 * G, 2));
-  RET_IF(imdcu_multi_allreduce(c, t.dsum.p, 3 * G, 0));
+  RET_IF(imdcu_multi_allreduce2(c, t.isum.p, 4 * G, 2, t.dsum.p, 3 * G, 0));      // one NCCL launch for both
   if (n > 0) {
     k_ttm_atoms2<<<nb, TTM_ANT, 0, st>>>(n, G, t.fd_hx, t.p.atomic_weight, c->mom4.p, c->type.p, t.fdi.p, t.isum.p,
                                      t.dsum.p);
