@@ -20,7 +20,9 @@ static int ensure_atom_capacity(imdcu_ctx *c, int64_t n)
   // arrays that also hold ghosts start with room for 50 % ghosts and grow on demand
   CU_CHECK(c, c->pos4.ensure(n + n / 2 + 1024));  CU_CHECK(c, c->pos4_alt.ensure_exact(c->pos4.cap));
   CU_CHECK(c, c->type.ensure(n + n / 2 + 1024));  CU_CHECK(c, c->type_alt.ensure_exact(c->type.cap));
-  CU_CHECK(c, c->stage.ensure(10 * (size_t) n + 64));
+  // headroom like the arrays above: on several GPUs the atom count of a rank creeps up by migration, and growing this
+  // 320 MB buffer (cudaMalloc + cudaFree) in the middle of a list rebuild stalls every rank for tens of milliseconds
+  CU_CHECK(c, c->stage.ensure(10 * (size_t) n + 64, 1.25));
   return IMDCU_OK;
 }
 

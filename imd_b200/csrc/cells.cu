@@ -199,8 +199,9 @@ int imdcu_refresh_ghosts(imdcu_ctx *c, bool at_build)
     c->count_launch();
   }
   CU_CHECK(c, cudaGetLastError());
+  if (at_build) imdcu_dbg_mark(c, "g.refresh_yz");
   if (at_build && multi) RET_IF(imdcu_multi_ghost_build(c));
-  if (at_build) imdcu_dbg_mark(c, "ghost_refresh+build");
+  if (at_build) imdcu_dbg_mark(c, "g.build_x");
   return IMDCU_OK;
 }
 
@@ -279,6 +280,7 @@ int imdcu_rebuild_cells(imdcu_ctx *c)
         c->count_launch();
       }
     }
+    imdcu_dbg_mark(c, "g.counts");
     CU_CHECK(c, cub::DeviceScan::ExclusiveSum(c->cub_tmp.p, scan_bytes, c->gcell_off.p, c->gcell_off.p,
                                               nplan + 1, st));
     c->count_launch();
@@ -287,6 +289,7 @@ int imdcu_rebuild_cells(imdcu_ctx *c)
       CU_CHECK(c, cudaMemcpyAsync(&h_off[s], c->gcell_off.p + c->gstage_cells[s], sizeof(int),
                                   cudaMemcpyDeviceToHost, st));
     CU_CHECK(c, cudaStreamSynchronize(st));
+    imdcu_dbg_mark(c, "g.scan");
     for (int s = 0; s < 4; s++) c->gstage_atoms[s] = h_off[s];
     c->ng = h_off[3];
     const int64_t nt = c->n + c->ng;
@@ -296,6 +299,7 @@ int imdcu_rebuild_cells(imdcu_ctx *c)
     CU_CHECK(c, c->ghost_root.ensure(c->ng, 1.1)); CU_CHECK(c, c->ghost_tcode.ensure(c->ng, 1.1));
     CU_CHECK(c, c->ghost_gid.ensure(c->ng, 1.1));
     CU_CHECK(c, c->ghost_raw.ensure(3 * c->ng, 1.1));
+    imdcu_dbg_mark(c, "g.alloc");
     k_ghost_begin<<<div_up(nplan, 256), 256, 0, st>>>(nplan, n, c->d_gplan.p, c->gcell_off.p, c->cell_begin.p);
     c->count_launch();
     for (int s = 0; s < 3; s++) {

@@ -66,7 +66,7 @@ extern "C" int imdcu_create(imdcu_ctx **out, int device)
     c->tune.fused_table = env_int("IMDCU_FUSED_TABLE", 2);
     c->tune.rep4_block = env_int("IMDCU_REP4_BLOCK", 896);
     c->tune.nbl_filter = env_int("IMDCU_NBL_FILTER", 1);
-    c->dbg_rebuild = env_int("IMDCU_DEBUG_REBUILD", 0);
+    c->dbg_rebuild = getenv("IMDCU_DEBUG_REBUILD") != nullptr && strcmp(getenv("IMDCU_DEBUG_REBUILD"), "0") != 0;
     c->tune.ttm3d_variant = env_int("IMDCU_TTM3D_VARIANT", 9);
     c->tune.ttm_overlap = env_int("IMDCU_TTM_OVERLAP", 1);
     c->tune.ttm_lat_smem = env_int("IMDCU_TTM_LAT_SMEM", 1);
@@ -290,7 +290,20 @@ void imdcu_dbg_mark(imdcu_ctx *c, const char *label, bool flush)
     c->dbg_line += buf;
   } else c->dbg_line.clear();
   c->dbg_t = std::chrono::steady_clock::now();
-  if (flush) { fprintf(stderr, "REBUILD rank %d n %lld ng %lld:%s\n", c->comm.rank, (long long) c->n, (long long) c->ng, c->dbg_line.c_str()); c->dbg_line.clear(); }
+  if (flush) {
+    // IMDCU_DEBUG_REBUILD=<prefix>: one file per rank (<prefix>.rank<r>), otherwise stderr (the ranks of a node share it)
+    const char *pre = getenv("IMDCU_DEBUG_REBUILD");
+    FILE *f = stderr;
+    if (pre && pre[0] && strcmp(pre, "1") != 0) {
+      const std::string path = std::string(pre) + ".rank" + std::to_string(c->comm.rank);
+      f = fopen(path.c_str(), "a");
+      if (!f) f = stderr;
+    }
+    fprintf(f, "REBUILD rank %d n %lld ng %lld cap %d:%s\n", c->comm.rank, (long long) c->n, (long long) c->ng, c->nbl_cap,
+            c->dbg_line.c_str());
+    if (f != stderr) fclose(f);
+    c->dbg_line.clear();
+  }
 }
 
 // ----------------------------------------------------------------------------- tuning

@@ -206,13 +206,14 @@ static int build_nblist_local(imdcu_ctx *c)
   const int n = (int) c->n;
   cudaStream_t st = c->stream;
   RET_IF(imdcu_check_flags(c));
+  imdcu_dbg_mark(c, "n.flags");
   if (n == 0) return IMDCU_OK;
   const int nb = div_up(n, 128);
   const size_t ntiles = (size_t) div_up(n, 32);
   const bool two_phase = c->tune.nbl_filter != 0;
   if (two_phase) {                           // single-precision copies of owned atoms and images, max |coordinate|
     const int ntot = n + (int) c->ng;
-    CU_CHECK(c, c->posf.ensure((size_t) ntot + 64));
+    CU_CHECK(c, c->posf.ensure((size_t) ntot + 64, 1.1));     // headroom: the ghost count changes at every rebuild
     CU_CHECK(c, cudaMemsetAsync(c->d_xmax, 0, sizeof(unsigned int), st));
     k_posf<<<div_up(ntot, 256), 256, 0, st>>>(ntot, c->pos4.p, c->posf.p, c->d_xmax);
     c->count_launch();
@@ -253,7 +254,9 @@ static int build_nblist_local(imdcu_ctx *c)
   // 3 % headroom: with migration the number of owned atoms creeps up, and every new maximum would otherwise
   // reallocate the whole list (cudaMalloc + cudaFree of ~1.6 GB at 4 M atoms) in the middle of a rebuild
   CU_CHECK(c, c->nbl_idx.ensure(ntiles * (size_t) c->nbl_cap * 32, 1.03));
+  imdcu_dbg_mark(c, "n.alloc");
   RET_IF(run(false));
+  imdcu_dbg_mark(c, "n.build");
   if (c->h_flags[1] > c->nbl_cap) {          // "neighbor table full": grow and redo once
     RET_IF(grow(c->h_flags[1]));
     RET_IF(run(false));
