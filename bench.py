@@ -486,6 +486,32 @@ def rear_boundary_state(cells, world):
     return nrb.init_nrb(pos, ids, box, (0, 1, 1), spec.a, 0.3)
 
 
+def bind_to_gpu_cpus(local_rank):
+    """Several ranks on one node: keep this rank's host thread -- and with it the pinned buffers it is about to allocate
+    -- on the CPUs NVML names as closest to its GPU (nvmlDeviceSetCpuAffinity).  Matters for the host-buffer (e2e)
+    path only: eight processes moving 384 MB per step each should not cross sockets.  Never fatal."""
+    try:
+        import pynvml
+        import torch
+        pynvml.nvmlInit()
+        uuid = str(torch.cuda.get_device_properties(local_rank).uuid)
+        h = None
+        for cand in (uuid, "GPU-" + uuid):
+            try:
+                h = pynvml.nvmlDeviceGetHandleByUUID(cand.encode() if hasattr(cand, "encode") else cand)
+                break
+            except Exception:
+                continue
+        if h is None:
+            h = pynvml.nvmlDeviceGetHandleByIndex(local_rank)
+        before = len(os.sched_getaffinity(0))
+        pynvml.nvmlDeviceSetCpuAffinity(h)
+        cpus = sorted(os.sched_getaffinity(0))
+        return "bound to %d of %d CPUs (%d..%d) near GPU %d" % (len(cpus), before, cpus[0], cpus[-1], local_rank)
+    except Exception as ex:
+        return "not bound (%s)" % str(ex)[:80]
+
+
 def our_arm(args, rank, local_rank, world):
     import torch
     import torch.distributed as dist
@@ -494,6 +520,7 @@ def our_arm(args, rank, local_rank, world):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (the product path has no CPU fallback)")
     torch.cuda.set_device(local_rank)
+    host_binding = bind_to_gpu_cpus(local_rank) if world > 1 and not args.no_cpu_binding else "one rank: not bound"
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
@@ -686,6 +713,10 @@ def our_arm(args, rank, local_rank, world):
                 "roofline": roofline, "cpu_baseline": cpu, "phases": phases}
         if slabs:
             line["slabs"] = slabs
+        line["e2e"]["host_binding_rank0"] = host_binding
+        if world > 1:
+            line["e2e"]["bound_by"] = ("every rank moves its atoms through host buffers each step (%.0f MB up, %.0f MB down per rank): "
+                                       "%d ranks share this node's PCIe root complexes and host memory" % (h2d / 1e6, d2h / 1e6, world))
     imd.close()
     if rank == 0:
         # second end-to-end figure: the drop-in binary itself (the number a user of the reference sees)
@@ -888,6 +919,7 @@ def main():
     ap.add_argument("--profile-steps", type=int, default=5)
     ap.add_argument("--imd-binary-steps", type=int, default=400,
                     help="N = 1: steps of the extra run of IMD-with-CUDA (integration/_bin), 0 = skip")
+    ap.add_argument("--no-cpu-binding", action="store_true", help="N > 1: do not bind the rank's host thread to the CPUs near its GPU")
     ap.add_argument("--per-step", type=int, default=0, help="diagnostic: also time this many single steps, printed to stderr")
     ap.add_argument("--equal-slabs", action="store_true", help="N > 1: the reference's equal-width x slabs instead of slabs of equal atom count")
     ap.add_argument("--no-cpu-baseline", action="store_true")
