@@ -260,8 +260,9 @@ def run_reference_ttm(cells, world, steps, nproc, nrb, substeps, binary=None, en
         synth.write_param_file(os.path.join(run, "run.param"), spec, (ncx, cells[1], cells[2]), steps, "out/run",
                                potdir="..", pbc=(0, 1, 1), starttemp=0.0258, nbl_margin=0.4, eng_int=0, extra=ex,
                                ensemble="ttm", cpu_dim=(nproc, 1, 1))
-        # shmpi ring per rank pair (virtual, touched where used): one yz plane of cells as 10 doubles per atom, x2
-        ring_mb = max(4, int(4 * cells[1] * cells[2] * 2 * 80 * 2 / 1e6) + 1)
+        # shmpi ring per rank pair (virtual memory, touched where used): two cell layers of a yz plane (~4 atoms per cubic
+        # cell and layer) at up to 240 bytes per atom (the -DNRB -DREFPOS build sends 18 doubles and more), x2 headroom
+        ring_mb = max(8, int(4 * cells[1] * cells[2] * 2 * 240 * 2 / 1e6) + 1)
         env = dict(os.environ, SHMPI_NP=str(nproc), SHMPI_RING_MB=str(ring_mb),
                    IMD_SRC_MU="%.17g" % tp.src_mu, IMD_SRC_ABS="%.17g" % tp.src_abs)
         env.pop("IMD_DUMP_DIR", None)
@@ -387,13 +388,17 @@ def reference_arm(args, rank, world):
     if rank != 0:
         return 0
     steps = reference_steps(args.cells, max(1, args.gpus), args.steps + args.warmup)
-    r = reference_sample(args, max(1, args.gpus), steps)
+    failure = None
+    try:
+        r = reference_sample(args, max(1, args.gpus), steps)
+    except Exception as ex:                               # the arm must always print its line
+        r, failure = None, "reference run failed: %s" % " ".join(str(ex).split())[-400:]
     base = {"metric": metric_name(args), "unit": UNIT, "impl": "reference", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": workload_config(args)}
     if r is None:
-        base["unavailable"] = "oracle/_ref binaries not built (make -C oracle ref needs /root/reference)"
+        base["unavailable"] = failure or "oracle/_ref binaries not built (make -C oracle ref needs /root/reference)"
         print(json.dumps(base))
         return 0
     sample = r["sample"]

@@ -345,7 +345,10 @@ static void ring_write(int dst, int tag, const char *data, int nbytes)
   char *ring = g_ring + ((size_t) g_rank * g_np + dst) * g_sh->ring_bytes;
   const size_t cap = g_sh->ring_bytes;
   const size_t need = sizeof(msg_hdr) + (((size_t) nbytes + 7) & ~(size_t) 7);
-  if (need > cap) die("message larger than the ring: raise SHMPI_RING_MB");
+  if (need > cap) {
+    fprintf(stderr, "shmpi[%d]: message of %d bytes (tag %d, to rank %d) does not fit the ring of %zu bytes\n", g_rank, nbytes, tag, dst, cap);
+    die("message larger than the ring: raise SHMPI_RING_MB");
+  }
   unsigned n = 0;
   uint64_t head = c->head;
   while (cap - (head - __atomic_load_n(&c->tail, __ATOMIC_ACQUIRE)) < need) spin_pause(&n);
