@@ -17,9 +17,10 @@
  *
  * Data flow: atoms live on the device from the first calc_forces on.  cell_array (types.h:188-349) is
  * refilled by imdcu_sync_to_host() before every writer (write_config, write_config_select, write_distrib,
- * write_pictures are entered through the one-line wrappers at the end of this file), so .chkpt, .force,
- * .dist files are written by the reference's own writers in the reference's own formats; .eng needs only
- * the global sums and .ttm only the FD lattice, which is assembled on rank 0 from the device.
+ * write_pictures are entered through the wrappers at the end of this file), so .chkpt, .force and picture
+ * files are written by the reference's own writers in the reference's own formats; .eng needs only the
+ * global sums, .ttm only the FD lattice, which is assembled on rank 0 from the device, and the distribution
+ * files (.dens .Ekin .Epot .vxavg) only per-bin sums, which imdcu_distrib makes on the device.
  * There is no CPU fallback: every entry point either runs on the GPU or stops with imderror().
  */
 #include "imd.h"
@@ -490,7 +491,126 @@ void __wrap_write_config_select(int fzhlr, char *suffix, void (*write_atoms_fun)
   imdcu_sync_to_host();
   __real_write_config_select(fzhlr, suffix, write_atoms_fun, write_header_fun);
 }
+/* ------------------------------------------------------------------ write_distrib (imd_distrib.c:33-218)
+ * dist_dens / dist_Ekin / dist_Epot / dist_vxavg need per-bin sums only: imdcu_distrib makes them on the device, and
+ * dist_size floats per quantity come back instead of every atom.  The files stay the reference's:
+ * headers by its write_distrib_header (:805), the density file by its write_distrib_density (:434, which reads
+ * num_1 / dist_size and fills dat_1, the globals of imd_distrib.c), the averaged quantities normalised and laid out
+ * as make_write_distrib_select does (:721-800).  Sums over the ranks are the reference's MPI_Reduce of float arrays.
+ * Any other dist_*_flag (press*, shock*, mdtemp) selects per-atom data this path does not carry: cell_array is
+ * refilled and the reference's own write_distrib runs.  IMD_CUDA_HOST_DISTRIB=1 forces that path for every flag. */
 void __real_write_distrib(int steps);
-void __wrap_write_distrib(int steps) { imdcu_sync_to_host(); __real_write_distrib(steps); }
+extern float *dat_1, *num_1;
+extern int dist_size;
+
+static int cu_dist_on_device(void)
+{
+  const char *e = getenv("IMD_CUDA_HOST_DISTRIB");
+  if (e != NULL && atoi(e) > 0) return 0;
+  if (cu == NULL || !cu_resident) return 0;
+  if (dist_mdtemp_flag) return 0;
+#ifdef STRESS_TENS
+  if (dist_press_flag || dist_presstens_flag) return 0;
+#endif
+#ifdef SHOCK
+  if (dist_Ekin_long_flag || dist_Ekin_trans_flag || dist_Ekin_comp_flag || dist_shock_shear_flag ||
+      dist_shear_aniso_flag || dist_pressoff_flag) return 0;
+#endif
+#ifdef DISLOC
+  if (Epot_diff == 1) return 0;
+#endif
+  return 1;
+}
+
+/* one averaged quantity: sum over ranks, divide by the count where there are atoms, write file and minmax line */
+static void cu_write_dist_select(float *sum, float *red, int mode, int fzhlr, char *suffix)
+{
+  FILE *out;
+  char fname[255];
+  float lo = 1e+10, hi = -1e+10;
+  int i, r = 0, s = 0, t = 0;
+#ifdef MPI
+  MPI_Reduce(sum, red, dist_size, MPI_FLOAT, MPI_SUM, 0, cpugrid);
+#else
+  red = sum;
+#endif
+  if (myid != 0) return;
+  for (i = 0; i < dist_size; i++)
+    if (num_1[i] > 0.0) {
+      red[i] /= num_1[i];
+      lo = MIN(lo, red[i]);
+      hi = MAX(hi, red[i]);
+    }
+  sprintf(fname, "%s.%u.%s", outfilename, fzhlr, suffix);
+  out = fopen(fname, "w");
+  if (NULL == out) error("Cannot open distribution file.");
+  write_distrib_header(out, mode, 1, suffix);
+  if (mode == DIST_FORMAT_BINARY) {
+    if (fwrite(red, sizeof(float), dist_size, out) != (size_t) dist_size) warning("distribution write incomplete!");
+  }
+  else if (mode == DIST_FORMAT_ASCII || mode == DIST_FORMAT_ASCII_COORD) {
+    for (i = 0; i < dist_size; i++) {
+      if (mode == DIST_FORMAT_ASCII_COORD) {
+        fprintf(out, "%d %d %d", r, s, t++);
+        if (t == dist_dim.z) { t = 0; s++; }
+        if (s == dist_dim.y) { s = 0; r++; }
+      }
+      fprintf(out, " %e\n", red[i]);
+    }
+  }
+  else error("unknown distribution output format");
+  fclose(out);
+  sprintf(fname, "%s.minmax.%s", outfilename, suffix);
+  out = fopen(fname, "a");
+  if (NULL == out) error("Cannot open minmax file.");
+  fprintf(out, "%d  %e %e\n", fzhlr, lo, hi);
+  fclose(out);
+}
+
+static void cu_write_distrib(int steps)
+{
+  static int told = 0;
+  int dim[3], fzhlr;
+  double ll[3], ur[3];
+  float *loc, *red;
+  is_big_endian = endian();
+  if (0.0 == dist_ur.x) {                            /* backup if dist_ur is not set, :41-47 */
+    dist_ur.x = box_x.x; dist_ur.y = box_y.y; dist_ur.z = box_z.z;
+  }
+  dim[0] = dist_dim.x; dim[1] = dist_dim.y; dim[2] = dist_dim.z;
+  ll[0] = dist_ll.x; ll[1] = dist_ll.y; ll[2] = dist_ll.z;
+  ur[0] = dist_ur.x; ur[1] = dist_ur.y; ur[2] = dist_ur.z;
+  dist_size = dist_dim.x * dist_dim.y * dist_dim.z;
+  fzhlr = steps / dist_int;
+  loc = cu_alloc((size_t) 4 * dist_size * sizeof *loc);        /* this rank: count, Ekin, Epot, v_x sums */
+  red = cu_alloc((size_t) 2 * dist_size * sizeof *red);        /* rank 0: summed count | one summed quantity */
+  CK(imdcu_distrib(cu, dim, ll, ur, loc, loc + dist_size, loc + 2 * dist_size, loc + 3 * dist_size));
+#ifdef MPI
+  MPI_Reduce(loc, red, dist_size, MPI_FLOAT, MPI_SUM, 0, cpugrid);     /* make_distrib_density, :423 */
+  num_1 = red;
+#else
+  num_1 = loc;
+#endif
+  dat_1 = red + dist_size;
+  if (!told && myid == 0) {
+    printf("imd_cuda: distributions (%d bins) are summed on the device\n", dist_size);
+    told = 1;
+  }
+  if (dist_Ekin_flag) cu_write_dist_select(loc + dist_size, dat_1, dist_Ekin_flag, fzhlr, "Ekin");
+  if (dist_Epot_flag) cu_write_dist_select(loc + 2 * dist_size, dat_1, dist_Epot_flag, fzhlr, "Epot");
+#if defined(SHOCK) || defined(TTM)
+  if (dist_vxavg_flag) cu_write_dist_select(loc + 3 * dist_size, dat_1, dist_vxavg_flag, fzhlr, "vxavg");
+#endif
+  if (myid == 0 && dist_dens_flag) write_distrib_density(dist_dens_flag, fzhlr);
+  num_1 = dat_1 = NULL;
+  free(loc); free(red);
+}
+
+void __wrap_write_distrib(int steps)
+{
+  if (cu_dist_on_device()) { cu_write_distrib(steps); return; }
+  imdcu_sync_to_host();
+  __real_write_distrib(steps);
+}
 void __real_write_pictures(int steps);
 void __wrap_write_pictures(int steps) { imdcu_sync_to_host(); __real_write_pictures(steps); }

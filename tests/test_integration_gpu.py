@@ -34,8 +34,8 @@ def write_inputs(work, steps, box=(8, 8, 8), extra=""):
                            starttemp=0.08, nbl_margin=0.5, eng_int=1, extra=extra)
 
 
-def run(binary, work, *args):
-    env = dict(os.environ)
+def run(binary, work, *args, env_extra=None):
+    env = dict(os.environ, **(env_extra or {}))
     env.pop("IMD_DUMP_DIR", None)
     res = subprocess.run([binary, "-p", "run.param", *args], cwd=work, env=env, stdout=subprocess.PIPE,
                          stderr=subprocess.STDOUT, text=True, timeout=600)
@@ -117,6 +117,7 @@ def test_chkpt_written_by_cuda_build_restarts_in_reference(tmp_path):
     ra, rb = run(REF_BIN, wa), run(CUDA_BIN, wb)
     assert ra.returncode == 0, ra.stdout[-3000:]
     assert rb.returncode == 0, rb.stdout[-3000:]
+    assert "distributions (60 bins) are summed on the device" in rb.stdout
     ca, cb = read_chkpt(chkpt_path(wa, 1)), read_chkpt(chkpt_path(wb, 1))
     assert ca.shape == cb.shape
     assert np.array_equal(ca[:, :3], cb[:, :3])                     # number, type, mass
@@ -124,14 +125,30 @@ def test_chkpt_written_by_cuda_build_restarts_in_reference(tmp_path):
     err = (np.abs(ca[:, 3:] - cb[:, 3:]).max(axis=0) / scale).max()
     print("run.1.chkpt (step %d), CUDA build vs reference: max rel err over columns %.2e" % (at, err))
     assert err < 1e-8
-    # write_distrib (imd_distrib.c:33-218) of the same steps, the reference's own writer behind sync_to_host:
-    # binary float32 after the header; the count (density) is exact, the averages are float sums in cell order
+    # write_distrib (imd_distrib.c:33-218) of the same steps.  wb: per-bin sums from the device (imdcu_distrib) in
+    # the reference's file layout; wc: the same binary with IMD_CUDA_HOST_DISTRIB=1, i.e. the reference's own
+    # write_distrib behind sync_to_host.  Binary float32 after the header; the count (density) is exact, the
+    # averages are float sums in cell order in the reference and double sums rounded once on the device.
+    wc = str(tmp_path / "cuda_hostdist")
+    os.makedirs(wc)
+    write_inputs(wc, steps, extra=extra)
+    rc = run(CUDA_BIN, wc, env_extra={"IMD_CUDA_HOST_DISTRIB": "1"})
+    assert rc.returncode == 0, rc.stdout[-3000:]
+    assert "summed on the device" not in rc.stdout
+    worst = 0.0
     for n in (0, 1, 2):
         for key, tol in (("dens", 0.0), ("Ekin", 1e-5), ("Epot", 1e-5)):
-            fa, fb = (np.frombuffer(open(os.path.join(w, "out", "run.%d.%s" % (n, key)), "rb").read().split(b"#E\n", 1)[1],
-                                    dtype="<f4") for w in (wa, wb))
-            assert fa.shape == fb.shape == (60,)
-            assert np.abs(fa - fb).max() <= tol * np.abs(fa).max(), (n, key, np.abs(fa - fb).max())
+            fa, fb, fc = (np.frombuffer(open(os.path.join(w, "out", "run.%d.%s" % (n, key)), "rb").read().split(b"#E\n", 1)[1],
+                                        dtype="<f4") for w in (wa, wb, wc))
+            assert fa.shape == fb.shape == fc.shape == (60,)
+            for f in (fb, fc):
+                assert np.abs(fa - f).max() <= tol * np.abs(fa).max(), (n, key, np.abs(fa - f).max())
+            worst = max(worst, np.abs(fa - fb).max() / np.abs(fa).max())
+    for key in ("dens", "Ekin", "Epot"):                            # <outfiles>.minmax.<key>: one line per file
+        ma, mb = (np.loadtxt(os.path.join(w, "out", "run.minmax.%s" % key)) for w in (wa, wb))
+        assert ma.shape == mb.shape == (3, 3)
+        assert np.allclose(ma, mb, rtol=1e-5, atol=0)
+    print("device-side distributions vs the reference's files: worst rel err %.2e" % worst)
     eng_full = eng_of(wa)
     rc = run(REF_BIN, wb, "-r", "1")                                # the reference continues the CUDA build's run
     assert rc.returncode == 0, rc.stdout[-3000:]
@@ -185,6 +202,31 @@ def test_mpi_cuda_binary_on_one_rank_equals_serial_reference(tmp_path):
     assert err_pot < 1e-9 and err_kin < 1e-8
 
 
+def read_dist_text(path):
+    """A distribution file in one of the ASCII formats (write_distrib_header, imd_distrib.c:805): the header lines
+    start with '#'; rows are [ix iy iz] value."""
+    rows = [ln.split() for ln in open(path) if ln.strip() and not ln.startswith("#")]
+    return np.array(rows, dtype=np.float64)
+
+
+def compare_text_dists(wa, wb, numbers, bins):
+    """dist_vxavg_flag 2 (ASCII with bin coordinates) and dist_dens_flag 3 (plain ASCII), printed with %e."""
+    worst = 0.0
+    for n in numbers:
+        va, vb = (read_dist_text(os.path.join(w, "out", "run.%d.vxavg" % n)) for w in (wa, wb))
+        assert va.shape == vb.shape == (bins, 4)
+        assert np.array_equal(va[:, :3], vb[:, :3])
+        assert np.abs(va[:, 3] - vb[:, 3]).max() <= 1e-5 * np.abs(va[:, 3]).max(), n
+        worst = max(worst, np.abs(va[:, 3] - vb[:, 3]).max() / np.abs(va[:, 3]).max())
+        da, db = (read_dist_text(os.path.join(w, "out", "run.%d.dens" % n)) for w in (wa, wb))
+        assert da.shape == db.shape == (bins, 1)
+        assert np.array_equal(da, db) and da.sum() > 0
+    return worst
+
+
+DIST_TTM = "dist_int 6\ndist_dim 14 2 1\ndist_vxavg_flag 2\ndist_dens_flag 3\n"
+
+
 def read_ttm(path):
     """<outfiles>.<n>.ttm (ttm_writeout, imd_ttm.c:1683-1969): one line per FD cell, then the virtual lattice."""
     rows = [ln.split() for ln in open(path) if ln.strip() and not ln.startswith("#")]
@@ -215,7 +257,7 @@ def test_ttm_cuda_binary_equals_reference_ttm_build(tmp_path):
     for name, ranks in (("ref", 2), ("cuda", 1)):
         w = os.path.join(work, name)
         os.makedirs(os.path.join(w, "out"))
-        ex = tp.param_text() + "box_from_header 1\nshiftx_front 20\nshiftx_rear 20\nttm_int %d\n" % ttm_int
+        ex = tp.param_text() + "box_from_header 1\nshiftx_front 20\nshiftx_rear 20\nttm_int %d\n" % ttm_int + DIST_TTM
         sy.write_param_file(os.path.join(w, "run.param"), sy.AL, (56, 6, 6), steps, "out/run", potdir="..",
                             pbc=(0, 1, 1), starttemp=0.0258, nbl_margin=0.4, eng_int=1, extra=ex, ensemble="ttm",
                             cpu_dim=(ranks, 1, 1), coordname="../start.conf")
@@ -265,6 +307,9 @@ def test_ttm_cuda_binary_equals_reference_ttm_build(tmp_path):
             print("  .ttm column %-8s worst relative difference %.2e  (%s)" % (cols[col], worst[col], where[col]))
     print(".ttm files 0..%d: worst relative difference %.2e" % (steps // ttm_int, worst.max()))
     assert worst.max() < 5e-6
+    assert "distributions (28 bins) are summed on the device" in rb.stdout
+    wd = compare_text_dists(runs["ref"], runs["cuda"], (0, 1, 2), 28)
+    print(".vxavg / .dens files (ASCII formats) vs the reference's: worst relative difference %.2e" % wd)
 
 
 def _ngpu():
@@ -326,7 +371,7 @@ def test_ttm_cuda_binary_on_two_gpus_equals_reference_ttm_build(tmp_path):
     for name in ("ref", "cuda"):
         w = os.path.join(work, name)
         os.makedirs(os.path.join(w, "out"))
-        ex = tp.param_text() + "box_from_header 1\nshiftx_front 20\nshiftx_rear 20\nttm_int %d\n" % ttm_int
+        ex = tp.param_text() + "box_from_header 1\nshiftx_front 20\nshiftx_rear 20\nttm_int %d\n" % ttm_int + DIST_TTM
         sy.write_param_file(os.path.join(w, "run.param"), sy.AL, (56, 6, 6), steps, "out/run", potdir="..",
                             pbc=(0, 1, 1), starttemp=0.0258, nbl_margin=0.4, eng_int=1, extra=ex, ensemble="ttm",
                             cpu_dim=(2, 1, 1), coordname="../start.conf")
@@ -357,3 +402,6 @@ def test_ttm_cuda_binary_on_two_gpus_equals_reference_ttm_build(tmp_path):
         worst = max(worst, rel.max())
     print(".ttm files 1..%d on 2 GPUs: worst relative difference %.2e" % (steps // ttm_int, worst))
     assert worst < 5e-6
+    assert "distributions (28 bins) are summed on the device" in rb.stdout
+    wd = compare_text_dists(runs["ref"], runs["cuda"], (0, 1, 2), 28)          # per-rank device sums + MPI_Reduce
+    print(".vxavg / .dens files on 2 GPUs vs the reference's: worst relative difference %.2e" % wd)
