@@ -164,6 +164,56 @@ def test_chkpt_written_by_cuda_build_restarts_in_reference(tmp_path):
     assert err_pot < 1e-9 and err_kin < 1e-8
 
 
+REF_FORCE_BIN = os.path.join(ROOT, "oracle", "_ref", "imd_ref_eam_nve_nbl_force")
+CUDA_FORCE_BIN = os.path.join(ROOT, "integration", "_bin", "imd_eam_nve_nbl_force_cuda")
+
+
+def read_force_file(path):
+    """<outfiles>.<n>.force (write_atoms_force, imd_io.c:1950-1973): type x y z Fx Fy Fz per atom, in cell order."""
+    rows = np.loadtxt(path, comments="#")
+    return rows[:, 1:4], rows[:, 4:7]
+
+
+@pytest.mark.skipif(not (os.path.exists(REF_FORCE_BIN) and os.path.exists(CUDA_FORCE_BIN)),
+                    reason="the -DFORCE builds are missing (needs the reference sources)")
+@pytest.mark.gpu
+def test_configs0_eng_and_force_files_equal_reference(tmp_path):
+    """BASELINE configs[0] through IMD's own files: Cu fcc, 32^3 cells = 131 072 atoms, 100 NVE steps, the
+    reference's -DFORCE build against the same build with the CUDA hot path.  .eng row by row, and the .force files
+    of steps 0, 50 and 100: write_atoms_force runs right after calc_forces (imd_main_3d.c:429-434), so the files
+    show KRAFT as imdcu_sync_to_host stages it back.  The files carry no atom numbers and the two programs keep
+    their cells in different orders: rows are matched by position (periodic nearest neighbour)."""
+    from scipy.spatial import cKDTree
+    steps = 100
+    wa, wb = str(tmp_path / "ref"), str(tmp_path / "cuda")
+    for w in (wa, wb):
+        os.makedirs(w)
+        write_inputs(w, steps, box=(32, 32, 32), extra="force_int 50\n")
+    ra, rb = run(REF_FORCE_BIN, wa), run(CUDA_FORCE_BIN, wb)
+    assert ra.returncode == 0, ra.stdout[-3000:]
+    assert rb.returncode == 0, rb.stdout[-3000:]
+    assert "131072 atoms" in ra.stdout and "hot path on CUDA device" in rb.stdout
+    ea, eb = eng_of(wa), eng_of(wb)
+    assert ea.shape == eb.shape and ea.shape[0] >= steps
+    err_pot = np.abs(ea[:, 1] - eb[:, 1]).max() / np.abs(ea[:, 1]).max()
+    err_kin = np.abs(ea[:, 2] - eb[:, 2]).max() / np.abs(ea[:, 2]).max()
+    box = 32 * synth.CU.a
+    worst_x = worst_f = fmax = 0.0                                   # step 0 is the perfect lattice: forces ~1e-15
+    for n in (0, 1, 2):
+        xa, fa = read_force_file(os.path.join(wa, "out", "run.%05d.force" % n))
+        xb, fb = read_force_file(os.path.join(wb, "out", "run.%05d.force" % n))
+        assert xa.shape == xb.shape == (131072, 3)
+        dist, perm = cKDTree(np.mod(xb, box), boxsize=box).query(np.mod(xa, box))
+        assert np.array_equal(np.sort(perm), np.arange(131072))          # a one-to-one match
+        worst_x = max(worst_x, dist.max())
+        worst_f, fmax = max(worst_f, np.abs(fa - fb[perm]).max()), max(fmax, np.abs(fa).max())
+    worst_f /= fmax
+    print("configs[0], 131 072 Cu atoms, 100 steps: .eng Epot rel %.2e, T rel %.2e; .force files: positions %.2e A, "
+          "forces %.2e of the largest component (%.2f eV/A)" % (err_pot, err_kin, worst_x, worst_f, fmax))
+    assert err_pot < 3e-10 and err_kin < 1e-12                       # observed 2.3e-11, 2.7e-14
+    assert worst_x < 1e-12 and worst_f < 2e-12                       # observed 5.7e-14 A, 1.4e-13
+
+
 # ----------------------------------------------------------------------------- MPI hosts (one rank per GPU)
 REF_MPI_TTM = os.path.join(ROOT, "oracle", "_ref", "imd_ref_mpi_eam_ttm")
 CUDA_MPI_NVE = os.path.join(ROOT, "integration", "_bin", "imd_mpi_eam_nve_nbl_cuda")
