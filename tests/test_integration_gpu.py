@@ -386,8 +386,8 @@ def test_mpi_cuda_binary_on_two_gpus_equals_serial_reference(tmp_path):
         w = os.path.join(work, name)
         os.makedirs(os.path.join(w, "out"))
         synth.write_param_file(os.path.join(w, "run.param"), synth.CU, (12, 6, 6), steps, "out/run", potdir="..",
-                               pbc=(1, 1, 1), starttemp=0.1, nbl_margin=0.5, eng_int=1, extra="box_from_header 1\n",
-                               cpu_dim=(ranks, 1, 1), coordname="../start.conf")
+                               pbc=(1, 1, 1), starttemp=0.1, nbl_margin=0.5, eng_int=1,
+                               extra="box_from_header 1\ncheckpt_int 15\n", cpu_dim=(ranks, 1, 1), coordname="../start.conf")
         runs[name] = w
     ra, rb = run(REF_BIN, runs["ref"]), run_mpi(CUDA_MPI_NVE, runs["cuda"], 2)
     assert ra.returncode == 0, ra.stdout[-3000:]
@@ -399,6 +399,19 @@ def test_mpi_cuda_binary_on_two_gpus_equals_serial_reference(tmp_path):
     err_kin = np.abs(ea[:, 2] - eb[:, 2]).max() / np.abs(ea[:, 2]).max()
     print("imd_mpi_eam_nve_nbl_cuda on 2 GPUs vs serial reference: Epot rel %.2e, T rel %.2e" % (err_pot, err_kin))
     assert err_pot < 1e-9 and err_kin < 1e-8
+    # .chkpt of steps 15 and 30: every rank refills its cell_array (imdcu_sync_to_host) and the reference's write_config
+    # collects the ranks' atoms (imd_io_3d.c:721-979); compared by atom number with the serial reference's files
+    worst = 0.0
+    for n in (1, 2):
+        ca, cb = read_chkpt(chkpt_path(runs["ref"], n)), read_chkpt(chkpt_path(runs["cuda"], n))
+        assert ca.shape == cb.shape and ca.shape[0] == pos.shape[0]
+        assert np.array_equal(ca[:, :3], cb[:, :3])
+        d = np.abs(ca[:, 3:6] - cb[:, 3:6])
+        d = np.minimum(d, np.abs(d - np.diag(box)[None, :]))             # a position on the periodic boundary
+        scale = np.abs(ca[:, 6:]).max(axis=0) + 1e-300
+        worst = max(worst, d.max() / box.max(), (np.abs(ca[:, 6:] - cb[:, 6:]).max(axis=0) / scale).max())
+    print(".chkpt files of two ranks / two GPUs vs the serial reference's: worst rel err %.2e" % worst)
+    assert worst < 1e-12                                                 # observed 1.2e-14
 
 
 @needs_mpi_bins
