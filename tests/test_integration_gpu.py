@@ -362,6 +362,66 @@ def test_ttm_cuda_binary_equals_reference_ttm_build(tmp_path):
     print(".vxavg / .dens files (ASCII formats) vs the reference's: worst relative difference %.2e" % wd)
 
 
+REF_MPI_TMM = os.path.join(ROOT, "oracle", "_ref", "imd_ref_mpi_eam_ttm_tmm")
+
+
+@pytest.mark.skipif(not (os.path.exists(REF_MPI_TMM) and os.path.exists(CUDA_MPI_TTM)),
+                    reason="integration/_bin or oracle/_ref not built (needs the reference sources)")
+@pytest.mark.gpu
+def test_ttm_cuda_binary_with_do_tmm_equals_reference_tmm_build(tmp_path):
+    """The laser source by the transfer-matrix solver, through the files: the reference build that keeps its OWN
+    tmm_init / do_tmm (imd_tmm.c:98-696; 2 ranks over shmpi) against imd_mpi_eam_ttm_tmm_nbl_cuda, whose tmm_init
+    reads ../alu_eps_bb.dat and ../K12.dat itself and hands them to imdcu_ttm_set_tmm (do_tmm then runs inside the
+    device lattice kernel).  Same film as the library-level golden ttm_tmm_al_96x5x5_p2; .eng with its E_el column
+    and the .ttm files (source column included) are compared."""
+    from imd_b200 import synth as sy
+    steps, ttm_int = 14, 7
+    tp = sy.TtmParams(ttmdimx=26, fd_n_timesteps=20, I0=2.0e16, tmm_threshold=5.0, use_tmm=1)
+    work = str(tmp_path)
+    sy.make_eam_tables(sy.AL, work)
+    sy.write_eos_files(sy.make_eos_tables(), work)
+    sy.write_tmm_files(sy.make_tmm_tables(), work)
+    pos, box = sy.fcc_lattice((96, 5, 5), sy.AL.a)
+    sy.write_config_file(os.path.join(work, "start.conf"), pos, sy.maxwell_momenta(pos.shape[0], sy.AL.mass, 0.0258),
+                         sy.AL.mass, box)
+    runs = {}
+    for name, ranks in (("ref", 2), ("cuda", 1)):
+        w = os.path.join(work, name)
+        os.makedirs(os.path.join(w, "out"))
+        ex = tp.param_text() + "box_from_header 1\nshiftx_front 20\nshiftx_rear 20\nttm_int %d\n" % ttm_int
+        sy.write_param_file(os.path.join(w, "run.param"), sy.AL, (96, 5, 5), steps, "out/run", potdir="..",
+                            pbc=(0, 1, 1), starttemp=0.0258, nbl_margin=0.4, eng_int=1, extra=ex, ensemble="ttm",
+                            cpu_dim=(ranks, 1, 1), coordname="../start.conf")
+        runs[name] = w
+    ra = run_mpi(REF_MPI_TMM, runs["ref"], 2)
+    rb = run_mpi(CUDA_MPI_TTM, runs["cuda"], 1, {"IMDCU_TTM_REF_RANKS": "2"})
+    assert ra.returncode == 0, ra.stdout[-3000:]
+    assert rb.returncode == 0, rb.stdout[-3000:]
+    assert "transfer-matrix method (do_tmm on the device)" in rb.stdout
+    ea, eb = eng_of(runs["ref"]), eng_of(runs["cuda"])
+    assert ea.shape == eb.shape and ea.shape[1] >= 6
+    err_pot = np.abs(ea[:, 1] - eb[:, 1]).max() / np.abs(ea[:, 1]).max()
+    err_kin = np.abs(ea[:, 2] - eb[:, 2]).max() / np.abs(ea[:, 2]).max()
+    err_el = (np.abs(ea[:, 5] - eb[:, 5]) / np.abs(ea[:, 5])).max()
+    assert ea[-1, 5] > 1.5 * ea[0, 5]                               # the pulse has heated the electrons
+    worst, src_max = 0.0, 0.0
+    for n in range(1, steps // ttm_int + 1):                        # file 0: rank 0's uninitialised virtual lattice
+        ta = read_ttm(os.path.join(runs["ref"], "out", "run.%d.ttm" % n))
+        tb = read_ttm(os.path.join(runs["cuda"], "out", "run.%d.ttm" % n))
+        assert ta.shape == tb.shape, (n, ta.shape, tb.shape)
+        assert np.array_equal(ta[:, [0, 1, 2, 3, 16]], tb[:, [0, 1, 2, 3, 16]]), n
+        num = np.abs(ta - tb)
+        rel = np.where(np.abs(ta) > 1e-12, num / np.maximum(np.abs(ta), 1e-30), num)
+        for col in (8, 10, 11, 12):                                 # source, vx vy vz: against the column's largest entry
+            rel[:, col] = num[:, col] / max(np.abs(ta[:, col]).max(), 1e-30)
+        worst, src_max = max(worst, rel.max()), max(src_max, np.abs(ta[:, 8]).max())
+    print("do_tmm through the files: Epot rel %.2e, T rel %.2e, E_el rel %.2e; .ttm files 1..%d worst relative "
+          "difference %.2e (largest source term %.3e)" % (err_pot, err_kin, err_el, steps // ttm_int, worst, src_max))
+    assert src_max > 0
+    # observed 2e-14, 2e-12, 0 and 3.6e-7 (the .ttm files carry seven digits: one unit of the last is up to 1e-6)
+    assert err_pot < 1e-11 and err_kin < 1e-10 and err_el < 2e-6 and worst < 2e-6
+
+
 def _ngpu():
     import torch
     return torch.cuda.device_count()
