@@ -57,6 +57,11 @@ static void cu_fail(const char *where, int rc)
 }
 #define CK(call) do { int rc_ = (call); if (rc_ != IMDCU_OK) cu_fail(#call, rc_); } while (0)
 
+#ifdef NRB
+static void cu_nrb_restore(cell *p, int i);          /* the NRB members of an atom refilled into cell_array */
+static void cu_nrb_resolve(void);
+#endif
+
 static void *cu_alloc(size_t bytes)
 {
   void *p = malloc(bytes > 0 ? bytes : 1);
@@ -278,7 +283,13 @@ void imdcu_sync_to_host(void)
 #ifdef TTM
     NUMNEIGHS(to, i) = nn[m];
 #endif
+#ifdef NRB
+    cu_nrb_restore(to, i);
+#endif
   }
+#ifdef NRB
+  cu_nrb_resolve();
+#endif
   free(id); free(type); free(vtype); free(nn); free(mass); free(pos); free(mom); free(frc); free(epot); free(rho); free(dF);
   cu_host_stale = 0;
   cu_syncs++;
@@ -286,14 +297,194 @@ void imdcu_sync_to_host(void)
 
 /* ------------------------------------------------------------------ the hot-path entry points */
 
+#ifdef NRB
+/* ------------------------------------------------------------------ non-reflecting boundary (make-target substring nrb)
+ * The one-time setup stays the reference's own: init_nrb (imd_nrb.c:125-768, compiled in place) marks the boundary
+ * atoms, finds their lattice-site neighbours by atom number and sets the reference positions -- the reference calls it
+ * from make_nblist (imd_forces_nbl.c:281-282), i.e. in the first calc_forces with the buffer cells filled.  What it
+ * leaves in cell_array goes to the device once (imdcu_set_nrb); nrb_forces (imd_nrb.c:792-1129) and the integrator
+ * hooks (imd_integrate.c:233-259,712-751) then run there.  The table is kept on the host too, sorted by atom number,
+ * so that imdcu_sync_to_host can give the atoms their NRB members back for nrb_writerestart (imd_main_3d.c:707-709). */
+typedef struct { int id, bnd, neigh, nrbi[12]; double ref[3]; } cu_nrb_ent;
+static cu_nrb_ent *cu_nrb_tab = NULL;
+static long cu_nrb_n = 0;
+static double cu_nrb_k = 0.0;
+/* REF_POS of EVERY atom is part of the checkpoint (-DREFPOS, "refpos_x refpos_y refpos_z"): the atoms this rank owned
+ * when init_nrb set them, sorted by number; an atom that has come from another slab since is asked for over MPI */
+typedef struct { int id; double ref[3]; } cu_ref_ent;
+static cu_ref_ent *cu_ref_tab = NULL;
+static long cu_ref_n = 0;
+typedef struct { cell *p; int i; } cu_ref_miss;
+static cu_ref_miss *cu_miss = NULL;
+static long cu_miss_n = 0, cu_miss_cap = 0;
+
+static int cu_ref_cmp(const void *a, const void *b)
+{
+  const int x = ((const cu_ref_ent *) a)->id, y = ((const cu_ref_ent *) b)->id;
+  return (x > y) - (x < y);
+}
+
+static int cu_nrb_cmp(const void *a, const void *b)
+{
+  const int x = ((const cu_nrb_ent *) a)->id, y = ((const cu_nrb_ent *) b)->id;
+  return (x > y) - (x < y);
+}
+
+static void cu_nrb_setup(void)
+{
+  cu_nrb_ent *loc;
+  long nloc = 0, cap = 1024, m;
+  int k, i, j;
+  cu_nrb_k = nrbk;                                   /* the parameter nrb_k; init_nrb replaces it by sqrt(nrb_k / m), :158 */
+#ifdef MPI
+  setup_buffers();                                   /* message buffers first (imd_forces_nbl.c:304) */
+#endif
+  send_cells(copy_cell, pack_cell, unpack_cell);     /* buffer cells, as calc_forces fills them (imd_forces_nbl.c:311) */
+  init_nrb();
+  loc = cu_alloc(cap * sizeof *loc);
+  for (k = 0, cu_ref_n = 0; k < ncells; k++) cu_ref_n += CELLPTR(k)->n;
+  cu_ref_tab = cu_alloc((size_t) (cu_ref_n > 0 ? cu_ref_n : 1) * sizeof *cu_ref_tab);
+  for (k = 0, m = 0; k < ncells; k++) {
+    cell *p = CELLPTR(k);
+    for (i = 0; i < p->n; i++, m++) {
+      cu_ref_tab[m].id = NUMMER(p, i);
+      cu_ref_tab[m].ref[0] = REF_POS(p, i, X); cu_ref_tab[m].ref[1] = REF_POS(p, i, Y); cu_ref_tab[m].ref[2] = REF_POS(p, i, Z);
+    }
+  }
+  qsort(cu_ref_tab, cu_ref_n, sizeof *cu_ref_tab, cu_ref_cmp);
+  for (k = 0; k < ncells; k++) {
+    cell *p = CELLPTR(k);
+    for (i = 0; i < p->n; i++) {
+      if (NRBBND(p, i) == 0 && NRBNEIGH(p, i) == 0) continue;
+      if (nloc == cap) { cap *= 2; loc = realloc(loc, cap * sizeof *loc); if (loc == NULL) error("imd_cuda: out of host memory"); }
+      memset(&loc[nloc], 0, sizeof *loc);
+      loc[nloc].id = NUMMER(p, i); loc[nloc].bnd = NRBBND(p, i); loc[nloc].neigh = NRBNEIGH(p, i);
+      for (j = 0; j < 12; j++) loc[nloc].nrbi[j] = NRBI(p, i, j);
+      loc[nloc].ref[0] = REF_POS(p, i, X); loc[nloc].ref[1] = REF_POS(p, i, Y); loc[nloc].ref[2] = REF_POS(p, i, Z);
+      nloc++;
+    }
+  }
+#ifdef MPI
+  {                                                  /* every rank hands the full table to the library */
+    int mine = (int) nloc, most = 0, r, *counts = cu_alloc(num_cpus * sizeof *counts);
+    cu_nrb_ent *pad, *all;
+    MPI_Allgather(&mine, 1, MPI_INT, counts, 1, MPI_INT, cpugrid);
+    for (r = 0; r < num_cpus; r++) if (counts[r] > most) most = counts[r];
+    pad = calloc((size_t) (most > 0 ? most : 1), sizeof *pad);
+    all = cu_alloc((size_t) (most > 0 ? most : 1) * num_cpus * sizeof *all);
+    memcpy(pad, loc, nloc * sizeof *loc);
+    MPI_Allgather(pad, most * (int) sizeof *pad, MPI_CHAR, all, most * (int) sizeof *pad, MPI_CHAR, cpugrid);
+    cu_nrb_n = 0;
+    for (r = 0; r < num_cpus; r++) cu_nrb_n += counts[r];
+    cu_nrb_tab = cu_alloc((size_t) (cu_nrb_n > 0 ? cu_nrb_n : 1) * sizeof *cu_nrb_tab);
+    for (r = 0, m = 0; r < num_cpus; r++) { memcpy(cu_nrb_tab + m, all + (size_t) r * most, counts[r] * sizeof *all); m += counts[r]; }
+    free(pad); free(all); free(counts); free(loc);
+  }
+#else
+  cu_nrb_tab = loc; cu_nrb_n = nloc;
+#endif
+  qsort(cu_nrb_tab, cu_nrb_n, sizeof *cu_nrb_tab, cu_nrb_cmp);
+}
+
+static void cu_nrb_to_device(void)
+{
+  int32_t *id = cu_alloc(cu_nrb_n * sizeof *id), *bnd = cu_alloc(cu_nrb_n * sizeof *bnd), *nrbi = cu_alloc(12 * cu_nrb_n * sizeof *nrbi);
+  double *ref = cu_alloc(3 * cu_nrb_n * sizeof *ref);
+  long m;
+  int j;
+  for (m = 0; m < cu_nrb_n; m++) {
+    id[m] = cu_nrb_tab[m].id; bnd[m] = cu_nrb_tab[m].bnd;
+    for (j = 0; j < 12; j++) nrbi[12 * m + j] = cu_nrb_tab[m].nrbi[j];
+    for (j = 0; j < 3; j++) ref[3 * m + j] = cu_nrb_tab[m].ref[j];
+  }
+  /* startup_images = 1: what the reference's send_forces does to the boundary momenta in steps 0 and 1 (imdcu.h) */
+  CK(imdcu_set_nrb(cu, cu_nrb_k, cu_nrb_n, id, bnd, nrbi, ref, 1));
+  if (myid == 0) printf("imd_cuda: non-reflecting boundary on the device, %ld boundary and neighbour atoms, nrb_k %g\n", cu_nrb_n, cu_nrb_k);
+  free(id); free(bnd); free(nrbi); free(ref);
+}
+
+/* the NRB members of one atom of cell_array (imdcu_sync_to_host) */
+static void cu_nrb_restore(cell *p, int i)
+{
+  cu_nrb_ent key, *e;
+  int j;
+  key.id = NUMMER(p, i);
+  e = cu_nrb_n > 0 ? bsearch(&key, cu_nrb_tab, cu_nrb_n, sizeof *cu_nrb_tab, cu_nrb_cmp) : NULL;
+  NRBBND(p, i) = e ? e->bnd : 0;
+  NRBNEIGH(p, i) = e ? e->neigh : 0;
+  for (j = 0; j < 12; j++) NRBI(p, i, j) = e ? e->nrbi[j] : 0;
+  if (e) { REF_POS(p, i, X) = e->ref[0]; REF_POS(p, i, Y) = e->ref[1]; REF_POS(p, i, Z) = e->ref[2]; }
+  else {
+    cu_ref_ent rk, *r;
+    rk.id = key.id;
+    r = cu_ref_n > 0 ? bsearch(&rk, cu_ref_tab, cu_ref_n, sizeof *cu_ref_tab, cu_ref_cmp) : NULL;
+    if (r) { REF_POS(p, i, X) = r->ref[0]; REF_POS(p, i, Y) = r->ref[1]; REF_POS(p, i, Z) = r->ref[2]; }
+    else {                                           /* arrived from another rank: cu_nrb_resolve asks its first owner */
+      if (cu_miss_n == cu_miss_cap) {
+        cu_miss_cap = cu_miss_cap ? 2 * cu_miss_cap : 256;
+        cu_miss = realloc(cu_miss, cu_miss_cap * sizeof *cu_miss);
+        if (cu_miss == NULL) error("imd_cuda: out of host memory");
+      }
+      cu_miss[cu_miss_n].p = p; cu_miss[cu_miss_n].i = i; cu_miss_n++;
+    }
+  }
+}
+
+/* collective, at the end of imdcu_sync_to_host: reference positions of the atoms that changed their rank */
+static void cu_nrb_resolve(void)
+{
+#ifdef MPI
+  int mine = (int) cu_miss_n, most = 0, r, q, *counts, *ask, *all;
+  double *ans, *sum;
+  if (num_cpus == 1) { if (cu_miss_n > 0) error("imd_cuda: an atom without reference position"); return; }
+  counts = cu_alloc(num_cpus * sizeof *counts);
+  MPI_Allgather(&mine, 1, MPI_INT, counts, 1, MPI_INT, cpugrid);
+  for (r = 0; r < num_cpus; r++) if (counts[r] > most) most = counts[r];
+  if (most > 0) {
+    static int told = 0;
+    if (!told && myid == 0) { printf("imd_cuda: reference positions of atoms that changed their rank are fetched from their first owner\n"); told = 1; }
+    ask = calloc(most, sizeof *ask); all = cu_alloc((size_t) most * num_cpus * sizeof *all);
+    for (q = 0; q < mine; q++) ask[q] = NUMMER(cu_miss[q].p, cu_miss[q].i);
+    MPI_Allgather(ask, most, MPI_INT, all, most, MPI_INT, cpugrid);
+    ans = calloc((size_t) 4 * most * num_cpus, sizeof *ans); sum = cu_alloc((size_t) 4 * most * num_cpus * sizeof *sum);
+    for (r = 0; r < num_cpus; r++)
+      for (q = 0; q < counts[r]; q++) {
+        cu_ref_ent rk, *e;
+        rk.id = all[r * most + q];
+        e = cu_ref_n > 0 ? bsearch(&rk, cu_ref_tab, cu_ref_n, sizeof *cu_ref_tab, cu_ref_cmp) : NULL;
+        if (e) { double *a = ans + 4 * ((size_t) r * most + q); a[0] = e->ref[0]; a[1] = e->ref[1]; a[2] = e->ref[2]; a[3] = 1.0; }
+      }
+    MPI_Allreduce(ans, sum, 4 * most * num_cpus, MPI_DOUBLE, MPI_SUM, cpugrid);
+    for (q = 0; q < mine; q++) {
+      const double *a = sum + 4 * ((size_t) myid * most + q);
+      if (a[3] != 1.0) error("imd_cuda: an atom without reference position");
+      REF_POS(cu_miss[q].p, cu_miss[q].i, X) = a[0]; REF_POS(cu_miss[q].p, cu_miss[q].i, Y) = a[1]; REF_POS(cu_miss[q].p, cu_miss[q].i, Z) = a[2];
+    }
+    free(ask); free(all); free(ans); free(sum);
+  }
+  free(counts);
+#else
+  if (cu_miss_n > 0) error("imd_cuda: an atom without reference position");
+#endif
+  cu_miss_n = 0;
+}
+#endif /* NRB */
+
 void calc_forces(int steps)                          /* replaces imd_forces_nbl.c:295-1054 */
 {
   double out8[8];
   double t0;
   if (cu_timing < 0) { cu_timing = getenv("IMD_CUDA_TIMING") != NULL; if (cu_timing) atexit(cu_report); }
   t0 = cu_timing ? cu_now() : 0.0;
+#ifdef NRB
+  if (!cu_resident && !have_valid_nrb) cu_nrb_setup();             /* host only */
+#endif
   cu_attach();
+#ifdef NRB
+  if (!cu_resident) { cu_upload(); cu_nrb_to_device(); }
+#else
   if (!cu_resident) cu_upload();
+#endif
   if (!have_valid_nbl) CK(imdcu_invalidate_nblist(cu));   /* the host asked for a new list (imd_main_3d.c:273) */
 #ifdef TTM
   /* calc_ttm() follows at imd_main_3d.c:534 with nothing in between that touches the atoms: both in one call, so that

@@ -422,6 +422,85 @@ def test_ttm_cuda_binary_with_do_tmm_equals_reference_tmm_build(tmp_path):
     assert err_pot < 1e-11 and err_kin < 1e-10 and err_el < 2e-6 and worst < 2e-6
 
 
+REF_MPI_NRB = os.path.join(ROOT, "oracle", "_ref", "imd_ref_mpi_eam_ttm_nrb")
+CUDA_MPI_NRB = os.path.join(ROOT, "integration", "_bin", "imd_mpi_eam_ttm_tmm_nrb_nbl_cuda")
+needs_nrb_bins = pytest.mark.skipif(not (os.path.exists(REF_MPI_NRB) and os.path.exists(CUDA_MPI_NRB)),
+                                    reason="the -DNRB builds are missing (needs the reference sources)")
+
+
+def _nrb_film_runs(work, ranks_cuda):
+    """BASELINE configs[3] in small: Al film + TTM + non-reflecting rear boundary (nrb_k 1.2), warm lattice and a
+    pulse so that the boundary plane moves; the film of the library-level golden ttm_nrb_al_40x5x5_p2."""
+    from imd_b200 import synth as sy
+    steps, ttm_int = 24, 12
+    tp = sy.TtmParams(ttmdimx=10, fd_n_timesteps=20, I0=2.0e16)
+    sy.make_eam_tables(sy.AL, work)
+    sy.write_eos_files(sy.make_eos_tables(), work)
+    pos, box = sy.fcc_lattice((40, 5, 5), sy.AL.a)
+    sy.write_config_file(os.path.join(work, "start.conf"), pos, sy.maxwell_momenta(pos.shape[0], sy.AL.mass, 0.05),
+                         sy.AL.mass, box)
+    runs = {}
+    for name, ranks in (("ref", 2), ("cuda", ranks_cuda)):
+        w = os.path.join(work, name)
+        os.makedirs(os.path.join(w, "out"))
+        ex = (tp.param_text() + "box_from_header 1\nshiftx_front 20\nshiftx_rear 20\nttm_int %d\ncheckpt_int %d\n"
+              "nrb_alat 4.05\nnrb_eps 0.3\nnrb_k 1.2\n" % (ttm_int, ttm_int))
+        sy.write_param_file(os.path.join(w, "run.param"), sy.AL, (40, 5, 5), steps, "out/run", potdir="..",
+                            pbc=(0, 1, 1), starttemp=0.05, nbl_margin=0.4, eng_int=1, extra=ex, ensemble="ttm",
+                            cpu_dim=(ranks, 1, 1), coordname="../start.conf")
+        runs[name] = w
+    src = {"IMD_SRC_MU": "%.17g" % tp.src_mu, "IMD_SRC_ABS": "%.17g" % tp.src_abs}
+    ra = run_mpi(REF_MPI_NRB, runs["ref"], 2, src)
+    rb = run_mpi(CUDA_MPI_NRB, runs["cuda"], ranks_cuda, dict(src, IMDCU_TTM_REF_RANKS="2") if ranks_cuda == 1 else src)
+    assert ra.returncode == 0, ra.stdout[-3000:]
+    assert rb.returncode == 0, rb.stdout[-3000:]
+    assert "non-reflecting boundary on the device" in rb.stdout
+    return runs, steps, ttm_int, pos.shape[0]
+
+
+def _compare_nrb_runs(runs, steps, ttm_int, natoms, label):
+    ea, eb = eng_of(runs["ref"]), eng_of(runs["cuda"])
+    assert ea.shape == eb.shape and ea.shape[1] >= 6
+    err_pot = np.abs(ea[:, 1] - eb[:, 1]).max() / np.abs(ea[:, 1]).max()
+    err_kin = np.abs(ea[:, 2] - eb[:, 2]).max() / np.abs(ea[:, 2]).max()
+    err_el = (np.abs(ea[:, 5] - eb[:, 5]) / np.abs(ea[:, 5])).max()
+    worst_ttm = worst_chk = 0.0
+    for n in range(1, steps // ttm_int + 1):
+        ta = read_ttm(os.path.join(runs["ref"], "out", "run.%d.ttm" % n))
+        tb = read_ttm(os.path.join(runs["cuda"], "out", "run.%d.ttm" % n))
+        assert ta.shape == tb.shape, (n, ta.shape, tb.shape)
+        assert np.array_equal(ta[:, [0, 1, 2, 3, 16]], tb[:, [0, 1, 2, 3, 16]]), n
+        num = np.abs(ta - tb)
+        rel = np.where(np.abs(ta) > 1e-12, num / np.maximum(np.abs(ta), 1e-30), num)
+        for col in (10, 11, 12):
+            rel[:, col] = num[:, col] / max(np.abs(ta[:, col]).max(), 1e-30)
+        worst_ttm = max(worst_ttm, rel.max())
+        # .chkpt through imdcu_sync_to_host and the .nrb restart file beside it (nrb_writerestart, imd_nrb.c:2143-2214:
+        # number, NRBBND, NRBNEIGH, position, NRBI[12], REF_POS of every boundary and neighbour atom)
+        ca, cb = read_chkpt(chkpt_path(runs["ref"], n)), read_chkpt(chkpt_path(runs["cuda"], n))
+        assert ca.shape == cb.shape and ca.shape[0] == natoms
+        assert np.array_equal(ca[:, :3], cb[:, :3])
+        scale = np.abs(ca[:, 3:]).max(axis=0) + 1e-300
+        worst_chk = max(worst_chk, (np.abs(ca[:, 3:] - cb[:, 3:]).max(axis=0) / scale).max())
+        na, nb = (np.loadtxt(os.path.join(runs[k], "out", "run.%05d.nrb" % n)) for k in ("ref", "cuda"))
+        na, nb = na[np.argsort(na[:, 0])], nb[np.argsort(nb[:, 0])]
+        assert na.shape == nb.shape and na.shape[0] > 0
+        assert np.array_equal(na[:, [0, 1, 2] + list(range(6, 18))], nb[:, [0, 1, 2] + list(range(6, 18))]), n
+        assert np.abs(na[:, 3:6] - nb[:, 3:6]).max() < 2e-6 and np.array_equal(na[:, 18:], nb[:, 18:]), n   # %lf: 6 decimals
+    print("%s: Epot rel %.2e, T rel %.2e, E_el rel %.2e; .ttm worst %.2e; .chkpt worst %.2e; .nrb files equal"
+          % (label, err_pot, err_kin, err_el, worst_ttm, worst_chk))
+    assert err_pot < 1e-8 and err_kin < 1e-7 and err_el < 2e-6 and worst_ttm < 5e-6 and worst_chk < 1e-8
+
+
+@needs_nrb_bins
+@pytest.mark.gpu
+def test_nrb_cuda_binary_equals_reference_nrb_build(tmp_path):
+    """The -DNRB -DREFPOS build with the CUDA hot path (init_nrb on the host once, nrb_forces and the integrator hooks
+    on the device) against the reference's own NRB build on two ranks: .eng, .ttm, .chkpt and .nrb files."""
+    runs, steps, ttm_int, natoms = _nrb_film_runs(str(tmp_path), 1)
+    _compare_nrb_runs(runs, steps, ttm_int, natoms, "imd_mpi_eam_ttm_tmm_nrb_nbl_cuda vs the reference NRB build")
+
+
 def _ngpu():
     import torch
     return torch.cuda.device_count()
@@ -528,3 +607,53 @@ def test_ttm_cuda_binary_on_two_gpus_equals_reference_ttm_build(tmp_path):
     assert "distributions (28 bins) are summed on the device" in rb.stdout
     wd = compare_text_dists(runs["ref"], runs["cuda"], (0, 1, 2), 28)          # per-rank device sums + MPI_Reduce
     print(".vxavg / .dens files on 2 GPUs vs the reference's: worst relative difference %.2e" % wd)
+
+
+@needs_nrb_bins
+@pytest.mark.gpu
+def test_nrb_cuda_binary_on_two_gpus_equals_reference_nrb_build(tmp_path):
+    """The same film on two ranks / two GPUs (the NRB table is gathered over the ranks; the boundary lives on the
+    last rank): BASELINE configs[3] in small, through IMD's own files."""
+    if _ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    runs, steps, ttm_int, natoms = _nrb_film_runs(str(tmp_path), 2)
+    _compare_nrb_runs(runs, steps, ttm_int, natoms, "imd_mpi_eam_ttm_tmm_nrb_nbl_cuda on 2 GPUs vs the reference NRB build")
+
+
+@needs_nrb_bins
+@pytest.mark.gpu
+def test_nrb_reference_positions_follow_atoms_across_ranks(tmp_path):
+    """-DREFPOS puts REF_POS of every atom into the checkpoint.  The CUDA build keeps them on the host of the rank
+    that owned the atom when init_nrb set them; an atom that has moved to the other slab since is asked for over MPI
+    (imd_cuda.c: cu_nrb_resolve).  Film shifted so that an atomic plane lies ON the cut between the two slabs: half
+    of its atoms change rank at the first list rebuilds.  Expected refpos: the start configuration, shifted."""
+    if _ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    from imd_b200 import synth as sy
+    steps = 40
+    front = 101.0 - 1.0125 - 39 * 2.025                   # plane 39 at x = 101.0 = 15 of 30 cell layers of the 202 A box
+    tp = sy.TtmParams(ttmdimx=10, fd_n_timesteps=20, I0=2.0e16)
+    work = str(tmp_path)
+    sy.make_eam_tables(sy.AL, work)
+    sy.write_eos_files(sy.make_eos_tables(), work)
+    pos, box = sy.fcc_lattice((40, 5, 5), sy.AL.a)
+    sy.write_config_file(os.path.join(work, "start.conf"), pos, sy.maxwell_momenta(pos.shape[0], sy.AL.mass, 0.05),
+                         sy.AL.mass, box)
+    w = os.path.join(work, "cuda")
+    os.makedirs(os.path.join(w, "out"))
+    ex = (tp.param_text() + "box_from_header 1\nshiftx_front %.17g\nshiftx_rear %.17g\nttm_int 0\ncheckpt_int %d\n"
+          "nrb_alat 4.05\nnrb_eps 0.3\nnrb_k 1.2\n" % (front, 40.0 - front, steps))
+    sy.write_param_file(os.path.join(w, "run.param"), sy.AL, (40, 5, 5), steps, "out/run", potdir="..",
+                        pbc=(0, 1, 1), starttemp=0.05, nbl_margin=0.4, eng_int=1, extra=ex, ensemble="ttm",
+                        cpu_dim=(2, 1, 1), coordname="../start.conf")
+    r = run_mpi(CUDA_MPI_NRB, w, 2, {"IMD_SRC_MU": "%.17g" % tp.src_mu, "IMD_SRC_ABS": "%.17g" % tp.src_abs})
+    assert r.returncode == 0, r.stdout[-3000:]
+    assert "changed their rank are fetched from their first owner" in r.stdout, r.stdout[-3000:]
+    c = read_chkpt(chkpt_path(w, 1))                       # number type mass x y z vx vy vz Epot refpos_x refpos_y refpos_z eam_rho
+    assert c.shape[0] == pos.shape[0] and np.array_equal(c[:, 0], np.arange(1, pos.shape[0] + 1))
+    want = pos + np.array([front, 0.0, 0.0])
+    err = np.abs(c[:, 10:13] - want).max()
+    moved = np.abs(c[:, 3:6] - want).max()
+    print("refpos of %d atoms after %d steps on two ranks: max |refpos - start| %.2e A (atoms moved up to %.2f A)"
+          % (c.shape[0], steps, err, moved))
+    assert err < 1e-12 and moved > 0.1
