@@ -236,7 +236,7 @@ def film_geometry(cells, world):
     return ncx, lx, gx
 
 
-def run_reference_ttm(cells, world, steps, nproc, nrb, substeps, binary=None, env_extra=None):
+def run_reference_ttm(cells, world, steps, nproc, nrb, substeps, binary=None, env_extra=None, timeout=1500):
     """The reference's own EAM + TTM(1-D) MPI build (imd_ttm.c:75-156 per step, move_atoms_ttm) over oracle/shmpi on
     the bench film: ensemble ttm, pbc 0 1 1, shiftx_front/rear vacuum, the same FD lattice, sub-step count and pulse
     as the GPU arm (analytic Beer-Lambert source on both sides, ref_hooks_ttm.c).  TTM1D talks to ranks myid +- 1
@@ -269,7 +269,7 @@ def run_reference_ttm(cells, world, steps, nproc, nrb, substeps, binary=None, en
         env.update(env_extra or {})
         t0 = time.perf_counter()
         res = subprocess.run([binary, "-p", "run.param"], cwd=run, env=env, stdout=subprocess.PIPE,
-                             stderr=subprocess.STDOUT, text=True, timeout=1500)
+                             stderr=subprocess.STDOUT, text=True, timeout=timeout)
         wall = time.perf_counter() - t0
         m = re.search(r"([0-9.eE+-]+) seconds excluding setup time", res.stdout)
         n = re.search(r"Did (\d+) steps with (\d+) atoms", res.stdout)
@@ -285,17 +285,20 @@ def run_reference_ttm(cells, world, steps, nproc, nrb, substeps, binary=None, en
 
 
 IMD_CUDA_TTM = os.path.join(ROOT, "integration", "_bin", "imd_mpi_eam_ttm_tmm_nbl_cuda")
+IMD_CUDA_TTM_NRB = os.path.join(ROOT, "integration", "_bin", "imd_mpi_eam_ttm_tmm_nrb_nbl_cuda")
 
 
-def run_imd_cuda_binary(cells, steps, substeps):
+def run_imd_cuda_binary(cells, steps, substeps, world=1, nrb=False):
     """IMD ITSELF with the CUDA hot path (integration/imd_cuda.c: the reference's own host program, parameter parser,
-    generator and main loop, linked against libimdcu.so) on the bench film, one rank on one GPU: the same parameter
-    file the reference arm gets except cpu_dim 1 1 1.  Atoms stay on the device; per step only the global sums come
+    generator and main loop, linked against libimdcu.so) on the bench film, one rank per GPU (cpu_dim world 1 1 over
+    oracle/shmpi, x slabs over NCCL; with the non-reflecting boundary the -DNRB -DREFPOS binary): the same parameter
+    file the reference arm gets except cpu_dim.  Atoms stay on the device; per step only the global sums come
     back.  Timed by IMD's own main-loop timer (MPI_Wtime: wall clock), like the reference arm.  That timer also
     holds what happens ONCE inside the first calc_forces (CUDA context, cell_array packed and uploaded, the count pass
     of the first list build: ~1.2 s, and it varies between runs); the stub reports the duration of that first call
     (IMD_CUDA_TIMING=1) and the rate is the other steps over the rest of the timer."""
-    r = run_reference_ttm(cells, 1, steps, 1, False, substeps, binary=IMD_CUDA_TTM, env_extra={"IMD_CUDA_TIMING": "1"})
+    r = run_reference_ttm(cells, world, steps, world, nrb, substeps, binary=IMD_CUDA_TTM_NRB if nrb else IMD_CUDA_TTM,
+                          env_extra={"IMD_CUDA_TIMING": "1"}, timeout=600)
     if not r:
         return None
     m = re.search(r"first calc_forces ([0-9.eE+-]+) s; per step calc_forces ([0-9.eE+-]+) ms, calc_ttm ([0-9.eE+-]+) ms, "
@@ -306,11 +309,13 @@ def run_imd_cuda_binary(cells, steps, substeps):
     rest, nrest = r["main_loop_s"] - first, r["steps"] - 1
     return {"value": r["natoms"] * nrest / rest, "steps": nrest, "ms_per_step": 1e3 * rest / nrest, "first_call_s": first,
             "ms_per_step_in_library": in_lib, "binary": r["binary"],
-            "sample": ("integration/_bin/%s (IMD's own host + libimdcu.so), 1 rank on 1 GPU, the bench film, %d steps: "
+            "sample": ("integration/_bin/%s (IMD's own host + libimdcu.so), %d rank(s) on %d GPU(s)%s, the bench film "
+                       "(%d atoms; the host's equal-width x slabs), %d steps: "
                        "IMD's main-loop timer %.3f s, of which the first calc_forces %.3f s (CUDA context, cell_array "
                        "packed and uploaded, first list build; not part of the rate); the other %d steps %.3f ms each, "
-                       "%.3f ms of that inside libimdcu.so" % (r["binary"], r["steps"], r["main_loop_s"], first, nrest,
-                                                                1e3 * rest / nrest, in_lib))}
+                       "%.3f ms of that inside libimdcu.so on rank 0"
+                       % (r["binary"], world, world, ", non-reflecting rear boundary" if nrb else "", r["natoms"], r["steps"],
+                          r["main_loop_s"], first, nrest, 1e3 * rest / nrest, in_lib))}
 
 
 def bench_ttm_params(gx, substeps, tmm):
@@ -725,10 +730,10 @@ def our_arm(args, rank, local_rank, world):
     imd.close()
     if rank == 0:
         # second end-to-end figure: the drop-in binary itself (the number a user of the reference sees)
-        if world == 1 and args.ttm and not args.nrb and not args.tmm and not args.no_cpu_baseline and args.imd_binary_steps > 0:
+        if args.ttm and not args.tmm and not args.no_cpu_baseline and args.imd_binary_steps > 0:
             try:
                 torch.cuda.synchronize()
-                rb = run_imd_cuda_binary(args.cells, args.imd_binary_steps, args.ttm_substeps)
+                rb = run_imd_cuda_binary(args.cells, args.imd_binary_steps, args.ttm_substeps, world, bool(args.nrb))
                 if rb:
                     line["e2e_imd_binary"] = {"value": rb["value"], "unit": UNIT, "ms_per_step": rb["ms_per_step"],
                                               "ms_per_step_in_library": rb["ms_per_step_in_library"],
