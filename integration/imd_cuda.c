@@ -8,12 +8,13 @@
  *     imd_integrate.c    move_atoms_nve (:35-561), move_atoms_ttm (:581-811)   [the other ensembles stay]
  *     imd_ttm.c          init_ttm (:955), calc_ttm (:75), ttm_writeout (:1683), ttm_read (:1983)
  *     imd_tmm.c          tmm_init (:98)                       [do_tmm runs inside the device lattice kernel]
+ *     imd_nrb.c          nrb_forces (:792-1129) and its exchanges    [init_nrb, nrb_writerestart stay; -DNRB builds]
  *
  * behind the reference's own names and call sites: calc_forces(steps) imd_main_3d.c:406, calc_ttm() :534,
  * move_atoms() :564 (function pointer set in imd_param.c:382,439), check_nblist() :812, init_ttm / tmm_init
  * imd.c:237,245, ttm_writeout imd_main_3d.c:735.  Make-target spelling: the reference selects sources by
  * substrings of the target name (Makefile:141-291,425-460); this is the substring "cuda"
- * (imd_eam_nve_nbl_cuda, imd_mpi_eam_ttm_tmm_nbl_cuda), see integration/Makefile and INTEGRATION.md.
+ * (imd_eam_nve_nbl_cuda, imd_mpi_eam_ttm_tmm_nbl_cuda, imd_mpi_eam_ttm_tmm_nrb_nbl_cuda), see integration/Makefile and INTEGRATION.md.
  *
  * Data flow: atoms live on the device from the first calc_forces on.  cell_array (types.h:188-349) is
  * refilled by imdcu_sync_to_host() before every writer (write_config, write_config_select, write_distrib,
