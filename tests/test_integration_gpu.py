@@ -101,6 +101,45 @@ def test_cuda_binary_eng_equals_reference(tmp_path):
     assert err_drift < 1e-9 * abs(eta[0])
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["4point", "spline"])
+def test_cuda_binary_other_interpolation_modes_equal_reference(tmp_path, mode):
+    """The reference's compile-time FOURPOINT / SPLINE table access (make-target substrings, potaccess.h:365-457,
+    503-582) in the drop-in: imd_eam_nve_nbl_<mode>_cuda hands the mode (and, for the spline, the second-derivative
+    tables read_pot_table built, pot_table_t.table2) to the library; .eng against the reference built the same way."""
+    ref = os.path.join(ROOT, "oracle", "_ref", "imd_ref_eam_nve_nbl_" + mode)
+    cuda = os.path.join(ROOT, "integration", "_bin", "imd_eam_nve_nbl_%s_cuda" % mode)
+    if not (os.path.exists(ref) and os.path.exists(cuda)):
+        pytest.skip("the %s builds are missing (needs the reference sources)" % mode)
+    steps = 40
+    wa, wb = str(tmp_path / "ref"), str(tmp_path / "cuda")
+    for w in (wa, wb):
+        os.makedirs(w)
+        write_inputs(w, steps)
+    ra, rb = run(ref, wa), run(cuda, wb)
+    assert ra.returncode == 0, ra.stdout[-3000:]
+    assert rb.returncode == 0, rb.stdout[-3000:]
+    ea, eb = eng_of(wa), eng_of(wb)
+    assert ea.shape == eb.shape and ea.shape[0] >= steps
+    err_pot = np.abs(ea[:, 1] - eb[:, 1]).max() / np.abs(ea[:, 1]).max()
+    err_kin = np.abs(ea[:, 2] - eb[:, 2]).max() / np.abs(ea[:, 2]).max()
+    e3 = eng_of_3point(tmp_path, steps)
+    differs = np.abs(ea[:, 1] - e3[:, 1]).max() / np.abs(ea[:, 1]).max()
+    print("imd_eam_nve_nbl_%s_cuda vs the reference built with the same mode: Epot rel %.2e, T rel %.2e "
+          "(the 3-point reference differs by %.1e)" % (mode, err_pot, err_kin, differs))
+    assert err_pot < 1e-11 and err_kin < 1e-13                      # observed 7e-13 / 3e-13 and 2e-15
+    assert differs > 100 * max(err_pot, 1e-13)                     # the mode matters: not the 3-point path by accident
+
+
+def eng_of_3point(tmp_path, steps):
+    w = str(tmp_path / "ref3")
+    os.makedirs(w)
+    write_inputs(w, steps)
+    r = run(REF_BIN, w)
+    assert r.returncode == 0, r.stdout[-3000:]
+    return eng_of(w)
+
+
 @needs_bins
 @pytest.mark.gpu
 def test_chkpt_written_by_cuda_build_restarts_in_reference(tmp_path):
