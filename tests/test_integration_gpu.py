@@ -131,6 +131,43 @@ def test_cuda_binary_other_interpolation_modes_equal_reference(tmp_path, mode):
     assert differs > 100 * max(err_pot, 1e-13)                     # the mode matters: not the 3-point path by accident
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["3point", "4point", "spline"])
+def test_cuda_binary_two_species_equals_reference(tmp_path, mode):
+    """ntypes = 2 through the files: Ni3Al on the L1_2 structure (IMD's own generator, coordname _l12),
+    4/4/2-column potential files with every column on its own r^2 grid and asymmetric rho columns; free x surfaces.
+    The drop-in hands pot_table_t with its columns to the library as the reference's readers left it."""
+    suffix = "" if mode == "3point" else "_" + mode
+    ref = os.path.join(ROOT, "oracle", "_ref", "imd_ref_eam_nve_nbl" + suffix)
+    cuda = os.path.join(ROOT, "integration", "_bin", "imd_eam_nve_nbl%s_cuda" % suffix)
+    if not (os.path.exists(ref) and os.path.exists(cuda)):
+        pytest.skip("the %s builds are missing (needs the reference sources)" % mode)
+    steps = 30
+    spec = synth.NI3AL
+    wa, wb = str(tmp_path / "ref"), str(tmp_path / "cuda")
+    for w in (wa, wb):
+        os.makedirs(os.path.join(w, "out"))
+        synth.make_eam_tables_binary(spec, w)
+        synth.write_param_file(os.path.join(w, "run.param"), spec, (7, 5, 6), steps, "out/run", pbc=(0, 1, 1),
+                               starttemp=0.08, nbl_margin=0.4, eng_int=1, coordname="_l12", masses=spec.masses,
+                               extra="checkpt_int %d\n" % steps)
+    ra, rb = run(ref, wa), run(cuda, wb)
+    assert ra.returncode == 0, ra.stdout[-3000:]
+    assert rb.returncode == 0, rb.stdout[-3000:]
+    ea, eb = eng_of(wa), eng_of(wb)
+    assert ea.shape == eb.shape and ea.shape[0] >= steps
+    err_pot = np.abs(ea[:, 1] - eb[:, 1]).max() / np.abs(ea[:, 1]).max()
+    err_kin = np.abs(ea[:, 2] - eb[:, 2]).max() / np.abs(ea[:, 2]).max()
+    ca, cb = read_chkpt(chkpt_path(wa, 1)), read_chkpt(chkpt_path(wb, 1))
+    assert ca.shape == cb.shape and np.array_equal(ca[:, :3], cb[:, :3])
+    assert set(np.unique(ca[:, 1])) == {0.0, 1.0}                   # both species present
+    scale = np.abs(ca[:, 3:]).max(axis=0) + 1e-300
+    err_chk = (np.abs(ca[:, 3:] - cb[:, 3:]).max(axis=0) / scale).max()
+    print("two species, %s: Epot rel %.2e, T rel %.2e, .chkpt of step %d worst column %.2e"
+          % (mode, err_pot, err_kin, steps, err_chk))
+    assert err_pot < 1e-12 and err_kin < 1e-13 and err_chk < 1e-11   # observed 5e-14, 4e-15, 4e-13
+
+
 def eng_of_3point(tmp_path, steps):
     w = str(tmp_path / "ref3")
     os.makedirs(w)
@@ -399,6 +436,58 @@ def test_ttm_cuda_binary_equals_reference_ttm_build(tmp_path):
     assert "distributions (28 bins) are summed on the device" in rb.stdout
     wd = compare_text_dists(runs["ref"], runs["cuda"], (0, 1, 2), 28)
     print(".vxavg / .dens files (ASCII formats) vs the reference's: worst relative difference %.2e" % wd)
+
+
+@needs_mpi_bins
+@pytest.mark.gpu
+def test_ttm_cuda_binary_hot_film_with_pdecay_equals_reference(tmp_path):
+    """Hot lattice + strong pulse + the -DPDECAY rear absorber (xipdecay, ramp_start, ramp_end: imd_integrate.c:
+    690-705 in move_atoms_ttm) through the files: atoms cross FD slabs (advection fluxes), cells deactivate.  The
+    film of the library-level golden ttm_al_48x5x5_p2_hot; tolerances are those of that golden's comparison."""
+    from imd_b200 import synth as sy
+    steps, ttm_int = 30, 15
+    tp = sy.TtmParams(ttmdimx=12, fd_n_timesteps=30, I0=4.0e16, fd_min_atoms=20, vlatbuffer=1)
+    work = str(tmp_path)
+    sy.make_eam_tables(sy.AL, work)
+    sy.write_eos_files(sy.make_eos_tables(), work)
+    pos, box = sy.fcc_lattice((48, 5, 5), sy.AL.a)
+    sy.write_config_file(os.path.join(work, "start.conf"), pos, sy.maxwell_momenta(pos.shape[0], sy.AL.mass, 0.12),
+                         sy.AL.mass, box)
+    runs = {}
+    for name, ranks in (("ref", 2), ("cuda", 1)):
+        w = os.path.join(work, name)
+        os.makedirs(os.path.join(w, "out"))
+        ex = (tp.param_text() + "box_from_header 1\nshiftx_front 25\nshiftx_rear 15\nttm_int %d\n"
+              "xipdecay 0.5\nramp_start 180.0\nramp_end 200.0\n" % ttm_int)
+        sy.write_param_file(os.path.join(w, "run.param"), sy.AL, (48, 5, 5), steps, "out/run", potdir="..",
+                            pbc=(0, 1, 1), starttemp=0.12, nbl_margin=0.4, eng_int=1, extra=ex, ensemble="ttm",
+                            cpu_dim=(ranks, 1, 1), coordname="../start.conf")
+        runs[name] = w
+    src = {"IMD_SRC_MU": "%.17g" % tp.src_mu, "IMD_SRC_ABS": "%.17g" % tp.src_abs}
+    ra = run_mpi(REF_MPI_TTM, runs["ref"], 2, src)
+    rb = run_mpi(CUDA_MPI_TTM, runs["cuda"], 1, dict(src, IMDCU_TTM_REF_RANKS="2"))
+    assert ra.returncode == 0, ra.stdout[-3000:]
+    assert rb.returncode == 0, rb.stdout[-3000:]
+    ea, eb = eng_of(runs["ref"]), eng_of(runs["cuda"])
+    assert ea.shape == eb.shape and ea.shape[1] >= 6
+    err_pot = np.abs(ea[:, 1] - eb[:, 1]).max() / np.abs(ea[:, 1]).max()
+    err_kin = np.abs(ea[:, 2] - eb[:, 2]).max() / np.abs(ea[:, 2]).max()
+    err_el = (np.abs(ea[:, 5] - eb[:, 5]) / np.abs(ea[:, 5])).max()
+    worst = 0.0
+    for n in range(1, steps // ttm_int + 1):
+        ta = read_ttm(os.path.join(runs["ref"], "out", "run.%d.ttm" % n))
+        tb = read_ttm(os.path.join(runs["cuda"], "out", "run.%d.ttm" % n))
+        assert ta.shape == tb.shape, (n, ta.shape, tb.shape)
+        assert np.array_equal(ta[:, [0, 1, 2, 3, 16]], tb[:, [0, 1, 2, 3, 16]]), n
+        num = np.abs(ta - tb)
+        rel = np.where(np.abs(ta) > 1e-12, num / np.maximum(np.abs(ta), 1e-30), num)
+        for col in (10, 11, 12):
+            rel[:, col] = num[:, col] / max(np.abs(ta[:, col]).max(), 1e-30)
+        worst = max(worst, rel.max())
+    print("hot film with the rear absorber through the files: Epot rel %.2e, T rel %.2e, E_el rel %.2e, .ttm worst %.2e"
+          % (err_pot, err_kin, err_el, worst))
+    # observed 2e-13, 4e-12, 1.4e-7 (E_el is printed with seven digits) and equal .ttm files
+    assert err_pot < 1e-11 and err_kin < 1e-10 and err_el < 2e-6 and worst < 2e-6
 
 
 REF_MPI_TMM = os.path.join(ROOT, "oracle", "_ref", "imd_ref_mpi_eam_ttm_tmm")
