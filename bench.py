@@ -80,16 +80,52 @@ def measured_peak_gbs():
 
 # ----------------------------------------------------------------------------- clocks
 
+def nvml_handle(local_rank):
+    """NVML handle of the GPU torch calls `local_rank` (by UUID: CUDA_VISIBLE_DEVICES may renumber), or None."""
+    try:
+        import pynvml
+        import torch
+        pynvml.nvmlInit()
+        uuid = str(torch.cuda.get_device_properties(local_rank).uuid)
+        for cand in (uuid, "GPU-" + uuid):
+            try:
+                return pynvml.nvmlDeviceGetHandleByUUID(cand.encode() if hasattr(cand, "encode") else cand)
+            except Exception:
+                continue
+        return pynvml.nvmlDeviceGetHandleByIndex(local_rank)
+    except Exception:
+        return None
+
+
 class ClockSampler:
-    """Polls nvidia-smi (one-shot queries from a thread) while the GPU is under load."""
+    """SM clock and throttle reasons while the GPU is under load: NVML queries from a thread every 10 ms (the timed
+    region of the default run lasts ~140 ms); one-shot nvidia-smi queries every 0.2 s where NVML cannot be loaded."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NVML_REASONS = ((0x8, "hw_slowdown"), (0x40, "hw_thermal_slowdown"), (0x20, "sw_thermal_slowdown"), (0x4, "sw_power_cap"))
 
     def __init__(self, gpu_index, period=0.2):
         self.idx, self.period = gpu_index, period
         self.lines, self.stop_flag, self.t = [], threading.Event(), None
+        self.h = nvml_handle(gpu_index)
+
+    def _poll_nvml(self):
+        import pynvml
+        mx = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        while not self.stop_flag.is_set():
+            sm = pynvml.nvmlDeviceGetClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            bits = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+            f = ["Active" if bits & b else "Not Active" for b, _ in self.NVML_REASONS]
+            self.lines.append("%d, %d, %s" % (sm, mx, ", ".join(f)))
+            self.stop_flag.wait(0.01)
 
     def _poll(self):
+        if self.h is not None:
+            try:
+                self._poll_nvml()
+                return
+            except Exception:
+                pass                                 # fall back to nvidia-smi below
         while not self.stop_flag.is_set():
             try:
                 out = subprocess.run(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
@@ -298,7 +334,7 @@ def run_imd_cuda_binary(cells, steps, substeps, world=1, nrb=False):
     of the first list build: ~1.2 s, and it varies between runs); the stub reports the duration of that first call
     (IMD_CUDA_TIMING=1) and the rate is the other steps over the rest of the timer."""
     r = run_reference_ttm(cells, world, steps, world, nrb, substeps, binary=IMD_CUDA_TTM_NRB if nrb else IMD_CUDA_TTM,
-                          env_extra={"IMD_CUDA_TIMING": "1"}, timeout=600)
+                          env_extra={"IMD_CUDA_TIMING": "1"}, timeout=300)
     if not r:
         return None
     m = re.search(r"first calc_forces ([0-9.eE+-]+) s; per step calc_forces ([0-9.eE+-]+) ms, calc_ttm ([0-9.eE+-]+) ms, "
@@ -502,18 +538,9 @@ def bind_to_gpu_cpus(local_rank):
     path only: eight processes moving 384 MB per step each should not cross sockets.  Never fatal."""
     try:
         import pynvml
-        import torch
-        pynvml.nvmlInit()
-        uuid = str(torch.cuda.get_device_properties(local_rank).uuid)
-        h = None
-        for cand in (uuid, "GPU-" + uuid):
-            try:
-                h = pynvml.nvmlDeviceGetHandleByUUID(cand.encode() if hasattr(cand, "encode") else cand)
-                break
-            except Exception:
-                continue
+        h = nvml_handle(local_rank)
         if h is None:
-            h = pynvml.nvmlDeviceGetHandleByIndex(local_rank)
+            return "not bound (NVML unavailable)"
         before = len(os.sched_getaffinity(0))
         pynvml.nvmlDeviceSetCpuAffinity(h)
         cpus = sorted(os.sched_getaffinity(0))
