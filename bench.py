@@ -19,7 +19,7 @@ e2e   : the same step driven through the C ABI with HOST buffers: every step upl
 roofline : dominant kernel (k_eam_pass1_rep4), algorithmic bytes (64 + 4*N_h per atom,
         SURVEY.md 8d) / its mean launch time measured live with CUDA events.
 cpu_baseline : the UNMODIFIED reference (oracle/_ref, author's flags), its own MPI build run
-        over oracle/shmpi with one rank per host core (cpu_dim P 1 1), a bounded sample of the
+        over shmpi/ with one rank per host core (cpu_dim P 1 1), a bounded sample of the
         same workload; falls back to P concurrent serial runs if the MPI run fails.
 N > 1  : weak scaling -- every GPU owns an x slab of --cells cubic cells (cpu_dim = N 1 1), halo
         planes over NCCL; --ttm adds calc_ttm + move_atoms_ttm (BASELINE.json configs[2]).
@@ -206,7 +206,7 @@ def run_reference_sample(box_cells, steps, nproc, use_fast=True):
 
 def run_reference_mpi(global_cells, steps, cpu_dim):
     """The reference's own MPI build (cpu_dim = x slabs like the GPU decomposition, or IMD's 3-D process grid) over
-    oracle/shmpi; throughput from the reference's own main-loop timer (imd.c:387-392, MPI_Wtime)."""
+    shmpi/; throughput from the reference's own main-loop timer (imd.c:387-392, MPI_Wtime)."""
     from imd_b200 import synth
     if not os.path.exists(REF_MPI):
         return None
@@ -273,7 +273,7 @@ def film_geometry(cells, world):
 
 
 def run_reference_ttm(cells, world, steps, nproc, nrb, substeps, binary=None, env_extra=None, timeout=1500):
-    """The reference's own EAM + TTM(1-D) MPI build (imd_ttm.c:75-156 per step, move_atoms_ttm) over oracle/shmpi on
+    """The reference's own EAM + TTM(1-D) MPI build (imd_ttm.c:75-156 per step, move_atoms_ttm) over shmpi/ on
     the bench film: ensemble ttm, pbc 0 1 1, shiftx_front/rear vacuum, the same FD lattice, sub-step count and pulse
     as the GPU arm (analytic Beer-Lambert source on both sides, ref_hooks_ttm.c).  TTM1D talks to ranks myid +- 1
     (imd_ttm.c:884-939, 3290-3333): cpu_dim must be P 1 1, P >= 2."""
@@ -327,7 +327,7 @@ IMD_CUDA_TTM_NRB = os.path.join(ROOT, "integration", "_bin", "imd_mpi_eam_ttm_tm
 def run_imd_cuda_binary(cells, steps, substeps, world=1, nrb=False):
     """IMD ITSELF with the CUDA hot path (integration/imd_cuda.c: the reference's own host program, parameter parser,
     generator and main loop, linked against libimdcu.so) on the bench film, one rank per GPU (cpu_dim world 1 1 over
-    oracle/shmpi, x slabs over NCCL; with the non-reflecting boundary the -DNRB -DREFPOS binary): the same parameter
+    shmpi/, x slabs over NCCL; with the non-reflecting boundary the -DNRB -DREFPOS binary): the same parameter
     file the reference arm gets except cpu_dim.  Atoms stay on the device; per step only the global sums come
     back.  Timed by IMD's own main-loop timer (MPI_Wtime: wall clock), like the reference arm.  That timer also
     holds what happens ONCE inside the first calc_forces (CUDA context, cell_array packed and uploaded, the count pass
@@ -373,7 +373,7 @@ def reference_sample(args, world, steps):
         r = run_reference_ttm(cells, world, steps, nproc, args.nrb, args.ttm_substeps)
         if r:
             r["sample"] = ("the reference's own EAM+TTM MPI build (%s: -DMPI -DNBL -DEAM2 -DTTM -DTTM1D -DTMM -DPDECAY%s, author's "
-                           "flags -O3 -mavx2 -ffast-math) over oracle/shmpi, %d ranks (cpu_dim %d 1 1, the only layout TTM1D "
+                           "flags -O3 -mavx2 -ffast-math) over shmpi/, %d ranks (cpu_dim %d 1 1, the only layout TTM1D "
                            "supports) on %d host cores, Al film %dx%dx%d cells = %d atoms, ttmdimx %d, fd_n_timesteps %d, "
                            "%d steps (main loop %.1f s, wall %.1f s)"
                            % (r["binary"], " -DNRB -DREFPOS" if args.nrb else "", nproc, nproc, cores, ncx, cells[1], cells[2],
@@ -397,7 +397,7 @@ def reference_sample(args, world, steps):
                     best = r
         if best:
             cd = best["cpu_dim"]
-            best["sample"] = ("the reference's MPI build (%s, author's flags) over oracle/shmpi on %d host cores, Al fcc %dx%dx%d "
+            best["sample"] = ("the reference's MPI build (%s, author's flags) over shmpi/ on %d host cores, Al fcc %dx%dx%d "
                               "cells = %d atoms, %d NVE steps, 300 K; tried %s; reported cpu_dim %d %d %d = %d ranks "
                               "(main loop %.1f s)" % (best["binary"], cores, gx, cells[1], cells[2], best["natoms"], best["steps"],
                                                       "; ".join(tried), cd[0], cd[1], cd[2], best["nproc"], best["main_loop_s"]))

@@ -1,7 +1,7 @@
 /* oracle/ref_hooks_ttm.c -- TEST INFRASTRUCTURE, not product code.
  *
  * Link-time hooks for the UNMODIFIED reference's TTM build (-DMPI -DTTM -DTTM1D -DTMM over
- * oracle/shmpi).  Linked with  -Wl,--wrap=tmm_init,--wrap=do_tmm,--wrap=calc_ttm .
+ * shmpi/).  Linked with  -Wl,--wrap=tmm_init,--wrap=do_tmm,--wrap=calc_ttm .
  *
  *  __wrap_tmm_init / __wrap_do_tmm : the reference's Helmholtz/transfer-matrix laser source
  *      (imd_tmm.c:98-190, 193-445) needs the data files alu_eps_bb.dat and K12.dat, which

@@ -9,7 +9,7 @@
  * as plain copies.  P is a parameter (num_cpus of the reference run being matched).
  *
  * Parity status: PINNED against dumps of the unmodified reference built with -DMPI over
- * oracle/shmpi (oracle/_ref/imd_ref_mpi_eam_ttm; tests/golden/ttm_*.npz,
+ * shmpi/ (oracle/_ref/imd_ref_mpi_eam_ttm; tests/golden/ttm_*.npz,
  * tests/test_ttm_oracle_vs_reference.py).  Two substitutions are shared by both sides and
  * documented in DESIGN.md: the laser source is the analytic Beer-Lambert term of
  * oracle/ref_hooks_ttm.c (the reference's transfer-matrix solver needs data files that are

@@ -1,4 +1,4 @@
-/* oracle/shmpi/mpi.h -- TEST INFRASTRUCTURE ONLY (never part of the product library).
+/* shmpi/mpi.h -- a stand-in for an MPI library in an image that has none (never part of libimdcu.so).
  *
  * "shmpi": a small single-node MPI subset over fork() + shared memory, written from
  * scratch so that the UNMODIFIED reference (fmqeisfeld/IMD) can be built with -DMPI in an

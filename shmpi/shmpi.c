@@ -1,4 +1,4 @@
-/* oracle/shmpi/shmpi.c -- TEST INFRASTRUCTURE ONLY: fork + shared-memory MPI subset.
+/* shmpi/shmpi.c -- a stand-in for an MPI library in an image that has none: fork + shared-memory MPI subset.
  * See mpi.h in this directory for scope and semantics.  Written from scratch; it contains
  * nothing of the reference. */
 #define _GNU_SOURCE

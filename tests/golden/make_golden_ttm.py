@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Generate the TTM golden fixtures (tests/golden/ttm_*.npz) by RUNNING THE UNMODIFIED
-REFERENCE's MPI + TTM build over oracle/shmpi.
+REFERENCE's MPI + TTM build over shmpi/.
 
 Needs oracle/_ref/imd_ref_mpi_eam_ttm and oracle/_ref/nn_probe (``make -C oracle ref``).
 The binary is the reference compiled with -DMPI -DNBL -DEAM2 -DTTM -DTTM1D -DTMM -DPDECAY,

@@ -39,10 +39,12 @@ def test_no_cpu_fallback():
 
 
 def test_product_does_not_touch_oracle():
-    """The product package must never import, link or call anything under oracle/."""
-    pkg = os.path.join(ROOT, "imd_b200")
-    for dirpath, _, files in os.walk(pkg):
-        for f in files:
-            if f.endswith((".py", ".cu", ".cuh", ".h", "Makefile")):
-                src = open(os.path.join(dirpath, f), errors="ignore").read()
-                assert "oracle" not in src.replace("oracle/_ref", ""), os.path.join(dirpath, f)
+    """The product -- the library package, the C ABI header and the IMD-side drop-in with its build recipe -- must
+    never import, link or call anything under oracle/ (comments may name oracle/_ref as the sibling output directory)."""
+    for top in ("imd_b200", "integration", "include", "shmpi"):
+        for dirpath, dirs, files in os.walk(os.path.join(ROOT, top)):
+            dirs[:] = [d for d in dirs if d not in ("_bin", "__pycache__")]
+            for f in files:
+                if f.endswith((".py", ".cu", ".cuh", ".h", ".c", "Makefile")):
+                    src = open(os.path.join(dirpath, f), errors="ignore").read()
+                    assert "oracle" not in src.replace("oracle/_ref", ""), os.path.join(dirpath, f)

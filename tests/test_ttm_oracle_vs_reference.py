@@ -1,5 +1,5 @@
 """Pins the CPU restatement of the 1-D TTM (oracle/ttm_oracle.c) against dumps of the
-UNMODIFIED reference's -DMPI -DTTM build run over oracle/shmpi with 2 and 4 ranks
+UNMODIFIED reference's -DMPI -DTTM build run over shmpi/ with 2 and 4 ranks
 (tests/golden/ttm_*.npz, made by tests/golden/make_golden_ttm.py).  CPU only."""
 import numpy as np
 import pytest
